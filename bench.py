@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""Benchmark of the per-candidate train+evaluate path (contract: see the task statement / DESIGN.md).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload nas1|lenet5|wide]
+
+A "step" is one optimisation step (forward, loss, backward, Adam) over one batch of 128
+synthetic images of the candidate named by BASELINE.json configs[1]: product #4 of the
+seed-0 sample of main_1block_nas.xml (5 cells, 1 block) on CIFAR-shaped 32x32x3 data.
+`value` is device-timed whole-job train images/s with the dataset resident in HBM; `e2e` is
+the same step driven through the public API (`Network.train_on_batch`) from pinned HOST
+buffers, H2D and D2H inside the timed region.  With N > 1 every rank trains its own copy of
+the candidate (population sharding: no data-path collective), weak scaling.
+`--impl reference` times the CPU port of the same step (oracle/torch_cpu.py, all host
+threads): the reference's own TF 1.12 / Keras 2.2.4 cannot be installed on this box.
+"""
+import argparse
+import contextlib
+import io
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import featurenet_b200  # noqa: E402
+
+featurenet_b200.install_compat()
+
+BATCH = 128
+METRIC = "per-candidate train images/sec (candidates trained+evaluated/hour reported beside it)"
+WORKLOADS = {
+    # name: (product file or template, product index, dataset, description)
+    "nas1": ("featurenet_b200/data/main_1block_nas_5cells_seed0.pdt", 4, "cifar",
+             "main_1block_nas.xml (5 cells, 1 block) seed-0 sample, product #4, CIFAR-shape 32x32x3, batch 128"),
+    "lenet5": ("lenet5", None, "mnist", "lenet5 template, MNIST-shape 28x28x1, batch 128"),
+    "wide": ("tests/golden/nas_5_5_10_seed0.pdt", 9, "cifar",
+             "nas_5_5_10.xml seed-0 sample, product #9 (98.6 MFLOP/img fwd), CIFAR-shape, batch 128"),
+}
+
+
+def quiet():
+    return contextlib.redirect_stdout(io.StringIO())
+
+
+def build_candidate(workload):
+    from model.keras_model import KerasFeatureModel
+    from products_tree import ProductSet
+    from featurenet_b200 import synth
+    source, index, dataset, _ = WORKLOADS[workload]
+    with quiet():
+        if index is None:
+            model = KerasFeatureModel.parse_feature_model(source)
+        else:
+            product, original = ProductSet(os.path.join(ROOT, source)).format_products()[index]
+            model = KerasFeatureModel.parse_feature_model(product, product_features=original)
+        net = model.build(synth.SHAPES[dataset], synth.CLASSES[dataset])
+    if not net:
+        raise SystemExit("benchmark candidate did not build")
+    return model, net, dataset
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        with open(path) as handle:
+            p = json.load(handle)
+        return {"hbm_gbs": p["hbm_gbs"], "tflops": p["bf16_tflops"], "source": "measured (MEASURED_PEAKS.json, burst)"}
+    return {"hbm_gbs": 6650.0, "tflops": 1590.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) == 7:
+                self.rows.append(parts)
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        self.proc.wait()          # our own child, by handle -- never by pattern
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def cpu_port_rate(net, dataset, seconds, steps=None, threads=None):
+    """Train images/s of the CPU port (oracle/torch_cpu.py) on batches of the same workload."""
+    import torch
+    from oracle.torch_cpu import TorchCpuNet
+    from featurenet_b200 import synth
+    from tests.util import init_weights
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    rng = np.random.default_rng(1236)
+    port = TorchCpuNet(net.describe(), init_weights(net, rng), threads=threads)
+    shape, classes = synth.SHAPES[dataset], synth.CLASSES[dataset]
+    x = rng.random((BATCH,) + shape).astype(np.float32)
+    t = np.eye(classes, dtype=np.float32)[rng.integers(0, classes, BATCH)]
+    for _ in range(2):
+        port.train_step(x, t)
+    done, t0 = 0, time.perf_counter()
+    while True:
+        port.train_step(x, t)
+        done += 1
+        elapsed = time.perf_counter() - t0
+        if (steps is not None and done >= steps) or (steps is None and elapsed >= seconds):
+            break
+    return done * BATCH / elapsed, done, elapsed, threads
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    _, net, dataset = build_candidate(args.workload)
+    port_steps = args.steps
+    t0 = time.perf_counter()
+    rate, done, elapsed, threads = cpu_port_rate(net, dataset, seconds=0, steps=args.warmup + port_steps)
+    rate, done, elapsed, threads = cpu_port_rate(net, dataset, seconds=0, steps=port_steps)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / done, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload][3], "batch": BATCH},
+        "cpu_baseline": {"value": rate, "unit": "images/s", "cores": threads, "kind": "port",
+                         "sample": "%d train steps of batch %d through oracle/torch_cpu.py (TF1.12/Keras2.2.4 "
+                                   "is not installable here)" % (done, BATCH)},
+        "e2e": {"value": rate, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "wall_s": time.perf_counter() - t0,
+    }
+    print(json.dumps(line))
+
+
+def measure_workload(workload, args, torch, dist, world, device_index, full=True):
+    """Device-timed steps (+ optionally e2e, per-kernel profile, whole-candidate cycle) for one workload."""
+    from featurenet_b200 import synth
+    from featurenet_b200.optimizers import Adam
+    model, net, dataset = build_candidate(workload)
+    with quiet():
+        (x_train, y_train), (x_test, y_test) = synth.load(dataset)
+    n = x_train.shape[0]
+    net.compile(loss="categorical_crossentropy", metrics=["accuracy"], optimizer=Adam(lr=1e-3))
+    eng = net._need_engine()
+    eng._ensure_capacity(BATCH)
+    eng._set_data("train", x_train, y_train)
+    perm = torch.from_numpy(np.random.default_rng(1237).permutation(n).astype(np.int32))
+    with torch.cuda.stream(eng.stream):
+        eng.data["train"][2].copy_(perm)
+    eng._sync_lr()
+    steps_per_epoch = n // BATCH
+
+    def run(k):
+        for i in range(k):
+            if i % steps_per_epoch == 0:
+                eng._zero_metrics(eng.state)            # epoch boundary: cursor back to 0
+            eng._step("train", BATCH)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    run(max(args.warmup, 3))
+    barrier()
+    sampler = ClockSampler(device_index)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(eng.stream)
+    run(args.steps)
+    e1.record(eng.stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    out = {"ms": ms, "value": world * args.steps * BATCH / (ms / 1e3), "clocks": clocks,
+           "launch_calls_per_step": eng.launches_per_step[("train", BATCH)],
+           "params": net.count_params(), "layers": len(net.layers),
+           "train_mflop_per_image": 3 * net.train_flops_per_image() / 1e6}
+    if not full:
+        net.release()
+        return out, net
+
+    # ---- end to end through the public API with host buffers
+    k = args.steps
+    xs = torch.from_numpy(x_train[: BATCH * 8]).pin_memory()
+    ys = torch.from_numpy(y_train[: BATCH * 8]).pin_memory()
+    for i in range(3):
+        net_loss = eng.train_on_batch(xs[:BATCH], ys[:BATCH])
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(k):
+        lo = (i % 8) * BATCH
+        net_loss = eng.train_on_batch(xs[lo: lo + BATCH], ys[lo: lo + BATCH])
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    out["e2e"] = {"value": world * k * BATCH / e2e_s, "unit": "images/s",
+                  "h2d_bytes_per_step": int(BATCH * (np.prod(x_train.shape[1:]) + y_train.shape[1]) * 4),
+                  "d2h_bytes_per_step": 16, "last_loss": net_loss[0]}
+
+    # ---- per-kernel profile (CUDA events around every launch on the launching stream)
+    table = eng.profile_steps("train", BATCH, steps=min(args.steps, 50))
+    out["profile"] = table
+
+    # ---- one whole candidate: build + compile + 1 epoch + validation + evaluate (rank-local)
+    from tensorflow_generator import TensorflowGenerator
+    TensorflowGenerator.dataset = dataset
+    TensorflowGenerator.X_train, TensorflowGenerator.Y_train = x_train, y_train
+    TensorflowGenerator.X_test, TensorflowGenerator.Y_test = x_test, y_test
+    TensorflowGenerator.input_shape = synth.SHAPES[dataset]
+    source, index, _, _ = WORKLOADS[workload]
+    if index is None:
+        product = source
+    else:
+        from products_tree import ProductSet
+        with quiet():
+            product = ProductSet(os.path.join(ROOT, source)).format_products()[index][0]
+    net.release()
+    cycles = []
+    for _ in range(2):                                   # second cycle = steady state (dataset resident)
+        barrier()
+        t0 = time.perf_counter()
+        with quiet():
+            gen = TensorflowGenerator(product, epochs=1, dataset=dataset, data_augmentation=False, batch_size=BATCH)
+        barrier()
+        cycles.append(time.perf_counter() - t0)
+    out["candidate_cycle_s"] = cycles[-1]
+    out["candidate_accuracy"] = float(gen.accuracy)
+    return out, net
+
+
+def roofline_from(table, pk):
+    label = max(table, key=lambda k: table[k]["ms_total"])
+    row = table[label]
+    total_ms = sum(r["ms_total"] for r in table.values())
+    secs = row["ms_total"] / 1e3
+    intensity = row["flops"] / max(row["bytes"], 1)
+    ridge = pk["tflops"] * 1e12 / (pk["hbm_gbs"] * 1e9)
+    if row["flops"] and intensity >= ridge:
+        achieved, peak, unit, bound = row["flops"] / secs / 1e12, pk["tflops"], "TFLOP/s", "tensor"
+    else:
+        achieved, peak, unit, bound = row["bytes"] / secs / 1e9, pk["hbm_gbs"], "GB/s", "hbm"
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.isfile(tpath):
+        with open(tpath) as handle:
+            traffic = json.load(handle).get(label)
+    return {"bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
+            "traffic": traffic, "kernel": label, "launches": row["launches"],
+            "avg_us": 1e3 * row["ms_total"] / row["launches"], "share_of_step": row["ms_total"] / total_ms,
+            "algorithmic_bytes_per_launch": row["bytes"] / row["launches"],
+            "algorithmic_flops_per_launch": row["flops"] / row["launches"], "peak_source": pk["source"],
+            "tflops_achieved": row["flops"] / secs / 1e12}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    t_wall = time.perf_counter()
+    main, net = measure_workload(args.workload, args, torch, dist, world, local, full=True)
+    extra = {}
+    if rank == 0 and world == 1 and not args.quick:
+        for other in ("lenet5", "wide"):
+            if other != args.workload:
+                res, _ = measure_workload(other, args, torch, dist, 1, local, full=False)
+                extra[other] = {"images_per_s": res["value"], "ms_per_step": res["ms"] / args.steps,
+                                "params": res["params"], "train_mflop_per_image": res["train_mflop_per_image"],
+                                "launch_calls_per_step": res["launch_calls_per_step"],
+                                "workload": WORKLOADS[other][3]}
+    if rank == 0:
+        pk = peaks()
+        line = {
+            "metric": METRIC, "value": main["value"], "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": main["ms"] / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload][3], "batch": BATCH, "optimizer": "adam(1e-3)",
+                       "parallelism": "candidate-sharded x%d (no collective)" % world,
+                       "l2": "inputs larger than L2: the 614 MB resident dataset is streamed batch by batch; "
+                             "activations and weights are step-resident by design",
+                       "params": main["params"], "layers": main["layers"],
+                       "train_mflop_per_image": main["train_mflop_per_image"]},
+            "clocks": main["clocks"], "e2e": main["e2e"],
+            "gpu_launches": main["launch_calls_per_step"] * args.steps,
+            "roofline": roofline_from(main["profile"], pk),
+            "candidates_per_hour": world * 3600.0 / main["candidate_cycle_s"],
+            "candidate_cycle": {"seconds": main["candidate_cycle_s"], "accuracy": main["candidate_accuracy"],
+                                "what": "build + compile + 1 epoch (full-size synthetic set) + validation + evaluate"},
+            "profile": {k: {"launches": v["launches"], "ms_total": round(v["ms_total"], 4)}
+                        for k, v in sorted(main["profile"].items(), key=lambda kv: -kv[1]["ms_total"])},
+            "other_workloads": extra,
+        }
+        if world == 1:
+            _, net2, dataset = build_candidate(args.workload)
+            rate, done, elapsed, threads = cpu_port_rate(net2, dataset, seconds=args.cpu_seconds)
+            line["cpu_baseline"] = {"value": rate, "unit": "images/s", "cores": threads, "kind": "port",
+                                    "sample": "%d train steps of batch %d in %.1f s through oracle/torch_cpu.py"
+                                              % (done, BATCH, elapsed)}
+        line["wall_s"] = time.perf_counter() - t_wall
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="nas1", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--quick", action="store_true", help="skip the secondary workloads")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

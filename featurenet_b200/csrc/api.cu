@@ -1,0 +1,151 @@
+// libfnet: error reporting, CUDA-graph helpers, loop-state kernels and batch gathering.
+#include "common.cuh"
+
+namespace fnet {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+// ---------------------------------------------------------------- loop state
+// state[0] t (completed iterations)  state[1] cursor  state[2] lr  state[3] lr_t
+__global__ void step_begin_kernel(int32_t *state, float beta1, float beta2) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        double t = (double)(state[0] + 1);
+        double lr = (double)__int_as_float(state[2]);
+        // Keras Adam: lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t); evaluated once per step
+        // (in double, rounded to fp32) instead of once per parameter tensor
+        double lr_t = lr * sqrt(1.0 - pow((double)beta2, t)) / (1.0 - pow((double)beta1, t));
+        state[3] = __float_as_int((float)lr_t);
+    }
+}
+
+__global__ void step_end_kernel(int32_t *state, int32_t batch) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        state[0] += 1;
+        state[1] += batch;
+    }
+}
+
+__global__ void fill_kernel(int64_t n, float value, float *__restrict__ dst) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) dst[i] = value;
+}
+
+__global__ void u8_to_f32_kernel(int64_t n, const uint8_t *__restrict__ src, float scale, float *__restrict__ dst) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // same rounding as numpy: x.astype(float32) then an fp32 divide by 255 (scale is the divisor)
+    for (; i < n; i += stride) dst[i] = (float)src[i] / scale;
+}
+
+// One CTA per (row, chunk); rows are contiguous so float4 copies are coalesced.
+__global__ void gather_rows_kernel(int32_t batch, int64_t row_elems, const int32_t *__restrict__ perm,
+                                   const int32_t *__restrict__ state, const float *__restrict__ src,
+                                   float *__restrict__ dst) {
+    int32_t cursor = state[1];
+    for (int32_t row = blockIdx.y; row < batch; row += gridDim.y) {
+        int64_t from = (int64_t)perm[cursor + row] * row_elems;
+        int64_t to = (int64_t)row * row_elems;
+        if ((row_elems & 3) == 0) {
+            const float4 *s4 = reinterpret_cast<const float4 *>(src + from);
+            float4 *d4 = reinterpret_cast<float4 *>(dst + to);
+            for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < row_elems / 4;
+                 i += (int64_t)gridDim.x * blockDim.x)
+                d4[i] = __ldg(s4 + i);
+        } else {
+            for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < row_elems;
+                 i += (int64_t)gridDim.x * blockDim.x)
+                dst[to + i] = __ldg(src + from + i);
+        }
+    }
+}
+
+}  // namespace fnet
+
+using namespace fnet;
+
+extern "C" {
+
+int fnet_version(void) { return FNET_VERSION; }
+
+const char *fnet_last_error(void) { return g_error; }
+
+int fnet_step_begin(int32_t *state, float beta1, float beta2, void *stream) {
+    FNET_REQUIRE(state != nullptr, "fnet_step_begin: null state");
+    step_begin_kernel<<<1, 32, 0, as_stream(stream)>>>(state, beta1, beta2);
+    return check_launch("fnet_step_begin");
+}
+
+int fnet_step_end(int32_t *state, int32_t batch, void *stream) {
+    FNET_REQUIRE(state != nullptr, "fnet_step_end: null state");
+    step_end_kernel<<<1, 32, 0, as_stream(stream)>>>(state, batch);
+    return check_launch("fnet_step_end");
+}
+
+int fnet_fill(int64_t n, float value, float *dst, void *stream) {
+    FNET_REQUIRE(n >= 0 && (dst != nullptr || n == 0), "fnet_fill: bad arguments");
+    if (n == 0) return FNET_OK;
+    fill_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(n, value, dst);
+    return check_launch("fnet_fill");
+}
+
+int fnet_u8_to_f32(int64_t n, const uint8_t *src, float scale, float *dst, void *stream) {
+    FNET_REQUIRE(n >= 0 && scale != 0.f, "fnet_u8_to_f32: bad arguments");
+    if (n == 0) return FNET_OK;
+    u8_to_f32_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(n, src, scale, dst);
+    return check_launch("fnet_u8_to_f32");
+}
+
+int fnet_gather_rows(int32_t batch, int64_t row_elems, const int32_t *perm, const int32_t *state,
+                     const float *src, float *dst, void *stream) {
+    FNET_REQUIRE(batch >= 0 && row_elems > 0, "fnet_gather_rows: bad sizes");
+    FNET_REQUIRE(perm && state && src && dst, "fnet_gather_rows: null pointer");
+    if (batch == 0) return FNET_OK;
+    int64_t vec = (row_elems & 3) == 0 ? row_elems / 4 : row_elems;
+    int bx = (int)ceil_div<int64_t>(vec, 256);
+    if (bx > 8) bx = 8;
+    dim3 grid(bx, batch > 4096 ? 4096 : batch);
+    gather_rows_kernel<<<grid, 256, 0, as_stream(stream)>>>(batch, row_elems, perm, state, src, dst);
+    return check_launch("fnet_gather_rows");
+}
+
+// ---------------------------------------------------------------- CUDA graphs
+int fnet_graph_begin(void *stream) {
+    FNET_CUDA(cudaStreamBeginCapture(as_stream(stream), cudaStreamCaptureModeThreadLocal));
+    return FNET_OK;
+}
+
+int fnet_graph_end(void *stream, void **graph_exec_out) {
+    FNET_REQUIRE(graph_exec_out != nullptr, "fnet_graph_end: null output");
+    cudaGraph_t graph = nullptr;
+    FNET_CUDA(cudaStreamEndCapture(as_stream(stream), &graph));
+    cudaGraphExec_t exec = nullptr;
+    cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) {
+        set_error("cudaGraphInstantiate: %s", cudaGetErrorString(e));
+        return FNET_ERR_CUDA;
+    }
+    *graph_exec_out = exec;
+    return FNET_OK;
+}
+
+int fnet_graph_launch(void *graph_exec, void *stream) {
+    FNET_REQUIRE(graph_exec != nullptr, "fnet_graph_launch: null graph");
+    FNET_CUDA(cudaGraphLaunch(reinterpret_cast<cudaGraphExec_t>(graph_exec), as_stream(stream)));
+    return FNET_OK;
+}
+
+int fnet_graph_destroy(void *graph_exec) {
+    if (graph_exec) FNET_CUDA(cudaGraphExecDestroy(reinterpret_cast<cudaGraphExec_t>(graph_exec)));
+    return FNET_OK;
+}
+
+}  // extern "C"

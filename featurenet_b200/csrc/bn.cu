@@ -1,0 +1,243 @@
+// Batch normalisation over axis 1 of a tensor viewed as [outer, A, inner]  (Keras axis=1 on
+// NHWC: one statistic per image ROW h, over batch x width x channels).
+//
+// Two launches per direction:
+//   1. partial sums per (a, split) -> workspace       (reads x [and dy] once)
+//   2. every CTA of row a folds the <= 64 partials in a fixed order, then normalises its chunk
+//      (reads x [and dy] again, writes y / dx); the first CTA of the row also writes the saved
+//      statistics, the moving averages or dgamma/dbeta.
+// Sums are taken on (x - x[first element of the row]) so that one pass in fp32 does not lose
+// the variance to cancellation.  Algorithmic traffic: forward 2 reads + 1 write of x,
+// backward 2 reads of x, 2 of dy, 1 write; HBM-bound.
+#include "common.cuh"
+
+namespace fnet {
+
+constexpr int kBnMaxSplits = 64;
+
+struct BnShape {
+    int outer, a, inner, splits;
+    int outer_per_split;
+};
+
+static BnShape bn_shape(int outer, int a, int inner) {
+    BnShape s;
+    s.outer = outer; s.a = a; s.inner = inner;
+    int want = ceil_div(2 * kNumSMs, a);
+    if (want > kBnMaxSplits) want = kBnMaxSplits;
+    if (want > outer) want = outer;
+    if (want < 1) want = 1;
+    s.outer_per_split = ceil_div(outer, want);
+    s.splits = ceil_div(outer, s.outer_per_split);
+    return s;
+}
+
+// element e of the chunk [o0, o1) x inner of row a
+__device__ __forceinline__ int64_t bn_index(const BnShape &s, int a, int o0, int64_t e) {
+    int64_t o = o0 + e / s.inner;
+    int64_t j = e - (e / s.inner) * s.inner;
+    return (o * s.a + a) * s.inner + j;
+}
+
+__global__ void __launch_bounds__(256) bn_stats_partial_kernel(BnShape s, const float *__restrict__ x,
+                                                               float *__restrict__ partial) {
+    __shared__ float red[32];
+    int a = blockIdx.x, part = blockIdx.y;
+    int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
+    float shift = __ldg(x + (int64_t)a * s.inner);
+    int64_t count = (int64_t)(o1 - o0) * s.inner;
+    float s1 = 0.f, s2 = 0.f;
+    for (int64_t e = threadIdx.x; e < count; e += blockDim.x) {
+        float v = __ldg(x + bn_index(s, a, o0, e)) - shift;
+        s1 += v;
+        s2 = fmaf(v, v, s2);
+    }
+    s1 = block_sum(s1, red);
+    s2 = block_sum(s2, red);
+    if (threadIdx.x == 0) {
+        partial[((int64_t)a * kBnMaxSplits + part) * 2 + 0] = s1;
+        partial[((int64_t)a * kBnMaxSplits + part) * 2 + 1] = s2;
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_normalize_train_kernel(BnShape s, float eps, float momentum,
+                                                                 const float *__restrict__ x,
+                                                                 const float *__restrict__ gamma,
+                                                                 const float *__restrict__ beta,
+                                                                 const float *__restrict__ partial, float *__restrict__ y,
+                                                                 float *__restrict__ save_mean, float *__restrict__ save_rstd,
+                                                                 float *__restrict__ moving_mean,
+                                                                 float *__restrict__ moving_var) {
+    __shared__ float stat[2];
+    int a = blockIdx.x, part = blockIdx.y;
+    if (threadIdx.x == 0) {
+        float s1 = 0.f, s2 = 0.f;
+        for (int z = 0; z < s.splits; ++z) {
+            s1 += partial[((int64_t)a * kBnMaxSplits + z) * 2 + 0];
+            s2 += partial[((int64_t)a * kBnMaxSplits + z) * 2 + 1];
+        }
+        float n = (float)s.outer * (float)s.inner;
+        float d = s1 / n;
+        float mean = __ldg(x + (int64_t)a * s.inner) + d;
+        float var = fmaxf(s2 / n - d * d, 0.f);
+        float rstd = rsqrtf(var + eps);
+        rstd = rstd * (1.5f - 0.5f * (var + eps) * rstd * rstd);   // one Newton step: full fp32 accuracy
+        stat[0] = mean;
+        stat[1] = rstd;
+        if (part == 0) {
+            save_mean[a] = mean;
+            save_rstd[a] = rstd;
+            // Keras: moving <- moving*momentum + value*(1-momentum); variance corrected by n/(n-(1+eps))
+            moving_mean[a] = moving_mean[a] * momentum + mean * (1.f - momentum);
+            moving_var[a] = moving_var[a] * momentum + (var * n / (n - (1.f + eps))) * (1.f - momentum);
+        }
+    }
+    __syncthreads();
+    // tf.nn.batch_normalization: inv = rsqrt(var+eps)*gamma; y = x*inv + (beta - mean*inv)
+    float inv = stat[1] * __ldg(gamma + a);
+    float off = __ldg(beta + a) - stat[0] * inv;
+    int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
+    int64_t count = (int64_t)(o1 - o0) * s.inner;
+    for (int64_t e = threadIdx.x; e < count; e += blockDim.x) {
+        int64_t at = bn_index(s, a, o0, e);
+        y[at] = fmaf(__ldg(x + at), inv, off);
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_infer_kernel(int64_t total, int a_len, int inner, float eps,
+                                                       const float *__restrict__ x, const float *__restrict__ gamma,
+                                                       const float *__restrict__ beta, const float *__restrict__ mean,
+                                                       const float *__restrict__ var, float *__restrict__ y) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int a = (int)((i / inner) % a_len);
+        float v = __ldg(var + a) + eps;
+        float rstd = rsqrtf(v);
+        rstd = rstd * (1.5f - 0.5f * v * rstd * rstd);
+        float inv = rstd * __ldg(gamma + a);
+        y[i] = fmaf(__ldg(x + i), inv, __ldg(beta + a) - __ldg(mean + a) * inv);
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_partial_kernel(BnShape s, const float *__restrict__ x,
+                                                             const float *__restrict__ dy,
+                                                             const float *__restrict__ save_mean,
+                                                             const float *__restrict__ save_rstd,
+                                                             float *__restrict__ partial) {
+    __shared__ float red[32];
+    int a = blockIdx.x, part = blockIdx.y;
+    int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
+    float mean = __ldg(save_mean + a), rstd = __ldg(save_rstd + a);
+    int64_t count = (int64_t)(o1 - o0) * s.inner;
+    float sb = 0.f, sg = 0.f;
+    for (int64_t e = threadIdx.x; e < count; e += blockDim.x) {
+        int64_t at = bn_index(s, a, o0, e);
+        float g = __ldg(dy + at);
+        sb += g;
+        sg = fmaf(g, (__ldg(x + at) - mean) * rstd, sg);
+    }
+    sb = block_sum(sb, red);
+    sg = block_sum(sg, red);
+    if (threadIdx.x == 0) {
+        partial[((int64_t)a * kBnMaxSplits + part) * 2 + 0] = sb;
+        partial[((int64_t)a * kBnMaxSplits + part) * 2 + 1] = sg;
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_dx_kernel(BnShape s, const float *__restrict__ x,
+                                                        const float *__restrict__ dy, const float *__restrict__ gamma,
+                                                        const float *__restrict__ save_mean,
+                                                        const float *__restrict__ save_rstd,
+                                                        const float *__restrict__ partial, float *__restrict__ dx,
+                                                        float *__restrict__ dgamma, float *__restrict__ dbeta,
+                                                        int accumulate) {
+    __shared__ float sums[2];
+    int a = blockIdx.x, part = blockIdx.y;
+    if (threadIdx.x == 0) {
+        float sb = 0.f, sg = 0.f;
+        for (int z = 0; z < s.splits; ++z) {
+            sb += partial[((int64_t)a * kBnMaxSplits + z) * 2 + 0];
+            sg += partial[((int64_t)a * kBnMaxSplits + z) * 2 + 1];
+        }
+        sums[0] = sb;
+        sums[1] = sg;
+        if (part == 0) {
+            dbeta[a] = sb;
+            dgamma[a] = sg;
+        }
+    }
+    __syncthreads();
+    float n = (float)s.outer * (float)s.inner;
+    float mean = __ldg(save_mean + a), rstd = __ldg(save_rstd + a);
+    float k = __ldg(gamma + a) * rstd / n;
+    float sb = sums[0], sg = sums[1];
+    int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
+    int64_t count = (int64_t)(o1 - o0) * s.inner;
+    for (int64_t e = threadIdx.x; e < count; e += blockDim.x) {
+        int64_t at = bn_index(s, a, o0, e);
+        float xhat = (__ldg(x + at) - mean) * rstd;
+        float v = k * (n * __ldg(dy + at) - sb - xhat * sg);
+        dx[at] = accumulate ? dx[at] + v : v;
+    }
+}
+
+}  // namespace fnet
+
+using namespace fnet;
+
+extern "C" {
+
+size_t fnet_bn_workspace_bytes(int32_t a) { return a > 0 ? (size_t)a * kBnMaxSplits * 2 * sizeof(float) : 0; }
+
+int fnet_bn_fwd_train(int32_t outer, int32_t a, int32_t inner, float eps, float momentum, const float *x,
+                      const float *gamma, const float *beta, float *y, float *save_mean, float *save_rstd,
+                      float *moving_mean, float *moving_var, void *ws, size_t ws_bytes, void *stream) {
+    FNET_REQUIRE(outer > 0 && a > 0 && inner > 0, "fnet_bn_fwd_train: bad shape");
+    FNET_REQUIRE(x && gamma && beta && y && save_mean && save_rstd && moving_mean && moving_var,
+                 "fnet_bn_fwd_train: null pointer");
+    if (!ws || ws_bytes < fnet_bn_workspace_bytes(a)) {
+        set_error("fnet_bn_fwd_train: workspace of %zu bytes needed, %zu given", fnet_bn_workspace_bytes(a), ws_bytes);
+        return FNET_ERR_WORKSPACE;
+    }
+    BnShape s = bn_shape(outer, a, inner);
+    dim3 grid(a, s.splits);
+    float *partial = reinterpret_cast<float *>(ws);
+    bn_stats_partial_kernel<<<grid, 256, 0, as_stream(stream)>>>(s, x, partial);
+    int rc = check_launch("fnet_bn_fwd_train");
+    if (rc) return rc;
+    bn_normalize_train_kernel<<<grid, 256, 0, as_stream(stream)>>>(s, eps, momentum, x, gamma, beta, partial, y,
+                                                                   save_mean, save_rstd, moving_mean, moving_var);
+    return check_launch("fnet_bn_fwd_train");
+}
+
+int fnet_bn_fwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const float *x, const float *gamma,
+                      const float *beta, const float *moving_mean, const float *moving_var, float *y, void *stream) {
+    FNET_REQUIRE(outer >= 0 && a > 0 && inner > 0, "fnet_bn_fwd_infer: bad shape");
+    FNET_REQUIRE(x && gamma && beta && moving_mean && moving_var && y, "fnet_bn_fwd_infer: null pointer");
+    int64_t total = (int64_t)outer * a * inner;
+    if (total == 0) return FNET_OK;
+    bn_infer_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(total, a, inner, eps, x, gamma, beta,
+                                                                            moving_mean, moving_var, y);
+    return check_launch("fnet_bn_fwd_infer");
+}
+
+int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,
+                const float *save_mean, const float *save_rstd, float *dx, float *dgamma, float *dbeta,
+                int accumulate, void *ws, size_t ws_bytes, void *stream) {
+    FNET_REQUIRE(outer > 0 && a > 0 && inner > 0, "fnet_bn_bwd: bad shape");
+    FNET_REQUIRE(x && dy && gamma && save_mean && save_rstd && dx && dgamma && dbeta, "fnet_bn_bwd: null pointer");
+    if (!ws || ws_bytes < fnet_bn_workspace_bytes(a)) {
+        set_error("fnet_bn_bwd: workspace of %zu bytes needed, %zu given", fnet_bn_workspace_bytes(a), ws_bytes);
+        return FNET_ERR_WORKSPACE;
+    }
+    BnShape s = bn_shape(outer, a, inner);
+    dim3 grid(a, s.splits);
+    float *partial = reinterpret_cast<float *>(ws);
+    bn_bwd_partial_kernel<<<grid, 256, 0, as_stream(stream)>>>(s, x, dy, save_mean, save_rstd, partial);
+    int rc = check_launch("fnet_bn_bwd");
+    if (rc) return rc;
+    bn_bwd_dx_kernel<<<grid, 256, 0, as_stream(stream)>>>(s, x, dy, gamma, save_mean, save_rstd, partial, dx, dgamma,
+                                                          dbeta, accumulate);
+    return check_launch("fnet_bn_bwd");
+}
+
+}  // extern "C"

@@ -1,0 +1,98 @@
+// Shared helpers for libfnet's kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/fnet.h"
+
+namespace fnet {
+
+constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+void set_error(const char *fmt, ...);
+
+inline int check_launch(const char *what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return FNET_ERR_CUDA;
+    }
+    return FNET_OK;
+}
+
+#define FNET_REQUIRE(cond, ...)                 \
+    do {                                        \
+        if (!(cond)) {                          \
+            fnet::set_error(__VA_ARGS__);       \
+            return FNET_ERR_ARG;                \
+        }                                       \
+    } while (0)
+
+#define FNET_CUDA(call)                                                        \
+    do {                                                                       \
+        cudaError_t e_ = (call);                                               \
+        if (e_ != cudaSuccess) {                                               \
+            fnet::set_error("%s: %s", #call, cudaGetErrorString(e_));          \
+            return FNET_ERR_CUDA;                                              \
+        }                                                                      \
+    } while (0)
+
+inline cudaStream_t as_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
+
+template <typename T>
+__host__ __device__ constexpr T ceil_div(T a, T b) { return (a + b - 1) / b; }
+
+// grid for a grid-stride element-wise kernel: enough CTAs to cover n, capped at 8 per SM
+inline int stream_grid(int64_t work_items, int threads) {
+    int64_t blocks = ceil_div<int64_t>(work_items, threads);
+    int64_t cap = (int64_t)kNumSMs * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+__device__ __forceinline__ float act_apply(float z, int act) {
+    switch (act) {
+        case FNET_ACT_RELU: return fmaxf(z, 0.f);
+        case FNET_ACT_TANH: return tanhf(z);
+        case FNET_ACT_SIGMOID: return 1.f / (1.f + expf(-z));
+        default: return z;
+    }
+}
+
+// derivative factor from the activation OUTPUT y
+__device__ __forceinline__ float act_grad(float y, int act) {
+    switch (act) {
+        case FNET_ACT_RELU: return y > 0.f ? 1.f : 0.f;
+        case FNET_ACT_TANH: return 1.f - y * y;
+        case FNET_ACT_SIGMOID: return y * (1.f - y);
+        default: return 1.f;
+    }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// block-wide sum for blockDim.x a multiple of 32 (<= 1024); result valid in every thread
+__device__ __forceinline__ float block_sum(float v, float *smem32) {
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) smem32[wid] = v;
+    __syncthreads();
+    float r = (lane < nw) ? smem32[lane] : 0.f;
+    r = warp_sum(r);
+    return r;
+}
+
+}  // namespace fnet

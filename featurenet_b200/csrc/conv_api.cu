@@ -1,0 +1,133 @@
+// C-ABI entry points of the GEMM-shaped ops (Conv2D, Dense): argument checks and the choice
+// between the fp32 FFMA kernels and the tcgen05 tensor-core kernels.
+#include "igemm.cuh"
+
+using namespace fnet;
+
+namespace {
+
+inline size_t max_sz(size_t a, size_t b) { return a > b ? a : b; }
+
+int check_math(int math, const char *what) {
+    if (math != FNET_MATH_FP32 && math != FNET_MATH_TF32 && math != FNET_MATH_BF16) {
+        set_error("%s: unknown math mode %d", what, math);
+        return FNET_ERR_ARG;
+    }
+    return FNET_OK;
+}
+
+int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
+             void *ws, size_t ws_bytes, cudaStream_t s) {
+    int rc;
+    if (math != FNET_MATH_FP32 && tc_supported(g, math, 0)) rc = tc_conv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
+    else rc = simt_conv_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
+    if (rc == FNET_OK && act == FNET_ACT_SOFTMAX)
+        rc = run_softmax_rows((int64_t)g.B * g.Ho * g.Wo, g.K, y, y, s);
+    return rc;
+}
+
+int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+               size_t ws_bytes, cudaStream_t s) {
+    if (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) return tc_conv_dgrad(g, math, dz, w, dx, accumulate, ws, ws_bytes, s);
+    return simt_conv_dgrad(g, dz, w, dx, accumulate, ws, ws_bytes, s);
+}
+
+int conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
+               size_t ws_bytes, cudaStream_t s) {
+    if (math != FNET_MATH_FP32 && tc_supported(g, math, 2)) return tc_conv_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
+    return simt_conv_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
+}
+
+int check_dense(int64_t m, int64_t k, int64_t n, const char *what) {
+    if (m < 0 || k <= 0 || n <= 0 || m > 0x7fffffffLL || k > 0x7fffffffLL || n > 0x7fffffffLL) {
+        set_error("%s: bad GEMM shape m=%lld k=%lld n=%lld", what, (long long)m, (long long)k, (long long)n);
+        return FNET_ERR_ARG;
+    }
+    return FNET_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
+    ConvGeom g;
+    if (geom_checked(d, g, "fnet_conv2d_workspace_bytes") != FNET_OK) return 0;
+    size_t need = simt_conv_workspace(g);
+    if (d->math != FNET_MATH_FP32) need = max_sz(need, tc_conv_workspace(g, d->math));
+    return need;
+}
+
+int fnet_conv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w, const float *bias, float *y, void *ws,
+                    size_t ws_bytes, void *stream) {
+    ConvGeom g;
+    int rc = geom_checked(d, g, "fnet_conv2d_fwd");
+    if (rc) return rc;
+    if ((rc = check_math(d->math, "fnet_conv2d_fwd"))) return rc;
+    FNET_REQUIRE(x && w && y, "fnet_conv2d_fwd: null pointer");
+    FNET_REQUIRE(d->act >= FNET_ACT_NONE && d->act <= FNET_ACT_SOFTMAX, "fnet_conv2d_fwd: unknown activation");
+    return conv_fwd(g, d->math, d->act, x, w, bias, y, ws, ws_bytes, as_stream(stream));
+}
+
+int fnet_conv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const float *w, float *dx, int accumulate,
+                         void *ws, size_t ws_bytes, void *stream) {
+    ConvGeom g;
+    int rc = geom_checked(d, g, "fnet_conv2d_bwd_data");
+    if (rc) return rc;
+    if ((rc = check_math(d->math, "fnet_conv2d_bwd_data"))) return rc;
+    FNET_REQUIRE(dz && w && dx, "fnet_conv2d_bwd_data: null pointer");
+    return conv_dgrad(g, d->math, dz, w, dx, accumulate, ws, ws_bytes, as_stream(stream));
+}
+
+int fnet_conv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const float *dz, float *dw, float *dbias,
+                           void *ws, size_t ws_bytes, void *stream) {
+    ConvGeom g;
+    int rc = geom_checked(d, g, "fnet_conv2d_bwd_filter");
+    if (rc) return rc;
+    if ((rc = check_math(d->math, "fnet_conv2d_bwd_filter"))) return rc;
+    FNET_REQUIRE(x && dz && dw, "fnet_conv2d_bwd_filter: null pointer");
+    return conv_wgrad(g, d->math, x, dz, dw, dbias, ws, ws_bytes, as_stream(stream));
+}
+
+size_t fnet_dense_workspace_bytes(int64_t m, int64_t k, int64_t n) {
+    if (check_dense(m, k, n, "fnet_dense_workspace_bytes") != FNET_OK || m == 0) return 0;
+    ConvGeom g = dense_geom(m, k, n);
+    return max_sz(simt_conv_workspace(g), tc_conv_workspace(g, FNET_MATH_TF32));
+}
+
+int fnet_dense_fwd(int64_t m, int64_t k, int64_t n, int act, int math, const float *x, const float *w,
+                   const float *bias, float *y, void *ws, size_t ws_bytes, void *stream) {
+    int rc = check_dense(m, k, n, "fnet_dense_fwd");
+    if (rc) return rc;
+    if ((rc = check_math(math, "fnet_dense_fwd"))) return rc;
+    if (m == 0) return FNET_OK;
+    FNET_REQUIRE(x && w && y, "fnet_dense_fwd: null pointer");
+    FNET_REQUIRE(act >= FNET_ACT_NONE && act <= FNET_ACT_SOFTMAX, "fnet_dense_fwd: unknown activation");
+    return conv_fwd(dense_geom(m, k, n), math, act, x, w, bias, y, ws, ws_bytes, as_stream(stream));
+}
+
+int fnet_dense_bwd_data(int64_t m, int64_t k, int64_t n, int math, const float *dz, const float *w, float *dx,
+                        int accumulate, void *ws, size_t ws_bytes, void *stream) {
+    int rc = check_dense(m, k, n, "fnet_dense_bwd_data");
+    if (rc) return rc;
+    if ((rc = check_math(math, "fnet_dense_bwd_data"))) return rc;
+    if (m == 0) return FNET_OK;
+    FNET_REQUIRE(dz && w && dx, "fnet_dense_bwd_data: null pointer");
+    return conv_dgrad(dense_geom(m, k, n), math, dz, w, dx, accumulate, ws, ws_bytes, as_stream(stream));
+}
+
+int fnet_dense_bwd_filter(int64_t m, int64_t k, int64_t n, int math, const float *x, const float *dz, float *dw,
+                          float *dbias, void *ws, size_t ws_bytes, void *stream) {
+    int rc = check_dense(m, k, n, "fnet_dense_bwd_filter");
+    if (rc) return rc;
+    if ((rc = check_math(math, "fnet_dense_bwd_filter"))) return rc;
+    FNET_REQUIRE(x && dz && dw, "fnet_dense_bwd_filter: null pointer");
+    if (m == 0) {
+        rc = fnet_fill(k * n, 0.f, dw, stream);
+        if (rc == FNET_OK && dbias) rc = fnet_fill(n, 0.f, dbias, stream);
+        return rc;
+    }
+    return conv_wgrad(dense_geom(m, k, n), math, x, dz, dw, dbias, ws, ws_bytes, as_stream(stream));
+}
+
+}  // extern "C"

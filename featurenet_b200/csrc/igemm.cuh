@@ -1,0 +1,35 @@
+// Internal interface between the C-ABI wrappers (conv_api.cu) and the GEMM-shaped kernels.
+#pragma once
+#include "common.cuh"
+
+namespace fnet {
+
+struct ConvGeom {
+    int B, H, W, C, Ho, Wo, K, kh, kw, sh, sw, pt, pl, dh, dw;
+};
+
+int geom_checked(const fnet_conv2d_desc *d, ConvGeom &g, const char *what);
+ConvGeom dense_geom(long long m, long long k, long long n);
+
+// FNET_MATH_FP32: FFMA implicit GEMM (igemm_simt.cu)
+size_t simt_conv_workspace(const ConvGeom &g);
+int simt_conv_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, void *ws,
+                  size_t ws_bytes, cudaStream_t stream);
+int simt_conv_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+                    size_t ws_bytes, cudaStream_t stream);
+int simt_conv_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws,
+                    size_t ws_bytes, cudaStream_t stream);
+
+// FNET_MATH_TF32 / FNET_MATH_BF16: tcgen05 implicit GEMM (igemm_tc.cu)
+bool tc_supported(const ConvGeom &g, int math, int product);   // product: 0 fwd, 1 dgrad, 2 wgrad
+size_t tc_conv_workspace(const ConvGeom &g, int math);
+int tc_conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
+                void *ws, size_t ws_bytes, cudaStream_t stream);
+int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+                  size_t ws_bytes, cudaStream_t stream);
+int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
+                  size_t ws_bytes, cudaStream_t stream);
+
+int run_softmax_rows(int64_t rows, int64_t cols, const float *x, float *y, cudaStream_t stream);
+
+}  // namespace fnet

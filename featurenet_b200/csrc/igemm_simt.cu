@@ -1,0 +1,350 @@
+// fp32 implicit-GEMM convolution / dense kernels on the FFMA pipe (FNET_MATH_FP32).
+//
+// This is the parity path: fp32 operands, fp32 accumulation, a fixed reduction order, so the
+// result is reproducible run to run and comparable with the float64 oracle at 1e-5.  The
+// tensor-core path (igemm_tc.cu) shares the geometry code below.
+//
+// One kernel template serves the three products of a convolution; the "problem" type says
+// how GEMM coordinates map to tensor elements:
+//   forward        C[m, n]  m = (b, ho, wo)   n = out channel   k = (r, s, c)
+//   backward data  C[m, n]  m = (b, h, w)     n = in channel    k = (r, s, out channel)
+//   backward filter C[m, n] m = (r, s, c) (+1 row of ones = bias)  n = out channel  k = (b, ho, wo)
+// A tile rows keep a decoded context in shared memory (decoded once per CTA); the column
+// context is decoded once per thread per k-tile, so the inner gather has no divisions.
+// When the output has too few tiles to fill 148 SMs the reduction axis is split across
+// blockIdx.z; partial tiles go to the caller's workspace and are summed in a fixed order.
+#include "igemm.cuh"
+
+namespace fnet {
+
+struct PixelCtx {   // one output pixel (forward / filter) or one input pixel (data)
+    long long base; // element offset of the image it indexes into
+    int h0, w0;     // top-left input coordinate of the window, or padded input coordinate
+    int valid;
+};
+
+struct TapCtx {     // one (r, s, channel) of the reduction / filter row
+    int dr, ds;     // dilated tap offsets
+    int ch;         // channel inside the tap
+    int valid;      // 1 = real tap, 2 = the all-ones bias row (filter gradient only), 0 = out of range
+};
+
+__device__ __forceinline__ void decode_out_pixel(const ConvGeom &g, int m, int M, PixelCtx &p) {
+    p.valid = m < M;
+    int mm = p.valid ? m : 0;
+    int b = mm / (g.Ho * g.Wo);
+    int rem = mm - b * (g.Ho * g.Wo);
+    int ho = rem / g.Wo, wo = rem - ho * g.Wo;
+    p.base = (long long)b * g.H * g.W * g.C;
+    p.h0 = ho * g.sh - g.pt;
+    p.w0 = wo * g.sw - g.pl;
+}
+
+__device__ __forceinline__ void decode_in_pixel(const ConvGeom &g, int m, int M, PixelCtx &p) {
+    p.valid = m < M;
+    int mm = p.valid ? m : 0;
+    int b = mm / (g.H * g.W);
+    int rem = mm - b * (g.H * g.W);
+    int h = rem / g.W, w = rem - h * g.W;
+    p.base = (long long)b * g.Ho * g.Wo * g.K;
+    p.h0 = h + g.pt;
+    p.w0 = w + g.pl;
+}
+
+__device__ __forceinline__ void decode_tap(const ConvGeom &g, int k, int channels, int limit, TapCtx &t) {
+    t.valid = k < limit;
+    int kk = t.valid ? k : 0;
+    int tap = kk / channels;
+    t.ch = kk - tap * channels;
+    int r = tap / g.kw, s = tap - r * g.kw;
+    t.dr = r * g.dh;
+    t.ds = s * g.dw;
+}
+
+// x[b, h0+dr, w0+ds, ch] with zero padding
+__device__ __forceinline__ float gather_input(const ConvGeom &g, const float *__restrict__ x, const PixelCtx &p,
+                                              const TapCtx &t) {
+    int h = p.h0 + t.dr, w = p.w0 + t.ds;
+    if ((unsigned)h >= (unsigned)g.H || (unsigned)w >= (unsigned)g.W) return 0.f;
+    return __ldg(x + p.base + ((long long)h * g.W + w) * g.C + t.ch);
+}
+
+// dz[b, (hp-dr)/sh, (wp-ds)/sw, ch] when the divisions are exact and in range
+__device__ __forceinline__ float gather_grad(const ConvGeom &g, const float *__restrict__ dz, const PixelCtx &p,
+                                             const TapCtx &t) {
+    int hh = p.h0 - t.dr, ww = p.w0 - t.ds;
+    if (hh < 0 || ww < 0) return 0.f;
+    int ho = hh / g.sh, wo = ww / g.sw;
+    if (ho * g.sh != hh || wo * g.sw != ww || ho >= g.Ho || wo >= g.Wo) return 0.f;
+    return __ldg(dz + p.base + ((long long)ho * g.Wo + wo) * g.K + t.ch);
+}
+
+// ------------------------------------------------------------------ problems
+struct FwdProblem {
+    ConvGeom g;
+    const float *x, *w, *bias;
+    float *y;
+    int act;
+    typedef PixelCtx Row;
+    typedef TapCtx Col;
+    __device__ void make_row(int m, int M, Row &r) const { decode_out_pixel(g, m, M, r); }
+    __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.C, kend, c); }
+    __device__ float a(const Row &r, const Col &c) const { return gather_input(g, x, r, c); }
+    __device__ float b(int k, int n) const { return __ldg(w + (long long)k * g.K + n); }
+    __device__ void store(int m, int n, float v) const {
+        if (bias) v += __ldg(bias + n);
+        y[(long long)m * g.K + n] = act_apply(v, act);
+    }
+};
+
+struct DgradProblem {
+    ConvGeom g;
+    const float *dz, *w;
+    float *dx;
+    int accumulate;
+    typedef PixelCtx Row;
+    typedef TapCtx Col;
+    __device__ void make_row(int m, int M, Row &r) const { decode_in_pixel(g, m, M, r); }
+    __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.K, kend, c); }
+    __device__ float a(const Row &r, const Col &c) const { return gather_grad(g, dz, r, c); }
+    __device__ float b(int k, int n) const {
+        int tap = k / g.K, ko = k - tap * g.K;
+        return __ldg(w + ((long long)tap * g.C + n) * g.K + ko);
+    }
+    __device__ void store(int m, int n, float v) const {
+        long long at = (long long)m * g.C + n;
+        dx[at] = accumulate ? dx[at] + v : v;
+    }
+};
+
+struct WgradProblem {
+    ConvGeom g;
+    const float *x, *dz;
+    float *dw, *dbias;
+    int taps_c;   // kh*kw*C: rows below are filter taps, row == taps_c is the bias row
+    typedef TapCtx Row;
+    typedef PixelCtx Col;
+    __device__ void make_row(int k, int M, Row &r) const {
+        decode_tap(g, k, g.C, taps_c, r);
+        if (k == taps_c && k < M) r.valid = 2;
+    }
+    __device__ void make_col(int m, int mend, Col &c) const { decode_out_pixel(g, m, mend, c); }
+    __device__ float a(const Row &r, const Col &c) const { return r.valid == 2 ? 1.f : gather_input(g, x, c, r); }
+    __device__ float b(int m, int n) const { return __ldg(dz + (long long)m * g.K + n); }
+    __device__ void store(int k, int n, float v) const {
+        if (k < taps_c) dw[(long long)k * g.K + n] = v;
+        else if (dbias) dbias[n] = v;
+    }
+};
+
+// ------------------------------------------------------------------ the tile kernel
+constexpr int BK = 16;
+
+template <class P, int BM, int BN, int TM, int TN>
+__global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int Kg, int k_per_split,
+                                                          float *__restrict__ partial) {
+    static_assert((BM / TM) * (BN / TN) == 256, "256 threads per CTA");
+    static_assert(BM % 16 == 0 && TM % 4 == 0, "tile shape");
+    __shared__ __align__(16) float As[BK][BM + 4];
+    __shared__ __align__(16) float Bs[BK][BN + 4];
+    __shared__ typename P::Row rows[BM];
+
+    const int tid = threadIdx.x;
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const int kbeg = blockIdx.z * k_per_split;
+    const int kend = min(Kg, kbeg + k_per_split);
+
+    for (int i = tid; i < BM; i += 256) p.make_row(m0 + i, M, rows[i]);
+    __syncthreads();
+
+    const int tx = tid % (BN / TN), ty = tid / (BN / TN);
+    const int a_col = tid % BK, a_rg = tid / BK;   // 16 row groups
+
+    float acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+    for (int k0 = kbeg; k0 < kend; k0 += BK) {
+        typename P::Col col;
+        p.make_col(k0 + a_col, kend, col);
+#pragma unroll 4
+        for (int i = 0; i < BM / 16; ++i) {
+            int r = a_rg + 16 * i;
+            float v = 0.f;
+            if (col.valid && rows[r].valid) v = p.a(rows[r], col);
+            As[a_col][r] = v;
+        }
+        for (int e = tid; e < BK * BN; e += 256) {
+            int kk = e / BN, nn = e - kk * BN;
+            float v = 0.f;
+            if (k0 + kk < kend && n0 + nn < N) v = p.b(k0 + kk, n0 + nn);
+            Bs[kk][nn] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < BK; ++kk) {
+            float a[TM], b[TN];
+#pragma unroll
+            for (int i = 0; i < TM; i += 4) {
+                float4 t = *reinterpret_cast<const float4 *>(&As[kk][ty * TM + i]);
+                a[i] = t.x; a[i + 1] = t.y; a[i + 2] = t.z; a[i + 3] = t.w;
+            }
+#pragma unroll
+            for (int j = 0; j < TN; ++j) b[j] = Bs[kk][tx * TN + j];
+#pragma unroll
+            for (int i = 0; i < TM; ++i)
+#pragma unroll
+                for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+        int m = m0 + ty * TM + i;
+        if (m >= M) continue;
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+            int n = n0 + tx * TN + j;
+            if (n >= N) continue;
+            if (partial) partial[((long long)blockIdx.z * M + m) * N + n] = acc[i][j];
+            else p.store(m, n, acc[i][j]);
+        }
+    }
+}
+
+// sums the split partials in split order (deterministic) and applies the problem's epilogue
+template <class P>
+__global__ void __launch_bounds__(256) reduce_splits_kernel(P p, int M, int N, int splits,
+                                                             const float *__restrict__ partial) {
+    long long total = (long long)M * N;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += partial[(long long)z * total + i];
+        int m = (int)(i / N), n = (int)(i - (long long)m * N);
+        p.store(m, n, s);
+    }
+}
+
+struct SplitPlan {
+    int bm, bn, splits, k_per_split;
+    size_t ws_bytes;
+};
+
+static SplitPlan plan_for(long long M, long long N, long long Kg) {
+    SplitPlan s;
+    s.bn = N <= 8 ? 8 : (N <= 16 ? 16 : (N <= 32 ? 32 : 64));
+    s.bm = s.bn <= 16 ? 256 : 128;
+    long long tiles = ceil_div<long long>(M, s.bm) * ceil_div<long long>(N, s.bn);
+    long long splits = 1;
+    if (tiles < kNumSMs && Kg > 8 * BK) {
+        splits = ceil_div<long long>(2 * kNumSMs, tiles);
+        long long most = ceil_div<long long>(Kg, 4 * BK);
+        if (splits > most) splits = most;
+        if (splits < 1) splits = 1;
+    }
+    long long per = ceil_div<long long>(ceil_div<long long>(Kg, splits), BK) * BK;
+    s.k_per_split = (int)per;
+    s.splits = (int)ceil_div<long long>(Kg, per);
+    s.ws_bytes = s.splits > 1 ? (size_t)s.splits * M * N * sizeof(float) : 0;
+    return s;
+}
+
+template <class P>
+static int run_problem(const P &p, long long M, long long N, long long Kg, void *ws, size_t ws_bytes,
+                       cudaStream_t stream, const char *what) {
+    if (M <= 0 || N <= 0) return FNET_OK;
+    if (M > 0x7fffffffLL || Kg > 0x7fffffffLL || N > 0x7fffffffLL) {
+        set_error("%s: GEMM extent exceeds 2^31", what);
+        return FNET_ERR_UNSUPPORTED;
+    }
+    SplitPlan plan = plan_for(M, N, Kg);
+    float *partial = nullptr;
+    if (plan.splits > 1) {
+        if (ws == nullptr || ws_bytes < plan.ws_bytes) {
+            set_error("%s: workspace of %zu bytes needed, %zu given", what, plan.ws_bytes, ws_bytes);
+            return FNET_ERR_WORKSPACE;
+        }
+        partial = reinterpret_cast<float *>(ws);
+    }
+    dim3 grid((unsigned)ceil_div<long long>(M, plan.bm), (unsigned)ceil_div<long long>(N, plan.bn), plan.splits);
+    if (grid.y > 65535u) {
+        set_error("%s: too many column tiles (%u)", what, grid.y);
+        return FNET_ERR_UNSUPPORTED;
+    }
+    int m = (int)M, n = (int)N, kg = (int)Kg;
+    switch (plan.bn) {
+        case 8: igemm_simt_kernel<P, 256, 8, 4, 2><<<grid, 256, 0, stream>>>(p, m, n, kg, plan.k_per_split, partial); break;
+        case 16: igemm_simt_kernel<P, 256, 16, 4, 4><<<grid, 256, 0, stream>>>(p, m, n, kg, plan.k_per_split, partial); break;
+        case 32: igemm_simt_kernel<P, 128, 32, 4, 4><<<grid, 256, 0, stream>>>(p, m, n, kg, plan.k_per_split, partial); break;
+        default: igemm_simt_kernel<P, 128, 64, 8, 4><<<grid, 256, 0, stream>>>(p, m, n, kg, plan.k_per_split, partial); break;
+    }
+    int rc = check_launch(what);
+    if (rc != FNET_OK) return rc;
+    if (plan.splits > 1) {
+        reduce_splits_kernel<P><<<stream_grid(M * N, 256), 256, 0, stream>>>(p, m, n, plan.splits, partial);
+        rc = check_launch(what);
+    }
+    return rc;
+}
+
+static int geom_from_desc(const fnet_conv2d_desc *d, ConvGeom &g, const char *what) {
+    if (d == nullptr) { set_error("%s: null descriptor", what); return FNET_ERR_ARG; }
+    if (d->batch < 0 || d->in_h <= 0 || d->in_w <= 0 || d->in_c <= 0 || d->out_h <= 0 || d->out_w <= 0 ||
+        d->out_c <= 0 || d->kh <= 0 || d->kw <= 0 || d->stride_h <= 0 || d->stride_w <= 0 || d->dil_h <= 0 ||
+        d->dil_w <= 0 || d->pad_top < 0 || d->pad_left < 0) {
+        set_error("%s: bad convolution geometry", what);
+        return FNET_ERR_ARG;
+    }
+    // the last window must start inside the padded input
+    if ((d->out_h - 1) * d->stride_h - d->pad_top >= d->in_h || (d->out_w - 1) * d->stride_w - d->pad_left >= d->in_w) {
+        set_error("%s: output extent inconsistent with input, stride and padding", what);
+        return FNET_ERR_ARG;
+    }
+    g = ConvGeom{d->batch, d->in_h, d->in_w, d->in_c, d->out_h, d->out_w, d->out_c, d->kh, d->kw,
+                 d->stride_h, d->stride_w, d->pad_top, d->pad_left, d->dil_h, d->dil_w};
+    return FNET_OK;
+}
+
+size_t simt_conv_workspace(const ConvGeom &g) {
+    long long mo = (long long)g.B * g.Ho * g.Wo, mi = (long long)g.B * g.H * g.W;
+    long long taps = (long long)g.kh * g.kw;
+    size_t a = plan_for(mo, g.K, taps * g.C).ws_bytes;
+    size_t b = plan_for(mi, g.C, taps * g.K).ws_bytes;
+    size_t c = plan_for(taps * g.C + 1, g.K, mo).ws_bytes;
+    return a > b ? (a > c ? a : c) : (b > c ? b : c);
+}
+
+int simt_conv_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, void *ws,
+                  size_t ws_bytes, cudaStream_t stream) {
+    FwdProblem p{g, x, w, bias, y, act == FNET_ACT_SOFTMAX ? FNET_ACT_NONE : act};
+    return run_problem(p, (long long)g.B * g.Ho * g.Wo, g.K, (long long)g.kh * g.kw * g.C, ws, ws_bytes, stream,
+                       "conv2d_fwd");
+}
+
+int simt_conv_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+                    size_t ws_bytes, cudaStream_t stream) {
+    DgradProblem p{g, dz, w, dx, accumulate};
+    return run_problem(p, (long long)g.B * g.H * g.W, g.C, (long long)g.kh * g.kw * g.K, ws, ws_bytes, stream,
+                       "conv2d_bwd_data");
+}
+
+int simt_conv_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws,
+                    size_t ws_bytes, cudaStream_t stream) {
+    int taps_c = g.kh * g.kw * g.C;
+    WgradProblem p{g, x, dz, dw, dbias, taps_c};
+    return run_problem(p, (long long)taps_c + (dbias ? 1 : 0), g.K, (long long)g.B * g.Ho * g.Wo, ws, ws_bytes,
+                       stream, "conv2d_bwd_filter");
+}
+
+int geom_checked(const fnet_conv2d_desc *d, ConvGeom &g, const char *what) { return geom_from_desc(d, g, what); }
+
+ConvGeom dense_geom(long long m, long long k, long long n) {
+    // a dense layer is a 1x1 convolution over m "pixels" of one row each
+    return ConvGeom{(int)m, 1, 1, (int)k, 1, 1, (int)n, 1, 1, 1, 1, 0, 0, 1, 1};
+}
+
+}  // namespace fnet

@@ -1,0 +1,826 @@
+"""CUDA executor of one candidate network: memory plan, launch programs, CUDA-graph steps, fit loop.
+
+Replaces what Keras/TensorFlow do underneath /root/reference/helpers.py:105-111 (``model.fit``)
+and tensorflow_generator.py:270 (``model.evaluate``): one ``session.run`` per step with a host
+batch fed through feed_dict becomes one CUDA-graph launch per step on a device-resident
+dataset.
+
+Memory layout (all fp32, NHWC, allocated once per candidate through torch, sized for HBM):
+  * ``params`` / ``grads`` / ``adam_m`` / ``adam_v``: four flat arenas with identical layout,
+    every weight tensor at a 64-float (256 B) aligned offset, so the optimizer is one launch
+    and (for the data-parallel mode) the gradient exchange is one all-reduce;
+  * ``stats``: the non-trainable BatchNorm moving statistics;
+  * one activation and one gradient buffer per layer output, sized for the largest batch;
+  * one workspace shared by all split reductions (kernels of a step are serial on one stream);
+  * ``state`` (int32[8]): iteration count, epoch cursor, lr, lr_t -- read by the kernels so a
+    captured step is identical from launch to launch.
+
+PyTorch is used for allocation, streams and host<->device copies only; every arithmetic
+kernel is launched through the C ABI (featurenet_b200.lib).  No CPU execution path exists.
+"""
+import ctypes as C
+import math
+import time
+
+import numpy as np
+import torch
+
+from . import lib as fl
+from .layers import glorot_limit
+
+ALIGN = 64            # floats; weight tensors start on 256-byte boundaries
+GEMM_KINDS = ("conv2d", "sepconv2d", "dense")
+
+
+def _prod(shape):
+    n = 1
+    for s in shape:
+        n *= int(s)
+    return n
+
+
+class HistoryResult(object):
+    """What keras ``fit`` returns: ``.history`` maps metric name -> list per epoch."""
+
+    def __init__(self):
+        self.history = {}
+        self.epoch = []
+
+
+class DeviceDataCache(object):
+    """Datasets stay resident in HBM across candidates (the reference re-feeds every batch from host RAM)."""
+    _store = {}
+
+    @classmethod
+    def get(cls, array, device, dtype=torch.float32):
+        key = (id(array), array.shape, str(array.dtype), str(device))
+        hit = cls._store.get(key)
+        if hit is not None and hit[0] is array:
+            return hit[1]
+        host = np.ascontiguousarray(array)
+        t = torch.from_numpy(host).to(device=device, dtype=dtype, non_blocking=False).contiguous()
+        if len(cls._store) > 16:
+            cls._store.clear()
+        cls._store[key] = (array, t)
+        return t
+
+    @classmethod
+    def clear(cls):
+        cls._store.clear()
+
+
+class Engine(object):
+    def __init__(self, net, device=None, math_mode=None, seed=None):
+        if not torch.cuda.is_available():
+            raise fl.FnetError("featurenet_b200 needs a CUDA device: there is no CPU execution path")
+        import os
+        self.lib = fl.get()
+        self.net = net
+        self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
+        self.math = fl.MATH[(math_mode or os.environ.get("FNET_PRECISION", "fp32")).lower()]
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.sp = C.c_void_p(self.stream.cuda_stream)
+        self.nodes = list(net.layers)
+        self.index = {id(n): i for i, n in enumerate(self.nodes)}
+        self.src = [[self.index[id(t.node)] for t in n.inputs] for n in self.nodes]
+        self.shape = [tuple(n.output.shape.as_list()[1:]) for n in self.nodes]
+        self.n_out = _prod(self.shape[-1])
+        head = self.nodes[-1]
+        if head.kind != "dense" or head.cfg.get("activation") != "softmax":
+            raise NotImplementedError("the loss kernel expects a Dense(softmax) output layer (keras_model.py:124)")
+        self.seed = int(seed if seed is not None else int(os.environ.get("FNET_SEED", "0")) or
+                        np.random.SeedSequence().entropy % (1 << 62))
+        self.dropout_seed = (self.seed * 0x9E3779B97F4A7C15 + 0x1234567) & 0xFFFFFFFFFFFFFFFF
+        self.capacity = 0
+        self.graphs = {}
+        self.programs = {}
+        self.use_graphs = os.environ.get("FNET_NO_GRAPH", "0") != "1"
+        self._plan_params()
+        self._init_weights()
+        with torch.cuda.device(self.device):
+            self.state = torch.zeros(8, dtype=torch.int32, device=self.device)
+            self.state_eval = torch.zeros(8, dtype=torch.int32, device=self.device)
+            self.loss_sum = torch.zeros(1, dtype=torch.float64, device=self.device)
+            self.correct = torch.zeros(1, dtype=torch.int64, device=self.device)
+            self._lr_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self._lr_on_device = None
+        self.timeline = None          # when a list: (label, start_event, end_event) per launch (profiling mode)
+
+    # ------------------------------------------------------------------ parameters
+    def _plan_params(self):
+        self.w_off, self.s_off = {}, {}          # (node, k) -> (offset, size) in params / stats arena
+        p = s = 0
+        for i, node in enumerate(self.nodes):
+            for k, spec in enumerate(node.weights):
+                if spec.trainable:
+                    self.w_off[(i, k)] = (p, spec.size)
+                    p += -(-spec.size // ALIGN) * ALIGN
+                else:
+                    self.s_off[(i, k)] = (s, spec.size)
+                    s += -(-spec.size // ALIGN) * ALIGN
+        self.n_params, self.n_stats = p, s
+        with torch.cuda.device(self.device):
+            mk = lambda n: torch.zeros(max(n, ALIGN), dtype=torch.float32, device=self.device)
+            self.params, self.grads, self.adam_m, self.adam_v = mk(p), mk(p), mk(p), mk(p)
+            self.stats = mk(s)
+
+    def _wview(self, arena, i, k):
+        off, size = (self.w_off if (i, k) in self.w_off else self.s_off)[(i, k)]
+        return arena[off: off + size]
+
+    def _wp(self, i, k, arena=None):
+        """Device pointer of weight k of node i in the given arena (params by default, stats for BN moving)."""
+        if (i, k) in self.w_off:
+            base = self.params if arena is None else arena
+            return C.c_void_p(base.data_ptr() + 4 * self.w_off[(i, k)][0])
+        return C.c_void_p(self.stats.data_ptr() + 4 * self.s_off[(i, k)][0])
+
+    def _init_weights(self):
+        rng = np.random.default_rng(self.seed)
+        weights = []
+        for node in self.nodes:
+            for spec in node.weights:
+                if spec.init == "glorot_uniform":
+                    lim = glorot_limit(spec.fans)
+                    weights.append(rng.uniform(-lim, lim, size=spec.shape).astype(np.float32))
+                elif spec.init == "ones":
+                    weights.append(np.ones(spec.shape, np.float32))
+                else:
+                    weights.append(np.zeros(spec.shape, np.float32))
+        self.set_weights(weights)
+
+    def get_weights(self):
+        """Keras order: layer by layer, each layer's weights in its own order."""
+        self.stream.synchronize()
+        p, s = self.params.cpu().numpy(), self.stats.cpu().numpy()
+        out = []
+        for i, node in enumerate(self.nodes):
+            for k, spec in enumerate(node.weights):
+                arena, table = (p, self.w_off) if spec.trainable else (s, self.s_off)
+                off, size = table[(i, k)]
+                out.append(arena[off: off + size].reshape(spec.shape).copy())
+        return out
+
+    def set_weights(self, weights):
+        p = np.zeros(max(self.n_params, ALIGN), np.float32)
+        s = np.zeros(max(self.n_stats, ALIGN), np.float32)
+        it = iter(weights)
+        for i, node in enumerate(self.nodes):
+            for k, spec in enumerate(node.weights):
+                w = np.asarray(next(it), dtype=np.float32)
+                if w.shape != spec.shape:
+                    raise ValueError("weight %s of layer %s has shape %r, expected %r" % (spec.name, node.name, w.shape, spec.shape))
+                arena, table = (p, self.w_off) if spec.trainable else (s, self.s_off)
+                off, size = table[(i, k)]
+                arena[off: off + size] = w.reshape(-1)
+        with torch.cuda.stream(self.stream):
+            self.params.copy_(torch.from_numpy(p))
+            self.stats.copy_(torch.from_numpy(s))
+        self.stream.synchronize()
+
+    def reset_optimizer(self):
+        with torch.cuda.stream(self.stream):
+            self.adam_m.zero_()
+            self.adam_v.zero_()
+            self.state.zero_()
+        self._lr_on_device = None
+
+    def snapshot(self, into=None):
+        """Device-to-device copy of the weights (ModelCheckpoint / SGDR restarts)."""
+        with torch.cuda.stream(self.stream):
+            if into is None:
+                into = (torch.empty_like(self.params), torch.empty_like(self.stats))
+            into[0].copy_(self.params)
+            into[1].copy_(self.stats)
+        return into
+
+    def restore(self, snap):
+        with torch.cuda.stream(self.stream):
+            self.params.copy_(snap[0])
+            self.stats.copy_(snap[1])
+
+    def save(self, path):
+        names = []
+        arrays = {}
+        ws = iter(self.get_weights())
+        for node in self.nodes:
+            for spec in node.weights:
+                key = "%s/%s" % (node.name, spec.name)
+                names.append(key)
+                arrays[key] = next(ws)
+        with open(path, "wb") as handle:
+            np.savez(handle, __order__=np.array(names), **arrays)
+
+    # ------------------------------------------------------------------ activations
+    def _ensure_capacity(self, batch):
+        if batch <= self.capacity:
+            return
+        self._drop_graphs()
+        self.capacity = batch
+        dev = self.device
+        with torch.cuda.device(dev):
+            f32 = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)
+            self.act, self.gact, self.aux = {}, {}, {}
+            ws_bytes = 256
+            for i, node in enumerate(self.nodes):
+                if node.kind == "flatten":
+                    continue                       # a view of its input (resolved in _buf)
+                self.act[i] = f32(batch, *self.shape[i])
+                if node.kind != "input":
+                    self.gact[i] = f32(batch, *self.shape[i])
+                if node.kind == "maxpool":
+                    self.aux[i] = torch.empty((batch,) + self.shape[i], dtype=torch.uint8, device=dev)
+                elif node.kind == "sepconv2d":
+                    mid = self.shape[i][:2] + (self.shape[self.src[i][0]][2],)
+                    self.aux[i] = (f32(batch, *mid), f32(batch, *mid))
+                elif node.kind == "bn":
+                    a = self.shape[i][node.cfg["axis"] - 1]
+                    self.aux[i] = (f32(a), f32(a))
+                ws_bytes = max(ws_bytes, self._workspace_need(i, batch))
+            self.ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            self.yb = f32(batch, self.n_out)
+        self.ws_bytes = ws_bytes
+
+    def _workspace_need(self, i, batch):
+        node, need = self.nodes[i], 0
+        if node.kind == "conv2d":
+            need = self.lib.fnet_conv2d_workspace_bytes(C.byref(self._conv_desc(i, batch)))
+        elif node.kind == "dwconv2d":
+            need = self.lib.fnet_dwconv2d_workspace_bytes(C.byref(self._conv_desc(i, batch)))
+        elif node.kind == "sepconv2d":
+            dw, pw = self._sep_descs(i, batch)
+            need = max(self.lib.fnet_dwconv2d_workspace_bytes(C.byref(dw)), self.lib.fnet_conv2d_workspace_bytes(C.byref(pw)))
+        elif node.kind == "dense":
+            m, k, n = self._dense_mkn(i, batch)
+            need = self.lib.fnet_dense_workspace_bytes(m, k, n)
+        elif node.kind == "bn":
+            need = self.lib.fnet_bn_workspace_bytes(self.shape[i][node.cfg["axis"] - 1])
+        return int(need)
+
+    def _resolve(self, i, training):
+        """Index of the buffer that holds node i's output (flatten, and dropout at inference, are views)."""
+        node = self.nodes[i]
+        while node.kind == "flatten" or (node.kind == "dropout" and not training):
+            i = self.src[i][0]
+            node = self.nodes[i]
+        return i
+
+    def _a(self, i, training):
+        return C.c_void_p(self.act[self._resolve(i, training)].data_ptr())
+
+    def _g(self, i):
+        return C.c_void_p(self.gact[self._resolve(i, True)].data_ptr())
+
+    # ------------------------------------------------------------------ descriptors
+    def _conv_desc(self, i, batch, act=True):
+        node, cfg = self.nodes[i], self.nodes[i].cfg
+        h, w, c = self.shape[self.src[i][0]]
+        ho, wo, k = self.shape[i]
+        dil = cfg.get("dilation", (1, 1))
+        return fl.Conv2dDesc(batch, h, w, c, ho, wo, k, cfg["kernel"][0], cfg["kernel"][1], cfg["strides"][0],
+                             cfg["strides"][1], cfg["pad_top"], cfg["pad_left"], dil[0], dil[1],
+                             fl.ACT[cfg["activation"]] if act else 0, self.math)
+
+    def _sep_descs(self, i, batch):
+        cfg = self.nodes[i].cfg
+        h, w, c = self.shape[self.src[i][0]]
+        ho, wo, k = self.shape[i]
+        dw = fl.Conv2dDesc(batch, h, w, c, ho, wo, c, cfg["kernel"][0], cfg["kernel"][1], cfg["strides"][0],
+                           cfg["strides"][1], cfg["pad_top"], cfg["pad_left"], 1, 1, 0, self.math)
+        pw = fl.Conv2dDesc(batch, ho, wo, c, ho, wo, k, 1, 1, 1, 1, 0, 0, 1, 1, fl.ACT[cfg["activation"]], self.math)
+        return dw, pw
+
+    def _dense_mkn(self, i, batch):
+        in_shape = self.shape[self.src[i][0]]
+        return batch * _prod(in_shape[:-1]), in_shape[-1], self.shape[i][-1]
+
+    def _pool_desc(self, i, batch):
+        cfg = self.nodes[i].cfg
+        h, w, c = self.shape[self.src[i][0]]
+        ho, wo, _ = self.shape[i]
+        return fl.Pool2dDesc(batch, h, w, c, ho, wo, cfg["pool"][0], cfg["pool"][1], cfg["strides"][0],
+                             cfg["strides"][1], cfg["pad_top"], cfg["pad_left"],
+                             fl.POOL_MAX if self.nodes[i].kind == "maxpool" else fl.POOL_AVG)
+
+    def _bn_view(self, i, batch):
+        shp, axis = self.shape[i], self.nodes[i].cfg["axis"] - 1
+        return batch * _prod(shp[:axis]), shp[axis], _prod(shp[axis + 1:])
+
+    # ------------------------------------------------------------------ programs
+    def _forward_program(self, batch, training):
+        L, sp, ws, wsb = self.lib, self.sp, C.c_void_p(self.ws.data_ptr()), self.ws_bytes
+        ops = []
+        add = lambda label, fn, *args: ops.append((label, fn, args))
+        for i, node in enumerate(self.nodes):
+            kind, cfg = node.kind, node.cfg
+            if kind in ("input", "flatten") or (kind == "dropout" and not training):
+                continue
+            x = self._a(self.src[i][0], training)
+            y = self._a(i, training)
+            n_out = batch * _prod(self.shape[i])
+            if kind == "conv2d":
+                d = self._conv_desc(i, batch)
+                add("conv2d_fwd", L.fnet_conv2d_fwd, d, x, self._wp(i, 0), self._wp(i, 1), y, ws, wsb, sp)
+            elif kind == "dwconv2d":
+                d = self._conv_desc(i, batch)
+                add("dwconv2d_fwd", L.fnet_dwconv2d_fwd, d, x, self._wp(i, 0), self._wp(i, 1), y, sp)
+            elif kind == "sepconv2d":
+                dw, pw = self._sep_descs(i, batch)
+                mid = C.c_void_p(self.aux[i][0].data_ptr())
+                add("dwconv2d_fwd", L.fnet_dwconv2d_fwd, dw, x, self._wp(i, 0), None, mid, sp)
+                add("conv2d_fwd", L.fnet_conv2d_fwd, pw, mid, self._wp(i, 1), self._wp(i, 2), y, ws, wsb, sp)
+            elif kind == "dense":
+                m, k, n = self._dense_mkn(i, batch)
+                add("dense_fwd", L.fnet_dense_fwd, m, k, n, fl.ACT[cfg["activation"]], self.math, x, self._wp(i, 0),
+                    self._wp(i, 1), y, ws, wsb, sp)
+            elif kind in ("maxpool", "avgpool"):
+                arg = C.c_void_p(self.aux[i].data_ptr()) if kind == "maxpool" and training else None
+                add("pool2d_fwd", L.fnet_pool2d_fwd, self._pool_desc(i, batch), x, y, arg, sp)
+            elif kind == "gap":
+                h, w, c = self.shape[self.src[i][0]]
+                add("gap_fwd", L.fnet_gap_fwd, batch, h * w, c, x, y, sp)
+            elif kind == "dropout":
+                add("dropout_fwd", L.fnet_dropout_fwd, n_out, cfg["rate"], self.dropout_seed, i,
+                    C.c_void_p(self.state.data_ptr()), x, y, sp)
+            elif kind == "bn":
+                outer, a, inner = self._bn_view(i, batch)
+                if training:
+                    mean, rstd = self.aux[i]
+                    add("bn_fwd_train", L.fnet_bn_fwd_train, outer, a, inner, cfg["epsilon"], cfg["momentum"], x,
+                        self._wp(i, 0), self._wp(i, 1), y, C.c_void_p(mean.data_ptr()), C.c_void_p(rstd.data_ptr()),
+                        self._wp(i, 2), self._wp(i, 3), ws, wsb, sp)
+                else:
+                    add("bn_fwd_infer", L.fnet_bn_fwd_infer, outer, a, inner, cfg["epsilon"], x, self._wp(i, 0),
+                        self._wp(i, 1), self._wp(i, 2), self._wp(i, 3), y, sp)
+            elif kind == "act":
+                cols = self.shape[i][-1]
+                add("act_fwd", L.fnet_act_fwd, fl.ACT[cfg["activation"]], n_out // cols, cols, x, y, sp)
+            elif kind in ("add", "mul"):
+                fn = L.fnet_add_fwd if kind == "add" else L.fnet_mul_fwd
+                add(kind + "_fwd", fn, n_out, x, self._a(self.src[i][1], training), y, sp)
+            elif kind == "concat":
+                axis = cfg["axis"] - 1
+                sa, sb = self.shape[self.src[i][0]], self.shape[self.src[i][1]]
+                outer, inner = batch * _prod(sa[:axis]), _prod(sa[axis + 1:])
+                ra, rb = sa[axis], sb[axis]
+                add("concat_fwd", L.fnet_copy_rows, outer, ra, 0, ra + rb, 0, ra, inner, x, y, 0, sp)
+                add("concat_fwd", L.fnet_copy_rows, outer, rb, 0, ra + rb, ra, rb, inner,
+                    self._a(self.src[i][1], training), y, 0, sp)
+            elif kind == "pad":
+                h, w, c = self.shape[self.src[i][0]]
+                add("pad2d_fwd", L.fnet_pad2d_fwd, batch, h, w, c, cfg["pad"][0], cfg["pad"][1], x, y, sp)
+            else:
+                raise NotImplementedError(kind)
+        return ops
+
+    def _needs_grad(self):
+        """True for nodes that have a trainable weight at or above them (a gradient must reach them)."""
+        need = [False] * len(self.nodes)
+        for i, node in enumerate(self.nodes):
+            has = any(spec.trainable for spec in node.weights)
+            need[i] = has or any(need[j] for j in self.src[i])
+        return need
+
+    def _backward_program(self, batch):
+        L, sp, ws, wsb = self.lib, self.sp, C.c_void_p(self.ws.data_ptr()), self.ws_bytes
+        ops = []
+        add = lambda label, fn, *args: ops.append((label, fn, args))
+        need = self._needs_grad()
+        written = set()
+
+        def acc_flag(j):
+            """0 for the first gradient piece that reaches buffer j, 1 for the following ones."""
+            r = self._resolve(j, True)
+            flag = 1 if r in written else 0
+            written.add(r)
+            return flag
+
+        gw = lambda i, k: self._wp(i, k, self.grads)
+        last = len(self.nodes) - 1
+        for i in range(last, 0, -1):
+            node, kind, cfg = self.nodes[i], self.nodes[i].kind, self.nodes[i].cfg
+            if kind == "flatten" or not need[i]:
+                continue
+            s0 = self.src[i][0]
+            x, y, dy = self._a(s0, True), self._a(i, True), self._g(i)
+            n_out = batch * _prod(self.shape[i])
+            want_dx = need[s0]
+            if kind in GEMM_KINDS or kind == "dwconv2d":
+                act = fl.ACT[cfg["activation"]]
+                if act and i != last:           # the head's dz comes straight from the loss kernel
+                    cols = self.shape[i][-1]
+                    add("act_bwd", L.fnet_act_bwd, act, n_out // cols, cols, y, dy, dy, 0, sp)
+            if kind == "conv2d":
+                d = self._conv_desc(i, batch)
+                add("conv2d_bwd_filter", L.fnet_conv2d_bwd_filter, d, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
+                if want_dx:
+                    add("conv2d_bwd_data", L.fnet_conv2d_bwd_data, d, dy, self._wp(i, 0), self._g(s0), acc_flag(s0), ws, wsb, sp)
+            elif kind == "dwconv2d":
+                d = self._conv_desc(i, batch)
+                add("dwconv2d_bwd_filter", L.fnet_dwconv2d_bwd_filter, d, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
+                if want_dx:
+                    add("dwconv2d_bwd_data", L.fnet_dwconv2d_bwd_data, d, dy, self._wp(i, 0), self._g(s0), acc_flag(s0), sp)
+            elif kind == "sepconv2d":
+                dw, pw = self._sep_descs(i, batch)
+                mid, gmid = (C.c_void_p(t.data_ptr()) for t in self.aux[i])
+                add("conv2d_bwd_filter", L.fnet_conv2d_bwd_filter, pw, mid, dy, gw(i, 1), gw(i, 2), ws, wsb, sp)
+                add("conv2d_bwd_data", L.fnet_conv2d_bwd_data, pw, dy, self._wp(i, 1), gmid, 0, ws, wsb, sp)
+                add("dwconv2d_bwd_filter", L.fnet_dwconv2d_bwd_filter, dw, x, gmid, gw(i, 0), None, ws, wsb, sp)
+                if want_dx:
+                    add("dwconv2d_bwd_data", L.fnet_dwconv2d_bwd_data, dw, gmid, self._wp(i, 0), self._g(s0), acc_flag(s0), sp)
+            elif kind == "dense":
+                m, k, n = self._dense_mkn(i, batch)
+                add("dense_bwd_filter", L.fnet_dense_bwd_filter, m, k, n, self.math, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
+                if want_dx:
+                    add("dense_bwd_data", L.fnet_dense_bwd_data, m, k, n, self.math, dy, self._wp(i, 0), self._g(s0),
+                        acc_flag(s0), ws, wsb, sp)
+            elif kind == "bn":
+                # dgamma/dbeta are always owed; when nothing upstream trains, dx lands on dy in place
+                outer, a, inner = self._bn_view(i, batch)
+                mean, rstd = self.aux[i]
+                dx, flag = (self._g(s0), acc_flag(s0)) if want_dx else (dy, 0)
+                add("bn_bwd", L.fnet_bn_bwd, outer, a, inner, x, dy, self._wp(i, 0), C.c_void_p(mean.data_ptr()),
+                    C.c_void_p(rstd.data_ptr()), dx, gw(i, 0), gw(i, 1), flag, ws, wsb, sp)
+            elif not want_dx:
+                continue
+            elif kind in ("maxpool", "avgpool"):
+                arg = C.c_void_p(self.aux[i].data_ptr()) if kind == "maxpool" else None
+                add("pool2d_bwd", L.fnet_pool2d_bwd, self._pool_desc(i, batch), dy, arg, self._g(s0), acc_flag(s0), sp)
+            elif kind == "gap":
+                h, w, c = self.shape[s0]
+                add("gap_bwd", L.fnet_gap_bwd, batch, h * w, c, dy, self._g(s0), acc_flag(s0), sp)
+            elif kind == "dropout":
+                add("dropout_bwd", L.fnet_dropout_bwd, n_out, cfg["rate"], self.dropout_seed, i,
+                    C.c_void_p(self.state.data_ptr()), dy, self._g(s0), acc_flag(s0), sp)
+            elif kind == "act":
+                cols = self.shape[i][-1]
+                add("act_bwd", L.fnet_act_bwd, fl.ACT[cfg["activation"]], n_out // cols, cols, y, dy, self._g(s0),
+                    acc_flag(s0), sp)
+            elif kind == "add":
+                for j in self.src[i]:
+                    if need[j]:
+                        add("add_bwd", L.fnet_accumulate, n_out, dy, self._g(j), acc_flag(j), sp)
+            elif kind == "mul":
+                a, b = self.src[i]
+                if need[a]:
+                    add("mul_bwd", L.fnet_mul_bwd, n_out, dy, self._a(b, True), self._g(a), acc_flag(a), sp)
+                if need[b]:
+                    add("mul_bwd", L.fnet_mul_bwd, n_out, dy, self._a(a, True), self._g(b), acc_flag(b), sp)
+            elif kind == "concat":
+                axis = cfg["axis"] - 1
+                a, b = self.src[i]
+                sa, sb = self.shape[a], self.shape[b]
+                outer, inner = batch * _prod(sa[:axis]), _prod(sa[axis + 1:])
+                ra, rb = sa[axis], sb[axis]
+                if need[a]:
+                    add("concat_bwd", L.fnet_copy_rows, outer, ra + rb, 0, ra, 0, ra, inner, dy, self._g(a), acc_flag(a), sp)
+                if need[b]:
+                    add("concat_bwd", L.fnet_copy_rows, outer, ra + rb, ra, rb, 0, rb, inner, dy, self._g(b), acc_flag(b), sp)
+            elif kind == "pad":
+                h, w, c = self.shape[s0]
+                add("pad2d_bwd", L.fnet_pad2d_bwd, batch, h, w, c, cfg["pad"][0], cfg["pad"][1], dy, self._g(s0), acc_flag(s0), sp)
+            else:
+                raise NotImplementedError(kind)
+        return ops
+
+    def _loss_op(self, batch, with_grad):
+        L = self.lib
+        last = len(self.nodes) - 1
+        dz = self._g(last) if with_grad else None
+        return ("softmax_cce", L.fnet_softmax_cce,
+                (batch, self.n_out, self._a(last, with_grad), C.c_void_p(self.yb.data_ptr()), 1.0 / batch, dz,
+                 C.c_void_p(self.loss_sum.data_ptr()), C.c_void_p(self.correct.data_ptr()), self.sp))
+
+    def _optimizer_op(self):
+        opt, L = self.net.optimizer, self.lib
+        st = C.c_void_p(self.state.data_ptr())
+        args4 = [C.c_void_p(t.data_ptr()) for t in (self.params, self.grads, self.adam_m, self.adam_v)]
+        if opt.kind == "adam":
+            return ("adam_step", L.fnet_adam_step, (self.n_params, args4[0], args4[1], args4[2], args4[3], st,
+                                                    opt.beta_1, opt.beta_2, opt.epsilon, self.sp))
+        return ("sgd_step", L.fnet_sgd_step, (self.n_params, args4[0], args4[1], args4[2], st, opt.momentum,
+                                              int(opt.nesterov), self.sp))
+
+    def _build_program(self, kind, batch):
+        """kind: 'train' / 'eval' read the resident dataset through the permutation; '*_fed' expect xb/yb filled."""
+        L, sp = self.lib, self.sp
+        training = kind.startswith("train")
+        state = self.state if training else self.state_eval
+        st = C.c_void_p(state.data_ptr())
+        ops = []
+        if training:
+            opt = self.net.optimizer
+            b1, b2 = (opt.beta_1, opt.beta_2) if opt.kind == "adam" else (0.9, 0.999)
+            ops.append(("step_begin", L.fnet_step_begin, (st, b1, b2, sp)))
+        if not kind.endswith("_fed"):
+            xdev, ydev, perm = self.data[kind.split("_")[0]]
+            row = _prod(self.shape[0])
+            ops.append(("gather_rows", L.fnet_gather_rows, (batch, row, C.c_void_p(perm.data_ptr()), st,
+                                                            C.c_void_p(xdev.data_ptr()), C.c_void_p(self.act[0].data_ptr()), sp)))
+            ops.append(("gather_rows", L.fnet_gather_rows, (batch, self.n_out, C.c_void_p(perm.data_ptr()), st,
+                                                            C.c_void_p(ydev.data_ptr()), C.c_void_p(self.yb.data_ptr()), sp)))
+        ops += self._forward_program(batch, training)
+        ops.append(self._loss_op(batch, training))
+        if training:
+            ops += self._backward_program(batch)
+            ops.append(self._optimizer_op())
+        ops.append(("step_end", L.fnet_step_end, (st, batch, sp)))
+        return ops
+
+    def _run_ops(self, ops):
+        if self.timeline is None:
+            for _, fn, args in ops:
+                fn(*args)
+            return
+        for label, fn, args in ops:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(self.stream)
+            fn(*args)
+            e1.record(self.stream)
+            self.timeline.append((label, e0, e1))
+
+    @staticmethod
+    def op_work(label, args):
+        """Algorithmic (flops, bytes) of one launch, the figures of SURVEY.md section 8(d) used for rooflines."""
+        f = b = 0
+        if label.startswith("conv2d") or label.startswith("dwconv2d"):
+            d = args[0]
+            m_out, m_in = d.batch * d.out_h * d.out_w, d.batch * d.in_h * d.in_w
+            taps = d.kh * d.kw
+            if label.startswith("conv2d"):
+                f = 2 * m_out * d.out_c * taps * d.in_c
+                b = 4 * (m_in * d.in_c + m_out * d.out_c + taps * d.in_c * d.out_c)
+            else:
+                f = 2 * m_out * d.in_c * taps
+                b = 4 * (m_in * d.in_c + m_out * d.in_c + taps * d.in_c)
+        elif label.startswith("dense"):
+            m, k, n = args[0], args[1], args[2]
+            f, b = 2 * m * k * n, 4 * (m * k + k * n + m * n)
+        elif label.startswith("pool2d"):
+            d = args[0]
+            b = 4 * d.channels * d.batch * (d.in_h * d.in_w + d.out_h * d.out_w) + d.batch * d.out_h * d.out_w * d.channels
+        elif label.startswith("gap"):
+            b = 4 * args[0] * args[2] * (args[1] + 1)
+        elif label.startswith("bn_"):
+            elems = args[0] * args[1] * args[2]
+            b = 4 * elems * {"bn_fwd_train": 3, "bn_fwd_infer": 2, "bn_bwd": 5}[label]
+        elif label in ("act_fwd", "act_bwd"):
+            b = 4 * args[1] * args[2] * (2 if label == "act_fwd" else 3)
+        elif label.startswith("dropout"):
+            b = 4 * 2 * args[0]
+        elif label in ("add_fwd", "mul_fwd", "mul_bwd"):
+            b = 4 * 3 * args[0]
+        elif label == "add_bwd":
+            b = 4 * 2 * args[0]
+        elif label.startswith("concat"):
+            b = 4 * 2 * args[0] * args[5] * args[6]
+        elif label.startswith("pad2d"):
+            b = 4 * 2 * args[0] * args[1] * args[2] * args[3]
+        elif label == "softmax_cce":
+            b = 4 * 3 * args[0] * args[1]
+        elif label == "adam_step":
+            b = 28 * args[0]
+        elif label == "sgd_step":
+            b = 16 * args[0]
+        elif label == "gather_rows":
+            b = 4 * 2 * args[0] * args[1]
+        return f, b
+
+    def profile_steps(self, kind, batch, steps, warmup=3):
+        """Run `steps` eager steps with a CUDA-event pair around every launch (on the launching stream).
+
+        Returns {label: dict(launches, ms_total, flops, bytes)}; used by bench.py for the roofline object.
+        """
+        for _ in range(warmup):
+            self._step(kind, batch)
+        self.stream.synchronize()
+        self.timeline = []
+        try:
+            # park the stream for ~25 ms so the host enqueues ahead and launches run back to back:
+            # otherwise every event pair would also time the host's launch latency
+            with torch.cuda.stream(self.stream):
+                torch.cuda._sleep(int(5e7))
+            for _ in range(steps):
+                self._step(kind, batch)
+            self.stream.synchronize()
+            ops = self.programs[(kind, batch)]
+            table = {}
+            for n, (label, e0, e1) in enumerate(self.timeline):
+                row = table.setdefault(label, dict(launches=0, ms_total=0.0, flops=0, bytes=0))
+                fl_, by_ = self.op_work(label, ops[n % len(ops)][2])
+                row["launches"] += 1
+                row["ms_total"] += e0.elapsed_time(e1)
+                row["flops"] += fl_
+                row["bytes"] += by_
+        finally:
+            self.timeline = None
+        return table
+
+    def _drop_graphs(self):
+        for g in self.graphs.values():
+            self.lib.fnet_graph_destroy(g)
+        self.graphs, self.programs = {}, {}
+
+    def _step(self, kind, batch):
+        """Enqueue one step (captured CUDA graph after the first, eager run)."""
+        key = (kind, batch)
+        ops = self.programs.get(key)
+        if ops is None:
+            ops = self.programs[key] = self._build_program(kind, batch)
+            self.launches_per_step = getattr(self, "launches_per_step", {})
+            self.launches_per_step[key] = len(ops)
+        if not self.use_graphs or self.timeline is not None:
+            self._run_ops(ops)
+            return
+        graph = self.graphs.get(key)
+        if graph is None:
+            # capture without executing: the captured launches run for the first time at graph launch
+            self.lib.fnet_graph_begin(self.sp)
+            try:
+                for _, fn, args in ops:
+                    fn(*args)
+            finally:
+                handle = C.c_void_p()
+                self.lib.fnet_graph_end(self.sp, C.byref(handle))
+            graph = self.graphs[key] = handle
+        self.lib.fnet_graph_launch(graph, self.sp)
+
+    # ------------------------------------------------------------------ host-side loop pieces
+    def _sync_lr(self):
+        lr = float(self.net.optimizer.lr)
+        if lr != self._lr_on_device:
+            self._lr_host[0] = lr
+            with torch.cuda.stream(self.stream):
+                self.state[2:3].view(torch.float32).copy_(self._lr_host, non_blocking=True)
+            self.stream.synchronize()      # the pinned scalar may be rewritten by the next call
+            self._lr_on_device = lr
+
+    def _set_data(self, split, x, y):
+        self.data = getattr(self, "data", {})
+        xd = DeviceDataCache.get(x, self.device)
+        yd = DeviceDataCache.get(y, self.device)
+        old = self.data.get(split)
+        if old is not None and old[0] is xd and old[1] is yd:
+            return old
+        n = xd.shape[0]
+        perm = torch.arange(n, dtype=torch.int32, device=self.device)
+        for key in [k for k in self.programs if k[0] == split]:
+            if key in self.graphs:
+                self.lib.fnet_graph_destroy(self.graphs.pop(key))
+            self.programs.pop(key)
+        self.data[split] = (xd, yd, perm)
+        return self.data[split]
+
+    def _read_metrics(self, n):
+        self.stream.synchronize()
+        return float(self.loss_sum.item()) / n, int(self.correct.item()) / n
+
+    def _zero_metrics(self, state):
+        with torch.cuda.stream(self.stream):
+            self.loss_sum.zero_()
+            self.correct.zero_()
+            state[1:2].zero_()
+
+    def _check_xy(self, x, y):
+        x, y = np.asarray(x), np.asarray(y)
+        if tuple(x.shape[1:]) != self.shape[0]:
+            raise ValueError("expected inputs of shape %r, got %r" % (self.shape[0], tuple(x.shape[1:])))
+        if y.ndim != 2 or y.shape[1] != self.n_out or y.shape[0] != x.shape[0]:
+            raise ValueError("expected one-hot targets of shape (%d, %d), got %r" % (x.shape[0], self.n_out, y.shape))
+        return x, y
+
+    def eval_batch_size(self, n):
+        """Inference batch: results do not depend on it, so use large batches bounded by activation size."""
+        widest = max(_prod(s) for s in self.shape)
+        cap = max(32, (256 << 20) // (4 * widest))
+        return int(min(n, cap, 1000))
+
+    def evaluate(self, x, y, batch_size=32):
+        """keras Model.evaluate -> [loss, accuracy] in inference phase (tensorflow_generator.py:270)."""
+        x, y = self._check_xy(x, y)
+        n = x.shape[0]
+        eb = self.eval_batch_size(n)
+        self._ensure_capacity(max(eb, self.capacity))
+        self._set_data("eval", x, y)
+        with torch.cuda.stream(self.stream):
+            self.data["eval"][2].copy_(torch.arange(n, dtype=torch.int32, device=self.device))
+        self._zero_metrics(self.state_eval)
+        done = 0
+        while done < n:
+            b = min(eb, n - done)
+            self._step("eval", b)
+            done += b
+        loss, acc = self._read_metrics(n)
+        return [loss, acc]
+
+    def predict(self, x, batch_size=32):
+        x = np.asarray(x, dtype=np.float32)
+        n = x.shape[0]
+        eb = self.eval_batch_size(n)
+        self._ensure_capacity(max(eb, self.capacity))
+        out = np.empty((n, self.n_out), np.float32)
+        last = len(self.nodes) - 1
+        for lo in range(0, n, eb):
+            b = min(eb, n - lo)
+            with torch.cuda.stream(self.stream):
+                self.act[0][:b].copy_(torch.from_numpy(np.ascontiguousarray(x[lo: lo + b])))
+                self._run_ops(self._forward_program(b, False))
+                self.stream.synchronize()
+                out[lo: lo + b] = self.act[self._resolve(last, False)][:b].cpu().numpy()
+        return out
+
+    def train_on_batch(self, x, y):
+        """keras Model.train_on_batch with HOST buffers: H2D copy, one optimisation step, D2H of (loss, acc)."""
+        if self.net.optimizer is None:
+            raise RuntimeError("compile() the model first")
+        b = x.shape[0]
+        self._ensure_capacity(max(b, self.capacity))
+        self._sync_lr()
+        xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+        yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
+        with torch.cuda.stream(self.stream):
+            self.loss_sum.zero_()
+            self.correct.zero_()
+            self.act[0][:b].copy_(xt, non_blocking=True)
+            self.yb[:b].copy_(yt, non_blocking=True)
+        self._step("train_fed", b)
+        loss, acc = self._read_metrics(b)
+        return [loss, acc]
+
+    def fit(self, x, y, batch_size=32, epochs=1, validation_data=None, shuffle=True, callbacks=(), verbose=0,
+            permutations=None, initial_epoch=0, **_):
+        """keras Model.fit semantics: see module docstring.  ``permutations[e]`` overrides the shuffle (tests)."""
+        from .callbacks import History, Callback
+        if self.net.optimizer is None:
+            raise RuntimeError("compile() the model first")
+        x, y = self._check_xy(x, y)
+        n = x.shape[0]
+        batch_size = int(min(batch_size, n))
+        val = None
+        if validation_data is not None:
+            val = self._check_xy(validation_data[0], validation_data[1])
+        cap = max(batch_size, self.eval_batch_size(val[0].shape[0]) if val else 0, self.capacity)
+        self._ensure_capacity(cap)
+        self._set_data("train", x, y)
+        perm_dev = self.data["train"][2]
+        history = History()
+        cbs = [history] + list(callbacks)
+        per_batch = [cb for cb in cbs if getattr(type(cb), "on_batch_end", None) not in (None, Callback.on_batch_end)]
+        for cb in cbs:
+            cb.set_model(self.net)
+            cb.set_params({"epochs": epochs, "batch_size": batch_size, "samples": n, "steps": -(-n // batch_size)})
+        self.net.stop_training = False
+        for cb in cbs:
+            cb.on_train_begin({})
+        rng = np.random.default_rng((self.seed + 0x5EED) & 0xFFFFFFFF)
+        steps = -(-n // batch_size)
+        t_start = time.time()
+        for epoch in range(initial_epoch, epochs):
+            for cb in cbs:
+                cb.on_epoch_begin(epoch, {})
+            if permutations is not None:
+                order = np.asarray(permutations[epoch], dtype=np.int32)
+            elif shuffle:
+                order = rng.permutation(n).astype(np.int32)
+            else:
+                order = np.arange(n, dtype=np.int32)
+            with torch.cuda.stream(self.stream):
+                perm_dev.copy_(torch.from_numpy(order))
+            self._zero_metrics(self.state)
+            for step in range(steps):
+                b = min(batch_size, n - step * batch_size)
+                self._sync_lr()
+                self._step("train", b)
+                for cb in per_batch:
+                    cb.on_batch_end(step, {"batch": step, "size": b})
+            loss, acc = self._read_metrics(n)
+            logs = {"loss": loss, "acc": acc}
+            if val is not None:
+                logs["val_loss"], logs["val_acc"] = self.evaluate(val[0], val[1])
+            for cb in cbs:
+                cb.on_epoch_end(epoch, logs)
+            if verbose:
+                print("Epoch %d/%d - %.1fs - %s" % (epoch + 1, epochs, time.time() - t_start,
+                                                    " - ".join("%s: %.4f" % kv for kv in logs.items())))
+            if self.net.stop_training:
+                break
+        for cb in cbs:
+            cb.on_train_end({})
+        result = HistoryResult()
+        result.history, result.epoch = history.history, history.epoch
+        return result
+
+    def fit_generator(self, generator, steps_per_epoch=None, epochs=1, validation_data=None, callbacks=(), verbose=0, **kw):
+        """The augmentation path of helpers.py:115-167; the generator must expose the arrays it flows from."""
+        if not hasattr(generator, "x") or not hasattr(generator, "y"):
+            raise NotImplementedError("fit_generator needs a featurenet_b200 data generator (device-side augmentation)")
+        return self.fit(generator.x, generator.y, batch_size=generator.batch_size, epochs=epochs,
+                        validation_data=validation_data, callbacks=callbacks, verbose=verbose, **kw)
+
+    def release(self):
+        self.stream.synchronize()
+        self._drop_graphs()
+        for name in ("act", "gact", "aux", "ws", "params", "grads", "adam_m", "adam_v", "stats", "data"):
+            if hasattr(self, name):
+                delattr(self, name)
+        self.capacity = 0

@@ -1,0 +1,216 @@
+/*
+ * fnet.h -- C ABI of libfnet.so: the sm_100a kernels behind FeatureNet's per-candidate
+ * train+evaluate path.
+ *
+ * The reference (yqtianust/FeatureNet) has no FFI layer of its own: every arithmetic step is
+ * a Keras 2.2.4 layer call executed by TensorFlow 1.12 inside `session.run`.  Each entry
+ * point below therefore names the reference call site whose device work it replaces
+ * (paths relative to the reference tree).  INTEGRATION.md shows the ctypes binding that the
+ * Python host side (featurenet_b200/lib.py) uses.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name says host; tensors are fp32, NHWC,
+ *     dense, allocated and owned by the caller; nothing here allocates or frees memory;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing
+ *     synchronises, so every call may be captured into a CUDA graph;
+ *   - functions return 0 on success and a negative code otherwise; fnet_last_error() returns
+ *     the thread-local message of the last failure; no exception crosses the boundary;
+ *   - `accumulate != 0` means "add into the output" (a tensor with several consumers
+ *     receives its gradient in several pieces), 0 means "overwrite";
+ *   - workspaces are caller-provided: ask fnet_*_workspace_bytes() first.
+ */
+#ifndef FNET_H
+#define FNET_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FNET_VERSION 100
+
+enum { FNET_OK = 0, FNET_ERR_ARG = -1, FNET_ERR_CUDA = -2, FNET_ERR_WORKSPACE = -3, FNET_ERR_UNSUPPORTED = -4 };
+
+/* keras.activations used by model/input.py:190,294-298 and model/operation.py:165 */
+enum { FNET_ACT_NONE = 0, FNET_ACT_RELU = 1, FNET_ACT_TANH = 2, FNET_ACT_SIGMOID = 3, FNET_ACT_SOFTMAX = 4 };
+
+enum { FNET_POOL_MAX = 0, FNET_POOL_AVG = 1 };
+
+/* arithmetic used by the GEMM-shaped kernels */
+enum { FNET_MATH_FP32 = 0,   /* FFMA, fp32 end to end: the parity mode                  */
+       FNET_MATH_TF32 = 1,   /* tcgen05.mma kind::tf32, fp32 accumulate in TMEM         */
+       FNET_MATH_BF16 = 2 }; /* tcgen05.mma kind::f16 (bf16 operands), fp32 accumulate  */
+
+int fnet_version(void);
+const char *fnet_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Convolution.  Replaces keras.layers.Conv2D (model/input.py:294; the channel-aligning
+ * "Reg_" convolution of model/operation.py:186) and, with kh = kw = 1, the pointwise half of
+ * SeparableConv2D (model/input.py:296).  x[B,H,W,C], w[kh,kw,C,K] (HWIO), y[B,Ho,Wo,K].
+ * Padding is explicit (TF SAME puts the smaller half first): out = (in + pads - k_eff)/stride + 1.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+    int32_t batch, in_h, in_w, in_c;
+    int32_t out_h, out_w, out_c;
+    int32_t kh, kw, stride_h, stride_w, pad_top, pad_left, dil_h, dil_w;
+    int32_t act;  /* FNET_ACT_*: fused into the forward epilogue (softmax runs as a second kernel) */
+    int32_t math; /* FNET_MATH_* */
+} fnet_conv2d_desc;
+
+size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d);
+/* y = act(conv(x, w) + bias); bias may be NULL */
+int fnet_conv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w, const float *bias, float *y,
+                    void *ws, size_t ws_bytes, void *stream);
+/* dx (+)= conv_transpose(dz, w), dz = dL/d(pre-activation) */
+int fnet_conv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const float *w, float *dx, int accumulate,
+                         void *ws, size_t ws_bytes, void *stream);
+/* dw = x (*) dz, dbias = column sums of dz (dbias may be NULL); deterministic split reduction */
+int fnet_conv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const float *dz, float *dw, float *dbias,
+                           void *ws, size_t ws_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Dense.  Replaces keras.layers.Dense on the last axis of a rank-2 or rank-4 tensor
+ * (model/input.py:190) and the classifier head (model/keras_model.py:124).
+ * x[M,K], w[K,N], y[M,N]; M = product of the leading axes.
+ * ------------------------------------------------------------------------------------------ */
+size_t fnet_dense_workspace_bytes(int64_t m, int64_t k, int64_t n);
+int fnet_dense_fwd(int64_t m, int64_t k, int64_t n, int act, int math, const float *x, const float *w,
+                   const float *bias, float *y, void *ws, size_t ws_bytes, void *stream);
+int fnet_dense_bwd_data(int64_t m, int64_t k, int64_t n, int math, const float *dz, const float *w, float *dx,
+                        int accumulate, void *ws, size_t ws_bytes, void *stream);
+int fnet_dense_bwd_filter(int64_t m, int64_t k, int64_t n, int math, const float *x, const float *dz, float *dw,
+                          float *dbias, void *ws, size_t ws_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Depthwise convolution, depth multiplier 1.  Replaces keras.layers.DepthwiseConv2D
+ * (model/input.py:298) and the depthwise half of SeparableConv2D (model/input.py:296).
+ * x[B,H,W,C], w[kh,kw,C], y[B,Ho,Wo,C].  Memory-bound: 2*kh*kw flops per element moved.
+ * ------------------------------------------------------------------------------------------ */
+size_t fnet_dwconv2d_workspace_bytes(const fnet_conv2d_desc *d);
+int fnet_dwconv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w, const float *bias, float *y,
+                      void *stream);
+int fnet_dwconv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const float *w, float *dx, int accumulate,
+                           void *stream);
+int fnet_dwconv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const float *dz, float *dw, float *dbias,
+                             void *ws, size_t ws_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Pooling.  Replaces MaxPooling2D / AveragePooling2D / GlobalAveragePooling2D
+ * (model/input.py:233,237,240).  Average divides by the number of in-bounds taps; the max
+ * backward routes to the first maximum in row-major window order (argmax holds that tap).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+    int32_t batch, in_h, in_w, channels;
+    int32_t out_h, out_w;
+    int32_t kh, kw, stride_h, stride_w, pad_top, pad_left;
+    int32_t kind; /* FNET_POOL_* */
+} fnet_pool2d_desc;
+
+int fnet_pool2d_fwd(const fnet_pool2d_desc *d, const float *x, float *y, uint8_t *argmax /* max only, may be NULL */,
+                    void *stream);
+int fnet_pool2d_bwd(const fnet_pool2d_desc *d, const float *dy, const uint8_t *argmax, float *dx, int accumulate,
+                    void *stream);
+int fnet_gap_fwd(int32_t batch, int32_t hw, int32_t channels, const float *x, float *y, void *stream);
+int fnet_gap_bwd(int32_t batch, int32_t hw, int32_t channels, const float *dy, float *dx, int accumulate,
+                 void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Batch normalisation over axis 1.  Replaces keras.layers.BatchNormalization(axis=1)
+ * (model/operation.py:142,150): the tensor is viewed as [outer, A, inner] (NHWC rank 4:
+ * outer=B, A=H, inner=W*C; rank 2: outer=B, A=features, inner=1); statistics are per a over
+ * outer*inner elements.  Training normalises with the biased batch variance and feeds
+ * var*n/(n-(1+eps)) to the moving variance (Keras 2.2.x).
+ * ws: fnet_bn_workspace_bytes(A) bytes.
+ * ------------------------------------------------------------------------------------------ */
+size_t fnet_bn_workspace_bytes(int32_t a);
+int fnet_bn_fwd_train(int32_t outer, int32_t a, int32_t inner, float eps, float momentum, const float *x,
+                      const float *gamma, const float *beta, float *y, float *save_mean, float *save_rstd,
+                      float *moving_mean, float *moving_var, void *ws, size_t ws_bytes, void *stream);
+int fnet_bn_fwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const float *x, const float *gamma,
+                      const float *beta, const float *moving_mean, const float *moving_var, float *y,
+                      void *stream);
+int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,
+                const float *save_mean, const float *save_rstd, float *dx, float *dgamma, float *dbeta,
+                int accumulate, void *ws, size_t ws_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Element-wise and data-movement ops.
+ * act:      keras.layers.Activation (model/operation.py:165); softmax is over rows of `cols`.
+ * dropout:  keras.layers.Dropout / tf.nn.dropout (model/operation.py:114): keep <=> philox word
+ *           >= ceil(rate*2^32); element i uses word i%4 of philox4x32-10(counter=(i/4, *step,
+ *           stream_id, 0), key=seed); kept values are scaled by 1/(1-rate).  The backward
+ *           recomputes the mask.  `step` is a device int32 (the optimizer iteration).
+ * add/mul:  keras.layers.Add / Multiply (model/operation.py:222,248).
+ * rows:     copy `rows` rows of `inner` floats between [batch, *_rows, inner] tensors:
+ *           Concatenate(axis=1) forward/backward (model/operation.py:238).
+ * pad2d:    keras.layers.ZeroPadding2D (model/operation.py:136).
+ * ------------------------------------------------------------------------------------------ */
+int fnet_act_fwd(int act, int64_t rows, int64_t cols, const float *x, float *y, void *stream);
+/* dx (+)= dy * act'(.) given the activation OUTPUT y */
+int fnet_act_bwd(int act, int64_t rows, int64_t cols, const float *y, const float *dy, float *dx, int accumulate,
+                 void *stream);
+int fnet_dropout_fwd(int64_t n, float rate, uint64_t seed, uint32_t stream_id, const int32_t *step,
+                     const float *x, float *y, void *stream);
+int fnet_dropout_bwd(int64_t n, float rate, uint64_t seed, uint32_t stream_id, const int32_t *step,
+                     const float *dy, float *dx, int accumulate, void *stream);
+int fnet_add_fwd(int64_t n, const float *a, const float *b, float *y, void *stream);
+int fnet_mul_fwd(int64_t n, const float *a, const float *b, float *y, void *stream);
+/* dx (+)= dy * other */
+int fnet_mul_bwd(int64_t n, const float *dy, const float *other, float *dx, int accumulate, void *stream);
+/* dst (+)= src */
+int fnet_accumulate(int64_t n, const float *src, float *dst, int accumulate, void *stream);
+int fnet_copy_rows(int32_t batch, int32_t src_rows, int32_t src_row0, int32_t dst_rows, int32_t dst_row0,
+                   int32_t rows, int32_t inner, const float *src, float *dst, int accumulate, void *stream);
+int fnet_pad2d_fwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h, int32_t pad_w, const float *x,
+                   float *y, void *stream);
+int fnet_pad2d_bwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h, int32_t pad_w, const float *dy,
+                   float *dx, int accumulate, void *stream);
+int fnet_fill(int64_t n, float value, float *dst, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Loss and metric.  Replaces loss='categorical_crossentropy', metrics=['accuracy'] of
+ * tensorflow_generator.py:233-235 on the softmax output of the "out" layer
+ * (model/keras_model.py:124): per row, renormalise p, clip to [1e-7, 1-1e-7], -sum t*log p;
+ * correct <=> argmax(t) == argmax(p) (first index on ties, integer compare).
+ * Adds the batch loss to *loss_sum (double) and the number of correct rows to *correct.
+ * If dlogits != NULL also writes scale * dL/d(logits) through softmax, renormalisation and clip.
+ * ------------------------------------------------------------------------------------------ */
+int fnet_softmax_cce(int32_t batch, int32_t classes, const float *probs, const float *targets, float scale,
+                     float *dlogits, double *loss_sum, int64_t *correct, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Optimizer and loop state.  Replaces keras.optimizers.Adam(lr=1e-3) of
+ * tensorflow_generator.py:232 (and "sgd" of lenet5.py:21) as ONE launch over the flat
+ * parameter arena, plus the per-step bookkeeping that Keras does on the host.
+ * state (device, int32[8] viewed loosely): [0] t = completed iterations, [1] cursor = next
+ * sample of the epoch, [2] lr (float bits), [3] lr_t (float bits, written by step_begin).
+ * ------------------------------------------------------------------------------------------ */
+int fnet_step_begin(int32_t *state, float beta1, float beta2, void *stream);
+int fnet_step_end(int32_t *state, int32_t batch, void *stream);
+int fnet_adam_step(int64_t n, float *params, const float *grads, float *m, float *v, const int32_t *state,
+                   float beta1, float beta2, float eps, void *stream);
+int fnet_sgd_step(int64_t n, float *params, const float *grads, float *velocity, const int32_t *state,
+                  float momentum, int nesterov, void *stream);
+/* dst[i, :] = src[perm[cursor + i], :] for i < batch; replaces the host-side batch slicing of
+ * keras Model.fit(shuffle=True) (helpers.py:105-111) on a device-resident dataset */
+int fnet_gather_rows(int32_t batch, int64_t row_elems, const int32_t *perm, const int32_t *state,
+                     const float *src, float *dst, void *stream);
+/* dst = float(src) * scale : the `astype('float32') / 255` of tensorflow_generator.py:310-313 */
+int fnet_u8_to_f32(int64_t n, const uint8_t *src, float scale, float *dst, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * CUDA-graph helpers: one train step (or eval step) is captured once and replayed, which
+ * replaces one `session.run` per step.
+ * ------------------------------------------------------------------------------------------ */
+int fnet_graph_begin(void *stream);
+int fnet_graph_end(void *stream, void **graph_exec_out);
+int fnet_graph_launch(void *graph_exec, void *stream);
+int fnet_graph_destroy(void *graph_exec);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FNET_H */

@@ -335,7 +335,8 @@ def dropout_keep_mask(n, rate, seed, stream, step):
 
 def dropout_threshold(rate):
     import math
-    return min(int(math.ceil(float(rate) * 4294967296.0)), 4294967296)
+    # the rate crosses the C ABI as a float: the threshold is taken from its fp32 value
+    return min(int(math.ceil(float(np.float32(rate)) * 4294967296.0)), 4294967296)
 
 
 # ----------------------------------------------------------------------------- merges / reshapes

@@ -1,0 +1,239 @@
+"""Whole-candidate parity: the CUDA engine vs the oracle network on identical weights, batches,
+permutations and dropout masks -- forward, loss, every weight gradient, Adam steps, the Keras
+fit loop (callbacks, best-checkpoint restore) and evaluate; plus properties at BASELINE sizes.
+"""
+import contextlib
+import io
+
+import numpy as np
+import pytest
+
+from oracle import ops
+from oracle.net import OracleNet
+
+from tests.util import init_weights, build_template, tiny_graphs
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4           # north_star: per-layer forward/backward within 1e-4 relative in fp32
+
+
+def relerr(got, want):
+    want = np.asarray(want, np.float64)
+    scale = np.abs(want).max()
+    return np.abs(np.asarray(got, np.float64) - want).max() / (scale if scale > 0 else 1.0)
+
+
+def flat(weights):
+    return [w for ws in weights for w in ws]
+
+
+def engine_for(net, weights, optimizer=None):
+    from featurenet_b200.optimizers import Adam
+    net.compile(loss="categorical_crossentropy", metrics=["accuracy"], optimizer=optimizer or Adam(lr=1e-3))
+    eng = net._need_engine()
+    eng.set_weights([w.astype(np.float32) for w in flat(weights)])
+    return eng
+
+
+def oracle_masks(eng, rows, step, batch):
+    masks = {}
+    for i, row in enumerate(rows):
+        if row["class"] == "Dropout":
+            n = batch * int(np.prod(row["out_shape"][1:]))
+            masks[i] = ops.dropout_keep_mask(n, row["cfg"]["rate"], eng.dropout_seed, i, step)
+    return masks
+
+
+def grads_from_engine(eng):
+    torch.cuda.synchronize()
+    g = eng.grads.cpu().numpy()
+    out = {}
+    for (i, k), (off, size) in eng.w_off.items():
+        out[(i, k)] = g[off: off + size].reshape(eng.nodes[i].weights[k].shape)
+    return out
+
+
+GRAPHS = sorted(tiny_graphs().keys()) + ["lenet5@mnist", "keras@cifar"]
+
+
+def make_net(name):
+    with contextlib.redirect_stdout(io.StringIO()):
+        if "@" in name:
+            tpl, ds = name.split("@")
+            return build_template(tpl, (28, 28, 1) if ds == "mnist" else (32, 32, 3))
+        return tiny_graphs()[name]()
+
+
+@pytest.mark.parametrize("name", GRAPHS)
+def test_forward_backward_and_adam_match_the_oracle(name):
+    net = make_net(name)
+    rows = net.describe()
+    rng = np.random.default_rng(21)
+    weights = init_weights(net, rng, jitter=True)
+    weights32 = [[w.astype(np.float32).astype(np.float64) for w in ws] for ws in weights]
+    batch = 4 if name == "keras@cifar" else 6
+    classes = net.output_shape[-1]
+    eng = engine_for(net, weights)
+    oracle = OracleNet(rows, weights32)
+    for step in range(3):
+        x = rng.random((batch,) + tuple(net.input_shape[1:])).astype(np.float32)
+        t = np.eye(classes, dtype=np.float32)[rng.integers(0, classes, batch)]
+        masks = oracle_masks(eng, rows, step, batch)
+        loss_o, correct_o = oracle.train_step(x.astype(np.float64), t.astype(np.float64), float(np.float32(1e-3)), masks)
+        loss_e, acc_e = eng.train_on_batch(x, t)
+        assert abs(loss_e * batch - loss_o) <= TOL * max(1.0, abs(loss_o)), "loss at step %d" % step
+        assert round(acc_e * batch) == correct_o
+        # activations of every layer (engine buffers hold the training-phase forward of this step)
+        torch.cuda.synchronize()
+        for i, row in enumerate(rows):
+            got = eng.act[eng._resolve(i, True)][:batch].cpu().numpy().reshape(oracle.outs[i].shape)
+            assert relerr(got, oracle.outs[i]) <= TOL, "layer %d (%s) forward, step %d" % (i, row["class"], step)
+        got_grads = grads_from_engine(eng)
+        for (i, k), g in got_grads.items():
+            assert relerr(g, oracle.last_grads[i][k]) <= TOL, "grad of layer %d (%s) weight %d, step %d" % (
+                i, rows[i]["class"], k, step)
+        got_w = eng.get_weights()
+        for a, b in zip(got_w, flat(oracle.weights)):
+            assert relerr(a, b) <= TOL, "weights after step %d" % step
+
+
+def test_inference_phase_uses_moving_statistics_and_no_dropout():
+    net = make_net("dropout_pad_act_gap")
+    rng = np.random.default_rng(5)
+    weights = init_weights(net, rng, jitter=True)
+    eng = engine_for(net, weights)
+    oracle = OracleNet(net.describe(), [[w.astype(np.float32).astype(np.float64) for w in ws] for ws in weights])
+    x = rng.random((10,) + tuple(net.input_shape[1:])).astype(np.float32)
+    t = np.eye(3, dtype=np.float32)[rng.integers(0, 3, 10)]
+    loss_o, acc_o = oracle.evaluate(x.astype(np.float64), t.astype(np.float64))
+    loss_e, acc_e = eng.evaluate(x, t)
+    assert abs(loss_e - loss_o) <= TOL * max(1.0, abs(loss_o)) and acc_e == acc_o
+    assert relerr(eng.predict(x), oracle.forward(x.astype(np.float64))[-1]) <= TOL
+
+
+def small_problem(rng, n, shape, classes):
+    x = rng.random((n,) + shape).astype(np.float32)
+    teacher = rng.standard_normal((int(np.prod(shape)), classes))
+    y = np.eye(classes, dtype=np.float32)[np.argmax((x.reshape(n, -1) - 0.5) @ teacher, axis=1)]
+    return x, y
+
+
+@pytest.mark.parametrize("name", ["pools_and_bn", "dropout_pad_act_gap"])
+def test_fit_loop_matches_the_oracle_loop(name):
+    """helpers.train_model semantics end to end: 4 epochs, batch 32 with a ragged last batch, validation,
+    best-val_loss restore -- same permutations and dropout masks on both sides."""
+    from helpers import train_model
+    net = make_net(name)
+    rows = net.describe()
+    rng = np.random.default_rng(33)
+    shape = tuple(net.input_shape[1:])
+    x, y = small_problem(rng, 200, shape, 3)
+    xv, yv = small_problem(rng, 72, shape, 3)
+    weights = init_weights(net, rng)
+    eng = engine_for(net, weights)
+    perms = [rng.permutation(200) for _ in range(4)]
+    oracle = OracleNet(rows, [[w.astype(np.float32).astype(np.float64) for w in ws] for ws in weights])
+
+    def mask_fn(step, layer, shp):
+        return ops.dropout_keep_mask(int(np.prod(shp)), rows[layer]["cfg"]["rate"], eng.dropout_seed, layer, step)
+
+    hist_o = oracle.fit(x.astype(np.float64), y.astype(np.float64), xv.astype(np.float64), yv.astype(np.float64),
+                        epochs=4, batch_size=32, permutations=perms, dropout_mask_fn=mask_fn)
+    # drive the engine through the reference-named entry point
+    import featurenet_b200.engine as engine_mod
+    real_fit = engine_mod.Engine.fit
+    engine_mod.Engine.fit = lambda self, *a, **k: real_fit(self, *a, permutations=perms, **k)
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            model, hist_e = train_model(net, x, y, xv, yv, 4, 32, scheduler=True, data_augmentation=False)
+    finally:
+        engine_mod.Engine.fit = real_fit
+    assert model is net
+    for key in ("loss", "val_loss"):
+        assert relerr(hist_e.history[key], hist_o[key]) <= 2e-4, key
+    for key in ("acc", "val_acc"):
+        assert np.abs(np.array(hist_e.history[key]) - np.array(hist_o[key])).max() <= 1.0 / 72 + 1e-9, key
+    # the best-val_loss epoch's weights are the ones installed at the end (helpers.py:169)
+    for a, b in zip(eng.get_weights(), flat(oracle.weights)):
+        assert relerr(a, b) <= 5e-4
+    loss_e, acc_e = net.evaluate(xv, yv)
+    best = int(np.argmin(hist_o["val_loss"]))
+    assert abs(loss_e - hist_o["val_loss"][best]) <= 2e-4 * max(1.0, hist_o["val_loss"][best])
+
+
+def test_graph_replay_equals_eager_launches(monkeypatch):
+    net_a, net_b = make_net("merges"), make_net("merges")
+    rng = np.random.default_rng(8)
+    weights = init_weights(net_a, rng, jitter=True)
+    x, y = small_problem(rng, 96, tuple(net_a.input_shape[1:]), 3)
+    perms = [rng.permutation(96) for _ in range(2)]
+    eng_a = engine_for(net_a, weights)
+    h_a = net_a.fit(x, y, batch_size=40, epochs=2, permutations=perms)
+    monkeypatch.setenv("FNET_NO_GRAPH", "1")
+    eng_b = engine_for(net_b, weights)
+    assert not eng_b.use_graphs and eng_a.use_graphs
+    h_b = net_b.fit(x, y, batch_size=40, epochs=2, permutations=perms)
+    assert h_a.history["loss"] == h_b.history["loss"] and h_a.history["acc"] == h_b.history["acc"]
+    for a, b in zip(eng_a.get_weights(), eng_b.get_weights()):
+        assert np.array_equal(a, b)                       # bit-identical
+
+
+def test_sgd_optimizer_and_sgdr_schedule():
+    from featurenet_b200.optimizers import SGD
+    from sgdr import SGDRScheduler
+    net = make_net("conv_chain")
+    rng = np.random.default_rng(17)
+    weights = init_weights(net, rng)
+    eng = engine_for(net, weights, optimizer=SGD(lr=0.01, momentum=0.9))
+    x, y = small_problem(rng, 64, tuple(net.input_shape[1:]), 3)
+    sched = SGDRScheduler(min_lr=1e-4, max_lr=5e-2, steps_per_epoch=2, lr_decay=0.5, cycle_length=1, mult_factor=2)
+    hist = net.fit(x, y, batch_size=32, epochs=3, callbacks=[sched], shuffle=False)
+    # cosine restarts: lr recorded per batch starts at max_lr, and max_lr halves after each completed cycle
+    assert sched.history["lr"][0] == pytest.approx(5e-2)
+    assert sched.max_lr == pytest.approx(5e-2 * 0.5 * 0.5)
+    assert len(sched.history["lr"]) == 6 and len(hist.history["loss"]) == 3
+    # one plain-SGD step against the oracle (momentum 0 so that the velocity plays no role)
+    net2 = make_net("conv_chain")
+    eng2 = engine_for(net2, weights, optimizer=SGD(lr=0.05))
+    oracle = OracleNet(net2.describe(), [[w.astype(np.float32).astype(np.float64) for w in ws] for ws in weights])
+    oracle.train_step(x[:32].astype(np.float64), y[:32].astype(np.float64), float(np.float32(0.05)), None, optimizer="sgd")
+    eng2.train_on_batch(x[:32], y[:32])
+    for a, b in zip(eng2.get_weights(), flat(oracle.weights)):
+        assert relerr(a, b) <= TOL
+
+
+def test_lenet5_full_batch_properties():
+    """BASELINE config 1 at full batch (128 x 28x28x1): determinism, probabilities, learning signal."""
+    rng = np.random.default_rng(3)
+    x, y = small_problem(rng, 1024, (28, 28, 1), 10)
+    results = []
+    for _ in range(2):
+        net = make_net("lenet5@mnist")
+        weights = init_weights(net, np.random.default_rng(99))
+        eng = engine_for(net, weights)
+        h = net.fit(x, y, batch_size=128, epochs=2, validation_data=(x[:256], y[:256]), shuffle=False)
+        results.append((h.history, eng.get_weights(), eng.predict(x[:64])))
+    assert results[0][0] == results[1][0]                                  # same run twice -> identical history
+    assert all(np.array_equal(a, b) for a, b in zip(results[0][1], results[1][1]))
+    probs = results[0][2]
+    assert np.allclose(probs.sum(axis=1), 1.0, atol=1e-5) and probs.min() >= 0
+    assert results[0][0]["loss"][1] < results[0][0]["loss"][0]
+
+
+def test_tensorflow_generator_drop_in(monkeypatch):
+    """The reference entry point end to end on a reduced synthetic MNIST-shaped set."""
+    monkeypatch.setenv("FNET_SYNTH_TRAIN", "2048")
+    monkeypatch.setenv("FNET_SYNTH_TEST", "512")
+    from tensorflow_generator import TensorflowGenerator
+    TensorflowGenerator.dataset = None
+    with contextlib.redirect_stdout(io.StringIO()):
+        gen = TensorflowGenerator("lenet5", epochs=2, dataset="mnist", data_augmentation=False, batch_size=128)
+    assert gen.params == 212902
+    assert len(gen.history[0]) == 2 and len(gen.history[1]) == 2
+    assert 0.0 <= gen.accuracy <= 1.0 and gen.training_time > 0
+    assert gen.model.model is not None and gen.model.nb_params == 212902
+    vec = gen.model.to_kerasvector().to_vector()
+    assert vec[0] == gen.accuracy and vec[1][1][:3] == [5, 9, 212902]
+    TensorflowGenerator.dataset = None
