@@ -138,14 +138,20 @@ struct WgradProblem {
 };
 
 // ------------------------------------------------------------------ the tile kernel
-constexpr int BK = 16;
-
-template <class P, int BM, int BN, int TM, int TN>
+// 256 threads compute a BM x BN tile; the reduction axis is walked BK at a time.  The operands of
+// tile k+1 are gathered into registers (all loads of a tile are issued back to back) while tile k
+// is being multiplied out of shared memory, so the global-load latency of the small, latency-bound
+// problems FeatureNet produces overlaps with the FFMA work.
+template <class P, int BM, int BN, int TM, int TN, int BK>
 __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int Kg, int k_per_split,
                                                           float *__restrict__ partial) {
     static_assert((BM / TM) * (BN / TN) == 256, "256 threads per CTA");
-    static_assert(BM % 16 == 0 && TM % 4 == 0, "tile shape");
-    __shared__ __align__(16) float As[BK][BM + 4];
+    constexpr int RG = 256 / BK;                 // row groups of the A loader
+    constexpr int A_PER = BM / RG;               // A elements gathered per thread per tile
+    constexpr int B_PER = (BK * BN + 255) / 256; // B elements per thread per tile
+    constexpr int PAD = TM == 1 ? 1 : (TM == 2 ? 2 : 4);
+    static_assert(BM % RG == 0, "loader shape");
+    __shared__ __align__(16) float As[BK][BM + PAD];
     __shared__ __align__(16) float Bs[BK][BN + 4];
     __shared__ typename P::Row rows[BM];
 
@@ -158,7 +164,7 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
     __syncthreads();
 
     const int tx = tid % (BN / TN), ty = tid / (BN / TN);
-    const int a_col = tid % BK, a_rg = tid / BK;   // 16 row groups
+    const int a_col = tid % BK, a_rg = tid / BK;
 
     float acc[TM][TN];
 #pragma unroll
@@ -166,30 +172,48 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
 
-    for (int k0 = kbeg; k0 < kend; k0 += BK) {
+    float a_reg[A_PER], b_reg[B_PER];
+    auto gather = [&](int k0) {
         typename P::Col col;
         p.make_col(k0 + a_col, kend, col);
-#pragma unroll 4
-        for (int i = 0; i < BM / 16; ++i) {
-            int r = a_rg + 16 * i;
-            float v = 0.f;
-            if (col.valid && rows[r].valid) v = p.a(rows[r], col);
-            As[a_col][r] = v;
+#pragma unroll
+        for (int i = 0; i < A_PER; ++i) {
+            const typename P::Row &row = rows[a_rg + RG * i];
+            a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
         }
-        for (int e = tid; e < BK * BN; e += 256) {
+#pragma unroll
+        for (int i = 0; i < B_PER; ++i) {
+            int e = tid + 256 * i;
             int kk = e / BN, nn = e - kk * BN;
-            float v = 0.f;
-            if (k0 + kk < kend && n0 + nn < N) v = p.b(k0 + kk, n0 + nn);
-            Bs[kk][nn] = v;
+            b_reg[i] = (e < BK * BN && k0 + kk < kend && n0 + nn < N) ? p.b(k0 + kk, n0 + nn) : 0.f;
+        }
+    };
+
+    if (kbeg < kend) gather(kbeg);
+    for (int k0 = kbeg; k0 < kend; k0 += BK) {
+#pragma unroll
+        for (int i = 0; i < A_PER; ++i) As[a_col][a_rg + RG * i] = a_reg[i];
+#pragma unroll
+        for (int i = 0; i < B_PER; ++i) {
+            int e = tid + 256 * i;
+            if (e < BK * BN) Bs[e / BN][e % BN] = b_reg[i];
         }
         __syncthreads();
+        if (k0 + BK < kend) gather(k0 + BK);      // in flight while this tile is multiplied
 #pragma unroll
         for (int kk = 0; kk < BK; ++kk) {
             float a[TM], b[TN];
+            if constexpr (TM % 4 == 0) {
 #pragma unroll
-            for (int i = 0; i < TM; i += 4) {
-                float4 t = *reinterpret_cast<const float4 *>(&As[kk][ty * TM + i]);
-                a[i] = t.x; a[i + 1] = t.y; a[i + 2] = t.z; a[i + 3] = t.w;
+                for (int i = 0; i < TM; i += 4) {
+                    float4 t = *reinterpret_cast<const float4 *>(&As[kk][ty * TM + i]);
+                    a[i] = t.x; a[i + 1] = t.y; a[i + 2] = t.z; a[i + 3] = t.w;
+                }
+            } else if constexpr (TM == 2) {
+                float2 t = *reinterpret_cast<const float2 *>(&As[kk][ty * 2]);
+                a[0] = t.x; a[1] = t.y;
+            } else {
+                a[0] = As[kk][ty];
             }
 #pragma unroll
             for (int j = 0; j < TN; ++j) b[j] = Bs[kk][tx * TN + j];
@@ -215,42 +239,60 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
     }
 }
 
-// sums the split partials in split order (deterministic) and applies the problem's epilogue
+// Sums the split partials and applies the problem's epilogue.  One warp per output element: lanes
+// take splits lane, lane+32, ... and a fixed xor-shuffle tree adds them, so the result does not
+// depend on scheduling (deterministic) while the reduction is 32-way parallel.
 template <class P>
 __global__ void __launch_bounds__(256) reduce_splits_kernel(P p, int M, int N, int splits,
                                                              const float *__restrict__ partial) {
     long long total = (long long)M * N;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
+    int lane = threadIdx.x & 31;
+    long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+    for (long long i = warp; i < total; i += nwarps) {
         float s = 0.f;
-        for (int z = 0; z < splits; ++z) s += partial[(long long)z * total + i];
-        int m = (int)(i / N), n = (int)(i - (long long)m * N);
-        p.store(m, n, s);
+        for (int z = lane; z < splits; z += 32) s += partial[(long long)z * total + i];
+        s = warp_sum(s);
+        if (lane == 0) {
+            int m = (int)(i / N), n = (int)(i - (long long)m * N);
+            p.store(m, n, s);
+        }
     }
 }
 
 struct SplitPlan {
-    int bm, bn, splits, k_per_split;
+    int bm, bn, splits, k_per_split, bk;
     size_t ws_bytes;
 };
 
 static SplitPlan plan_for(long long M, long long N, long long Kg) {
     SplitPlan s;
     s.bn = N <= 8 ? 8 : (N <= 16 ? 16 : (N <= 32 ? 32 : 64));
-    s.bm = s.bn <= 16 ? 256 : 128;
-    long long tiles = ceil_div<long long>(M, s.bm) * ceil_div<long long>(N, s.bn);
+    int big = s.bn <= 16 ? 256 : 128;
+    long long ntiles_n = ceil_div<long long>(N, s.bn);
+    // full-size tiles when they fill two waves of 148 SMs; otherwise smaller tiles (less padding on
+    // skinny outputs, more CTAs), and the reduction axis is split to occupy the remaining SMs
+    if (ceil_div<long long>(M, big) * ntiles_n >= 2 * kNumSMs) { s.bm = big; s.bk = 16; }
+    else if (M > 32) { s.bm = 64; s.bk = 32; }
+    else { s.bm = 32; s.bk = 64; }
+    long long tiles = ceil_div<long long>(M, s.bm) * ntiles_n;
     long long splits = 1;
-    if (tiles < kNumSMs && Kg > 8 * BK) {
+    if (tiles < 2 * kNumSMs && Kg >= 4 * s.bk) {
         splits = ceil_div<long long>(2 * kNumSMs, tiles);
-        long long most = ceil_div<long long>(Kg, 4 * BK);
+        long long most = Kg / (2 * s.bk);          // at least two k-tiles per split
         if (splits > most) splits = most;
         if (splits < 1) splits = 1;
     }
-    long long per = ceil_div<long long>(ceil_div<long long>(Kg, splits), BK) * BK;
+    long long per = ceil_div<long long>(ceil_div<long long>(Kg, splits), s.bk) * s.bk;
     s.k_per_split = (int)per;
     s.splits = (int)ceil_div<long long>(Kg, per);
     s.ws_bytes = s.splits > 1 ? (size_t)s.splits * M * N * sizeof(float) : 0;
     return s;
+}
+
+template <class P, int BM, int BN, int TM, int TN, int BKT>
+static void launch_tile(const P &p, dim3 grid, int m, int n, int kg, int per, float *partial, cudaStream_t stream) {
+    igemm_simt_kernel<P, BM, BN, TM, TN, BKT><<<grid, 256, 0, stream>>>(p, m, n, kg, per, partial);
 }
 
 template <class P>
@@ -271,21 +313,32 @@ static int run_problem(const P &p, long long M, long long N, long long Kg, void 
         partial = reinterpret_cast<float *>(ws);
     }
     dim3 grid((unsigned)ceil_div<long long>(M, plan.bm), (unsigned)ceil_div<long long>(N, plan.bn), plan.splits);
-    if (grid.y > 65535u) {
-        set_error("%s: too many column tiles (%u)", what, grid.y);
+    if (grid.y > 65535u || grid.z > 65535u) {
+        set_error("%s: too many tiles (%u x %u)", what, grid.y, grid.z);
         return FNET_ERR_UNSUPPORTED;
     }
-    int m = (int)M, n = (int)N, kg = (int)Kg;
-    switch (plan.bn) {
-        case 8: igemm_simt_kernel<P, 256, 8, 4, 2><<<grid, 256, 0, stream>>>(p, m, n, kg, plan.k_per_split, partial); break;
-        case 16: igemm_simt_kernel<P, 256, 16, 4, 4><<<grid, 256, 0, stream>>>(p, m, n, kg, plan.k_per_split, partial); break;
-        case 32: igemm_simt_kernel<P, 128, 32, 4, 4><<<grid, 256, 0, stream>>>(p, m, n, kg, plan.k_per_split, partial); break;
-        default: igemm_simt_kernel<P, 128, 64, 8, 4><<<grid, 256, 0, stream>>>(p, m, n, kg, plan.k_per_split, partial); break;
+    int m = (int)M, n = (int)N, kg = (int)Kg, per = plan.k_per_split;
+    switch (plan.bn * 1000 + plan.bm) {
+        case 8 * 1000 + 256: launch_tile<P, 256, 8, 4, 2, 16>(p, grid, m, n, kg, per, partial, stream); break;
+        case 8 * 1000 + 64: launch_tile<P, 64, 8, 2, 1, 32>(p, grid, m, n, kg, per, partial, stream); break;
+        case 8 * 1000 + 32: launch_tile<P, 32, 8, 1, 1, 64>(p, grid, m, n, kg, per, partial, stream); break;
+        case 16 * 1000 + 256: launch_tile<P, 256, 16, 4, 4, 16>(p, grid, m, n, kg, per, partial, stream); break;
+        case 16 * 1000 + 64: launch_tile<P, 64, 16, 2, 2, 32>(p, grid, m, n, kg, per, partial, stream); break;
+        case 16 * 1000 + 32: launch_tile<P, 32, 16, 1, 2, 64>(p, grid, m, n, kg, per, partial, stream); break;
+        case 32 * 1000 + 128: launch_tile<P, 128, 32, 4, 4, 16>(p, grid, m, n, kg, per, partial, stream); break;
+        case 32 * 1000 + 64: launch_tile<P, 64, 32, 2, 4, 32>(p, grid, m, n, kg, per, partial, stream); break;
+        case 32 * 1000 + 32: launch_tile<P, 32, 32, 2, 2, 64>(p, grid, m, n, kg, per, partial, stream); break;
+        case 64 * 1000 + 128: launch_tile<P, 128, 64, 8, 4, 16>(p, grid, m, n, kg, per, partial, stream); break;
+        case 64 * 1000 + 64: launch_tile<P, 64, 64, 4, 4, 32>(p, grid, m, n, kg, per, partial, stream); break;
+        default: launch_tile<P, 32, 64, 2, 4, 64>(p, grid, m, n, kg, per, partial, stream); break;
     }
     int rc = check_launch(what);
     if (rc != FNET_OK) return rc;
     if (plan.splits > 1) {
-        reduce_splits_kernel<P><<<stream_grid(M * N, 256), 256, 0, stream>>>(p, m, n, plan.splits, partial);
+        long long warps = M * N;
+        long long blocks = ceil_div<long long>(warps, 8);
+        long long cap = (long long)kNumSMs * 8;
+        reduce_splits_kernel<P><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, m, n, plan.splits, partial);
         rc = check_launch(what);
     }
     return rc;

@@ -23,8 +23,21 @@ def L():
     return fl.get()
 
 
+_KEEP = []      # device tensors made by dev() stay alive until the test ends: `ptr(dev(a))` passes a raw
+                # pointer, and a temporary freed right away would be handed to the next allocation
+
+
+@pytest.fixture(autouse=True)
+def _release_device_tensors():
+    yield
+    torch.cuda.synchronize()
+    del _KEEP[:]
+
+
 def dev(a, dtype=np.float32):
-    return torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=dtype))).cuda()
+    t = torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=dtype))).cuda()
+    _KEEP.append(t)
+    return t
 
 
 def ptr(t):
@@ -391,7 +404,8 @@ def test_gather_rows_and_u8_scaling_are_exact(L):
         assert np.array_equal(dst.cpu().numpy(), src[perm[13:45]])
     u8 = rng.integers(0, 256, 100001, dtype=np.uint8)
     out = torch.empty(u8.size, device="cuda")
-    L.fnet_u8_to_f32(u8.size, ptr(torch.from_numpy(u8).cuda()), 255.0, ptr(out), None)
+    u8d = torch.from_numpy(u8).cuda()
+    L.fnet_u8_to_f32(u8.size, ptr(u8d), 255.0, ptr(out), None)
     torch.cuda.synchronize()
     want = u8.astype("float32")
     want /= 255
