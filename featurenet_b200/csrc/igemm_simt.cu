@@ -401,3 +401,74 @@ ConvGeom dense_geom(long long m, long long k, long long n) {
 }
 
 }  // namespace fnet
+
+// =====================================================================================
+// Allocation-free dense forward.
+//
+// Who needs it: a host that cannot hand this library a workspace because it cannot allocate
+// device memory itself.  The case this was written for is libfnet loaded into the reference's
+// own runtime: a TensorFlow 1.x session reserves nearly all of the GPU when it is created, so a
+// plain cudaMalloc from a plug-in may simply fail, and TF's allocator is not reachable from C.
+// The same holds for an evaluation worker that shares the GPU with any framework whose memory
+// pool already owns the device, and for loops that must avoid the implicit device-wide
+// synchronisation of cudaMalloc/cudaFree.
+//
+// The split-reduction partials, which fnet_dense_fwd keeps in the caller's workspace, live here
+// in a fixed array inside the library image.  Every GPU that loads libfnet.so carries these
+// FNET_STATIC_SCRATCH_BYTES (4 MiB) until the process exits.
+// =====================================================================================
+namespace fnet {
+
+constexpr size_t kStaticScratchBytes = FNET_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) float g_static_scratch[kStaticScratchBytes / sizeof(float)];
+
+constexpr int kMaxDevices = 64;
+static float *g_static_scratch_ptr[kMaxDevices];   // device address of the array, per device ordinal
+
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address; the
+// address a kernel can use comes from cudaGetSymbolAddress, once per device, with that device current.
+static int static_scratch_for_current_device(float **out) {
+    int device = -1;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) { set_error("fnet_dense_fwd_static: cudaGetDevice: %s", cudaGetErrorString(e)); return FNET_ERR_CUDA; }
+    if (device < 0 || device >= kMaxDevices) { set_error("fnet_dense_fwd_static: device ordinal %d not supported", device); return FNET_ERR_UNSUPPORTED; }
+    if (g_static_scratch_ptr[device] == nullptr) {
+        void *address = nullptr;
+        e = cudaGetSymbolAddress(&address, g_static_scratch);
+        if (e != cudaSuccess || address == nullptr) {
+            set_error("fnet_dense_fwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return FNET_ERR_CUDA;
+        }
+        g_static_scratch_ptr[device] = reinterpret_cast<float *>(address);
+    }
+    *out = g_static_scratch_ptr[device];
+    return FNET_OK;
+}
+
+}  // namespace fnet
+
+extern "C" int fnet_dense_fwd_static(int64_t m, int64_t k, int64_t n, int act, const float *x, const float *w,
+                                     const float *bias, float *y, void *stream) {
+    using namespace fnet;
+    if (m < 0 || k <= 0 || n <= 0 || m > 0x7fffffffLL || k > 0x7fffffffLL || n > 0x7fffffffLL) {
+        set_error("fnet_dense_fwd_static: bad GEMM shape m=%lld k=%lld n=%lld", (long long)m, (long long)k, (long long)n);
+        return FNET_ERR_ARG;
+    }
+    if (act < FNET_ACT_NONE || act > FNET_ACT_SOFTMAX) { set_error("fnet_dense_fwd_static: unknown activation %d", act); return FNET_ERR_ARG; }
+    if (m == 0) return FNET_OK;
+    if (!x || !w || !y) { set_error("fnet_dense_fwd_static: null pointer"); return FNET_ERR_ARG; }
+    size_t need = plan_for(m, n, k).ws_bytes;
+    if (need > kStaticScratchBytes) {
+        set_error("fnet_dense_fwd_static: this shape needs %zu bytes of scratch, the built-in array holds %zu; "
+                  "use fnet_dense_fwd with a caller-provided workspace", need, kStaticScratchBytes);
+        return FNET_ERR_WORKSPACE;
+    }
+    float *scratch = nullptr;
+    int rc = static_scratch_for_current_device(&scratch);
+    if (rc != FNET_OK) return rc;
+    // Nothing in the scratch has to start at zero: every partial the reduction reads is written
+    // earlier in this same call, so whatever the previous call left behind is never looked at.
+    rc = simt_conv_fwd(dense_geom(m, k, n), act, x, w, bias, y, scratch, kStaticScratchBytes, as_stream(stream));
+    if (rc == FNET_OK && act == FNET_ACT_SOFTMAX) rc = run_softmax_rows(m, n, y, y, as_stream(stream));
+    return rc;
+}

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(CSRC, "libfnet.so")
 ACT = {None: 0, "linear": 0, "relu": 1, "tanh": 2, "sigmoid": 3, "softmax": 4}
 POOL_MAX, POOL_AVG = 0, 1
 MATH = {"fp32": 0, "tf32": 1, "bf16": 2}
+STATIC_SCRATCH_BYTES = 4 << 20      # FNET_STATIC_SCRATCH_BYTES in include/fnet.h
 
 
 class FnetError(RuntimeError):
@@ -46,6 +47,7 @@ SIGNATURES = {
     "fnet_conv2d_bwd_filter": (C.c_int, [_CD, _P, _P, _P, _P, _P, _SZ, _P]),
     "fnet_dense_workspace_bytes": (_SZ, [_I64, _I64, _I64]),
     "fnet_dense_fwd": (C.c_int, [_I64, _I64, _I64, C.c_int, C.c_int, _P, _P, _P, _P, _P, _SZ, _P]),
+    "fnet_dense_fwd_static": (C.c_int, [_I64, _I64, _I64, C.c_int, _P, _P, _P, _P, _P]),
     "fnet_dense_bwd_data": (C.c_int, [_I64, _I64, _I64, C.c_int, _P, _P, _P, C.c_int, _P, _SZ, _P]),
     "fnet_dense_bwd_filter": (C.c_int, [_I64, _I64, _I64, C.c_int, _P, _P, _P, _P, _P, _SZ, _P]),
     "fnet_dwconv2d_workspace_bytes": (_SZ, [_CD]),

@@ -85,6 +85,32 @@ int fnet_dense_bwd_filter(int64_t m, int64_t k, int64_t n, int math, const float
                           float *dbias, void *ws, size_t ws_bytes, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Dense forward that allocates nothing and needs no workspace.  It has no counterpart in the
+ * reference; it exists for hosts that cannot allocate device memory -- above all libfnet
+ * loaded into a TensorFlow 1.x process (the reference's own runtime), where the session has
+ * already reserved almost the whole GPU and a plug-in's cudaMalloc may fail, and more generally
+ * a worker sharing the device with a framework whose pool owns the memory, or a loop that must
+ * not pay the device-wide synchronisation of cudaMalloc/cudaFree.
+ *
+ * Same arithmetic as fnet_dense_fwd with FNET_MATH_FP32 (same kernels, same reduction order,
+ * so the same bits).  The partial sums of the split reduction go to an array of
+ * FNET_STATIC_SCRATCH_BYTES built into the library; every GPU that loads libfnet.so holds that
+ * array until the process exits.  Shapes whose reduction needs more than that are rejected
+ * with FNET_ERR_WORKSPACE and a message (use fnet_dense_fwd and a workspace of
+ * fnet_dense_workspace_bytes() for those).
+ *
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ * with that device current); make that first call before starting any stream capture.
+ * All calls on a device share the one array: the array keeps whatever the last call wrote, and
+ * no call depends on it (every partial is written before it is read, nothing is assumed zero);
+ * but two calls that run on the GPU at the same time -- different streams, or different host
+ * threads -- race on it, so keep calls to this entry point ordered on one stream per device.
+ * ------------------------------------------------------------------------------------------ */
+#define FNET_STATIC_SCRATCH_BYTES (4u << 20)
+int fnet_dense_fwd_static(int64_t m, int64_t k, int64_t n, int act, const float *x, const float *w,
+                          const float *bias, float *y, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Depthwise convolution, depth multiplier 1.  Replaces keras.layers.DepthwiseConv2D
  * (model/input.py:298) and the depthwise half of SeparableConv2D (model/input.py:296).
  * x[B,H,W,C], w[kh,kw,C], y[B,Ho,Wo,C].  Memory-bound: 2*kh*kw flops per element moved.
