@@ -1,0 +1,132 @@
+// Geometry of the three GEMM-shaped products of a convolution, shared by the FFMA kernels
+// (igemm_simt.cu) and the tcgen05 kernels (igemm_tc.cu).  A "problem" maps GEMM coordinates to
+// tensor elements:
+//   forward         C[m, n]  m = (b, ho, wo)   n = out channel   k = (r, s, c)
+//   backward data   C[m, n]  m = (b, h, w)     n = in channel    k = (r, s, out channel)
+//   backward filter C[m, n]  m = (r, s, c) (+1 row of ones = bias)  n = out channel  k = (b, ho, wo)
+#pragma once
+#include "igemm.cuh"
+
+namespace fnet {
+
+struct PixelCtx {   // one output pixel (forward / filter) or one input pixel (data)
+    long long base; // element offset of the image it indexes into
+    int h0, w0;     // top-left input coordinate of the window, or padded input coordinate
+    int valid;
+};
+
+struct TapCtx {     // one (r, s, channel) of the reduction / filter row
+    int dr, ds;     // dilated tap offsets
+    int ch;         // channel inside the tap
+    int valid;      // 1 = real tap, 2 = the all-ones bias row (filter gradient only), 0 = out of range
+};
+
+__device__ __forceinline__ void decode_out_pixel(const ConvGeom &g, int m, int M, PixelCtx &p) {
+    p.valid = m < M;
+    int mm = p.valid ? m : 0;
+    int b = mm / (g.Ho * g.Wo);
+    int rem = mm - b * (g.Ho * g.Wo);
+    int ho = rem / g.Wo, wo = rem - ho * g.Wo;
+    p.base = (long long)b * g.H * g.W * g.C;
+    p.h0 = ho * g.sh - g.pt;
+    p.w0 = wo * g.sw - g.pl;
+}
+
+__device__ __forceinline__ void decode_in_pixel(const ConvGeom &g, int m, int M, PixelCtx &p) {
+    p.valid = m < M;
+    int mm = p.valid ? m : 0;
+    int b = mm / (g.H * g.W);
+    int rem = mm - b * (g.H * g.W);
+    int h = rem / g.W, w = rem - h * g.W;
+    p.base = (long long)b * g.Ho * g.Wo * g.K;
+    p.h0 = h + g.pt;
+    p.w0 = w + g.pl;
+}
+
+__device__ __forceinline__ void decode_tap(const ConvGeom &g, int k, int channels, int limit, TapCtx &t) {
+    t.valid = k < limit;
+    int kk = t.valid ? k : 0;
+    int tap = kk / channels;
+    t.ch = kk - tap * channels;
+    int r = tap / g.kw, s = tap - r * g.kw;
+    t.dr = r * g.dh;
+    t.ds = s * g.dw;
+}
+
+// x[b, h0+dr, w0+ds, ch] with zero padding
+__device__ __forceinline__ float gather_input(const ConvGeom &g, const float *__restrict__ x, const PixelCtx &p,
+                                              const TapCtx &t) {
+    int h = p.h0 + t.dr, w = p.w0 + t.ds;
+    if ((unsigned)h >= (unsigned)g.H || (unsigned)w >= (unsigned)g.W) return 0.f;
+    return __ldg(x + p.base + ((long long)h * g.W + w) * g.C + t.ch);
+}
+
+// dz[b, (hp-dr)/sh, (wp-ds)/sw, ch] when the divisions are exact and in range
+__device__ __forceinline__ float gather_grad(const ConvGeom &g, const float *__restrict__ dz, const PixelCtx &p,
+                                             const TapCtx &t) {
+    int hh = p.h0 - t.dr, ww = p.w0 - t.ds;
+    if (hh < 0 || ww < 0) return 0.f;
+    int ho = hh / g.sh, wo = ww / g.sw;
+    if (ho * g.sh != hh || wo * g.sw != ww || ho >= g.Ho || wo >= g.Wo) return 0.f;
+    return __ldg(dz + p.base + ((long long)ho * g.Wo + wo) * g.K + t.ch);
+}
+
+// ------------------------------------------------------------------ problems
+struct FwdProblem {
+    ConvGeom g;
+    const float *x, *w, *bias;
+    float *y;
+    int act;
+    typedef PixelCtx Row;
+    typedef TapCtx Col;
+    __device__ void make_row(int m, int M, Row &r) const { decode_out_pixel(g, m, M, r); }
+    __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.C, kend, c); }
+    __device__ float a(const Row &r, const Col &c) const { return gather_input(g, x, r, c); }
+    __device__ float b(int k, int n) const { return __ldg(w + (long long)k * g.K + n); }
+    __device__ void store(int m, int n, float v) const {
+        if (bias) v += __ldg(bias + n);
+        y[(long long)m * g.K + n] = act_apply(v, act);
+    }
+};
+
+struct DgradProblem {
+    ConvGeom g;
+    const float *dz, *w;
+    float *dx;
+    int accumulate;
+    typedef PixelCtx Row;
+    typedef TapCtx Col;
+    __device__ void make_row(int m, int M, Row &r) const { decode_in_pixel(g, m, M, r); }
+    __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.K, kend, c); }
+    __device__ float a(const Row &r, const Col &c) const { return gather_grad(g, dz, r, c); }
+    __device__ float b(int k, int n) const {
+        int tap = k / g.K, ko = k - tap * g.K;
+        return __ldg(w + ((long long)tap * g.C + n) * g.K + ko);
+    }
+    __device__ void store(int m, int n, float v) const {
+        long long at = (long long)m * g.C + n;
+        dx[at] = accumulate ? dx[at] + v : v;
+    }
+};
+
+struct WgradProblem {
+    ConvGeom g;
+    const float *x, *dz;
+    float *dw, *dbias;
+    int taps_c;   // kh*kw*C: rows below are filter taps, row == taps_c is the bias row
+    typedef TapCtx Row;
+    typedef PixelCtx Col;
+    __device__ void make_row(int k, int M, Row &r) const {
+        decode_tap(g, k, g.C, taps_c, r);
+        if (k == taps_c && k < M) r.valid = 2;
+    }
+    __device__ void make_col(int m, int mend, Col &c) const { decode_out_pixel(g, m, mend, c); }
+    __device__ float a(const Row &r, const Col &c) const { return r.valid == 2 ? 1.f : gather_input(g, x, c, r); }
+    __device__ float b(int m, int n) const { return __ldg(dz + (long long)m * g.K + n); }
+    __device__ void store(int k, int n, float v) const {
+        if (k < taps_c) dw[(long long)k * g.K + n] = v;
+        else if (dbias) dbias[n] = v;
+    }
+};
+
+}  // namespace fnet

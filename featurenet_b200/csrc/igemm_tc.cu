@@ -1,16 +1,346 @@
-// tcgen05 / TMEM implicit-GEMM kernels (FNET_MATH_TF32, FNET_MATH_BF16).  Placeholder until the
-// tensor-core kernels land: nothing is "supported", so every call takes the fp32 FFMA path.
-#include "igemm.cuh"
+// tcgen05 / TMEM implicit-GEMM kernels for the wide layers (FNET_MATH_TF32).
+//
+// D[128 x BN] (fp32, in tensor memory) += A[128 x 32] * B[BN x 32]^T per k-tile, issued by one
+// thread as four tcgen05.mma.kind::tf32 (K = 8 each).  The operands are gathered by all 256
+// threads straight from the NHWC tensors (implicit im2col, any channel count, any stride or
+// padding -- FeatureNet's channel counts are rarely multiples of 4, which rules out TMA's
+// 16-byte global strides) into shared memory in the canonical K-major SWIZZLE_128B layout,
+// rounded to tf32, three stages deep: while the tensor core multiplies stage s the threads fill
+// stage s+1 from registers and have the loads of stage s+2 in flight.  Completion of the MMAs
+// that read a stage is tracked with tcgen05.commit -> mbarrier, the accumulator never leaves
+// TMEM until the epilogue (tcgen05.ld, bias + activation, store).
+//
+// The same "problem" types as the FFMA kernels describe forward, data gradient and filter
+// gradient; split reductions write fp32 partial tiles to the caller's workspace and are summed
+// in a fixed order (no atomics).
+#include <stdlib.h>
+#include "igemm_problems.cuh"
 
 namespace fnet {
 
-bool tc_supported(const ConvGeom &, int, int) { return false; }
-size_t tc_conv_workspace(const ConvGeom &, int) { return 0; }
-int tc_conv_fwd(const ConvGeom &, int, int, const float *, const float *, const float *, float *, void *, size_t,
-                cudaStream_t) { set_error("tensor-core path not built"); return FNET_ERR_UNSUPPORTED; }
-int tc_conv_dgrad(const ConvGeom &, int, const float *, const float *, float *, int, void *, size_t, cudaStream_t) {
-    set_error("tensor-core path not built"); return FNET_ERR_UNSUPPORTED; }
-int tc_conv_wgrad(const ConvGeom &, int, const float *, const float *, float *, float *, void *, size_t,
-                  cudaStream_t) { set_error("tensor-core path not built"); return FNET_ERR_UNSUPPORTED; }
+constexpr int TC_BM = 128;
+constexpr int TC_BK = 32;        // fp32 elements per k-tile row: 128 bytes = one swizzle row
+constexpr int TC_THREADS = 256;
+constexpr int TC_STAGES = 3;
+constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t addr = smem_u32(bar), done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+    }
+}
+
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+__device__ __forceinline__ float to_tf32(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return __uint_as_float(r);
+}
+
+// byte offset of element (row, kc) of a [rows x 32 fp32] K-major tile
+__device__ __forceinline__ uint32_t tile_offset(int row, int kc, int layout) {
+    if (layout == 0)   // SWIZZLE_128B: 8-row x 128-byte atoms, 16-byte chunks XOR-ed with the row
+        return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((kc >> 2) ^ (row & 7)) << 4) | ((kc & 3) << 2)));
+    // no swizzle: 8-row x 16-byte core matrices, K-adjacent core matrices 128 bytes apart
+    return (uint32_t)((row >> 3) * 1024 + (kc >> 2) * 128 + (row & 7) * 16 + ((kc & 3) << 2));
+}
+
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, int layout) {
+    uint64_t d = (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(layout == 0 ? 1 : (128 >> 4)) << 16;   // leading byte offset (ignored when swizzled)
+    d |= (uint64_t)(1024 >> 4) << 32;                      // stride byte offset: next 8-row group
+    d |= (uint64_t)1 << 46;                                // descriptor version for sm_100
+    d |= (uint64_t)(layout == 0 ? 2 : 0) << 61;            // SWIZZLE_128B / SWIZZLE_NONE
+    return d;
+}
+
+template <class P, int BN>
+__global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int N, int Kg, int k_per_split,
+                                                                 float *__restrict__ partial, int layout) {
+    constexpr int B_BYTES = BN * TC_BK * 4;
+    constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
+    constexpr int B_PER = BN / 8;
+    constexpr int TMEM_COLS = BN < 32 ? 32 : BN;          // BN is 64 / 128 / 256: already a power of two
+    extern __shared__ uint8_t tc_smem_raw[];
+    __shared__ uint64_t empty_bar[TC_STAGES];
+    __shared__ uint64_t done_bar;
+    __shared__ uint32_t tmem_holder;
+    __shared__ typename P::Row rows[TC_BM];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
+    const int kbeg = blockIdx.z * k_per_split;
+    const int kend = min(Kg, kbeg + k_per_split);
+    const int n_tile = min(BN, ((N - n0) + 15) & ~15);     // UMMA N: multiple of 16
+
+    for (int i = tid; i < TC_BM; i += TC_THREADS) p.make_row(m0 + i, M, rows[i]);
+    if (tid == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) mbar_init(&empty_bar[s], 1);
+        mbar_init(&done_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_holder)),
+                     "r"((uint32_t)TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_holder;
+
+    // loader mapping: a warp handles one tile row at a time, lanes walk the 32 k of the tile
+    const int kc = lane, r0 = warp;
+    float a_reg[16], b_reg[B_PER];
+    auto gather = [&](int k0) {
+        typename P::Col col;
+        p.make_col(k0 + kc, kend, col);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const typename P::Row &row = rows[r0 + 8 * i];
+            a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < B_PER; ++i) {
+            int n = n0 + r0 + 8 * i;
+            b_reg[i] = (k0 + kc < kend && n < N) ? p.b(k0 + kc, n) : 0.f;
+        }
+    };
+
+    // instruction descriptor: D fp32, A/B tf32, both K-major, N = n_tile, M = 128
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n_tile >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+    const int kadv = layout == 0 ? 2 : 16;                 // descriptor start-address step per 8 k (in 16-byte units)
+
+    const int KT = (kend - kbeg + TC_BK - 1) / TC_BK;
+    if (KT > 0) gather(kbeg);
+    for (int kt = 0; kt < KT; ++kt) {
+        const int s = kt % TC_STAGES;
+        uint8_t *sa = smem + s * STAGE_BYTES, *sb = sa + TC_A_BYTES;
+        if (kt >= TC_STAGES) mbar_wait(&empty_bar[s], (uint32_t)((kt / TC_STAGES - 1) & 1));
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            *reinterpret_cast<float *>(sa + tile_offset(r0 + 8 * i, kc, layout)) = to_tf32(a_reg[i]);
+#pragma unroll
+        for (int i = 0; i < B_PER; ++i)
+            *reinterpret_cast<float *>(sb + tile_offset(r0 + 8 * i, kc, layout)) = to_tf32(b_reg[i]);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            uint64_t da = make_smem_desc(smem_u32(sa), layout), db = make_smem_desc(smem_u32(sb), layout);
+#pragma unroll
+            for (int j = 0; j < TC_BK / 8; ++j)
+                tc_mma_tf32(tmem, da + (uint64_t)(j * kadv), db + (uint64_t)(j * kadv), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+            tc_commit(&empty_bar[s]);                                   // arrives when these MMAs have read the stage
+            if (kt == KT - 1) tc_commit(&done_bar);
+        }
+        if (kt + 1 < KT) gather(kbeg + (kt + 1) * TC_BK);               // in flight while the tensor core works
+    }
+
+    // epilogue: warp w reads TMEM lanes 32*(w%4).. (its quadrant), the two warpgroups split the columns
+    if (KT > 0) {
+        mbar_wait(&done_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    const int quad = warp & 3, half = warp >> 2;
+    const int m = m0 + quad * 32 + lane;
+    for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 16) {
+        if (c0 >= n_tile) break;                            // warp-uniform
+        uint32_t v[16];
+        if (KT > 0) {
+            uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = 0u;
+        }
+        if (m < M) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                int n = n0 + c0 + j;
+                if (n < N) {
+                    float val = __uint_as_float(v[j]);
+                    if (partial) partial[((long long)blockIdx.z * M + m) * N + n] = val;
+                    else p.store(m, n, val);
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)TMEM_COLS) : "memory");
+}
+
+template <class P>
+__global__ void __launch_bounds__(256) tc_reduce_splits_kernel(P p, int M, int N, int splits,
+                                                                const float *__restrict__ partial) {
+    long long total = (long long)M * N;
+    int lane = threadIdx.x & 31;
+    long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+    for (long long i = warp; i < total; i += nwarps) {
+        float s = 0.f;
+        for (int z = lane; z < splits; z += 32) s += partial[(long long)z * total + i];
+        s = warp_sum(s);
+        if (lane == 0) {
+            int m = (int)(i / N), n = (int)(i - (long long)m * N);
+            p.store(m, n, s);
+        }
+    }
+}
+
+struct TcPlan {
+    int bn, splits, k_per_split;
+    size_t ws_bytes, smem_bytes;
+};
+
+static TcPlan tc_plan(long long M, long long N, long long Kg) {
+    TcPlan t;
+    t.bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+    long long tiles = ceil_div<long long>(M, TC_BM) * ceil_div<long long>(N, t.bn);
+    long long splits = 1;
+    if (tiles < kNumSMs && Kg >= 8 * TC_BK) {
+        splits = ceil_div<long long>(2 * kNumSMs, tiles);
+        long long most = Kg / (4 * TC_BK);
+        if (splits > most) splits = most;
+        if (splits < 1) splits = 1;
+    }
+    long long per = ceil_div<long long>(ceil_div<long long>(Kg, splits), TC_BK) * TC_BK;
+    t.k_per_split = (int)per;
+    t.splits = (int)ceil_div<long long>(Kg, per);
+    t.ws_bytes = t.splits > 1 ? (size_t)t.splits * M * N * sizeof(float) : 0;
+    t.smem_bytes = (size_t)TC_STAGES * (TC_A_BYTES + t.bn * TC_BK * 4) + 1024;
+    return t;
+}
+
+static int tc_layout_mode() {
+    static int mode = -1;
+    if (mode < 0) {
+        const char *e = getenv("FNET_TC_LAYOUT");      // 0 = SWIZZLE_128B (default), 1 = no swizzle; for bring-up
+        mode = (e && e[0] == '1') ? 1 : 0;
+    }
+    return mode;
+}
+
+template <class P, int BN>
+static int tc_launch(const P &p, dim3 grid, size_t smem, int m, int n, int kg, int per, float *partial,
+                     cudaStream_t stream, const char *what) {
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(tc_igemm_kernel<P, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
+        configured = true;
+    }
+    tc_igemm_kernel<P, BN><<<grid, TC_THREADS, smem, stream>>>(p, m, n, kg, per, partial, tc_layout_mode());
+    return check_launch(what);
+}
+
+template <class P>
+static int tc_run(const P &p, long long M, long long N, long long Kg, void *ws, size_t ws_bytes, cudaStream_t stream,
+                  const char *what) {
+    if (M <= 0 || N <= 0) return FNET_OK;
+    TcPlan plan = tc_plan(M, N, Kg);
+    float *partial = nullptr;
+    if (plan.splits > 1) {
+        if (!ws || ws_bytes < plan.ws_bytes) {
+            set_error("%s: workspace of %zu bytes needed, %zu given", what, plan.ws_bytes, ws_bytes);
+            return FNET_ERR_WORKSPACE;
+        }
+        partial = reinterpret_cast<float *>(ws);
+    }
+    dim3 grid((unsigned)ceil_div<long long>(M, TC_BM), (unsigned)ceil_div<long long>(N, plan.bn), plan.splits);
+    int m = (int)M, n = (int)N, kg = (int)Kg, rc;
+    if (plan.bn == 64) rc = tc_launch<P, 64>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
+    else if (plan.bn == 128) rc = tc_launch<P, 128>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
+    else rc = tc_launch<P, 256>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
+    if (rc != FNET_OK) return rc;
+    if (plan.splits > 1) {
+        long long blocks = ceil_div<long long>(M * N, 8), cap = (long long)kNumSMs * 8;
+        tc_reduce_splits_kernel<P><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, m, n, plan.splits, partial);
+        rc = check_launch(what);
+    }
+    return rc;
+}
+
+// The tensor-core tile is 128 x >=64: only worth it (and only exercised) for wide GEMMs.
+static bool tc_shape_ok(long long M, long long N, long long Kg) {
+    return M >= 128 && N >= 32 && Kg >= 32 && M <= 0x7fffffffLL && Kg <= 0x7fffffffLL && N <= 65535LL * 64;
+}
+
+bool tc_supported(const ConvGeom &g, int math, int product) {
+    if (math != FNET_MATH_TF32) return false;              // bf16 operands: not built yet
+    long long mo = (long long)g.B * g.Ho * g.Wo, mi = (long long)g.B * g.H * g.W, taps = (long long)g.kh * g.kw;
+    if (product == 0) return tc_shape_ok(mo, g.K, taps * g.C);
+    if (product == 1) return tc_shape_ok(mi, g.C, taps * g.K);
+    return tc_shape_ok(taps * g.C + 1, g.K, mo);
+}
+
+size_t tc_conv_workspace(const ConvGeom &g, int math) {
+    if (math != FNET_MATH_TF32) return 0;
+    long long mo = (long long)g.B * g.Ho * g.Wo, mi = (long long)g.B * g.H * g.W, taps = (long long)g.kh * g.kw;
+    size_t need = 0;
+    if (tc_supported(g, math, 0)) need = tc_plan(mo, g.K, taps * g.C).ws_bytes;
+    if (tc_supported(g, math, 1)) { size_t b = tc_plan(mi, g.C, taps * g.K).ws_bytes; need = b > need ? b : need; }
+    if (tc_supported(g, math, 2)) { size_t c = tc_plan(taps * g.C + 1, g.K, mo).ws_bytes; need = c > need ? c : need; }
+    return need;
+}
+
+int tc_conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
+                void *ws, size_t ws_bytes, cudaStream_t stream) {
+    (void)math;
+    FwdProblem p{g, x, w, bias, y, act == FNET_ACT_SOFTMAX ? FNET_ACT_NONE : act};
+    return tc_run(p, (long long)g.B * g.Ho * g.Wo, g.K, (long long)g.kh * g.kw * g.C, ws, ws_bytes, stream, "conv2d_fwd[tf32]");
+}
+
+int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+                  size_t ws_bytes, cudaStream_t stream) {
+    (void)math;
+    DgradProblem p{g, dz, w, dx, accumulate};
+    return tc_run(p, (long long)g.B * g.H * g.W, g.C, (long long)g.kh * g.kw * g.K, ws, ws_bytes, stream, "conv2d_bwd_data[tf32]");
+}
+
+int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
+                  size_t ws_bytes, cudaStream_t stream) {
+    (void)math;
+    int taps_c = g.kh * g.kw * g.C;
+    WgradProblem p{g, x, dz, dw, dbias, taps_c};
+    return tc_run(p, (long long)taps_c + (dbias ? 1 : 0), g.K, (long long)g.B * g.Ho * g.Wo, ws, ws_bytes, stream,
+                  "conv2d_bwd_filter[tf32]");
+}
 
 }  // namespace fnet

@@ -1,0 +1,77 @@
+"""Tensor-core path (tcgen05.mma kind::tf32, TMEM accumulators) vs the float64 oracle.
+
+tf32 operands carry 10 mantissa bits (2^-11 relative rounding) with fp32 accumulation, so the
+stated tolerance for this mode is 3e-3 relative (max-norm) per layer; the fp32 path keeps 1e-4.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from oracle import ops
+from tests.test_gpu_ops import (L, _release_device_tensors, assert_close, conv_desc, dev, host, ptr,  # noqa: F401
+                                workspace)
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+TF32_TOL = 3e-3
+
+TC_CONV_CASES = [
+    # x shape, kernel, out channels, stride: all have M >= 128, N >= 32, K >= 32 on the forward
+    ((4, 16, 16, 24), (3, 1), 192, (1, 1)),     # the 24 -> 192 expansion of the x8 blocks (N = 192: 256-wide tile, ragged)
+    ((2, 16, 16, 192), (1, 1), 24, (1, 1)),     # 1x1 reduction: the data gradient is the wide product
+    ((2, 12, 12, 64), (3, 3), 64, (1, 1)),      # keras-template style 3x3, K = 576
+    ((3, 9, 9, 40), (5, 5), 72, (2, 2)),        # stride 2, ragged M (75 rows), K = 1000
+    ((2, 8, 8, 33), (3, 3), 130, (1, 1)),       # nothing aligned: C = 33, N = 130
+]
+
+
+@pytest.mark.parametrize("case_id", range(len(TC_CONV_CASES)))
+def test_conv2d_tf32_tensor_core(L, case_id):
+    from featurenet_b200 import lib as fl
+    xs, k, kout, s = TC_CONV_CASES[case_id]
+    rng = np.random.default_rng(2000 + case_id)
+    x = rng.standard_normal(xs)
+    w = rng.standard_normal(k + (xs[3], kout)) / np.sqrt(k[0] * k[1] * xs[3])
+    b = rng.standard_normal(kout)
+    desc = conv_desc(fl, xs, k, kout, s, "same", act="relu", math="tf32")
+    ws = workspace(L.fnet_conv2d_workspace_bytes(C.byref(desc)))
+    y = ops.act_fwd(ops.conv2d_fwd(x, w, b, s, "same"), "relu")
+    dz = rng.standard_normal(y.shape)
+    dx, dw, db = ops.conv2d_bwd(x, w, dz, s, "same")
+    xd, wd, bd, dzd = dev(x), dev(w), dev(b), dev(dz)
+    yd = torch.empty(y.shape, device="cuda")
+    L.fnet_conv2d_fwd(desc, ptr(xd), ptr(wd), ptr(bd), ptr(yd), ptr(ws), ws.numel(), None)
+    assert_close(host(yd), y, tol=TF32_TOL, what="tf32 conv fwd")
+    dxd = torch.empty(xs, device="cuda")
+    L.fnet_conv2d_bwd_data(desc, ptr(dzd), ptr(wd), ptr(dxd), 0, ptr(ws), ws.numel(), None)
+    assert_close(host(dxd), dx, tol=TF32_TOL, what="tf32 conv dgrad")
+    dwd, dbd = torch.empty(w.shape, device="cuda"), torch.empty(kout, device="cuda")
+    L.fnet_conv2d_bwd_filter(desc, ptr(xd), ptr(dzd), ptr(dwd), ptr(dbd), ptr(ws), ws.numel(), None)
+    assert_close(host(dwd), dw, tol=TF32_TOL, what="tf32 conv wgrad")
+    assert_close(host(dbd), db, tol=TF32_TOL, what="tf32 conv bias grad")
+    dw2 = torch.empty(w.shape, device="cuda")
+    L.fnet_conv2d_bwd_filter(desc, ptr(xd), ptr(dzd), ptr(dw2), None, ptr(ws), ws.numel(), None)
+    assert torch.equal(dwd, dw2)                                        # still deterministic
+
+
+@pytest.mark.parametrize("m,k,n", [(4096, 64, 512), (16384, 64, 512), (1000, 200, 33), (256, 4096, 100)])
+def test_dense_tf32_tensor_core(L, m, k, n):
+    from featurenet_b200 import lib as fl
+    rng = np.random.default_rng(m + n)
+    x, w, b = rng.standard_normal((m, k)), rng.standard_normal((k, n)) / np.sqrt(k), rng.standard_normal(n)
+    y = ops.act_fwd(ops.dense_fwd(x, w, b), "tanh")
+    dz = rng.standard_normal((m, n))
+    dx, dw, db = ops.dense_bwd(x, w, dz)
+    ws = workspace(L.fnet_dense_workspace_bytes(m, k, n))
+    xd, wd, bd, dzd = dev(x), dev(w), dev(b), dev(dz)
+    yd = torch.empty((m, n), device="cuda")
+    L.fnet_dense_fwd(m, k, n, fl.ACT["tanh"], fl.MATH["tf32"], ptr(xd), ptr(wd), ptr(bd), ptr(yd), ptr(ws), ws.numel(), None)
+    assert_close(host(yd), y, tol=TF32_TOL, what="tf32 dense fwd")
+    dxd, dwd, dbd = torch.empty((m, k), device="cuda"), torch.empty((k, n), device="cuda"), torch.empty(n, device="cuda")
+    L.fnet_dense_bwd_data(m, k, n, fl.MATH["tf32"], ptr(dzd), ptr(wd), ptr(dxd), 0, ptr(ws), ws.numel(), None)
+    L.fnet_dense_bwd_filter(m, k, n, fl.MATH["tf32"], ptr(xd), ptr(dzd), ptr(dwd), ptr(dbd), ptr(ws), ws.numel(), None)
+    assert_close(host(dxd), dx, tol=TF32_TOL, what="tf32 dense dgrad")
+    assert_close(host(dwd), dw, tol=TF32_TOL, what="tf32 dense wgrad")
+    assert_close(host(dbd), db, tol=TF32_TOL, what="tf32 dense bias grad")
