@@ -4,6 +4,9 @@
 //   forward         C[m, n]  m = (b, ho, wo)   n = out channel   k = (r, s, c)
 //   backward data   C[m, n]  m = (b, h, w)     n = in channel    k = (r, s, out channel)
 //   backward filter C[m, n]  m = (r, s, c) (+1 row of ones = bias)  n = out channel  k = (b, ho, wo)
+// Each problem also says along which GEMM axis its operands are contiguous in memory
+// (kAContigK / kBContigK), so that a loader can put the lanes of a warp on that axis, and offers a
+// 16-byte gather (a4) for the cases where four consecutive k are four consecutive channels.
 #pragma once
 #include "igemm.cuh"
 
@@ -53,22 +56,27 @@ __device__ __forceinline__ void decode_tap(const ConvGeom &g, int k, int channel
     t.ds = s * g.dw;
 }
 
-// x[b, h0+dr, w0+ds, ch] with zero padding
-__device__ __forceinline__ float gather_input(const ConvGeom &g, const float *__restrict__ x, const PixelCtx &p,
-                                              const TapCtx &t) {
+// address of x[b, h0+dr, w0+ds, ch], or nullptr in the zero padding
+__device__ __forceinline__ const float *input_at(const ConvGeom &g, const float *__restrict__ x, const PixelCtx &p,
+                                                 const TapCtx &t) {
     int h = p.h0 + t.dr, w = p.w0 + t.ds;
-    if ((unsigned)h >= (unsigned)g.H || (unsigned)w >= (unsigned)g.W) return 0.f;
-    return __ldg(x + p.base + ((long long)h * g.W + w) * g.C + t.ch);
+    if ((unsigned)h >= (unsigned)g.H || (unsigned)w >= (unsigned)g.W) return nullptr;
+    return x + p.base + ((long long)h * g.W + w) * g.C + t.ch;
 }
 
-// dz[b, (hp-dr)/sh, (wp-ds)/sw, ch] when the divisions are exact and in range
-__device__ __forceinline__ float gather_grad(const ConvGeom &g, const float *__restrict__ dz, const PixelCtx &p,
-                                             const TapCtx &t) {
+// address of dz[b, (hp-dr)/sh, (wp-ds)/sw, ch] when the divisions are exact and in range
+__device__ __forceinline__ const float *grad_at(const ConvGeom &g, const float *__restrict__ dz, const PixelCtx &p,
+                                                const TapCtx &t) {
     int hh = p.h0 - t.dr, ww = p.w0 - t.ds;
-    if (hh < 0 || ww < 0) return 0.f;
+    if (hh < 0 || ww < 0) return nullptr;
     int ho = hh / g.sh, wo = ww / g.sw;
-    if (ho * g.sh != hh || wo * g.sw != ww || ho >= g.Ho || wo >= g.Wo) return 0.f;
-    return __ldg(dz + p.base + ((long long)ho * g.Wo + wo) * g.K + t.ch);
+    if (ho * g.sh != hh || wo * g.sw != ww || ho >= g.Ho || wo >= g.Wo) return nullptr;
+    return dz + p.base + ((long long)ho * g.Wo + wo) * g.K + t.ch;
+}
+
+__device__ __forceinline__ float load1(const float *q) { return q ? __ldg(q) : 0.f; }
+__device__ __forceinline__ float4 load4(const float *q) {
+    return q ? __ldg(reinterpret_cast<const float4 *>(q)) : make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
 // ------------------------------------------------------------------ problems
@@ -79,9 +87,13 @@ struct FwdProblem {
     int act;
     typedef PixelCtx Row;
     typedef TapCtx Col;
+    static constexpr bool kAContigK = true;     // A(m, k): consecutive k = consecutive input channels
+    static constexpr bool kBContigK = false;    // B(k, n) = w[k][n]: consecutive n
+    __device__ bool vec4_ok() const { return (g.C & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }
     __device__ void make_row(int m, int M, Row &r) const { decode_out_pixel(g, m, M, r); }
     __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.C, kend, c); }
-    __device__ float a(const Row &r, const Col &c) const { return gather_input(g, x, r, c); }
+    __device__ float a(const Row &r, const Col &c) const { return load1(input_at(g, x, r, c)); }
+    __device__ float4 a4(const Row &r, const Col &c) const { return load4(input_at(g, x, r, c)); }
     __device__ float b(int k, int n) const { return __ldg(w + (long long)k * g.K + n); }
     __device__ void store(int m, int n, float v) const {
         if (bias) v += __ldg(bias + n);
@@ -96,9 +108,13 @@ struct DgradProblem {
     int accumulate;
     typedef PixelCtx Row;
     typedef TapCtx Col;
+    static constexpr bool kAContigK = true;     // consecutive k = consecutive output channels of dz
+    static constexpr bool kBContigK = true;     // B(k, n) = w[tap][n][ko]: consecutive ko
+    __device__ bool vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(dz) & 15) == 0; }
     __device__ void make_row(int m, int M, Row &r) const { decode_in_pixel(g, m, M, r); }
     __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.K, kend, c); }
-    __device__ float a(const Row &r, const Col &c) const { return gather_grad(g, dz, r, c); }
+    __device__ float a(const Row &r, const Col &c) const { return load1(grad_at(g, dz, r, c)); }
+    __device__ float4 a4(const Row &r, const Col &c) const { return load4(grad_at(g, dz, r, c)); }
     __device__ float b(int k, int n) const {
         int tap = k / g.K, ko = k - tap * g.K;
         return __ldg(w + ((long long)tap * g.C + n) * g.K + ko);
@@ -116,12 +132,16 @@ struct WgradProblem {
     int taps_c;   // kh*kw*C: rows below are filter taps, row == taps_c is the bias row
     typedef TapCtx Row;
     typedef PixelCtx Col;
+    static constexpr bool kAContigK = false;    // A(m, k) = x[pixel k][tap/channel m]: consecutive m (channels)
+    static constexpr bool kBContigK = false;    // B(k, n) = dz[pixel k][n]: consecutive n
+    __device__ bool vec4_ok() const { return false; }
     __device__ void make_row(int k, int M, Row &r) const {
         decode_tap(g, k, g.C, taps_c, r);
         if (k == taps_c && k < M) r.valid = 2;
     }
     __device__ void make_col(int m, int mend, Col &c) const { decode_out_pixel(g, m, mend, c); }
-    __device__ float a(const Row &r, const Col &c) const { return r.valid == 2 ? 1.f : gather_input(g, x, c, r); }
+    __device__ float a(const Row &r, const Col &c) const { return r.valid == 2 ? 1.f : load1(input_at(g, x, c, r)); }
+    __device__ float4 a4(const Row &, const Col &) const { return make_float4(0.f, 0.f, 0.f, 0.f); }
     __device__ float b(int m, int n) const { return __ldg(dz + (long long)m * g.K + n); }
     __device__ void store(int k, int n, float v) const {
         if (k < taps_c) dw[(long long)k * g.K + n] = v;

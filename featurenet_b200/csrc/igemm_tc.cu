@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int
     constexpr int B_BYTES = BN * TC_BK * 4;
     constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
     constexpr int B_PER = BN / 8;
-    constexpr int TMEM_COLS = BN < 32 ? 32 : BN;          // BN is 64 / 128 / 256: already a power of two
+    constexpr int TMEM_COLS = BN < 32 ? 32 : BN;          // BN is 32 / 64 / 128 / 256: a power of two
     extern __shared__ uint8_t tc_smem_raw[];
     __shared__ uint64_t empty_bar[TC_STAGES];
     __shared__ uint64_t done_bar;
@@ -118,21 +118,90 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = tmem_holder;
 
-    // loader mapping: a warp handles one tile row at a time, lanes walk the 32 k of the tile
-    const int kc = lane, r0 = warp;
+    // ---- operand loaders.  The lanes of a warp sit on the axis along which the operand is contiguous
+    // in global memory (coalesced loads); where four consecutive k are four consecutive channels the A
+    // operand is fetched 16 bytes at a time.  Element (row, k) always lands at tile_offset(row, k).
+    const bool vec4 = P::kAContigK && p.vec4_ok();
     float a_reg[16], b_reg[B_PER];
     auto gather = [&](int k0) {
-        typename P::Col col;
-        p.make_col(k0 + kc, kend, col);
+        if (vec4) {
+            // lane = (row sub-index, 16-byte chunk); 4 passes of 32 rows
+            typename P::Col col;
+            p.make_col(k0 + 4 * (lane & 7), kend, col);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const typename P::Row &row = rows[r0 + 8 * i];
-            a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+            for (int i = 0; i < 4; ++i) {
+                const typename P::Row &row = rows[warp * 4 + (lane >> 3) + 32 * i];
+                float4 v = (col.valid && row.valid) ? p.a4(row, col) : make_float4(0.f, 0.f, 0.f, 0.f);
+                a_reg[4 * i] = v.x; a_reg[4 * i + 1] = v.y; a_reg[4 * i + 2] = v.z; a_reg[4 * i + 3] = v.w;
+            }
+        } else if (P::kAContigK) {
+            typename P::Col col;
+            p.make_col(k0 + lane, kend, col);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const typename P::Row &row = rows[warp + 8 * i];
+                a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+            }
+        } else {
+            // lanes along the rows: row = lane + 32*i, k = warp + 8*j
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                typename P::Col col;
+                p.make_col(k0 + warp + 8 * j, kend, col);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const typename P::Row &row = rows[lane + 32 * i];
+                    a_reg[4 * j + i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+                }
+            }
         }
+        if (P::kBContigK) {
 #pragma unroll
-        for (int i = 0; i < B_PER; ++i) {
-            int n = n0 + r0 + 8 * i;
-            b_reg[i] = (k0 + kc < kend && n < N) ? p.b(k0 + kc, n) : 0.f;
+            for (int i = 0; i < B_PER; ++i) {
+                int n = n0 + warp + 8 * i;
+                b_reg[i] = (k0 + lane < kend && n < N) ? p.b(k0 + lane, n) : 0.f;
+            }
+        } else {
+            // lanes along n: n = lane + 32*i, k = warp + 8*j
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int i = 0; i < BN / 32; ++i) {
+                    int n = n0 + lane + 32 * i, k = k0 + warp + 8 * j;
+                    b_reg[j * (BN / 32) + i] = (k < kend && n < N) ? p.b(k, n) : 0.f;
+                }
+        }
+    };
+    auto stash = [&](uint8_t *sa, uint8_t *sb) {
+        if (vec4) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float4 v = make_float4(to_tf32(a_reg[4 * i]), to_tf32(a_reg[4 * i + 1]), to_tf32(a_reg[4 * i + 2]),
+                                       to_tf32(a_reg[4 * i + 3]));
+                *reinterpret_cast<float4 *>(sa + tile_offset(warp * 4 + (lane >> 3) + 32 * i, 4 * (lane & 7), layout)) = v;
+            }
+        } else if (P::kAContigK) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                *reinterpret_cast<float *>(sa + tile_offset(warp + 8 * i, lane, layout)) = to_tf32(a_reg[i]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<float *>(sa + tile_offset(lane + 32 * i, warp + 8 * j, layout)) = to_tf32(a_reg[4 * j + i]);
+        }
+        if (P::kBContigK) {
+#pragma unroll
+            for (int i = 0; i < B_PER; ++i)
+                *reinterpret_cast<float *>(sb + tile_offset(warp + 8 * i, lane, layout)) = to_tf32(b_reg[i]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int i = 0; i < BN / 32; ++i)
+                    *reinterpret_cast<float *>(sb + tile_offset(lane + 32 * i, warp + 8 * j, layout)) =
+                        to_tf32(b_reg[j * (BN / 32) + i]);
         }
     };
 
@@ -146,12 +215,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int
         const int s = kt % TC_STAGES;
         uint8_t *sa = smem + s * STAGE_BYTES, *sb = sa + TC_A_BYTES;
         if (kt >= TC_STAGES) mbar_wait(&empty_bar[s], (uint32_t)((kt / TC_STAGES - 1) & 1));
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-            *reinterpret_cast<float *>(sa + tile_offset(r0 + 8 * i, kc, layout)) = to_tf32(a_reg[i]);
-#pragma unroll
-        for (int i = 0; i < B_PER; ++i)
-            *reinterpret_cast<float *>(sb + tile_offset(r0 + 8 * i, kc, layout)) = to_tf32(b_reg[i]);
+        stash(sa, sb);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
         __syncthreads();
         if (tid == 0) {
@@ -166,39 +230,46 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int
         if (kt + 1 < KT) gather(kbeg + (kt + 1) * TC_BK);               // in flight while the tensor core works
     }
 
-    // epilogue: warp w reads TMEM lanes 32*(w%4).. (its quadrant), the two warpgroups split the columns
+    // ---- epilogue.  Warp w owns TMEM lanes 32*(w%4)..+31 (its quadrant); 32-column chunks alternate
+    // between the two warpgroups.  Each chunk is transposed through shared memory (the pipeline stages
+    // are free by now) so that a warp stores 32 consecutive floats of one output row: 128-byte lines.
     if (KT > 0) {
         mbar_wait(&done_bar, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     }
     const int quad = warp & 3, half = warp >> 2;
-    const int m = m0 + quad * 32 + lane;
-    for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 16) {
-        if (c0 >= n_tile) break;                            // warp-uniform
-        uint32_t v[16];
+    float *xpose = reinterpret_cast<float *>(smem) + warp * (32 * 33);
+    for (int c0 = half * 32; c0 < n_tile; c0 += 64) {       // warp-uniform bounds
+        uint32_t v[32];
         if (KT > 0) {
             uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0;
             asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                  "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
                 : "r"(taddr));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         } else {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = 0u;
+            for (int j = 0; j < 32; ++j) v[j] = 0u;
         }
-        if (m < M) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                int n = n0 + c0 + j;
-                if (n < N) {
-                    float val = __uint_as_float(v[j]);
-                    if (partial) partial[((long long)blockIdx.z * M + m) * N + n] = val;
-                    else p.store(m, n, val);
-                }
+        for (int j = 0; j < 32; ++j) xpose[lane * 33 + j] = __uint_as_float(v[j]);   // thread = row
+        __syncwarp();
+        const int n = n0 + c0 + lane;                                                   // thread = column
+        for (int r = 0; r < 32; ++r) {
+            int m = m0 + quad * 32 + r;
+            if (m >= M) break;
+            if (n < N) {
+                float val = xpose[r * 33 + lane];
+                if (partial) partial[((long long)blockIdx.z * M + m) * N + n] = val;
+                else p.store(m, n, val);
             }
         }
+        __syncwarp();
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -231,7 +302,7 @@ struct TcPlan {
 
 static TcPlan tc_plan(long long M, long long N, long long Kg) {
     TcPlan t;
-    t.bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+    t.bn = N <= 32 ? 32 : (N <= 64 ? 64 : (N <= 128 ? 128 : 256));
     long long tiles = ceil_div<long long>(M, TC_BM) * ceil_div<long long>(N, t.bn);
     long long splits = 1;
     if (tiles < kNumSMs && Kg >= 8 * TC_BK) {
@@ -285,7 +356,8 @@ static int tc_run(const P &p, long long M, long long N, long long Kg, void *ws, 
     }
     dim3 grid((unsigned)ceil_div<long long>(M, TC_BM), (unsigned)ceil_div<long long>(N, plan.bn), plan.splits);
     int m = (int)M, n = (int)N, kg = (int)Kg, rc;
-    if (plan.bn == 64) rc = tc_launch<P, 64>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
+    if (plan.bn == 32) rc = tc_launch<P, 32>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
+    else if (plan.bn == 64) rc = tc_launch<P, 64>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
     else if (plan.bn == 128) rc = tc_launch<P, 128>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
     else rc = tc_launch<P, 256>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
     if (rc != FNET_OK) return rc;
@@ -297,9 +369,10 @@ static int tc_run(const P &p, long long M, long long N, long long Kg, void *ws, 
     return rc;
 }
 
-// The tensor-core tile is 128 x >=64: only worth it (and only exercised) for wide GEMMs.
+// The tensor-core tile is 128 rows x 32..256 columns x 32 deep; below these sizes it would be mostly
+// padding and the FFMA kernels take over.
 static bool tc_shape_ok(long long M, long long N, long long Kg) {
-    return M >= 128 && N >= 32 && Kg >= 32 && M <= 0x7fffffffLL && Kg <= 0x7fffffffLL && N <= 65535LL * 64;
+    return M >= 96 && N >= 8 && Kg >= 24 && M <= 0x7fffffffLL && Kg <= 0x7fffffffLL && N <= 65535LL * 64;
 }
 
 bool tc_supported(const ConvGeom &g, int math, int product) {

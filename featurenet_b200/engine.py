@@ -626,6 +626,14 @@ class Engine(object):
         key = (kind, batch)
         ops = self.programs.get(key)
         if ops is None:
+            # split plans depend on the batch (fewer rows -> more splits), so the shared workspace may have to grow
+            need = max(self._workspace_need(i, batch) for i in range(len(self.nodes)))
+            if need > self.ws_bytes:
+                self.stream.synchronize()
+                self._drop_graphs()                      # programs hold the old workspace pointer
+                with torch.cuda.device(self.device):
+                    self.ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+                self.ws_bytes = need
             ops = self.programs[key] = self._build_program(kind, batch)
             self.launches_per_step = getattr(self, "launches_per_step", {})
             self.launches_per_step[key] = len(ops)

@@ -24,6 +24,9 @@ TC_CONV_CASES = [
     ((2, 12, 12, 64), (3, 3), 64, (1, 1)),      # keras-template style 3x3, K = 576
     ((3, 9, 9, 40), (5, 5), 72, (2, 2)),        # stride 2, ragged M (75 rows), K = 1000
     ((2, 8, 8, 33), (3, 3), 130, (1, 1)),       # nothing aligned: C = 33, N = 130
+    ((4, 14, 14, 12), (5, 5), 120, (1, 1)),     # lenet5 conv3: the data gradient has N = 12 (one 16-wide MMA), K = 3000
+    ((2, 32, 32, 6), (5, 5), 12, (1, 1)),       # lenet5 conv2: N = 12 forward, C = 6 (scalar gather)
+    ((3, 16, 16, 192), (1, 1), 3, (1, 1)),      # 192 -> 3 "Reg_" conv: forward N = 3 stays on the FFMA path, dgrad N = 192
 ]
 
 
