@@ -262,6 +262,50 @@ def measure_workload(workload, args, torch, dist, world, device_index, full=True
     return out, net
 
 
+def run_population_bench(args, dist, world, rank):
+    """A fixed population (nas_5_5_10 sample) sharded by candidate over the ranks: build + 1 epoch + evaluate each."""
+    from featurenet_b200 import population as pop
+    from featurenet_b200 import synth
+    from model.keras_model import KerasFeatureModel
+    from products_tree import ProductSet
+    from tensorflow_generator import TensorflowGenerator
+    import torch
+    n_train, n_test = 10000, 2000
+    with quiet():
+        formatted = ProductSet(os.path.join(ROOT, "featurenet_b200/data/nas_5_5_10_pop32_seed7.pdt")).format_products()
+        formatted = formatted[: args.population]
+        (x_train, y_train), (x_test, y_test) = synth.load("cifar", n_train, n_test)
+    TensorflowGenerator.dataset = "cifar"
+    TensorflowGenerator.X_train, TensorflowGenerator.Y_train = x_train, y_train
+    TensorflowGenerator.X_test, TensorflowGenerator.Y_test = x_test, y_test
+    TensorflowGenerator.input_shape = synth.SHAPES["cifar"]
+    costs = []
+    for product, _ in formatted:
+        with quiet():
+            import copy
+            net = KerasFeatureModel.parse_feature_model(copy.deepcopy(product)).build(synth.SHAPES["cifar"], 10)
+        costs.append(pop.estimate_cost(net, n_train, n_test, 1) if net else 1.0)
+
+    def train_one(index, item):
+        product, original = item
+        return pop.train_product(product, "cifar", epochs=1, batch_size=BATCH, product_features=original)
+
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    results = pop.run_population(formatted, train_one, costs, rank=rank, world_size=world,
+                                 dist=dist if world > 1 else None)
+    torch.cuda.synchronize()
+    seconds = pop.max_over_ranks(time.perf_counter() - t0, dist if world > 1 else None, device="cuda")
+    valid = [r for _, r in results if r.get("valid")]
+    return {"candidates": len(results), "valid": len(valid), "seconds": seconds,
+            "candidates_per_hour": 3600.0 * len(results) / seconds, "scaling": "strong (fixed population, LPT-sharded)",
+            "what": "nas_5_5_10 seed-7 sample: build + 1 epoch on %d synthetic CIFAR-shape images + evaluate on %d" % (n_train, n_test),
+            "mean_accuracy": float(np.mean([r["accuracy"] for r in valid])) if valid else 0.0,
+            "per_rank_candidates": [sum(1 for _, r in results if r.get("rank") == k) for k in range(world)]}
+
+
 def roofline_from(table, pk):
     label = max(table, key=lambda k: table[k]["ms_total"])
     row = table[label]
@@ -309,6 +353,7 @@ def run_ours(args):
                                 "params": res["params"], "train_mflop_per_image": res["train_mflop_per_image"],
                                 "launch_calls_per_step": res["launch_calls_per_step"],
                                 "workload": WORKLOADS[other][3]}
+    population = run_population_bench(args, dist, world, rank) if args.population > 0 else None
     if rank == 0:
         pk = peaks()
         line = {
@@ -330,6 +375,7 @@ def run_ours(args):
             "profile": {k: {"launches": v["launches"], "ms_total": round(v["ms_total"], 4)}
                         for k, v in sorted(main["profile"].items(), key=lambda kv: -kv[1]["ms_total"])},
             "other_workloads": extra,
+            "population": population,
         }
         if world == 1:
             _, net2, dataset = build_candidate(args.workload)
@@ -353,6 +399,7 @@ def main():
     ap.add_argument("--workload", default="nas1", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--quick", action="store_true", help="skip the secondary workloads")
+    ap.add_argument("--population", type=int, default=16, help="candidates of the sharded population run (0 = skip)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -372,7 +372,7 @@ static int tc_run(const P &p, long long M, long long N, long long Kg, void *ws, 
 // The tensor-core tile is 128 rows x 32..256 columns x 32 deep; below these sizes it would be mostly
 // padding and the FFMA kernels take over.
 static bool tc_shape_ok(long long M, long long N, long long Kg) {
-    return M >= 96 && N >= 8 && Kg >= 24 && M <= 0x7fffffffLL && Kg <= 0x7fffffffLL && N <= 65535LL * 64;
+    return M >= 32 && N >= 1 && Kg >= 24 && M * N * Kg >= (1LL << 22) && M <= 0x7fffffffLL && Kg <= 0x7fffffffLL && N <= 65535LL * 64;
 }
 
 bool tc_supported(const ConvGeom &g, int math, int product) {

@@ -1,0 +1,91 @@
+"""Population scheduling: whole candidates are placed on GPUs, one process per GPU, no data-path collective.
+
+The reference trains the candidates of a population one after the other in a single process
+(/root/reference/full.py:28-36, pledge_evolution.py:117-125, full_evolution.py:244-256; its
+multiprocessing attempts are commented out, evolution.py:93-98).  Candidates are independent
+(build, train, evaluate) jobs, so here they are sharded by candidate:
+
+* every rank (launched by torchrun, one per GPU) computes the SAME assignment from the same
+  cost estimates -- longest-processing-time-first onto the least loaded rank -- so no work
+  has to be communicated;
+* each rank trains its share with the ordinary single-GPU engine;
+* results travel back as Python objects over the control plane (``all_gather_object``), in
+  candidate order, so report files are identical to a sequential run.
+
+A generation barrier exists only because the evolution drivers select on all fitnesses.
+"""
+import contextlib
+import io
+import time
+
+
+def estimate_cost(network, n_train, n_eval, epochs):
+    """Relative cost of one candidate: analytic train flops plus a per-launch latency term.
+
+    Small candidates are launch-bound (a step costs ~ #layers x a few microseconds), large
+    ones FLOP-bound; the sum of the two orders them well enough for LPT placement.
+    """
+    flops_per_image = 3.0 * network.train_flops_per_image()
+    steps_images = float(n_train) * epochs
+    launch_term = 4.0e6 * len(network.layers)          # ~ flops a B200 could do in one launch latency, per image-batch
+    return steps_images * (flops_per_image + launch_term / 128.0) + n_eval * flops_per_image / 3.0
+
+
+def assign_lpt(costs, world_size):
+    """Longest-processing-time-first: returns a list (per rank) of candidate indices, deterministic."""
+    order = sorted(range(len(costs)), key=lambda i: (-costs[i], i))
+    loads = [0.0] * world_size
+    shards = [[] for _ in range(world_size)]
+    for i in order:
+        r = min(range(world_size), key=lambda j: (loads[j], j))
+        shards[r].append(i)
+        loads[r] += costs[i]
+    return shards
+
+
+def max_over_ranks(value, dist=None, device=None):
+    """The slowest rank's value (a multi-GPU time is the max over ranks, never a wall clock of one)."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return float(value)
+    import torch
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device or "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def run_population(products, train_one, costs, rank=0, world_size=1, dist=None):
+    """Train this rank's share of ``products``; gather (index, result) pairs on every rank, in index order.
+
+    train_one(index, product) -> picklable result (e.g. dict(accuracy=..., history=..., params=...)).
+    Failures are reported, not raised: an invalid or out-of-memory candidate yields ``{"error": ...}``,
+    as the reference turns them into accuracy 0 (tensorflow_generator.py:109-111, helpers.py:172-174).
+    """
+    mine = assign_lpt(costs, world_size)[rank]
+    local = []
+    for index in mine:
+        started = time.time()
+        try:
+            result = train_one(index, products[index])
+        except Exception as e:                       # noqa: BLE001 -- one bad candidate must not kill the population
+            result = {"error": "%s: %s" % (type(e).__name__, e), "accuracy": 0}
+        if isinstance(result, dict):
+            result.setdefault("seconds", time.time() - started)
+            result.setdefault("rank", rank)
+        local.append((index, result))
+    if dist is not None and dist.is_initialized() and world_size > 1:
+        gathered = [None] * world_size
+        dist.all_gather_object(gathered, local)
+        merged = [pair for part in gathered for pair in part]
+    else:
+        merged = local
+    return sorted(merged, key=lambda pair: pair[0])
+
+
+def train_product(product, dataset, epochs, batch_size, product_features=None, data_augmentation=False):
+    """One candidate through the reference-named runner; returns the fields the drivers log."""
+    from tensorflow_generator import TensorflowGenerator
+    with contextlib.redirect_stdout(io.StringIO()):
+        gen = TensorflowGenerator(product, epochs=epochs, dataset=dataset, data_augmentation=data_augmentation,
+                                  batch_size=batch_size, product_features=product_features)
+    return {"accuracy": float(gen.accuracy), "params": int(gen.params), "training_time": float(gen.training_time),
+            "history": (list(gen.history[0]), list(gen.history[1])), "valid": bool(gen.params)}

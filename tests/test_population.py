@@ -1,0 +1,86 @@
+"""Candidate sharding on CPU: LPT placement, and the N>1 control plane under gloo with world_size 2."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from featurenet_b200 import population as pop
+
+
+def test_lpt_assignment_is_balanced_and_deterministic():
+    costs = [9.0, 1.0, 8.0, 2.0, 7.0, 3.0, 6.0, 4.0, 5.0]
+    shards = pop.assign_lpt(costs, 2)
+    assert sorted(i for s in shards for i in s) == list(range(9))
+    loads = [sum(costs[i] for i in s) for s in shards]
+    assert abs(loads[0] - loads[1]) <= max(costs) * 0.15
+    assert pop.assign_lpt(costs, 2) == shards
+    assert pop.assign_lpt(costs, 1) == [sorted(range(9), key=lambda i: (-costs[i], i))]
+    assert pop.assign_lpt([], 4) == [[], [], [], []]
+
+
+def test_single_rank_run_collects_results_and_survives_a_bad_candidate():
+    def train_one(index, product):
+        if product == "bad":
+            raise ValueError("cannot build")
+        return {"accuracy": 0.1 * index}
+    out = pop.run_population(["a", "bad", "c"], train_one, [1.0, 1.0, 1.0])
+    assert [i for i, _ in out] == [0, 1, 2]
+    assert out[1][1]["accuracy"] == 0 and "cannot build" in out[1][1]["error"]
+    assert out[2][1]["accuracy"] == pytest.approx(0.2)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, queue):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        products = ["p%d" % i for i in range(7)]
+        costs = [7.0, 1.0, 6.0, 2.0, 5.0, 3.0, 4.0]
+        trained_here = []
+
+        def train_one(index, product):
+            trained_here.append(index)
+            return {"accuracy": index / 10.0, "name": product}
+
+        results = pop.run_population(products, train_one, costs, rank=rank, world_size=world, dist=dist)
+        slowest = pop.max_over_ranks(10.0 * (rank + 1), dist)
+        queue.put((rank, trained_here, results, slowest))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_under_gloo_share_the_population_without_overlap():
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, queue)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [queue.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    got.sort()
+    (r0, mine0, res0, slow0), (r1, mine1, res1, slow1) = got
+    assert sorted(mine0 + mine1) == list(range(7)) and not set(mine0) & set(mine1)
+    assert res0 == res1                                            # every rank ends with the full, ordered result list
+    assert [i for i, _ in res0] == list(range(7))
+    assert [r["name"] for _, r in res0] == ["p%d" % i for i in range(7)]
+    assert {r["rank"] for _, r in res0} == {0, 1}
+    assert slow0 == slow1 == 20.0                                  # max over ranks
+
+
+def test_cost_estimate_orders_small_and_large_candidates():
+    from tests.util import build_template
+    small = build_template("lenet5", (28, 28, 1))
+    large = build_template("keras", (32, 32, 3))
+    assert pop.estimate_cost(large, 50000, 10000, 1) > 3 * pop.estimate_cost(small, 50000, 10000, 1)
