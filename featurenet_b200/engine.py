@@ -515,8 +515,16 @@ class Engine(object):
         if not kind.endswith("_fed"):
             xdev, ydev, perm = self.data[kind.split("_")[0]]
             row = _prod(self.shape[0])
-            ops.append(("gather_rows", L.fnet_gather_rows, (batch, row, C.c_void_p(perm.data_ptr()), st,
-                                                            C.c_void_p(xdev.data_ptr()), C.c_void_p(self.act[0].data_ptr()), sp)))
+            if kind == "train_aug":
+                h, w, c = self.shape[0]
+                tx, ty, flip = self.aug_dev
+                ops.append(("gather_shift_flip", L.fnet_gather_shift_flip,
+                            (batch, h, w, c, C.c_void_p(perm.data_ptr()), st, C.c_void_p(tx.data_ptr()),
+                             C.c_void_p(ty.data_ptr()), C.c_void_p(flip.data_ptr()), C.c_void_p(xdev.data_ptr()),
+                             C.c_void_p(self.act[0].data_ptr()), sp)))
+            else:
+                ops.append(("gather_rows", L.fnet_gather_rows, (batch, row, C.c_void_p(perm.data_ptr()), st,
+                                                                C.c_void_p(xdev.data_ptr()), C.c_void_p(self.act[0].data_ptr()), sp)))
             ops.append(("gather_rows", L.fnet_gather_rows, (batch, self.n_out, C.c_void_p(perm.data_ptr()), st,
                                                             C.c_void_p(ydev.data_ptr()), C.c_void_p(self.yb.data_ptr()), sp)))
         ops += self._forward_program(batch, training)
@@ -584,6 +592,8 @@ class Engine(object):
             b = 16 * args[0]
         elif label == "gather_rows":
             b = 4 * 2 * args[0] * args[1]
+        elif label == "gather_shift_flip":
+            b = 4 * 2 * args[0] * args[1] * args[2] * args[3]
         return f, b
 
     def profile_steps(self, kind, batch, steps, warmup=3):
@@ -756,7 +766,7 @@ class Engine(object):
         return [loss, acc]
 
     def fit(self, x, y, batch_size=32, epochs=1, validation_data=None, shuffle=True, callbacks=(), verbose=0,
-            permutations=None, initial_epoch=0, **_):
+            permutations=None, initial_epoch=0, augment=None, **_):
         """keras Model.fit semantics: see module docstring.  ``permutations[e]`` overrides the shuffle (tests)."""
         from .callbacks import History, Callback
         if self.net.optimizer is None:
@@ -771,6 +781,21 @@ class Engine(object):
         self._ensure_capacity(cap)
         self._set_data("train", x, y)
         perm_dev = self.data["train"][2]
+        train_kind = "train"
+        if augment is not None:
+            if len(self.shape[0]) != 3:
+                raise ValueError("shift/flip augmentation needs image inputs [H, W, C]")
+            train_kind = "train_aug"
+            old = getattr(self, "aug_dev", None)
+            if old is None or old[0].numel() != n:
+                for key in [k for k in self.programs if k[0] == "train_aug"]:
+                    if key in self.graphs:
+                        self.lib.fnet_graph_destroy(self.graphs.pop(key))
+                    self.programs.pop(key)
+                with torch.cuda.device(self.device):
+                    self.aug_dev = (torch.zeros(n, dtype=torch.float32, device=self.device),
+                                    torch.zeros(n, dtype=torch.float32, device=self.device),
+                                    torch.zeros(n, dtype=torch.uint8, device=self.device))
         history = History()
         cbs = [history] + list(callbacks)
         per_batch = [cb for cb in cbs if getattr(type(cb), "on_batch_end", None) not in (None, Callback.on_batch_end)]
@@ -794,11 +819,14 @@ class Engine(object):
                 order = np.arange(n, dtype=np.int32)
             with torch.cuda.stream(self.stream):
                 perm_dev.copy_(torch.from_numpy(order))
+                if augment is not None:                 # this epoch's random shifts / flips, indexed by position
+                    for dev_arr, host_arr in zip(self.aug_dev, augment.draw(n)):
+                        dev_arr.copy_(torch.from_numpy(host_arr))
             self._zero_metrics(self.state)
             for step in range(steps):
                 b = min(batch_size, n - step * batch_size)
                 self._sync_lr()
-                self._step("train", b)
+                self._step(train_kind, b)
                 for cb in per_batch:
                     cb.on_batch_end(step, {"batch": step, "size": b})
             loss, acc = self._read_metrics(n)
@@ -822,8 +850,9 @@ class Engine(object):
         """The augmentation path of helpers.py:115-167; the generator must expose the arrays it flows from."""
         if not hasattr(generator, "x") or not hasattr(generator, "y"):
             raise NotImplementedError("fit_generator needs a featurenet_b200 data generator (device-side augmentation)")
+        kw.pop("workers", None)
         return self.fit(generator.x, generator.y, batch_size=generator.batch_size, epochs=epochs,
-                        validation_data=validation_data, callbacks=callbacks, verbose=verbose, **kw)
+                        validation_data=validation_data, callbacks=callbacks, verbose=verbose, augment=generator, **kw)
 
     def release(self):
         self.stream.synchronize()

@@ -80,6 +80,7 @@ SIGNATURES = {
     "fnet_adam_step": (C.c_int, [_I64, _P, _P, _P, _P, _P, _F, _F, _F, _P]),
     "fnet_sgd_step": (C.c_int, [_I64, _P, _P, _P, _P, _F, C.c_int, _P]),
     "fnet_gather_rows": (C.c_int, [_I32, _I64, _P, _P, _P, _P, _P]),
+    "fnet_gather_shift_flip": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "fnet_u8_to_f32": (C.c_int, [_I64, _P, _F, _P, _P]),
     "fnet_graph_begin": (C.c_int, [_P]),
     "fnet_graph_end": (C.c_int, [_P, C.POINTER(_P)]),

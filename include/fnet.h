@@ -224,6 +224,15 @@ int fnet_sgd_step(int64_t n, float *params, const float *grads, float *velocity,
  * keras Model.fit(shuffle=True) (helpers.py:105-111) on a device-resident dataset */
 int fnet_gather_rows(int32_t batch, int64_t row_elems, const int32_t *perm, const int32_t *state,
                      const float *src, float *dst, void *stream);
+/* The augmenting variant of fnet_gather_rows for images [*, h, w, c]: replaces
+ * ImageDataGenerator(width_shift_range, height_shift_range, horizontal_flip, fill_mode='nearest').flow()
+ * of helpers.py:115-167.  For position p = cursor + i of the epoch:
+ * dst[i, r, q, :] = bilinear(src[perm[p]], r + tx[p], q' + ty[p]) with q' = w-1-q when flip[p] != 0,
+ * coordinates clamped to the image (order-1 interpolation, 'nearest' fill).  tx, ty, flip are
+ * per-epoch arrays (device), drawn by the host. */
+int fnet_gather_shift_flip(int32_t batch, int32_t h, int32_t w, int32_t c, const int32_t *perm,
+                           const int32_t *state, const float *tx, const float *ty, const uint8_t *flip,
+                           const float *src, float *dst, void *stream);
 /* dst = float(src) * scale : the `astype('float32') / 255` of tensorflow_generator.py:310-313 */
 int fnet_u8_to_f32(int64_t n, const uint8_t *src, float scale, float *dst, void *stream);
 
