@@ -483,12 +483,14 @@ class Engine(object):
                 raise NotImplementedError(kind)
         return ops
 
-    def _loss_op(self, batch, with_grad):
+    def _loss_op(self, batch, with_grad, scale_batch=None):
+        """scale_batch: the batch the mean is taken over (the GLOBAL batch in data-parallel training)."""
         L = self.lib
         last = len(self.nodes) - 1
         dz = self._g(last) if with_grad else None
         return ("softmax_cce", L.fnet_softmax_cce,
-                (batch, self.n_out, self._a(last, with_grad), C.c_void_p(self.yb.data_ptr()), 1.0 / batch, dz,
+                (batch, self.n_out, self._a(last, with_grad), C.c_void_p(self.yb.data_ptr()),
+                 1.0 / (scale_batch or batch), dz,
                  C.c_void_p(self.loss_sum.data_ptr()), C.c_void_p(self.correct.data_ptr()), self.sp))
 
     def _optimizer_op(self):
@@ -652,16 +654,19 @@ class Engine(object):
             return
         graph = self.graphs.get(key)
         if graph is None:
-            # capture without executing: the captured launches run for the first time at graph launch
-            self.lib.fnet_graph_begin(self.sp)
-            try:
-                for _, fn, args in ops:
-                    fn(*args)
-            finally:
-                handle = C.c_void_p()
-                self.lib.fnet_graph_end(self.sp, C.byref(handle))
-            graph = self.graphs[key] = handle
+            graph = self.graphs[key] = self._capture(ops)
         self.lib.fnet_graph_launch(graph, self.sp)
+
+    def _capture(self, ops):
+        """Record a launch list into a CUDA graph (nothing executes until the graph is launched)."""
+        self.lib.fnet_graph_begin(self.sp)
+        try:
+            for _, fn, args in ops:
+                fn(*args)
+        finally:
+            handle = C.c_void_p()
+            self.lib.fnet_graph_end(self.sp, C.byref(handle))
+        return handle
 
     # ------------------------------------------------------------------ host-side loop pieces
     def _sync_lr(self):
