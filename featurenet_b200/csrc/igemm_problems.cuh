@@ -95,6 +95,9 @@ struct FwdProblem {
     __device__ float a(const Row &r, const Col &c) const { return load1(input_at(g, x, r, c)); }
     __device__ float4 a4(const Row &r, const Col &c) const { return load4(input_at(g, x, r, c)); }
     __device__ float b(int k, int n) const { return __ldg(w + (long long)k * g.K + n); }
+    __device__ const float *a_ptr(const Row &r, const Col &c) const { return input_at(g, x, r, c); }
+    __device__ const float *b_ptr(int k, int n) const { return w + (long long)k * g.K + n; }
+    __device__ const float *any_ptr() const { return x; }
     __device__ void store(int m, int n, float v) const {
         if (bias) v += __ldg(bias + n);
         y[(long long)m * g.K + n] = act_apply(v, act);
@@ -119,6 +122,12 @@ struct DgradProblem {
         int tap = k / g.K, ko = k - tap * g.K;
         return __ldg(w + ((long long)tap * g.C + n) * g.K + ko);
     }
+    __device__ const float *a_ptr(const Row &r, const Col &c) const { return grad_at(g, dz, r, c); }
+    __device__ const float *b_ptr(int k, int n) const {
+        int tap = k / g.K, ko = k - tap * g.K;
+        return w + ((long long)tap * g.C + n) * g.K + ko;
+    }
+    __device__ const float *any_ptr() const { return dz; }
     __device__ void store(int m, int n, float v) const {
         long long at = (long long)m * g.C + n;
         dx[at] = accumulate ? dx[at] + v : v;
@@ -143,6 +152,9 @@ struct WgradProblem {
     __device__ float a(const Row &r, const Col &c) const { return r.valid == 2 ? 1.f : load1(input_at(g, x, c, r)); }
     __device__ float4 a4(const Row &, const Col &) const { return make_float4(0.f, 0.f, 0.f, 0.f); }
     __device__ float b(int m, int n) const { return __ldg(dz + (long long)m * g.K + n); }
+    __device__ const float *a_ptr(const Row &r, const Col &c) const { return input_at(g, x, c, r); }
+    __device__ const float *b_ptr(int m, int n) const { return dz + (long long)m * g.K + n; }
+    __device__ const float *any_ptr() const { return x; }
     __device__ void store(int k, int n, float v) const {
         if (k < taps_c) dw[(long long)k * g.K + n] = v;
         else if (dbias) dbias[n] = v;

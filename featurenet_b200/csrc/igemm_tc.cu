@@ -21,7 +21,6 @@ namespace fnet {
 constexpr int TC_BM = 128;
 constexpr int TC_BK = 32;        // fp32 elements per k-tile row: 128 bytes = one swizzle row
 constexpr int TC_THREADS = 256;
-constexpr int TC_STAGES = 3;
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -81,13 +80,25 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, int layout) {
     return d;
 }
 
-template <class P, int BN>
-__global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int N, int Kg, int k_per_split,
+// cp.async (LDGSTS): global -> shared without passing through registers; bytes beyond src_bytes are zero-filled,
+// which is how padding, ragged tiles and out-of-range taps become zeros.
+__device__ __forceinline__ void cp_async4(uint32_t dst, const float *src, uint32_t src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const float *src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+
+template <class P, int BN, int TC_STAGES>
+__global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int N, int Kg, int k_per_split,
                                                                  float *__restrict__ partial, int layout) {
     constexpr int B_BYTES = BN * TC_BK * 4;
     constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
     constexpr int B_PER = BN / 8;
-    constexpr int TMEM_COLS = BN < 32 ? 32 : BN;          // BN is 32 / 64 / 128 / 256: a power of two
+    constexpr int TMEM_COLS = BN < 32 ? 32 : BN;          // BN is 32 / 64 / 128: a power of two
+    // LAG = how many tiles ago the stage being refilled was multiplied: with 4 stages the refill waits on an
+    // MMA issued two iterations earlier, so long reductions never stall on the tensor core's latency
+    constexpr int LAG = TC_STAGES >= 4 ? 2 : 1;
     extern __shared__ uint8_t tc_smem_raw[];
     __shared__ uint64_t empty_bar[TC_STAGES];
     __shared__ uint64_t done_bar;
@@ -96,6 +107,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
     const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
     const int kbeg = blockIdx.z * k_per_split;
     const int kend = min(Kg, kbeg + k_per_split);
@@ -118,90 +130,66 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = tmem_holder;
 
-    // ---- operand loaders.  The lanes of a warp sit on the axis along which the operand is contiguous
-    // in global memory (coalesced loads); where four consecutive k are four consecutive channels the A
-    // operand is fetched 16 bytes at a time.  Element (row, k) always lands at tile_offset(row, k).
+    // ---- operand loaders: every element (row, k) of a tile is copied global -> shared by cp.async straight
+    // to tile_offset(row, k).  The lanes of a warp sit on the axis along which the operand is contiguous in
+    // global memory (coalesced); where four consecutive k are four consecutive channels the A operand moves
+    // 16 bytes per copy.  Up to TC_STAGES-1 tiles are in flight per CTA.
     const bool vec4 = P::kAContigK && p.vec4_ok();
-    float a_reg[16], b_reg[B_PER];
-    auto gather = [&](int k0) {
+    auto issue = [&](int k0, int stage) {
+        const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + TC_A_BYTES;
         if (vec4) {
-            // lane = (row sub-index, 16-byte chunk); 4 passes of 32 rows
-            typename P::Col col;
+            typename P::Col col;                            // lane = (row sub-index, 16-byte chunk); 4 passes of 32 rows
             p.make_col(k0 + 4 * (lane & 7), kend, col);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const typename P::Row &row = rows[warp * 4 + (lane >> 3) + 32 * i];
-                float4 v = (col.valid && row.valid) ? p.a4(row, col) : make_float4(0.f, 0.f, 0.f, 0.f);
-                a_reg[4 * i] = v.x; a_reg[4 * i + 1] = v.y; a_reg[4 * i + 2] = v.z; a_reg[4 * i + 3] = v.w;
+                int r = warp * 4 + (lane >> 3) + 32 * i;
+                const float *src = (col.valid && rows[r].valid) ? p.a_ptr(rows[r], col) : nullptr;
+                cp_async16(sa + tile_offset(r, 4 * (lane & 7), layout), src ? src : p.any_ptr(), src ? 16u : 0u);
             }
         } else if (P::kAContigK) {
             typename P::Col col;
             p.make_col(k0 + lane, kend, col);
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-                const typename P::Row &row = rows[warp + 8 * i];
-                a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+                int r = warp + 8 * i;
+                const float *src = (col.valid && rows[r].valid) ? p.a_ptr(rows[r], col) : nullptr;
+                cp_async4(sa + tile_offset(r, lane, layout), src ? src : p.any_ptr(), src ? 4u : 0u);
             }
         } else {
-            // lanes along the rows: row = lane + 32*i, k = warp + 8*j
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < 4; ++j) {                   // lanes along the rows: row = lane + 32*i, k = warp + 8*j
                 typename P::Col col;
                 p.make_col(k0 + warp + 8 * j, kend, col);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const typename P::Row &row = rows[lane + 32 * i];
-                    a_reg[4 * j + i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+                    int r = lane + 32 * i;
+                    uint32_t dst = sa + tile_offset(r, warp + 8 * j, layout);
+                    if (rows[r].valid == 2) {               // the all-ones row that yields the bias gradient
+                        float one = col.valid ? 1.f : 0.f;
+                        asm volatile("st.shared.f32 [%0], %1;" ::"r"(dst), "f"(one) : "memory");
+                    } else {
+                        const float *src = (col.valid && rows[r].valid) ? p.a_ptr(rows[r], col) : nullptr;
+                        cp_async4(dst, src ? src : p.any_ptr(), src ? 4u : 0u);
+                    }
                 }
             }
         }
         if (P::kBContigK) {
 #pragma unroll
             for (int i = 0; i < B_PER; ++i) {
-                int n = n0 + warp + 8 * i;
-                b_reg[i] = (k0 + lane < kend && n < N) ? p.b(k0 + lane, n) : 0.f;
+                int nn = warp + 8 * i, n = n0 + nn, k = k0 + lane;
+                bool ok = k < kend && n < N;
+                cp_async4(sb + tile_offset(nn, lane, layout), ok ? p.b_ptr(k, n) : p.any_ptr(), ok ? 4u : 0u);
             }
         } else {
-            // lanes along n: n = lane + 32*i, k = warp + 8*j
 #pragma unroll
             for (int j = 0; j < 4; ++j)
 #pragma unroll
-                for (int i = 0; i < BN / 32; ++i) {
-                    int n = n0 + lane + 32 * i, k = k0 + warp + 8 * j;
-                    b_reg[j * (BN / 32) + i] = (k < kend && n < N) ? p.b(k, n) : 0.f;
+                for (int i = 0; i < BN / 32; ++i) {         // lanes along n: n = lane + 32*i, k = warp + 8*j
+                    int nn = lane + 32 * i, n = n0 + nn, k = k0 + warp + 8 * j;
+                    bool ok = k < kend && n < N;
+                    cp_async4(sb + tile_offset(nn, warp + 8 * j, layout), ok ? p.b_ptr(k, n) : p.any_ptr(), ok ? 4u : 0u);
                 }
-        }
-    };
-    auto stash = [&](uint8_t *sa, uint8_t *sb) {
-        if (vec4) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                float4 v = make_float4(to_tf32(a_reg[4 * i]), to_tf32(a_reg[4 * i + 1]), to_tf32(a_reg[4 * i + 2]),
-                                       to_tf32(a_reg[4 * i + 3]));
-                *reinterpret_cast<float4 *>(sa + tile_offset(warp * 4 + (lane >> 3) + 32 * i, 4 * (lane & 7), layout)) = v;
-            }
-        } else if (P::kAContigK) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i)
-                *reinterpret_cast<float *>(sa + tile_offset(warp + 8 * i, lane, layout)) = to_tf32(a_reg[i]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    *reinterpret_cast<float *>(sa + tile_offset(lane + 32 * i, warp + 8 * j, layout)) = to_tf32(a_reg[4 * j + i]);
-        }
-        if (P::kBContigK) {
-#pragma unroll
-            for (int i = 0; i < B_PER; ++i)
-                *reinterpret_cast<float *>(sb + tile_offset(warp + 8 * i, lane, layout)) = to_tf32(b_reg[i]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-#pragma unroll
-                for (int i = 0; i < BN / 32; ++i)
-                    *reinterpret_cast<float *>(sb + tile_offset(lane + 32 * i, warp + 8 * j, layout)) =
-                        to_tf32(b_reg[j * (BN / 32) + i]);
         }
     };
 
@@ -210,24 +198,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_igemm_kernel(P p, int M, int
     const int kadv = layout == 0 ? 2 : 16;                 // descriptor start-address step per 8 k (in 16-byte units)
 
     const int KT = (kend - kbeg + TC_BK - 1) / TC_BK;
-    if (KT > 0) gather(kbeg);
+#pragma unroll
+    for (int t = 0; t < TC_STAGES - LAG; ++t) {            // prologue: tiles 0 .. STAGES-LAG-1 in flight
+        if (t < KT) issue(kbeg + t * TC_BK, t);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
     for (int kt = 0; kt < KT; ++kt) {
         const int s = kt % TC_STAGES;
-        uint8_t *sa = smem + s * STAGE_BYTES, *sb = sa + TC_A_BYTES;
-        if (kt >= TC_STAGES) mbar_wait(&empty_bar[s], (uint32_t)((kt / TC_STAGES - 1) & 1));
-        stash(sa, sb);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+        // refill the stage that tile kt-LAG used (its MMAs must have finished reading it) with tile kt+STAGES-LAG
+        const int nt = kt + TC_STAGES - LAG;
+        if (nt < KT) {
+            const int ns = nt % TC_STAGES;
+            if (kt >= LAG) mbar_wait(&empty_bar[ns], (uint32_t)(((kt - LAG) / TC_STAGES) & 1));
+            issue(kbeg + nt * TC_BK, ns);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group %0;" ::"n"(TC_STAGES - LAG) : "memory"); // tile kt has landed (this thread's part)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");               // ... and is visible to the tensor core
         __syncthreads();
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            uint64_t da = make_smem_desc(smem_u32(sa), layout), db = make_smem_desc(smem_u32(sb), layout);
+            const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + TC_A_BYTES;
+            uint64_t da = make_smem_desc(sa, layout), db = make_smem_desc(sb, layout);
 #pragma unroll
             for (int j = 0; j < TC_BK / 8; ++j)
                 tc_mma_tf32(tmem, da + (uint64_t)(j * kadv), db + (uint64_t)(j * kadv), idesc, (kt > 0 || j > 0) ? 1u : 0u);
             tc_commit(&empty_bar[s]);                                   // arrives when these MMAs have read the stage
             if (kt == KT - 1) tc_commit(&done_bar);
         }
-        if (kt + 1 < KT) gather(kbeg + (kt + 1) * TC_BK);               // in flight while the tensor core works
     }
 
     // ---- epilogue.  Warp w owns TMEM lanes 32*(w%4)..+31 (its quadrant); 32-column chunks alternate
@@ -296,13 +294,13 @@ __global__ void __launch_bounds__(256) tc_reduce_splits_kernel(P p, int M, int N
 }
 
 struct TcPlan {
-    int bn, splits, k_per_split;
+    int bn, splits, k_per_split, stages;
     size_t ws_bytes, smem_bytes;
 };
 
 static TcPlan tc_plan(long long M, long long N, long long Kg) {
     TcPlan t;
-    t.bn = N <= 32 ? 32 : (N <= 64 ? 64 : (N <= 128 ? 128 : 256));
+    t.bn = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
     long long tiles = ceil_div<long long>(M, TC_BM) * ceil_div<long long>(N, t.bn);
     long long splits = 1;
     if (tiles < kNumSMs && Kg >= 8 * TC_BK) {
@@ -315,7 +313,8 @@ static TcPlan tc_plan(long long M, long long N, long long Kg) {
     t.k_per_split = (int)per;
     t.splits = (int)ceil_div<long long>(Kg, per);
     t.ws_bytes = t.splits > 1 ? (size_t)t.splits * M * N * sizeof(float) : 0;
-    t.smem_bytes = (size_t)TC_STAGES * (TC_A_BYTES + t.bn * TC_BK * 4) + 1024;
+    t.stages = per >= 8 * TC_BK ? 4 : 3;          // long reductions: deeper pipeline; short ones: more CTAs per SM
+    t.smem_bytes = (size_t)t.stages * (TC_A_BYTES + t.bn * TC_BK * 4) + 1024;
     return t;
 }
 
@@ -328,16 +327,16 @@ static int tc_layout_mode() {
     return mode;
 }
 
-template <class P, int BN>
+template <class P, int BN, int STAGES>
 static int tc_launch(const P &p, dim3 grid, size_t smem, int m, int n, int kg, int per, float *partial,
                      cudaStream_t stream, const char *what) {
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(tc_igemm_kernel<P, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(tc_igemm_kernel<P, BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
         configured = true;
     }
-    tc_igemm_kernel<P, BN><<<grid, TC_THREADS, smem, stream>>>(p, m, n, kg, per, partial, tc_layout_mode());
+    tc_igemm_kernel<P, BN, STAGES><<<grid, TC_THREADS, smem, stream>>>(p, m, n, kg, per, partial, tc_layout_mode());
     return check_launch(what);
 }
 
@@ -356,10 +355,10 @@ static int tc_run(const P &p, long long M, long long N, long long Kg, void *ws, 
     }
     dim3 grid((unsigned)ceil_div<long long>(M, TC_BM), (unsigned)ceil_div<long long>(N, plan.bn), plan.splits);
     int m = (int)M, n = (int)N, kg = (int)Kg, rc;
-    if (plan.bn == 32) rc = tc_launch<P, 32>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
-    else if (plan.bn == 64) rc = tc_launch<P, 64>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
-    else if (plan.bn == 128) rc = tc_launch<P, 128>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
-    else rc = tc_launch<P, 256>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what);
+#define FNET_TC_LAUNCH(BN_, ST_) tc_launch<P, BN_, ST_>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what)
+    if (plan.stages == 4) rc = plan.bn == 32 ? FNET_TC_LAUNCH(32, 4) : (plan.bn == 64 ? FNET_TC_LAUNCH(64, 4) : FNET_TC_LAUNCH(128, 4));
+    else rc = plan.bn == 32 ? FNET_TC_LAUNCH(32, 3) : (plan.bn == 64 ? FNET_TC_LAUNCH(64, 3) : FNET_TC_LAUNCH(128, 3));
+#undef FNET_TC_LAUNCH
     if (rc != FNET_OK) return rc;
     if (plan.splits > 1) {
         long long blocks = ceil_div<long long>(M * N, 8), cap = (long long)kNumSMs * 8;

@@ -15,7 +15,8 @@ from tests.test_gpu_ops import (L, _release_device_tensors, assert_close, conv_d
 torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
 
-TF32_TOL = 3e-3
+TF32_TOL = 5e-3     # operands reach shared memory by cp.async, so the tensor core truncates them to tf32 (no rounding pass):
+                    # up to 2^-10 per operand, biased towards zero, hence a little above the 3e-3 a rounded tf32 GEMM gives
 
 TC_CONV_CASES = [
     # x shape, kernel, out channels, stride: all have M >= 128, N >= 32, K >= 32 on the forward
