@@ -67,11 +67,58 @@ __global__ void gather_rows_kernel(int32_t batch, int64_t row_elems, const int32
     }
 }
 
+// Inputs and targets of one batch in ONE launch (+ the per-step lr_t of fnet_step_begin when asked):
+// grid = (chunks of the x row, batch); the first chunk of every row also copies the target row.
+__global__ void gather_batch_kernel(int32_t batch, int64_t x_row, int64_t y_row, const int32_t *__restrict__ perm,
+                                    int32_t *__restrict__ state, const float *__restrict__ x_src,
+                                    const float *__restrict__ y_src, float *__restrict__ x_dst, float *__restrict__ y_dst,
+                                    int begin_step, float beta1, float beta2) {
+    const int32_t cursor = state[1];
+    if (begin_step && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+        double t = (double)(state[0] + 1);
+        double lr = (double)__int_as_float(state[2]);
+        state[3] = __float_as_int((float)(lr * sqrt(1.0 - pow((double)beta2, t)) / (1.0 - pow((double)beta1, t))));
+    }
+    for (int32_t row = blockIdx.y; row < batch; row += gridDim.y) {
+        const int64_t from = (int64_t)perm[cursor + row];
+        const float *xs = x_src + from * x_row;
+        float *xd = x_dst + (int64_t)row * x_row;
+        if ((x_row & 3) == 0) {
+            const float4 *s4 = reinterpret_cast<const float4 *>(xs);
+            float4 *d4 = reinterpret_cast<float4 *>(xd);
+            for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < x_row / 4; i += (int64_t)gridDim.x * blockDim.x)
+                d4[i] = __ldg(s4 + i);
+        } else {
+            for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < x_row; i += (int64_t)gridDim.x * blockDim.x)
+                xd[i] = __ldg(xs + i);
+        }
+        if (blockIdx.x == 0)
+            for (int64_t i = threadIdx.x; i < y_row; i += blockDim.x) y_dst[(int64_t)row * y_row + i] = __ldg(y_src + from * y_row + i);
+    }
+}
+
 }  // namespace fnet
 
 using namespace fnet;
 
 extern "C" {
+
+int fnet_gather_batch(int32_t batch, int64_t x_row, int64_t y_row, const int32_t *perm, int32_t *state,
+                      const float *x_src, const float *y_src, float *x_dst, float *y_dst, int begin_step, float beta1,
+                      float beta2, void *stream) {
+    FNET_REQUIRE(batch >= 0 && x_row > 0 && y_row > 0, "fnet_gather_batch: bad sizes");
+    FNET_REQUIRE(perm && state && x_src && y_src && x_dst && y_dst, "fnet_gather_batch: null pointer");
+    FNET_REQUIRE((x_row & 3) != 0 || ((reinterpret_cast<uintptr_t>(x_src) | reinterpret_cast<uintptr_t>(x_dst)) & 15) == 0,
+                 "fnet_gather_batch: 16-byte aligned buffers needed for rows that are a multiple of 4 floats");
+    if (batch == 0) return begin_step ? fnet_step_begin(state, beta1, beta2, stream) : FNET_OK;
+    int64_t vec = (x_row & 3) == 0 ? x_row / 4 : x_row;
+    int bx = (int)ceil_div<int64_t>(vec, 256);
+    if (bx > 8) bx = 8;
+    dim3 grid(bx, batch > 4096 ? 4096 : batch);
+    gather_batch_kernel<<<grid, 256, 0, as_stream(stream)>>>(batch, x_row, y_row, perm, state, x_src, y_src, x_dst, y_dst,
+                                                             begin_step, beta1, beta2);
+    return check_launch("fnet_gather_batch");
+}
 
 int fnet_version(void) { return FNET_VERSION; }
 

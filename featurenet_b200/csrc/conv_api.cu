@@ -19,7 +19,8 @@ int check_math(int math, const char *what) {
 int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
              void *ws, size_t ws_bytes, cudaStream_t s) {
     int rc;
-    if (math != FNET_MATH_FP32 && tc_supported(g, math, 0)) rc = tc_conv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
+    if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, s);
+    else if (math != FNET_MATH_FP32 && tc_supported(g, math, 0)) rc = tc_conv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
     else rc = simt_conv_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
     if (rc == FNET_OK && act == FNET_ACT_SOFTMAX)
         rc = run_softmax_rows((int64_t)g.B * g.Ho * g.Wo, g.K, y, y, s);
@@ -28,12 +29,14 @@ int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *
 
 int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
                size_t ws_bytes, cudaStream_t s) {
+    if (skinny_supported(g, 1, false)) return skinny_dgrad(g, dz, w, dx, accumulate, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) return tc_conv_dgrad(g, math, dz, w, dx, accumulate, ws, ws_bytes, s);
     return simt_conv_dgrad(g, dz, w, dx, accumulate, ws, ws_bytes, s);
 }
 
 int conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                size_t ws_bytes, cudaStream_t s) {
+    if (skinny_supported(g, 2, dbias != nullptr)) return skinny_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 2)) return tc_conv_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
     return simt_conv_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
 }
@@ -53,7 +56,7 @@ extern "C" {
 size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
     ConvGeom g;
     if (geom_checked(d, g, "fnet_conv2d_workspace_bytes") != FNET_OK) return 0;
-    size_t need = simt_conv_workspace(g);
+    size_t need = max_sz(simt_conv_workspace(g), skinny_workspace(g));
     if (d->math != FNET_MATH_FP32) need = max_sz(need, tc_conv_workspace(g, d->math));
     return need;
 }

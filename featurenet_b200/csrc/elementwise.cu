@@ -213,6 +213,36 @@ __global__ void __launch_bounds__(256) pad2d_bwd_kernel(int batch, int h, int w,
     }
 }
 
+// Concatenate(axis=1) of two [outer, rows_*, inner] tensors in one launch, and its backward (either gradient
+// may be skipped with a null pointer).
+__global__ void __launch_bounds__(256) concat_rows_fwd_kernel(int outer, int rows_a, int rows_b, int inner,
+                                                              const float *__restrict__ a, const float *__restrict__ b,
+                                                              float *__restrict__ y) {
+    const int64_t blk_a = (int64_t)rows_a * inner, blk_b = (int64_t)rows_b * inner, blk = blk_a + blk_b;
+    const int64_t total = (int64_t)outer * blk;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t o = i / blk, e = i - o * blk;
+        y[i] = e < blk_a ? __ldg(a + o * blk_a + e) : __ldg(b + o * blk_b + (e - blk_a));
+    }
+}
+
+__global__ void __launch_bounds__(256) concat_rows_bwd_kernel(int outer, int rows_a, int rows_b, int inner,
+                                                              const float *__restrict__ dy, float *__restrict__ da,
+                                                              float *__restrict__ db, int acc_a, int acc_b) {
+    const int64_t blk_a = (int64_t)rows_a * inner, blk_b = (int64_t)rows_b * inner, blk = blk_a + blk_b;
+    const int64_t total = (int64_t)outer * blk;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t o = i / blk, e = i - o * blk;
+        float g = __ldg(dy + i);
+        if (e < blk_a) {
+            if (da) { float *d = da + o * blk_a + e; *d = acc_a ? *d + g : g; }
+        } else if (db) {
+            float *d = db + o * blk_b + (e - blk_a);
+            *d = acc_b ? *d + g : g;
+        }
+    }
+}
+
 int run_softmax_rows(int64_t rows, int64_t cols, const float *x, float *y, cudaStream_t stream) {
     int64_t blocks = ceil_div<int64_t>(rows, 8);
     int64_t cap = (int64_t)kNumSMs * 8;
@@ -292,6 +322,25 @@ int fnet_copy_rows(int32_t batch, int32_t src_rows, int32_t src_row0, int32_t ds
     copy_rows_kernel<<<stream_grid((int64_t)batch * block_elems, 256), 256, 0, as_stream(stream)>>>(
         batch, src_rows, src_row0, dst_rows, dst_row0, block_elems, inner, src, dst, accumulate);
     return check_launch("fnet_copy_rows");
+}
+
+int fnet_concat_rows_fwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t inner, const float *a, const float *b,
+                         float *y, void *stream) {
+    FNET_REQUIRE(outer >= 0 && rows_a >= 0 && rows_b >= 0 && inner > 0 && a && b && y, "fnet_concat_rows_fwd: bad arguments");
+    int64_t total = (int64_t)outer * (rows_a + rows_b) * inner;
+    if (total == 0) return FNET_OK;
+    concat_rows_fwd_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(outer, rows_a, rows_b, inner, a, b, y);
+    return check_launch("fnet_concat_rows_fwd");
+}
+
+int fnet_concat_rows_bwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t inner, const float *dy, float *da,
+                         float *db, int acc_a, int acc_b, void *stream) {
+    FNET_REQUIRE(outer >= 0 && rows_a >= 0 && rows_b >= 0 && inner > 0 && dy, "fnet_concat_rows_bwd: bad arguments");
+    int64_t total = (int64_t)outer * (rows_a + rows_b) * inner;
+    if (total == 0 || (!da && !db)) return FNET_OK;
+    concat_rows_bwd_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(outer, rows_a, rows_b, inner, dy, da, db,
+                                                                                 acc_a, acc_b);
+    return check_launch("fnet_concat_rows_bwd");
 }
 
 int fnet_pad2d_fwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h, int32_t pad_w, const float *x,

@@ -303,9 +303,10 @@ static TcPlan tc_plan(long long M, long long N, long long Kg) {
     t.bn = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
     long long tiles = ceil_div<long long>(M, TC_BM) * ceil_div<long long>(N, t.bn);
     long long splits = 1;
-    if (tiles < kNumSMs && Kg >= 8 * TC_BK) {
-        splits = ceil_div<long long>(2 * kNumSMs, tiles);
-        long long most = Kg / (4 * TC_BK);
+    if (tiles < 4 * kNumSMs && Kg >= 16 * TC_BK) {
+        // a CTA walks its k-tiles serially (~1 us each): keep at least ~4 CTAs per SM busy
+        splits = ceil_div<long long>(4 * kNumSMs, tiles);
+        long long most = Kg / (8 * TC_BK);
         if (splits > most) splits = most;
         if (splits < 1) splits = 1;
     }

@@ -1,32 +1,43 @@
-// Softmax cross-entropy on probabilities + categorical accuracy.
-// Follows Keras' categorical_crossentropy(from_logits=False): renormalise, clip to
-// [1e-7, 1-1e-7], -sum t*log p; the optional gradient goes back through the clip (zero where
-// clipped), the renormalisation and the softmax that produced p, so it is dL/d(logits).
+// Softmax + categorical cross-entropy + categorical accuracy in one launch.
+// Follows Keras' categorical_crossentropy(from_logits=False) on the output of the softmax "out"
+// layer: renormalise p, clip to [1e-7, 1-1e-7], -sum t*log p; the optional gradient goes back
+// through the clip (zero where clipped), the renormalisation and the softmax, so it is
+// dL/d(logits).  With from_logits the kernel computes the softmax itself (writing the
+// probabilities, in place if asked), which saves the separate softmax launch of the head.
 //
 // One thread per sample (rows are 10..100 floats and a batch is <= a few thousand rows), one CTA
-// of up to 1024 threads: the batch loss is then reduced in a fixed order (shuffle tree, then warp
-// order) and added to the double accumulator by a single thread -- deterministic, no atomics race.
+// of up to 1024 threads: the batch loss is reduced in a fixed order (shuffle tree, then warp
+// order) and added to the double accumulator by a single thread -- deterministic.
 #include "common.cuh"
 
 namespace fnet {
 
-__global__ void __launch_bounds__(1024) softmax_cce_kernel(int batch, int classes, const float *__restrict__ probs,
+__global__ void __launch_bounds__(1024) softmax_cce_kernel(int batch, int classes, const float *input /* may alias probs_out */,
                                                            const float *__restrict__ targets, float scale,
-                                                           float *__restrict__ dlogits, double *__restrict__ loss_sum,
-                                                           long long *__restrict__ correct) {
+                                                           int from_logits, float *probs_out, float *__restrict__ dlogits,
+                                                           double *__restrict__ loss_sum, long long *__restrict__ correct) {
     __shared__ double warp_loss[32];
     __shared__ int warp_correct[32];
     const float kEps = 1e-7f;
     double my_loss = 0.0;
     int my_correct = 0;
     for (int row = threadIdx.x; row < batch; row += blockDim.x) {
-        const float *p = probs + (int64_t)row * classes;
+        const float *p = input + (int64_t)row * classes;
         const float *t = targets + (int64_t)row * classes;
+        if (from_logits) {
+            // keras softmax: exp(z - max) / sum, written where the loss (and the caller) will read it
+            float mx = -INFINITY, se = 0.f;
+            for (int c = 0; c < classes; ++c) mx = fmaxf(mx, p[c]);
+            for (int c = 0; c < classes; ++c) se += expf(p[c] - mx);
+            float *q = probs_out + (int64_t)row * classes;
+            for (int c = 0; c < classes; ++c) q[c] = expf(p[c] - mx) / se;     // in place is fine: one thread owns the row
+            p = q;
+        }
         // pass 1: sum(p), argmax p, argmax t (first index on ties: strict > while scanning upwards)
         float sum = 0.f, bp = -INFINITY, bt = -INFINITY;
         int ip = 0, it = 0;
         for (int c = 0; c < classes; ++c) {
-            float pv = __ldg(p + c), tv = __ldg(t + c);
+            float pv = p[c], tv = __ldg(t + c);
             sum += pv;
             if (pv > bp) { bp = pv; ip = c; }
             if (tv > bt) { bt = tv; it = c; }
@@ -34,7 +45,7 @@ __global__ void __launch_bounds__(1024) softmax_cce_kernel(int batch, int classe
         // pass 2: loss, and g = dL/dq masked by the clip; dot = sum g*q
         float loss = 0.f, dot = 0.f;
         for (int c = 0; c < classes; ++c) {
-            float q = __ldg(p + c) / sum;
+            float q = p[c] / sum;
             float cl = fminf(fmaxf(q, kEps), 1.f - kEps);
             float tv = __ldg(t + c);
             loss -= tv * logf(cl);
@@ -45,13 +56,13 @@ __global__ void __launch_bounds__(1024) softmax_cce_kernel(int batch, int classe
             // dL/dp_k = (g_k - dot)/sum ; softmax backward: dz_j = p_j*(dp_j - sum_k dp_k p_k)
             float dot2 = 0.f;
             for (int c = 0; c < classes; ++c) {
-                float pv = __ldg(p + c), q = pv / sum;
+                float pv = p[c], q = pv / sum;
                 float cl = fminf(fmaxf(q, kEps), 1.f - kEps);
                 float g = (q >= kEps && q <= 1.f - kEps) ? -__ldg(t + c) / cl : 0.f;
                 dot2 = fmaf((g - dot) / sum, pv, dot2);
             }
             for (int c = 0; c < classes; ++c) {
-                float pv = __ldg(p + c), q = pv / sum;
+                float pv = p[c], q = pv / sum;
                 float cl = fminf(fmaxf(q, kEps), 1.f - kEps);
                 float g = (q >= kEps && q <= 1.f - kEps) ? -__ldg(t + c) / cl : 0.f;
                 dlogits[(int64_t)row * classes + c] = scale * pv * ((g - dot) / sum - dot2);
@@ -82,12 +93,15 @@ __global__ void __launch_bounds__(1024) softmax_cce_kernel(int batch, int classe
 
 using namespace fnet;
 
-extern "C" int fnet_softmax_cce(int32_t batch, int32_t classes, const float *probs, const float *targets, float scale,
-                                float *dlogits, double *loss_sum, int64_t *correct, void *stream) {
-    FNET_REQUIRE(batch >= 0 && classes > 0 && probs && targets, "fnet_softmax_cce: bad arguments");
+extern "C" int fnet_softmax_cce(int32_t batch, int32_t classes, const float *input, const float *targets, float scale,
+                                int from_logits, float *probs_out, float *dlogits, double *loss_sum, int64_t *correct,
+                                void *stream) {
+    FNET_REQUIRE(batch >= 0 && classes > 0 && input && targets, "fnet_softmax_cce: bad arguments");
+    FNET_REQUIRE(!from_logits || probs_out != nullptr, "fnet_softmax_cce: from_logits needs a place for the probabilities");
+    FNET_REQUIRE(dlogits == nullptr || dlogits != probs_out, "fnet_softmax_cce: dlogits must not alias the probabilities");
     if (batch == 0) return FNET_OK;
     int threads = batch >= 1024 ? 1024 : ((batch + 31) / 32) * 32;
-    softmax_cce_kernel<<<1, threads, 0, as_stream(stream)>>>(batch, classes, probs, targets, scale, dlogits, loss_sum,
-                                                             reinterpret_cast<long long *>(correct));
+    softmax_cce_kernel<<<1, threads, 0, as_stream(stream)>>>(batch, classes, input, targets, scale, from_logits, probs_out,
+                                                             dlogits, loss_sum, reinterpret_cast<long long *>(correct));
     return check_launch("fnet_softmax_cce");
 }

@@ -1,0 +1,373 @@
+// Direct kernels for the two GEMM shapes that every FeatureNet candidate has and that no tile fits:
+//
+//  * the classifier head: Dense(flatten -> n_classes) with N <= 16 columns and K = 6 144 ... 524 288
+//    (model/keras_model.py:121-124).  Forward = one CTA per sample, threads stride over K with N
+//    accumulators each; filter gradient = one thread per weight row k (coalesced over k, dz staged in
+//    shared memory); data gradient = one thread per dx element.  One launch each, no workspace, a fixed
+//    reduction order.
+//  * convolutions with few channels on both sides (out <= 16, taps*in <= 256), the only kind the
+//    main_1block_nas vocabulary produces (6 features) and the first layers of everything else:
+//    one thread per pixel with the whole filter in shared memory -- no tiles, no barriers in the main
+//    loop, fully coalesced stores.  The filter gradient of the smallest ones ((taps*in+1)*out <= 64)
+//    keeps every partial sum in registers and reduces deterministically through the workspace.
+//
+// All of them are memory- or latency-bound by construction (<= 32 flops per byte moved).
+#include "igemm_problems.cuh"
+
+namespace fnet {
+
+constexpr int kSkinnyN = 16;
+
+// ------------------------------------------------------------------ dense, N <= 16
+template <int NMAX>
+__global__ void __launch_bounds__(256) dense_skinny_fwd_kernel(int K, int N, int act, const float *__restrict__ x,
+                                                               const float *__restrict__ w, const float *__restrict__ bias,
+                                                               float *__restrict__ y) {
+    __shared__ float red[8][NMAX];
+    const int m = blockIdx.x;
+    const float *xr = x + (long long)m * K;
+    float acc[NMAX];
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n) acc[n] = 0.f;
+    for (int k = threadIdx.x; k < K; k += 256) {
+        float xv = __ldg(xr + k);
+        const float *wr = w + (long long)k * N;
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n)
+            if (n < N) acc[n] = fmaf(xv, __ldg(wr + n), acc[n]);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n) {
+        float v = warp_sum(acc[n]);
+        if (lane == 0) red[warp][n] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < N) {
+        float v = 0.f;
+#pragma unroll
+        for (int wv = 0; wv < 8; ++wv) v += red[wv][threadIdx.x];
+        if (bias) v += __ldg(bias + threadIdx.x);
+        y[(long long)m * N + threadIdx.x] = act_apply(v, act);
+    }
+}
+
+// dW[k][n] = sum_m x[m][k] * dz[m][n];  block 0 also writes dbias[n] = sum_m dz[m][n]
+template <int NMAX>
+__global__ void __launch_bounds__(256) dense_skinny_wgrad_kernel(int M, int K, int N, const float *__restrict__ x,
+                                                                 const float *__restrict__ dz, float *__restrict__ dw,
+                                                                 float *__restrict__ dbias) {
+    extern __shared__ float dz_s[];                 // a chunk of dz rows, [rows][N]
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    float acc[NMAX];
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n) acc[n] = 0.f;
+    float bsum = 0.f;                               // thread n < N of block 0 sums column n
+    constexpr int CHUNK = 256;
+    for (int m0 = 0; m0 < M; m0 += CHUNK) {
+        int rows = min(CHUNK, M - m0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < rows * N; i += 256) dz_s[i] = __ldg(dz + (long long)m0 * N + i);
+        __syncthreads();
+        if (k < K) {
+            for (int r = 0; r < rows; ++r) {
+                float xv = __ldg(x + (long long)(m0 + r) * K + k);
+#pragma unroll
+                for (int n = 0; n < NMAX; ++n)
+                    if (n < N) acc[n] = fmaf(xv, dz_s[r * N + n], acc[n]);
+            }
+        }
+        if (dbias && blockIdx.x == 0 && threadIdx.x < N)
+            for (int r = 0; r < rows; ++r) bsum += dz_s[r * N + threadIdx.x];
+    }
+    if (k < K) {
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n)
+            if (n < N) dw[(long long)k * N + n] = acc[n];
+    }
+    if (dbias && blockIdx.x == 0 && threadIdx.x < N) dbias[threadIdx.x] = bsum;
+}
+
+// dx[m][k] (+)= sum_n dz[m][n] * w[k][n]
+template <int NMAX>
+__global__ void __launch_bounds__(256) dense_skinny_dgrad_kernel(int M, int K, int N, const float *__restrict__ dz,
+                                                                 const float *__restrict__ w, float *__restrict__ dx,
+                                                                 int accumulate) {
+    const int m = blockIdx.y;
+    float g[NMAX];
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n) g[n] = n < N ? __ldg(dz + (long long)m * N + n) : 0.f;
+    for (int k = blockIdx.x * 256 + threadIdx.x; k < K; k += gridDim.x * 256) {
+        const float *wr = w + (long long)k * N;
+        float v = 0.f;
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n)
+            if (n < N) v = fmaf(g[n], __ldg(wr + n), v);
+        long long at = (long long)m * K + k;
+        dx[at] = accumulate ? dx[at] + v : v;
+    }
+}
+
+static bool is_dense_geom(const ConvGeom &g) { return g.H == 1 && g.W == 1 && g.kh == 1 && g.kw == 1 && g.Ho == 1 && g.Wo == 1; }
+
+// ------------------------------------------------------------------ small-channel convolutions
+// forward: one thread per output pixel, all out channels (<= NMAX) in registers
+template <int NMAX>
+__global__ void __launch_bounds__(256) conv_small_fwd_kernel(ConvGeom g, int act, const float *__restrict__ x,
+                                                             const float *__restrict__ w, const float *__restrict__ bias,
+                                                             float *__restrict__ y) {
+    extern __shared__ float w_s[];                  // [taps*C][K] as in memory (HWIO), then the bias
+    const int KG = g.kh * g.kw * g.C, N = g.K;
+    for (int i = threadIdx.x; i < KG * N; i += 256) w_s[i] = __ldg(w + i);
+    for (int i = threadIdx.x; i < N; i += 256) w_s[KG * N + i] = bias ? __ldg(bias + i) : 0.f;
+    __syncthreads();
+    const long long M = (long long)g.B * g.Ho * g.Wo;
+    for (long long m = (long long)blockIdx.x * 256 + threadIdx.x; m < M; m += (long long)gridDim.x * 256) {
+        int wo = (int)(m % g.Wo);
+        long long t = m / g.Wo;
+        int ho = (int)(t % g.Ho);
+        long long b = t / g.Ho;
+        const float *img = x + b * g.H * g.W * g.C;
+        float acc[NMAX];
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) acc[n] = n < N ? w_s[KG * N + n] : 0.f;
+        for (int r = 0; r < g.kh; ++r) {
+            int h = ho * g.sh - g.pt + r * g.dh;
+            if ((unsigned)h >= (unsigned)g.H) continue;
+            for (int s = 0; s < g.kw; ++s) {
+                int ww = wo * g.sw - g.pl + s * g.dw;
+                if ((unsigned)ww >= (unsigned)g.W) continue;
+                const float *px = img + ((long long)h * g.W + ww) * g.C;
+                const float *wt = w_s + (r * g.kw + s) * g.C * N;
+                for (int c = 0; c < g.C; ++c) {
+                    float xv = __ldg(px + c);
+#pragma unroll
+                    for (int n = 0; n < NMAX; ++n)
+                        if (n < N) acc[n] = fmaf(xv, wt[c * N + n], acc[n]);
+                }
+            }
+        }
+        float *out = y + m * N;
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n)
+            if (n < N) out[n] = act_apply(acc[n], act);
+    }
+}
+
+// data gradient: one thread per input pixel, all in channels (<= NMAX) in registers
+template <int NMAX>
+__global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const float *__restrict__ dz,
+                                                               const float *__restrict__ w, float *__restrict__ dx,
+                                                               int accumulate) {
+    extern __shared__ float w_s[];                  // [taps][C][K]
+    const int total_w = g.kh * g.kw * g.C * g.K, C = g.C, K = g.K;
+    for (int i = threadIdx.x; i < total_w; i += 256) w_s[i] = __ldg(w + i);
+    __syncthreads();
+    const long long M = (long long)g.B * g.H * g.W;
+    for (long long m = (long long)blockIdx.x * 256 + threadIdx.x; m < M; m += (long long)gridDim.x * 256) {
+        int wi = (int)(m % g.W);
+        long long t = m / g.W;
+        int hi = (int)(t % g.H);
+        long long b = t / g.H;
+        const float *img = dz + b * g.Ho * g.Wo * K;
+        float acc[NMAX];
+#pragma unroll
+        for (int c = 0; c < NMAX; ++c) acc[c] = 0.f;
+        for (int r = 0; r < g.kh; ++r) {
+            int hh = hi + g.pt - r * g.dh;
+            if (hh < 0) continue;
+            int ho = hh / g.sh;
+            if (ho * g.sh != hh || ho >= g.Ho) continue;
+            for (int s = 0; s < g.kw; ++s) {
+                int ww = wi + g.pl - s * g.dw;
+                if (ww < 0) continue;
+                int wo = ww / g.sw;
+                if (wo * g.sw != ww || wo >= g.Wo) continue;
+                const float *pz = img + ((long long)ho * g.Wo + wo) * K;
+                const float *wt = w_s + (r * g.kw + s) * C * K;
+                for (int ko = 0; ko < K; ++ko) {
+                    float gv = __ldg(pz + ko);
+#pragma unroll
+                    for (int c = 0; c < NMAX; ++c)
+                        if (c < C) acc[c] = fmaf(gv, wt[c * K + ko], acc[c]);
+                }
+            }
+        }
+        float *out = dx + m * C;
+#pragma unroll
+        for (int c = 0; c < NMAX; ++c)
+            if (c < C) out[c] = accumulate ? out[c] + acc[c] : acc[c];
+    }
+}
+
+// filter gradient of the smallest convolutions: every (tap, c, k) partial sum (and the bias sums) lives in
+// registers; partial[block][row][k] goes to the workspace and is reduced in a fixed order afterwards
+constexpr int kWgradRegs = 64;
+constexpr int kWgradBlocks = 2 * kNumSMs;
+
+template <int KT>     // KT = number of output channels (compile time, so that every partial sum has a fixed register)
+__global__ void __launch_bounds__(256) conv_small_wgrad_kernel(ConvGeom g, int rows, const float *__restrict__ x,
+                                                               const float *__restrict__ dz, float *__restrict__ partial) {
+    constexpr int ROWS_MAX = kWgradRegs / KT;
+    __shared__ float red[8][kWgradRegs];
+    const int C = g.C, taps_c = g.kh * g.kw * C;
+    const int total = rows * KT;                    // rows = taps*C (+1 bias row) <= ROWS_MAX
+    float acc[ROWS_MAX][KT];
+#pragma unroll
+    for (int i = 0; i < ROWS_MAX; ++i)
+#pragma unroll
+        for (int k = 0; k < KT; ++k) acc[i][k] = 0.f;
+    const long long M = (long long)g.B * g.Ho * g.Wo;
+    for (long long m = (long long)blockIdx.x * 256 + threadIdx.x; m < M; m += (long long)gridDim.x * 256) {
+        int wo = (int)(m % g.Wo);
+        long long t = m / g.Wo;
+        int ho = (int)(t % g.Ho);
+        long long b = t / g.Ho;
+        const float *img = x + b * g.H * g.W * C;
+        float gz[KT];
+#pragma unroll
+        for (int k = 0; k < KT; ++k) gz[k] = __ldg(dz + m * KT + k);
+        int r = 0, s = 0, c = 0;                    // rows are walked in (tap, c) order
+#pragma unroll
+        for (int row = 0; row < ROWS_MAX; ++row) {
+            if (row < rows) {
+                float xv = 1.f;                     // the bias row
+                if (row < taps_c) {
+                    int h = ho * g.sh - g.pt + r * g.dh, ww = wo * g.sw - g.pl + s * g.dw;
+                    xv = ((unsigned)h < (unsigned)g.H && (unsigned)ww < (unsigned)g.W)
+                             ? __ldg(img + ((long long)h * g.W + ww) * C + c) : 0.f;
+                    if (++c == C) { c = 0; if (++s == g.kw) { s = 0; ++r; } }
+                }
+#pragma unroll
+                for (int k = 0; k < KT; ++k) acc[row][k] = fmaf(xv, gz[k], acc[row][k]);
+            }
+        }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < ROWS_MAX; ++i)
+#pragma unroll
+        for (int k = 0; k < KT; ++k) {
+            float v = warp_sum(acc[i][k]);
+            if (lane == 0) red[warp][i * KT + k] = v;
+        }
+    __syncthreads();
+    if (threadIdx.x < total) {
+        float v = 0.f;
+#pragma unroll
+        for (int wv = 0; wv < 8; ++wv) v += red[wv][threadIdx.x];
+        partial[(long long)blockIdx.x * total + threadIdx.x] = v;
+    }
+}
+
+__global__ void __launch_bounds__(256) conv_small_wgrad_reduce_kernel(int blocks, int taps_c, int K, int total,
+                                                                      const float *__restrict__ partial,
+                                                                      float *__restrict__ dw, float *__restrict__ dbias) {
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = warp; i < total; i += 8) {
+        float s = 0.f;
+        for (int z = lane; z < blocks; z += 32) s += partial[(long long)z * total + i];
+        s = warp_sum(s);
+        if (lane == 0) {
+            if (i < taps_c * K) dw[i] = s;
+            else if (dbias) dbias[i - taps_c * K] = s;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ dispatch (called from conv_api.cu)
+static bool small_fwd_ok(const ConvGeom &g) {
+    return !is_dense_geom(g) && g.K <= kSkinnyN && (long long)g.kh * g.kw * g.C <= 256 &&
+           ((long long)g.kh * g.kw * g.C + 1) * g.K * 4 <= 40 * 1024;
+}
+static bool small_dgrad_ok(const ConvGeom &g) {
+    return !is_dense_geom(g) && g.C <= kSkinnyN && (long long)g.kh * g.kw * g.K <= 256 &&
+           (long long)g.kh * g.kw * g.C * g.K * 4 <= 40 * 1024;
+}
+static bool small_wgrad_ok(const ConvGeom &g, bool with_bias) {
+    return !is_dense_geom(g) && g.K <= 8 && ((long long)g.kh * g.kw * g.C + (with_bias ? 1 : 0)) * g.K <= kWgradRegs;
+}
+
+bool skinny_supported(const ConvGeom &g, int product, bool with_bias) {
+    // head-like only: a long reduction axis and a modest number of rows (one CTA per row / one thread per k)
+    if (is_dense_geom(g)) return g.K <= kSkinnyN && g.C >= 512 && g.B >= 1 && g.B <= 8192;
+    if (product == 0) return small_fwd_ok(g);
+    if (product == 1) return small_dgrad_ok(g);
+    return small_wgrad_ok(g, with_bias);
+}
+
+size_t skinny_workspace(const ConvGeom &g) {
+    if (is_dense_geom(g)) return 0;
+    if (small_wgrad_ok(g, true)) return (size_t)kWgradBlocks * kWgradRegs * sizeof(float);
+    return 0;
+}
+
+static int pixel_grid(long long pixels) {
+    long long blocks = ceil_div<long long>(pixels, 256);
+    long long cap = (long long)kNumSMs * 8;
+    return (int)(blocks > cap ? cap : (blocks < 1 ? 1 : blocks));
+}
+
+int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t s) {
+    if (act == FNET_ACT_SOFTMAX) act = FNET_ACT_NONE;      // the caller runs the softmax pass
+    if (is_dense_geom(g)) {
+        dense_skinny_fwd_kernel<kSkinnyN><<<g.B, 256, 0, s>>>(g.C, g.K, act, x, w, bias, y);
+        return check_launch("dense_fwd[skinny]");
+    }
+    size_t smem = ((size_t)g.kh * g.kw * g.C + 1) * g.K * sizeof(float);
+    long long M = (long long)g.B * g.Ho * g.Wo;
+    if (g.K <= 8) conv_small_fwd_kernel<8><<<pixel_grid(M), 256, smem, s>>>(g, act, x, w, bias, y);
+    else conv_small_fwd_kernel<16><<<pixel_grid(M), 256, smem, s>>>(g, act, x, w, bias, y);
+    return check_launch("conv2d_fwd[small]");
+}
+
+int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t s) {
+    if (is_dense_geom(g)) {
+        int bx = (int)ceil_div<long long>(g.C, 256);
+        if (bx > 64) bx = 64;
+        dense_skinny_dgrad_kernel<kSkinnyN><<<dim3(bx, g.B), 256, 0, s>>>(g.B, g.C, g.K, dz, w, dx, accumulate);
+        return check_launch("dense_bwd_data[skinny]");
+    }
+    size_t smem = (size_t)g.kh * g.kw * g.C * g.K * sizeof(float);
+    long long M = (long long)g.B * g.H * g.W;
+    if (g.C <= 8) conv_small_dgrad_kernel<8><<<pixel_grid(M), 256, smem, s>>>(g, dz, w, dx, accumulate);
+    else conv_small_dgrad_kernel<16><<<pixel_grid(M), 256, smem, s>>>(g, dz, w, dx, accumulate);
+    return check_launch("conv2d_bwd_data[small]");
+}
+
+int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
+                 cudaStream_t s) {
+    if (is_dense_geom(g)) {
+        size_t smem = (size_t)256 * g.K * sizeof(float);
+        dense_skinny_wgrad_kernel<kSkinnyN><<<(unsigned)ceil_div<long long>(g.C, 256), 256, smem, s>>>(g.B, g.C, g.K, x, dz,
+                                                                                                     dw, dbias);
+        return check_launch("dense_bwd_filter[skinny]");
+    }
+    int taps_c = g.kh * g.kw * g.C, rows = taps_c + (dbias ? 1 : 0), total = rows * g.K;
+    long long M = (long long)g.B * g.Ho * g.Wo;
+    int blocks = (int)ceil_div<long long>(M, 256);
+    if (blocks > kWgradBlocks) blocks = kWgradBlocks;
+    if (blocks < 1) blocks = 1;
+    size_t need = (size_t)blocks * total * sizeof(float);
+    if (!ws || ws_bytes < need) {
+        set_error("conv2d_bwd_filter[small]: workspace of %zu bytes needed, %zu given", need, ws_bytes);
+        return FNET_ERR_WORKSPACE;
+    }
+    float *partial = reinterpret_cast<float *>(ws);
+    switch (g.K) {
+        case 1: conv_small_wgrad_kernel<1><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+        case 2: conv_small_wgrad_kernel<2><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+        case 3: conv_small_wgrad_kernel<3><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+        case 4: conv_small_wgrad_kernel<4><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+        case 5: conv_small_wgrad_kernel<5><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+        case 6: conv_small_wgrad_kernel<6><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+        case 7: conv_small_wgrad_kernel<7><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+        default: conv_small_wgrad_kernel<8><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+    }
+    int rc = check_launch("conv2d_bwd_filter[small]");
+    if (rc) return rc;
+    conv_small_wgrad_reduce_kernel<<<1, 256, 0, s>>>(blocks, taps_c, g.K, total, partial, dw, dbias);
+    return check_launch("conv2d_bwd_filter[small]");
+}
+
+}  // namespace fnet

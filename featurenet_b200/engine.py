@@ -307,10 +307,13 @@ class Engine(object):
         return batch * _prod(shp[:axis]), shp[axis], _prod(shp[axis + 1:])
 
     # ------------------------------------------------------------------ programs
-    def _forward_program(self, batch, training):
+    def _forward_program(self, batch, training, head_logits=True):
+        """head_logits: the "out" layer stops at its logits (the loss kernel does the softmax and writes the
+        probabilities in place); False makes the layer apply its own softmax (predict())."""
         L, sp, ws, wsb = self.lib, self.sp, C.c_void_p(self.ws.data_ptr()), self.ws_bytes
         ops = []
         add = lambda label, fn, *args: ops.append((label, fn, args))
+        last = len(self.nodes) - 1
         for i, node in enumerate(self.nodes):
             kind, cfg = node.kind, node.cfg
             if kind in ("input", "flatten") or (kind == "dropout" and not training):
@@ -331,7 +334,8 @@ class Engine(object):
                 add("conv2d_fwd", L.fnet_conv2d_fwd, pw, mid, self._wp(i, 1), self._wp(i, 2), y, ws, wsb, sp)
             elif kind == "dense":
                 m, k, n = self._dense_mkn(i, batch)
-                add("dense_fwd", L.fnet_dense_fwd, m, k, n, fl.ACT[cfg["activation"]], self.math, x, self._wp(i, 0),
+                act = 0 if (i == last and head_logits) else fl.ACT[cfg["activation"]]
+                add("dense_fwd", L.fnet_dense_fwd, m, k, n, act, self.math, x, self._wp(i, 0),
                     self._wp(i, 1), y, ws, wsb, sp)
             elif kind in ("maxpool", "avgpool"):
                 arg = C.c_void_p(self.aux[i].data_ptr()) if kind == "maxpool" and training else None
@@ -363,9 +367,7 @@ class Engine(object):
                 sa, sb = self.shape[self.src[i][0]], self.shape[self.src[i][1]]
                 outer, inner = batch * _prod(sa[:axis]), _prod(sa[axis + 1:])
                 ra, rb = sa[axis], sb[axis]
-                add("concat_fwd", L.fnet_copy_rows, outer, ra, 0, ra + rb, 0, ra, inner, x, y, 0, sp)
-                add("concat_fwd", L.fnet_copy_rows, outer, rb, 0, ra + rb, ra, rb, inner,
-                    self._a(self.src[i][1], training), y, 0, sp)
+                add("concat_fwd", L.fnet_concat_rows_fwd, outer, ra, rb, inner, x, self._a(self.src[i][1], training), y, sp)
             elif kind == "pad":
                 h, w, c = self.shape[self.src[i][0]]
                 add("pad2d_fwd", L.fnet_pad2d_fwd, batch, h, w, c, cfg["pad"][0], cfg["pad"][1], x, y, sp)
@@ -472,10 +474,15 @@ class Engine(object):
                 sa, sb = self.shape[a], self.shape[b]
                 outer, inner = batch * _prod(sa[:axis]), _prod(sa[axis + 1:])
                 ra, rb = sa[axis], sb[axis]
-                if need[a]:
-                    add("concat_bwd", L.fnet_copy_rows, outer, ra + rb, 0, ra, 0, ra, inner, dy, self._g(a), acc_flag(a), sp)
-                if need[b]:
-                    add("concat_bwd", L.fnet_copy_rows, outer, ra + rb, ra, rb, 0, rb, inner, dy, self._g(b), acc_flag(b), sp)
+                if self._resolve(a, True) == self._resolve(b, True):
+                    # the same tensor on both sides: two ordered row copies into one gradient buffer
+                    if need[a]:
+                        add("copy_rows", L.fnet_copy_rows, outer, ra + rb, 0, ra, 0, ra, inner, dy, self._g(a), acc_flag(a), sp)
+                        add("copy_rows", L.fnet_copy_rows, outer, ra + rb, ra, rb, 0, rb, inner, dy, self._g(b), acc_flag(b), sp)
+                elif need[a] or need[b]:
+                    ga, fa = (self._g(a), acc_flag(a)) if need[a] else (None, 0)
+                    gb, fb = (self._g(b), acc_flag(b)) if need[b] else (None, 0)
+                    add("concat_bwd", L.fnet_concat_rows_bwd, outer, ra, rb, inner, dy, ga, gb, fa, fb, sp)
             elif kind == "pad":
                 h, w, c = self.shape[s0]
                 add("pad2d_bwd", L.fnet_pad2d_bwd, batch, h, w, c, cfg["pad"][0], cfg["pad"][1], dy, self._g(s0), acc_flag(s0), sp)
@@ -490,18 +497,19 @@ class Engine(object):
         dz = self._g(last) if with_grad else None
         return ("softmax_cce", L.fnet_softmax_cce,
                 (batch, self.n_out, self._a(last, with_grad), C.c_void_p(self.yb.data_ptr()),
-                 1.0 / (scale_batch or batch), dz,
+                 1.0 / (scale_batch or batch), 1, self._a(last, with_grad), dz,       # from logits, softmax in place
                  C.c_void_p(self.loss_sum.data_ptr()), C.c_void_p(self.correct.data_ptr()), self.sp))
 
-    def _optimizer_op(self):
+    def _optimizer_op(self, advance=-1):
+        """advance >= 0: the optimizer launch also closes the step (iteration += 1, cursor += advance)."""
         opt, L = self.net.optimizer, self.lib
         st = C.c_void_p(self.state.data_ptr())
         args4 = [C.c_void_p(t.data_ptr()) for t in (self.params, self.grads, self.adam_m, self.adam_v)]
         if opt.kind == "adam":
             return ("adam_step", L.fnet_adam_step, (self.n_params, args4[0], args4[1], args4[2], args4[3], st,
-                                                    opt.beta_1, opt.beta_2, opt.epsilon, self.sp))
+                                                    opt.beta_1, opt.beta_2, opt.epsilon, advance, self.sp))
         return ("sgd_step", L.fnet_sgd_step, (self.n_params, args4[0], args4[1], args4[2], st, opt.momentum,
-                                              int(opt.nesterov), self.sp))
+                                              int(opt.nesterov), advance, self.sp))
 
     def _build_program(self, kind, batch):
         """kind: 'train' / 'eval' read the resident dataset through the permutation; '*_fed' expect xb/yb filled."""
@@ -510,11 +518,20 @@ class Engine(object):
         state = self.state if training else self.state_eval
         st = C.c_void_p(state.data_ptr())
         ops = []
+        b1 = b2 = 0.0
         if training:
             opt = self.net.optimizer
             b1, b2 = (opt.beta_1, opt.beta_2) if opt.kind == "adam" else (0.9, 0.999)
+        fused_gather = kind in ("train", "eval")         # inputs + targets (+ lr_t) in one launch
+        if training and not fused_gather:
             ops.append(("step_begin", L.fnet_step_begin, (st, b1, b2, sp)))
-        if not kind.endswith("_fed"):
+        if fused_gather:
+            xdev, ydev, perm = self.data[kind]
+            ops.append(("gather_batch", L.fnet_gather_batch,
+                        (batch, _prod(self.shape[0]), self.n_out, C.c_void_p(perm.data_ptr()), st,
+                         C.c_void_p(xdev.data_ptr()), C.c_void_p(ydev.data_ptr()), C.c_void_p(self.act[0].data_ptr()),
+                         C.c_void_p(self.yb.data_ptr()), 1 if training else 0, b1, b2, sp)))
+        elif not kind.endswith("_fed"):
             xdev, ydev, perm = self.data[kind.split("_")[0]]
             row = _prod(self.shape[0])
             if kind == "train_aug":
@@ -533,8 +550,9 @@ class Engine(object):
         ops.append(self._loss_op(batch, training))
         if training:
             ops += self._backward_program(batch)
-            ops.append(self._optimizer_op())
-        ops.append(("step_end", L.fnet_step_end, (st, batch, sp)))
+            ops.append(self._optimizer_op(advance=batch))       # the update also closes the step
+        else:
+            ops.append(("step_end", L.fnet_step_end, (st, batch, sp)))
         return ops
 
     def _run_ops(self, ops):
@@ -582,8 +600,10 @@ class Engine(object):
             b = 4 * 3 * args[0]
         elif label == "add_bwd":
             b = 4 * 2 * args[0]
-        elif label.startswith("concat"):
+        elif label == "copy_rows":
             b = 4 * 2 * args[0] * args[5] * args[6]
+        elif label.startswith("concat"):
+            b = 4 * 2 * args[0] * (args[1] + args[2]) * args[3]
         elif label.startswith("pad2d"):
             b = 4 * 2 * args[0] * args[1] * args[2] * args[3]
         elif label == "softmax_cce":
@@ -594,6 +614,8 @@ class Engine(object):
             b = 16 * args[0]
         elif label == "gather_rows":
             b = 4 * 2 * args[0] * args[1]
+        elif label == "gather_batch":
+            b = 4 * 2 * args[0] * (args[1] + args[2])
         elif label == "gather_shift_flip":
             b = 4 * 2 * args[0] * args[1] * args[2] * args[3]
         return f, b
@@ -747,7 +769,7 @@ class Engine(object):
             b = min(eb, n - lo)
             with torch.cuda.stream(self.stream):
                 self.act[0][:b].copy_(torch.from_numpy(np.ascontiguousarray(x[lo: lo + b])))
-                self._run_ops(self._forward_program(b, False))
+                self._run_ops(self._forward_program(b, False, head_logits=False))
                 self.stream.synchronize()
                 out[lo: lo + b] = self.act[self._resolve(last, False)][:b].cpu().numpy()
         return out

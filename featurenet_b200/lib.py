@@ -74,11 +74,14 @@ SIGNATURES = {
     "fnet_pad2d_fwd": (C.c_int, [_I32, _I32, _I32, _I32, _I32, _I32, _P, _P, _P]),
     "fnet_pad2d_bwd": (C.c_int, [_I32, _I32, _I32, _I32, _I32, _I32, _P, _P, C.c_int, _P]),
     "fnet_fill": (C.c_int, [_I64, _F, _P, _P]),
-    "fnet_softmax_cce": (C.c_int, [_I32, _I32, _P, _P, _F, _P, _P, _P, _P]),
+    "fnet_softmax_cce": (C.c_int, [_I32, _I32, _P, _P, _F, C.c_int, _P, _P, _P, _P, _P]),
     "fnet_step_begin": (C.c_int, [_P, _F, _F, _P]),
     "fnet_step_end": (C.c_int, [_P, _I32, _P]),
-    "fnet_adam_step": (C.c_int, [_I64, _P, _P, _P, _P, _P, _F, _F, _F, _P]),
-    "fnet_sgd_step": (C.c_int, [_I64, _P, _P, _P, _P, _F, C.c_int, _P]),
+    "fnet_adam_step": (C.c_int, [_I64, _P, _P, _P, _P, _P, _F, _F, _F, _I32, _P]),
+    "fnet_sgd_step": (C.c_int, [_I64, _P, _P, _P, _P, _F, C.c_int, _I32, _P]),
+    "fnet_gather_batch": (C.c_int, [_I32, _I64, _I64, _P, _P, _P, _P, _P, _P, C.c_int, _F, _F, _P]),
+    "fnet_concat_rows_fwd": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _P]),
+    "fnet_concat_rows_bwd": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, C.c_int, C.c_int, _P]),
     "fnet_gather_rows": (C.c_int, [_I32, _I64, _P, _P, _P, _P, _P]),
     "fnet_gather_shift_flip": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "fnet_u8_to_f32": (C.c_int, [_I64, _P, _F, _P, _P]),

@@ -92,8 +92,9 @@ int fnet_dense_bwd_filter(int64_t m, int64_t k, int64_t n, int math, const float
  * a worker sharing the device with a framework whose pool owns the memory, or a loop that must
  * not pay the device-wide synchronisation of cudaMalloc/cudaFree.
  *
- * Same arithmetic as fnet_dense_fwd with FNET_MATH_FP32 (same kernels, same reduction order,
- * so the same bits).  The partial sums of the split reduction go to an array of
+ * Same arithmetic as fnet_dense_fwd with FNET_MATH_FP32: fp32 FFMA tiles with a fixed reduction
+ * order (fnet_dense_fwd may choose another fp32 kernel for a shape, so the two agree to rounding,
+ * not to the bit).  The partial sums of the split reduction go to an array of
  * FNET_STATIC_SCRATCH_BYTES built into the library; every GPU that loads libfnet.so holds that
  * array until the process exits.  Shapes whose reduction needs more than that are rejected
  * with FNET_ERR_WORKSPACE and a message (use fnet_dense_fwd and a workspace of
@@ -190,6 +191,12 @@ int fnet_mul_bwd(int64_t n, const float *dy, const float *other, float *dx, int 
 int fnet_accumulate(int64_t n, const float *src, float *dst, int accumulate, void *stream);
 int fnet_copy_rows(int32_t batch, int32_t src_rows, int32_t src_row0, int32_t dst_rows, int32_t dst_row0,
                    int32_t rows, int32_t inner, const float *src, float *dst, int accumulate, void *stream);
+/* Concatenate(axis=1) of a[outer, rows_a, inner] and b[outer, rows_b, inner] in one launch, and its backward
+ * (da / db may be NULL when that input needs no gradient; a and b must be distinct buffers) */
+int fnet_concat_rows_fwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t inner, const float *a, const float *b,
+                         float *y, void *stream);
+int fnet_concat_rows_bwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t inner, const float *dy, float *da,
+                         float *db, int acc_a, int acc_b, void *stream);
 int fnet_pad2d_fwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h, int32_t pad_w, const float *x,
                    float *y, void *stream);
 int fnet_pad2d_bwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h, int32_t pad_w, const float *dy,
@@ -204,8 +211,12 @@ int fnet_fill(int64_t n, float value, float *dst, void *stream);
  * Adds the batch loss to *loss_sum (double) and the number of correct rows to *correct.
  * If dlogits != NULL also writes scale * dL/d(logits) through softmax, renormalisation and clip.
  * ------------------------------------------------------------------------------------------ */
-int fnet_softmax_cce(int32_t batch, int32_t classes, const float *probs, const float *targets, float scale,
-                     float *dlogits, double *loss_sum, int64_t *correct, void *stream);
+int fnet_softmax_cce(int32_t batch, int32_t classes, const float *input, const float *targets, float scale,
+                     int from_logits, float *probs_out, float *dlogits, double *loss_sum, int64_t *correct,
+                     void *stream);
+/* from_logits = 0: `input` holds the probabilities of the "out" layer, probs_out is ignored.
+ * from_logits = 1: `input` holds the logits; the kernel computes the softmax itself and writes the
+ * probabilities to probs_out (which may be `input`: in place), saving the head's softmax launch. */
 
 /* ------------------------------------------------------------------------------------------
  * Optimizer and loop state.  Replaces keras.optimizers.Adam(lr=1e-3) of
@@ -216,10 +227,16 @@ int fnet_softmax_cce(int32_t batch, int32_t classes, const float *probs, const f
  * ------------------------------------------------------------------------------------------ */
 int fnet_step_begin(int32_t *state, float beta1, float beta2, void *stream);
 int fnet_step_end(int32_t *state, int32_t batch, void *stream);
-int fnet_adam_step(int64_t n, float *params, const float *grads, float *m, float *v, const int32_t *state,
-                   float beta1, float beta2, float eps, void *stream);
-int fnet_sgd_step(int64_t n, float *params, const float *grads, float *velocity, const int32_t *state,
-                  float momentum, int nesterov, void *stream);
+/* advance >= 0: the optimizer launch also does fnet_step_end(state, advance); advance < 0: state is only read */
+int fnet_adam_step(int64_t n, float *params, const float *grads, float *m, float *v, int32_t *state, float beta1,
+                   float beta2, float eps, int32_t advance, void *stream);
+int fnet_sgd_step(int64_t n, float *params, const float *grads, float *velocity, int32_t *state, float momentum,
+                  int nesterov, int32_t advance, void *stream);
+/* fnet_gather_rows for the inputs AND the targets of a batch in one launch; begin_step != 0 also does the work of
+ * fnet_step_begin(state, beta1, beta2).  x_dst[i, :] = x_src[perm[cursor+i], :], y_dst likewise. */
+int fnet_gather_batch(int32_t batch, int64_t x_row, int64_t y_row, const int32_t *perm, int32_t *state,
+                      const float *x_src, const float *y_src, float *x_dst, float *y_dst, int begin_step, float beta1,
+                      float beta2, void *stream);
 /* dst[i, :] = src[perm[cursor + i], :] for i < batch; replaces the host-side batch slicing of
  * keras Model.fit(shuffle=True) (helpers.py:105-111) on a device-resident dataset */
 int fnet_gather_rows(int32_t batch, int64_t row_elems, const int32_t *perm, const int32_t *state,

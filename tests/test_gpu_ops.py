@@ -162,7 +162,7 @@ def test_dense_forward_backward(L, m, k, n, act):
 
 def test_workspace_too_small_is_an_error_not_a_crash(L):
     from featurenet_b200 import lib as fl
-    m, k, n = 128, 16464, 10
+    m, k, n = 128, 16464, 24          # 24 columns: not the head kernel (<= 16), one output tile, split reduction
     need = L.fnet_dense_workspace_bytes(m, k, n)
     assert need > 0
     x, w, y = dev(np.zeros((m, k))), dev(np.zeros((k, n))), torch.empty((m, n), device="cuda")
@@ -331,6 +331,17 @@ def test_merges_copies_and_padding(L):
     back = torch.empty((3, 2, 5, 6), device="cuda")
     L.fnet_copy_rows(3, 6, 4, 2, 0, 2, 30, ptr(cat), ptr(back), 0, None)
     assert np.array_equal(host(back), c.astype(np.float32).astype(np.float64))
+    # the one-launch versions
+    cd = dev(c)
+    cat2 = torch.empty((3, 6, 5, 6), device="cuda")
+    L.fnet_concat_rows_fwd(3, 4, 2, 30, ptr(ad), ptr(cd), ptr(cat2), None)
+    assert torch.equal(cat2, cat)
+    ga, gc = torch.ones((3, 4, 5, 6), device="cuda"), torch.full((3, 2, 5, 6), 9.0, device="cuda")
+    L.fnet_concat_rows_bwd(3, 4, 2, 30, ptr(cat), ptr(ga), ptr(gc), 1, 0, None)
+    assert np.array_equal(host(ga), (a.astype(np.float32) + np.float32(1)).astype(np.float64))
+    assert np.array_equal(host(gc), c.astype(np.float32).astype(np.float64))
+    L.fnet_concat_rows_bwd(3, 4, 2, 30, ptr(cat), None, ptr(gc), 0, 1, None)        # only one side wants a gradient
+    assert np.array_equal(host(gc), (2 * c.astype(np.float32)).astype(np.float64))
     pd = torch.empty((3, 8, 11, 6), device="cuda")
     L.fnet_pad2d_fwd(3, 4, 5, 6, 2, 3, ptr(ad), ptr(pd), None)
     assert np.array_equal(host(pd), ops.pad2d_fwd(a, (2, 3)).astype(np.float32).astype(np.float64))
@@ -357,11 +368,23 @@ def test_softmax_cross_entropy_and_accuracy(L, batch, classes):
     loss_d = torch.zeros(1, dtype=torch.float64, device="cuda")
     corr_d = torch.zeros(1, dtype=torch.int64, device="cuda")
     for _ in range(2):                                      # accumulates across calls
-        L.fnet_softmax_cce(batch, classes, ptr(dev(p)), ptr(dev(t)), 1.0 / batch, ptr(dzd), ptr(loss_d), ptr(corr_d), None)
+        L.fnet_softmax_cce(batch, classes, ptr(dev(p)), ptr(dev(t)), 1.0 / batch, 0, None, ptr(dzd), ptr(loss_d),
+                           ptr(corr_d), None)
     torch.cuda.synchronize()
     assert int(corr_d.item()) == 2 * int(correct.sum())                      # integer, exact
     assert abs(loss_d.item() - 2 * loss.sum()) <= 1e-5 * abs(2 * loss.sum())
     assert_close(host(dzd), dz, tol=5e-5, what="dlogits")
+    # the same from the logits: the kernel runs the softmax itself and leaves the probabilities in place
+    zd = dev(logits)
+    loss2, corr2 = torch.zeros(1, dtype=torch.float64, device="cuda"), torch.zeros(1, dtype=torch.int64, device="cuda")
+    dz2 = torch.empty((batch, classes), device="cuda")
+    L.fnet_softmax_cce(batch, classes, ptr(zd), ptr(dev(t)), 1.0 / batch, 1, ptr(zd), ptr(dz2), ptr(loss2), ptr(corr2), None)
+    p64 = ops.act_fwd(logits.astype(np.float32).astype(np.float64), "softmax")
+    loss64, correct64 = ops.cce_fwd(p64, t)
+    assert_close(host(zd), p64, what="softmax in place")
+    assert abs(loss2.item() - loss64.sum()) <= 1e-5 * abs(loss64.sum())
+    assert abs(int(corr2.item()) - int(correct64.sum())) <= 1            # a near-tie may flip between fp32 and fp64
+    assert_close(host(dz2), ops.act_bwd(p64, ops.cce_bwd_probs(p64, t, 1.0 / batch), "softmax"), tol=5e-5, what="dlogits from logits")
 
 
 def test_adam_and_sgd_follow_keras(L):
@@ -376,8 +399,11 @@ def test_adam_and_sgd_follow_keras(L):
         g = rng.standard_normal(n) * (10.0 ** rng.integers(-3, 2))
         g32 = g.astype(np.float32).astype(np.float64)
         L.fnet_step_begin(ptr(state), 0.9, 0.999, None)
-        L.fnet_adam_step(n, ptr(pd), ptr(dev(g)), ptr(md), ptr(vd), ptr(state), 0.9, 0.999, 1e-7, None)
-        L.fnet_step_end(ptr(state), 128, None)
+        if t % 2:       # the optimizer launch can close the step itself (advance >= 0) or leave it to fnet_step_end
+            L.fnet_adam_step(n, ptr(pd), ptr(dev(g)), ptr(md), ptr(vd), ptr(state), 0.9, 0.999, 1e-7, 128, None)
+        else:
+            L.fnet_adam_step(n, ptr(pd), ptr(dev(g)), ptr(md), ptr(vd), ptr(state), 0.9, 0.999, 1e-7, -1, None)
+            L.fnet_step_end(ptr(state), 128, None)
         p32, m, v = ops.adam_step(p32, g32, m, v, t, float(np.float32(1e-3)))
         assert_close(host(pd), p32, what="adam step %d" % t)
     torch.cuda.synchronize()
@@ -387,7 +413,7 @@ def test_adam_and_sgd_follow_keras(L):
     qd, veld = dev(p), dev(vel)
     for _ in range(3):
         g = rng.standard_normal(n)
-        L.fnet_sgd_step(n, ptr(qd), ptr(dev(g)), ptr(veld), ptr(state), 0.9, 0, None)
+        L.fnet_sgd_step(n, ptr(qd), ptr(dev(g)), ptr(veld), ptr(state), 0.9, 0, -1, None)
         q, vel = ops.sgd_step(q, g.astype(np.float32).astype(np.float64), vel, float(np.float32(1e-3)), 0.9)
     assert_close(host(qd), q, what="sgd")
 
@@ -402,6 +428,21 @@ def test_gather_rows_and_u8_scaling_are_exact(L):
         L.fnet_gather_rows(32, row, ptr(dev(perm, np.int32)), ptr(state), ptr(dev(src)), ptr(dst), None)
         torch.cuda.synchronize()
         assert np.array_equal(dst.cpu().numpy(), src[perm[13:45]])
+    # inputs and targets in one launch, with the per-step lr_t of fnet_step_begin folded in
+    xs, ys = rng.standard_normal((50, 3072)).astype(np.float32), rng.standard_normal((50, 10)).astype(np.float32)
+    perm = rng.permutation(50).astype(np.int32)
+    state = torch.zeros(8, dtype=torch.int32, device="cuda")
+    state[0], state[1] = 4, 9
+    state[2:3].view(torch.float32).fill_(1e-3)
+    xd, yd = torch.empty((40, 3072), device="cuda"), torch.empty((40, 10), device="cuda")
+    L.fnet_gather_batch(40, 3072, 10, ptr(dev(perm, np.int32)), ptr(state), ptr(dev(xs)), ptr(dev(ys)), ptr(xd), ptr(yd),
+                        1, 0.9, 0.999, None)
+    torch.cuda.synchronize()
+    assert np.array_equal(xd.cpu().numpy(), xs[perm[9:49]]) and np.array_equal(yd.cpu().numpy(), ys[perm[9:49]])
+    lr_t = float(state[3:4].view(torch.float32).item())
+    b1, b2 = float(np.float32(0.9)), float(np.float32(0.999))        # the betas cross the ABI as floats
+    want_lr_t = float(np.float32(1e-3)) * np.sqrt(1 - b2 ** 5) / (1 - b1 ** 5)
+    assert abs(lr_t - want_lr_t) <= 1e-6 * want_lr_t and state[0].item() == 4 and state[1].item() == 9
     u8 = rng.integers(0, 256, 100001, dtype=np.uint8)
     out = torch.empty(u8.size, device="cuda")
     u8d = torch.from_numpy(u8).cuda()
