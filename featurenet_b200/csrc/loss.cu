@@ -6,70 +6,142 @@
 // probabilities, in place if asked), which saves the separate softmax launch of the head.
 //
 // One thread per sample (rows are 10..100 floats and a batch is <= a few thousand rows), one CTA
-// of up to 1024 threads: the batch loss is reduced in a fixed order (shuffle tree, then warp
-// order) and added to the double accumulator by a single thread -- deterministic.
+// of up to 256 threads: the batch loss is reduced in a fixed order (shuffle tree, then warp
+// order) and added to the double accumulator by a single thread -- deterministic.  Rows of up to
+// 16 classes (the 10-class heads of MNIST / CIFAR-10) are held in registers: one read, one write.
 #include "common.cuh"
 
 namespace fnet {
 
-__global__ void __launch_bounds__(1024) softmax_cce_kernel(int batch, int classes, const float *input /* may alias probs_out */,
+constexpr float kClipEps = 1e-7f;
+
+// Everything for one row whose values are addressable through P (registers or memory):
+// returns the loss, sets `hit`, optionally writes scale * dL/dlogits.
+template <class P, class T>
+__device__ __forceinline__ float row_loss(int classes, const P &p, const T &t, float scale, float *dz, bool &hit) {
+    float sum = 0.f, bp = -INFINITY, bt = -INFINITY;
+    int ip = 0, it = 0;
+    for (int c = 0; c < classes; ++c) {           // argmax: first index on ties (strict > while scanning upwards)
+        float pv = p(c), tv = t(c);
+        sum += pv;
+        if (pv > bp) { bp = pv; ip = c; }
+        if (tv > bt) { bt = tv; it = c; }
+    }
+    hit = ip == it;
+    float loss = 0.f, dot = 0.f;
+    for (int c = 0; c < classes; ++c) {           // loss, and g = dL/dq masked by the clip; dot = sum g*q
+        float q = p(c) / sum;
+        float cl = fminf(fmaxf(q, kClipEps), 1.f - kClipEps);
+        float tv = t(c);
+        loss -= tv * logf(cl);
+        float g = (q >= kClipEps && q <= 1.f - kClipEps) ? -tv / cl : 0.f;
+        dot = fmaf(g, q, dot);
+    }
+    if (dz) {
+        // dL/dp_k = (g_k - dot)/sum ; softmax backward: dz_j = p_j*(dp_j - sum_k dp_k p_k)
+        float dot2 = 0.f;
+        for (int c = 0; c < classes; ++c) {
+            float pv = p(c), q = pv / sum;
+            float cl = fminf(fmaxf(q, kClipEps), 1.f - kClipEps);
+            float g = (q >= kClipEps && q <= 1.f - kClipEps) ? -t(c) / cl : 0.f;
+            dot2 = fmaf((g - dot) / sum, pv, dot2);
+        }
+        for (int c = 0; c < classes; ++c) {
+            float pv = p(c), q = pv / sum;
+            float cl = fminf(fmaxf(q, kClipEps), 1.f - kClipEps);
+            float g = (q >= kClipEps && q <= 1.f - kClipEps) ? -t(c) / cl : 0.f;
+            dz[c] = scale * pv * ((g - dot) / sum - dot2);
+        }
+    }
+    return loss;
+}
+
+struct MemRow {
+    const float *q;
+    __device__ float operator()(int c) const { return q[c]; }
+};
+
+template <int CMAX>
+struct RegRow {
+    float v[CMAX];          // only ever indexed with compile-time constants, so it lives in registers
+};
+
+__global__ void __launch_bounds__(256) softmax_cce_kernel(int batch, int classes, const float *input /* may alias probs_out */,
                                                            const float *__restrict__ targets, float scale,
                                                            int from_logits, float *probs_out, float *__restrict__ dlogits,
                                                            double *__restrict__ loss_sum, long long *__restrict__ correct) {
     __shared__ double warp_loss[32];
     __shared__ int warp_correct[32];
-    const float kEps = 1e-7f;
     double my_loss = 0.0;
     int my_correct = 0;
     for (int row = threadIdx.x; row < batch; row += blockDim.x) {
-        const float *p = input + (int64_t)row * classes;
-        const float *t = targets + (int64_t)row * classes;
-        if (from_logits) {
-            // keras softmax: exp(z - max) / sum, written where the loss (and the caller) will read it
-            float mx = -INFINITY, se = 0.f;
-            for (int c = 0; c < classes; ++c) mx = fmaxf(mx, p[c]);
-            for (int c = 0; c < classes; ++c) se += expf(p[c] - mx);
-            float *q = probs_out + (int64_t)row * classes;
-            for (int c = 0; c < classes; ++c) q[c] = expf(p[c] - mx) / se;     // in place is fine: one thread owns the row
-            p = q;
-        }
-        // pass 1: sum(p), argmax p, argmax t (first index on ties: strict > while scanning upwards)
-        float sum = 0.f, bp = -INFINITY, bt = -INFINITY;
-        int ip = 0, it = 0;
-        for (int c = 0; c < classes; ++c) {
-            float pv = p[c], tv = __ldg(t + c);
-            sum += pv;
-            if (pv > bp) { bp = pv; ip = c; }
-            if (tv > bt) { bt = tv; it = c; }
-        }
-        // pass 2: loss, and g = dL/dq masked by the clip; dot = sum g*q
-        float loss = 0.f, dot = 0.f;
-        for (int c = 0; c < classes; ++c) {
-            float q = p[c] / sum;
-            float cl = fminf(fmaxf(q, kEps), 1.f - kEps);
-            float tv = __ldg(t + c);
-            loss -= tv * logf(cl);
-            float g = (q >= kEps && q <= 1.f - kEps) ? -tv / cl : 0.f;
-            dot = fmaf(g, q, dot);
-        }
-        if (dlogits) {
-            // dL/dp_k = (g_k - dot)/sum ; softmax backward: dz_j = p_j*(dp_j - sum_k dp_k p_k)
-            float dot2 = 0.f;
-            for (int c = 0; c < classes; ++c) {
-                float pv = p[c], q = pv / sum;
-                float cl = fminf(fmaxf(q, kEps), 1.f - kEps);
-                float g = (q >= kEps && q <= 1.f - kEps) ? -__ldg(t + c) / cl : 0.f;
-                dot2 = fmaf((g - dot) / sum, pv, dot2);
+        const float *in = input + (int64_t)row * classes;
+        const float *tg = targets + (int64_t)row * classes;
+        float *dz = dlogits ? dlogits + (int64_t)row * classes : nullptr;
+        bool hit = false;
+        float loss;
+        if (classes <= 16) {
+            RegRow<16> p, t;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                p.v[c] = c < classes ? in[c] : 0.f;
+                t.v[c] = c < classes ? __ldg(tg + c) : 0.f;
             }
-            for (int c = 0; c < classes; ++c) {
-                float pv = p[c], q = pv / sum;
-                float cl = fminf(fmaxf(q, kEps), 1.f - kEps);
-                float g = (q >= kEps && q <= 1.f - kEps) ? -__ldg(t + c) / cl : 0.f;
-                dlogits[(int64_t)row * classes + c] = scale * pv * ((g - dot) / sum - dot2);
+            if (from_logits) {
+                float mx = -INFINITY, se = 0.f;
+#pragma unroll
+                for (int c = 0; c < 16; ++c) if (c < classes) mx = fmaxf(mx, p.v[c]);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) if (c < classes) { p.v[c] = expf(p.v[c] - mx); se += p.v[c]; }
+                float *q = probs_out + (int64_t)row * classes;
+#pragma unroll
+                for (int c = 0; c < 16; ++c) if (c < classes) { p.v[c] = p.v[c] / se; q[c] = p.v[c]; }
             }
+            float dzr[16];
+            // fully unrolled register version of row_loss (indices must be compile-time constants)
+            float sum = 0.f, bp = -INFINITY, bt = -INFINITY;
+            int ip = 0, it = 0;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) if (c < classes) {
+                sum += p.v[c];
+                if (p.v[c] > bp) { bp = p.v[c]; ip = c; }
+                if (t.v[c] > bt) { bt = t.v[c]; it = c; }
+            }
+            hit = ip == it;
+            float dot = 0.f, g[16];
+            loss = 0.f;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) if (c < classes) {
+                float q = p.v[c] / sum;
+                float cl = fminf(fmaxf(q, kClipEps), 1.f - kClipEps);
+                loss -= t.v[c] * logf(cl);
+                g[c] = (q >= kClipEps && q <= 1.f - kClipEps) ? -t.v[c] / cl : 0.f;
+                dot = fmaf(g[c], q, dot);
+            }
+            if (dz) {
+                float dot2 = 0.f;
+#pragma unroll
+                for (int c = 0; c < 16; ++c) if (c < classes) dot2 = fmaf((g[c] - dot) / sum, p.v[c], dot2);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) if (c < classes) dzr[c] = scale * p.v[c] * ((g[c] - dot) / sum - dot2);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) if (c < classes) dz[c] = dzr[c];
+            }
+        } else {
+            const float *pp = in;
+            if (from_logits) {
+                // keras softmax: exp(z - max) / sum, written where the loss (and the caller) will read it
+                float mx = -INFINITY, se = 0.f;
+                for (int c = 0; c < classes; ++c) mx = fmaxf(mx, in[c]);
+                for (int c = 0; c < classes; ++c) se += expf(in[c] - mx);
+                float *q = probs_out + (int64_t)row * classes;
+                for (int c = 0; c < classes; ++c) q[c] = expf(in[c] - mx) / se;    // in place is fine: one thread owns the row
+                pp = q;
+            }
+            loss = row_loss(classes, MemRow{pp}, MemRow{tg}, scale, dz, hit);
         }
         my_loss += (double)loss;
-        my_correct += (ip == it) ? 1 : 0;
+        my_correct += hit ? 1 : 0;
     }
     // fixed-order block reduction
 #pragma unroll
@@ -100,7 +172,7 @@ extern "C" int fnet_softmax_cce(int32_t batch, int32_t classes, const float *inp
     FNET_REQUIRE(!from_logits || probs_out != nullptr, "fnet_softmax_cce: from_logits needs a place for the probabilities");
     FNET_REQUIRE(dlogits == nullptr || dlogits != probs_out, "fnet_softmax_cce: dlogits must not alias the probabilities");
     if (batch == 0) return FNET_OK;
-    int threads = batch >= 1024 ? 1024 : ((batch + 31) / 32) * 32;
+    int threads = batch >= 256 ? 256 : ((batch + 31) / 32) * 32;
     softmax_cce_kernel<<<1, threads, 0, as_stream(stream)>>>(batch, classes, input, targets, scale, from_logits, probs_out,
                                                              dlogits, loss_sum, reinterpret_cast<long long *>(correct));
     return check_launch("fnet_softmax_cce");

@@ -19,17 +19,20 @@ namespace fnet {
 constexpr int kSkinnyN = 16;
 
 // ------------------------------------------------------------------ dense, N <= 16
+// one CTA of 1024 threads per sample: 32 warps keep ~4 independent k-steps each in flight, which is what hides
+// the L2 latency of the weight rows (the whole reduction is only K/1024 steps per thread)
 template <int NMAX>
-__global__ void __launch_bounds__(256) dense_skinny_fwd_kernel(int K, int N, int act, const float *__restrict__ x,
-                                                               const float *__restrict__ w, const float *__restrict__ bias,
-                                                               float *__restrict__ y) {
-    __shared__ float red[8][NMAX];
+__global__ void __launch_bounds__(1024) dense_skinny_fwd_kernel(int K, int N, int act, const float *__restrict__ x,
+                                                                const float *__restrict__ w, const float *__restrict__ bias,
+                                                                float *__restrict__ y) {
+    __shared__ float red[32][NMAX];
     const int m = blockIdx.x;
     const float *xr = x + (long long)m * K;
     float acc[NMAX];
 #pragma unroll
     for (int n = 0; n < NMAX; ++n) acc[n] = 0.f;
-    for (int k = threadIdx.x; k < K; k += 256) {
+#pragma unroll 4
+    for (int k = threadIdx.x; k < K; k += 1024) {
         float xv = __ldg(xr + k);
         const float *wr = w + (long long)k * N;
 #pragma unroll
@@ -46,7 +49,7 @@ __global__ void __launch_bounds__(256) dense_skinny_fwd_kernel(int K, int N, int
     if (threadIdx.x < N) {
         float v = 0.f;
 #pragma unroll
-        for (int wv = 0; wv < 8; ++wv) v += red[wv][threadIdx.x];
+        for (int wv = 0; wv < 32; ++wv) v += red[wv][threadIdx.x];
         if (bias) v += __ldg(bias + threadIdx.x);
         y[(long long)m * N + threadIdx.x] = act_apply(v, act);
     }
@@ -57,8 +60,12 @@ template <int NMAX>
 __global__ void __launch_bounds__(256) dense_skinny_wgrad_kernel(int M, int K, int N, const float *__restrict__ x,
                                                                  const float *__restrict__ dz, float *__restrict__ dw,
                                                                  float *__restrict__ dbias) {
+    // a CTA owns 32 consecutive weight rows k; its 8 warps split the samples (warp g takes rows g, g+8, ...), so a
+    // warp reads 128 contiguous bytes of x per sample and there are K/32 CTAs instead of K/256
     extern __shared__ float dz_s[];                 // a chunk of dz rows, [rows][N]
-    const int k = blockIdx.x * 256 + threadIdx.x;
+    __shared__ float red[8][32][NMAX + 1];
+    const int kk = threadIdx.x & 31, mg = threadIdx.x >> 5;
+    const int k = blockIdx.x * 32 + kk;
     float acc[NMAX];
 #pragma unroll
     for (int n = 0; n < NMAX; ++n) acc[n] = 0.f;
@@ -70,7 +77,8 @@ __global__ void __launch_bounds__(256) dense_skinny_wgrad_kernel(int M, int K, i
         for (int i = threadIdx.x; i < rows * N; i += 256) dz_s[i] = __ldg(dz + (long long)m0 * N + i);
         __syncthreads();
         if (k < K) {
-            for (int r = 0; r < rows; ++r) {
+#pragma unroll 4
+            for (int r = mg; r < rows; r += 8) {
                 float xv = __ldg(x + (long long)(m0 + r) * K + k);
 #pragma unroll
                 for (int n = 0; n < NMAX; ++n)
@@ -80,10 +88,19 @@ __global__ void __launch_bounds__(256) dense_skinny_wgrad_kernel(int M, int K, i
         if (dbias && blockIdx.x == 0 && threadIdx.x < N)
             for (int r = 0; r < rows; ++r) bsum += dz_s[r * N + threadIdx.x];
     }
-    if (k < K) {
 #pragma unroll
-        for (int n = 0; n < NMAX; ++n)
-            if (n < N) dw[(long long)k * N + n] = acc[n];
+    for (int n = 0; n < NMAX; ++n) red[mg][kk][n] = acc[n];
+    __syncthreads();
+    if (mg == 0 && k < K) {
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) {
+            if (n < N) {
+                float v = 0.f;
+#pragma unroll
+                for (int g2 = 0; g2 < 8; ++g2) v += red[g2][kk][n];      // fixed order: deterministic
+                dw[(long long)k * N + n] = v;
+            }
+        }
     }
     if (dbias && blockIdx.x == 0 && threadIdx.x < N) dbias[threadIdx.x] = bsum;
 }
@@ -276,12 +293,14 @@ __global__ void __launch_bounds__(256) conv_small_wgrad_reduce_kernel(int blocks
 }
 
 // ------------------------------------------------------------------ dispatch (called from conv_api.cu)
+// "small" = few channels on BOTH sides: a thread walks its pixel's channels serially, which only coalesces
+// (through L1) when a pixel is a few dozen bytes
 static bool small_fwd_ok(const ConvGeom &g) {
-    return !is_dense_geom(g) && g.K <= kSkinnyN && (long long)g.kh * g.kw * g.C <= 256 &&
+    return !is_dense_geom(g) && g.K <= kSkinnyN && g.C <= kSkinnyN && (long long)g.kh * g.kw * g.C <= 256 &&
            ((long long)g.kh * g.kw * g.C + 1) * g.K * 4 <= 40 * 1024;
 }
 static bool small_dgrad_ok(const ConvGeom &g) {
-    return !is_dense_geom(g) && g.C <= kSkinnyN && (long long)g.kh * g.kw * g.K <= 256 &&
+    return !is_dense_geom(g) && g.C <= kSkinnyN && g.K <= kSkinnyN && (long long)g.kh * g.kw * g.K <= 256 &&
            (long long)g.kh * g.kw * g.C * g.K * 4 <= 40 * 1024;
 }
 static bool small_wgrad_ok(const ConvGeom &g, bool with_bias) {
@@ -311,7 +330,7 @@ static int pixel_grid(long long pixels) {
 int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t s) {
     if (act == FNET_ACT_SOFTMAX) act = FNET_ACT_NONE;      // the caller runs the softmax pass
     if (is_dense_geom(g)) {
-        dense_skinny_fwd_kernel<kSkinnyN><<<g.B, 256, 0, s>>>(g.C, g.K, act, x, w, bias, y);
+        dense_skinny_fwd_kernel<kSkinnyN><<<g.B, 1024, 0, s>>>(g.C, g.K, act, x, w, bias, y);
         return check_launch("dense_fwd[skinny]");
     }
     size_t smem = ((size_t)g.kh * g.kw * g.C + 1) * g.K * sizeof(float);
@@ -339,7 +358,7 @@ int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, 
                  cudaStream_t s) {
     if (is_dense_geom(g)) {
         size_t smem = (size_t)256 * g.K * sizeof(float);
-        dense_skinny_wgrad_kernel<kSkinnyN><<<(unsigned)ceil_div<long long>(g.C, 256), 256, smem, s>>>(g.B, g.C, g.K, x, dz,
+        dense_skinny_wgrad_kernel<kSkinnyN><<<(unsigned)ceil_div<long long>(g.C, 32), 256, smem, s>>>(g.B, g.C, g.K, x, dz,
                                                                                                      dw, dbias);
         return check_launch("dense_bwd_filter[skinny]");
     }

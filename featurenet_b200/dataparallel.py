@@ -79,8 +79,8 @@ class DataParallelTrainer(object):
         eng = self.eng
         with torch.cuda.stream(eng.stream):
             eng.data["train"][2].copy_(torch.from_numpy(np.asarray(order, dtype=np.int32)))
-            eng.loss_sum.zero_()
-            eng.correct.zero_()
+            eng.metrics.zero_()
+        eng._metrics_seen = (0.0, 0)
         self._cursor_base = 0
 
     def step(self, global_batch):

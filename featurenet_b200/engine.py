@@ -100,8 +100,12 @@ class Engine(object):
         with torch.cuda.device(self.device):
             self.state = torch.zeros(8, dtype=torch.int32, device=self.device)
             self.state_eval = torch.zeros(8, dtype=torch.int32, device=self.device)
-            self.loss_sum = torch.zeros(1, dtype=torch.float64, device=self.device)
-            self.correct = torch.zeros(1, dtype=torch.int64, device=self.device)
+            # one 16-byte block: [loss sum (double bits), correct count] -> a single D2H copy reads both
+            self.metrics = torch.zeros(2, dtype=torch.int64, device=self.device)
+            self.loss_sum = self.metrics[0:1].view(torch.float64)
+            self.correct = self.metrics[1:2]
+            self._metrics_host = torch.zeros(2, dtype=torch.int64).pin_memory()
+            self._metrics_seen = (0.0, 0)
             self._lr_host = torch.zeros(1, dtype=torch.float32).pin_memory()
         self._lr_on_device = None
         self.timeline = None          # when a list: (label, start_event, end_event) per launch (profiling mode)
@@ -716,15 +720,22 @@ class Engine(object):
         self.data[split] = (xd, yd, perm)
         return self.data[split]
 
-    def _read_metrics(self, n):
+    def _fetch_metrics(self):
+        """(loss sum, correct count) accumulated on the device so far: one 16-byte copy into pinned memory."""
+        with torch.cuda.stream(self.stream):
+            self._metrics_host.copy_(self.metrics, non_blocking=True)
         self.stream.synchronize()
-        return float(self.loss_sum.item()) / n, int(self.correct.item()) / n
+        return float(self._metrics_host[0:1].view(torch.float64)[0]), int(self._metrics_host[1])
+
+    def _read_metrics(self, n):
+        loss_sum, correct = self._fetch_metrics()
+        return loss_sum / n, correct / n
 
     def _zero_metrics(self, state):
         with torch.cuda.stream(self.stream):
-            self.loss_sum.zero_()
-            self.correct.zero_()
+            self.metrics.zero_()
             state[1:2].zero_()
+        self._metrics_seen = (0.0, 0)
 
     def _check_xy(self, x, y):
         x, y = np.asarray(x), np.asarray(y)
@@ -784,13 +795,16 @@ class Engine(object):
         xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
         yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
         with torch.cuda.stream(self.stream):
-            self.loss_sum.zero_()
-            self.correct.zero_()
             self.act[0][:b].copy_(xt, non_blocking=True)
             self.yb[:b].copy_(yt, non_blocking=True)
         self._step("train_fed", b)
-        loss, acc = self._read_metrics(b)
-        return [loss, acc]
+        # the device accumulators keep running (no per-step zeroing launches); this step = the difference
+        loss_sum, correct = self._fetch_metrics()
+        seen_loss, seen_correct = self._metrics_seen
+        if loss_sum < seen_loss or correct < seen_correct:      # someone reset the accumulators (fit / evaluate)
+            seen_loss, seen_correct = 0.0, 0
+        self._metrics_seen = (loss_sum, correct)
+        return [(loss_sum - seen_loss) / b, (correct - seen_correct) / b]
 
     def fit(self, x, y, batch_size=32, epochs=1, validation_data=None, shuffle=True, callbacks=(), verbose=0,
             permutations=None, initial_epoch=0, augment=None, **_):

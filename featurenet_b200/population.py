@@ -53,16 +53,21 @@ def max_over_ranks(value, dist=None, device=None):
     return float(t.item())
 
 
-def run_population(products, train_one, costs, rank=0, world_size=1, dist=None):
+def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, workers=1):
     """Train this rank's share of ``products``; gather (index, result) pairs on every rank, in index order.
 
     train_one(index, product) -> picklable result (e.g. dict(accuracy=..., history=..., params=...)).
     Failures are reported, not raised: an invalid or out-of-memory candidate yields ``{"error": ...}``,
     as the reference turns them into accuracy 0 (tensorflow_generator.py:109-111, helpers.py:172-174).
+
+    workers > 1 keeps that many candidates resident on this rank's GPU at once, each driven by its own host
+    thread on its own CUDA stream.  FeatureNet's candidates are mostly launch-latency-bound chains of tiny
+    kernels (a step of a 6-feature network is ~15 launches of a few microseconds), so several chains
+    interleave on the 148 SMs almost for free; the work queue is longest-first, pulled dynamically.
     """
     mine = assign_lpt(costs, world_size)[rank]
-    local = []
-    for index in mine:
+
+    def one(index):
         started = time.time()
         try:
             result = train_one(index, products[index])
@@ -71,7 +76,22 @@ def run_population(products, train_one, costs, rank=0, world_size=1, dist=None):
         if isinstance(result, dict):
             result.setdefault("seconds", time.time() - started)
             result.setdefault("rank", rank)
-        local.append((index, result))
+        return (index, result)
+
+    if workers > 1 and len(mine) > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        initializer = None
+        try:
+            import torch
+            if torch.cuda.is_available():
+                device = torch.cuda.current_device()     # the current device is per thread: hand it to the workers
+                initializer = lambda: torch.cuda.set_device(device)
+        except ImportError:
+            pass
+        with ThreadPoolExecutor(max_workers=workers, initializer=initializer) as pool:
+            local = list(pool.map(one, mine))            # `mine` is already longest-first
+    else:
+        local = [one(index) for index in mine]
     if dist is not None and dist.is_initialized() and world_size > 1:
         gathered = [None] * world_size
         dist.all_gather_object(gathered, local)
@@ -81,11 +101,23 @@ def run_population(products, train_one, costs, rank=0, world_size=1, dist=None):
     return sorted(merged, key=lambda pair: pair[0])
 
 
-def train_product(product, dataset, epochs, batch_size, product_features=None, data_augmentation=False):
-    """One candidate through the reference-named runner; returns the fields the drivers log."""
+def train_product(product, dataset, epochs, batch_size, product_features=None, data_augmentation=False, shared_gpu=False):
+    """One candidate through the reference-named runner; returns the fields the drivers log.
+
+    shared_gpu=True is for candidates that run side by side on one GPU (run_population(workers > 1)): the runner
+    must not tear down "the previous candidate" (it may be a neighbour that is still training), so this function
+    releases its own network when it is done, and it does not touch the process-wide stdout.
+    """
     from tensorflow_generator import TensorflowGenerator
-    with contextlib.redirect_stdout(io.StringIO()):
+    if shared_gpu:
         gen = TensorflowGenerator(product, epochs=epochs, dataset=dataset, data_augmentation=data_augmentation,
-                                  batch_size=batch_size, product_features=product_features)
+                                  batch_size=batch_size, product_features=product_features, clear_memory=False)
+        network = getattr(getattr(gen, "model", None), "model", None)
+        if network is not None:
+            network.release()
+    else:
+        with contextlib.redirect_stdout(io.StringIO()):
+            gen = TensorflowGenerator(product, epochs=epochs, dataset=dataset, data_augmentation=data_augmentation,
+                                      batch_size=batch_size, product_features=product_features)
     return {"accuracy": float(gen.accuracy), "params": int(gen.params), "training_time": float(gen.training_time),
             "history": (list(gen.history[0]), list(gen.history[1])), "valid": bool(gen.params)}
