@@ -29,6 +29,17 @@ int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *
 
 int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
                size_t ws_bytes, cudaStream_t s) {
+    if (size_t t_bytes = col2im_t_bytes(g)) {
+        // T = dz x w^T as the data gradient of a dense layer [taps*C] -> [K], then dx = col2im(T)
+        if (!ws || ws_bytes < t_bytes) {
+            set_error("conv2d_bwd_data: workspace of %zu bytes needed, %zu given", t_bytes, ws_bytes);
+            return FNET_ERR_WORKSPACE;
+        }
+        float *t = reinterpret_cast<float *>(ws);
+        ConvGeom gd = dense_geom((long long)g.B * g.Ho * g.Wo, (long long)g.kh * g.kw * g.C, g.K);
+        int rc = conv_dgrad(gd, math, dz, w, t, 0, reinterpret_cast<char *>(ws) + t_bytes, ws_bytes - t_bytes, s);
+        return rc == FNET_OK ? col2im_scatter(g, t, dx, accumulate, s) : rc;
+    }
     if (skinny_supported(g, 1, false)) return skinny_dgrad(g, dz, w, dx, accumulate, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) return tc_conv_dgrad(g, math, dz, w, dx, accumulate, ws, ws_bytes, s);
     return simt_conv_dgrad(g, dz, w, dx, accumulate, ws, ws_bytes, s);
@@ -58,6 +69,10 @@ size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
     if (geom_checked(d, g, "fnet_conv2d_workspace_bytes") != FNET_OK) return 0;
     size_t need = max_sz(simt_conv_workspace(g), skinny_workspace(g));
     if (d->math != FNET_MATH_FP32) need = max_sz(need, tc_conv_workspace(g, d->math));
+    if (size_t t_bytes = col2im_t_bytes(g)) {
+        ConvGeom gd = dense_geom((long long)g.B * g.Ho * g.Wo, (long long)g.kh * g.kw * g.C, g.K);
+        need = max_sz(need, t_bytes + max_sz(simt_conv_workspace(gd), tc_conv_workspace(gd, FNET_MATH_TF32)));
+    }
     return need;
 }
 

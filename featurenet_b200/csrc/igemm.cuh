@@ -38,6 +38,10 @@ int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, 
 int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
                  cudaStream_t s);
 
+// data gradient for few input channels: dense GEMM into T (workspace) + col2im (col2im.cu)
+size_t col2im_t_bytes(const ConvGeom &g);                    // 0 = not applicable
+int col2im_scatter(const ConvGeom &g, const float *t, float *dx, int accumulate, cudaStream_t stream);
+
 int run_softmax_rows(int64_t rows, int64_t cols, const float *x, float *y, cudaStream_t stream);
 
 }  // namespace fnet

@@ -7,6 +7,10 @@
 // Each problem also says along which GEMM axis its operands are contiguous in memory
 // (kAContigK / kBContigK), so that a loader can put the lanes of a warp on that axis, and offers a
 // 16-byte gather (a4) for the cases where four consecutive k are four consecutive channels.
+//
+// Integer address arithmetic is what these kernels execute most, so the reduction index is never
+// divided in the main loop: a column context is decoded once (make_col) and then stepped from one
+// k-tile to the next (next_col); the same for the B operand of the data gradient (BCursor).
 #pragma once
 #include "igemm.cuh"
 
@@ -19,7 +23,7 @@ struct PixelCtx {   // one output pixel (forward / filter) or one input pixel (d
 };
 
 struct TapCtx {     // one (r, s, channel) of the reduction / filter row
-    int dr, ds;     // dilated tap offsets
+    int r, s;       // tap coordinates (undilated)
     int ch;         // channel inside the tap
     int valid;      // 1 = real tap, 2 = the all-ones bias row (filter gradient only), 0 = out of range
 };
@@ -33,6 +37,25 @@ __device__ __forceinline__ void decode_out_pixel(const ConvGeom &g, int m, int M
     p.base = (long long)b * g.H * g.W * g.C;
     p.h0 = ho * g.sh - g.pt;
     p.w0 = wo * g.sw - g.pl;
+}
+
+// the context of output pixel m + step given that of m: carries instead of divisions unless rows are very short
+__device__ __forceinline__ void step_out_pixel(const ConvGeom &g, int m_new, int step, int M, PixelCtx &p) {
+    if (g.Wo * 4 < step) {
+        decode_out_pixel(g, m_new, M, p);
+        return;
+    }
+    p.valid = m_new < M;
+    const int row_w = g.Wo * g.sw, img_h = g.Ho * g.sh;
+    p.w0 += step * g.sw;
+    while (p.w0 >= row_w - g.pl) {
+        p.w0 -= row_w;
+        p.h0 += g.sh;
+        if (p.h0 >= img_h - g.pt) {
+            p.h0 -= img_h;
+            p.base += (long long)g.H * g.W * g.C;
+        }
+    }
 }
 
 __device__ __forceinline__ void decode_in_pixel(const ConvGeom &g, int m, int M, PixelCtx &p) {
@@ -51,26 +74,48 @@ __device__ __forceinline__ void decode_tap(const ConvGeom &g, int k, int channel
     int kk = t.valid ? k : 0;
     int tap = kk / channels;
     t.ch = kk - tap * channels;
-    int r = tap / g.kw, s = tap - r * g.kw;
-    t.dr = r * g.dh;
-    t.ds = s * g.dw;
+    t.r = tap / g.kw;
+    t.s = tap - t.r * g.kw;
 }
 
-// address of x[b, h0+dr, w0+ds, ch], or nullptr in the zero padding
+// the context of k + step given the context of k: no division when a tap holds at least a few channels
+__device__ __forceinline__ void step_tap(const ConvGeom &g, int k_new, int step, int channels, int limit, TapCtx &t) {
+    if (channels * 4 < step) {          // tiny channel counts would loop many times: decode from scratch
+        decode_tap(g, k_new, channels, limit, t);
+        return;
+    }
+    t.valid = k_new < limit;
+    t.ch += step;
+    while (t.ch >= channels) {
+        t.ch -= channels;
+        if (++t.s == g.kw) { t.s = 0; ++t.r; }
+    }
+}
+
+// address of x[b, h0 + r*dh, w0 + s*dw, ch], or nullptr in the zero padding
 __device__ __forceinline__ const float *input_at(const ConvGeom &g, const float *__restrict__ x, const PixelCtx &p,
                                                  const TapCtx &t) {
-    int h = p.h0 + t.dr, w = p.w0 + t.ds;
+    int h = p.h0 + t.r * g.dh, w = p.w0 + t.s * g.dw;
     if ((unsigned)h >= (unsigned)g.H || (unsigned)w >= (unsigned)g.W) return nullptr;
     return x + p.base + ((long long)h * g.W + w) * g.C + t.ch;
 }
 
-// address of dz[b, (hp-dr)/sh, (wp-ds)/sw, ch] when the divisions are exact and in range
+// o = v / stride when the division is exact and 0 <= o < extent, else -1 (strides are 1 or 2 in practice)
+__device__ __forceinline__ int exact_div(int v, int stride, int extent) {
+    if (v < 0) return -1;
+    int o;
+    if (stride == 1) o = v;
+    else if (stride == 2) { if (v & 1) return -1; o = v >> 1; }
+    else { o = v / stride; if (o * stride != v) return -1; }
+    return o < extent ? o : -1;
+}
+
+// address of dz[b, (hp - r*dh)/sh, (wp - s*dw)/sw, ch] when the divisions are exact and in range
 __device__ __forceinline__ const float *grad_at(const ConvGeom &g, const float *__restrict__ dz, const PixelCtx &p,
                                                 const TapCtx &t) {
-    int hh = p.h0 - t.dr, ww = p.w0 - t.ds;
-    if (hh < 0 || ww < 0) return nullptr;
-    int ho = hh / g.sh, wo = ww / g.sw;
-    if (ho * g.sh != hh || wo * g.sw != ww || ho >= g.Ho || wo >= g.Wo) return nullptr;
+    int ho = exact_div(p.h0 - t.r * g.dh, g.sh, g.Ho);
+    int wo = exact_div(p.w0 - t.s * g.dw, g.sw, g.Wo);
+    if ((ho | wo) < 0) return nullptr;
     return dz + p.base + ((long long)ho * g.Wo + wo) * g.K + t.ch;
 }
 
@@ -87,21 +132,30 @@ struct FwdProblem {
     int act;
     typedef PixelCtx Row;
     typedef TapCtx Col;
+    typedef const float *BCursor;               // B(k, n) = w[k][n]: a pointer that moves down the rows
     static constexpr bool kAContigK = true;     // A(m, k): consecutive k = consecutive input channels
-    static constexpr bool kBContigK = false;    // B(k, n) = w[k][n]: consecutive n
+    static constexpr bool kBContigK = false;    // consecutive n
     __device__ bool vec4_ok() const { return (g.C & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }
     __device__ void make_row(int m, int M, Row &r) const { decode_out_pixel(g, m, M, r); }
     __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.C, kend, c); }
-    __device__ float a(const Row &r, const Col &c) const { return load1(input_at(g, x, r, c)); }
-    __device__ float4 a4(const Row &r, const Col &c) const { return load4(input_at(g, x, r, c)); }
-    __device__ float b(int k, int n) const { return __ldg(w + (long long)k * g.K + n); }
+    __device__ void next_col(int k_new, int step, int kend, Col &c) const { step_tap(g, k_new, step, g.C, kend, c); }
     __device__ const float *a_ptr(const Row &r, const Col &c) const { return input_at(g, x, r, c); }
-    __device__ const float *b_ptr(int k, int n) const { return w + (long long)k * g.K + n; }
+    __device__ float a(const Row &r, const Col &c) const { return load1(a_ptr(r, c)); }
+    __device__ float4 a4(const Row &r, const Col &c) const { return load4(a_ptr(r, c)); }
+    __device__ BCursor b_begin(int k, int n) const { return w + (long long)k * g.K + n; }
+    __device__ void b_next(BCursor &c, int step) const { c += (long long)step * g.K; }
+    __device__ const float *b_ptr(const BCursor &c) const { return c; }
+    __device__ long long b_stride_n() const { return 1; }
+    __device__ long long b_stride_k() const { return g.K; }
     __device__ const float *any_ptr() const { return x; }
     __device__ void store(int m, int n, float v) const {
         if (bias) v += __ldg(bias + n);
         y[(long long)m * g.K + n] = act_apply(v, act);
     }
+};
+
+struct DgradCursor {
+    int tap, ko, n;
 };
 
 struct DgradProblem {
@@ -111,22 +165,31 @@ struct DgradProblem {
     int accumulate;
     typedef PixelCtx Row;
     typedef TapCtx Col;
+    typedef DgradCursor BCursor;                // B(k, n) = w[tap][n][ko] with k = tap*K + ko
     static constexpr bool kAContigK = true;     // consecutive k = consecutive output channels of dz
-    static constexpr bool kBContigK = true;     // B(k, n) = w[tap][n][ko]: consecutive ko
+    static constexpr bool kBContigK = true;     // consecutive ko
     __device__ bool vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(dz) & 15) == 0; }
     __device__ void make_row(int m, int M, Row &r) const { decode_in_pixel(g, m, M, r); }
     __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.K, kend, c); }
-    __device__ float a(const Row &r, const Col &c) const { return load1(grad_at(g, dz, r, c)); }
-    __device__ float4 a4(const Row &r, const Col &c) const { return load4(grad_at(g, dz, r, c)); }
-    __device__ float b(int k, int n) const {
-        int tap = k / g.K, ko = k - tap * g.K;
-        return __ldg(w + ((long long)tap * g.C + n) * g.K + ko);
-    }
+    __device__ void next_col(int k_new, int step, int kend, Col &c) const { step_tap(g, k_new, step, g.K, kend, c); }
     __device__ const float *a_ptr(const Row &r, const Col &c) const { return grad_at(g, dz, r, c); }
-    __device__ const float *b_ptr(int k, int n) const {
-        int tap = k / g.K, ko = k - tap * g.K;
-        return w + ((long long)tap * g.C + n) * g.K + ko;
+    __device__ float a(const Row &r, const Col &c) const { return load1(a_ptr(r, c)); }
+    __device__ float4 a4(const Row &r, const Col &c) const { return load4(a_ptr(r, c)); }
+    __device__ BCursor b_begin(int k, int n) const {
+        BCursor c;
+        c.tap = k / g.K;
+        c.ko = k - c.tap * g.K;
+        c.n = n;
+        return c;
     }
+    __device__ void b_next(BCursor &c, int step) const {
+        c.ko += step;
+        if (g.K * 4 < step) { c.tap += c.ko / g.K; c.ko %= g.K; return; }
+        while (c.ko >= g.K) { c.ko -= g.K; ++c.tap; }
+    }
+    __device__ const float *b_ptr(const BCursor &c) const { return w + ((long long)c.tap * g.C + c.n) * g.K + c.ko; }
+    __device__ long long b_stride_n() const { return g.K; }
+    __device__ long long b_stride_k() const { return 1; }
     __device__ const float *any_ptr() const { return dz; }
     __device__ void store(int m, int n, float v) const {
         long long at = (long long)m * g.C + n;
@@ -141,19 +204,24 @@ struct WgradProblem {
     int taps_c;   // kh*kw*C: rows below are filter taps, row == taps_c is the bias row
     typedef TapCtx Row;
     typedef PixelCtx Col;
+    typedef const float *BCursor;               // B(k, n) = dz[pixel k][n]
     static constexpr bool kAContigK = false;    // A(m, k) = x[pixel k][tap/channel m]: consecutive m (channels)
-    static constexpr bool kBContigK = false;    // B(k, n) = dz[pixel k][n]: consecutive n
+    static constexpr bool kBContigK = false;    // consecutive n
     __device__ bool vec4_ok() const { return false; }
     __device__ void make_row(int k, int M, Row &r) const {
         decode_tap(g, k, g.C, taps_c, r);
         if (k == taps_c && k < M) r.valid = 2;
     }
     __device__ void make_col(int m, int mend, Col &c) const { decode_out_pixel(g, m, mend, c); }
-    __device__ float a(const Row &r, const Col &c) const { return r.valid == 2 ? 1.f : load1(input_at(g, x, c, r)); }
-    __device__ float4 a4(const Row &, const Col &) const { return make_float4(0.f, 0.f, 0.f, 0.f); }
-    __device__ float b(int m, int n) const { return __ldg(dz + (long long)m * g.K + n); }
+    __device__ void next_col(int m_new, int step, int mend, Col &c) const { step_out_pixel(g, m_new, step, mend, c); }
     __device__ const float *a_ptr(const Row &r, const Col &c) const { return input_at(g, x, c, r); }
-    __device__ const float *b_ptr(int m, int n) const { return dz + (long long)m * g.K + n; }
+    __device__ float a(const Row &r, const Col &c) const { return r.valid == 2 ? 1.f : load1(a_ptr(r, c)); }
+    __device__ float4 a4(const Row &, const Col &) const { return make_float4(0.f, 0.f, 0.f, 0.f); }
+    __device__ BCursor b_begin(int m, int n) const { return dz + (long long)m * g.K + n; }
+    __device__ void b_next(BCursor &c, int step) const { c += (long long)step * g.K; }
+    __device__ const float *b_ptr(const BCursor &c) const { return c; }
+    __device__ long long b_stride_n() const { return 1; }
+    __device__ long long b_stride_k() const { return g.K; }
     __device__ const float *any_ptr() const { return x; }
     __device__ void store(int k, int n, float v) const {
         if (k < taps_c) dw[(long long)k * g.K + n] = v;

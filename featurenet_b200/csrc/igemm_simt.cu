@@ -52,10 +52,20 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
 
+    // column context and B cursors are decoded once and then stepped from tile to tile (no divisions)
     float a_reg[A_PER], b_reg[B_PER];
+    typename P::Col col;
+    typename P::BCursor bcur[B_PER];
+    bool b_live[B_PER];
+    p.make_col(kbeg + a_col, kend, col);
+#pragma unroll
+    for (int i = 0; i < B_PER; ++i) {
+        int e = tid + 256 * i;
+        int kk = e / BN, nn = e - kk * BN;
+        b_live[i] = e < BK * BN && n0 + nn < N;
+        bcur[i] = p.b_begin(kbeg + kk, b_live[i] ? n0 + nn : 0);
+    }
     auto gather = [&](int k0) {
-        typename P::Col col;
-        p.make_col(k0 + a_col, kend, col);
 #pragma unroll
         for (int i = 0; i < A_PER; ++i) {
             const typename P::Row &row = rows[a_rg + RG * i];
@@ -63,10 +73,12 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
         }
 #pragma unroll
         for (int i = 0; i < B_PER; ++i) {
-            int e = tid + 256 * i;
-            int kk = e / BN, nn = e - kk * BN;
-            b_reg[i] = (e < BK * BN && k0 + kk < kend && n0 + nn < N) ? p.b(k0 + kk, n0 + nn) : 0.f;
+            int kk = (tid + 256 * i) / BN;
+            b_reg[i] = (b_live[i] && k0 + kk < kend) ? __ldg(p.b_ptr(bcur[i])) : 0.f;
         }
+        p.next_col(k0 + BK + a_col, BK, kend, col);
+#pragma unroll
+        for (int i = 0; i < B_PER; ++i) p.b_next(bcur[i], BK);
     };
 
     if (kbeg < kend) gather(kbeg);

@@ -134,63 +134,75 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
     // to tile_offset(row, k).  The lanes of a warp sit on the axis along which the operand is contiguous in
     // global memory (coalesced); where four consecutive k are four consecutive channels the A operand moves
     // 16 bytes per copy.  Up to TC_STAGES-1 tiles are in flight per CTA.
+    // Tiles are issued in order, so the reduction-axis contexts are decoded once here and stepped by TC_BK per
+    // tile: the loop below has no integer divisions (they, not the copies, used to bound the kernel).
     const bool vec4 = P::kAContigK && p.vec4_ok();
-    auto issue = [&](int k0, int stage) {
+    constexpr int ACOLS = P::kAContigK ? 1 : 4;
+    typename P::Col acol[ACOLS];
+    const int a_koff = P::kAContigK ? (vec4 ? 4 * (lane & 7) : lane) : warp;
+#pragma unroll
+    for (int j = 0; j < ACOLS; ++j) p.make_col(kbeg + a_koff + 8 * j, kend, acol[j]);
+    typename P::BCursor bcur = P::kBContigK ? p.b_begin(kbeg + lane, n0 + warp) : p.b_begin(kbeg + warp, n0 + lane);
+    const long long b_step_n = p.b_stride_n(), b_step_k = p.b_stride_k();
+    int k_next = kbeg;
+    auto issue = [&](int stage) {
+        const int k0 = k_next;
         const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + TC_A_BYTES;
-        if (vec4) {
-            typename P::Col col;                            // lane = (row sub-index, 16-byte chunk); 4 passes of 32 rows
-            p.make_col(k0 + 4 * (lane & 7), kend, col);
+        if (vec4) {                                         // lane = (row sub-index, 16-byte chunk); 4 passes of 32 rows
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 int r = warp * 4 + (lane >> 3) + 32 * i;
-                const float *src = (col.valid && rows[r].valid) ? p.a_ptr(rows[r], col) : nullptr;
+                const float *src = (acol[0].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[0]) : nullptr;
                 cp_async16(sa + tile_offset(r, 4 * (lane & 7), layout), src ? src : p.any_ptr(), src ? 16u : 0u);
             }
         } else if (P::kAContigK) {
-            typename P::Col col;
-            p.make_col(k0 + lane, kend, col);
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
                 int r = warp + 8 * i;
-                const float *src = (col.valid && rows[r].valid) ? p.a_ptr(rows[r], col) : nullptr;
+                const float *src = (acol[0].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[0]) : nullptr;
                 cp_async4(sa + tile_offset(r, lane, layout), src ? src : p.any_ptr(), src ? 4u : 0u);
             }
         } else {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {                   // lanes along the rows: row = lane + 32*i, k = warp + 8*j
-                typename P::Col col;
-                p.make_col(k0 + warp + 8 * j, kend, col);
+            for (int j = 0; j < ACOLS; ++j) {               // lanes along the rows: row = lane + 32*i, k = warp + 8*j
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     int r = lane + 32 * i;
                     uint32_t dst = sa + tile_offset(r, warp + 8 * j, layout);
                     if (rows[r].valid == 2) {               // the all-ones row that yields the bias gradient
-                        float one = col.valid ? 1.f : 0.f;
+                        float one = acol[j].valid ? 1.f : 0.f;
                         asm volatile("st.shared.f32 [%0], %1;" ::"r"(dst), "f"(one) : "memory");
                     } else {
-                        const float *src = (col.valid && rows[r].valid) ? p.a_ptr(rows[r], col) : nullptr;
+                        const float *src = (acol[j].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[j]) : nullptr;
                         cp_async4(dst, src ? src : p.any_ptr(), src ? 4u : 0u);
                     }
                 }
             }
         }
+        const float *bsrc = p.b_ptr(bcur);
         if (P::kBContigK) {
+            const bool k_ok = k0 + lane < kend;
 #pragma unroll
             for (int i = 0; i < B_PER; ++i) {
-                int nn = warp + 8 * i, n = n0 + nn, k = k0 + lane;
-                bool ok = k < kend && n < N;
-                cp_async4(sb + tile_offset(nn, lane, layout), ok ? p.b_ptr(k, n) : p.any_ptr(), ok ? 4u : 0u);
+                int nn = warp + 8 * i;
+                bool ok = k_ok && n0 + nn < N;
+                cp_async4(sb + tile_offset(nn, lane, layout), ok ? bsrc + b_step_n * (8 * i) : p.any_ptr(), ok ? 4u : 0u);
             }
         } else {
 #pragma unroll
             for (int j = 0; j < 4; ++j)
 #pragma unroll
                 for (int i = 0; i < BN / 32; ++i) {         // lanes along n: n = lane + 32*i, k = warp + 8*j
-                    int nn = lane + 32 * i, n = n0 + nn, k = k0 + warp + 8 * j;
-                    bool ok = k < kend && n < N;
-                    cp_async4(sb + tile_offset(nn, warp + 8 * j, layout), ok ? p.b_ptr(k, n) : p.any_ptr(), ok ? 4u : 0u);
+                    int nn = lane + 32 * i;
+                    bool ok = k0 + warp + 8 * j < kend && n0 + nn < N;
+                    cp_async4(sb + tile_offset(nn, warp + 8 * j, layout), ok ? bsrc + b_step_k * (8 * j) + 32 * i : p.any_ptr(),
+                              ok ? 4u : 0u);
                 }
         }
+        k_next = k0 + TC_BK;
+#pragma unroll
+        for (int j = 0; j < ACOLS; ++j) p.next_col(k_next + a_koff + 8 * j, TC_BK, kend, acol[j]);
+        p.b_next(bcur, TC_BK);
     };
 
     // instruction descriptor: D fp32, A/B tf32, both K-major, N = n_tile, M = 128
@@ -200,7 +212,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
     const int KT = (kend - kbeg + TC_BK - 1) / TC_BK;
 #pragma unroll
     for (int t = 0; t < TC_STAGES - LAG; ++t) {            // prologue: tiles 0 .. STAGES-LAG-1 in flight
-        if (t < KT) issue(kbeg + t * TC_BK, t);
+        if (t < KT) issue(t);
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
     for (int kt = 0; kt < KT; ++kt) {
@@ -210,7 +222,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
         if (nt < KT) {
             const int ns = nt % TC_STAGES;
             if (kt >= LAG) mbar_wait(&empty_bar[ns], (uint32_t)(((kt - LAG) / TC_STAGES) & 1));
-            issue(kbeg + nt * TC_BK, ns);
+            issue(ns);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
         asm volatile("cp.async.wait_group %0;" ::"n"(TC_STAGES - LAG) : "memory"); // tile kt has landed (this thread's part)

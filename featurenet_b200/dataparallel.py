@@ -94,9 +94,7 @@ class DataParallelTrainer(object):
             need = max(eng._workspace_need(i, max(local, 1)) for i in range(len(eng.nodes)))
             if need > eng.ws_bytes:
                 eng.stream.synchronize()
-                with torch.cuda.device(eng.device):
-                    eng.ws = torch.empty(need, dtype=torch.uint8, device=eng.device)
-                eng.ws_bytes = need
+                eng._alloc_workspace(need)
                 for fb, op in self.graphs.values():
                     eng.lib.fnet_graph_destroy(fb)
                     eng.lib.fnet_graph_destroy(op)

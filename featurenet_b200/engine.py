@@ -69,6 +69,10 @@ class DeviceDataCache(object):
         cls._store.clear()
 
 
+class SideLabel(str):
+    """Label of a launch that runs on the engine's side stream (see Engine._backward_program)."""
+
+
 class Engine(object):
     def __init__(self, net, device=None, math_mode=None, seed=None):
         if not torch.cuda.is_available():
@@ -80,6 +84,11 @@ class Engine(object):
         self.math = fl.MATH[(math_mode or os.environ.get("FNET_PRECISION", "fp32")).lower()]
         self.stream = torch.cuda.Stream(device=self.device)
         self.sp = C.c_void_p(self.stream.cuda_stream)
+        # filter gradients run on a second stream, beside the data gradient of the same layer (both only read
+        # dz); inside a captured step this becomes a fork/join of the CUDA graph, see _backward_program
+        self.side = torch.cuda.Stream(device=self.device)
+        self.sp2 = C.c_void_p(self.side.cuda_stream)
+        self.overlap_wgrad = os.environ.get("FNET_NO_OVERLAP", "0") != "1"
         self.nodes = list(net.layers)
         self.index = {id(n): i for i, n in enumerate(self.nodes)}
         self.src = [[self.index[id(t.node)] for t in n.inputs] for n in self.nodes]
@@ -241,9 +250,15 @@ class Engine(object):
                     a = self.shape[i][node.cfg["axis"] - 1]
                     self.aux[i] = (f32(a), f32(a))
                 ws_bytes = max(ws_bytes, self._workspace_need(i, batch))
-            self.ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            self._alloc_workspace(ws_bytes)
             self.yb = f32(batch, self.n_out)
-        self.ws_bytes = ws_bytes
+
+    def _alloc_workspace(self, need):
+        """Two halves of `need` bytes: the main stream's scratch and the side stream's (they run concurrently)."""
+        need = -(-int(need) // 256) * 256
+        with torch.cuda.device(self.device):
+            self.ws = torch.empty(2 * need, dtype=torch.uint8, device=self.device)
+        self.ws_bytes = need
 
     def _workspace_need(self, i, batch):
         node, need = self.nodes[i], 0
@@ -393,6 +408,20 @@ class Engine(object):
         add = lambda label, fn, *args: ops.append((label, fn, args))
         need = self._needs_grad()
         written = set()
+        ws2 = C.c_void_p(self.ws.data_ptr() + self.ws_bytes)
+        forked = [False]
+
+        def add_wgrad(overlap, label, fn, *args):
+            """A filter-gradient launch (args end with ws, ws_bytes, stream).  With a data gradient to overlap
+            with, it goes to the side stream (own scratch half) behind a fork; _run_ops/_capture turn the fork
+            and the final join into event dependencies.  Nothing later in the step writes what it reads (the
+            layer's input activation and dz) or reads what it writes (the grads arena) before the join."""
+            if overlap and self.overlap_wgrad:
+                ops.append(("fork", None, ()))
+                ops.append((SideLabel(label), fn, args[:-3] + (ws2, wsb, self.sp2)))
+                forked[0] = True
+            else:
+                ops.append((label, fn, args))
 
         def acc_flag(j):
             """0 for the first gradient piece that reaches buffer j, 1 for the following ones."""
@@ -418,25 +447,25 @@ class Engine(object):
                     add("act_bwd", L.fnet_act_bwd, act, n_out // cols, cols, y, dy, dy, 0, sp)
             if kind == "conv2d":
                 d = self._conv_desc(i, batch)
-                add("conv2d_bwd_filter", L.fnet_conv2d_bwd_filter, d, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
+                add_wgrad(want_dx, "conv2d_bwd_filter", L.fnet_conv2d_bwd_filter, d, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
                 if want_dx:
                     add("conv2d_bwd_data", L.fnet_conv2d_bwd_data, d, dy, self._wp(i, 0), self._g(s0), acc_flag(s0), ws, wsb, sp)
             elif kind == "dwconv2d":
                 d = self._conv_desc(i, batch)
-                add("dwconv2d_bwd_filter", L.fnet_dwconv2d_bwd_filter, d, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
+                add_wgrad(want_dx, "dwconv2d_bwd_filter", L.fnet_dwconv2d_bwd_filter, d, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
                 if want_dx:
                     add("dwconv2d_bwd_data", L.fnet_dwconv2d_bwd_data, d, dy, self._wp(i, 0), self._g(s0), acc_flag(s0), sp)
             elif kind == "sepconv2d":
                 dw, pw = self._sep_descs(i, batch)
                 mid, gmid = (C.c_void_p(t.data_ptr()) for t in self.aux[i])
-                add("conv2d_bwd_filter", L.fnet_conv2d_bwd_filter, pw, mid, dy, gw(i, 1), gw(i, 2), ws, wsb, sp)
+                add_wgrad(True, "conv2d_bwd_filter", L.fnet_conv2d_bwd_filter, pw, mid, dy, gw(i, 1), gw(i, 2), ws, wsb, sp)
                 add("conv2d_bwd_data", L.fnet_conv2d_bwd_data, pw, dy, self._wp(i, 1), gmid, 0, ws, wsb, sp)
-                add("dwconv2d_bwd_filter", L.fnet_dwconv2d_bwd_filter, dw, x, gmid, gw(i, 0), None, ws, wsb, sp)
+                add_wgrad(want_dx, "dwconv2d_bwd_filter", L.fnet_dwconv2d_bwd_filter, dw, x, gmid, gw(i, 0), None, ws, wsb, sp)
                 if want_dx:
                     add("dwconv2d_bwd_data", L.fnet_dwconv2d_bwd_data, dw, gmid, self._wp(i, 0), self._g(s0), acc_flag(s0), sp)
             elif kind == "dense":
                 m, k, n = self._dense_mkn(i, batch)
-                add("dense_bwd_filter", L.fnet_dense_bwd_filter, m, k, n, self.math, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
+                add_wgrad(want_dx, "dense_bwd_filter", L.fnet_dense_bwd_filter, m, k, n, self.math, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
                 if want_dx:
                     add("dense_bwd_data", L.fnet_dense_bwd_data, m, k, n, self.math, dy, self._wp(i, 0), self._g(s0),
                         acc_flag(s0), ws, wsb, sp)
@@ -492,6 +521,8 @@ class Engine(object):
                 add("pad2d_bwd", L.fnet_pad2d_bwd, batch, h, w, c, cfg["pad"][0], cfg["pad"][1], dy, self._g(s0), acc_flag(s0), sp)
             else:
                 raise NotImplementedError(kind)
+        if forked[0]:
+            ops.append(("join", None, ()))
         return ops
 
     def _loss_op(self, batch, with_grad, scale_batch=None):
@@ -559,16 +590,44 @@ class Engine(object):
             ops.append(("step_end", L.fnet_step_end, (st, batch, sp)))
         return ops
 
+    def _fork(self):
+        """Everything enqueued so far on the main stream happens before what the side stream gets next."""
+        event = torch.cuda.Event()
+        event.record(self.stream)
+        self.side.wait_event(event)
+
+    def _join(self):
+        """What the side stream has been given happens before what the main stream gets next."""
+        event = torch.cuda.Event()
+        event.record(self.side)
+        self.stream.wait_event(event)
+
     def _run_ops(self, ops):
+        """Enqueue a launch list (eagerly, or into the capture that _capture opened)."""
         if self.timeline is None:
-            for _, fn, args in ops:
-                fn(*args)
+            for label, fn, args in ops:
+                if fn is not None:
+                    fn(*args)
+                elif label == "fork":
+                    self._fork()
+                else:
+                    self._join()
             return
+        # profiling: one event pair per launch, on the stream it runs on; side launches are serialised
+        # (fork, launch, join) so that every kernel is timed alone
         for label, fn, args in ops:
+            if fn is None:
+                continue
+            on_side = isinstance(label, SideLabel)
+            stream = self.side if on_side else self.stream
+            if on_side:
+                self._fork()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(self.stream)
+            e0.record(stream)
             fn(*args)
-            e1.record(self.stream)
+            e1.record(stream)
+            if on_side:
+                self._join()
             self.timeline.append((label, e0, e1))
 
     @staticmethod
@@ -641,7 +700,7 @@ class Engine(object):
             for _ in range(steps):
                 self._step(kind, batch)
             self.stream.synchronize()
-            ops = self.programs[(kind, batch)]
+            ops = [op for op in self.programs[(kind, batch)] if op[1] is not None]
             table = {}
             for n, (label, e0, e1) in enumerate(self.timeline):
                 row = table.setdefault(label, dict(launches=0, ms_total=0.0, flops=0, bytes=0))
@@ -669,12 +728,10 @@ class Engine(object):
             if need > self.ws_bytes:
                 self.stream.synchronize()
                 self._drop_graphs()                      # programs hold the old workspace pointer
-                with torch.cuda.device(self.device):
-                    self.ws = torch.empty(need, dtype=torch.uint8, device=self.device)
-                self.ws_bytes = need
+                self._alloc_workspace(need)
             ops = self.programs[key] = self._build_program(kind, batch)
             self.launches_per_step = getattr(self, "launches_per_step", {})
-            self.launches_per_step[key] = len(ops)
+            self.launches_per_step[key] = sum(1 for op in ops if op[1] is not None)
         if not self.use_graphs or self.timeline is not None:
             self._run_ops(ops)
             return
@@ -687,8 +744,7 @@ class Engine(object):
         """Record a launch list into a CUDA graph (nothing executes until the graph is launched)."""
         self.lib.fnet_graph_begin(self.sp)
         try:
-            for _, fn, args in ops:
-                fn(*args)
+            self._run_ops(ops)
         finally:
             handle = C.c_void_p()
             self.lib.fnet_graph_end(self.sp, C.byref(handle))

@@ -82,6 +82,9 @@ CONV_CASES = [
     ((1, 5, 5, 2), (7, 7), 4, (1, 1), "same", (1, 1), "relu"),          # mutated 7x7 kernel larger than the image
     ((2, 8, 8, 64), (3, 3), 96, (1, 1), "same", (1, 1), "relu"),        # wide layer
     ((130, 6, 6, 4), (3, 3), 16, (1, 1), "same", (1, 1), None),         # many rows, N=16 tile
+    ((16, 14, 14, 12), (5, 5), 120, (1, 1), "same", (1, 1), "tanh"),    # few in-channels: dgrad = dense GEMM + col2im
+    ((64, 32, 32, 8), (3, 3), 64, (2, 2), "same", (1, 1), "relu"),      # col2im dgrad with stride 2
+    ((48, 20, 20, 4), (3, 3), 100, (1, 1), "same", (2, 2), None),       # col2im dgrad with dilation 2
 ]
 
 
