@@ -19,7 +19,7 @@ int check_math(int math, const char *what) {
 int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
              void *ws, size_t ws_bytes, cudaStream_t s) {
     int rc;
-    if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, s);
+    if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
     else if (math != FNET_MATH_FP32 && tc_supported(g, math, 0)) rc = tc_conv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
     else rc = simt_conv_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
     if (rc == FNET_OK && act == FNET_ACT_SOFTMAX)
@@ -110,7 +110,7 @@ int fnet_conv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const floa
 size_t fnet_dense_workspace_bytes(int64_t m, int64_t k, int64_t n) {
     if (check_dense(m, k, n, "fnet_dense_workspace_bytes") != FNET_OK || m == 0) return 0;
     ConvGeom g = dense_geom(m, k, n);
-    return max_sz(simt_conv_workspace(g), tc_conv_workspace(g, FNET_MATH_TF32));
+    return max_sz(max_sz(simt_conv_workspace(g), skinny_workspace(g)), tc_conv_workspace(g, FNET_MATH_TF32));
 }
 
 int fnet_dense_fwd(int64_t m, int64_t k, int64_t n, int act, int math, const float *x, const float *w,

@@ -33,7 +33,11 @@ int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, 
 // direct kernels for the classifier head and for small-channel convolutions (skinny.cu); fp32, any math mode
 bool skinny_supported(const ConvGeom &g, int product, bool with_bias);
 size_t skinny_workspace(const ConvGeom &g);
-int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t s);
+int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, void *ws,
+               size_t ws_bytes, cudaStream_t s);
+// y = act(bias + sum of `splits` partial [M x N] products), fixed order (igemm_simt.cu)
+int simt_reduce_fwd_partials(const ConvGeom &g, int act, const float *bias, float *y, int splits, const float *partial,
+                             cudaStream_t stream);
 int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t s);
 int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
                  cudaStream_t s);

@@ -136,6 +136,8 @@ struct FwdProblem {
     static constexpr bool kAContigK = true;     // A(m, k): consecutive k = consecutive input channels
     static constexpr bool kBContigK = false;    // consecutive n
     __device__ bool vec4_ok() const { return (g.C & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }
+    __device__ bool a_rows_vec4_ok() const { return false; }
+    __device__ bool b_rows_vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0; }
     __device__ void make_row(int m, int M, Row &r) const { decode_out_pixel(g, m, M, r); }
     __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.C, kend, c); }
     __device__ void next_col(int k_new, int step, int kend, Col &c) const { step_tap(g, k_new, step, g.C, kend, c); }
@@ -151,6 +153,23 @@ struct FwdProblem {
     __device__ void store(int m, int n, float v) const {
         if (bias) v += __ldg(bias + n);
         y[(long long)m * g.K + n] = act_apply(v, act);
+    }
+    // rows m .. m+count-1 of column n; src[r * src_stride] holds row r.  Bias and the activation switch are
+    // taken out of the row loop (the tensor-core epilogue spends most of its instructions here).
+    __device__ void store_col(int m, int count, int n, const float *src, int src_stride) const {
+        const float bv = bias ? __ldg(bias + n) : 0.f;
+        float *q = y + (long long)m * g.K + n;
+        const long long ld = g.K;
+        if (act == FNET_ACT_NONE) {
+#pragma unroll 8
+            for (int r = 0; r < count; ++r) q[r * ld] = src[r * src_stride] + bv;
+        } else if (act == FNET_ACT_RELU) {
+#pragma unroll 8
+            for (int r = 0; r < count; ++r) q[r * ld] = fmaxf(src[r * src_stride] + bv, 0.f);
+        } else {
+#pragma unroll 4
+            for (int r = 0; r < count; ++r) q[r * ld] = act_apply(src[r * src_stride] + bv, act);
+        }
     }
 };
 
@@ -169,6 +188,8 @@ struct DgradProblem {
     static constexpr bool kAContigK = true;     // consecutive k = consecutive output channels of dz
     static constexpr bool kBContigK = true;     // consecutive ko
     __device__ bool vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(dz) & 15) == 0; }
+    __device__ bool a_rows_vec4_ok() const { return false; }
+    __device__ bool b_rows_vec4_ok() const { return false; }
     __device__ void make_row(int m, int M, Row &r) const { decode_in_pixel(g, m, M, r); }
     __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.K, kend, c); }
     __device__ void next_col(int k_new, int step, int kend, Col &c) const { step_tap(g, k_new, step, g.K, kend, c); }
@@ -195,6 +216,17 @@ struct DgradProblem {
         long long at = (long long)m * g.C + n;
         dx[at] = accumulate ? dx[at] + v : v;
     }
+    __device__ void store_col(int m, int count, int n, const float *src, int src_stride) const {
+        float *q = dx + (long long)m * g.C + n;
+        const long long ld = g.C;
+        if (accumulate) {
+#pragma unroll 8
+            for (int r = 0; r < count; ++r) q[r * ld] += src[r * src_stride];
+        } else {
+#pragma unroll 8
+            for (int r = 0; r < count; ++r) q[r * ld] = src[r * src_stride];
+        }
+    }
 };
 
 struct WgradProblem {
@@ -208,6 +240,9 @@ struct WgradProblem {
     static constexpr bool kAContigK = false;    // A(m, k) = x[pixel k][tap/channel m]: consecutive m (channels)
     static constexpr bool kBContigK = false;    // consecutive n
     __device__ bool vec4_ok() const { return false; }
+    // four consecutive rows = four consecutive channels of one tap; four consecutive columns of dz
+    __device__ bool a_rows_vec4_ok() const { return (g.C & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }
+    __device__ bool b_rows_vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(dz) & 15) == 0; }
     __device__ void make_row(int k, int M, Row &r) const {
         decode_tap(g, k, g.C, taps_c, r);
         if (k == taps_c && k < M) r.valid = 2;
@@ -226,6 +261,10 @@ struct WgradProblem {
     __device__ void store(int k, int n, float v) const {
         if (k < taps_c) dw[(long long)k * g.K + n] = v;
         else if (dbias) dbias[n] = v;
+    }
+    __device__ void store_col(int k, int count, int n, const float *src, int src_stride) const {
+#pragma unroll 4
+        for (int r = 0; r < count; ++r) store(k + r, n, src[r * src_stride]);
     }
 };
 

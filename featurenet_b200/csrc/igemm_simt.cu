@@ -285,6 +285,15 @@ int simt_conv_wgrad(const ConvGeom &g, const float *x, const float *dz, float *d
                        stream, "conv2d_bwd_filter");
 }
 
+int simt_reduce_fwd_partials(const ConvGeom &g, int act, const float *bias, float *y, int splits, const float *partial,
+                             cudaStream_t stream) {
+    FwdProblem p{g, nullptr, nullptr, bias, y, act};
+    long long M = (long long)g.B * g.Ho * g.Wo;
+    long long blocks = ceil_div<long long>(M * g.K, 8), cap = (long long)kNumSMs * 8;
+    reduce_splits_kernel<FwdProblem><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, (int)M, g.K, splits, partial);
+    return check_launch("reduce_partials");
+}
+
 int geom_checked(const fnet_conv2d_desc *d, ConvGeom &g, const char *what) { return geom_from_desc(d, g, what); }
 
 ConvGeom dense_geom(long long m, long long k, long long n) {

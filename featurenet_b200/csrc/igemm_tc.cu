@@ -80,6 +80,26 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, int layout) {
     return d;
 }
 
+// MN-major operands (the contiguous global axis is the tile's row axis, not k: the weights [k][n] of the forward
+// product, dz [pixel][n] and x [pixel][channel] of the filter gradient).  tcgen05 reads them in place when the
+// instruction descriptor says so, which lets 16 contiguous bytes of global memory stay 16 contiguous bytes of
+// shared memory instead of being scattered 4 bytes at a time into a K-major tile.  For 32-bit operands the only
+// MN-major layout is SWIZZLE_128B with 32-byte atomicity: atoms of 4 k-rows x 128 bytes (32 elements along MN),
+// the four 32-byte chunks of a row XOR-ed with k%4; atoms along MN are 512 bytes apart (leading byte offset),
+// atoms along K `atoms`*512 bytes apart (stride byte offset); one K=8 MMA reads two atoms along K.
+__device__ __forceinline__ uint32_t tile_offset_mn(int mn, int k, int atoms) {
+    return (uint32_t)(((k >> 2) * atoms + (mn >> 5)) * 512 + (k & 3) * 128 + (((((mn >> 3) & 3) ^ (k & 3)) << 5) | ((mn & 7) << 2)));
+}
+
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t saddr, int atoms) {
+    uint64_t d = (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(512 >> 4) << 16;                       // leading byte offset: next atom along MN
+    d |= (uint64_t)((atoms * 512) >> 4) << 32;             // stride byte offset: next atom along K
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)1 << 61;                                // SWIZZLE_128B_BASE32B
+    return d;
+}
+
 // cp.async (LDGSTS): global -> shared without passing through registers; bytes beyond src_bytes are zero-filled,
 // which is how padding, ragged tiles and out-of-range taps become zeros.
 __device__ __forceinline__ void cp_async4(uint32_t dst, const float *src, uint32_t src_bytes) {
@@ -136,40 +156,47 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
     // 16 bytes per copy.  Up to TC_STAGES-1 tiles are in flight per CTA.
     // Tiles are issued in order, so the reduction-axis contexts are decoded once here and stepped by TC_BK per
     // tile: the loop below has no integer divisions (they, not the copies, used to bound the kernel).
+    constexpr bool A_MN = !P::kAContigK, B_MN = !P::kBContigK;   // operand kept MN-major in shared memory
+    constexpr int B_ATOMS = BN / 32;
+    constexpr int B_CH = BN / 4;                            // 16-byte chunks per k-row of an MN-major B tile
+    constexpr int B_KPW = 32 / B_CH;                        // k-rows one warp covers per pass (1, 2, 4)
     const bool vec4 = P::kAContigK && p.vec4_ok();
+    const bool a_rows4 = A_MN && p.a_rows_vec4_ok();
+    const bool b_rows4 = B_MN && p.b_rows_vec4_ok();
     constexpr int ACOLS = P::kAContigK ? 1 : 4;
     typename P::Col acol[ACOLS];
     const int a_koff = P::kAContigK ? (vec4 ? 4 * (lane & 7) : lane) : warp;
 #pragma unroll
     for (int j = 0; j < ACOLS; ++j) p.make_col(kbeg + a_koff + 8 * j, kend, acol[j]);
-    typename P::BCursor bcur = P::kBContigK ? p.b_begin(kbeg + lane, n0 + warp) : p.b_begin(kbeg + warp, n0 + lane);
+    const int b_kl = warp * B_KPW + lane / B_CH, b_chunk = lane % B_CH;     // MN-major, 16-byte copies
+    typename P::BCursor bcur = P::kBContigK ? p.b_begin(kbeg + lane, n0 + warp)
+                               : (b_rows4 ? p.b_begin(kbeg + b_kl, n0 + 4 * b_chunk) : p.b_begin(kbeg + warp, n0 + lane));
     const long long b_step_n = p.b_stride_n(), b_step_k = p.b_stride_k();
     int k_next = kbeg;
     auto issue = [&](int stage) {
         const int k0 = k_next;
         const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + TC_A_BYTES;
-        if (vec4) {                                         // lane = (row sub-index, 16-byte chunk); 4 passes of 32 rows
+        if (a_rows4) {                                      // MN-major A, lane = 4 consecutive rows (channels of one tap)
+            const typename P::Row &row = rows[4 * lane];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                int r = warp * 4 + (lane >> 3) + 32 * i;
-                const float *src = (acol[0].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[0]) : nullptr;
-                cp_async16(sa + tile_offset(r, 4 * (lane & 7), layout), src ? src : p.any_ptr(), src ? 16u : 0u);
+            for (int j = 0; j < ACOLS; ++j) {
+                uint32_t dst = sa + tile_offset_mn(4 * lane, warp + 8 * j, 4);
+                if (row.valid == 2) {                       // the all-ones row that yields the bias gradient
+                    float one = acol[j].valid ? 1.f : 0.f;
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %2, %2};" ::"r"(dst), "f"(one), "f"(0.f) : "memory");
+                } else {
+                    const float *src = (acol[j].valid && row.valid) ? p.a_ptr(row, acol[j]) : nullptr;
+                    cp_async16(dst, src ? src : p.any_ptr(), src ? 16u : 0u);
+                }
             }
-        } else if (P::kAContigK) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                int r = warp + 8 * i;
-                const float *src = (acol[0].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[0]) : nullptr;
-                cp_async4(sa + tile_offset(r, lane, layout), src ? src : p.any_ptr(), src ? 4u : 0u);
-            }
-        } else {
+        } else if (A_MN) {
 #pragma unroll
             for (int j = 0; j < ACOLS; ++j) {               // lanes along the rows: row = lane + 32*i, k = warp + 8*j
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     int r = lane + 32 * i;
-                    uint32_t dst = sa + tile_offset(r, warp + 8 * j, layout);
-                    if (rows[r].valid == 2) {               // the all-ones row that yields the bias gradient
+                    uint32_t dst = sa + tile_offset_mn(r, warp + 8 * j, 4);
+                    if (rows[r].valid == 2) {
                         float one = acol[j].valid ? 1.f : 0.f;
                         asm volatile("st.shared.f32 [%0], %1;" ::"r"(dst), "f"(one) : "memory");
                     } else {
@@ -177,6 +204,20 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
                         cp_async4(dst, src ? src : p.any_ptr(), src ? 4u : 0u);
                     }
                 }
+            }
+        } else if (vec4) {                                  // lane = (row sub-index, 16-byte chunk); 4 passes of 32 rows
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                int r = warp * 4 + (lane >> 3) + 32 * i;
+                const float *src = (acol[0].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[0]) : nullptr;
+                cp_async16(sa + tile_offset(r, 4 * (lane & 7), layout), src ? src : p.any_ptr(), src ? 16u : 0u);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                int r = warp + 8 * i;
+                const float *src = (acol[0].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[0]) : nullptr;
+                cp_async4(sa + tile_offset(r, lane, layout), src ? src : p.any_ptr(), src ? 4u : 0u);
             }
         }
         const float *bsrc = p.b_ptr(bcur);
@@ -188,6 +229,15 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
                 bool ok = k_ok && n0 + nn < N;
                 cp_async4(sb + tile_offset(nn, lane, layout), ok ? bsrc + b_step_n * (8 * i) : p.any_ptr(), ok ? 4u : 0u);
             }
+        } else if (b_rows4) {                               // MN-major B: 16 bytes = 4 consecutive n of one k-row
+            const bool n_ok = n0 + 4 * b_chunk < N;
+#pragma unroll
+            for (int ps = 0; ps < 4 / B_KPW; ++ps) {
+                int kl = b_kl + ps * 8 * B_KPW;
+                bool ok = n_ok && k0 + kl < kend;
+                cp_async16(sb + tile_offset_mn(4 * b_chunk, kl, B_ATOMS), ok ? bsrc + b_step_k * (ps * 8 * B_KPW) : p.any_ptr(),
+                           ok ? 16u : 0u);
+            }
         } else {
 #pragma unroll
             for (int j = 0; j < 4; ++j)
@@ -195,7 +245,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
                 for (int i = 0; i < BN / 32; ++i) {         // lanes along n: n = lane + 32*i, k = warp + 8*j
                     int nn = lane + 32 * i;
                     bool ok = k0 + warp + 8 * j < kend && n0 + nn < N;
-                    cp_async4(sb + tile_offset(nn, warp + 8 * j, layout), ok ? bsrc + b_step_k * (8 * j) + 32 * i : p.any_ptr(),
+                    cp_async4(sb + tile_offset_mn(nn, warp + 8 * j, B_ATOMS), ok ? bsrc + b_step_k * (8 * j) + 32 * i : p.any_ptr(),
                               ok ? 4u : 0u);
                 }
         }
@@ -206,8 +256,12 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
     };
 
     // instruction descriptor: D fp32, A/B tf32, both K-major, N = n_tile, M = 128
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n_tile >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-    const int kadv = layout == 0 ? 2 : 16;                 // descriptor start-address step per 8 k (in 16-byte units)
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (A_MN ? (1u << 15) : 0u) | (B_MN ? (1u << 16) : 0u) |
+                           ((uint32_t)(n_tile >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+    // descriptor start-address step per 8 k, in 16-byte units: 32 bytes along a swizzled K-major row, one atom
+    // row (all MN atoms) of an MN-major tile
+    const int kadv = layout == 0 ? 2 : 16;
+    const int kadv_a = A_MN ? 4 * 64 : kadv, kadv_b = B_MN ? B_ATOMS * 64 : kadv;
 
     const int KT = (kend - kbeg + TC_BK - 1) / TC_BK;
 #pragma unroll
@@ -231,10 +285,11 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + TC_A_BYTES;
-            uint64_t da = make_smem_desc(sa, layout), db = make_smem_desc(sb, layout);
+            uint64_t da = A_MN ? make_smem_desc_mn(sa, 4) : make_smem_desc(sa, layout);
+            uint64_t db = B_MN ? make_smem_desc_mn(sb, B_ATOMS) : make_smem_desc(sb, layout);
 #pragma unroll
             for (int j = 0; j < TC_BK / 8; ++j)
-                tc_mma_tf32(tmem, da + (uint64_t)(j * kadv), db + (uint64_t)(j * kadv), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+                tc_mma_tf32(tmem, da + (uint64_t)(j * kadv_a), db + (uint64_t)(j * kadv_b), idesc, (kt > 0 || j > 0) ? 1u : 0u);
             tc_commit(&empty_bar[s]);                                   // arrives when these MMAs have read the stage
             if (kt == KT - 1) tc_commit(&done_bar);
         }
@@ -270,13 +325,14 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
         for (int j = 0; j < 32; ++j) xpose[lane * 33 + j] = __uint_as_float(v[j]);   // thread = row
         __syncwarp();
         const int n = n0 + c0 + lane;                                                   // thread = column
-        for (int r = 0; r < 32; ++r) {
-            int m = m0 + quad * 32 + r;
-            if (m >= M) break;
-            if (n < N) {
-                float val = xpose[r * 33 + lane];
-                if (partial) partial[((long long)blockIdx.z * M + m) * N + n] = val;
-                else p.store(m, n, val);
+        const int m_first = m0 + quad * 32, count = min(32, M - m_first);
+        if (n < N && count > 0) {
+            if (partial) {
+                float *q = partial + ((long long)blockIdx.z * M + m_first) * N + n;
+#pragma unroll 8
+                for (int r = 0; r < count; ++r) q[(long long)r * N] = xpose[r * 33 + lane];
+            } else {
+                p.store_col(m_first, count, n, xpose + lane, 33);
             }
         }
         __syncwarp();

@@ -125,7 +125,149 @@ __global__ void __launch_bounds__(256) dense_skinny_dgrad_kernel(int M, int K, i
     }
 }
 
+// ------------------------------------------------------------------ dense, N <= 16, streaming variants
+// The "keras" template flattens 32x32x512 activations into a 524 288-wide head: x is 268 MB per batch, and each
+// of the three products has to stream it (or dx) through the SMs exactly once while the 21 MB weight matrix is
+// read from DRAM once and reused out of shared memory / registers.  Lanes always sit on consecutive k, so every
+// x / dx access of a warp is one 128-byte line; dz (a few KB) is staged in shared memory, zero-padded to NMAX
+// columns, and read back as broadcast float4s.
+
+constexpr int kStreamMinK = 32768;      // heads at least this long take the streaming kernels
+constexpr int kStreamChunk = 512;       // weight rows staged per step of the forward kernel
+constexpr int kStreamRows = 64;         // samples per CTA of the forward kernel: 16 warps x 4 samples
+
+// forward: partial[b][m][n] = sum over the k-chunks CTA b walks of x[m][k] * w[k][n]
+template <int NMAX>
+__global__ void __launch_bounds__(512) dense_stream_fwd_kernel(int M, int K, int N, const float *__restrict__ x,
+                                                               const float *__restrict__ w, float *__restrict__ partial) {
+    __shared__ float w_s[kStreamChunk * (NMAX + 1)];          // odd row stride: conflict-free when lanes walk k
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int m0 = blockIdx.y * kStreamRows + warp * 4;
+    float acc[4][NMAX];
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) acc[s][n] = 0.f;
+    for (int i = threadIdx.x; i < kStreamChunk * (NMAX + 1); i += 512) w_s[i] = 0.f;   // padding columns stay zero
+    const float *xr[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) xr[s] = x + (long long)min(m0 + s, M - 1) * K;         // clamped rows are never stored
+    for (int kb = blockIdx.x * kStreamChunk; kb < K; kb += gridDim.x * kStreamChunk) {
+        const int kc = min(kStreamChunk, K - kb);
+        __syncthreads();
+        for (int i = threadIdx.x; i < kc * N; i += 512) {
+            int kk = i / N, n = i - kk * N;
+            w_s[kk * (NMAX + 1) + n] = __ldg(w + (long long)kb * N + i);
+        }
+        __syncthreads();
+#pragma unroll 2
+        for (int kk = lane; kk < kc; kk += 32) {
+            float xv[4];
+#pragma unroll
+            for (int s = 0; s < 4; ++s) xv[s] = __ldg(xr[s] + kb + kk);
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n) {
+                float wv = w_s[kk * (NMAX + 1) + n];
+#pragma unroll
+                for (int s = 0; s < 4; ++s) acc[s][n] = fmaf(xv[s], wv, acc[s][n]);
+            }
+        }
+    }
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) {
+            float v = warp_sum(acc[s][n]);
+            if (lane == 0 && m0 + s < M && n < N) partial[((long long)blockIdx.x * M + m0 + s) * N + n] = v;
+        }
+}
+
+// filter gradient: one thread per weight row k, all samples in sequence -- no cross-thread reduction at all
+template <int NMAX>
+__global__ void __launch_bounds__(256) dense_stream_wgrad_kernel(int M, int K, int N, const float *__restrict__ x,
+                                                                 const float *__restrict__ dz, float *__restrict__ dw,
+                                                                 float *__restrict__ dbias) {
+    constexpr int ROWS = 128;
+    __shared__ __align__(16) float dz_s[ROWS][NMAX];
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    const float *xk = x + min(k, K - 1);
+    float acc[NMAX];
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n) acc[n] = 0.f;
+    float bsum = 0.f;
+    for (int m0 = 0; m0 < M; m0 += ROWS) {
+        const int rows = min(ROWS, M - m0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < ROWS * NMAX; i += 256) {
+            int r = i / NMAX, n = i - r * NMAX;
+            dz_s[r][n] = (r < rows && n < N) ? __ldg(dz + (long long)(m0 + r) * N + n) : 0.f;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int r = 0; r < rows; ++r) {
+            float xv = __ldg(xk + (long long)(m0 + r) * K);
+#pragma unroll
+            for (int q = 0; q < NMAX / 4; ++q) {
+                float4 d = *reinterpret_cast<const float4 *>(&dz_s[r][4 * q]);
+                acc[4 * q] = fmaf(xv, d.x, acc[4 * q]);
+                acc[4 * q + 1] = fmaf(xv, d.y, acc[4 * q + 1]);
+                acc[4 * q + 2] = fmaf(xv, d.z, acc[4 * q + 2]);
+                acc[4 * q + 3] = fmaf(xv, d.w, acc[4 * q + 3]);
+            }
+        }
+        if (dbias && blockIdx.x == 0 && threadIdx.x < N)
+            for (int r = 0; r < rows; ++r) bsum += dz_s[r][threadIdx.x];
+    }
+    if (k < K) {
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n)
+            if (n < N) dw[(long long)k * N + n] = acc[n];
+    }
+    if (dbias && blockIdx.x == 0 && threadIdx.x < N) dbias[threadIdx.x] = bsum;
+}
+
+// data gradient (every K): a thread keeps its weight row in registers and walks the 16 samples of its CTA
+template <int NMAX>
+__global__ void __launch_bounds__(256) dense_rows_dgrad_kernel(int M, int K, int N, const float *__restrict__ dz,
+                                                               const float *__restrict__ w, float *__restrict__ dx,
+                                                               int accumulate) {
+    constexpr int ROWS = 16;
+    __shared__ __align__(16) float g_s[ROWS][NMAX];
+    const int m0 = blockIdx.y * ROWS, rows = min(ROWS, M - m0);
+    for (int i = threadIdx.x; i < ROWS * NMAX; i += 256) {
+        int r = i / NMAX, n = i - r * NMAX;
+        g_s[r][n] = (r < rows && n < N) ? __ldg(dz + (long long)(m0 + r) * N + n) : 0.f;
+    }
+    __syncthreads();
+    for (int k = blockIdx.x * 256 + threadIdx.x; k < K; k += gridDim.x * 256) {
+        float wr[NMAX];
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) wr[n] = n < N ? __ldg(w + (long long)k * N + n) : 0.f;
+        float *out = dx + (long long)m0 * K + k;
+#pragma unroll 4
+        for (int r = 0; r < rows; ++r) {
+            float v = 0.f;
+#pragma unroll
+            for (int q = 0; q < NMAX / 4; ++q) {
+                float4 d = *reinterpret_cast<const float4 *>(&g_s[r][4 * q]);
+                v = fmaf(d.x, wr[4 * q], v);
+                v = fmaf(d.y, wr[4 * q + 1], v);
+                v = fmaf(d.z, wr[4 * q + 2], v);
+                v = fmaf(d.w, wr[4 * q + 3], v);
+            }
+            out[(long long)r * K] = accumulate ? out[(long long)r * K] + v : v;
+        }
+    }
+}
+
 static bool is_dense_geom(const ConvGeom &g) { return g.H == 1 && g.W == 1 && g.kh == 1 && g.kw == 1 && g.Ho == 1 && g.Wo == 1; }
+
+static int stream_fwd_blocks(const ConvGeom &g) {
+    long long chunks = ceil_div<long long>(g.C, kStreamChunk);
+    long long per_row_group = 2LL * kNumSMs / ceil_div<long long>(g.B, kStreamRows);
+    long long b = chunks < per_row_group ? chunks : per_row_group;
+    return (int)(b < 1 ? 1 : b);
+}
 
 // ------------------------------------------------------------------ small-channel convolutions
 // forward: one thread per output pixel, all out channels (<= NMAX) in registers
@@ -316,7 +458,8 @@ bool skinny_supported(const ConvGeom &g, int product, bool with_bias) {
 }
 
 size_t skinny_workspace(const ConvGeom &g) {
-    if (is_dense_geom(g)) return 0;
+    if (is_dense_geom(g))
+        return (skinny_supported(g, 0, true) && g.C >= kStreamMinK) ? (size_t)stream_fwd_blocks(g) * g.B * g.K * sizeof(float) : 0;
     if (small_wgrad_ok(g, true)) return (size_t)kWgradBlocks * kWgradRegs * sizeof(float);
     return 0;
 }
@@ -327,8 +470,32 @@ static int pixel_grid(long long pixels) {
     return (int)(blocks > cap ? cap : (blocks < 1 ? 1 : blocks));
 }
 
-int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t s) {
+#define FNET_BY_COLUMNS(N_, CALL)                 \
+    do {                                          \
+        if ((N_) <= 4) { CALL(4); }               \
+        else if ((N_) <= 8) { CALL(8); }          \
+        else if ((N_) <= 12) { CALL(12); }        \
+        else { CALL(16); }                        \
+    } while (0)
+
+int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, void *ws,
+               size_t ws_bytes, cudaStream_t s) {
     if (act == FNET_ACT_SOFTMAX) act = FNET_ACT_NONE;      // the caller runs the softmax pass
+    if (is_dense_geom(g) && g.C >= kStreamMinK) {
+        int blocks = stream_fwd_blocks(g);
+        size_t need = (size_t)blocks * g.B * g.K * sizeof(float);
+        if (!ws || ws_bytes < need) {
+            set_error("dense_fwd[stream]: workspace of %zu bytes needed, %zu given", need, ws_bytes);
+            return FNET_ERR_WORKSPACE;
+        }
+        float *partial = reinterpret_cast<float *>(ws);
+        dim3 grid(blocks, (unsigned)ceil_div<long long>(g.B, kStreamRows));
+#define FNET_CALL(NM) dense_stream_fwd_kernel<NM><<<grid, 512, 0, s>>>(g.B, g.C, g.K, x, w, partial)
+        FNET_BY_COLUMNS(g.K, FNET_CALL);
+#undef FNET_CALL
+        int rc = check_launch("dense_fwd[stream]");
+        return rc ? rc : simt_reduce_fwd_partials(g, act, bias, y, blocks, partial, s);
+    }
     if (is_dense_geom(g)) {
         dense_skinny_fwd_kernel<kSkinnyN><<<g.B, 1024, 0, s>>>(g.C, g.K, act, x, w, bias, y);
         return check_launch("dense_fwd[skinny]");
@@ -342,9 +509,12 @@ int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const
 
 int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t s) {
     if (is_dense_geom(g)) {
-        int bx = (int)ceil_div<long long>(g.C, 256);
-        if (bx > 64) bx = 64;
-        dense_skinny_dgrad_kernel<kSkinnyN><<<dim3(bx, g.B), 256, 0, s>>>(g.B, g.C, g.K, dz, w, dx, accumulate);
+        long long bx = ceil_div<long long>(g.C, 256);
+        if (bx > 4096) bx = 4096;
+        dim3 grid((unsigned)bx, (unsigned)ceil_div<long long>(g.B, 16));
+#define FNET_CALL(NM) dense_rows_dgrad_kernel<NM><<<grid, 256, 0, s>>>(g.B, g.C, g.K, dz, w, dx, accumulate)
+        FNET_BY_COLUMNS(g.K, FNET_CALL);
+#undef FNET_CALL
         return check_launch("dense_bwd_data[skinny]");
     }
     size_t smem = (size_t)g.kh * g.kw * g.C * g.K * sizeof(float);
@@ -356,6 +526,13 @@ int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, 
 
 int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
                  cudaStream_t s) {
+    if (is_dense_geom(g) && g.C >= kStreamMinK) {
+        unsigned blocks = (unsigned)ceil_div<long long>(g.C, 256);
+#define FNET_CALL(NM) dense_stream_wgrad_kernel<NM><<<blocks, 256, 0, s>>>(g.B, g.C, g.K, x, dz, dw, dbias)
+        FNET_BY_COLUMNS(g.K, FNET_CALL);
+#undef FNET_CALL
+        return check_launch("dense_bwd_filter[stream]");
+    }
     if (is_dense_geom(g)) {
         size_t smem = (size_t)256 * g.K * sizeof(float);
         dense_skinny_wgrad_kernel<kSkinnyN><<<(unsigned)ceil_div<long long>(g.C, 32), 256, smem, s>>>(g.B, g.C, g.K, x, dz,

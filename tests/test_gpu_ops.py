@@ -139,7 +139,9 @@ def test_conv2d_softmax_activation_and_no_bias(L):
 
 DENSE_CASES = [(128, 16464, 10, "softmax"),      # lenet5 head: split-K forward, wide wgrad
                (1568, 120, 84, "tanh"),          # Dense applied to a rank-4 tensor (rows = B*H*W)
-               (64, 64, 512, "relu"), (7, 5, 3, None), (1, 1, 1, "sigmoid"), (300, 33, 17, None)]
+               (64, 64, 512, "relu"), (7, 5, 3, None), (1, 1, 1, "sigmoid"), (300, 33, 17, None),
+               (70, 40001, 10, "softmax"),       # long head (keras template class): streaming kernels, ragged K and rows
+               (5, 33000, 3, None), (130, 32768, 16, "tanh")]
 
 
 @pytest.mark.parametrize("m,k,n,act", DENSE_CASES)
