@@ -4,10 +4,10 @@
 // thread as four tcgen05.mma.kind::tf32 (K = 8 each).  The operands are gathered by all 256
 // threads straight from the NHWC tensors (implicit im2col, any channel count, any stride or
 // padding -- FeatureNet's channel counts are rarely multiples of 4, which rules out TMA's
-// 16-byte global strides) into shared memory in the canonical K-major SWIZZLE_128B layout,
-// rounded to tf32, three stages deep: while the tensor core multiplies stage s the threads fill
-// stage s+1 from registers and have the loads of stage s+2 in flight.  Completion of the MMAs
-// that read a stage is tracked with tcgen05.commit -> mbarrier, the accumulator never leaves
+// 16-byte global strides) with cp.async into shared memory in the canonical layouts (K-major
+// SWIZZLE_128B for im2col rows, MN-major SWIZZLE_128B_BASE32B for row-major weights / dz / x),
+// three or four stages deep.  The tensor core truncates the fp32 bits to tf32.  Completion of the
+// MMAs that read a stage is tracked with tcgen05.commit -> mbarrier, the accumulator never leaves
 // TMEM until the epilogue (tcgen05.ld, bias + activation, store).
 //
 // The same "problem" types as the FFMA kernels describe forward, data gradient and filter
@@ -173,11 +173,22 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
                                : (b_rows4 ? p.b_begin(kbeg + b_kl, n0 + 4 * b_chunk) : p.b_begin(kbeg + warp, n0 + lane));
     const long long b_step_n = p.b_stride_n(), b_step_k = p.b_stride_k();
     int k_next = kbeg;
+    // the row contexts a thread gathers for stay in registers (the copies below clobber memory, so shared-memory
+    // reads would be repeated for every k-row, with bank conflicts on the strided ones)
+    typename P::Row myrow[4];
+    if (a_rows4) myrow[0] = rows[4 * lane];
+    else if (A_MN) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) myrow[i] = rows[lane + 32 * i];
+    } else if (vec4) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) myrow[i] = rows[warp * 4 + (lane >> 3) + 32 * i];
+    }
     auto issue = [&](int stage) {
         const int k0 = k_next;
         const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + TC_A_BYTES;
         if (a_rows4) {                                      // MN-major A, lane = 4 consecutive rows (channels of one tap)
-            const typename P::Row &row = rows[4 * lane];
+            const typename P::Row &row = myrow[0];
 #pragma unroll
             for (int j = 0; j < ACOLS; ++j) {
                 uint32_t dst = sa + tile_offset_mn(4 * lane, warp + 8 * j, 4);
@@ -196,11 +207,11 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
                 for (int i = 0; i < 4; ++i) {
                     int r = lane + 32 * i;
                     uint32_t dst = sa + tile_offset_mn(r, warp + 8 * j, 4);
-                    if (rows[r].valid == 2) {
+                    if (myrow[i].valid == 2) {
                         float one = acol[j].valid ? 1.f : 0.f;
                         asm volatile("st.shared.f32 [%0], %1;" ::"r"(dst), "f"(one) : "memory");
                     } else {
-                        const float *src = (acol[j].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[j]) : nullptr;
+                        const float *src = (acol[j].valid && myrow[i].valid) ? p.a_ptr(myrow[i], acol[j]) : nullptr;
                         cp_async4(dst, src ? src : p.any_ptr(), src ? 4u : 0u);
                     }
                 }
@@ -209,7 +220,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 int r = warp * 4 + (lane >> 3) + 32 * i;
-                const float *src = (acol[0].valid && rows[r].valid) ? p.a_ptr(rows[r], acol[0]) : nullptr;
+                const float *src = (acol[0].valid && myrow[i].valid) ? p.a_ptr(myrow[i], acol[0]) : nullptr;
                 cp_async16(sa + tile_offset(r, 4 * (lane & 7), layout), src ? src : p.any_ptr(), src ? 16u : 0u);
             }
         } else {
@@ -370,11 +381,14 @@ static TcPlan tc_plan(long long M, long long N, long long Kg) {
     TcPlan t;
     t.bn = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
     long long tiles = ceil_div<long long>(M, TC_BM) * ceil_div<long long>(N, t.bn);
+    // Two CTAs are resident per SM (shared memory: 3 stages of a 128-wide tile or 4 stages of a narrower one
+    // are ~97 KB).  When the output has fewer tiles than that one wave, the reduction axis is split so that the
+    // grid is exactly one wave: never a few CTAs more, which would cost a whole extra pass over the k-tiles.
+    const long long slots = 2LL * kNumSMs;
     long long splits = 1;
-    if (tiles < 4 * kNumSMs && Kg >= 16 * TC_BK) {
-        // a CTA walks its k-tiles serially (~1 us each): keep at least ~4 CTAs per SM busy
-        splits = ceil_div<long long>(4 * kNumSMs, tiles);
-        long long most = Kg / (8 * TC_BK);
+    if (tiles < slots && Kg >= 16 * TC_BK) {
+        splits = slots / tiles;
+        long long most = Kg / (8 * TC_BK);        // at least 8 k-tiles per CTA
         if (splits > most) splits = most;
         if (splits < 1) splits = 1;
     }
@@ -382,7 +396,7 @@ static TcPlan tc_plan(long long M, long long N, long long Kg) {
     t.k_per_split = (int)per;
     t.splits = (int)ceil_div<long long>(Kg, per);
     t.ws_bytes = t.splits > 1 ? (size_t)t.splits * M * N * sizeof(float) : 0;
-    t.stages = per >= 8 * TC_BK ? 4 : 3;          // long reductions: deeper pipeline; short ones: more CTAs per SM
+    t.stages = (per >= 8 * TC_BK && t.bn < 128) ? 4 : 3;   // long reductions: deeper pipeline where it still fits twice
     t.smem_bytes = (size_t)t.stages * (TC_A_BYTES + t.bn * TC_BK * 4) + 1024;
     return t;
 }
