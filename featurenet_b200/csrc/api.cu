@@ -190,6 +190,22 @@ int fnet_graph_launch(void *graph_exec, void *stream) {
     return FNET_OK;
 }
 
+int fnet_graph_step_fed(void *graph_exec, void *x_dev, const void *x_host, size_t x_bytes, void *y_dev,
+                        const void *y_host, size_t y_bytes, const void *result_dev, void *result_host,
+                        size_t result_bytes, void *stream) {
+    FNET_REQUIRE(graph_exec != nullptr, "fnet_graph_step_fed: null graph");
+    FNET_REQUIRE((x_host == nullptr || x_dev != nullptr) && (y_host == nullptr || y_dev != nullptr),
+                 "fnet_graph_step_fed: host source without a device destination");
+    FNET_REQUIRE(result_bytes == 0 || (result_dev != nullptr && result_host != nullptr), "fnet_graph_step_fed: null result buffer");
+    cudaStream_t s = as_stream(stream);
+    if (x_host && x_bytes) FNET_CUDA(cudaMemcpyAsync(x_dev, x_host, x_bytes, cudaMemcpyHostToDevice, s));
+    if (y_host && y_bytes) FNET_CUDA(cudaMemcpyAsync(y_dev, y_host, y_bytes, cudaMemcpyHostToDevice, s));
+    FNET_CUDA(cudaGraphLaunch(reinterpret_cast<cudaGraphExec_t>(graph_exec), s));
+    if (result_bytes) FNET_CUDA(cudaMemcpyAsync(result_host, result_dev, result_bytes, cudaMemcpyDeviceToHost, s));
+    FNET_CUDA(cudaStreamSynchronize(s));
+    return FNET_OK;
+}
+
 int fnet_graph_destroy(void *graph_exec) {
     if (graph_exec) FNET_CUDA(cudaGraphExecDestroy(reinterpret_cast<cudaGraphExec_t>(graph_exec)));
     return FNET_OK;

@@ -31,20 +31,37 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
     constexpr int B_PER = (BK * BN + 255) / 256; // B elements per thread per tile
     constexpr int PAD = TM == 1 ? 1 : (TM == 2 ? 2 : 4);
     static_assert(BM % RG == 0, "loader shape");
+    // Lanes of a warp sit on the axis along which an operand is contiguous in global memory.  A: along k
+    // (channels of an im2col row) for forward / data gradient, along the rows (channels of x) for the filter
+    // gradient; B: along n for row-major weights / dz, along k for the data gradient's w[tap][c][ko].
+    constexpr bool A_ROWS = !P::kAContigK;
+    constexpr bool B_KLANES = P::kBContigK;
+    constexpr int KG = BM >= 256 ? 1 : 256 / BM;  // k-groups of the row-wise A loader
+    static_assert(!A_ROWS || (BK % KG == 0 && BK / KG == A_PER), "row-wise loader shape");
     __shared__ __align__(16) float As[BK][BM + PAD];
     __shared__ __align__(16) float Bs[BK][BN + 4];
-    __shared__ typename P::Row rows[BM];
+    __shared__ typename P::Row rows[A_ROWS ? 1 : BM];
+    __shared__ typename P::Col cols[A_ROWS ? 2 : 1][A_ROWS ? BK : 1];   // per-tile k contexts, double-buffered
 
     const int tid = threadIdx.x;
     const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
     const int kbeg = blockIdx.z * k_per_split;
     const int kend = min(Kg, kbeg + k_per_split);
 
-    for (int i = tid; i < BM; i += 256) p.make_row(m0 + i, M, rows[i]);
+    // column context and B cursors are decoded once and then stepped from tile to tile (no divisions)
+    typename P::Col col;
+    typename P::Row myrow;
+    const int a_col = A_ROWS ? 0 : tid % BK, a_rg = A_ROWS ? 0 : tid / BK;
+    if constexpr (A_ROWS) {
+        p.make_row(m0 + tid % BM, M, myrow);
+        if (tid < BK) { p.make_col(kbeg + tid, kend, col); cols[0][tid] = col; }
+    } else {
+        for (int i = tid; i < BM; i += 256) p.make_row(m0 + i, M, rows[i]);
+        p.make_col(kbeg + a_col, kend, col);
+    }
     __syncthreads();
 
     const int tx = tid % (BN / TN), ty = tid / (BN / TN);
-    const int a_col = tid % BK, a_rg = tid / BK;
 
     float acc[TM][TN];
 #pragma unroll
@@ -52,44 +69,53 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
 
-    // column context and B cursors are decoded once and then stepped from tile to tile (no divisions)
     float a_reg[A_PER], b_reg[B_PER];
-    typename P::Col col;
     typename P::BCursor bcur[B_PER];
     bool b_live[B_PER];
-    p.make_col(kbeg + a_col, kend, col);
+    auto b_kk = [&](int i) { int e = tid + 256 * i; return B_KLANES ? e % BK : e / BN; };
+    auto b_nn = [&](int i) { int e = tid + 256 * i; return B_KLANES ? e / BK : e % BN; };
 #pragma unroll
     for (int i = 0; i < B_PER; ++i) {
-        int e = tid + 256 * i;
-        int kk = e / BN, nn = e - kk * BN;
-        b_live[i] = e < BK * BN && n0 + nn < N;
-        bcur[i] = p.b_begin(kbeg + kk, b_live[i] ? n0 + nn : 0);
+        b_live[i] = tid + 256 * i < BK * BN && n0 + b_nn(i) < N;
+        bcur[i] = p.b_begin(kbeg + b_kk(i), b_live[i] ? n0 + b_nn(i) : 0);
     }
+    int parity = 0;
     auto gather = [&](int k0) {
+        if constexpr (A_ROWS) {
 #pragma unroll
-        for (int i = 0; i < A_PER; ++i) {
-            const typename P::Row &row = rows[a_rg + RG * i];
-            a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+            for (int i = 0; i < A_PER; ++i) {
+                const typename P::Col &c = cols[parity][tid / BM + KG * i];
+                a_reg[i] = (c.valid && myrow.valid) ? p.a(myrow, c) : 0.f;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < A_PER; ++i) {
+                const typename P::Row &row = rows[a_rg + RG * i];
+                a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+            }
+            p.next_col(k0 + BK + a_col, BK, kend, col);
         }
 #pragma unroll
-        for (int i = 0; i < B_PER; ++i) {
-            int kk = (tid + 256 * i) / BN;
-            b_reg[i] = (b_live[i] && k0 + kk < kend) ? __ldg(p.b_ptr(bcur[i])) : 0.f;
-        }
-        p.next_col(k0 + BK + a_col, BK, kend, col);
+        for (int i = 0; i < B_PER; ++i)
+            b_reg[i] = (b_live[i] && k0 + b_kk(i) < kend) ? __ldg(p.b_ptr(bcur[i])) : 0.f;
 #pragma unroll
         for (int i = 0; i < B_PER; ++i) p.b_next(bcur[i], BK);
     };
 
     if (kbeg < kend) gather(kbeg);
     for (int k0 = kbeg; k0 < kend; k0 += BK) {
+        if constexpr (A_ROWS) {
 #pragma unroll
-        for (int i = 0; i < A_PER; ++i) As[a_col][a_rg + RG * i] = a_reg[i];
+            for (int i = 0; i < A_PER; ++i) As[tid / BM + KG * i][tid % BM] = a_reg[i];
+            parity ^= 1;                              // contexts of the next tile, read after the barrier
+            if (tid < BK) { p.next_col(k0 + BK + tid, BK, kend, col); cols[parity][tid] = col; }
+        } else {
 #pragma unroll
-        for (int i = 0; i < B_PER; ++i) {
-            int e = tid + 256 * i;
-            if (e < BK * BN) Bs[e / BN][e % BN] = b_reg[i];
+            for (int i = 0; i < A_PER; ++i) As[a_col][a_rg + RG * i] = a_reg[i];
         }
+#pragma unroll
+        for (int i = 0; i < B_PER; ++i)
+            if (tid + 256 * i < BK * BN) Bs[b_kk(i)][b_nn(i)] = b_reg[i];
         __syncthreads();
         if (k0 + BK < kend) gather(k0 + BK);      // in flight while this tile is multiplied
 #pragma unroll
@@ -259,7 +285,9 @@ size_t simt_conv_workspace(const ConvGeom &g) {
     long long taps = (long long)g.kh * g.kw;
     size_t a = plan_for(mo, g.K, taps * g.C).ws_bytes;
     size_t b = plan_for(mi, g.C, taps * g.K).ws_bytes;
-    size_t c = plan_for(taps * g.C + 1, g.K, mo).ws_bytes;
+    size_t c = plan_for(taps * g.C + 1, g.K, mo).ws_bytes;       // with the bias row ...
+    size_t c0 = plan_for(taps * g.C, g.K, mo).ws_bytes;          // ... and without (dbias == nullptr)
+    if (c0 > c) c = c0;
     return a > b ? (a > c ? a : c) : (b > c ? b : c);
 }
 

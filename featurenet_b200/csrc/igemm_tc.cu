@@ -471,7 +471,11 @@ size_t tc_conv_workspace(const ConvGeom &g, int math) {
     size_t need = 0;
     if (tc_supported(g, math, 0)) need = tc_plan(mo, g.K, taps * g.C).ws_bytes;
     if (tc_supported(g, math, 1)) { size_t b = tc_plan(mi, g.C, taps * g.K).ws_bytes; need = b > need ? b : need; }
-    if (tc_supported(g, math, 2)) { size_t c = tc_plan(taps * g.C + 1, g.K, mo).ws_bytes; need = c > need ? c : need; }
+    if (tc_supported(g, math, 2)) {
+        size_t c = tc_plan(taps * g.C + 1, g.K, mo).ws_bytes, c0 = tc_plan(taps * g.C, g.K, mo).ws_bytes;   // with / without bias row
+        c = c0 > c ? c0 : c;
+        need = c > need ? c : need;
+    }
     return need;
 }
 

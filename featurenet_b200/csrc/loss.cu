@@ -161,6 +161,79 @@ __global__ void __launch_bounds__(256) softmax_cce_kernel(int batch, int classes
     }
 }
 
+// The same computation with G lanes per row (G = 16 or 32 >= classes): every exp / log / divide chain is one
+// element long and the row sums are shuffle trees, so the launch costs about one dependent chain instead of
+// `classes` of them -- this kernel sits on the critical path of every training step.  One CTA (fixed-order
+// loss reduction), rows are processed blockDim/G at a time.
+template <int G>
+__device__ __forceinline__ float group_sum(float v) {
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <int G>
+__device__ __forceinline__ int group_argmax(float v, int idx) {      // first index on ties
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, v, o);
+        int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+    }
+    return idx;
+}
+
+template <int G>
+__global__ void __launch_bounds__(1024) softmax_cce_group_kernel(int batch, int classes, const float *input /* may alias probs_out */,
+                                                                  const float *__restrict__ targets, float scale,
+                                                                  int from_logits, float *probs_out, float *__restrict__ dlogits,
+                                                                  double *__restrict__ loss_sum, long long *__restrict__ correct) {
+    __shared__ double group_loss[1024 / G];
+    __shared__ int group_correct[1024 / G];
+    const int c = threadIdx.x % G, group = threadIdx.x / G, groups = blockDim.x / G;
+    double my_loss = 0.0;
+    int my_correct = 0;
+    for (int row0 = 0; row0 < batch; row0 += groups) {               // same trip count for every thread (shuffles)
+        const int row = row0 + group;
+        const bool live = row < batch && c < classes;
+        const int64_t at = (int64_t)row * classes + c;
+        const float xin = live ? input[at] : 0.f;
+        const float tv = live ? __ldg(targets + at) : 0.f;
+        float p = xin;
+        if (from_logits) {
+            float mx = live ? xin : -INFINITY;
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            float e = live ? expf(xin - mx) : 0.f;
+            p = e / group_sum<G>(e);
+            if (live) probs_out[at] = p;
+        }
+        const float sum = group_sum<G>(p);
+        const int ip = group_argmax<G>(live ? p : -INFINITY, c);
+        const int it = group_argmax<G>(live ? tv : -INFINITY, c);
+        const float q = p / sum;
+        const float cl = fminf(fmaxf(q, kClipEps), 1.f - kClipEps);
+        const float loss = group_sum<G>(live ? -tv * logf(cl) : 0.f);
+        const float g = (live && q >= kClipEps && q <= 1.f - kClipEps) ? -tv / cl : 0.f;
+        const float dot = group_sum<G>(g * q);
+        if (dlogits) {
+            const float dp = (g - dot) / sum;                        // dL/dp through the renormalisation
+            const float dot2 = group_sum<G>(live ? dp * p : 0.f);    // softmax backward
+            if (live) dlogits[at] = scale * p * (dp - dot2);
+        }
+        if (c == 0 && row < batch) { my_loss += (double)loss; my_correct += ip == it ? 1 : 0; }
+    }
+    if (c == 0) { group_loss[group] = my_loss; group_correct[group] = my_correct; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double l = 0.0;
+        int k = 0;
+        for (int i = 0; i < groups; ++i) { l += group_loss[i]; k += group_correct[i]; }     // fixed order
+        if (loss_sum) *loss_sum += l;
+        if (correct) *correct += (long long)k;
+    }
+}
+
 }  // namespace fnet
 
 using namespace fnet;
@@ -172,6 +245,20 @@ extern "C" int fnet_softmax_cce(int32_t batch, int32_t classes, const float *inp
     FNET_REQUIRE(!from_logits || probs_out != nullptr, "fnet_softmax_cce: from_logits needs a place for the probabilities");
     FNET_REQUIRE(dlogits == nullptr || dlogits != probs_out, "fnet_softmax_cce: dlogits must not alias the probabilities");
     if (batch == 0) return FNET_OK;
+    if (classes <= 32) {
+        const int lanes = classes <= 16 ? 16 : 32;
+        long long want = (long long)batch * lanes;
+        int threads = want >= 1024 ? 1024 : (int)((want + 31) / 32) * 32;
+        if (lanes == 16)
+            softmax_cce_group_kernel<16><<<1, threads, 0, as_stream(stream)>>>(batch, classes, input, targets, scale, from_logits,
+                                                                               probs_out, dlogits, loss_sum,
+                                                                               reinterpret_cast<long long *>(correct));
+        else
+            softmax_cce_group_kernel<32><<<1, threads, 0, as_stream(stream)>>>(batch, classes, input, targets, scale, from_logits,
+                                                                               probs_out, dlogits, loss_sum,
+                                                                               reinterpret_cast<long long *>(correct));
+        return check_launch("fnet_softmax_cce");
+    }
     int threads = batch >= 256 ? 256 : ((batch + 31) / 32) * 32;
     softmax_cce_kernel<<<1, threads, 0, as_stream(stream)>>>(batch, classes, input, targets, scale, from_logits, probs_out,
                                                              dlogits, loss_sum, reinterpret_cast<long long *>(correct));

@@ -114,6 +114,7 @@ class Engine(object):
             self.loss_sum = self.metrics[0:1].view(torch.float64)
             self.correct = self.metrics[1:2]
             self._metrics_host = torch.zeros(2, dtype=torch.int64).pin_memory()
+            self._metrics_np = self._metrics_host.numpy()      # same pinned memory, cheap to read from Python
             self._metrics_seen = (0.0, 0)
             self._lr_host = torch.zeros(1, dtype=torch.float32).pin_memory()
         self._lr_on_device = None
@@ -850,12 +851,21 @@ class Engine(object):
         self._sync_lr()
         xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
         yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
-        with torch.cuda.stream(self.stream):
-            self.act[0][:b].copy_(xt, non_blocking=True)
-            self.yb[:b].copy_(yt, non_blocking=True)
-        self._step("train_fed", b)
+        graph = self.graphs.get(("train_fed", b)) if (self.use_graphs and self.timeline is None) else None
+        if graph is not None and xt.dtype == torch.float32 and yt.dtype == torch.float32 and xt.is_contiguous() \
+                and yt.is_contiguous() and not xt.is_cuda and not yt.is_cuda:
+            # steady state: both copies, the captured step, the 16-byte result read and the wait in ONE C call
+            self.lib.fnet_graph_step_fed(graph, self.act[0].data_ptr(), xt.data_ptr(), xt.numel() * 4, self.yb.data_ptr(),
+                                         yt.data_ptr(), yt.numel() * 4, self.metrics.data_ptr(),
+                                         self._metrics_host.data_ptr(), 16, self.sp)
+            loss_sum, correct = float(self._metrics_np.view(np.float64)[0]), int(self._metrics_np[1])
+        else:
+            with torch.cuda.stream(self.stream):
+                self.act[0][:b].copy_(xt, non_blocking=True)
+                self.yb[:b].copy_(yt, non_blocking=True)
+            self._step("train_fed", b)
+            loss_sum, correct = self._fetch_metrics()
         # the device accumulators keep running (no per-step zeroing launches); this step = the difference
-        loss_sum, correct = self._fetch_metrics()
         seen_loss, seen_correct = self._metrics_seen
         if loss_sum < seen_loss or correct < seen_correct:      # someone reset the accumulators (fit / evaluate)
             seen_loss, seen_correct = 0.0, 0

@@ -261,6 +261,14 @@ int fnet_graph_begin(void *stream);
 int fnet_graph_end(void *stream, void **graph_exec_out);
 int fnet_graph_launch(void *graph_exec, void *stream);
 int fnet_graph_destroy(void *graph_exec);
+/* One step fed from HOST memory, the shape of keras' train_on_batch / test_on_batch (one session.run with a
+ * feed_dict, helpers.py:105 -> Model.fit -> train_function): copy the inputs and the targets to the device,
+ * replay the captured step, copy `result_bytes` of results (loss sum, correct count) back and wait for them.
+ * All on `stream`; host buffers may be pageable (pinned ones make the copies asynchronous until the final
+ * wait).  Either host source may be NULL to skip that copy. */
+int fnet_graph_step_fed(void *graph_exec, void *x_dev, const void *x_host, size_t x_bytes, void *y_dev,
+                        const void *y_host, size_t y_bytes, const void *result_dev, void *result_host,
+                        size_t result_bytes, void *stream);
 
 #ifdef __cplusplus
 }
