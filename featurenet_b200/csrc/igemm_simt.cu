@@ -51,7 +51,13 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
     // column context and B cursors are decoded once and then stepped from tile to tile (no divisions)
     typename P::Col col;
     typename P::Row myrow;
-    const int a_col = A_ROWS ? 0 : tid % BK, a_rg = A_ROWS ? 0 : tid / BK;
+    // when four consecutive k are four consecutive channels (C % 4 == 0) a thread gathers 16 bytes at a time:
+    // a quarter of the address arithmetic, which is what this kernel mostly executes besides FFMA
+    constexpr int CPR = BK / 4;                   // 16-byte chunks per tile row
+    constexpr int RPP = 256 / CPR;                // rows covered per pass of the vector loader
+    static_assert(A_PER % 4 == 0 && BM % RPP == 0 && BM / RPP == A_PER / 4, "vector loader shape");
+    const bool v4 = !A_ROWS && p.vec4_ok();
+    const int a_col = A_ROWS ? 0 : (v4 ? 4 * (tid % CPR) : tid % BK), a_rg = A_ROWS ? 0 : (v4 ? tid / CPR : tid / BK);
     if constexpr (A_ROWS) {
         p.make_row(m0 + tid % BM, M, myrow);
         if (tid < BK) { p.make_col(kbeg + tid, kend, col); cols[0][tid] = col; }
@@ -88,10 +94,19 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
                 a_reg[i] = (c.valid && myrow.valid) ? p.a(myrow, c) : 0.f;
             }
         } else {
+            if (v4) {
 #pragma unroll
-            for (int i = 0; i < A_PER; ++i) {
-                const typename P::Row &row = rows[a_rg + RG * i];
-                a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+                for (int i = 0; i < A_PER / 4; ++i) {
+                    const typename P::Row &row = rows[a_rg + RPP * i];
+                    float4 v = (col.valid && row.valid) ? p.a4(row, col) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    a_reg[4 * i] = v.x; a_reg[4 * i + 1] = v.y; a_reg[4 * i + 2] = v.z; a_reg[4 * i + 3] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < A_PER; ++i) {
+                    const typename P::Row &row = rows[a_rg + RG * i];
+                    a_reg[i] = (col.valid && row.valid) ? p.a(row, col) : 0.f;
+                }
             }
             p.next_col(k0 + BK + a_col, BK, kend, col);
         }
@@ -109,6 +124,11 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
             for (int i = 0; i < A_PER; ++i) As[tid / BM + KG * i][tid % BM] = a_reg[i];
             parity ^= 1;                              // contexts of the next tile, read after the barrier
             if (tid < BK) { p.next_col(k0 + BK + tid, BK, kend, col); cols[parity][tid] = col; }
+        } else if (v4) {
+#pragma unroll
+            for (int i = 0; i < A_PER / 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) As[a_col + j][a_rg + RPP * i] = a_reg[4 * i + j];
         } else {
 #pragma unroll
             for (int i = 0; i < A_PER; ++i) As[a_col][a_rg + RG * i] = a_reg[i];
@@ -133,8 +153,19 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
             } else {
                 a[0] = As[kk][ty];
             }
+            if constexpr (TN % 4 == 0) {
 #pragma unroll
-            for (int j = 0; j < TN; ++j) b[j] = Bs[kk][tx * TN + j];
+                for (int j = 0; j < TN; j += 4) {
+                    float4 t = *reinterpret_cast<const float4 *>(&Bs[kk][tx * TN + j]);
+                    b[j] = t.x; b[j + 1] = t.y; b[j + 2] = t.z; b[j + 3] = t.w;
+                }
+            } else if constexpr (TN == 2) {
+                float2 t = *reinterpret_cast<const float2 *>(&Bs[kk][tx * 2]);
+                b[0] = t.x; b[1] = t.y;
+            } else {
+#pragma unroll
+                for (int j = 0; j < TN; ++j) b[j] = Bs[kk][tx * TN + j];
+            }
 #pragma unroll
             for (int i = 0; i < TM; ++i)
 #pragma unroll
@@ -196,7 +227,7 @@ static SplitPlan plan_for(long long M, long long N, long long Kg) {
     long long tiles = ceil_div<long long>(M, s.bm) * ntiles_n;
     long long splits = 1;
     if (tiles < 2 * kNumSMs && Kg >= 4 * s.bk) {
-        splits = ceil_div<long long>(2 * kNumSMs, tiles);
+        splits = 2 * kNumSMs / tiles;               // one wave of two CTAs per SM, never a few CTAs more
         long long most = Kg / (2 * s.bk);          // at least two k-tiles per split
         if (splits > most) splits = most;
         if (splits < 1) splits = 1;
