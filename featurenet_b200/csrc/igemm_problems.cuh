@@ -135,6 +135,9 @@ struct FwdProblem {
     typedef const float *BCursor;               // B(k, n) = w[k][n]: a pointer that moves down the rows
     static constexpr bool kAContigK = true;     // A(m, k): consecutive k = consecutive input channels
     static constexpr bool kBContigK = false;    // consecutive n
+    static constexpr bool kBiasRow = false;
+    __host__ __device__ bool has_bias_row() const { return false; }
+    __device__ int colsum_row(int) const { return -1; }
     __device__ bool vec4_ok() const { return (g.C & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }
     __device__ bool a_rows_vec4_ok() const { return false; }
     __device__ bool b_rows_vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0; }
@@ -187,6 +190,9 @@ struct DgradProblem {
     typedef DgradCursor BCursor;                // B(k, n) = w[tap][n][ko] with k = tap*K + ko
     static constexpr bool kAContigK = true;     // consecutive k = consecutive output channels of dz
     static constexpr bool kBContigK = true;     // consecutive ko
+    static constexpr bool kBiasRow = false;
+    __host__ __device__ bool has_bias_row() const { return false; }
+    __device__ int colsum_row(int) const { return -1; }
     __device__ bool vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(dz) & 15) == 0; }
     __device__ bool a_rows_vec4_ok() const { return false; }
     __device__ bool b_rows_vec4_ok() const { return false; }
@@ -239,6 +245,10 @@ struct WgradProblem {
     typedef const float *BCursor;               // B(k, n) = dz[pixel k][n]
     static constexpr bool kAContigK = false;    // A(m, k) = x[pixel k][tap/channel m]: consecutive m (channels)
     static constexpr bool kBContigK = false;    // consecutive n
+    static constexpr bool kBiasRow = true;      // row taps_c is the all-ones row whose products are the bias gradient
+    __host__ __device__ bool has_bias_row() const { return dbias != nullptr; }
+    // when the tap rows fill bm-row tiles exactly, the bias row is produced from column sums of B instead
+    __device__ int colsum_row(int bm) const { return (dbias != nullptr && taps_c % bm == 0) ? taps_c : -1; }
     __device__ bool vec4_ok() const { return false; }
     // four consecutive rows = four consecutive channels of one tap; four consecutive columns of dz
     __device__ bool a_rows_vec4_ok() const { return (g.C & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }

@@ -74,6 +74,13 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
     for (int i = 0; i < TM; ++i)
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+    // Filter gradient whose tap rows fill the tiles exactly: the all-ones bias row would cost a whole extra
+    // row of tiles, so the first row of CTAs sums the columns of its B tiles (dz) instead -- same result.
+    const int bias_row = P::kBiasRow ? p.colsum_row(BM) : -1;
+    const bool do_colsum = bias_row >= 0 && blockIdx.x == 0 && ty == 0;
+    float colsum[TN];
+#pragma unroll
+    for (int j = 0; j < TN; ++j) colsum[j] = 0.f;
 
     float a_reg[A_PER], b_reg[B_PER];
     typename P::BCursor bcur[B_PER];
@@ -170,8 +177,21 @@ __global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int 
             for (int i = 0; i < TM; ++i)
 #pragma unroll
                 for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+            if (do_colsum) {
+#pragma unroll
+                for (int j = 0; j < TN; ++j) colsum[j] += b[j];
+            }
         }
         __syncthreads();
+    }
+    if (do_colsum) {
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+            int n = n0 + tx * TN + j;
+            if (n >= N) continue;
+            if (partial) partial[((long long)blockIdx.z * M + bias_row) * N + n] = colsum[j];
+            else p.store(bias_row, n, colsum[j]);
+        }
     }
 
 #pragma unroll
@@ -210,11 +230,12 @@ __global__ void __launch_bounds__(256) reduce_splits_kernel(P p, int M, int N, i
 }
 
 struct SplitPlan {
-    int bm, bn, splits, k_per_split, bk;
+    int bm, bn, splits, k_per_split, bk, m_tiles;
     size_t ws_bytes;
 };
 
-static SplitPlan plan_for(long long M, long long N, long long Kg) {
+// bias_row: the last of the M rows is the filter gradient's all-ones row (see do_colsum in the kernel)
+static SplitPlan plan_for(long long M, long long N, long long Kg, bool bias_row = false) {
     SplitPlan s;
     s.bn = N <= 8 ? 8 : (N <= 16 ? 16 : (N <= 32 ? 32 : 64));
     int big = s.bn <= 16 ? 256 : 128;
@@ -224,7 +245,9 @@ static SplitPlan plan_for(long long M, long long N, long long Kg) {
     if (ceil_div<long long>(M, big) * ntiles_n >= 2 * kNumSMs) { s.bm = big; s.bk = 16; }
     else if (M > 32) { s.bm = 64; s.bk = 32; }
     else { s.bm = 32; s.bk = 64; }
-    long long tiles = ceil_div<long long>(M, s.bm) * ntiles_n;
+    const long long tiled_rows = (bias_row && M > 1 && (M - 1) % s.bm == 0) ? M - 1 : M;
+    s.m_tiles = (int)ceil_div<long long>(tiled_rows, s.bm);
+    long long tiles = s.m_tiles * ntiles_n;
     long long splits = 1;
     if (tiles < 2 * kNumSMs && Kg >= 4 * s.bk) {
         splits = 2 * kNumSMs / tiles;               // one wave of two CTAs per SM, never a few CTAs more
@@ -252,7 +275,7 @@ static int run_problem(const P &p, long long M, long long N, long long Kg, void 
         set_error("%s: GEMM extent exceeds 2^31", what);
         return FNET_ERR_UNSUPPORTED;
     }
-    SplitPlan plan = plan_for(M, N, Kg);
+    SplitPlan plan = plan_for(M, N, Kg, P::kBiasRow && p.has_bias_row());
     float *partial = nullptr;
     if (plan.splits > 1) {
         if (ws == nullptr || ws_bytes < plan.ws_bytes) {
@@ -261,7 +284,7 @@ static int run_problem(const P &p, long long M, long long N, long long Kg, void 
         }
         partial = reinterpret_cast<float *>(ws);
     }
-    dim3 grid((unsigned)ceil_div<long long>(M, plan.bm), (unsigned)ceil_div<long long>(N, plan.bn), plan.splits);
+    dim3 grid((unsigned)plan.m_tiles, (unsigned)ceil_div<long long>(N, plan.bn), plan.splits);
     if (grid.y > 65535u || grid.z > 65535u) {
         set_error("%s: too many tiles (%u x %u)", what, grid.y, grid.z);
         return FNET_ERR_UNSUPPORTED;
@@ -316,7 +339,7 @@ size_t simt_conv_workspace(const ConvGeom &g) {
     long long taps = (long long)g.kh * g.kw;
     size_t a = plan_for(mo, g.K, taps * g.C).ws_bytes;
     size_t b = plan_for(mi, g.C, taps * g.K).ws_bytes;
-    size_t c = plan_for(taps * g.C + 1, g.K, mo).ws_bytes;       // with the bias row ...
+    size_t c = plan_for(taps * g.C + 1, g.K, mo, true).ws_bytes; // with the bias row ...
     size_t c0 = plan_for(taps * g.C, g.K, mo).ws_bytes;          // ... and without (dbias == nullptr)
     if (c0 > c) c = c0;
     return a > b ? (a > c ? a : c) : (b > c ? b : c);
