@@ -23,7 +23,7 @@ namespace fnet {
 // is being multiplied out of shared memory, so the global-load latency of the small, latency-bound
 // problems FeatureNet produces overlaps with the FFMA work.
 template <class P, int BM, int BN, int TM, int TN, int BK>
-__global__ void __launch_bounds__(256) igemm_simt_kernel(P p, int M, int N, int Kg, int k_per_split,
+__global__ void __launch_bounds__(256, 3) igemm_simt_kernel(P p, int M, int N, int Kg, int k_per_split,
                                                           float *__restrict__ partial) {
     static_assert((BM / TM) * (BN / TN) == 256, "256 threads per CTA");
     constexpr int RG = 256 / BK;                 // row groups of the A loader
@@ -249,8 +249,8 @@ static SplitPlan plan_for(long long M, long long N, long long Kg, bool bias_row 
     s.m_tiles = (int)ceil_div<long long>(tiled_rows, s.bm);
     long long tiles = s.m_tiles * ntiles_n;
     long long splits = 1;
-    if (tiles < 2 * kNumSMs && Kg >= 4 * s.bk) {
-        splits = 2 * kNumSMs / tiles;               // one wave of two CTAs per SM, never a few CTAs more
+    if (tiles < 3 * kNumSMs && Kg >= 4 * s.bk) {
+        splits = 3 * kNumSMs / tiles;               // one wave of three CTAs per SM (launch bounds), never a few CTAs more
         long long most = Kg / (2 * s.bk);          // at least two k-tiles per split
         if (splits > most) splits = most;
         if (splits < 1) splits = 1;
