@@ -57,9 +57,14 @@ __global__ void __launch_bounds__(256, 3) igemm_simt_kernel(P p, int M, int N, i
     constexpr int RPP = 256 / CPR;                // rows covered per pass of the vector loader
     static_assert(A_PER % 4 == 0 && BM % RPP == 0 && BM / RPP == A_PER / 4, "vector loader shape");
     const bool v4 = !A_ROWS && p.vec4_ok();
+    // row-wise loader, 16 bytes = four consecutive rows (channels of one tap) of one k
+    constexpr int RC = BM / 4;                    // row chunks per k
+    constexpr int KG4 = 256 / RC;                 // k-groups of the vector row-wise loader
+    static_assert(!A_ROWS || (BK % KG4 == 0 && BK / KG4 == A_PER / 4), "vector row-wise loader shape");
+    const bool r4 = A_ROWS && p.a_rows_vec4_ok();
     const int a_col = A_ROWS ? 0 : (v4 ? 4 * (tid % CPR) : tid % BK), a_rg = A_ROWS ? 0 : (v4 ? tid / CPR : tid / BK);
     if constexpr (A_ROWS) {
-        p.make_row(m0 + tid % BM, M, myrow);
+        p.make_row(r4 ? m0 + 4 * (tid % RC) : m0 + tid % BM, M, myrow);
         if (tid < BK) { p.make_col(kbeg + tid, kend, col); cols[0][tid] = col; }
     } else {
         for (int i = tid; i < BM; i += 256) p.make_row(m0 + i, M, rows[i]);
@@ -95,10 +100,21 @@ __global__ void __launch_bounds__(256, 3) igemm_simt_kernel(P p, int M, int N, i
     int parity = 0;
     auto gather = [&](int k0) {
         if constexpr (A_ROWS) {
+            if (r4) {
 #pragma unroll
-            for (int i = 0; i < A_PER; ++i) {
-                const typename P::Col &c = cols[parity][tid / BM + KG * i];
-                a_reg[i] = (c.valid && myrow.valid) ? p.a(myrow, c) : 0.f;
+                for (int i = 0; i < A_PER / 4; ++i) {
+                    const typename P::Col &c = cols[parity][tid / RC + KG4 * i];
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (c.valid && myrow.valid == 2) v.x = 1.f;                  // the bias row opens its chunk
+                    else if (c.valid && myrow.valid) v = load4(p.a_ptr(myrow, c));
+                    a_reg[4 * i] = v.x; a_reg[4 * i + 1] = v.y; a_reg[4 * i + 2] = v.z; a_reg[4 * i + 3] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < A_PER; ++i) {
+                    const typename P::Col &c = cols[parity][tid / BM + KG * i];
+                    a_reg[i] = (c.valid && myrow.valid) ? p.a(myrow, c) : 0.f;
+                }
             }
         } else {
             if (v4) {
@@ -127,8 +143,21 @@ __global__ void __launch_bounds__(256, 3) igemm_simt_kernel(P p, int M, int N, i
     if (kbeg < kend) gather(kbeg);
     for (int k0 = kbeg; k0 < kend; k0 += BK) {
         if constexpr (A_ROWS) {
+            if (r4) {
 #pragma unroll
-            for (int i = 0; i < A_PER; ++i) As[tid / BM + KG * i][tid % BM] = a_reg[i];
+                for (int i = 0; i < A_PER / 4; ++i) {
+                    float *dst = &As[tid / RC + KG4 * i][4 * (tid % RC)];
+                    if constexpr ((BM + PAD) % 4 == 0) {
+                        *reinterpret_cast<float4 *>(dst) = make_float4(a_reg[4 * i], a_reg[4 * i + 1], a_reg[4 * i + 2], a_reg[4 * i + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) dst[j] = a_reg[4 * i + j];
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < A_PER; ++i) As[tid / BM + KG * i][tid % BM] = a_reg[i];
+            }
             parity ^= 1;                              // contexts of the next tile, read after the barrier
             if (tid < BK) { p.next_col(k0 + BK + tid, BK, kend, col); cols[parity][tid] = col; }
         } else if (v4) {
