@@ -9,7 +9,7 @@ namespace {
 inline size_t max_sz(size_t a, size_t b) { return a > b ? a : b; }
 
 int check_math(int math, const char *what) {
-    if (math != FNET_MATH_FP32 && math != FNET_MATH_TF32 && math != FNET_MATH_BF16) {
+    if (math != FNET_MATH_FP32 && math != FNET_MATH_TF32 && math != FNET_MATH_BF16 && math != FNET_MATH_TF32X3) {
         set_error("%s: unknown math mode %d", what, math);
         return FNET_ERR_ARG;
     }

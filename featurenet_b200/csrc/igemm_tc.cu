@@ -109,7 +109,13 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const float *src, uint3
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 
-template <class P, int BN, int TC_STAGES>
+// X3 = 1: fp32 accuracy from tf32 MMAs.  Each landed stage is rewritten in place as hi = rna_tf32(v) and its
+// tail lo = rna_tf32(v - hi) goes to one extra tile set behind the pipeline stages (same layout, so the same
+// descriptors with another base address); a k-step is then three MMAs, hi*hi + lo*hi + hi*lo.  The dropped
+// lo*lo term and the rounding of lo are ~2^-22 relative: the result sits with the FFMA kernels' against the
+// float64 oracle.  The tensor pipe is idle most of the time in these gather-bound kernels, so the extra MMAs
+// are free; the cost is one pass of the CTA over the stage in shared memory.
+template <class P, int BN, int TC_STAGES, int X3>
 __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int N, int Kg, int k_per_split,
                                                                  float *__restrict__ partial, int layout) {
     constexpr int B_BYTES = BN * TC_BK * 4;
@@ -293,11 +299,38 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
         asm volatile("cp.async.wait_group %0;" ::"n"(TC_STAGES - LAG) : "memory"); // tile kt has landed (this thread's part)
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");               // ... and is visible to the tensor core
         __syncthreads();
+        if constexpr (X3) {
+            // the MMAs of tile kt-1 read the (single) tail buffer: they must be done before it is rewritten
+            if (kt >= 1) mbar_wait(&empty_bar[(kt - 1) % TC_STAGES], (uint32_t)(((kt - 1) / TC_STAGES) & 1));
+            float4 *hi = reinterpret_cast<float4 *>(smem + s * STAGE_BYTES);
+            float4 *lo = reinterpret_cast<float4 *>(smem + TC_STAGES * STAGE_BYTES);
+#pragma unroll
+            for (int c = tid; c < STAGE_BYTES / 16; c += TC_THREADS) {
+                float4 v = hi[c], h, l;
+                h.x = to_tf32(v.x); h.y = to_tf32(v.y); h.z = to_tf32(v.z); h.w = to_tf32(v.w);
+                l.x = to_tf32(v.x - h.x); l.y = to_tf32(v.y - h.y); l.z = to_tf32(v.z - h.z); l.w = to_tf32(v.w - h.w);
+                hi[c] = h;
+                lo[c] = l;
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+        }
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + TC_A_BYTES;
             uint64_t da = A_MN ? make_smem_desc_mn(sa, 4) : make_smem_desc(sa, layout);
             uint64_t db = B_MN ? make_smem_desc_mn(sb, B_ATOMS) : make_smem_desc(sb, layout);
+            if constexpr (X3) {
+                const uint32_t la = smem_base + TC_STAGES * STAGE_BYTES, lb = la + TC_A_BYTES;
+                uint64_t dla = A_MN ? make_smem_desc_mn(la, 4) : make_smem_desc(la, layout);
+                uint64_t dlb = B_MN ? make_smem_desc_mn(lb, B_ATOMS) : make_smem_desc(lb, layout);
+#pragma unroll
+                for (int j = 0; j < TC_BK / 8; ++j) {
+                    tc_mma_tf32(tmem, dla + (uint64_t)(j * kadv_a), db + (uint64_t)(j * kadv_b), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+                    tc_mma_tf32(tmem, da + (uint64_t)(j * kadv_a), dlb + (uint64_t)(j * kadv_b), idesc, 1u);
+                    tc_mma_tf32(tmem, da + (uint64_t)(j * kadv_a), db + (uint64_t)(j * kadv_b), idesc, 1u);   // the large term last
+                }
+            } else
 #pragma unroll
             for (int j = 0; j < TC_BK / 8; ++j)
                 tc_mma_tf32(tmem, da + (uint64_t)(j * kadv_a), db + (uint64_t)(j * kadv_b), idesc, (kt > 0 || j > 0) ? 1u : 0u);
@@ -377,9 +410,9 @@ struct TcPlan {
     size_t ws_bytes, smem_bytes;
 };
 
-static TcPlan tc_plan(long long M, long long N, long long Kg) {
+static TcPlan tc_plan(long long M, long long N, long long Kg, bool x3 = false) {
     TcPlan t;
-    t.bn = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+    t.bn = N <= 32 ? 32 : ((N <= 64 || x3) ? 64 : 128);     // x3 keeps a tail tile set: narrower tiles so two CTAs still fit
     long long tiles = ceil_div<long long>(M, TC_BM) * ceil_div<long long>(N, t.bn);
     // Two CTAs are resident per SM (shared memory: 3 stages of a 128-wide tile or 4 stages of a narrower one
     // are ~97 KB).  When the output has fewer tiles than that one wave, the reduction axis is split so that the
@@ -396,8 +429,8 @@ static TcPlan tc_plan(long long M, long long N, long long Kg) {
     t.k_per_split = (int)per;
     t.splits = (int)ceil_div<long long>(Kg, per);
     t.ws_bytes = t.splits > 1 ? (size_t)t.splits * M * N * sizeof(float) : 0;
-    t.stages = (per >= 8 * TC_BK && t.bn < 128) ? 4 : 3;   // long reductions: deeper pipeline where it still fits twice
-    t.smem_bytes = (size_t)t.stages * (TC_A_BYTES + t.bn * TC_BK * 4) + 1024;
+    t.stages = (per >= 8 * TC_BK && t.bn < 128 && !x3) ? 4 : 3;   // long reductions: deeper pipeline where it still fits twice
+    t.smem_bytes = (size_t)(t.stages + (x3 ? 1 : 0)) * (TC_A_BYTES + t.bn * TC_BK * 4) + 1024;
     return t;
 }
 
@@ -410,24 +443,25 @@ static int tc_layout_mode() {
     return mode;
 }
 
-template <class P, int BN, int STAGES>
+template <class P, int BN, int STAGES, int X3>
 static int tc_launch(const P &p, dim3 grid, size_t smem, int m, int n, int kg, int per, float *partial,
                      cudaStream_t stream, const char *what) {
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(tc_igemm_kernel<P, BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(tc_igemm_kernel<P, BN, STAGES, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
         configured = true;
     }
-    tc_igemm_kernel<P, BN, STAGES><<<grid, TC_THREADS, smem, stream>>>(p, m, n, kg, per, partial, tc_layout_mode());
+    tc_igemm_kernel<P, BN, STAGES, X3><<<grid, TC_THREADS, smem, stream>>>(p, m, n, kg, per, partial, tc_layout_mode());
     return check_launch(what);
 }
 
 template <class P>
-static int tc_run(const P &p, long long M, long long N, long long Kg, void *ws, size_t ws_bytes, cudaStream_t stream,
+static int tc_run(const P &p, int math, long long M, long long N, long long Kg, void *ws, size_t ws_bytes, cudaStream_t stream,
                   const char *what) {
     if (M <= 0 || N <= 0) return FNET_OK;
-    TcPlan plan = tc_plan(M, N, Kg);
+    const bool x3 = math == FNET_MATH_TF32X3;
+    TcPlan plan = tc_plan(M, N, Kg, x3);
     float *partial = nullptr;
     if (plan.splits > 1) {
         if (!ws || ws_bytes < plan.ws_bytes) {
@@ -438,9 +472,10 @@ static int tc_run(const P &p, long long M, long long N, long long Kg, void *ws, 
     }
     dim3 grid((unsigned)ceil_div<long long>(M, TC_BM), (unsigned)ceil_div<long long>(N, plan.bn), plan.splits);
     int m = (int)M, n = (int)N, kg = (int)Kg, rc;
-#define FNET_TC_LAUNCH(BN_, ST_) tc_launch<P, BN_, ST_>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what)
-    if (plan.stages == 4) rc = plan.bn == 32 ? FNET_TC_LAUNCH(32, 4) : (plan.bn == 64 ? FNET_TC_LAUNCH(64, 4) : FNET_TC_LAUNCH(128, 4));
-    else rc = plan.bn == 32 ? FNET_TC_LAUNCH(32, 3) : (plan.bn == 64 ? FNET_TC_LAUNCH(64, 3) : FNET_TC_LAUNCH(128, 3));
+#define FNET_TC_LAUNCH(BN_, ST_, X3_) tc_launch<P, BN_, ST_, X3_>(p, grid, plan.smem_bytes, m, n, kg, plan.k_per_split, partial, stream, what)
+    if (x3) rc = plan.bn == 32 ? FNET_TC_LAUNCH(32, 3, 1) : FNET_TC_LAUNCH(64, 3, 1);
+    else if (plan.stages == 4) rc = plan.bn == 32 ? FNET_TC_LAUNCH(32, 4, 0) : FNET_TC_LAUNCH(64, 4, 0);
+    else rc = plan.bn == 32 ? FNET_TC_LAUNCH(32, 3, 0) : (plan.bn == 64 ? FNET_TC_LAUNCH(64, 3, 0) : FNET_TC_LAUNCH(128, 3, 0));
 #undef FNET_TC_LAUNCH
     if (rc != FNET_OK) return rc;
     if (plan.splits > 1) {
@@ -458,7 +493,7 @@ static bool tc_shape_ok(long long M, long long N, long long Kg) {
 }
 
 bool tc_supported(const ConvGeom &g, int math, int product) {
-    if (math != FNET_MATH_TF32) return false;              // bf16 operands: not built yet
+    if (math != FNET_MATH_TF32 && math != FNET_MATH_TF32X3) return false;   // bf16 operands: not built yet
     long long mo = (long long)g.B * g.Ho * g.Wo, mi = (long long)g.B * g.H * g.W, taps = (long long)g.kh * g.kw;
     if (product == 0) return tc_shape_ok(mo, g.K, taps * g.C);
     if (product == 1) return tc_shape_ok(mi, g.C, taps * g.K);
@@ -466,39 +501,38 @@ bool tc_supported(const ConvGeom &g, int math, int product) {
 }
 
 size_t tc_conv_workspace(const ConvGeom &g, int math) {
-    if (math != FNET_MATH_TF32) return 0;
+    if (math != FNET_MATH_TF32 && math != FNET_MATH_TF32X3) return 0;
     long long mo = (long long)g.B * g.Ho * g.Wo, mi = (long long)g.B * g.H * g.W, taps = (long long)g.kh * g.kw;
     size_t need = 0;
-    if (tc_supported(g, math, 0)) need = tc_plan(mo, g.K, taps * g.C).ws_bytes;
-    if (tc_supported(g, math, 1)) { size_t b = tc_plan(mi, g.C, taps * g.K).ws_bytes; need = b > need ? b : need; }
-    if (tc_supported(g, math, 2)) {
-        size_t c = tc_plan(taps * g.C + 1, g.K, mo).ws_bytes, c0 = tc_plan(taps * g.C, g.K, mo).ws_bytes;   // with / without bias row
-        c = c0 > c ? c0 : c;
-        need = c > need ? c : need;
+    for (int x3 = 0; x3 < 2; ++x3) {                        // the caller's buffer serves either tensor-core mode
+        auto upto = [&](size_t v) { need = v > need ? v : need; };
+        if (tc_supported(g, math, 0)) upto(tc_plan(mo, g.K, taps * g.C, x3).ws_bytes);
+        if (tc_supported(g, math, 1)) upto(tc_plan(mi, g.C, taps * g.K, x3).ws_bytes);
+        if (tc_supported(g, math, 2)) {                     // with / without the bias row
+            upto(tc_plan(taps * g.C + 1, g.K, mo, x3).ws_bytes);
+            upto(tc_plan(taps * g.C, g.K, mo, x3).ws_bytes);
+        }
     }
     return need;
 }
 
 int tc_conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
                 void *ws, size_t ws_bytes, cudaStream_t stream) {
-    (void)math;
     FwdProblem p{g, x, w, bias, y, act == FNET_ACT_SOFTMAX ? FNET_ACT_NONE : act};
-    return tc_run(p, (long long)g.B * g.Ho * g.Wo, g.K, (long long)g.kh * g.kw * g.C, ws, ws_bytes, stream, "conv2d_fwd[tf32]");
+    return tc_run(p, math, (long long)g.B * g.Ho * g.Wo, g.K, (long long)g.kh * g.kw * g.C, ws, ws_bytes, stream, "conv2d_fwd[tf32]");
 }
 
 int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
                   size_t ws_bytes, cudaStream_t stream) {
-    (void)math;
     DgradProblem p{g, dz, w, dx, accumulate};
-    return tc_run(p, (long long)g.B * g.H * g.W, g.C, (long long)g.kh * g.kw * g.K, ws, ws_bytes, stream, "conv2d_bwd_data[tf32]");
+    return tc_run(p, math, (long long)g.B * g.H * g.W, g.C, (long long)g.kh * g.kw * g.K, ws, ws_bytes, stream, "conv2d_bwd_data[tf32]");
 }
 
 int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                   size_t ws_bytes, cudaStream_t stream) {
-    (void)math;
     int taps_c = g.kh * g.kw * g.C;
     WgradProblem p{g, x, dz, dw, dbias, taps_c};
-    return tc_run(p, (long long)taps_c + (dbias ? 1 : 0), g.K, (long long)g.B * g.Ho * g.Wo, ws, ws_bytes, stream,
+    return tc_run(p, math, (long long)taps_c + (dbias ? 1 : 0), g.K, (long long)g.B * g.Ho * g.Wo, ws, ws_bytes, stream,
                   "conv2d_bwd_filter[tf32]");
 }
 

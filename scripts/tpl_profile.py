@@ -11,7 +11,11 @@ from model.keras_model import KerasFeatureModel
 
 tpl, ds = sys.argv[1], sys.argv[2]
 with contextlib.redirect_stdout(io.StringIO()):
-    net = KerasFeatureModel.parse_feature_model(tpl).build(synth.SHAPES[ds], 10)
+    if tpl in ("nas1", "wide"):                     # bench.py workloads that are products of a .pdt, not templates
+        import bench
+        _, net, ds = bench.build_candidate(tpl)
+    else:
+        net = KerasFeatureModel.parse_feature_model(tpl).build(synth.SHAPES[ds], 10)
     (xtr, ytr), _ = synth.load(ds, 16384, 16)
 net.compile(loss="categorical_crossentropy", optimizer=Adam(1e-3))
 eng = net._need_engine()

@@ -1,7 +1,8 @@
 """Tensor-core path (tcgen05.mma kind::tf32, TMEM accumulators) vs the float64 oracle.
 
-tf32 operands carry 10 mantissa bits (2^-11 relative rounding) with fp32 accumulation, so the
-stated tolerance for this mode is 3e-3 relative (max-norm) per layer; the fp32 path keeps 1e-4.
+tf32 operands carry 10 mantissa bits with fp32 accumulation, so the stated tolerance for FNET_MATH_TF32
+is 5e-3 relative (max-norm) per layer.  FNET_MATH_TF32X3 splits every operand into a tf32 head and tail
+(three MMAs per product) and has to meet the bar of the fp32 path: asserted at 2e-5, stated 1e-4.
 """
 import ctypes as C
 
@@ -31,15 +32,19 @@ TC_CONV_CASES = [
 ]
 
 
+MODES = [("tf32", TF32_TOL), ("tf32x3", 2e-5)]
+
+
+@pytest.mark.parametrize("math,tol", MODES)
 @pytest.mark.parametrize("case_id", range(len(TC_CONV_CASES)))
-def test_conv2d_tf32_tensor_core(L, case_id):
+def test_conv2d_tf32_tensor_core(L, case_id, math, tol):
     from featurenet_b200 import lib as fl
     xs, k, kout, s = TC_CONV_CASES[case_id]
     rng = np.random.default_rng(2000 + case_id)
     x = rng.standard_normal(xs)
     w = rng.standard_normal(k + (xs[3], kout)) / np.sqrt(k[0] * k[1] * xs[3])
     b = rng.standard_normal(kout)
-    desc = conv_desc(fl, xs, k, kout, s, "same", act="relu", math="tf32")
+    desc = conv_desc(fl, xs, k, kout, s, "same", act="relu", math=math)
     ws = workspace(L.fnet_conv2d_workspace_bytes(C.byref(desc)))
     y = ops.act_fwd(ops.conv2d_fwd(x, w, b, s, "same"), "relu")
     dz = rng.standard_normal(y.shape)
@@ -47,21 +52,22 @@ def test_conv2d_tf32_tensor_core(L, case_id):
     xd, wd, bd, dzd = dev(x), dev(w), dev(b), dev(dz)
     yd = torch.empty(y.shape, device="cuda")
     L.fnet_conv2d_fwd(desc, ptr(xd), ptr(wd), ptr(bd), ptr(yd), ptr(ws), ws.numel(), None)
-    assert_close(host(yd), y, tol=TF32_TOL, what="tf32 conv fwd")
+    assert_close(host(yd), y, tol=tol, what="%s " % math + "conv fwd")
     dxd = torch.empty(xs, device="cuda")
     L.fnet_conv2d_bwd_data(desc, ptr(dzd), ptr(wd), ptr(dxd), 0, ptr(ws), ws.numel(), None)
-    assert_close(host(dxd), dx, tol=TF32_TOL, what="tf32 conv dgrad")
+    assert_close(host(dxd), dx, tol=tol, what="%s " % math + "conv dgrad")
     dwd, dbd = torch.empty(w.shape, device="cuda"), torch.empty(kout, device="cuda")
     L.fnet_conv2d_bwd_filter(desc, ptr(xd), ptr(dzd), ptr(dwd), ptr(dbd), ptr(ws), ws.numel(), None)
-    assert_close(host(dwd), dw, tol=TF32_TOL, what="tf32 conv wgrad")
-    assert_close(host(dbd), db, tol=TF32_TOL, what="tf32 conv bias grad")
+    assert_close(host(dwd), dw, tol=tol, what="%s " % math + "conv wgrad")
+    assert_close(host(dbd), db, tol=tol, what="%s " % math + "conv bias grad")
     dw2 = torch.empty(w.shape, device="cuda")
     L.fnet_conv2d_bwd_filter(desc, ptr(xd), ptr(dzd), ptr(dw2), None, ptr(ws), ws.numel(), None)
     assert torch.equal(dwd, dw2)                                        # still deterministic
 
 
+@pytest.mark.parametrize("math,tol", MODES)
 @pytest.mark.parametrize("m,k,n", [(4096, 64, 512), (16384, 64, 512), (1000, 200, 33), (256, 4096, 100)])
-def test_dense_tf32_tensor_core(L, m, k, n):
+def test_dense_tf32_tensor_core(L, m, k, n, math, tol):
     from featurenet_b200 import lib as fl
     rng = np.random.default_rng(m + n)
     x, w, b = rng.standard_normal((m, k)), rng.standard_normal((k, n)) / np.sqrt(k), rng.standard_normal(n)
@@ -71,11 +77,11 @@ def test_dense_tf32_tensor_core(L, m, k, n):
     ws = workspace(L.fnet_dense_workspace_bytes(m, k, n))
     xd, wd, bd, dzd = dev(x), dev(w), dev(b), dev(dz)
     yd = torch.empty((m, n), device="cuda")
-    L.fnet_dense_fwd(m, k, n, fl.ACT["tanh"], fl.MATH["tf32"], ptr(xd), ptr(wd), ptr(bd), ptr(yd), ptr(ws), ws.numel(), None)
-    assert_close(host(yd), y, tol=TF32_TOL, what="tf32 dense fwd")
+    L.fnet_dense_fwd(m, k, n, fl.ACT["tanh"], fl.MATH[math], ptr(xd), ptr(wd), ptr(bd), ptr(yd), ptr(ws), ws.numel(), None)
+    assert_close(host(yd), y, tol=tol, what="%s " % math + "dense fwd")
     dxd, dwd, dbd = torch.empty((m, k), device="cuda"), torch.empty((k, n), device="cuda"), torch.empty(n, device="cuda")
-    L.fnet_dense_bwd_data(m, k, n, fl.MATH["tf32"], ptr(dzd), ptr(wd), ptr(dxd), 0, ptr(ws), ws.numel(), None)
-    L.fnet_dense_bwd_filter(m, k, n, fl.MATH["tf32"], ptr(xd), ptr(dzd), ptr(dwd), ptr(dbd), ptr(ws), ws.numel(), None)
-    assert_close(host(dxd), dx, tol=TF32_TOL, what="tf32 dense dgrad")
-    assert_close(host(dwd), dw, tol=TF32_TOL, what="tf32 dense wgrad")
-    assert_close(host(dbd), db, tol=TF32_TOL, what="tf32 dense bias grad")
+    L.fnet_dense_bwd_data(m, k, n, fl.MATH[math], ptr(dzd), ptr(wd), ptr(dxd), 0, ptr(ws), ws.numel(), None)
+    L.fnet_dense_bwd_filter(m, k, n, fl.MATH[math], ptr(xd), ptr(dzd), ptr(dwd), ptr(dbd), ptr(ws), ws.numel(), None)
+    assert_close(host(dxd), dx, tol=tol, what="%s " % math + "dense dgrad")
+    assert_close(host(dwd), dw, tol=tol, what="%s " % math + "dense wgrad")
+    assert_close(host(dbd), db, tol=tol, what="%s " % math + "dense bias grad")
