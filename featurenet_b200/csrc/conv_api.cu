@@ -20,6 +20,7 @@ int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *
              void *ws, size_t ws_bytes, cudaStream_t s) {
     int rc;
     if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
+    else if (tma_gemm_supported(g, math, 0)) rc = tma_gemm_fwd(g, act, x, w, bias, y, s);
     else if (math != FNET_MATH_FP32 && tc_supported(g, math, 0)) rc = tc_conv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
     else rc = simt_conv_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
     if (rc == FNET_OK && act == FNET_ACT_SOFTMAX)
@@ -41,6 +42,7 @@ int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, flo
         return rc == FNET_OK ? col2im_scatter(g, t, dx, accumulate, s) : rc;
     }
     if (skinny_supported(g, 1, false)) return skinny_dgrad(g, dz, w, dx, accumulate, s);
+    if (tma_gemm_supported(g, math, 1)) return tma_gemm_dgrad(g, dz, w, dx, accumulate, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) return tc_conv_dgrad(g, math, dz, w, dx, accumulate, ws, ws_bytes, s);
     return simt_conv_dgrad(g, dz, w, dx, accumulate, ws, ws_bytes, s);
 }
