@@ -50,6 +50,7 @@ int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, flo
 int conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                size_t ws_bytes, cudaStream_t s) {
     if (skinny_supported(g, 2, dbias != nullptr)) return skinny_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
+    if (tma_gemm_supported(g, math, 2)) return tma_gemm_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 2)) return tc_conv_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
     return simt_conv_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
 }
@@ -70,7 +71,7 @@ size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
     ConvGeom g;
     if (geom_checked(d, g, "fnet_conv2d_workspace_bytes") != FNET_OK) return 0;
     size_t need = max_sz(simt_conv_workspace(g), skinny_workspace(g));
-    if (d->math != FNET_MATH_FP32) need = max_sz(need, tc_conv_workspace(g, d->math));
+    if (d->math != FNET_MATH_FP32) need = max_sz(need, max_sz(tc_conv_workspace(g, d->math), tma_gemm_workspace(g, d->math)));
     if (size_t t_bytes = col2im_t_bytes(g)) {
         ConvGeom gd = dense_geom((long long)g.B * g.Ho * g.Wo, (long long)g.kh * g.kw * g.C, g.K);
         need = max_sz(need, t_bytes + max_sz(simt_conv_workspace(gd), tc_conv_workspace(gd, FNET_MATH_TF32)));
@@ -112,7 +113,8 @@ int fnet_conv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const floa
 size_t fnet_dense_workspace_bytes(int64_t m, int64_t k, int64_t n) {
     if (check_dense(m, k, n, "fnet_dense_workspace_bytes") != FNET_OK || m == 0) return 0;
     ConvGeom g = dense_geom(m, k, n);
-    return max_sz(max_sz(simt_conv_workspace(g), skinny_workspace(g)), tc_conv_workspace(g, FNET_MATH_TF32));
+    return max_sz(max_sz(simt_conv_workspace(g), skinny_workspace(g)),
+                  max_sz(tc_conv_workspace(g, FNET_MATH_TF32), tma_gemm_workspace(g, FNET_MATH_TF32)));
 }
 
 int fnet_dense_fwd(int64_t m, int64_t k, int64_t n, int act, int math, const float *x, const float *w,

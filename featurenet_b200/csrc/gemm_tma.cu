@@ -208,6 +208,145 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_co
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)tmem_cols) : "memory");
 }
 
+// Filter gradient of a plain GEMM layer: dw[C][N] = x^T[C][pixels] * dz[pixels][N].  Both operands are MN-major
+// (their contiguous axis is the tile's row axis), the reduction runs over the pixels and is long, the output is
+// small: one (output tile, slice of the pixel axis) per CTA, partial tiles to the workspace, fixed-order reduce.
+// The bias gradient is the column sum of dz, i.e. a second accumulator fed by an all-ones A tile (an extra MMA per
+// k-step on a tensor pipe that is otherwise idle; the first row of that accumulator is the answer).
+__global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                                  const __grid_constant__ CUtensorMap map_b, WgradProblem p,
+                                                                  int M /* C (+1 bias row) */, int N, int pixels, int BN,
+                                                                  int n_tiles, int tiles, int kt_per_split, int stages,
+                                                                  int tmem_cols, float *__restrict__ partial) {
+    extern __shared__ uint8_t tg_smem_raw[];
+    __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], acc_full;
+    __shared__ uint32_t tmem_holder;
+    __shared__ float xpose[4][32 * 33];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(tg_smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = tg_smem(smem);
+    const int b_bytes = BN * TG_BK * 4, stage_bytes = TG_A_BYTES + b_bytes;
+    const int tile = blockIdx.x % tiles, split = blockIdx.x / tiles;
+    const int m0 = (tile / n_tiles) * TG_BM, n0 = (tile % n_tiles) * BN;
+    const int KT_all = (pixels + TG_BK - 1) / TG_BK;
+    const int kt_begin = split * kt_per_split, kt_end = min(KT_all, kt_begin + kt_per_split);
+    const bool with_bias = p.dbias != nullptr && m0 == 0;
+    float *ones = reinterpret_cast<float *>(smem + stages * stage_bytes);
+
+    if (threadIdx.x == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < stages; ++s) { tg_bar_init(&full_bar[s], 1); tg_bar_init(&empty_bar[s], 1); }
+            tg_bar_init(&acc_full, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tg_smem(&tmem_holder)),
+                     "r"((uint32_t)tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    } else if (warp >= 2 && with_bias) {
+        for (int i = threadIdx.x - 64; i < TG_A_BYTES / 4; i += 128) ones[i] = 1.f;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_holder;
+    const uint32_t bias_col = (uint32_t)tmem_cols / 2;        // the column-sum accumulator
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kt = kt_begin; kt < kt_end; ++kt) {
+                tg_bar_wait(&empty_bar[stage], phase ^ 1);
+                const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
+                tg_bar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+                for (int j = 0; j < TG_BM / 32; ++j) tg_tma_2d(sa + j * 4096, &map_a, &full_bar[stage], m0 + 32 * j, kt * TG_BK);
+                for (int j = 0; j < BN / 32; ++j) tg_tma_2d(sb + j * 4096, &map_b, &full_bar[stage], n0 + 32 * j, kt * TG_BK);
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) |
+                                   ((uint32_t)(TG_BM >> 4) << 24);
+            const uint32_t idesc_ones = idesc & ~(1u << 15);  // the all-ones tile is read K-major (any layout of ones is ones)
+            const uint64_t d_ones = tg_desc_k(tg_smem(ones));
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kt = kt_begin; kt < kt_end; ++kt) {
+                tg_bar_wait(&full_bar[stage], phase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
+                const uint64_t da = tg_desc_mn(sa), db = tg_desc_mn(sb);
+#pragma unroll
+                for (int j = 0; j < TG_BK / 8; ++j) {
+                    const uint32_t accumulate = (kt > kt_begin || j > 0) ? 1u : 0u;
+                    tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, accumulate);
+                    if (with_bias) tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(64 * j), idesc_ones, accumulate);
+                }
+                tg_commit(&empty_bar[stage]);
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+            }
+            tg_commit(&acc_full);
+        }
+    } else {
+        const int quad = warp & 3;
+        float *xp = xpose[warp - 2];
+        const bool any = kt_end > kt_begin;
+        if (any) {
+            tg_bar_wait(&acc_full, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+        const int taps_c = p.taps_c;
+        const int m_first = m0 + quad * 32, count = min(32, taps_c - m_first);
+        for (int pass = 0; pass < (with_bias && quad == 0 ? 2 : 1); ++pass) {
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t v[32];
+                if (any) {
+                    uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + (pass ? bias_col : 0u) + (uint32_t)c0;
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                        : "r"(taddr));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = 0u;
+                }
+#pragma unroll
+                for (int j = 0; j < 32; ++j) xp[lane * 33 + j] = __uint_as_float(v[j]);
+                __syncwarp();
+                const int n = n0 + c0 + lane;
+                if (n < N) {
+                    // pass 0: rows of dw; pass 1: row 0 of the column-sum accumulator is the bias gradient (row taps_c)
+                    const int first = pass ? taps_c : m_first, rows = pass ? 1 : count;
+                    for (int r = 0; r < rows; ++r) {
+                        float val = xp[r * 33 + lane];
+                        if (partial) partial[((long long)split * M + first + r) * N + n] = val;
+                        else p.store(first + r, n, val);
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)tmem_cols) : "memory");
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -250,15 +389,42 @@ static int tg_bn(long long n) {
     return (int)(bn > 256 ? 256 : bn);
 }
 
-// product: 0 forward (N = g.K, reduction g.C), 1 data gradient (N = g.C, reduction g.K)
+struct TgWgradPlan {
+    int bn, n_tiles, tiles, splits, kt_per_split, stages, tmem_cols;
+    size_t smem, ws_bytes;
+};
+
+static TgWgradPlan tg_wgrad_plan(const ConvGeom &g) {
+    TgWgradPlan t;
+    const long long pixels = (long long)g.B * g.H * g.W, KT = ceil_div<long long>(pixels, TG_BK);
+    t.bn = tg_bn(g.K);
+    t.n_tiles = (int)ceil_div<long long>(g.K, t.bn);
+    t.tiles = (int)ceil_div<long long>(g.C, TG_BM) * t.n_tiles;
+    long long splits = kNumSMs / t.tiles, most = KT / 8;     // one CTA per SM, at least 8 k-tiles each
+    if (splits > most) splits = most;
+    if (splits < 1) splits = 1;
+    t.kt_per_split = (int)ceil_div<long long>(KT, splits);
+    t.splits = (int)ceil_div<long long>(KT, t.kt_per_split);
+    t.stages = 3;
+    t.tmem_cols = 64;
+    while (t.tmem_cols < 2 * t.bn) t.tmem_cols *= 2;
+    t.smem = (size_t)t.stages * (TG_A_BYTES + t.bn * TG_BK * 4) + TG_A_BYTES + 1024;
+    t.ws_bytes = t.splits > 1 ? (size_t)t.splits * (g.C + 1) * g.K * sizeof(float) : 0;
+    return t;
+}
+
+// product: 0 forward (N = g.K, reduction g.C), 1 data gradient (N = g.C, reduction g.K), 2 filter gradient
 bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
     static int mode = -1;                                    // FNET_TMA=0 disables (A/B measurements)
     if (mode < 0) {
         const char *e = getenv("FNET_TMA");
         mode = (e && e[0] == '0') ? 0 : 1;
     }
-    if (!mode || math != FNET_MATH_TF32 || product > 1 || !is_plain_gemm(g) || !encode_tiled()) return false;
+    if (!mode || math != FNET_MATH_TF32 || product > 2 || !is_plain_gemm(g) || !encode_tiled()) return false;
     long long M = (long long)g.B * g.H * g.W;
+    if (product == 2)
+        return !(g.C & 3) && !(g.K & 3) && g.C >= 16 && g.K >= 16 && M >= 8192 && M <= 0x7fffffffLL &&
+               (long long)g.C * g.K * M >= (1LL << 24);
     long long N = product == 0 ? g.K : g.C, Kg = product == 0 ? g.C : g.K;
     if ((g.C & 3) || (g.K & 3) || N < 16 || Kg < 8 || M > 0x7fffffffLL) return false;      // 16-byte global strides
     long long tiles = ceil_div<long long>(M, TG_BM) * ceil_div<long long>(N, tg_bn(N));
@@ -303,6 +469,48 @@ int tma_gemm_fwd(const ConvGeom &g, int act, const float *x, const float *w, con
 int tma_gemm_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t stream) {
     DgradProblem p{g, dz, w, dx, accumulate};
     return tma_gemm_run(p, dz, (long long)g.B * g.H * g.W, g.K, w, g.C, false, stream, "conv2d_bwd_data[tf32,tma]");
+}
+
+size_t tma_gemm_workspace(const ConvGeom &g, int math) {
+    return tma_gemm_supported(g, math, 2) ? tg_wgrad_plan(g).ws_bytes : 0;
+}
+
+int tma_gemm_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
+                   cudaStream_t stream) {
+    const char *what = "conv2d_bwd_filter[tf32,tma]";
+    if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(dz) & 15)) {
+        set_error("%s: operands must be 16-byte aligned for the TMA path", what);
+        return FNET_ERR_ARG;
+    }
+    TgWgradPlan t = tg_wgrad_plan(g);
+    float *partial = nullptr;
+    if (t.splits > 1) {
+        if (!ws || ws_bytes < t.ws_bytes) {
+            set_error("%s: workspace of %zu bytes needed, %zu given", what, t.ws_bytes, ws_bytes);
+            return FNET_ERR_WORKSPACE;
+        }
+        partial = reinterpret_cast<float *>(ws);
+    }
+    const long long pixels = (long long)g.B * g.H * g.W;
+    CUtensorMap map_a, map_b;
+    if (!make_map(&map_a, x, pixels, g.C, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) ||
+        !make_map(&map_b, dz, pixels, g.K, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) {
+        set_error("%s: cuTensorMapEncodeTiled failed", what);
+        return FNET_ERR_CUDA;
+    }
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(tma_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
+        configured = true;
+    }
+    WgradProblem p{g, x, dz, dw, dbias, g.C};
+    const int M = g.C + (dbias ? 1 : 0);
+    tma_wgrad_kernel<<<(unsigned)(t.tiles * t.splits), TG_THREADS, t.smem, stream>>>(map_a, map_b, p, M, g.K, (int)pixels, t.bn, t.n_tiles,
+                                                                                     t.tiles, t.kt_per_split, t.stages, t.tmem_cols, partial);
+    int rc = check_launch(what);
+    if (rc == FNET_OK && t.splits > 1) rc = simt_reduce_wgrad_partials(g, dw, dbias, M, t.splits, partial, stream);
+    return rc;
 }
 
 }  // namespace fnet

@@ -34,6 +34,11 @@ int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, 
 bool tma_gemm_supported(const ConvGeom &g, int math, int product);   // product: 0 fwd, 1 dgrad
 int tma_gemm_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t stream);
 int tma_gemm_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t stream);
+size_t tma_gemm_workspace(const ConvGeom &g, int math);
+int tma_gemm_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
+                   cudaStream_t stream);
+int simt_reduce_wgrad_partials(const ConvGeom &g, float *dw, float *dbias, int M, int splits, const float *partial,
+                               cudaStream_t stream);
 
 // direct kernels for the classifier head and for small-channel convolutions (skinny.cu); fp32, any math mode
 bool skinny_supported(const ConvGeom &g, int product, bool with_bias);

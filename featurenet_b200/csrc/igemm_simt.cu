@@ -405,6 +405,14 @@ int simt_reduce_fwd_partials(const ConvGeom &g, int act, const float *bias, floa
     return check_launch("reduce_partials");
 }
 
+int simt_reduce_wgrad_partials(const ConvGeom &g, float *dw, float *dbias, int M, int splits, const float *partial,
+                               cudaStream_t stream) {
+    WgradProblem p{g, nullptr, nullptr, dw, dbias, g.kh * g.kw * g.C};
+    long long blocks = ceil_div<long long>((long long)M * g.K, 8), cap = (long long)kNumSMs * 8;
+    reduce_splits_kernel<WgradProblem><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, M, g.K, splits, partial);
+    return check_launch("reduce_partials");
+}
+
 int geom_checked(const fnet_conv2d_desc *d, ConvGeom &g, const char *what) { return geom_from_desc(d, g, what); }
 
 ConvGeom dense_geom(long long m, long long k, long long n) {
