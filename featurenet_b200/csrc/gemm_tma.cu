@@ -122,23 +122,27 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_co
     const uint32_t acc_stride = (uint32_t)tmem_cols / 2;      // column offset of the second accumulator
 
     if (warp == 0) {
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int m0 = (tile / n_tiles) * TG_BM, n0 = (tile % n_tiles) * BN;
-                for (int kt = 0; kt < KT; ++kt) {
-                    tg_bar_wait(&empty_bar[stage], phase ^ 1);
-                    const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
+        // every lane issues at most one box per stage: a 4 KB box costs as much issue time as a 16 KB one, so the
+        // MN-major operand (32 x 32 boxes) is spread over the lanes instead of being issued serially by one
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int m0 = (tile / n_tiles) * TG_BM, n0 = (tile % n_tiles) * BN;
+            for (int kt = 0; kt < KT; ++kt) {
+                tg_bar_wait(&empty_bar[stage], phase ^ 1);
+                const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
+                if (lane == 0) {
                     tg_bar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
                     tg_tma_2d(sa, &map_a, &full_bar[stage], kt * TG_BK, m0);
-                    if (B_MN) {
-                        for (int j = 0; j < BN / 32; ++j) tg_tma_2d(sb + j * 4096, &map_b, &full_bar[stage], n0 + 32 * j, kt * TG_BK);
-                    } else {
-                        tg_tma_2d(sb, &map_b, &full_bar[stage], kt * TG_BK, n0);
-                    }
-                    if (++stage == TG_STAGES) { stage = 0; phase ^= 1; }
                 }
+                if (B_MN) {
+                    if (lane >= 1 && lane <= BN / 32)
+                        tg_tma_2d(sb + (lane - 1) * 4096, &map_b, &full_bar[stage], n0 + 32 * (lane - 1), kt * TG_BK);
+                } else if (lane == 1) {
+                    tg_tma_2d(sb, &map_b, &full_bar[stage], kt * TG_BK, n0);
+                }
+                __syncwarp();
+                if (++stage == TG_STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -260,17 +264,17 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_c
     const uint32_t bias_col = (uint32_t)tmem_cols / 2;        // the column-sum accumulator
 
     if (warp == 0) {
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int kt = kt_begin; kt < kt_end; ++kt) {
-                tg_bar_wait(&empty_bar[stage], phase ^ 1);
-                const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
-                tg_bar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
-                for (int j = 0; j < TG_BM / 32; ++j) tg_tma_2d(sa + j * 4096, &map_a, &full_bar[stage], m0 + 32 * j, kt * TG_BK);
-                for (int j = 0; j < BN / 32; ++j) tg_tma_2d(sb + j * 4096, &map_b, &full_bar[stage], n0 + 32 * j, kt * TG_BK);
-                if (++stage == stages) { stage = 0; phase ^= 1; }
-            }
+        int stage = 0;                                        // lanes 0..3: the A boxes, lanes 4..: the B boxes
+        uint32_t phase = 0;
+        for (int kt = kt_begin; kt < kt_end; ++kt) {
+            tg_bar_wait(&empty_bar[stage], phase ^ 1);
+            const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
+            if (lane == 0) tg_bar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+            if (lane < TG_BM / 32) tg_tma_2d(sa + lane * 4096, &map_a, &full_bar[stage], m0 + 32 * lane, kt * TG_BK);
+            else if (lane - TG_BM / 32 < BN / 32)
+                tg_tma_2d(sb + (lane - TG_BM / 32) * 4096, &map_b, &full_bar[stage], n0 + 32 * (lane - TG_BM / 32), kt * TG_BK);
+            __syncwarp();
+            if (++stage == stages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
         if (lane == 0) {
