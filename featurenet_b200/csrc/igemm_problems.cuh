@@ -278,4 +278,52 @@ struct WgradProblem {
     }
 };
 
+// ------------------------------------------------------------------ split reductions
+// partial[z][M][N], z < splits: summed in a fixed order and handed to the problem's epilogue (no atomics, so a
+// result never depends on scheduling).  Few outputs and many splits: one warp per output element, lanes over
+// the splits and a fixed shuffle tree.  Many outputs: one thread per element, splits in sequence (coalesced).
+template <class P>
+__global__ void __launch_bounds__(256) reduce_splits_warp_kernel(P p, int M, int N, int splits,
+                                                                  const float *__restrict__ partial) {
+    long long total = (long long)M * N;
+    int lane = threadIdx.x & 31;
+    long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+    for (long long i = warp; i < total; i += nwarps) {
+        float s = 0.f;
+        for (int z = lane; z < splits; z += 32) s += partial[(long long)z * total + i];
+        s = warp_sum(s);
+        if (lane == 0) {
+            int m = (int)(i / N), n = (int)(i - (long long)m * N);
+            p.store(m, n, s);
+        }
+    }
+}
+
+template <class P>
+__global__ void __launch_bounds__(256) reduce_splits_flat_kernel(P p, int M, int N, int splits,
+                                                                  const float *__restrict__ partial) {
+    long long total = (long long)M * N;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += partial[(long long)z * total + i];
+        int m = (int)(i / N), n = (int)(i - (long long)m * N);
+        p.store(m, n, s);
+    }
+}
+
+template <class P>
+static int launch_reduce_splits(const P &p, int M, int N, int splits, const float *partial, cudaStream_t stream,
+                                const char *what) {
+    long long total = (long long)M * N;
+    if (splits <= 16 || total >= (1LL << 16)) {
+        long long blocks = ceil_div<long long>(total, 256), cap = (long long)kNumSMs * 8;
+        reduce_splits_flat_kernel<P><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, M, N, splits, partial);
+    } else {
+        long long blocks = ceil_div<long long>(total, 8), cap = (long long)kNumSMs * 8;
+        reduce_splits_warp_kernel<P><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, M, N, splits, partial);
+    }
+    return check_launch(what);
+}
+
 }  // namespace fnet

@@ -237,27 +237,6 @@ __global__ void __launch_bounds__(256, 3) igemm_simt_kernel(P p, int M, int N, i
     }
 }
 
-// Sums the split partials and applies the problem's epilogue.  One warp per output element: lanes
-// take splits lane, lane+32, ... and a fixed xor-shuffle tree adds them, so the result does not
-// depend on scheduling (deterministic) while the reduction is 32-way parallel.
-template <class P>
-__global__ void __launch_bounds__(256) reduce_splits_kernel(P p, int M, int N, int splits,
-                                                             const float *__restrict__ partial) {
-    long long total = (long long)M * N;
-    int lane = threadIdx.x & 31;
-    long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
-    for (long long i = warp; i < total; i += nwarps) {
-        float s = 0.f;
-        for (int z = lane; z < splits; z += 32) s += partial[(long long)z * total + i];
-        s = warp_sum(s);
-        if (lane == 0) {
-            int m = (int)(i / N), n = (int)(i - (long long)m * N);
-            p.store(m, n, s);
-        }
-    }
-}
-
 struct SplitPlan {
     int bm, bn, splits, k_per_split, bk, m_tiles;
     size_t ws_bytes;
@@ -335,13 +314,7 @@ static int run_problem(const P &p, long long M, long long N, long long Kg, void 
     }
     int rc = check_launch(what);
     if (rc != FNET_OK) return rc;
-    if (plan.splits > 1) {
-        long long warps = M * N;
-        long long blocks = ceil_div<long long>(warps, 8);
-        long long cap = (long long)kNumSMs * 8;
-        reduce_splits_kernel<P><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, m, n, plan.splits, partial);
-        rc = check_launch(what);
-    }
+    if (plan.splits > 1) rc = launch_reduce_splits(p, m, n, plan.splits, partial, stream, what);
     return rc;
 }
 
@@ -400,17 +373,13 @@ int simt_reduce_fwd_partials(const ConvGeom &g, int act, const float *bias, floa
                              cudaStream_t stream) {
     FwdProblem p{g, nullptr, nullptr, bias, y, act};
     long long M = (long long)g.B * g.Ho * g.Wo;
-    long long blocks = ceil_div<long long>(M * g.K, 8), cap = (long long)kNumSMs * 8;
-    reduce_splits_kernel<FwdProblem><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, (int)M, g.K, splits, partial);
-    return check_launch("reduce_partials");
+    return launch_reduce_splits(p, (int)M, g.K, splits, partial, stream, "reduce_partials");
 }
 
 int simt_reduce_wgrad_partials(const ConvGeom &g, float *dw, float *dbias, int M, int splits, const float *partial,
                                cudaStream_t stream) {
     WgradProblem p{g, nullptr, nullptr, dw, dbias, g.kh * g.kw * g.C};
-    long long blocks = ceil_div<long long>((long long)M * g.K, 8), cap = (long long)kNumSMs * 8;
-    reduce_splits_kernel<WgradProblem><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, M, g.K, splits, partial);
-    return check_launch("reduce_partials");
+    return launch_reduce_splits(p, M, g.K, splits, partial, stream, "reduce_partials");
 }
 
 int geom_checked(const fnet_conv2d_desc *d, ConvGeom &g, const char *what) { return geom_from_desc(d, g, what); }

@@ -387,24 +387,6 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)TMEM_COLS) : "memory");
 }
 
-template <class P>
-__global__ void __launch_bounds__(256) tc_reduce_splits_kernel(P p, int M, int N, int splits,
-                                                                const float *__restrict__ partial) {
-    long long total = (long long)M * N;
-    int lane = threadIdx.x & 31;
-    long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
-    for (long long i = warp; i < total; i += nwarps) {
-        float s = 0.f;
-        for (int z = lane; z < splits; z += 32) s += partial[(long long)z * total + i];
-        s = warp_sum(s);
-        if (lane == 0) {
-            int m = (int)(i / N), n = (int)(i - (long long)m * N);
-            p.store(m, n, s);
-        }
-    }
-}
-
 struct TcPlan {
     int bn, splits, k_per_split, stages;
     size_t ws_bytes, smem_bytes;
@@ -478,11 +460,7 @@ static int tc_run(const P &p, int math, long long M, long long N, long long Kg, 
     else rc = plan.bn == 32 ? FNET_TC_LAUNCH(32, 3, 0) : (plan.bn == 64 ? FNET_TC_LAUNCH(64, 3, 0) : FNET_TC_LAUNCH(128, 3, 0));
 #undef FNET_TC_LAUNCH
     if (rc != FNET_OK) return rc;
-    if (plan.splits > 1) {
-        long long blocks = ceil_div<long long>(M * N, 8), cap = (long long)kNumSMs * 8;
-        tc_reduce_splits_kernel<P><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, m, n, plan.splits, partial);
-        rc = check_launch(what);
-    }
+    if (plan.splits > 1) rc = launch_reduce_splits(p, m, n, plan.splits, partial, stream, what);
     return rc;
 }
 
