@@ -48,6 +48,24 @@ def quiet():
     return contextlib.redirect_stdout(io.StringIO())
 
 
+# The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner), so
+# file descriptor 1 is pointed at stderr for the whole run and the JSON line goes to a private copy of the real one.
+_JSON_OUT = None
+
+
+def claim_stdout():
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def build_candidate(workload):
     from model.keras_model import KerasFeatureModel
     from products_tree import ProductSet
@@ -156,7 +174,7 @@ def run_reference(args):
         "e2e": {"value": rate, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": time.perf_counter() - t0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def measure_workload(workload, args, torch, dist, world, device_index, full=True):
@@ -394,7 +412,7 @@ def run_ours(args):
                                     "sample": "%d train steps of batch %d in %.1f s through oracle/torch_cpu.py"
                                               % (done, BATCH, elapsed)}
         line["wall_s"] = time.perf_counter() - t_wall
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -412,6 +430,7 @@ def main():
     ap.add_argument("--population", type=int, default=32, help="candidates of the sharded population run (0 = skip)")
     ap.add_argument("--resident", type=int, default=4, help="candidates kept resident per GPU in the population run")
     args = ap.parse_args()
+    claim_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
