@@ -380,14 +380,27 @@ def run_ours(args):
                 extra[other] = {"images_per_s": res["value"], "ms_per_step": res["ms"] / args.steps,
                                 "params": res["params"], "train_mflop_per_image": res["train_mflop_per_image"],
                                 "launch_calls_per_step": res["launch_calls_per_step"],
-                                "workload": WORKLOADS[other][3]}
+                                "workload": WORKLOADS[other][3], "dtype": "f32"}
+                # the same step in the two tensor-core modes (reported beside, never as the headline):
+                # tf32x3 = split operands, fp32 tolerance; tf32 = plain tf32 operands, 5e-3 per-op tolerance
+                saved = os.environ.get("FNET_PRECISION")
+                by_mode = {}
+                for mode in ("tf32x3", "tf32"):
+                    os.environ["FNET_PRECISION"] = mode
+                    alt, _ = measure_workload(other, args, torch, dist, 1, local, full=False)
+                    by_mode[mode] = alt["ms"] / args.steps
+                if saved is None:
+                    os.environ.pop("FNET_PRECISION", None)
+                else:
+                    os.environ["FNET_PRECISION"] = saved
+                extra[other]["ms_per_step_tensor_core_modes"] = by_mode
     population = run_population_bench(args, dist, world, rank) if args.population > 0 else None
     if rank == 0:
         pk = peaks()
         line = {
             "metric": METRIC, "value": main["value"], "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": main["ms"] / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "f32 (tf32x3 on tensor cores)"}.get(os.environ.get("FNET_PRECISION", "fp32").lower(), "f32"), "data": "synthetic",
             "config": {"workload": WORKLOADS[args.workload][3], "batch": BATCH, "optimizer": "adam(1e-3)",
                        "parallelism": "candidate-sharded x%d (no collective)" % world,
                        "l2": "inputs larger than L2: the 614 MB resident dataset is streamed batch by batch; "
