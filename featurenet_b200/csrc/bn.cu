@@ -32,11 +32,12 @@ static BnShape bn_shape(int outer, int a, int inner) {
     return s;
 }
 
-// element e of the chunk [o0, o1) x inner of row a
-__device__ __forceinline__ int64_t bn_index(const BnShape &s, int a, int o0, int64_t e) {
-    int64_t o = o0 + e / s.inner;
-    int64_t j = e - (e / s.inner) * s.inner;
-    return (o * s.a + a) * s.inner + j;
+// element e of the chunk [o0, o1) x inner of row a.  32-bit on purpose: a 64-bit division per element made
+// these kernels instruction-bound (outer * inner < 2^31 is checked on the host).
+__device__ __forceinline__ int64_t bn_index(const BnShape &s, int a, int o0, unsigned e) {
+    unsigned q = e / (unsigned)s.inner;
+    unsigned j = e - q * (unsigned)s.inner;
+    return ((int64_t)(o0 + q) * s.a + a) * s.inner + j;
 }
 
 __global__ void __launch_bounds__(256) bn_stats_partial_kernel(BnShape s, const float *__restrict__ x,
@@ -47,7 +48,7 @@ __global__ void __launch_bounds__(256) bn_stats_partial_kernel(BnShape s, const 
     float shift = __ldg(x + (int64_t)a * s.inner);
     int64_t count = (int64_t)(o1 - o0) * s.inner;
     float s1 = 0.f, s2 = 0.f;
-    for (int64_t e = threadIdx.x; e < count; e += blockDim.x) {
+    for (unsigned e = threadIdx.x; e < (unsigned)count; e += blockDim.x) {
         float v = __ldg(x + bn_index(s, a, o0, e)) - shift;
         s1 += v;
         s2 = fmaf(v, v, s2);
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(256) bn_normalize_train_kernel(BnShape s, floa
     float off = __ldg(beta + a) - stat[0] * inv;
     int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
     int64_t count = (int64_t)(o1 - o0) * s.inner;
-    for (int64_t e = threadIdx.x; e < count; e += blockDim.x) {
+    for (unsigned e = threadIdx.x; e < (unsigned)count; e += blockDim.x) {
         int64_t at = bn_index(s, a, o0, e);
         y[at] = fmaf(__ldg(x + at), inv, off);
     }
@@ -109,7 +110,7 @@ __global__ void __launch_bounds__(256) bn_infer_kernel(int64_t total, int a_len,
                                                        const float *__restrict__ beta, const float *__restrict__ mean,
                                                        const float *__restrict__ var, float *__restrict__ y) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        int a = (int)((i / inner) % a_len);
+        int a = (int)(((unsigned)i / (unsigned)inner) % (unsigned)a_len);
         float v = __ldg(var + a) + eps;
         float rstd = rsqrtf(v);
         rstd = rstd * (1.5f - 0.5f * v * rstd * rstd);
@@ -129,7 +130,7 @@ __global__ void __launch_bounds__(256) bn_bwd_partial_kernel(BnShape s, const fl
     float mean = __ldg(save_mean + a), rstd = __ldg(save_rstd + a);
     int64_t count = (int64_t)(o1 - o0) * s.inner;
     float sb = 0.f, sg = 0.f;
-    for (int64_t e = threadIdx.x; e < count; e += blockDim.x) {
+    for (unsigned e = threadIdx.x; e < (unsigned)count; e += blockDim.x) {
         int64_t at = bn_index(s, a, o0, e);
         float g = __ldg(dy + at);
         sb += g;
@@ -172,7 +173,7 @@ __global__ void __launch_bounds__(256) bn_bwd_dx_kernel(BnShape s, const float *
     float sb = sums[0], sg = sums[1];
     int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
     int64_t count = (int64_t)(o1 - o0) * s.inner;
-    for (int64_t e = threadIdx.x; e < count; e += blockDim.x) {
+    for (unsigned e = threadIdx.x; e < (unsigned)count; e += blockDim.x) {
         int64_t at = bn_index(s, a, o0, e);
         float xhat = (__ldg(x + at) - mean) * rstd;
         float v = k * (n * __ldg(dy + at) - sb - xhat * sg);
@@ -191,7 +192,7 @@ size_t fnet_bn_workspace_bytes(int32_t a) { return a > 0 ? (size_t)a * kBnMaxSpl
 int fnet_bn_fwd_train(int32_t outer, int32_t a, int32_t inner, float eps, float momentum, const float *x,
                       const float *gamma, const float *beta, float *y, float *save_mean, float *save_rstd,
                       float *moving_mean, float *moving_var, void *ws, size_t ws_bytes, void *stream) {
-    FNET_REQUIRE(outer > 0 && a > 0 && inner > 0, "fnet_bn_fwd_train: bad shape");
+    FNET_REQUIRE(outer > 0 && a > 0 && inner > 0 && (int64_t)outer * a * inner < 0x7fffffffLL, "fnet_bn_fwd_train: bad shape");
     FNET_REQUIRE(x && gamma && beta && y && save_mean && save_rstd && moving_mean && moving_var,
                  "fnet_bn_fwd_train: null pointer");
     if (!ws || ws_bytes < fnet_bn_workspace_bytes(a)) {
@@ -211,7 +212,7 @@ int fnet_bn_fwd_train(int32_t outer, int32_t a, int32_t inner, float eps, float 
 
 int fnet_bn_fwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const float *x, const float *gamma,
                       const float *beta, const float *moving_mean, const float *moving_var, float *y, void *stream) {
-    FNET_REQUIRE(outer >= 0 && a > 0 && inner > 0, "fnet_bn_fwd_infer: bad shape");
+    FNET_REQUIRE(outer >= 0 && a > 0 && inner > 0 && (int64_t)outer * a * inner < 0x7fffffffLL, "fnet_bn_fwd_infer: bad shape");
     FNET_REQUIRE(x && gamma && beta && moving_mean && moving_var && y, "fnet_bn_fwd_infer: null pointer");
     int64_t total = (int64_t)outer * a * inner;
     if (total == 0) return FNET_OK;
@@ -223,7 +224,7 @@ int fnet_bn_fwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const 
 int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,
                 const float *save_mean, const float *save_rstd, float *dx, float *dgamma, float *dbeta,
                 int accumulate, void *ws, size_t ws_bytes, void *stream) {
-    FNET_REQUIRE(outer > 0 && a > 0 && inner > 0, "fnet_bn_bwd: bad shape");
+    FNET_REQUIRE(outer > 0 && a > 0 && inner > 0 && (int64_t)outer * a * inner < 0x7fffffffLL, "fnet_bn_bwd: bad shape");
     FNET_REQUIRE(x && dy && gamma && save_mean && save_rstd && dx && dgamma && dbeta, "fnet_bn_bwd: null pointer");
     if (!ws || ws_bytes < fnet_bn_workspace_bytes(a)) {
         set_error("fnet_bn_bwd: workspace of %zu bytes needed, %zu given", fnet_bn_workspace_bytes(a), ws_bytes);

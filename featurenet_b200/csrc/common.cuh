@@ -52,6 +52,27 @@ inline int stream_grid(int64_t work_items, int threads) {
     return (int)blocks;
 }
 
+// i -> (b, h, w, c) of a dense [B][d1][d2][d3] tensor.  32-bit arithmetic whenever the index allows: a 64-bit
+// division is a long software routine, and the streaming kernels do three per element to decode their index.
+__device__ __forceinline__ void decode4(int64_t i, int d1, int d2, int d3, int64_t &b, int &h, int &w, int &c) {
+    if (i < 0x7fffffffLL) {
+        unsigned u = (unsigned)i, t = u / (unsigned)d3;
+        c = (int)(u - t * (unsigned)d3);
+        unsigned t2 = t / (unsigned)d2;
+        w = (int)(t - t2 * (unsigned)d2);
+        unsigned t3 = t2 / (unsigned)d1;
+        h = (int)(t2 - t3 * (unsigned)d1);
+        b = t3;
+    } else {
+        c = (int)(i % d3);
+        int64_t t = i / d3;
+        w = (int)(t % d2);
+        t /= d2;
+        h = (int)(t % d1);
+        b = t / d1;
+    }
+}
+
 __device__ __forceinline__ float act_apply(float z, int act) {
     switch (act) {
         case FNET_ACT_RELU: return fmaxf(z, 0.f);

@@ -14,12 +14,9 @@ __global__ void __launch_bounds__(256) dw_fwd_kernel(fnet_conv2d_desc d, const f
     int C = d.in_c;
     int64_t total = (int64_t)d.batch * d.out_h * d.out_w * C;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        int c = (int)(i % C);
-        int64_t t = i / C;
-        int wo = (int)(t % d.out_w);
-        t /= d.out_w;
-        int ho = (int)(t % d.out_h);
-        int64_t b = t / d.out_h;
+        int c, wo, ho;
+        int64_t b;
+        decode4(i, d.out_h, d.out_w, C, b, ho, wo, c);
         int h0 = ho * d.stride_h - d.pad_top, w0 = wo * d.stride_w - d.pad_left;
         const float *img = x + b * d.in_h * d.in_w * C + c;
         float acc = 0.f;
@@ -43,12 +40,9 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(fnet_conv2d_desc d, const
     int C = d.in_c;
     int64_t total = (int64_t)d.batch * d.in_h * d.in_w * C;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        int c = (int)(i % C);
-        int64_t t = i / C;
-        int wi = (int)(t % d.in_w);
-        t /= d.in_w;
-        int hi = (int)(t % d.in_h);
-        int64_t b = t / d.in_h;
+        int c, wi, hi;
+        int64_t b;
+        decode4(i, d.in_h, d.in_w, C, b, hi, wi, c);
         const float *img = dz + b * d.out_h * d.out_w * C + c;
         float acc = 0.f;
         for (int r = 0; r < d.kh; ++r) {

@@ -7,18 +7,21 @@
 
 namespace fnet {
 
+// I = index type: 32-bit whenever the tensor has fewer than 2^31 elements (always, in practice) -- 64-bit
+// division is a long software routine and these kernels do four of them per element to decode an index.
+template <typename I>
 __global__ void __launch_bounds__(256) pool_fwd_kernel(fnet_pool2d_desc d, const float *__restrict__ x,
                                                        float *__restrict__ y, uint8_t *__restrict__ argmax) {
-    int64_t total = (int64_t)d.batch * d.out_h * d.out_w * d.channels;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        int c = (int)(i % d.channels);
-        int64_t t = i / d.channels;
-        int wo = (int)(t % d.out_w);
-        t /= d.out_w;
-        int ho = (int)(t % d.out_h);
-        int64_t b = t / d.out_h;
+    I total = (I)d.batch * d.out_h * d.out_w * d.channels;
+    for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
+        int c = (int)(i % (I)d.channels);
+        I t = i / (I)d.channels;
+        int wo = (int)(t % (I)d.out_w);
+        t /= (I)d.out_w;
+        int ho = (int)(t % (I)d.out_h);
+        I b = t / (I)d.out_h;
         int h0 = ho * d.stride_h - d.pad_top, w0 = wo * d.stride_w - d.pad_left;
-        const float *img = x + b * d.in_h * d.in_w * d.channels + c;
+        const float *img = x + (int64_t)b * d.in_h * d.in_w * d.channels + c;
         if (d.kind == FNET_POOL_MAX) {
             float best = -INFINITY;
             int arg = 0;
@@ -28,7 +31,7 @@ __global__ void __launch_bounds__(256) pool_fwd_kernel(fnet_pool2d_desc d, const
                 for (int s = 0; s < d.kw; ++s) {
                     int w = w0 + s;
                     if ((unsigned)w >= (unsigned)d.in_w) continue;
-                    float v = __ldg(img + ((int64_t)h * d.in_w + w) * d.channels);
+                    float v = __ldg(img + (h * d.in_w + w) * d.channels);
                     if (v > best) { best = v; arg = r * d.kw + s; }   // strict: first maximum wins
                 }
             }
@@ -43,7 +46,7 @@ __global__ void __launch_bounds__(256) pool_fwd_kernel(fnet_pool2d_desc d, const
                 for (int s = 0; s < d.kw; ++s) {
                     int w = w0 + s;
                     if ((unsigned)w >= (unsigned)d.in_w) continue;
-                    sum += __ldg(img + ((int64_t)h * d.in_w + w) * d.channels);
+                    sum += __ldg(img + (h * d.in_w + w) * d.channels);
                     ++cnt;
                 }
             }
@@ -59,30 +62,40 @@ __device__ __forceinline__ int taps_in_bounds(int o, int stride, int pad, int k,
     return hi - lo;
 }
 
+// v / stride when exact and below extent, else -1 (strides are 1 or 2 in practice: no division)
+__device__ __forceinline__ int pool_exact_div(int v, int stride, int extent) {
+    int o;
+    if (stride == 1) o = v;
+    else if (stride == 2) { if (v & 1) return -1; o = v >> 1; }
+    else { o = v / stride; if (o * stride != v) return -1; }
+    return o < extent ? o : -1;
+}
+
+template <typename I>
 __global__ void __launch_bounds__(256) pool_bwd_kernel(fnet_pool2d_desc d, const float *__restrict__ dy,
                                                        const uint8_t *__restrict__ argmax, float *__restrict__ dx,
                                                        int accumulate) {
-    int64_t total = (int64_t)d.batch * d.in_h * d.in_w * d.channels;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        int c = (int)(i % d.channels);
-        int64_t t = i / d.channels;
-        int w = (int)(t % d.in_w);
-        t /= d.in_w;
-        int h = (int)(t % d.in_h);
-        int64_t b = t / d.in_h;
-        int64_t out_img = b * d.out_h * d.out_w;
+    I total = (I)d.batch * d.in_h * d.in_w * d.channels;
+    for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
+        int c = (int)(i % (I)d.channels);
+        I t = i / (I)d.channels;
+        int w = (int)(t % (I)d.in_w);
+        t /= (I)d.in_w;
+        int h = (int)(t % (I)d.in_h);
+        I b = t / (I)d.in_h;
+        I out_img = b * d.out_h * d.out_w;
         float g = 0.f;
         for (int r = 0; r < d.kh; ++r) {
             int hh = h + d.pad_top - r;
             if (hh < 0) break;
-            int ho = hh / d.stride_h;
-            if (ho * d.stride_h != hh || ho >= d.out_h) continue;
+            int ho = pool_exact_div(hh, d.stride_h, d.out_h);
+            if (ho < 0) continue;
             for (int s = 0; s < d.kw; ++s) {
                 int ww = w + d.pad_left - s;
                 if (ww < 0) break;
-                int wo = ww / d.stride_w;
-                if (wo * d.stride_w != ww || wo >= d.out_w) continue;
-                int64_t o = ((out_img + (int64_t)ho * d.out_w + wo) * d.channels) + c;
+                int wo = pool_exact_div(ww, d.stride_w, d.out_w);
+                if (wo < 0) continue;
+                I o = ((out_img + (I)ho * d.out_w + wo) * d.channels) + c;
                 if (d.kind == FNET_POOL_MAX) {
                     if (argmax[o] == (uint8_t)(r * d.kw + s)) g += __ldg(dy + o);
                 } else {
@@ -150,7 +163,11 @@ int fnet_pool2d_fwd(const fnet_pool2d_desc *d, const float *x, float *y, uint8_t
     FNET_REQUIRE(x && y, "fnet_pool2d_fwd: null pointer");
     int64_t total = (int64_t)d->batch * d->out_h * d->out_w * d->channels;
     if (total == 0) return FNET_OK;
-    pool_fwd_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, x, y, argmax);
+    int64_t in_total = (int64_t)d->batch * d->in_h * d->in_w * d->channels;
+    if (total < 0x7fffffffLL - (1 << 26) && in_total < 0x7fffffffLL)      // the grid-stride increment must not overflow either
+        pool_fwd_kernel<int><<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, x, y, argmax);
+    else
+        pool_fwd_kernel<int64_t><<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, x, y, argmax);
     return check_launch("fnet_pool2d_fwd");
 }
 
@@ -162,7 +179,10 @@ int fnet_pool2d_bwd(const fnet_pool2d_desc *d, const float *dy, const uint8_t *a
     FNET_REQUIRE(d->kind != FNET_POOL_MAX || argmax != nullptr, "fnet_pool2d_bwd: max pooling needs the argmax of the forward");
     int64_t total = (int64_t)d->batch * d->in_h * d->in_w * d->channels;
     if (total == 0) return FNET_OK;
-    pool_bwd_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, dy, argmax, dx, accumulate);
+    if (total < 0x7fffffffLL - (1 << 26))
+        pool_bwd_kernel<int><<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, dy, argmax, dx, accumulate);
+    else
+        pool_bwd_kernel<int64_t><<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, dy, argmax, dx, accumulate);
     return check_launch("fnet_pool2d_bwd");
 }
 
