@@ -395,6 +395,18 @@ def run_ours(args):
                     os.environ["FNET_PRECISION"] = saved
                 extra[other]["ms_per_step_tensor_core_modes"] = by_mode
     population = run_population_bench(args, dist, world, rank) if args.population > 0 else None
+    if population is not None and world == 1 and not args.quick:
+        # the same population in the two tensor-core modes, reported beside the fp32 figure
+        saved = os.environ.get("FNET_PRECISION")
+        by_mode = {}
+        for mode in ("tf32x3", "tf32"):
+            os.environ["FNET_PRECISION"] = mode
+            by_mode[mode] = run_population_bench(args, dist, world, rank)["candidates_per_hour"]
+        if saved is None:
+            os.environ.pop("FNET_PRECISION", None)
+        else:
+            os.environ["FNET_PRECISION"] = saved
+        population["candidates_per_hour_tensor_core_modes"] = by_mode
     if rank == 0:
         pk = peaks()
         line = {
@@ -424,6 +436,13 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": rate, "unit": "images/s", "cores": threads, "kind": "port",
                                     "sample": "%d train steps of batch %d in %.1f s through oracle/torch_cpu.py"
                                               % (done, BATCH, elapsed)}
+        # whole-step roofline: every launch at the better of its two ceilings vs the measured step
+        profiled_steps = max(1, min(args.steps, 50))
+        ideal_s = sum(max(r["flops"] / (pk["tflops"] * 1e12), r["bytes"] / (pk["hbm_gbs"] * 1e9))
+                      for r in main["profile"].values()) / profiled_steps
+        line["roofline"]["whole_step"] = {
+            "ideal_us": 1e6 * ideal_s, "measured_us": 1e3 * line["ms_per_step"], "frac": 1e3 * ideal_s / line["ms_per_step"],
+            "formula": "sum over launches of max(flops / peak_tensor, bytes / peak_hbm), over the measured step time"}
         line["wall_s"] = time.perf_counter() - t_wall
         emit(line)
     if world > 1:
