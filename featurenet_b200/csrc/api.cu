@@ -15,6 +15,7 @@ void set_error(const char *fmt, ...) {
 // ---------------------------------------------------------------- loop state
 // state[0] t (completed iterations)  state[1] cursor  state[2] lr  state[3] lr_t
 __global__ void step_begin_kernel(int32_t *state, float beta1, float beta2) {
+    pdl_prologue();
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         double t = (double)(state[0] + 1);
         double lr = (double)__int_as_float(state[2]);
@@ -26,6 +27,7 @@ __global__ void step_begin_kernel(int32_t *state, float beta1, float beta2) {
 }
 
 __global__ void step_end_kernel(int32_t *state, int32_t batch) {
+    pdl_prologue();
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         state[0] += 1;
         state[1] += batch;
@@ -33,12 +35,14 @@ __global__ void step_end_kernel(int32_t *state, int32_t batch) {
 }
 
 __global__ void fill_kernel(int64_t n, float value, float *__restrict__ dst) {
+    pdl_prologue();
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; i < n; i += stride) dst[i] = value;
 }
 
 __global__ void u8_to_f32_kernel(int64_t n, const uint8_t *__restrict__ src, float scale, float *__restrict__ dst) {
+    pdl_prologue();
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     // same rounding as numpy: x.astype(float32) then an fp32 divide by 255 (scale is the divisor)
@@ -49,6 +53,7 @@ __global__ void u8_to_f32_kernel(int64_t n, const uint8_t *__restrict__ src, flo
 __global__ void gather_rows_kernel(int32_t batch, int64_t row_elems, const int32_t *__restrict__ perm,
                                    const int32_t *__restrict__ state, const float *__restrict__ src,
                                    float *__restrict__ dst) {
+    pdl_prologue();
     int32_t cursor = state[1];
     for (int32_t row = blockIdx.y; row < batch; row += gridDim.y) {
         int64_t from = (int64_t)perm[cursor + row] * row_elems;
@@ -73,6 +78,7 @@ __global__ void gather_batch_kernel(int32_t batch, int64_t x_row, int64_t y_row,
                                     int32_t *__restrict__ state, const float *__restrict__ x_src,
                                     const float *__restrict__ y_src, float *__restrict__ x_dst, float *__restrict__ y_dst,
                                     int begin_step, float beta1, float beta2) {
+    pdl_prologue();
     const int32_t cursor = state[1];
     if (begin_step && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
         double t = (double)(state[0] + 1);
@@ -115,7 +121,7 @@ int fnet_gather_batch(int32_t batch, int64_t x_row, int64_t y_row, const int32_t
     int bx = (int)ceil_div<int64_t>(vec, 256);
     if (bx > 8) bx = 8;
     dim3 grid(bx, batch > 4096 ? 4096 : batch);
-    gather_batch_kernel<<<grid, 256, 0, as_stream(stream)>>>(batch, x_row, y_row, perm, state, x_src, y_src, x_dst, y_dst,
+    launch_pdl(gather_batch_kernel, dim3(grid), dim3(256), 0, as_stream(stream), batch, x_row, y_row, perm, state, x_src, y_src, x_dst, y_dst,
                                                              begin_step, beta1, beta2);
     return check_launch("fnet_gather_batch");
 }
@@ -126,27 +132,27 @@ const char *fnet_last_error(void) { return g_error; }
 
 int fnet_step_begin(int32_t *state, float beta1, float beta2, void *stream) {
     FNET_REQUIRE(state != nullptr, "fnet_step_begin: null state");
-    step_begin_kernel<<<1, 32, 0, as_stream(stream)>>>(state, beta1, beta2);
+    launch_pdl(step_begin_kernel, dim3(1), dim3(32), 0, as_stream(stream), state, beta1, beta2);
     return check_launch("fnet_step_begin");
 }
 
 int fnet_step_end(int32_t *state, int32_t batch, void *stream) {
     FNET_REQUIRE(state != nullptr, "fnet_step_end: null state");
-    step_end_kernel<<<1, 32, 0, as_stream(stream)>>>(state, batch);
+    launch_pdl(step_end_kernel, dim3(1), dim3(32), 0, as_stream(stream), state, batch);
     return check_launch("fnet_step_end");
 }
 
 int fnet_fill(int64_t n, float value, float *dst, void *stream) {
     FNET_REQUIRE(n >= 0 && (dst != nullptr || n == 0), "fnet_fill: bad arguments");
     if (n == 0) return FNET_OK;
-    fill_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(n, value, dst);
+    launch_pdl(fill_kernel, dim3(stream_grid(n, 256)), dim3(256), 0, as_stream(stream), n, value, dst);
     return check_launch("fnet_fill");
 }
 
 int fnet_u8_to_f32(int64_t n, const uint8_t *src, float scale, float *dst, void *stream) {
     FNET_REQUIRE(n >= 0 && scale != 0.f, "fnet_u8_to_f32: bad arguments");
     if (n == 0) return FNET_OK;
-    u8_to_f32_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(n, src, scale, dst);
+    launch_pdl(u8_to_f32_kernel, dim3(stream_grid(n, 256)), dim3(256), 0, as_stream(stream), n, src, scale, dst);
     return check_launch("fnet_u8_to_f32");
 }
 
@@ -159,7 +165,7 @@ int fnet_gather_rows(int32_t batch, int64_t row_elems, const int32_t *perm, cons
     int bx = (int)ceil_div<int64_t>(vec, 256);
     if (bx > 8) bx = 8;
     dim3 grid(bx, batch > 4096 ? 4096 : batch);
-    gather_rows_kernel<<<grid, 256, 0, as_stream(stream)>>>(batch, row_elems, perm, state, src, dst);
+    launch_pdl(gather_rows_kernel, dim3(grid), dim3(256), 0, as_stream(stream), batch, row_elems, perm, state, src, dst);
     return check_launch("fnet_gather_rows");
 }
 

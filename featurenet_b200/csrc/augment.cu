@@ -14,6 +14,7 @@ __global__ void __launch_bounds__(256) gather_shift_flip_kernel(int batch, int H
                                                                 const float *__restrict__ tx, const float *__restrict__ ty,
                                                                 const uint8_t *__restrict__ flip,
                                                                 const float *__restrict__ src, float *__restrict__ dst) {
+    pdl_prologue();
     const int cursor = state[1];
     const int64_t per_image = (int64_t)H * W * C;
     const int64_t total = (int64_t)batch * per_image;
@@ -52,7 +53,7 @@ extern "C" int fnet_gather_shift_flip(int32_t batch, int32_t h, int32_t w, int32
     FNET_REQUIRE(perm && state && tx && ty && flip && src && dst, "fnet_gather_shift_flip: null pointer");
     if (batch == 0) return FNET_OK;
     int64_t total = (int64_t)batch * h * w * c;
-    gather_shift_flip_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(batch, h, w, c, perm, state, tx, ty,
+    launch_pdl(gather_shift_flip_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), batch, h, w, c, perm, state, tx, ty,
                                                                                    flip, src, dst);
     return check_launch("fnet_gather_shift_flip");
 }

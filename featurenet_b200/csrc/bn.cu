@@ -42,6 +42,7 @@ __device__ __forceinline__ int64_t bn_index(const BnShape &s, int a, int o0, uns
 
 __global__ void __launch_bounds__(256) bn_stats_partial_kernel(BnShape s, const float *__restrict__ x,
                                                                float *__restrict__ partial) {
+    pdl_prologue();
     __shared__ float red[32];
     int a = blockIdx.x, part = blockIdx.y;
     int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
@@ -69,6 +70,7 @@ __global__ void __launch_bounds__(256) bn_normalize_train_kernel(BnShape s, floa
                                                                  float *__restrict__ save_mean, float *__restrict__ save_rstd,
                                                                  float *__restrict__ moving_mean,
                                                                  float *__restrict__ moving_var) {
+    pdl_prologue();
     __shared__ float stat[2];
     int a = blockIdx.x, part = blockIdx.y;
     if (threadIdx.x == 0) {
@@ -109,6 +111,7 @@ __global__ void __launch_bounds__(256) bn_infer_kernel(int64_t total, int a_len,
                                                        const float *__restrict__ x, const float *__restrict__ gamma,
                                                        const float *__restrict__ beta, const float *__restrict__ mean,
                                                        const float *__restrict__ var, float *__restrict__ y) {
+    pdl_prologue();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         int a = (int)(((unsigned)i / (unsigned)inner) % (unsigned)a_len);
         float v = __ldg(var + a) + eps;
@@ -124,6 +127,7 @@ __global__ void __launch_bounds__(256) bn_bwd_partial_kernel(BnShape s, const fl
                                                              const float *__restrict__ save_mean,
                                                              const float *__restrict__ save_rstd,
                                                              float *__restrict__ partial) {
+    pdl_prologue();
     __shared__ float red[32];
     int a = blockIdx.x, part = blockIdx.y;
     int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
@@ -151,6 +155,7 @@ __global__ void __launch_bounds__(256) bn_bwd_dx_kernel(BnShape s, const float *
                                                         const float *__restrict__ partial, float *__restrict__ dx,
                                                         float *__restrict__ dgamma, float *__restrict__ dbeta,
                                                         int accumulate) {
+    pdl_prologue();
     __shared__ float sums[2];
     int a = blockIdx.x, part = blockIdx.y;
     if (threadIdx.x == 0) {
@@ -202,10 +207,10 @@ int fnet_bn_fwd_train(int32_t outer, int32_t a, int32_t inner, float eps, float 
     BnShape s = bn_shape(outer, a, inner);
     dim3 grid(a, s.splits);
     float *partial = reinterpret_cast<float *>(ws);
-    bn_stats_partial_kernel<<<grid, 256, 0, as_stream(stream)>>>(s, x, partial);
+    launch_pdl(bn_stats_partial_kernel, dim3(grid), dim3(256), 0, as_stream(stream), s, x, partial);
     int rc = check_launch("fnet_bn_fwd_train");
     if (rc) return rc;
-    bn_normalize_train_kernel<<<grid, 256, 0, as_stream(stream)>>>(s, eps, momentum, x, gamma, beta, partial, y,
+    launch_pdl(bn_normalize_train_kernel, dim3(grid), dim3(256), 0, as_stream(stream), s, eps, momentum, x, gamma, beta, partial, y,
                                                                    save_mean, save_rstd, moving_mean, moving_var);
     return check_launch("fnet_bn_fwd_train");
 }
@@ -216,7 +221,7 @@ int fnet_bn_fwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const 
     FNET_REQUIRE(x && gamma && beta && moving_mean && moving_var && y, "fnet_bn_fwd_infer: null pointer");
     int64_t total = (int64_t)outer * a * inner;
     if (total == 0) return FNET_OK;
-    bn_infer_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(total, a, inner, eps, x, gamma, beta,
+    launch_pdl(bn_infer_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), total, a, inner, eps, x, gamma, beta,
                                                                             moving_mean, moving_var, y);
     return check_launch("fnet_bn_fwd_infer");
 }
@@ -233,10 +238,10 @@ int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const f
     BnShape s = bn_shape(outer, a, inner);
     dim3 grid(a, s.splits);
     float *partial = reinterpret_cast<float *>(ws);
-    bn_bwd_partial_kernel<<<grid, 256, 0, as_stream(stream)>>>(s, x, dy, save_mean, save_rstd, partial);
+    launch_pdl(bn_bwd_partial_kernel, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, save_mean, save_rstd, partial);
     int rc = check_launch("fnet_bn_bwd");
     if (rc) return rc;
-    bn_bwd_dx_kernel<<<grid, 256, 0, as_stream(stream)>>>(s, x, dy, gamma, save_mean, save_rstd, partial, dx, dgamma,
+    launch_pdl(bn_bwd_dx_kernel, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, gamma, save_mean, save_rstd, partial, dx, dgamma,
                                                           dbeta, accumulate);
     return check_launch("fnet_bn_bwd");
 }

@@ -15,6 +15,7 @@ namespace fnet {
 
 __global__ void __launch_bounds__(256) col2im_kernel(ConvGeom g, const float *__restrict__ t, float *__restrict__ dx,
                                                      int accumulate, long long total) {
+    pdl_prologue();
     const int taps_c = g.kh * g.kw * g.C;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         int c = (int)(i % g.C);
@@ -63,7 +64,7 @@ int col2im_scatter(const ConvGeom &g, const float *t, float *dx, int accumulate,
     if (total == 0) return FNET_OK;
     long long blocks = ceil_div<long long>(total, 256);
     long long cap = (long long)kNumSMs * 16;
-    col2im_kernel<<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(g, t, dx, accumulate, total);
+    launch_pdl(col2im_kernel, dim3((unsigned)(blocks > cap ? cap : blocks)), dim3(256), 0, stream, g, t, dx, accumulate, total);
     return check_launch("conv2d_bwd_data[col2im]");
 }
 

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include "../../include/fnet.h"
 
 namespace fnet {
@@ -42,6 +43,43 @@ inline cudaStream_t as_stream(void *s) { return reinterpret_cast<cudaStream_t>(s
 
 template <typename T>
 __host__ __device__ constexpr T ceil_div(T a, T b) { return (a + b - 1) / b; }
+
+// ---------------------------------------------------------------- programmatic dependent launch
+// A FeatureNet step is a chain of small kernels, so the gap between one kernel's last CTA and the next
+// kernel's first instruction is a large part of the step.  Every kernel is launched with the programmatic
+// stream-serialisation attribute and opens with pdl_prologue(): `launch_dependents` lets the NEXT kernel's CTAs
+// be scheduled as soon as all CTAs of this one have started, and `wait` holds this kernel until its predecessor
+// has completed and flushed its writes.  The wait is the first thing a kernel does, so nothing is read or
+// written early: the ordering semantics are exactly those of a plain stream, only the launch latency overlaps.
+// Captured into a CUDA graph the attribute becomes a programmatic edge.  FNET_PDL=0 turns it off.
+__device__ __forceinline__ void pdl_prologue() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+inline bool pdl_enabled() {
+    static int mode = -1;
+    if (mode < 0) {
+        const char *e = getenv("FNET_PDL");
+        mode = (e && e[0] == '0') ? 0 : 1;
+    }
+    return mode == 1;
+}
+
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    (void)cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);     // errors surface in check_launch()
+}
 
 // grid for a grid-stride element-wise kernel: enough CTAs to cover n, capped at 8 per SM
 inline int stream_grid(int64_t work_items, int threads) {

@@ -11,6 +11,7 @@ namespace fnet {
 __global__ void __launch_bounds__(256) dw_fwd_kernel(fnet_conv2d_desc d, const float *__restrict__ x,
                                                      const float *__restrict__ w, const float *__restrict__ bias,
                                                      float *__restrict__ y, int act) {
+    pdl_prologue();
     int C = d.in_c;
     int64_t total = (int64_t)d.batch * d.out_h * d.out_w * C;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -37,6 +38,7 @@ __global__ void __launch_bounds__(256) dw_fwd_kernel(fnet_conv2d_desc d, const f
 __global__ void __launch_bounds__(256) dw_dgrad_kernel(fnet_conv2d_desc d, const float *__restrict__ dz,
                                                        const float *__restrict__ w, float *__restrict__ dx,
                                                        int accumulate) {
+    pdl_prologue();
     int C = d.in_c;
     int64_t total = (int64_t)d.batch * d.in_h * d.in_w * C;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -72,6 +74,7 @@ __global__ void __launch_bounds__(kDwChan * kDwPix) dw_wgrad_partial_kernel(fnet
                                                                            const float *__restrict__ x,
                                                                            const float *__restrict__ dz,
                                                                            float *__restrict__ partial, int rows) {
+    pdl_prologue();
     __shared__ float red[kDwPix][kDwChan + 1];
     int C = d.in_c;
     int c = blockIdx.x * kDwChan + threadIdx.x;
@@ -125,6 +128,7 @@ __global__ void __launch_bounds__(kDwChan * kDwPix) dw_wgrad_partial_kernel(fnet
 __global__ void __launch_bounds__(256) dw_wgrad_reduce_kernel(int splits, int rows, int taps, int C,
                                                               const float *__restrict__ partial, float *__restrict__ dw,
                                                               float *__restrict__ dbias) {
+    pdl_prologue();
     int total = rows * C;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         float s = 0.f;
@@ -176,7 +180,7 @@ int fnet_dwconv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w,
     int64_t total = (int64_t)d->batch * d->out_h * d->out_w * d->in_c;
     if (total == 0) return FNET_OK;
     int act = d->act == FNET_ACT_SOFTMAX ? FNET_ACT_NONE : d->act;
-    dw_fwd_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, x, w, bias, y, act);
+    launch_pdl(dw_fwd_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, x, w, bias, y, act);
     rc = check_launch("fnet_dwconv2d_fwd");
     if (rc == FNET_OK && d->act == FNET_ACT_SOFTMAX)
         rc = fnet_act_fwd(FNET_ACT_SOFTMAX, total / d->in_c, d->in_c, y, y, stream);
@@ -190,7 +194,7 @@ int fnet_dwconv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const flo
     FNET_REQUIRE(dz && w && dx, "fnet_dwconv2d_bwd_data: null pointer");
     int64_t total = (int64_t)d->batch * d->in_h * d->in_w * d->in_c;
     if (total == 0) return FNET_OK;
-    dw_dgrad_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, dz, w, dx, accumulate);
+    launch_pdl(dw_dgrad_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, dz, w, dx, accumulate);
     return check_launch("fnet_dwconv2d_bwd_data");
 }
 
@@ -214,18 +218,18 @@ int fnet_dwconv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const fl
     float *partial = reinterpret_cast<float *>(ws);
     dim3 grid(ceil_div(d->in_c, kDwChan), splits), block(kDwChan, kDwPix);
     if (taps + 1 <= 10)
-        dw_wgrad_partial_kernel<10><<<grid, block, 0, as_stream(stream)>>>(*d, pix_per_split, x, dz, partial, rows);
+        launch_pdl(dw_wgrad_partial_kernel<10>, dim3(grid), dim3(block), 0, as_stream(stream), *d, pix_per_split, x, dz, partial, rows);
     else if (taps + 1 <= 26)
-        dw_wgrad_partial_kernel<26><<<grid, block, 0, as_stream(stream)>>>(*d, pix_per_split, x, dz, partial, rows);
+        launch_pdl(dw_wgrad_partial_kernel<26>, dim3(grid), dim3(block), 0, as_stream(stream), *d, pix_per_split, x, dz, partial, rows);
     else if (taps + 1 <= 50)
-        dw_wgrad_partial_kernel<50><<<grid, block, 0, as_stream(stream)>>>(*d, pix_per_split, x, dz, partial, rows);
+        launch_pdl(dw_wgrad_partial_kernel<50>, dim3(grid), dim3(block), 0, as_stream(stream), *d, pix_per_split, x, dz, partial, rows);
     else {
         set_error("fnet_dwconv2d_bwd_filter: kernels above 7x7 are outside the FeatureNet vocabulary");
         return FNET_ERR_UNSUPPORTED;
     }
     rc = check_launch("fnet_dwconv2d_bwd_filter");
     if (rc) return rc;
-    dw_wgrad_reduce_kernel<<<stream_grid((int64_t)rows * d->in_c, 256), 256, 0, as_stream(stream)>>>(
+    launch_pdl(dw_wgrad_reduce_kernel, dim3(stream_grid((int64_t)rows * d->in_c, 256)), dim3(256), 0, as_stream(stream), 
         splits, rows, taps, d->in_c, partial, dw, dbias);
     return check_launch("fnet_dwconv2d_bwd_filter");
 }

@@ -12,6 +12,7 @@ namespace fnet {
 template <class F>
 __global__ void __launch_bounds__(256) map1_kernel(int64_t n, const float *__restrict__ a, float *__restrict__ y,
                                                    int accumulate, F f) {
+    pdl_prologue();
     int64_t n4 = n >> 2;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -32,6 +33,7 @@ __global__ void __launch_bounds__(256) map1_kernel(int64_t n, const float *__res
 template <class F>
 __global__ void __launch_bounds__(256) map2_kernel(int64_t n, const float *__restrict__ a, const float *__restrict__ b,
                                                    float *__restrict__ y, int accumulate, F f) {
+    pdl_prologue();
     int64_t n4 = n >> 2;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -57,7 +59,7 @@ static int launch_map1(int64_t n, const float *a, float *y, int accumulate, F f,
     if (n == 0) return FNET_OK;
     if (n < 0 || !a || !y) { set_error("%s: bad arguments", what); return FNET_ERR_ARG; }
     if (!aligned16(a) || !aligned16(y)) { set_error("%s: pointers must be 16-byte aligned", what); return FNET_ERR_ARG; }
-    map1_kernel<<<stream_grid(ceil_div<int64_t>(n, 4), 256), 256, 0, as_stream(stream)>>>(n, a, y, accumulate, f);
+    launch_pdl(map1_kernel<F>, dim3(stream_grid(ceil_div<int64_t>(n, 4), 256)), dim3(256), 0, as_stream(stream), n, a, y, accumulate, f);
     return check_launch(what);
 }
 
@@ -70,7 +72,7 @@ static int launch_map2(int64_t n, const float *a, const float *b, float *y, int 
         set_error("%s: pointers must be 16-byte aligned", what);
         return FNET_ERR_ARG;
     }
-    map2_kernel<<<stream_grid(ceil_div<int64_t>(n, 4), 256), 256, 0, as_stream(stream)>>>(n, a, b, y, accumulate, f);
+    launch_pdl(map2_kernel<F>, dim3(stream_grid(ceil_div<int64_t>(n, 4), 256)), dim3(256), 0, as_stream(stream), n, a, b, y, accumulate, f);
     return check_launch(what);
 }
 
@@ -124,6 +126,7 @@ static DropoutOp make_dropout(float rate, uint64_t seed, uint32_t stream_id, con
 // one warp per row; cols is the channel / class count (10..2048 here)
 __global__ void __launch_bounds__(256) softmax_rows_kernel(int64_t rows, int cols, const float *__restrict__ x,
                                                            float *__restrict__ y) {
+    pdl_prologue();
     int lane = threadIdx.x & 31;
     int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     int64_t nrow_stride = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -144,6 +147,7 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(int64_t rows, int col
 __global__ void __launch_bounds__(256) softmax_rows_bwd_kernel(int64_t rows, int cols, const float *__restrict__ y,
                                                                const float *__restrict__ dy, float *__restrict__ dx,
                                                                int accumulate) {
+    pdl_prologue();
     int lane = threadIdx.x & 31;
     int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     int64_t nrow_stride = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -165,6 +169,7 @@ __global__ void __launch_bounds__(256) copy_rows_kernel(int batch, int src_rows,
                                                         int dst_row0, int64_t block_elems, int inner,
                                                         const float *__restrict__ src, float *__restrict__ dst,
                                                         int accumulate) {
+    pdl_prologue();
     // per batch item the copied region is one contiguous block of rows*inner floats
     int64_t src_stride = (int64_t)src_rows * inner, dst_stride = (int64_t)dst_rows * inner;
     int64_t src_off = (int64_t)src_row0 * inner, dst_off = (int64_t)dst_row0 * inner;
@@ -187,6 +192,7 @@ __global__ void __launch_bounds__(256) copy_rows_kernel(int batch, int src_rows,
 
 __global__ void __launch_bounds__(256) pad2d_kernel(int batch, int h, int w, int c, int ph, int pw,
                                                     const float *__restrict__ x, float *__restrict__ y) {
+    pdl_prologue();
     int H2 = h + 2 * ph, W2 = w + 2 * pw;
     int64_t total = (int64_t)batch * H2 * W2 * c;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -203,6 +209,7 @@ __global__ void __launch_bounds__(256) pad2d_kernel(int batch, int h, int w, int
 __global__ void __launch_bounds__(256) pad2d_bwd_kernel(int batch, int h, int w, int c, int ph, int pw,
                                                         const float *__restrict__ dy, float *__restrict__ dx,
                                                         int accumulate) {
+    pdl_prologue();
     int H2 = h + 2 * ph, W2 = w + 2 * pw;
     (void)H2;
     int64_t total = (int64_t)batch * h * w * c;
@@ -225,6 +232,7 @@ __device__ __forceinline__ float vadd(float a, float b) { return a + b; }
 template <typename T, typename I>
 __global__ void __launch_bounds__(256) concat_rows_fwd_kernel(I outer, I blk_a, I blk_b, const T *__restrict__ a,
                                                               const T *__restrict__ b, T *__restrict__ y) {
+    pdl_prologue();
     const I blk = blk_a + blk_b, total = outer * blk;
     for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
         I o = i / blk, e = i - o * blk;
@@ -235,6 +243,7 @@ __global__ void __launch_bounds__(256) concat_rows_fwd_kernel(I outer, I blk_a, 
 template <typename T, typename I>
 __global__ void __launch_bounds__(256) concat_rows_bwd_kernel(I outer, I blk_a, I blk_b, const T *__restrict__ dy,
                                                               T *__restrict__ da, T *__restrict__ db, int acc_a, int acc_b) {
+    pdl_prologue();
     const I blk = blk_a + blk_b, total = outer * blk;
     for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
         I o = i / blk, e = i - o * blk;
@@ -252,7 +261,7 @@ __global__ void __launch_bounds__(256) concat_rows_bwd_kernel(I outer, I blk_a, 
 int run_softmax_rows(int64_t rows, int64_t cols, const float *x, float *y, cudaStream_t stream) {
     int64_t blocks = ceil_div<int64_t>(rows, 8);
     int64_t cap = (int64_t)kNumSMs * 8;
-    softmax_rows_kernel<<<(int)(blocks > cap ? cap : blocks), 256, 0, stream>>>(rows, (int)cols, x, y);
+    launch_pdl(softmax_rows_kernel, dim3((int)(blocks > cap ? cap : blocks)), dim3(256), 0, stream, rows, (int)cols, x, y);
     return check_launch("softmax");
 }
 
@@ -282,7 +291,7 @@ int fnet_act_bwd(int act, int64_t rows, int64_t cols, const float *y, const floa
         FNET_REQUIRE(y && dy && dx, "fnet_act_bwd: null pointer");
         int64_t blocks = ceil_div<int64_t>(rows, 8);
         int64_t cap = (int64_t)kNumSMs * 8;
-        softmax_rows_bwd_kernel<<<(int)(blocks > cap ? cap : blocks), 256, 0, as_stream(stream)>>>(
+        launch_pdl(softmax_rows_bwd_kernel, dim3((int)(blocks > cap ? cap : blocks)), dim3(256), 0, as_stream(stream), 
             rows, (int)cols, y, dy, dx, accumulate);
         return check_launch("fnet_act_bwd");
     }
@@ -325,7 +334,7 @@ int fnet_copy_rows(int32_t batch, int32_t src_rows, int32_t src_row0, int32_t ds
     FNET_REQUIRE(src && dst, "fnet_copy_rows: null pointer");
     int64_t block_elems = (int64_t)rows * inner;
     if (batch == 0 || block_elems == 0) return FNET_OK;
-    copy_rows_kernel<<<stream_grid((int64_t)batch * block_elems, 256), 256, 0, as_stream(stream)>>>(
+    launch_pdl(copy_rows_kernel, dim3(stream_grid((int64_t)batch * block_elems, 256)), dim3(256), 0, as_stream(stream), 
         batch, src_rows, src_row0, dst_rows, dst_row0, block_elems, inner, src, dst, accumulate);
     return check_launch("fnet_copy_rows");
 }
@@ -339,13 +348,13 @@ int fnet_concat_rows_fwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t 
     const bool small = total < 0x7fffffffLL - (1 << 26);
     cudaStream_t s = as_stream(stream);
     if (small && !(blk_a & 3) && !(blk_b & 3) && aligned16(a) && aligned16(b) && aligned16(y))
-        concat_rows_fwd_kernel<float4, int><<<stream_grid(total / 4, 256), 256, 0, s>>>(
+        launch_pdl(concat_rows_fwd_kernel<float4, int>, dim3(stream_grid(total / 4, 256)), dim3(256), 0, s, 
             outer, (int)(blk_a / 4), (int)(blk_b / 4), reinterpret_cast<const float4 *>(a), reinterpret_cast<const float4 *>(b),
             reinterpret_cast<float4 *>(y));
     else if (small)
-        concat_rows_fwd_kernel<float, int><<<stream_grid(total, 256), 256, 0, s>>>(outer, (int)blk_a, (int)blk_b, a, b, y);
+        launch_pdl(concat_rows_fwd_kernel<float, int>, dim3(stream_grid(total, 256)), dim3(256), 0, s, outer, (int)blk_a, (int)blk_b, a, b, y);
     else
-        concat_rows_fwd_kernel<float, int64_t><<<stream_grid(total, 256), 256, 0, s>>>(outer, blk_a, blk_b, a, b, y);
+        launch_pdl(concat_rows_fwd_kernel<float, int64_t>, dim3(stream_grid(total, 256)), dim3(256), 0, s, outer, blk_a, blk_b, a, b, y);
     return check_launch("fnet_concat_rows_fwd");
 }
 
@@ -358,13 +367,13 @@ int fnet_concat_rows_bwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t 
     const bool small = total < 0x7fffffffLL - (1 << 26);
     cudaStream_t s = as_stream(stream);
     if (small && !(blk_a & 3) && !(blk_b & 3) && aligned16(dy) && aligned16(da) && aligned16(db))
-        concat_rows_bwd_kernel<float4, int><<<stream_grid(total / 4, 256), 256, 0, s>>>(
+        launch_pdl(concat_rows_bwd_kernel<float4, int>, dim3(stream_grid(total / 4, 256)), dim3(256), 0, s, 
             outer, (int)(blk_a / 4), (int)(blk_b / 4), reinterpret_cast<const float4 *>(dy), reinterpret_cast<float4 *>(da),
             reinterpret_cast<float4 *>(db), acc_a, acc_b);
     else if (small)
-        concat_rows_bwd_kernel<float, int><<<stream_grid(total, 256), 256, 0, s>>>(outer, (int)blk_a, (int)blk_b, dy, da, db, acc_a, acc_b);
+        launch_pdl(concat_rows_bwd_kernel<float, int>, dim3(stream_grid(total, 256)), dim3(256), 0, s, outer, (int)blk_a, (int)blk_b, dy, da, db, acc_a, acc_b);
     else
-        concat_rows_bwd_kernel<float, int64_t><<<stream_grid(total, 256), 256, 0, s>>>(outer, blk_a, blk_b, dy, da, db, acc_a, acc_b);
+        launch_pdl(concat_rows_bwd_kernel<float, int64_t>, dim3(stream_grid(total, 256)), dim3(256), 0, s, outer, blk_a, blk_b, dy, da, db, acc_a, acc_b);
     return check_launch("fnet_concat_rows_bwd");
 }
 
@@ -373,7 +382,7 @@ int fnet_pad2d_fwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h
     FNET_REQUIRE(batch >= 0 && h > 0 && w > 0 && c > 0 && pad_h >= 0 && pad_w >= 0 && x && y, "fnet_pad2d_fwd: bad arguments");
     if (batch == 0) return FNET_OK;
     int64_t total = (int64_t)batch * (h + 2 * pad_h) * (w + 2 * pad_w) * c;
-    pad2d_kernel<<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(batch, h, w, c, pad_h, pad_w, x, y);
+    launch_pdl(pad2d_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), batch, h, w, c, pad_h, pad_w, x, y);
     return check_launch("fnet_pad2d_fwd");
 }
 
@@ -381,7 +390,7 @@ int fnet_pad2d_bwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h
                    float *dx, int accumulate, void *stream) {
     FNET_REQUIRE(batch >= 0 && h > 0 && w > 0 && c > 0 && pad_h >= 0 && pad_w >= 0 && dy && dx, "fnet_pad2d_bwd: bad arguments");
     if (batch == 0) return FNET_OK;
-    pad2d_bwd_kernel<<<stream_grid((int64_t)batch * h * w * c, 256), 256, 0, as_stream(stream)>>>(
+    launch_pdl(pad2d_bwd_kernel, dim3(stream_grid((int64_t)batch * h * w * c, 256)), dim3(256), 0, as_stream(stream), 
         batch, h, w, c, pad_h, pad_w, dy, dx, accumulate);
     return check_launch("fnet_pad2d_bwd");
 }

@@ -87,6 +87,7 @@ template <class P>
 __global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                  const __grid_constant__ CUtensorMap map_b, P p, int M, int N,
                                                                  int Kg, int BN, int n_tiles, int total_tiles, int tmem_cols) {
+    pdl_prologue();
     constexpr bool B_MN = !P::kBContigK;
     extern __shared__ uint8_t tg_smem_raw[];
     __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], acc_full[2], acc_empty[2];
@@ -222,6 +223,7 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_c
                                                                   int M /* C (+1 bias row) */, int N, int pixels, int BN,
                                                                   int n_tiles, int tiles, int kt_per_split, int stages,
                                                                   int tmem_cols, float *__restrict__ partial) {
+    pdl_prologue();
     extern __shared__ uint8_t tg_smem_raw[];
     __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], acc_full;
     __shared__ uint32_t tmem_holder;
@@ -460,7 +462,7 @@ static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, c
         configured = true;
     }
     const unsigned grid = (unsigned)(total < kNumSMs ? total : kNumSMs);
-    tma_gemm_kernel<P><<<grid, TG_THREADS, smem, stream>>>(map_a, map_b, p, (int)M, (int)N, (int)Kg, BN, n_tiles, (int)total,
+    launch_pdl(tma_gemm_kernel<P>, dim3(grid), dim3(TG_THREADS), smem, stream, map_a, map_b, p, (int)M, (int)N, (int)Kg, BN, n_tiles, (int)total,
                                                           tmem_cols);
     return check_launch(what);
 }
@@ -510,7 +512,7 @@ int tma_gemm_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw
     }
     WgradProblem p{g, x, dz, dw, dbias, g.C};
     const int M = g.C + (dbias ? 1 : 0);
-    tma_wgrad_kernel<<<(unsigned)(t.tiles * t.splits), TG_THREADS, t.smem, stream>>>(map_a, map_b, p, M, g.K, (int)pixels, t.bn, t.n_tiles,
+    launch_pdl(tma_wgrad_kernel, dim3((unsigned)(t.tiles * t.splits)), dim3(TG_THREADS), t.smem, stream, map_a, map_b, p, M, g.K, (int)pixels, t.bn, t.n_tiles,
                                                                                      t.tiles, t.kt_per_split, t.stages, t.tmem_cols, partial);
     int rc = check_launch(what);
     if (rc == FNET_OK && t.splits > 1) rc = simt_reduce_wgrad_partials(g, dw, dbias, M, t.splits, partial, stream);

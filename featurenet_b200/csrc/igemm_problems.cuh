@@ -285,6 +285,7 @@ struct WgradProblem {
 template <class P>
 __global__ void __launch_bounds__(256) reduce_splits_warp_kernel(P p, int M, int N, int splits,
                                                                   const float *__restrict__ partial) {
+    pdl_prologue();
     long long total = (long long)M * N;
     int lane = threadIdx.x & 31;
     long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -303,6 +304,7 @@ __global__ void __launch_bounds__(256) reduce_splits_warp_kernel(P p, int M, int
 template <class P>
 __global__ void __launch_bounds__(256) reduce_splits_flat_kernel(P p, int M, int N, int splits,
                                                                   const float *__restrict__ partial) {
+    pdl_prologue();
     long long total = (long long)M * N;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         float s = 0.f;
@@ -318,10 +320,10 @@ static int launch_reduce_splits(const P &p, int M, int N, int splits, const floa
     long long total = (long long)M * N;
     if (splits <= 16 || total >= (1LL << 16)) {
         long long blocks = ceil_div<long long>(total, 256), cap = (long long)kNumSMs * 8;
-        reduce_splits_flat_kernel<P><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, M, N, splits, partial);
+        launch_pdl(reduce_splits_flat_kernel<P>, dim3((unsigned)(blocks > cap ? cap : blocks)), dim3(256), 0, stream, p, M, N, splits, partial);
     } else {
         long long blocks = ceil_div<long long>(total, 8), cap = (long long)kNumSMs * 8;
-        reduce_splits_warp_kernel<P><<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, stream>>>(p, M, N, splits, partial);
+        launch_pdl(reduce_splits_warp_kernel<P>, dim3((unsigned)(blocks > cap ? cap : blocks)), dim3(256), 0, stream, p, M, N, splits, partial);
     }
     return check_launch(what);
 }

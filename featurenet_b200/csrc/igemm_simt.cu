@@ -25,6 +25,7 @@ namespace fnet {
 template <class P, int BM, int BN, int TM, int TN, int BK>
 __global__ void __launch_bounds__(256, 3) igemm_simt_kernel(P p, int M, int N, int Kg, int k_per_split,
                                                           float *__restrict__ partial) {
+    pdl_prologue();
     static_assert((BM / TM) * (BN / TN) == 256, "256 threads per CTA");
     constexpr int RG = 256 / BK;                 // row groups of the A loader
     constexpr int A_PER = BM / RG;               // A elements gathered per thread per tile
@@ -272,7 +273,7 @@ static SplitPlan plan_for(long long M, long long N, long long Kg, bool bias_row 
 
 template <class P, int BM, int BN, int TM, int TN, int BKT>
 static void launch_tile(const P &p, dim3 grid, int m, int n, int kg, int per, float *partial, cudaStream_t stream) {
-    igemm_simt_kernel<P, BM, BN, TM, TN, BKT><<<grid, 256, 0, stream>>>(p, m, n, kg, per, partial);
+    launch_pdl(igemm_simt_kernel<P, BM, BN, TM, TN, BKT>, dim3(grid), dim3(256), 0, stream, p, m, n, kg, per, partial);
 }
 
 template <class P>

@@ -118,6 +118,7 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const float *src, uint3
 template <class P, int BN, int TC_STAGES, int X3>
 __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int N, int Kg, int k_per_split,
                                                                  float *__restrict__ partial, int layout) {
+    pdl_prologue();
     constexpr int B_BYTES = BN * TC_BK * 4;
     constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
     constexpr int B_PER = BN / 8;
@@ -434,7 +435,7 @@ static int tc_launch(const P &p, dim3 grid, size_t smem, int m, int n, int kg, i
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
         configured = true;
     }
-    tc_igemm_kernel<P, BN, STAGES, X3><<<grid, TC_THREADS, smem, stream>>>(p, m, n, kg, per, partial, tc_layout_mode());
+    launch_pdl(tc_igemm_kernel<P, BN, STAGES, X3>, dim3(grid), dim3(TC_THREADS), smem, stream, p, m, n, kg, per, partial, tc_layout_mode());
     return check_launch(what);
 }
 

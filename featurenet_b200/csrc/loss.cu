@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(256) softmax_cce_kernel(int batch, int classes
                                                            const float *__restrict__ targets, float scale,
                                                            int from_logits, float *probs_out, float *__restrict__ dlogits,
                                                            double *__restrict__ loss_sum, long long *__restrict__ correct) {
+    pdl_prologue();
     __shared__ double warp_loss[32];
     __shared__ int warp_correct[32];
     double my_loss = 0.0;
@@ -188,6 +189,7 @@ __global__ void __launch_bounds__(1024) softmax_cce_group_kernel(int batch, int 
                                                                   const float *__restrict__ targets, float scale,
                                                                   int from_logits, float *probs_out, float *__restrict__ dlogits,
                                                                   double *__restrict__ loss_sum, long long *__restrict__ correct) {
+    pdl_prologue();
     __shared__ double group_loss[1024 / G];
     __shared__ int group_correct[1024 / G];
     const int c = threadIdx.x % G, group = threadIdx.x / G, groups = blockDim.x / G;
@@ -250,17 +252,17 @@ extern "C" int fnet_softmax_cce(int32_t batch, int32_t classes, const float *inp
         long long want = (long long)batch * lanes;
         int threads = want >= 1024 ? 1024 : (int)((want + 31) / 32) * 32;
         if (lanes == 16)
-            softmax_cce_group_kernel<16><<<1, threads, 0, as_stream(stream)>>>(batch, classes, input, targets, scale, from_logits,
+            launch_pdl(softmax_cce_group_kernel<16>, dim3(1), dim3(threads), 0, as_stream(stream), batch, classes, input, targets, scale, from_logits,
                                                                                probs_out, dlogits, loss_sum,
                                                                                reinterpret_cast<long long *>(correct));
         else
-            softmax_cce_group_kernel<32><<<1, threads, 0, as_stream(stream)>>>(batch, classes, input, targets, scale, from_logits,
+            launch_pdl(softmax_cce_group_kernel<32>, dim3(1), dim3(threads), 0, as_stream(stream), batch, classes, input, targets, scale, from_logits,
                                                                                probs_out, dlogits, loss_sum,
                                                                                reinterpret_cast<long long *>(correct));
         return check_launch("fnet_softmax_cce");
     }
     int threads = batch >= 256 ? 256 : ((batch + 31) / 32) * 32;
-    softmax_cce_kernel<<<1, threads, 0, as_stream(stream)>>>(batch, classes, input, targets, scale, from_logits, probs_out,
+    launch_pdl(softmax_cce_kernel, dim3(1), dim3(threads), 0, as_stream(stream), batch, classes, input, targets, scale, from_logits, probs_out,
                                                              dlogits, loss_sum, reinterpret_cast<long long *>(correct));
     return check_launch("fnet_softmax_cce");
 }

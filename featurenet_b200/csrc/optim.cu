@@ -18,6 +18,7 @@ __device__ __forceinline__ void close_step(int32_t *state, int32_t advance) {
 __global__ void __launch_bounds__(256) adam_kernel(int64_t n, float *__restrict__ p, const float *__restrict__ g,
                                                    float *__restrict__ m, float *__restrict__ v, int32_t *__restrict__ state,
                                                    float b1, float b2, float eps, int32_t advance) {
+    pdl_prologue();
     const float lr_t = __int_as_float(state[3]);
     const float c1 = 1.f - b1, c2 = 1.f - b2;
     int64_t n4 = n >> 2;
@@ -54,6 +55,7 @@ __global__ void __launch_bounds__(256) adam_kernel(int64_t n, float *__restrict_
 __global__ void __launch_bounds__(256) sgd_kernel(int64_t n, float *__restrict__ p, const float *__restrict__ g,
                                                   float *__restrict__ vel, int32_t *__restrict__ state, float momentum,
                                                   int nesterov, int32_t advance) {
+    pdl_prologue();
     const float lr = __int_as_float(state[2]);
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         float gg = __ldg(g + i);
@@ -77,7 +79,7 @@ int fnet_adam_step(int64_t n, float *params, const float *grads, float *m, float
                    reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0,
                  "fnet_adam_step: arenas must be 16-byte aligned");
     if (n == 0) return advance >= 0 ? fnet_step_end(state, advance, stream) : FNET_OK;
-    adam_kernel<<<stream_grid(ceil_div<int64_t>(n, 4), 256), 256, 0, as_stream(stream)>>>(n, params, grads, m, v, state,
+    launch_pdl(adam_kernel, dim3(stream_grid(ceil_div<int64_t>(n, 4), 256)), dim3(256), 0, as_stream(stream), n, params, grads, m, v, state,
                                                                                        beta1, beta2, eps, advance);
     return check_launch("fnet_adam_step");
 }
@@ -86,7 +88,7 @@ int fnet_sgd_step(int64_t n, float *params, const float *grads, float *velocity,
                   int nesterov, int32_t advance, void *stream) {
     FNET_REQUIRE(n >= 0 && params && grads && velocity && state, "fnet_sgd_step: bad arguments");
     if (n == 0) return advance >= 0 ? fnet_step_end(state, advance, stream) : FNET_OK;
-    sgd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(n, params, grads, velocity, state, momentum, nesterov,
+    launch_pdl(sgd_kernel, dim3(stream_grid(n, 256)), dim3(256), 0, as_stream(stream), n, params, grads, velocity, state, momentum, nesterov,
                                                                    advance);
     return check_launch("fnet_sgd_step");
 }

@@ -12,6 +12,7 @@ namespace fnet {
 template <typename I>
 __global__ void __launch_bounds__(256) pool_fwd_kernel(fnet_pool2d_desc d, const float *__restrict__ x,
                                                        float *__restrict__ y, uint8_t *__restrict__ argmax) {
+    pdl_prologue();
     I total = (I)d.batch * d.out_h * d.out_w * d.channels;
     for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
         int c = (int)(i % (I)d.channels);
@@ -75,6 +76,7 @@ template <typename I>
 __global__ void __launch_bounds__(256) pool_bwd_kernel(fnet_pool2d_desc d, const float *__restrict__ dy,
                                                        const uint8_t *__restrict__ argmax, float *__restrict__ dx,
                                                        int accumulate) {
+    pdl_prologue();
     I total = (I)d.batch * d.in_h * d.in_w * d.channels;
     for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
         int c = (int)(i % (I)d.channels);
@@ -112,6 +114,7 @@ __global__ void __launch_bounds__(256) pool_bwd_kernel(fnet_pool2d_desc d, const
 // one warp per (b, 32-channel group): lanes walk channels, the warp walks the hw pixels
 __global__ void __launch_bounds__(256) gap_fwd_kernel(int batch, int hw, int channels, const float *__restrict__ x,
                                                       float *__restrict__ y) {
+    pdl_prologue();
     int64_t total = (int64_t)batch * channels;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         int c = (int)(i % channels);
@@ -125,6 +128,7 @@ __global__ void __launch_bounds__(256) gap_fwd_kernel(int batch, int hw, int cha
 
 __global__ void __launch_bounds__(256) gap_bwd_kernel(int batch, int hw, int channels, const float *__restrict__ dy,
                                                       float *__restrict__ dx, int accumulate) {
+    pdl_prologue();
     int64_t total = (int64_t)batch * hw * channels;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         int c = (int)(i % channels);
@@ -165,9 +169,9 @@ int fnet_pool2d_fwd(const fnet_pool2d_desc *d, const float *x, float *y, uint8_t
     if (total == 0) return FNET_OK;
     int64_t in_total = (int64_t)d->batch * d->in_h * d->in_w * d->channels;
     if (total < 0x7fffffffLL - (1 << 26) && in_total < 0x7fffffffLL)      // the grid-stride increment must not overflow either
-        pool_fwd_kernel<int><<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, x, y, argmax);
+        launch_pdl(pool_fwd_kernel<int>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, x, y, argmax);
     else
-        pool_fwd_kernel<int64_t><<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, x, y, argmax);
+        launch_pdl(pool_fwd_kernel<int64_t>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, x, y, argmax);
     return check_launch("fnet_pool2d_fwd");
 }
 
@@ -180,16 +184,16 @@ int fnet_pool2d_bwd(const fnet_pool2d_desc *d, const float *dy, const uint8_t *a
     int64_t total = (int64_t)d->batch * d->in_h * d->in_w * d->channels;
     if (total == 0) return FNET_OK;
     if (total < 0x7fffffffLL - (1 << 26))
-        pool_bwd_kernel<int><<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, dy, argmax, dx, accumulate);
+        launch_pdl(pool_bwd_kernel<int>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, dy, argmax, dx, accumulate);
     else
-        pool_bwd_kernel<int64_t><<<stream_grid(total, 256), 256, 0, as_stream(stream)>>>(*d, dy, argmax, dx, accumulate);
+        launch_pdl(pool_bwd_kernel<int64_t>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, dy, argmax, dx, accumulate);
     return check_launch("fnet_pool2d_bwd");
 }
 
 int fnet_gap_fwd(int32_t batch, int32_t hw, int32_t channels, const float *x, float *y, void *stream) {
     FNET_REQUIRE(batch >= 0 && hw > 0 && channels > 0 && x && y, "fnet_gap_fwd: bad arguments");
     if (batch == 0) return FNET_OK;
-    gap_fwd_kernel<<<stream_grid((int64_t)batch * channels, 256), 256, 0, as_stream(stream)>>>(batch, hw, channels, x, y);
+    launch_pdl(gap_fwd_kernel, dim3(stream_grid((int64_t)batch * channels, 256)), dim3(256), 0, as_stream(stream), batch, hw, channels, x, y);
     return check_launch("fnet_gap_fwd");
 }
 
@@ -197,7 +201,7 @@ int fnet_gap_bwd(int32_t batch, int32_t hw, int32_t channels, const float *dy, f
                  void *stream) {
     FNET_REQUIRE(batch >= 0 && hw > 0 && channels > 0 && dy && dx, "fnet_gap_bwd: bad arguments");
     if (batch == 0) return FNET_OK;
-    gap_bwd_kernel<<<stream_grid((int64_t)batch * hw * channels, 256), 256, 0, as_stream(stream)>>>(
+    launch_pdl(gap_bwd_kernel, dim3(stream_grid((int64_t)batch * hw * channels, 256)), dim3(256), 0, as_stream(stream), 
         batch, hw, channels, dy, dx, accumulate);
     return check_launch("fnet_gap_bwd");
 }

@@ -25,6 +25,7 @@ template <int NMAX>
 __global__ void __launch_bounds__(1024) dense_skinny_fwd_kernel(int K, int N, int act, const float *__restrict__ x,
                                                                 const float *__restrict__ w, const float *__restrict__ bias,
                                                                 float *__restrict__ y) {
+    pdl_prologue();
     __shared__ float red[32][NMAX];
     const int m = blockIdx.x;
     const float *xr = x + (long long)m * K;
@@ -60,6 +61,7 @@ template <int NMAX>
 __global__ void __launch_bounds__(256) dense_skinny_wgrad_kernel(int M, int K, int N, const float *__restrict__ x,
                                                                  const float *__restrict__ dz, float *__restrict__ dw,
                                                                  float *__restrict__ dbias) {
+    pdl_prologue();
     // a CTA owns 32 consecutive weight rows k; its 8 warps split the samples (warp g takes rows g, g+8, ...), so a
     // warp reads 128 contiguous bytes of x per sample and there are K/32 CTAs instead of K/256
     extern __shared__ float dz_s[];                 // a chunk of dz rows, [rows][N]
@@ -110,6 +112,7 @@ template <int NMAX>
 __global__ void __launch_bounds__(256) dense_skinny_dgrad_kernel(int M, int K, int N, const float *__restrict__ dz,
                                                                  const float *__restrict__ w, float *__restrict__ dx,
                                                                  int accumulate) {
+    pdl_prologue();
     const int m = blockIdx.y;
     float g[NMAX];
 #pragma unroll
@@ -140,6 +143,7 @@ constexpr int kStreamRows = 64;         // samples per CTA of the forward kernel
 template <int NMAX>
 __global__ void __launch_bounds__(512) dense_stream_fwd_kernel(int M, int K, int N, const float *__restrict__ x,
                                                                const float *__restrict__ w, float *__restrict__ partial) {
+    pdl_prologue();
     __shared__ float w_s[kStreamChunk * (NMAX + 1)];          // odd row stride: conflict-free when lanes walk k
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int m0 = blockIdx.y * kStreamRows + warp * 4;
@@ -187,6 +191,7 @@ template <int NMAX>
 __global__ void __launch_bounds__(256) dense_stream_wgrad_kernel(int M, int K, int N, const float *__restrict__ x,
                                                                  const float *__restrict__ dz, float *__restrict__ dw,
                                                                  float *__restrict__ dbias) {
+    pdl_prologue();
     constexpr int ROWS = 128;
     __shared__ __align__(16) float dz_s[ROWS][NMAX];
     const int k = blockIdx.x * 256 + threadIdx.x;
@@ -231,6 +236,7 @@ template <int NMAX>
 __global__ void __launch_bounds__(256) dense_rows_dgrad_kernel(int M, int K, int N, const float *__restrict__ dz,
                                                                const float *__restrict__ w, float *__restrict__ dx,
                                                                int accumulate) {
+    pdl_prologue();
     constexpr int ROWS = 16;
     __shared__ __align__(16) float g_s[ROWS][NMAX];
     const int m0 = blockIdx.y * ROWS, rows = min(ROWS, M - m0);
@@ -275,6 +281,7 @@ template <int NMAX>
 __global__ void __launch_bounds__(256) conv_small_fwd_kernel(ConvGeom g, int act, const float *__restrict__ x,
                                                              const float *__restrict__ w, const float *__restrict__ bias,
                                                              float *__restrict__ y) {
+    pdl_prologue();
     extern __shared__ float w_s[];                  // [taps*C][K] as in memory (HWIO), then the bias
     const int KG = g.kh * g.kw * g.C, N = g.K;
     for (int i = threadIdx.x; i < KG * N; i += 256) w_s[i] = __ldg(w + i);
@@ -318,6 +325,7 @@ template <int NMAX>
 __global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const float *__restrict__ dz,
                                                                const float *__restrict__ w, float *__restrict__ dx,
                                                                int accumulate) {
+    pdl_prologue();
     extern __shared__ float w_s[];                  // [taps][C][K]
     const int total_w = g.kh * g.kw * g.C * g.K, C = g.C, K = g.K;
     for (int i = threadIdx.x; i < total_w; i += 256) w_s[i] = __ldg(w + i);
@@ -367,6 +375,7 @@ constexpr int kWgradBlocks = 2 * kNumSMs;
 template <int KT>     // KT = number of output channels (compile time, so that every partial sum has a fixed register)
 __global__ void __launch_bounds__(256) conv_small_wgrad_kernel(ConvGeom g, int rows, const float *__restrict__ x,
                                                                const float *__restrict__ dz, float *__restrict__ partial) {
+    pdl_prologue();
     constexpr int ROWS_MAX = kWgradRegs / KT;
     __shared__ float red[8][kWgradRegs];
     const int C = g.C, taps_c = g.kh * g.kw * C;
@@ -422,6 +431,7 @@ __global__ void __launch_bounds__(256) conv_small_wgrad_kernel(ConvGeom g, int r
 __global__ void __launch_bounds__(256) conv_small_wgrad_reduce_kernel(int blocks, int taps_c, int K, int total,
                                                                       const float *__restrict__ partial,
                                                                       float *__restrict__ dw, float *__restrict__ dbias) {
+    pdl_prologue();
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = warp; i < total; i += 8) {
         float s = 0.f;
@@ -490,20 +500,20 @@ int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const
         }
         float *partial = reinterpret_cast<float *>(ws);
         dim3 grid(blocks, (unsigned)ceil_div<long long>(g.B, kStreamRows));
-#define FNET_CALL(NM) dense_stream_fwd_kernel<NM><<<grid, 512, 0, s>>>(g.B, g.C, g.K, x, w, partial)
+#define FNET_CALL(NM) launch_pdl(dense_stream_fwd_kernel<NM>, dim3(grid), dim3(512), 0, s, g.B, g.C, g.K, x, w, partial)
         FNET_BY_COLUMNS(g.K, FNET_CALL);
 #undef FNET_CALL
         int rc = check_launch("dense_fwd[stream]");
         return rc ? rc : simt_reduce_fwd_partials(g, act, bias, y, blocks, partial, s);
     }
     if (is_dense_geom(g)) {
-        dense_skinny_fwd_kernel<kSkinnyN><<<g.B, 1024, 0, s>>>(g.C, g.K, act, x, w, bias, y);
+        launch_pdl(dense_skinny_fwd_kernel<kSkinnyN>, dim3(g.B), dim3(1024), 0, s, g.C, g.K, act, x, w, bias, y);
         return check_launch("dense_fwd[skinny]");
     }
     size_t smem = ((size_t)g.kh * g.kw * g.C + 1) * g.K * sizeof(float);
     long long M = (long long)g.B * g.Ho * g.Wo;
-    if (g.K <= 8) conv_small_fwd_kernel<8><<<pixel_grid(M), 256, smem, s>>>(g, act, x, w, bias, y);
-    else conv_small_fwd_kernel<16><<<pixel_grid(M), 256, smem, s>>>(g, act, x, w, bias, y);
+    if (g.K <= 8) launch_pdl(conv_small_fwd_kernel<8>, dim3(pixel_grid(M)), dim3(256), smem, s, g, act, x, w, bias, y);
+    else launch_pdl(conv_small_fwd_kernel<16>, dim3(pixel_grid(M)), dim3(256), smem, s, g, act, x, w, bias, y);
     return check_launch("conv2d_fwd[small]");
 }
 
@@ -512,15 +522,15 @@ int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, 
         long long bx = ceil_div<long long>(g.C, 256);
         if (bx > 4096) bx = 4096;
         dim3 grid((unsigned)bx, (unsigned)ceil_div<long long>(g.B, 16));
-#define FNET_CALL(NM) dense_rows_dgrad_kernel<NM><<<grid, 256, 0, s>>>(g.B, g.C, g.K, dz, w, dx, accumulate)
+#define FNET_CALL(NM) launch_pdl(dense_rows_dgrad_kernel<NM>, dim3(grid), dim3(256), 0, s, g.B, g.C, g.K, dz, w, dx, accumulate)
         FNET_BY_COLUMNS(g.K, FNET_CALL);
 #undef FNET_CALL
         return check_launch("dense_bwd_data[skinny]");
     }
     size_t smem = (size_t)g.kh * g.kw * g.C * g.K * sizeof(float);
     long long M = (long long)g.B * g.H * g.W;
-    if (g.C <= 8) conv_small_dgrad_kernel<8><<<pixel_grid(M), 256, smem, s>>>(g, dz, w, dx, accumulate);
-    else conv_small_dgrad_kernel<16><<<pixel_grid(M), 256, smem, s>>>(g, dz, w, dx, accumulate);
+    if (g.C <= 8) launch_pdl(conv_small_dgrad_kernel<8>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, accumulate);
+    else launch_pdl(conv_small_dgrad_kernel<16>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, accumulate);
     return check_launch("conv2d_bwd_data[small]");
 }
 
@@ -528,14 +538,14 @@ int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, 
                  cudaStream_t s) {
     if (is_dense_geom(g) && g.C >= kStreamMinK) {
         unsigned blocks = (unsigned)ceil_div<long long>(g.C, 256);
-#define FNET_CALL(NM) dense_stream_wgrad_kernel<NM><<<blocks, 256, 0, s>>>(g.B, g.C, g.K, x, dz, dw, dbias)
+#define FNET_CALL(NM) launch_pdl(dense_stream_wgrad_kernel<NM>, dim3(blocks), dim3(256), 0, s, g.B, g.C, g.K, x, dz, dw, dbias)
         FNET_BY_COLUMNS(g.K, FNET_CALL);
 #undef FNET_CALL
         return check_launch("dense_bwd_filter[stream]");
     }
     if (is_dense_geom(g)) {
         size_t smem = (size_t)256 * g.K * sizeof(float);
-        dense_skinny_wgrad_kernel<kSkinnyN><<<(unsigned)ceil_div<long long>(g.C, 32), 256, smem, s>>>(g.B, g.C, g.K, x, dz,
+        launch_pdl(dense_skinny_wgrad_kernel<kSkinnyN>, dim3((unsigned)ceil_div<long long>(g.C, 32)), dim3(256), smem, s, g.B, g.C, g.K, x, dz,
                                                                                                      dw, dbias);
         return check_launch("dense_bwd_filter[skinny]");
     }
@@ -551,18 +561,18 @@ int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, 
     }
     float *partial = reinterpret_cast<float *>(ws);
     switch (g.K) {
-        case 1: conv_small_wgrad_kernel<1><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
-        case 2: conv_small_wgrad_kernel<2><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
-        case 3: conv_small_wgrad_kernel<3><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
-        case 4: conv_small_wgrad_kernel<4><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
-        case 5: conv_small_wgrad_kernel<5><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
-        case 6: conv_small_wgrad_kernel<6><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
-        case 7: conv_small_wgrad_kernel<7><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
-        default: conv_small_wgrad_kernel<8><<<blocks, 256, 0, s>>>(g, rows, x, dz, partial); break;
+        case 1: launch_pdl(conv_small_wgrad_kernel<1>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
+        case 2: launch_pdl(conv_small_wgrad_kernel<2>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
+        case 3: launch_pdl(conv_small_wgrad_kernel<3>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
+        case 4: launch_pdl(conv_small_wgrad_kernel<4>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
+        case 5: launch_pdl(conv_small_wgrad_kernel<5>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
+        case 6: launch_pdl(conv_small_wgrad_kernel<6>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
+        case 7: launch_pdl(conv_small_wgrad_kernel<7>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
+        default: launch_pdl(conv_small_wgrad_kernel<8>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
     }
     int rc = check_launch("conv2d_bwd_filter[small]");
     if (rc) return rc;
-    conv_small_wgrad_reduce_kernel<<<1, 256, 0, s>>>(blocks, taps_c, g.K, total, partial, dw, dbias);
+    launch_pdl(conv_small_wgrad_reduce_kernel, dim3(1), dim3(256), 0, s, blocks, taps_c, g.K, total, partial, dw, dbias);
     return check_launch("conv2d_bwd_filter[small]");
 }
 
