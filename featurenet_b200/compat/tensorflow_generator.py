@@ -11,7 +11,8 @@ Differences that cannot be avoided on this box, all loud:
   * datasets: ``keras.datasets`` needs a download; ``init_dataset`` uses ``FNET_DATA_DIR/<name>.npz``
     (keys x_train, y_train, x_test, y_test; uint8 images, integer labels) when present, otherwise a
     synthetic set of the same shape and size (featurenet_b200.synth), and says which;
-  * robustness (``eval_robustness``, IBM ART attacks) is SURVEY.md 8(f) item 1 and is not built:
+  * robustness (``eval_robustness``): the L2 gradient attacks (fgsm, pgd) run on the engine
+    (featurenet_b200/robustness.py); Carlini-Wagner and CLEVER of SURVEY.md 8(f) item 1 are not built:
     the scores stay 0 and a notice is printed;
   * ``export_png`` needs Graphviz ``dot``; it is a no-op after the first failure, as in the reference.
 """
@@ -133,15 +134,46 @@ class TensorflowGenerator(object):
 
     @staticmethod
     def eval_attack_robustness(keras_model, attack_name, norm, robustness_set_size=0):
-        raise NotImplementedError("adversarial robustness (ART attacks) is outside the train+evaluate hot path")
+        """(empirical robustness, clean accuracy, adversarial accuracy) -- tensorflow_generator.py:151-173."""
+        from featurenet_b200 import robustness
+        attack_params = {"norm": norm}
+        if attack_name == "pgd":
+            attack_params["eps_step"] = 0.1
+            attack_params["eps"] = 1.
+        if robustness_set_size == 0:
+            adv_set, y_set = TensorflowGenerator.X_robustness, TensorflowGenerator.Y_robustness
+        else:
+            adv_set = TensorflowGenerator.X_test[0:min(len(TensorflowGenerator.X_test), robustness_set_size)]
+            y_set = TensorflowGenerator.Y_test[0:min(len(TensorflowGenerator.Y_test), robustness_set_size)]
+        return robustness.attack_robustness(keras_model, attack_name, adv_set, y_set, attack_params)
 
     @staticmethod
     def eval_robustness(model, scores=[], robustness_set_size=0):
+        """The second fitness of the evolution drivers (tensorflow_generator.py:175-218).  The gradient attacks
+        (fgsm, pgd) run on the engine; Carlini-Wagner and CLEVER are not built and keep their score of 0."""
         keras_model = model.model
         if not keras_model or model.accuracy < 0.5:
             return
-        print("robustness metrics {} are not built in this engine (SURVEY.md 8f.1); scores stay 0".format(
-            list(scores) if scores else model.robustness_scores))
+        begin_robustness = time.time()
+        score_metrics = model.robustness_scores if not scores else scores
+        try:
+            norm = 2
+            for name in ("clever", "cw"):
+                if name in score_metrics:
+                    print("robustness metric {} is not built in this engine (SURVEY.md 8f.1); its score stays 0".format(name))
+            if "pgd" in score_metrics:
+                model.pgd_score = TensorflowGenerator.eval_attack_robustness(keras_model, "pgd", norm, robustness_set_size)
+            if "fgsm" in score_metrics:
+                model.fgsm_score = TensorflowGenerator.eval_attack_robustness(keras_model, "fgsm", norm, robustness_set_size)
+        except Exception as e:
+            import traceback
+            print("error", e)
+            print(traceback.format_exc())
+        robustness_time = time.time() - begin_robustness
+        first = getattr(model, "{}_score".format(scores[0]), [0]) if len(scores) else model.clever_score
+        model.robustness_score = first[0] if isinstance(first, (list, tuple)) else first
+        print('model robustness (clever, pgd, cw, fgsm): {} time:{}'.format(
+            (model.clever_score, model.pgd_score, model.cw_score, model.fgsm_score), robustness_time))
 
     @staticmethod
     def build(model, dataset, clear_memory=True):

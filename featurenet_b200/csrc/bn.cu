@@ -122,6 +122,21 @@ __global__ void __launch_bounds__(256) bn_infer_kernel(int64_t total, int a_len,
     }
 }
 
+// inference-mode input gradient: the statistics are constants, so dx = dy * gamma / sqrt(moving_var + eps)
+__global__ void __launch_bounds__(256) bn_infer_bwd_kernel(int64_t total, int a_len, int inner, float eps,
+                                                           const float *__restrict__ dy, const float *__restrict__ gamma,
+                                                           const float *__restrict__ var, float *__restrict__ dx, int accumulate) {
+    pdl_prologue();
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int a = (int)(((unsigned)i / (unsigned)inner) % (unsigned)a_len);
+        float v = __ldg(var + a) + eps;
+        float rstd = rsqrtf(v);
+        rstd = rstd * (1.5f - 0.5f * v * rstd * rstd);
+        float g = __ldg(dy + i) * rstd * __ldg(gamma + a);
+        dx[i] = accumulate ? dx[i] + g : g;
+    }
+}
+
 __global__ void __launch_bounds__(256) bn_bwd_partial_kernel(BnShape s, const float *__restrict__ x,
                                                              const float *__restrict__ dy,
                                                              const float *__restrict__ save_mean,
@@ -224,6 +239,17 @@ int fnet_bn_fwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const 
     launch_pdl(bn_infer_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), total, a, inner, eps, x, gamma, beta,
                                                                             moving_mean, moving_var, y);
     return check_launch("fnet_bn_fwd_infer");
+}
+
+int fnet_bn_bwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const float *dy, const float *gamma,
+                      const float *moving_var, float *dx, int accumulate, void *stream) {
+    FNET_REQUIRE(outer >= 0 && a > 0 && inner > 0 && (int64_t)outer * a * inner < 0x7fffffffLL, "fnet_bn_bwd_infer: bad shape");
+    FNET_REQUIRE(dy && gamma && moving_var && dx, "fnet_bn_bwd_infer: null pointer");
+    int64_t total = (int64_t)outer * a * inner;
+    if (total == 0) return FNET_OK;
+    launch_pdl(bn_infer_bwd_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), total, a, inner, eps, dy, gamma,
+               moving_var, dx, accumulate);
+    return check_launch("fnet_bn_bwd_infer");
 }
 
 int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,

@@ -327,7 +327,7 @@ class Engine(object):
         return batch * _prod(shp[:axis]), shp[axis], _prod(shp[axis + 1:])
 
     # ------------------------------------------------------------------ programs
-    def _forward_program(self, batch, training, head_logits=True):
+    def _forward_program(self, batch, training, head_logits=True, save_for_backward=None):
         """head_logits: the "out" layer stops at its logits (the loss kernel does the softmax and writes the
         probabilities in place); False makes the layer apply its own softmax (predict())."""
         L, sp, ws, wsb = self.lib, self.sp, C.c_void_p(self.ws.data_ptr()), self.ws_bytes
@@ -358,7 +358,8 @@ class Engine(object):
                 add("dense_fwd", L.fnet_dense_fwd, m, k, n, act, self.math, x, self._wp(i, 0),
                     self._wp(i, 1), y, ws, wsb, sp)
             elif kind in ("maxpool", "avgpool"):
-                arg = C.c_void_p(self.aux[i].data_ptr()) if kind == "maxpool" and training else None
+                keep = training if save_for_backward is None else save_for_backward      # argmax taps for the backward
+                arg = C.c_void_p(self.aux[i].data_ptr()) if kind == "maxpool" and keep else None
                 add("pool2d_fwd", L.fnet_pool2d_fwd, self._pool_desc(i, batch), x, y, arg, sp)
             elif kind == "gap":
                 h, w, c = self.shape[self.src[i][0]]
@@ -395,19 +396,23 @@ class Engine(object):
                 raise NotImplementedError(kind)
         return ops
 
-    def _needs_grad(self):
-        """True for nodes that have a trainable weight at or above them (a gradient must reach them)."""
-        need = [False] * len(self.nodes)
+    def _needs_grad(self, input_grad=False):
+        """True for nodes that have a trainable weight at or above them (a gradient must reach them);
+        with input_grad, for every node: the gradient is wanted at the network input itself."""
+        need = [bool(input_grad)] * len(self.nodes)
         for i, node in enumerate(self.nodes):
             has = any(spec.trainable for spec in node.weights)
-            need[i] = has or any(need[j] for j in self.src[i])
+            need[i] = need[i] or has or any(need[j] for j in self.src[i])
         return need
 
-    def _backward_program(self, batch):
+    def _backward_program(self, batch, training=True, input_grad=False):
+        """training=False differentiates the INFERENCE graph (dropout is the identity, BatchNorm an affine map on
+        its moving statistics); input_grad carries the gradient down to the network input and skips the filter
+        gradients -- together they are what the adversarial attacks of the robustness fitness need."""
         L, sp, ws, wsb = self.lib, self.sp, C.c_void_p(self.ws.data_ptr()), self.ws_bytes
         ops = []
         add = lambda label, fn, *args: ops.append((label, fn, args))
-        need = self._needs_grad()
+        need = self._needs_grad(input_grad)
         written = set()
         ws2 = C.c_void_p(self.ws.data_ptr() + self.ws_bytes)
         forked = [False]
@@ -417,6 +422,8 @@ class Engine(object):
             with, it goes to the side stream (own scratch half) behind a fork; _run_ops/_capture turn the fork
             and the final join into event dependencies.  Nothing later in the step writes what it reads (the
             layer's input activation and dz) or reads what it writes (the grads arena) before the join."""
+            if input_grad:
+                return                                  # weights are constants for an attack
             if overlap and self.overlap_wgrad:
                 ops.append(("fork", None, ()))
                 ops.append((SideLabel(label), fn, args[:-3] + (ws2, wsb, self.sp2)))
@@ -438,7 +445,7 @@ class Engine(object):
             if kind == "flatten" or not need[i]:
                 continue
             s0 = self.src[i][0]
-            x, y, dy = self._a(s0, True), self._a(i, True), self._g(i)
+            x, y, dy = self._a(s0, training), self._a(i, training), self._g(i)
             n_out = batch * _prod(self.shape[i])
             want_dx = need[s0]
             if kind in GEMM_KINDS or kind == "dwconv2d":
@@ -470,6 +477,11 @@ class Engine(object):
                 if want_dx:
                     add("dense_bwd_data", L.fnet_dense_bwd_data, m, k, n, self.math, dy, self._wp(i, 0), self._g(s0),
                         acc_flag(s0), ws, wsb, sp)
+            elif kind == "bn" and not training:
+                if want_dx:
+                    outer, a, inner = self._bn_view(i, batch)
+                    add("bn_bwd_infer", L.fnet_bn_bwd_infer, outer, a, inner, cfg["epsilon"], dy, self._wp(i, 0), self._wp(i, 3),
+                        self._g(s0), acc_flag(s0), sp)
             elif kind == "bn":
                 # dgamma/dbeta are always owed; when nothing upstream trains, dx lands on dy in place
                 outer, a, inner = self._bn_view(i, batch)
@@ -485,6 +497,8 @@ class Engine(object):
             elif kind == "gap":
                 h, w, c = self.shape[s0]
                 add("gap_bwd", L.fnet_gap_bwd, batch, h * w, c, dy, self._g(s0), acc_flag(s0), sp)
+            elif kind == "dropout" and not training:
+                add("add_bwd", L.fnet_accumulate, n_out, dy, self._g(s0), acc_flag(s0), sp)     # identity at inference
             elif kind == "dropout":
                 add("dropout_bwd", L.fnet_dropout_bwd, n_out, cfg["rate"], self.dropout_seed, i,
                     C.c_void_p(self.state.data_ptr()), dy, self._g(s0), acc_flag(s0), sp)
@@ -499,9 +513,9 @@ class Engine(object):
             elif kind == "mul":
                 a, b = self.src[i]
                 if need[a]:
-                    add("mul_bwd", L.fnet_mul_bwd, n_out, dy, self._a(b, True), self._g(a), acc_flag(a), sp)
+                    add("mul_bwd", L.fnet_mul_bwd, n_out, dy, self._a(b, training), self._g(a), acc_flag(a), sp)
                 if need[b]:
-                    add("mul_bwd", L.fnet_mul_bwd, n_out, dy, self._a(a, True), self._g(b), acc_flag(b), sp)
+                    add("mul_bwd", L.fnet_mul_bwd, n_out, dy, self._a(a, training), self._g(b), acc_flag(b), sp)
             elif kind == "concat":
                 axis = cfg["axis"] - 1
                 a, b = self.src[i]
@@ -550,6 +564,9 @@ class Engine(object):
     def _build_program(self, kind, batch):
         """kind: 'train' / 'eval' read the resident dataset through the permutation; '*_fed' expect xb/yb filled."""
         L, sp = self.lib, self.sp
+        if kind == "grad_input":        # act[0] / yb are filled by the caller; inference graph, gradient down to the input
+            return (self._forward_program(batch, False, save_for_backward=True) + [self._loss_op(batch, True)] +
+                    self._backward_program(batch, training=False, input_grad=True))
         training = kind.startswith("train")
         state = self.state if training else self.state_eval
         st = C.c_void_p(state.data_ptr())
@@ -655,7 +672,7 @@ class Engine(object):
             b = 4 * args[0] * args[2] * (args[1] + 1)
         elif label.startswith("bn_"):
             elems = args[0] * args[1] * args[2]
-            b = 4 * elems * {"bn_fwd_train": 3, "bn_fwd_infer": 2, "bn_bwd": 5}[label]
+            b = 4 * elems * {"bn_fwd_train": 3, "bn_fwd_infer": 2, "bn_bwd": 5, "bn_bwd_infer": 2}[label]
         elif label in ("act_fwd", "act_bwd"):
             b = 4 * args[1] * args[2] * (2 if label == "act_fwd" else 3)
         elif label.startswith("dropout"):
@@ -871,6 +888,29 @@ class Engine(object):
             seen_loss, seen_correct = 0.0, 0
         self._metrics_seen = (loss_sum, correct)
         return [(loss_sum - seen_loss) / b, (correct - seen_correct) / b]
+
+    def input_gradient(self, x, y):
+        """dL/dx of the mean categorical cross-entropy of a batch, in INFERENCE mode (dropout off, BatchNorm on
+        its moving statistics): what ART's ``KerasClassifier.loss_gradient`` hands to the attacks of the
+        robustness fitness (tensorflow_generator.py:151-173).  x, y: host arrays or device tensors; returns a
+        device tensor of x's shape that stays valid until the next call."""
+        b = int(x.shape[0])
+        self._ensure_capacity(max(b, self.capacity))
+        if 0 not in self.gact or self.gact[0].shape[0] < self.capacity:
+            with torch.cuda.device(self.device):
+                self.gact[0] = torch.empty((self.capacity,) + tuple(self.shape[0]), dtype=torch.float32, device=self.device)
+            for key in [k for k in self.programs if k[0] == "grad_input"]:
+                if key in self.graphs:
+                    self.lib.fnet_graph_destroy(self.graphs.pop(key))
+                self.programs.pop(key)
+        xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+        yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
+        with torch.cuda.stream(self.stream):
+            self.act[0][:b].copy_(xt, non_blocking=True)
+            self.yb[:b].copy_(yt, non_blocking=True)
+        self._step("grad_input", b)
+        self.stream.synchronize()          # host sources may be temporaries
+        return self.gact[0][:b]
 
     def fit(self, x, y, batch_size=32, epochs=1, validation_data=None, shuffle=True, callbacks=(), verbose=0,
             permutations=None, initial_epoch=0, augment=None, **_):

@@ -61,6 +61,8 @@ SIGNATURES = {
     "fnet_bn_workspace_bytes": (_SZ, [_I32]),
     "fnet_bn_fwd_train": (C.c_int, [_I32, _I32, _I32, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "fnet_bn_fwd_infer": (C.c_int, [_I32, _I32, _I32, _F, _P, _P, _P, _P, _P, _P, _P]),
+    "fnet_bn_bwd_infer": (C.c_int, [_I32, _I32, _I32, _F, _P, _P, _P, _P, C.c_int, _P]),
+    "fnet_l2_attack_step": (C.c_int, [_I32, _I64, _P, _P, _P, _P, _F, _F, _F, _F, _P, _P]),
     "fnet_bn_bwd": (C.c_int, [_I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int, _P, _SZ, _P]),
     "fnet_act_fwd": (C.c_int, [C.c_int, _I64, _I64, _P, _P, _P]),
     "fnet_act_bwd": (C.c_int, [C.c_int, _I64, _I64, _P, _P, _P, C.c_int, _P]),

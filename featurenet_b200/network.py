@@ -113,6 +113,14 @@ class Network(object):
     def predict(self, x, batch_size=32, **_):
         return self._need_engine().predict(x, batch_size=batch_size)
 
+    def train_on_batch(self, x, y, **_):
+        """keras Model.train_on_batch: one optimisation step on a host batch, returns [loss, accuracy]."""
+        return self._need_engine().train_on_batch(x, y)
+
+    def input_gradient(self, x, y):
+        """dL/dx in inference mode (device tensor): what the robustness attacks differentiate."""
+        return self._need_engine().input_gradient(x, y)
+
     def get_weights(self):
         return self._need_engine().get_weights()
 

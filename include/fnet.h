@@ -161,6 +161,10 @@ int fnet_bn_fwd_train(int32_t outer, int32_t a, int32_t inner, float eps, float 
 int fnet_bn_fwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const float *x, const float *gamma,
                       const float *beta, const float *moving_mean, const float *moving_var, float *y,
                       void *stream);
+/* input gradient in inference mode (moving statistics are constants): dx (+)= dy * gamma / sqrt(moving_var + eps);
+ * what an adversarial attack differentiates (tensorflow_generator.py:151-173 through ART's loss_gradient) */
+int fnet_bn_bwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const float *dy, const float *gamma,
+                      const float *moving_var, float *dx, int accumulate, void *stream);
 int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,
                 const float *save_mean, const float *save_rstd, float *dx, float *dgamma, float *dbeta,
                 int accumulate, void *ws, size_t ws_bytes, void *stream);
@@ -254,6 +258,19 @@ int fnet_gather_shift_flip(int32_t batch, int32_t h, int32_t w, int32_t c, const
                            const float *src, float *dst, void *stream);
 /* dst = float(src) * scale : the `astype('float32') / 255` of tensorflow_generator.py:310-313 */
 int fnet_u8_to_f32(int64_t n, const uint8_t *src, float scale, float *dst, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * One step of an L2 gradient attack on a batch of inputs (the FGSM / PGD updates behind the robustness
+ * fitness, tensorflow_generator.py:151-218 -> model/metrics.py:57-91 -> ART 0.9.0 FastGradientMethod /
+ * ProjectedGradientDescent with norm 2).  Per row b with active[b] != 0 (active == NULL: all rows):
+ *   delta = (adv_in[b] - x0[b]) + step * grad[b] / (||grad[b]||_2 + 1e-7)
+ *   if radius > 0 and ||delta||_2 > radius: delta *= radius / (||delta||_2 + 1e-7)      (projection)
+ *   adv_out[b] = clip(x0[b] + delta, clip_lo, clip_hi)
+ * inactive rows of adv_out are left as they are.  adv_out may alias adv_in.  One CTA per row, fixed reduction order.
+ * ------------------------------------------------------------------------------------------ */
+int fnet_l2_attack_step(int32_t batch, int64_t row, const float *x0, const float *grad, const float *adv_in,
+                        float *adv_out, float step, float radius, float clip_lo, float clip_hi,
+                        const uint8_t *active, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * CUDA-graph helpers: one train step (or eval step) is captured once and replayed, which

@@ -111,8 +111,15 @@ class OracleNet(object):
         return outs
 
     # ------------------------------------------------------------------ backward
-    def backward(self, targets):
-        """Gradients of mean-over-batch CCE for the last forward(training=True). Returns per-layer weight grads."""
+    def input_gradient(self, x, targets):
+        """dL/dx of the mean-over-batch CCE in INFERENCE mode (dropout off, BatchNorm on its moving statistics):
+        what an adversarial attack differentiates (ART's KerasClassifier.loss_gradient runs with learning_phase 0)."""
+        self.forward(x, training=False)
+        self.backward(targets, training=False)
+        return self.douts[0]
+
+    def backward(self, targets, training=True):
+        """Gradients of mean-over-batch CCE for the last forward. Returns per-layer weight grads; self.douts[0] is dL/dx."""
         rows, outs = self.rows, self.outs
         B = outs[0].shape[0]
         douts = [None] * len(rows)
@@ -126,6 +133,12 @@ class OracleNet(object):
             row = rows[i]
             cls, cfg, W, dy = row["class"], row["cfg"], self.weights[i], douts[i]
             if dy is None or cls == "InputLayer":
+                continue
+            if not training and cls == "Dropout":
+                give(row["inbound"][0], dy)
+                continue
+            if not training and cls == "BatchNormalization":
+                give(row["inbound"][0], ops.bn_infer_bwd(dy, W[0], W[3], cfg["axis"]))
                 continue
             src = row["inbound"]
             x = outs[src[0]] if src else None

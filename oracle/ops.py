@@ -284,6 +284,11 @@ def bn_infer_fwd(x, gamma, beta, moving_mean, moving_var, axis=1, eps=1e-3):
     return x * _bn_bcast(inv, x.ndim, axis) + _bn_bcast(beta - moving_mean * inv, x.ndim, axis)
 
 
+def bn_infer_bwd(dy, gamma, moving_var, axis=1, eps=1e-3):
+    """Input gradient of the inference-mode affine map (the statistics are constants)."""
+    return dy * _bn_bcast(gamma / np.sqrt(moving_var + eps), dy.ndim, axis)
+
+
 def bn_moving_update(moving, value, momentum=0.99):
     """K.moving_average_update: moving <- moving*momentum + value*(1-momentum)."""
     return moving * momentum + value * (1.0 - momentum)
