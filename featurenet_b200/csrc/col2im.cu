@@ -14,7 +14,7 @@
 namespace fnet {
 
 __global__ void __launch_bounds__(256) col2im_kernel(ConvGeom g, const float *__restrict__ t, float *__restrict__ dx,
-                                                     int accumulate, long long total) {
+                                                     int accumulate, int act, const float *__restrict__ yact, long long total) {
     pdl_prologue();
     const int taps_c = g.kh * g.kw * g.C;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(256) col2im_kernel(ConvGeom g, const float *__
                 sum += __ldg(tb + ((long long)ho * g.Wo + wo) * taps_c + (r * g.kw + s) * g.C);
             }
         }
-        dx[i] = accumulate ? dx[i] + sum : sum;
+        store_dx(dx, i, sum, accumulate, act, yact);
     }
 }
 
@@ -59,12 +59,12 @@ size_t col2im_t_bytes(const ConvGeom &g) {
     return (size_t)((bytes + 255) & ~255LL);
 }
 
-int col2im_scatter(const ConvGeom &g, const float *t, float *dx, int accumulate, cudaStream_t stream) {
+int col2im_scatter(const ConvGeom &g, const float *t, float *dx, DxEpilogue ep, cudaStream_t stream) {
     long long total = (long long)g.B * g.H * g.W * g.C;
     if (total == 0) return FNET_OK;
     long long blocks = ceil_div<long long>(total, 256);
     long long cap = (long long)kNumSMs * 16;
-    launch_pdl(col2im_kernel, dim3((unsigned)(blocks > cap ? cap : blocks)), dim3(256), 0, stream, g, t, dx, accumulate, total);
+    launch_pdl(col2im_kernel, dim3((unsigned)(blocks > cap ? cap : blocks)), dim3(256), 0, stream, g, t, dx, ep.accumulate, ep.act, ep.y, total);
     return check_launch("conv2d_bwd_data[col2im]");
 }
 

@@ -130,6 +130,13 @@ __device__ __forceinline__ float act_grad(float y, int act) {
     }
 }
 
+// epilogue of every data gradient: dx = (accumulate ? dx + v : v) * act'(y)   (see DxEpilogue in igemm.cuh)
+__device__ __forceinline__ void store_dx(float *dx, long long at, float v, int accumulate, int act, const float *y) {
+    if (accumulate) v += dx[at];
+    if (act) v *= act_grad(__ldg(y + at), act);
+    dx[at] = v;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

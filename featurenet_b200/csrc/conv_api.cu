@@ -28,8 +28,10 @@ int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *
     return rc;
 }
 
-int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws,
                size_t ws_bytes, cudaStream_t s) {
+    // few channels on BOTH sides: the direct kernel beats GEMM + col2im (28x28x6 -> 12, 5x5: 54 vs 112 us)
+    if (skinny_supported(g, 1, false)) return skinny_dgrad(g, dz, w, dx, ep, s);
     if (size_t t_bytes = col2im_t_bytes(g)) {
         // T = dz x w^T as the data gradient of a dense layer [taps*C] -> [K], then dx = col2im(T)
         if (!ws || ws_bytes < t_bytes) {
@@ -38,13 +40,12 @@ int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, flo
         }
         float *t = reinterpret_cast<float *>(ws);
         ConvGeom gd = dense_geom((long long)g.B * g.Ho * g.Wo, (long long)g.kh * g.kw * g.C, g.K);
-        int rc = conv_dgrad(gd, math, dz, w, t, 0, reinterpret_cast<char *>(ws) + t_bytes, ws_bytes - t_bytes, s);
-        return rc == FNET_OK ? col2im_scatter(g, t, dx, accumulate, s) : rc;
+        int rc = conv_dgrad(gd, math, dz, w, t, DxEpilogue{0, 0, nullptr}, reinterpret_cast<char *>(ws) + t_bytes, ws_bytes - t_bytes, s);
+        return rc == FNET_OK ? col2im_scatter(g, t, dx, ep, s) : rc;
     }
-    if (skinny_supported(g, 1, false)) return skinny_dgrad(g, dz, w, dx, accumulate, s);
-    if (tma_gemm_supported(g, math, 1)) return tma_gemm_dgrad(g, dz, w, dx, accumulate, s);
-    if (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) return tc_conv_dgrad(g, math, dz, w, dx, accumulate, ws, ws_bytes, s);
-    return simt_conv_dgrad(g, dz, w, dx, accumulate, ws, ws_bytes, s);
+    if (tma_gemm_supported(g, math, 1)) return tma_gemm_dgrad(g, dz, w, dx, ep, s);
+    if (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) return tc_conv_dgrad(g, math, dz, w, dx, ep, ws, ws_bytes, s);
+    return simt_conv_dgrad(g, dz, w, dx, ep, ws, ws_bytes, s);
 }
 
 int conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
@@ -97,7 +98,19 @@ int fnet_conv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const float
     if (rc) return rc;
     if ((rc = check_math(d->math, "fnet_conv2d_bwd_data"))) return rc;
     FNET_REQUIRE(dz && w && dx, "fnet_conv2d_bwd_data: null pointer");
-    return conv_dgrad(g, d->math, dz, w, dx, accumulate, ws, ws_bytes, as_stream(stream));
+    return conv_dgrad(g, d->math, dz, w, dx, DxEpilogue{accumulate, 0, nullptr}, ws, ws_bytes, as_stream(stream));
+}
+
+int fnet_conv2d_bwd_data_act(const fnet_conv2d_desc *d, const float *dz, const float *w, float *dx, int accumulate,
+                             int act, const float *y, void *ws, size_t ws_bytes, void *stream) {
+    ConvGeom g;
+    int rc = geom_checked(d, g, "fnet_conv2d_bwd_data_act");
+    if (rc) return rc;
+    if ((rc = check_math(d->math, "fnet_conv2d_bwd_data_act"))) return rc;
+    FNET_REQUIRE(dz && w && dx, "fnet_conv2d_bwd_data_act: null pointer");
+    FNET_REQUIRE(act >= FNET_ACT_NONE && act <= FNET_ACT_SIGMOID && (act == FNET_ACT_NONE || y != nullptr),
+                 "fnet_conv2d_bwd_data_act: relu / tanh / sigmoid with the producing layer's output, or none");
+    return conv_dgrad(g, d->math, dz, w, dx, DxEpilogue{accumulate, act, y}, ws, ws_bytes, as_stream(stream));
 }
 
 int fnet_conv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const float *dz, float *dw, float *dbias,
@@ -135,7 +148,19 @@ int fnet_dense_bwd_data(int64_t m, int64_t k, int64_t n, int math, const float *
     if ((rc = check_math(math, "fnet_dense_bwd_data"))) return rc;
     if (m == 0) return FNET_OK;
     FNET_REQUIRE(dz && w && dx, "fnet_dense_bwd_data: null pointer");
-    return conv_dgrad(dense_geom(m, k, n), math, dz, w, dx, accumulate, ws, ws_bytes, as_stream(stream));
+    return conv_dgrad(dense_geom(m, k, n), math, dz, w, dx, DxEpilogue{accumulate, 0, nullptr}, ws, ws_bytes, as_stream(stream));
+}
+
+int fnet_dense_bwd_data_act(int64_t m, int64_t k, int64_t n, int math, const float *dz, const float *w, float *dx,
+                            int accumulate, int act, const float *y, void *ws, size_t ws_bytes, void *stream) {
+    int rc = check_dense(m, k, n, "fnet_dense_bwd_data_act");
+    if (rc) return rc;
+    if ((rc = check_math(math, "fnet_dense_bwd_data_act"))) return rc;
+    if (m == 0) return FNET_OK;
+    FNET_REQUIRE(dz && w && dx, "fnet_dense_bwd_data_act: null pointer");
+    FNET_REQUIRE(act >= FNET_ACT_NONE && act <= FNET_ACT_SIGMOID && (act == FNET_ACT_NONE || y != nullptr),
+                 "fnet_dense_bwd_data_act: relu / tanh / sigmoid with the producing layer's output, or none");
+    return conv_dgrad(dense_geom(m, k, n), math, dz, w, dx, DxEpilogue{accumulate, act, y}, ws, ws_bytes, as_stream(stream));
 }
 
 int fnet_dense_bwd_filter(int64_t m, int64_t k, int64_t n, int math, const float *x, const float *dz, float *dw,

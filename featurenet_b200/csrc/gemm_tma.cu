@@ -472,8 +472,8 @@ int tma_gemm_fwd(const ConvGeom &g, int act, const float *x, const float *w, con
     return tma_gemm_run(p, x, (long long)g.B * g.H * g.W, g.C, w, g.K, true, stream, "conv2d_fwd[tf32,tma]");
 }
 
-int tma_gemm_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t stream) {
-    DgradProblem p{g, dz, w, dx, accumulate};
+int tma_gemm_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t stream) {
+    DgradProblem p{g, dz, w, dx, ep.accumulate, ep.act, ep.y};
     return tma_gemm_run(p, dz, (long long)g.B * g.H * g.W, g.K, w, g.C, false, stream, "conv2d_bwd_data[tf32,tma]");
 }
 

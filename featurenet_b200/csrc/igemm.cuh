@@ -8,6 +8,15 @@ struct ConvGeom {
     int B, H, W, C, Ho, Wo, K, kh, kw, sh, sw, pt, pl, dh, dw;
 };
 
+// What a data gradient does with its result: dx = (accumulate ? dx + v : v) * act'(y).  act / y describe the
+// activation of the layer that PRODUCED x (y = that layer's output, same shape as dx): folding its derivative into
+// this epilogue saves the separate act_bwd pass over the tensor.  act == FNET_ACT_NONE: plain store.
+struct DxEpilogue {
+    int accumulate;
+    int act;
+    const float *y;
+};
+
 int geom_checked(const fnet_conv2d_desc *d, ConvGeom &g, const char *what);
 ConvGeom dense_geom(long long m, long long k, long long n);
 
@@ -15,7 +24,7 @@ ConvGeom dense_geom(long long m, long long k, long long n);
 size_t simt_conv_workspace(const ConvGeom &g);
 int simt_conv_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, void *ws,
                   size_t ws_bytes, cudaStream_t stream);
-int simt_conv_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+int simt_conv_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws,
                     size_t ws_bytes, cudaStream_t stream);
 int simt_conv_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                     size_t ws_bytes, cudaStream_t stream);
@@ -25,7 +34,7 @@ bool tc_supported(const ConvGeom &g, int math, int product);   // product: 0 fwd
 size_t tc_conv_workspace(const ConvGeom &g, int math);
 int tc_conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
                 void *ws, size_t ws_bytes, cudaStream_t stream);
-int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws,
                   size_t ws_bytes, cudaStream_t stream);
 int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                   size_t ws_bytes, cudaStream_t stream);
@@ -33,7 +42,7 @@ int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, 
 // FNET_MATH_TF32, layers that are plain GEMMs (Dense, 1x1 stride-1 convolutions): TMA-fed persistent kernel (gemm_tma.cu)
 bool tma_gemm_supported(const ConvGeom &g, int math, int product);   // product: 0 fwd, 1 dgrad
 int tma_gemm_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t stream);
-int tma_gemm_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t stream);
+int tma_gemm_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t stream);
 size_t tma_gemm_workspace(const ConvGeom &g, int math);
 int tma_gemm_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
                    cudaStream_t stream);
@@ -48,13 +57,13 @@ int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const
 // y = act(bias + sum of `splits` partial [M x N] products), fixed order (igemm_simt.cu)
 int simt_reduce_fwd_partials(const ConvGeom &g, int act, const float *bias, float *y, int splits, const float *partial,
                              cudaStream_t stream);
-int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t s);
+int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t s);
 int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
                  cudaStream_t s);
 
 // data gradient for few input channels: dense GEMM into T (workspace) + col2im (col2im.cu)
 size_t col2im_t_bytes(const ConvGeom &g);                    // 0 = not applicable
-int col2im_scatter(const ConvGeom &g, const float *t, float *dx, int accumulate, cudaStream_t stream);
+int col2im_scatter(const ConvGeom &g, const float *t, float *dx, DxEpilogue ep, cudaStream_t stream);
 
 int run_softmax_rows(int64_t rows, int64_t cols, const float *x, float *y, cudaStream_t stream);
 

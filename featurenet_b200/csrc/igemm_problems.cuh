@@ -185,6 +185,8 @@ struct DgradProblem {
     const float *dz, *w;
     float *dx;
     int accumulate;
+    int act;            // activation of the layer that produced x ...
+    const float *yact;  // ... and its output: dx is multiplied by act'(yact) (DxEpilogue)
     typedef PixelCtx Row;
     typedef TapCtx Col;
     typedef DgradCursor BCursor;                // B(k, n) = w[tap][n][ko] with k = tap*K + ko
@@ -219,13 +221,16 @@ struct DgradProblem {
     __device__ long long b_stride_k() const { return 1; }
     __device__ const float *any_ptr() const { return dz; }
     __device__ void store(int m, int n, float v) const {
-        long long at = (long long)m * g.C + n;
-        dx[at] = accumulate ? dx[at] + v : v;
+        store_dx(dx, (long long)m * g.C + n, v, accumulate, act, yact);
     }
     __device__ void store_col(int m, int count, int n, const float *src, int src_stride) const {
         float *q = dx + (long long)m * g.C + n;
         const long long ld = g.C;
-        if (accumulate) {
+        if (act) {
+            const long long at = (long long)m * g.C + n;
+#pragma unroll 4
+            for (int r = 0; r < count; ++r) store_dx(dx, at + r * ld, src[r * src_stride], accumulate, act, yact);
+        } else if (accumulate) {
 #pragma unroll 8
             for (int r = 0; r < count; ++r) q[r * ld] += src[r * src_stride];
         } else {

@@ -355,9 +355,9 @@ int simt_conv_fwd(const ConvGeom &g, int act, const float *x, const float *w, co
                        "conv2d_fwd");
 }
 
-int simt_conv_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+int simt_conv_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws,
                     size_t ws_bytes, cudaStream_t stream) {
-    DgradProblem p{g, dz, w, dx, accumulate};
+    DgradProblem p{g, dz, w, dx, ep.accumulate, ep.act, ep.y};
     return run_problem(p, (long long)g.B * g.H * g.W, g.C, (long long)g.kh * g.kw * g.K, ws, ws_bytes, stream,
                        "conv2d_bwd_data");
 }

@@ -501,9 +501,9 @@ int tc_conv_fwd(const ConvGeom &g, int math, int act, const float *x, const floa
     return tc_run(p, math, (long long)g.B * g.Ho * g.Wo, g.K, (long long)g.kh * g.kw * g.C, ws, ws_bytes, stream, "conv2d_fwd[tf32]");
 }
 
-int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, int accumulate, void *ws,
+int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws,
                   size_t ws_bytes, cudaStream_t stream) {
-    DgradProblem p{g, dz, w, dx, accumulate};
+    DgradProblem p{g, dz, w, dx, ep.accumulate, ep.act, ep.y};
     return tc_run(p, math, (long long)g.B * g.H * g.W, g.C, (long long)g.kh * g.kw * g.K, ws, ws_bytes, stream, "conv2d_bwd_data[tf32]");
 }
 

@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(256) dense_stream_wgrad_kernel(int M, int K, i
 template <int NMAX>
 __global__ void __launch_bounds__(256) dense_rows_dgrad_kernel(int M, int K, int N, const float *__restrict__ dz,
                                                                const float *__restrict__ w, float *__restrict__ dx,
-                                                               int accumulate) {
+                                                               int accumulate, int act, const float *__restrict__ yact) {
     pdl_prologue();
     constexpr int ROWS = 16;
     __shared__ __align__(16) float g_s[ROWS][NMAX];
@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(256) dense_rows_dgrad_kernel(int M, int K, int
                 v = fmaf(d.z, wr[4 * q + 2], v);
                 v = fmaf(d.w, wr[4 * q + 3], v);
             }
-            out[(long long)r * K] = accumulate ? out[(long long)r * K] + v : v;
+            store_dx(out, (long long)r * K, v, accumulate, act, yact ? yact + (long long)m0 * K + k : nullptr);
         }
     }
 }
@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(256) conv_small_fwd_kernel(ConvGeom g, int act
 template <int NMAX>
 __global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const float *__restrict__ dz,
                                                                const float *__restrict__ w, float *__restrict__ dx,
-                                                               int accumulate) {
+                                                               int accumulate, int act, const float *__restrict__ yact) {
     pdl_prologue();
     extern __shared__ float w_s[];                  // [taps][C][K]
     const int total_w = g.kh * g.kw * g.C * g.K, C = g.C, K = g.K;
@@ -363,7 +363,7 @@ __global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const
         float *out = dx + m * C;
 #pragma unroll
         for (int c = 0; c < NMAX; ++c)
-            if (c < C) out[c] = accumulate ? out[c] + acc[c] : acc[c];
+            if (c < C) store_dx(out, c, acc[c], accumulate, act, yact ? yact + (out - dx) : nullptr);
     }
 }
 
@@ -517,20 +517,20 @@ int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const
     return check_launch("conv2d_fwd[small]");
 }
 
-int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, int accumulate, cudaStream_t s) {
+int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t s) {
     if (is_dense_geom(g)) {
         long long bx = ceil_div<long long>(g.C, 256);
         if (bx > 4096) bx = 4096;
         dim3 grid((unsigned)bx, (unsigned)ceil_div<long long>(g.B, 16));
-#define FNET_CALL(NM) launch_pdl(dense_rows_dgrad_kernel<NM>, dim3(grid), dim3(256), 0, s, g.B, g.C, g.K, dz, w, dx, accumulate)
+#define FNET_CALL(NM) launch_pdl(dense_rows_dgrad_kernel<NM>, dim3(grid), dim3(256), 0, s, g.B, g.C, g.K, dz, w, dx, ep.accumulate, ep.act, ep.y)
         FNET_BY_COLUMNS(g.K, FNET_CALL);
 #undef FNET_CALL
         return check_launch("dense_bwd_data[skinny]");
     }
     size_t smem = (size_t)g.kh * g.kw * g.C * g.K * sizeof(float);
     long long M = (long long)g.B * g.H * g.W;
-    if (g.C <= 8) launch_pdl(conv_small_dgrad_kernel<8>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, accumulate);
-    else launch_pdl(conv_small_dgrad_kernel<16>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, accumulate);
+    if (g.C <= 8) launch_pdl(conv_small_dgrad_kernel<8>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, ep.accumulate, ep.act, ep.y);
+    else launch_pdl(conv_small_dgrad_kernel<16>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, ep.accumulate, ep.act, ep.y);
     return check_launch("conv2d_bwd_data[small]");
 }
 

@@ -89,6 +89,7 @@ class Engine(object):
         self.side = torch.cuda.Stream(device=self.device)
         self.sp2 = C.c_void_p(self.side.cuda_stream)
         self.overlap_wgrad = os.environ.get("FNET_NO_OVERLAP", "0") != "1"
+        self.fuse_act_bwd = os.environ.get("FNET_NO_ACT_FUSION", "0") != "1"
         self.nodes = list(net.layers)
         self.index = {id(n): i for i, n in enumerate(self.nodes)}
         self.src = [[self.index[id(t.node)] for t in n.inputs] for n in self.nodes]
@@ -440,6 +441,31 @@ class Engine(object):
 
         gw = lambda i, k: self._wp(i, k, self.grads)
         last = len(self.nodes) - 1
+        # Activation derivative folded into the data gradient that PRODUCES the tensor: when an activated GEMM layer
+        # has exactly one consumer and that consumer is a Conv2D / Dense, the consumer's data-gradient epilogue
+        # multiplies by act'(y) and the separate act_bwd pass over the tensor disappears.
+        fused_into = {}
+        if training and self.fuse_act_bwd:
+            consumers = {}
+            for j in range(1, len(self.nodes)):
+                if self.nodes[j].kind == "flatten":
+                    continue
+                for s in self.src[j]:
+                    consumers.setdefault(self._resolve(s, True), []).append(j)
+            for r, users in consumers.items():
+                node_r = self.nodes[r]
+                if (len(users) == 1 and r != last and node_r.kind in GEMM_KINDS + ("dwconv2d",) and need[r]
+                        and fl.ACT[node_r.cfg["activation"]] in (1, 2, 3)
+                        and self.nodes[users[0]].kind in ("conv2d", "dense") and len(self.src[users[0]]) == 1):
+                    fused_into[r] = users[0]
+
+        def dx_epilogue(i, s0):
+            """(act, y) for node i's data gradient when it carries the activation derivative of its producer."""
+            r = self._resolve(s0, True)
+            if fused_into.get(r) == i:
+                return fl.ACT[self.nodes[r].cfg["activation"]], self._a(r, True)
+            return None
+
         for i in range(last, 0, -1):
             node, kind, cfg = self.nodes[i], self.nodes[i].kind, self.nodes[i].cfg
             if kind == "flatten" or not need[i]:
@@ -450,14 +476,19 @@ class Engine(object):
             want_dx = need[s0]
             if kind in GEMM_KINDS or kind == "dwconv2d":
                 act = fl.ACT[cfg["activation"]]
-                if act and i != last:           # the head's dz comes straight from the loss kernel
+                if act and i != last and i not in fused_into:   # the head's dz comes straight from the loss kernel
                     cols = self.shape[i][-1]
                     add("act_bwd", L.fnet_act_bwd, act, n_out // cols, cols, y, dy, dy, 0, sp)
             if kind == "conv2d":
                 d = self._conv_desc(i, batch)
                 add_wgrad(want_dx, "conv2d_bwd_filter", L.fnet_conv2d_bwd_filter, d, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
                 if want_dx:
-                    add("conv2d_bwd_data", L.fnet_conv2d_bwd_data, d, dy, self._wp(i, 0), self._g(s0), acc_flag(s0), ws, wsb, sp)
+                    ep = dx_epilogue(i, s0)
+                    if ep:
+                        add("conv2d_bwd_data", L.fnet_conv2d_bwd_data_act, d, dy, self._wp(i, 0), self._g(s0), acc_flag(s0),
+                            ep[0], ep[1], ws, wsb, sp)
+                    else:
+                        add("conv2d_bwd_data", L.fnet_conv2d_bwd_data, d, dy, self._wp(i, 0), self._g(s0), acc_flag(s0), ws, wsb, sp)
             elif kind == "dwconv2d":
                 d = self._conv_desc(i, batch)
                 add_wgrad(want_dx, "dwconv2d_bwd_filter", L.fnet_dwconv2d_bwd_filter, d, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
@@ -475,8 +506,13 @@ class Engine(object):
                 m, k, n = self._dense_mkn(i, batch)
                 add_wgrad(want_dx, "dense_bwd_filter", L.fnet_dense_bwd_filter, m, k, n, self.math, x, dy, gw(i, 0), gw(i, 1), ws, wsb, sp)
                 if want_dx:
-                    add("dense_bwd_data", L.fnet_dense_bwd_data, m, k, n, self.math, dy, self._wp(i, 0), self._g(s0),
-                        acc_flag(s0), ws, wsb, sp)
+                    ep = dx_epilogue(i, s0)
+                    if ep:
+                        add("dense_bwd_data", L.fnet_dense_bwd_data_act, m, k, n, self.math, dy, self._wp(i, 0), self._g(s0),
+                            acc_flag(s0), ep[0], ep[1], ws, wsb, sp)
+                    else:
+                        add("dense_bwd_data", L.fnet_dense_bwd_data, m, k, n, self.math, dy, self._wp(i, 0), self._g(s0),
+                            acc_flag(s0), ws, wsb, sp)
             elif kind == "bn" and not training:
                 if want_dx:
                     outer, a, inner = self._bn_view(i, batch)

@@ -44,11 +44,13 @@ SIGNATURES = {
     "fnet_conv2d_workspace_bytes": (_SZ, [_CD]),
     "fnet_conv2d_fwd": (C.c_int, [_CD, _P, _P, _P, _P, _P, _SZ, _P]),
     "fnet_conv2d_bwd_data": (C.c_int, [_CD, _P, _P, _P, C.c_int, _P, _SZ, _P]),
+    "fnet_conv2d_bwd_data_act": (C.c_int, [_CD, _P, _P, _P, C.c_int, C.c_int, _P, _P, _SZ, _P]),
     "fnet_conv2d_bwd_filter": (C.c_int, [_CD, _P, _P, _P, _P, _P, _SZ, _P]),
     "fnet_dense_workspace_bytes": (_SZ, [_I64, _I64, _I64]),
     "fnet_dense_fwd": (C.c_int, [_I64, _I64, _I64, C.c_int, C.c_int, _P, _P, _P, _P, _P, _SZ, _P]),
     "fnet_dense_fwd_static": (C.c_int, [_I64, _I64, _I64, C.c_int, _P, _P, _P, _P, _P]),
     "fnet_dense_bwd_data": (C.c_int, [_I64, _I64, _I64, C.c_int, _P, _P, _P, C.c_int, _P, _SZ, _P]),
+    "fnet_dense_bwd_data_act": (C.c_int, [_I64, _I64, _I64, C.c_int, _P, _P, _P, C.c_int, C.c_int, _P, _P, _SZ, _P]),
     "fnet_dense_bwd_filter": (C.c_int, [_I64, _I64, _I64, C.c_int, _P, _P, _P, _P, _P, _SZ, _P]),
     "fnet_dwconv2d_workspace_bytes": (_SZ, [_CD]),
     "fnet_dwconv2d_fwd": (C.c_int, [_CD, _P, _P, _P, _P, _P]),

@@ -69,6 +69,13 @@ int fnet_conv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w, c
 /* dx (+)= conv_transpose(dz, w), dz = dL/d(pre-activation) */
 int fnet_conv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const float *w, float *dx, int accumulate,
                          void *ws, size_t ws_bytes, void *stream);
+/* the same, followed by the derivative of the activation of the layer that PRODUCED x:
+ *   dx = (accumulate ? dx + conv_transpose(dz, w) : conv_transpose(dz, w)) * act'(y)
+ * with y that layer's output (same shape as dx) and act relu / tanh / sigmoid.  This is Keras' backward through
+ * `Conv2D(..., activation=act)` followed by another layer, minus one pass over the tensor (the separate
+ * fnet_act_bwd).  With several gradient pieces, only the call that delivers the LAST one may carry the activation. */
+int fnet_conv2d_bwd_data_act(const fnet_conv2d_desc *d, const float *dz, const float *w, float *dx, int accumulate,
+                             int act, const float *y, void *ws, size_t ws_bytes, void *stream);
 /* dw = x (*) dz, dbias = column sums of dz (dbias may be NULL); deterministic split reduction */
 int fnet_conv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const float *dz, float *dw, float *dbias,
                            void *ws, size_t ws_bytes, void *stream);
@@ -83,6 +90,9 @@ int fnet_dense_fwd(int64_t m, int64_t k, int64_t n, int act, int math, const flo
                    const float *bias, float *y, void *ws, size_t ws_bytes, void *stream);
 int fnet_dense_bwd_data(int64_t m, int64_t k, int64_t n, int math, const float *dz, const float *w, float *dx,
                         int accumulate, void *ws, size_t ws_bytes, void *stream);
+/* fnet_dense_bwd_data with the activation derivative of the producing layer folded in (see fnet_conv2d_bwd_data_act) */
+int fnet_dense_bwd_data_act(int64_t m, int64_t k, int64_t n, int math, const float *dz, const float *w, float *dx,
+                            int accumulate, int act, const float *y, void *ws, size_t ws_bytes, void *stream);
 int fnet_dense_bwd_filter(int64_t m, int64_t k, int64_t n, int math, const float *x, const float *dz, float *dw,
                           float *dbias, void *ws, size_t ws_bytes, void *stream);
 
