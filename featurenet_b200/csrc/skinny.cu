@@ -370,13 +370,16 @@ __global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const
 // filter gradient of the smallest convolutions: every (tap, c, k) partial sum (and the bias sums) lives in
 // registers; partial[block][row][k] goes to the workspace and is reduced in a fixed order afterwards
 constexpr int kWgradRegs = 64;
-constexpr int kWgradBlocks = 2 * kNumSMs;
+constexpr int kWgradBlocks = 4 * kNumSMs;
 
-template <int KT>     // KT = number of output channels (compile time, so that every partial sum has a fixed register)
+// KT = number of output channels, RT = bound on the filter rows (both compile time, so that every partial sum has
+// a fixed register and no more registers are held than the layer needs: 142 registers for a 4 x 6 gradient meant
+// one CTA per SM and 340 GB/s on a kernel whose only job is to stream x and dz once)
+template <int KT, int RT>
 __global__ void __launch_bounds__(256) conv_small_wgrad_kernel(ConvGeom g, int rows, const float *__restrict__ x,
                                                                const float *__restrict__ dz, float *__restrict__ partial) {
     pdl_prologue();
-    constexpr int ROWS_MAX = kWgradRegs / KT;
+    constexpr int ROWS_MAX = RT < kWgradRegs / KT ? RT : kWgradRegs / KT;
     __shared__ float red[8][kWgradRegs];
     const int C = g.C, taps_c = g.kh * g.kw * C;
     const int total = rows * KT;                    // rows = taps*C (+1 bias row) <= ROWS_MAX
@@ -560,16 +563,24 @@ int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, 
         return FNET_ERR_WORKSPACE;
     }
     float *partial = reinterpret_cast<float *>(ws);
+#define FNET_WGRAD_ROWS(KT_)                                                                                              \
+    do {                                                                                                                  \
+        if (rows <= 4) launch_pdl(conv_small_wgrad_kernel<KT_, 4>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial);       \
+        else if (rows <= 8) launch_pdl(conv_small_wgrad_kernel<KT_, 8>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial);  \
+        else if (rows <= 16) launch_pdl(conv_small_wgrad_kernel<KT_, 16>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial);\
+        else launch_pdl(conv_small_wgrad_kernel<KT_, 64>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial);                \
+    } while (0)
     switch (g.K) {
-        case 1: launch_pdl(conv_small_wgrad_kernel<1>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
-        case 2: launch_pdl(conv_small_wgrad_kernel<2>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
-        case 3: launch_pdl(conv_small_wgrad_kernel<3>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
-        case 4: launch_pdl(conv_small_wgrad_kernel<4>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
-        case 5: launch_pdl(conv_small_wgrad_kernel<5>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
-        case 6: launch_pdl(conv_small_wgrad_kernel<6>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
-        case 7: launch_pdl(conv_small_wgrad_kernel<7>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
-        default: launch_pdl(conv_small_wgrad_kernel<8>, dim3(blocks), dim3(256), 0, s, g, rows, x, dz, partial); break;
+        case 1: FNET_WGRAD_ROWS(1); break;
+        case 2: FNET_WGRAD_ROWS(2); break;
+        case 3: FNET_WGRAD_ROWS(3); break;
+        case 4: FNET_WGRAD_ROWS(4); break;
+        case 5: FNET_WGRAD_ROWS(5); break;
+        case 6: FNET_WGRAD_ROWS(6); break;
+        case 7: FNET_WGRAD_ROWS(7); break;
+        default: FNET_WGRAD_ROWS(8); break;
     }
+#undef FNET_WGRAD_ROWS
     int rc = check_launch("conv2d_bwd_filter[small]");
     if (rc) return rc;
     launch_pdl(conv_small_wgrad_reduce_kernel, dim3(1), dim3(256), 0, s, blocks, taps_c, g.K, total, partial, dw, dbias);
