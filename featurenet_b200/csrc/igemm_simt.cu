@@ -224,6 +224,26 @@ __global__ void __launch_bounds__(256, 3) igemm_simt_kernel(P p, int M, int N, i
         }
     }
 
+    if (!partial && p.has_pre()) {
+        // data gradient that also carries an activation derivative: fetch all multipliers first (independent
+        // loads in flight together), then store -- a load between the stores would serialise on memory latency
+        float mult[TM][TN];
+#pragma unroll
+        for (int i = 0; i < TM; ++i)
+#pragma unroll
+            for (int j = 0; j < TN; ++j) {
+                int m = m0 + ty * TM + i, n = n0 + tx * TN + j;
+                mult[i][j] = (m < M && n < N) ? p.pre(m, n) : 0.f;
+            }
+#pragma unroll
+        for (int i = 0; i < TM; ++i)
+#pragma unroll
+            for (int j = 0; j < TN; ++j) {
+                int m = m0 + ty * TM + i, n = n0 + tx * TN + j;
+                if (m < M && n < N) p.store_pre(m, n, acc[i][j], mult[i][j]);
+            }
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < TM; ++i) {
         int m = m0 + ty * TM + i;

@@ -89,7 +89,9 @@ class Engine(object):
         self.side = torch.cuda.Stream(device=self.device)
         self.sp2 = C.c_void_p(self.side.cuda_stream)
         self.overlap_wgrad = os.environ.get("FNET_NO_OVERLAP", "0") != "1"
-        self.fuse_act_bwd = os.environ.get("FNET_NO_ACT_FUSION", "0") != "1"
+        # folding act'(y) into the producing data gradient pays on the FFMA kernels; the tensor-core epilogues are
+        # the critical path of their kernels (one tile's epilogue per main loop) and do not hide the extra loads
+        self.fuse_act_bwd = os.environ.get("FNET_NO_ACT_FUSION", "0") != "1" and self.math == fl.MATH["fp32"]
         self.nodes = list(net.layers)
         self.index = {id(n): i for i, n in enumerate(self.nodes)}
         self.src = [[self.index[id(t.node)] for t in n.inputs] for n in self.nodes]

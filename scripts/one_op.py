@@ -48,6 +48,7 @@ if kind == "dense":
     timed("fwd", lambda: L.fnet_dense_fwd(m, k, n, 0, math, ptr(x), ptr(w), ptr(b), ptr(y), ptr(ws), ws.numel(), None), flops, nbytes, reps)
     timed("dgrad", lambda: L.fnet_dense_bwd_data(m, k, n, math, ptr(dz), ptr(w), ptr(dx), 0, ptr(ws), ws.numel(), None), flops, nbytes, reps)
     timed("wgrad", lambda: L.fnet_dense_bwd_filter(m, k, n, math, ptr(x), ptr(dz), ptr(dw), ptr(db), ptr(ws), ws.numel(), None), flops, nbytes, reps)
+    timed("dgrad+act", lambda: L.fnet_dense_bwd_data_act(m, k, n, math, ptr(dz), ptr(w), ptr(dx), 0, 1, ptr(x), ptr(ws), ws.numel(), None), flops, nbytes, reps)
 else:
     bsz, h, wd, c, ko, kh, kw, st = (int(v) for v in sys.argv[2:10])
     math = fl.MATH[sys.argv[10] if len(sys.argv) > 10 else "fp32"]
