@@ -51,7 +51,7 @@ size_t col2im_t_bytes(const ConvGeom &g) {
         mode = (e && e[0] == '0') ? 0 : 1;
     }
     long long taps = (long long)g.kh * g.kw;
-    if (!mode || taps < 4 || g.C > 16) return 0;
+    if (!mode || taps < 4 || g.C > 16 || g.K < 32) return 0;   // few output channels: the implicit GEMM is cheaper (K = 12: 54 vs 107 us)
     long long mo = (long long)g.B * g.Ho * g.Wo;
     long long bytes = mo * taps * g.C * 4;
     // worth it once the gather it replaces is long enough; T must stay a reasonable fraction of HBM
