@@ -124,3 +124,47 @@ def test_dense_adjoint_full_size(L, m, k, n, math, tol):
     # against a library GEMM of the same size (fp32 reference of the same op)
     want = x.double() @ w.double()
     assert float((y.double() - want).abs().max()) <= (5e-3 if math == "tf32" else tol) * float(want.abs().max())
+
+
+GUARD = 4096      # floats on each side of every output
+
+
+def guarded(shape):
+    """An output tensor embedded in a larger allocation whose margins hold a sentinel."""
+    n = int(np.prod(shape))
+    whole = torch.full((n + 2 * GUARD,), 12345.0, device="cuda")
+    return whole, whole[GUARD: GUARD + n].view(*shape)
+
+
+def intact(whole, n):
+    return bool((whole[:GUARD] == 12345.0).all().item()) and bool((whole[GUARD + n:] == 12345.0).all().item())
+
+
+@pytest.mark.parametrize("math", ["fp32", "tf32", "tf32x3"])
+@pytest.mark.parametrize("xs,k,kout,s", [((3, 9, 7, 5), (3, 3), 7, (2, 2)), ((5, 13, 11, 33), (3, 3), 130, (1, 1)),
+                                         ((130, 6, 6, 4), (1, 1), 16, (1, 1)), ((67, 16, 16, 24), (1, 1), 100, (1, 1)),
+                                         ((40, 14, 14, 12), (5, 5), 120, (1, 1)), ((2, 5, 5, 2), (7, 7), 4, (1, 1))])
+def test_no_kernel_writes_outside_its_output(L, xs, k, kout, s, math):
+    """compute-sanitizer is closed on this pool: out-of-bounds WRITES are looked for with guard bands around every
+    output of the three products, on ragged shapes that exercise every tile edge, in all math modes."""
+    from featurenet_b200 import lib as fl
+    g = torch.Generator(device="cuda").manual_seed(7)
+    rnd = lambda *shape: torch.randn(*shape, device="cuda", generator=g)
+    desc = conv_desc(fl, xs, k, kout, s, "same", (1, 1), "relu", math)
+    ws_whole, ws = guarded((max(int(L.fnet_conv2d_workspace_bytes(C.byref(desc))) // 4, 64),))
+    ws_bytes = ws.numel() * 4
+    x, w, b = rnd(*xs), rnd(k[0], k[1], xs[3], kout) * 0.2, rnd(kout)
+    y_shape = (xs[0], desc.out_h, desc.out_w, kout)
+    dy = rnd(*y_shape)
+    yw, y = guarded(y_shape)
+    dxw, dx = guarded(xs)
+    dww, dw = guarded(tuple(w.shape))
+    dbw, db = guarded((kout,))
+    L.fnet_conv2d_fwd(desc, ptr(x), ptr(w), ptr(b), ptr(y), ptr(ws), ws_bytes, None)
+    L.fnet_conv2d_bwd_data(desc, ptr(dy), ptr(w), ptr(dx), 0, ptr(ws), ws_bytes, None)
+    L.fnet_conv2d_bwd_data_act(desc, ptr(dy), ptr(w), ptr(dx), 1, 2, ptr(x), ptr(ws), ws_bytes, None)
+    L.fnet_conv2d_bwd_filter(desc, ptr(x), ptr(dy), ptr(dw), ptr(db), ptr(ws), ws_bytes, None)
+    torch.cuda.synchronize()
+    for whole, t in ((yw, y), (dxw, dx), (dww, dw), (dbw, db), (ws_whole, ws)):
+        assert intact(whole, t.numel())
+    assert bool(torch.isfinite(y).all()) and bool(torch.isfinite(dx).all()) and bool(torch.isfinite(dw).all())
