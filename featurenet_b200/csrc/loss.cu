@@ -184,7 +184,17 @@ __device__ __forceinline__ int group_argmax(float v, int idx) {      // first in
     return idx;
 }
 
-template <int G>
+// R rows per lane group are processed side by side: their shuffle / exp / log chains are independent, so a batch
+// of 128 ten-class rows is ONE dependent chain for the whole (single-CTA) launch instead of two.
+template <int G, int R>
+__device__ __forceinline__ void group_sum_r(float (&v)[R]) {
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1)
+#pragma unroll
+        for (int u = 0; u < R; ++u) v[u] += __shfl_xor_sync(0xffffffffu, v[u], o);
+}
+
+template <int G, int R>
 __global__ void __launch_bounds__(1024) softmax_cce_group_kernel(int batch, int classes, const float *input /* may alias probs_out */,
                                                                   const float *__restrict__ targets, float scale,
                                                                   int from_logits, float *probs_out, float *__restrict__ dlogits,
@@ -195,35 +205,73 @@ __global__ void __launch_bounds__(1024) softmax_cce_group_kernel(int batch, int 
     const int c = threadIdx.x % G, group = threadIdx.x / G, groups = blockDim.x / G;
     double my_loss = 0.0;
     int my_correct = 0;
-    for (int row0 = 0; row0 < batch; row0 += groups) {               // same trip count for every thread (shuffles)
-        const int row = row0 + group;
-        const bool live = row < batch && c < classes;
-        const int64_t at = (int64_t)row * classes + c;
-        const float xin = live ? input[at] : 0.f;
-        const float tv = live ? __ldg(targets + at) : 0.f;
-        float p = xin;
-        if (from_logits) {
-            float mx = live ? xin : -INFINITY;
+    for (int row0 = 0; row0 < batch; row0 += groups * R) {           // same trip count for every thread (shuffles)
+        int row[R];
+        bool live[R];
+        int64_t at[R];
+        float xin[R], tv[R], p[R];
 #pragma unroll
-            for (int o = G / 2; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-            float e = live ? expf(xin - mx) : 0.f;
-            p = e / group_sum<G>(e);
-            if (live) probs_out[at] = p;
+        for (int u = 0; u < R; ++u) {
+            row[u] = row0 + u * groups + group;
+            live[u] = row[u] < batch && c < classes;
+            at[u] = (int64_t)row[u] * classes + c;
+            xin[u] = live[u] ? input[at[u]] : 0.f;
+            tv[u] = live[u] ? __ldg(targets + at[u]) : 0.f;
+            p[u] = xin[u];
         }
-        const float sum = group_sum<G>(p);
-        const int ip = group_argmax<G>(live ? p : -INFINITY, c);
-        const int it = group_argmax<G>(live ? tv : -INFINITY, c);
-        const float q = p / sum;
-        const float cl = fminf(fmaxf(q, kClipEps), 1.f - kClipEps);
-        const float loss = group_sum<G>(live ? -tv * logf(cl) : 0.f);
-        const float g = (live && q >= kClipEps && q <= 1.f - kClipEps) ? -tv / cl : 0.f;
-        const float dot = group_sum<G>(g * q);
+        if (from_logits) {
+            float mx[R], e[R];
+#pragma unroll
+            for (int u = 0; u < R; ++u) mx[u] = live[u] ? xin[u] : -INFINITY;
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1)
+#pragma unroll
+                for (int u = 0; u < R; ++u) mx[u] = fmaxf(mx[u], __shfl_xor_sync(0xffffffffu, mx[u], o));
+            float se[R];
+#pragma unroll
+            for (int u = 0; u < R; ++u) { e[u] = live[u] ? expf(xin[u] - mx[u]) : 0.f; se[u] = e[u]; }
+            group_sum_r<G, R>(se);
+#pragma unroll
+            for (int u = 0; u < R; ++u) {
+                p[u] = e[u] / se[u];
+                if (live[u]) probs_out[at[u]] = p[u];
+            }
+        }
+        float sum[R];
+        int ip[R], it[R];
+#pragma unroll
+        for (int u = 0; u < R; ++u) {
+            sum[u] = p[u];
+            ip[u] = group_argmax<G>(live[u] ? p[u] : -INFINITY, c);
+            it[u] = group_argmax<G>(live[u] ? tv[u] : -INFINITY, c);
+        }
+        group_sum_r<G, R>(sum);
+        float q[R], cl[R], loss[R], g[R], dot[R];
+#pragma unroll
+        for (int u = 0; u < R; ++u) {
+            q[u] = p[u] / sum[u];
+            cl[u] = fminf(fmaxf(q[u], kClipEps), 1.f - kClipEps);
+            loss[u] = live[u] ? -tv[u] * logf(cl[u]) : 0.f;
+            g[u] = (live[u] && q[u] >= kClipEps && q[u] <= 1.f - kClipEps) ? -tv[u] / cl[u] : 0.f;
+            dot[u] = g[u] * q[u];
+        }
+        group_sum_r<G, R>(loss);
+        group_sum_r<G, R>(dot);
         if (dlogits) {
-            const float dp = (g - dot) / sum;                        // dL/dp through the renormalisation
-            const float dot2 = group_sum<G>(live ? dp * p : 0.f);    // softmax backward
-            if (live) dlogits[at] = scale * p * (dp - dot2);
+            float dp[R], dot2[R];
+#pragma unroll
+            for (int u = 0; u < R; ++u) {
+                dp[u] = (g[u] - dot[u]) / sum[u];                    // dL/dp through the renormalisation
+                dot2[u] = live[u] ? dp[u] * p[u] : 0.f;              // softmax backward
+            }
+            group_sum_r<G, R>(dot2);
+#pragma unroll
+            for (int u = 0; u < R; ++u)
+                if (live[u]) dlogits[at[u]] = scale * p[u] * (dp[u] - dot2[u]);
         }
-        if (c == 0 && row < batch) { my_loss += (double)loss; my_correct += ip == it ? 1 : 0; }
+#pragma unroll
+        for (int u = 0; u < R; ++u)
+            if (c == 0 && row[u] < batch) { my_loss += (double)loss[u]; my_correct += ip[u] == it[u] ? 1 : 0; }
     }
     if (c == 0) { group_loss[group] = my_loss; group_correct[group] = my_correct; }
     __syncthreads();
@@ -252,11 +300,11 @@ extern "C" int fnet_softmax_cce(int32_t batch, int32_t classes, const float *inp
         long long want = (long long)batch * lanes;
         int threads = want >= 1024 ? 1024 : (int)((want + 31) / 32) * 32;
         if (lanes == 16)
-            launch_pdl(softmax_cce_group_kernel<16>, dim3(1), dim3(threads), 0, as_stream(stream), batch, classes, input, targets, scale, from_logits,
+            launch_pdl(softmax_cce_group_kernel<16, 2>, dim3(1), dim3(threads), 0, as_stream(stream), batch, classes, input, targets, scale, from_logits,
                                                                                probs_out, dlogits, loss_sum,
                                                                                reinterpret_cast<long long *>(correct));
         else
-            launch_pdl(softmax_cce_group_kernel<32>, dim3(1), dim3(threads), 0, as_stream(stream), batch, classes, input, targets, scale, from_logits,
+            launch_pdl(softmax_cce_group_kernel<32, 2>, dim3(1), dim3(threads), 0, as_stream(stream), batch, classes, input, targets, scale, from_logits,
                                                                                probs_out, dlogits, loss_sum,
                                                                                reinterpret_cast<long long *>(correct));
         return check_launch("fnet_softmax_cce");
