@@ -129,8 +129,11 @@ class ClockSampler(object):
                 "reasons": reasons, "samples": len(self.rows)}
 
 
-def cpu_port_rate(net, dataset, seconds, steps=None, threads=None):
-    """Train images/s of the CPU port (oracle/torch_cpu.py) on batches of the same workload."""
+def cpu_port_rate(net, dataset, seconds, steps=None, threads=None, warm_steps=2, warm_seconds=0.0):
+    """Train images/s of the CPU port (oracle/torch_cpu.py) on batches of the same workload.
+
+    The port is warmed (thread pool, oneDNN primitive cache) for at least `warm_steps` steps and
+    `warm_seconds` seconds before the timed part, so that a short run reports its steady state."""
     import torch
     from oracle.torch_cpu import TorchCpuNet
     from featurenet_b200 import synth
@@ -142,8 +145,10 @@ def cpu_port_rate(net, dataset, seconds, steps=None, threads=None):
     shape, classes = synth.SHAPES[dataset], synth.CLASSES[dataset]
     x = rng.random((BATCH,) + shape).astype(np.float32)
     t = np.eye(classes, dtype=np.float32)[rng.integers(0, classes, BATCH)]
-    for _ in range(2):
+    warmed, w0 = 0, time.perf_counter()
+    while warmed < warm_steps or time.perf_counter() - w0 < warm_seconds:
         port.train_step(x, t)
+        warmed += 1
     done, t0 = 0, time.perf_counter()
     while True:
         port.train_step(x, t)
@@ -161,8 +166,8 @@ def run_reference(args):
     _, net, dataset = build_candidate(args.workload)
     port_steps = args.steps
     t0 = time.perf_counter()
-    rate, done, elapsed, threads = cpu_port_rate(net, dataset, seconds=0, steps=args.warmup + port_steps)
-    rate, done, elapsed, threads = cpu_port_rate(net, dataset, seconds=0, steps=port_steps)
+    rate, done, elapsed, threads = cpu_port_rate(net, dataset, seconds=0, steps=port_steps, warm_steps=max(args.warmup, 3),
+                                                 warm_seconds=3.0)
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / done, "higher_is_better": True,
