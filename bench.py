@@ -140,6 +140,15 @@ def cpu_port_rate(net, dataset, seconds, steps=None, threads=None, warm_steps=2,
     from tests.util import init_weights
     threads = threads or os.cpu_count()
     torch.set_num_threads(threads)
+    try:
+        # keep freed activation buffers in the heap: a fresh process otherwise maps and faults in every temporary of
+        # every step (2x slower than the same port inside a long-running process, which hid this from the first runs)
+        import ctypes
+        libc = ctypes.CDLL("libc.so.6")
+        libc.mallopt(-1, 2 ** 31 - 1)       # M_TRIM_THRESHOLD
+        libc.mallopt(-3, 2 ** 30)           # M_MMAP_THRESHOLD
+    except OSError:
+        pass
     rng = np.random.default_rng(1236)
     port = TorchCpuNet(net.describe(), init_weights(net, rng), threads=threads)
     shape, classes = synth.SHAPES[dataset], synth.CLASSES[dataset]
