@@ -18,12 +18,9 @@ __global__ void __launch_bounds__(256) col2im_kernel(ConvGeom g, const float *__
     pdl_prologue();
     const int taps_c = g.kh * g.kw * g.C;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        int c = (int)(i % g.C);
-        long long pix = i / g.C;
-        int w = (int)(pix % g.W);
-        long long rest = pix / g.W;
-        int h = (int)(rest % g.H);
-        long long b = rest / g.H;
+        int c, w, h;
+        int64_t b;
+        decode4(i, g.H, g.W, g.C, b, h, w, c);
         const float *tb = t + b * g.Ho * g.Wo * taps_c + c;
         float sum = 0.f;
         for (int r = 0; r < g.kh; ++r) {

@@ -111,6 +111,22 @@ __device__ __forceinline__ void decode4(int64_t i, int d1, int d2, int d3, int64
     }
 }
 
+// m -> (b, h, w) of [B][d1][d2] pixels, 32-bit whenever possible (see decode4)
+__device__ __forceinline__ void decode3(long long m, int d1, int d2, long long &b, int &h, int &w) {
+    if (m < 0x7fffffffLL) {
+        unsigned u = (unsigned)m, t = u / (unsigned)d2;
+        w = (int)(u - t * (unsigned)d2);
+        unsigned bb = t / (unsigned)d1;
+        h = (int)(t - bb * (unsigned)d1);
+        b = bb;
+    } else {
+        w = (int)(m % d2);
+        long long t = m / d2;
+        h = (int)(t % d1);
+        b = t / d1;
+    }
+}
+
 __device__ __forceinline__ float act_apply(float z, int act) {
     switch (act) {
         case FNET_ACT_RELU: return fmaxf(z, 0.f);

@@ -305,10 +305,9 @@ __global__ void __launch_bounds__(256) conv_small_fwd_kernel(ConvGeom g, int act
     __syncthreads();
     const long long M = (long long)g.B * g.Ho * g.Wo;
     for (long long m = (long long)blockIdx.x * 256 + threadIdx.x; m < M; m += (long long)gridDim.x * 256) {
-        int wo = (int)(m % g.Wo);
-        long long t = m / g.Wo;
-        int ho = (int)(t % g.Ho);
-        long long b = t / g.Ho;
+        int wo, ho;
+        long long b;
+        decode3(m, g.Ho, g.Wo, b, ho, wo);
         const float *img = x + b * g.H * g.W * g.C;
         float acc[NMAX];
 #pragma unroll
@@ -348,10 +347,9 @@ __global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const
     __syncthreads();
     const long long M = (long long)g.B * g.H * g.W;
     for (long long m = (long long)blockIdx.x * 256 + threadIdx.x; m < M; m += (long long)gridDim.x * 256) {
-        int wi = (int)(m % g.W);
-        long long t = m / g.W;
-        int hi = (int)(t % g.H);
-        long long b = t / g.H;
+        int wi, hi;
+        long long b;
+        decode3(m, g.H, g.W, b, hi, wi);
         const float *img = dz + b * g.Ho * g.Wo * K;
         float acc[NMAX];
 #pragma unroll
@@ -406,10 +404,9 @@ __global__ void __launch_bounds__(256) conv_small_wgrad_kernel(ConvGeom g, int r
         for (int k = 0; k < KT; ++k) acc[i][k] = 0.f;
     const long long M = (long long)g.B * g.Ho * g.Wo;
     for (long long m = (long long)blockIdx.x * 256 + threadIdx.x; m < M; m += (long long)gridDim.x * 256) {
-        int wo = (int)(m % g.Wo);
-        long long t = m / g.Wo;
-        int ho = (int)(t % g.Ho);
-        long long b = t / g.Ho;
+        int wo, ho;
+        long long b;
+        decode3(m, g.Ho, g.Wo, b, ho, wo);
         const float *img = x + b * g.H * g.W * C;
         float gz[KT];
 #pragma unroll

@@ -7,6 +7,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# Engines draw their weight-init / dropout seed from the OS unless told otherwise; the tests pin it so that a run
+# is reproducible to the bit (a different dropout mask per run made one borderline tolerance fail once in ~20 runs).
+os.environ.setdefault("FNET_SEED", "20261106")
+
 import featurenet_b200  # noqa: E402
 
 featurenet_b200.install_compat()
