@@ -141,6 +141,7 @@ struct FwdProblem {
     __device__ bool vec4_ok() const { return (g.C & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }
     __device__ bool a_rows_vec4_ok() const { return false; }
     __device__ bool b_rows_vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0; }
+    __device__ bool b_k_vec4_ok() const { return false; }
     __device__ void make_row(int m, int M, Row &r) const { decode_out_pixel(g, m, M, r); }
     __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.C, kend, c); }
     __device__ void next_col(int k_new, int step, int kend, Col &c) const { step_tap(g, k_new, step, g.C, kend, c); }
@@ -201,6 +202,8 @@ struct DgradProblem {
     __device__ bool vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(dz) & 15) == 0; }
     __device__ bool a_rows_vec4_ok() const { return false; }
     __device__ bool b_rows_vec4_ok() const { return false; }
+    // w[tap][c][ko]: four consecutive ko of one (tap, c) row are 16 contiguous, aligned bytes when K % 4 == 0
+    __device__ bool b_k_vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0; }
     __device__ void make_row(int m, int M, Row &r) const { decode_in_pixel(g, m, M, r); }
     __device__ void make_col(int k, int kend, Col &c) const { decode_tap(g, k, g.K, kend, c); }
     __device__ void next_col(int k_new, int step, int kend, Col &c) const { step_tap(g, k_new, step, g.K, kend, c); }
@@ -280,6 +283,7 @@ struct WgradProblem {
     // four consecutive rows = four consecutive channels of one tap; four consecutive columns of dz
     __device__ bool a_rows_vec4_ok() const { return (g.C & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }
     __device__ bool b_rows_vec4_ok() const { return (g.K & 3) == 0 && (reinterpret_cast<uintptr_t>(dz) & 15) == 0; }
+    __device__ bool b_k_vec4_ok() const { return false; }
     __device__ void make_row(int k, int M, Row &r) const {
         decode_tap(g, k, g.C, taps_c, r);
         if (k == taps_c && k < M) r.valid = 2;

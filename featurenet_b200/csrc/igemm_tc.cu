@@ -176,7 +176,9 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
 #pragma unroll
     for (int j = 0; j < ACOLS; ++j) p.make_col(kbeg + a_koff + 8 * j, kend, acol[j]);
     const int b_kl = warp * B_KPW + lane / B_CH, b_chunk = lane % B_CH;     // MN-major, 16-byte copies
-    typename P::BCursor bcur = P::kBContigK ? p.b_begin(kbeg + lane, n0 + warp)
+    const bool b_k4 = P::kBContigK && p.b_k_vec4_ok();     // K-major B, 16 bytes = 4 consecutive k of one row
+    typename P::BCursor bcur = P::kBContigK ? (b_k4 ? p.b_begin(kbeg + 4 * (lane & 7), n0 + warp * 4 + (lane >> 3))
+                                                    : p.b_begin(kbeg + lane, n0 + warp))
                                : (b_rows4 ? p.b_begin(kbeg + b_kl, n0 + 4 * b_chunk) : p.b_begin(kbeg + warp, n0 + lane));
     const long long b_step_n = p.b_stride_n(), b_step_k = p.b_stride_k();
     int k_next = kbeg;
@@ -239,7 +241,15 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
             }
         }
         const float *bsrc = p.b_ptr(bcur);
-        if (P::kBContigK) {
+        if (b_k4) {
+            const bool k_ok = k0 + 4 * (lane & 7) < kend;
+#pragma unroll
+            for (int i = 0; i < BN / 32; ++i) {
+                int nn = warp * 4 + (lane >> 3) + 32 * i;
+                bool ok = k_ok && n0 + nn < N;
+                cp_async16(sb + tile_offset(nn, 4 * (lane & 7), layout), ok ? bsrc + b_step_n * (32 * i) : p.any_ptr(), ok ? 16u : 0u);
+            }
+        } else if (P::kBContigK) {
             const bool k_ok = k0 + lane < kend;
 #pragma unroll
             for (int i = 0; i < B_PER; ++i) {
