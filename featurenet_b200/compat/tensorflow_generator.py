@@ -137,7 +137,9 @@ class TensorflowGenerator(object):
         """(empirical robustness, clean accuracy, adversarial accuracy) -- tensorflow_generator.py:151-173."""
         from featurenet_b200 import robustness
         attack_params = {"norm": norm}
-        if attack_name == "pgd":
+        if attack_name == "cw":
+            attack_params["targeted"] = False
+        elif attack_name == "pgd":
             attack_params["eps_step"] = 0.1
             attack_params["eps"] = 1.
         if robustness_set_size == 0:
@@ -150,19 +152,30 @@ class TensorflowGenerator(object):
     @staticmethod
     def eval_robustness(model, scores=[], robustness_set_size=0):
         """The second fitness of the evolution drivers (tensorflow_generator.py:175-218).  The gradient attacks
-        (fgsm, pgd) run on the engine; Carlini-Wagner and CLEVER are not built and keep their score of 0."""
+        (fgsm, pgd, cw) and CLEVER all run on the engine."""
         keras_model = model.model
         if not keras_model or model.accuracy < 0.5:
             return
         begin_robustness = time.time()
         score_metrics = model.robustness_scores if not scores else scores
         try:
+            from featurenet_b200 import robustness
             norm = 2
-            for name in ("clever", "cw"):
-                if name in score_metrics:
-                    print("robustness metric {} is not built in this engine (SURVEY.md 8f.1); its score stays 0".format(name))
+            r_l1, r_l2, r_li = 40, 2, 0.1
+            nb_batches = 10
+            batch_size = 5
+            radius = r_l1 if norm == 1 else (r_l2 if norm == 2 else r_li)
+            if "clever" in score_metrics:
+                if robustness_set_size == 0:
+                    x_set = TensorflowGenerator.X_robustness
+                else:
+                    x_set = TensorflowGenerator.X_test[0:robustness_set_size]
+                model.clever_score = robustness.clever_score(keras_model, x_set, nb_batches, batch_size, radius, norm=norm,
+                                                             pool_factor=3)
             if "pgd" in score_metrics:
                 model.pgd_score = TensorflowGenerator.eval_attack_robustness(keras_model, "pgd", norm, robustness_set_size)
+            if "cw" in score_metrics:
+                model.cw_score = TensorflowGenerator.eval_attack_robustness(keras_model, "cw", norm, robustness_set_size)
             if "fgsm" in score_metrics:
                 model.fgsm_score = TensorflowGenerator.eval_attack_robustness(keras_model, "fgsm", norm, robustness_set_size)
         except Exception as e:

@@ -605,6 +605,11 @@ class Engine(object):
         if kind == "grad_input":        # act[0] / yb are filled by the caller; inference graph, gradient down to the input
             return (self._forward_program(batch, False, save_for_backward=True) + [self._loss_op(batch, True)] +
                     self._backward_program(batch, training=False, input_grad=True))
+        if kind == "logits":            # act[0] is filled by the caller; the head stops before its softmax
+            return self._forward_program(batch, False)
+        if kind == "grad_logits":       # as above, but the caller also fills the head's dz: no loss in between
+            return (self._forward_program(batch, False, save_for_backward=True) +
+                    self._backward_program(batch, training=False, input_grad=True))
         training = kind.startswith("train")
         state = self.state if training else self.state_eval
         st = C.c_void_p(state.data_ptr())
@@ -933,14 +938,7 @@ class Engine(object):
         robustness fitness (tensorflow_generator.py:151-173).  x, y: host arrays or device tensors; returns a
         device tensor of x's shape that stays valid until the next call."""
         b = int(x.shape[0])
-        self._ensure_capacity(max(b, self.capacity))
-        if 0 not in self.gact or self.gact[0].shape[0] < self.capacity:
-            with torch.cuda.device(self.device):
-                self.gact[0] = torch.empty((self.capacity,) + tuple(self.shape[0]), dtype=torch.float32, device=self.device)
-            for key in [k for k in self.programs if k[0] == "grad_input"]:
-                if key in self.graphs:
-                    self.lib.fnet_graph_destroy(self.graphs.pop(key))
-                self.programs.pop(key)
+        self._prepare_input_gradient(b)
         xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
         yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
         with torch.cuda.stream(self.stream):
@@ -949,6 +947,52 @@ class Engine(object):
         self._step("grad_input", b)
         self.stream.synchronize()          # host sources may be temporaries
         return self.gact[0][:b]
+
+    def logits(self, x):
+        """The head's pre-softmax outputs in inference mode (ART's ``predict(x, logits=True)``), as a host array."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        n = x.shape[0]
+        eb = self.eval_batch_size(n)
+        self._ensure_capacity(max(eb, self.capacity))
+        out = np.empty((n, self.n_out), np.float32)
+        last = self._resolve(len(self.nodes) - 1, False)
+        for lo in range(0, n, eb):
+            b = min(eb, n - lo)
+            with torch.cuda.stream(self.stream):
+                self.act[0][:b].copy_(torch.from_numpy(x[lo: lo + b]), non_blocking=True)
+            self._step("logits", b)
+            self.stream.synchronize()
+            out[lo: lo + b] = self.act[last][:b].cpu().numpy()
+        return out
+
+    def _prepare_input_gradient(self, b):
+        """Buffers for a gradient that reaches the network input (training never needs dL/dx)."""
+        self._ensure_capacity(max(b, self.capacity))
+        if 0 not in self.gact or self.gact[0].shape[0] < self.capacity:
+            with torch.cuda.device(self.device):
+                self.gact[0] = torch.empty((self.capacity,) + tuple(self.shape[0]), dtype=torch.float32, device=self.device)
+            for key in [k for k in self.programs if k[0] in ("grad_input", "grad_logits")]:
+                if key in self.graphs:
+                    self.lib.fnet_graph_destroy(self.graphs.pop(key))
+                self.programs.pop(key)
+
+    def logit_gradient(self, x, head_dz):
+        """Vector-Jacobian product of the head's LOGITS Z in inference mode: row b of the result is
+        sum_j head_dz[b, j] * dZ_j/dx[b].  A one-hot head_dz gives one row of ART's
+        ``KerasClassifier.class_gradient(x, logits=True)``; CLEVER (model/metrics.py:309-314) wants
+        grads[:, pred] - grads[:, target], i.e. head_dz = e_pred - e_target, in a single backward pass.
+        Returns (gradient, logits): device tensors valid until the next call."""
+        b = int(x.shape[0])
+        self._prepare_input_gradient(b)
+        last = self._resolve(len(self.nodes) - 1, True)
+        xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+        zt = head_dz if isinstance(head_dz, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(head_dz, dtype=np.float32))
+        with torch.cuda.stream(self.stream):
+            self.act[0][:b].copy_(xt, non_blocking=True)
+            self.gact[last][:b].copy_(zt, non_blocking=True)
+        self._step("grad_logits", b)
+        self.stream.synchronize()
+        return self.gact[0][:b], self.act[self._resolve(len(self.nodes) - 1, False)][:b]
 
     def fit(self, x, y, batch_size=32, epochs=1, validation_data=None, shuffle=True, callbacks=(), verbose=0,
             permutations=None, initial_epoch=0, augment=None, **_):

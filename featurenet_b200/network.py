@@ -121,6 +121,14 @@ class Network(object):
         """dL/dx in inference mode (device tensor): what the robustness attacks differentiate."""
         return self._need_engine().input_gradient(x, y)
 
+    def logits(self, x):
+        """Pre-softmax outputs of the head in inference mode (host array)."""
+        return self._need_engine().logits(x)
+
+    def logit_gradient(self, x, head_dz):
+        """(sum_j head_dz[:, j] * dlogit_j/dx, logits) in inference mode: class gradients for CLEVER."""
+        return self._need_engine().logit_gradient(x, head_dz)
+
     def get_weights(self):
         return self._need_engine().get_weights()
 

@@ -71,7 +71,10 @@ class OracleNet(object):
                 y = ops.act_fwd(z, cfg["activation"])
                 c = mid
             elif cls == "Dense":
-                y = ops.act_fwd(ops.dense_fwd(ins[0], W[0], W[1]), cfg["activation"])
+                z = ops.dense_fwd(ins[0], W[0], W[1])
+                y = ops.act_fwd(z, cfg["activation"])
+                if i == len(self.rows) - 1:
+                    self.logits = z                 # what ART's predict(logits=True) / class_gradient(logits=True) read
             elif cls == "MaxPooling2D":
                 y, c = ops.maxpool_fwd(ins[0], cfg["pool"], cfg["strides"], cfg["padding"])
             elif cls == "AveragePooling2D":
@@ -118,12 +121,24 @@ class OracleNet(object):
         self.backward(targets, training=False)
         return self.douts[0]
 
-    def backward(self, targets, training=True):
-        """Gradients of mean-over-batch CCE for the last forward. Returns per-layer weight grads; self.douts[0] is dL/dx."""
+    def logit_gradient(self, x, head_dz):
+        """sum_j head_dz[b, j] * dZ_j/dx[b] for the LOGITS Z of the head, in inference mode: one row of ART's
+        ``class_gradient(x, logits=True)`` per one-hot head_dz, any linear combination of rows otherwise
+        (model/metrics.py:309-314 uses grads[:, pred] - grads[:, target])."""
+        self.forward(x, training=False)
+        self.backward(None, training=False, head_dz=np.asarray(head_dz, F64))
+        return self.douts[0]
+
+    def backward(self, targets, training=True, head_dz=None):
+        """Gradients of mean-over-batch CCE for the last forward. Returns per-layer weight grads; self.douts[0] is dL/dx.
+        head_dz: start from this gradient with respect to the head's logits instead of from the loss."""
         rows, outs = self.rows, self.outs
         B = outs[0].shape[0]
         douts = [None] * len(rows)
-        douts[-1] = ops.cce_bwd_probs(outs[-1], np.asarray(targets, F64), 1.0 / B)
+        if head_dz is None:
+            douts[-1] = ops.cce_bwd_probs(outs[-1], np.asarray(targets, F64), 1.0 / B)
+        else:
+            douts[-1] = head_dz
         grads = [[np.zeros_like(w) for w in ws] for ws in self.weights]
 
         def give(j, g):
@@ -157,7 +172,7 @@ class OracleNet(object):
                 dx, grads[i][0], _ = ops.dwconv2d_bwd(x, W[0], dmid, cfg["strides"], cfg["padding"])
                 give(src[0], dx)
             elif cls == "Dense":
-                dz = ops.act_bwd(y, dy, cfg["activation"])
+                dz = dy if (head_dz is not None and i == len(rows) - 1) else ops.act_bwd(y, dy, cfg["activation"])
                 dx, grads[i][0], grads[i][1] = ops.dense_bwd(x, W[0], dz)
                 give(src[0], dx)
             elif cls == "MaxPooling2D":

@@ -103,3 +103,92 @@ def test_eval_robustness_through_the_reference_named_runner():
     assert model.robustness_score == model.fgsm_score[0]
     assert model.cw_score == 0 and model.clever_score == 0
     assert model.fgsm_score[1] == model.pgd_score[1]            # the same clean accuracy on the same rows
+
+
+@pytest.mark.parametrize("name", sorted(tiny_graphs()))
+def test_logit_gradient_matches_the_oracle(name):
+    net, eng, oracle = setup(name)
+    rng = np.random.default_rng(13)
+    x = rng.random((6,) + tuple(net.input_shape[1:])).astype(np.float32)
+    classes = net.output_shape[-1]
+    head = rng.standard_normal((6, classes)).astype(np.float32)
+    want = oracle.logit_gradient(x.astype(np.float64), head.astype(np.float64))
+    grad, logits = eng.logit_gradient(x, head)
+    got, z = grad.cpu().numpy(), logits.cpu().numpy()
+    assert relerr(got, want) <= 1e-4
+    assert relerr(z, oracle.logits) <= 1e-4
+    # linear in head_dz: the CLEVER shortcut (one pass with e_pred - e_target) equals the difference of two rows
+    e = np.eye(classes, dtype=np.float32)
+    g0 = eng.logit_gradient(x, np.tile(e[0], (6, 1)))[0].cpu().numpy()
+    g1 = eng.logit_gradient(x, np.tile(e[1], (6, 1)))[0].cpu().numpy()
+    gd = eng.logit_gradient(x, np.tile(e[0] - e[1], (6, 1)))[0].cpu().numpy()
+    assert np.abs(gd - (g0 - g1)).max() <= 1e-5 * max(1.0, np.abs(g0).max())
+    # the loss-gradient program and training are undisturbed
+    t = e[rng.integers(0, classes, 6)]
+    assert relerr(eng.input_gradient(x, t).cpu().numpy(), oracle.input_gradient(x.astype(np.float64), t.astype(np.float64))) <= 1e-4
+    assert np.isfinite(net.train_on_batch(x, t)[0])
+
+
+def test_clever_matches_the_oracle():
+    """Same numpy seed -> same pools and picks on both sides; the per-batch maxima of the gradient norm agree to
+    fp32 accuracy and the score (a Nelder-Mead Weibull fit on those maxima) to 1e-3."""
+    from featurenet_b200 import robustness
+    name = "pools_and_bn" if "pools_and_bn" in tiny_graphs() else sorted(tiny_graphs())[0]
+    net, eng, oracle = setup(name)
+    rng = np.random.default_rng(19)
+    xs = rng.random((3,) + tuple(net.input_shape[1:])).astype(np.float32)
+    for x in xs:
+        np.random.seed(77)
+        want, want_maxima = attacks.clever_u(oracle, x, nb_batches=6, batch_size=4, radius=2.0, pool_factor=3)
+        np.random.seed(77)
+        got, maxima = robustness.clever_u(net, x, 6, 4, 2.0, norm=2, pool_factor=3, return_maxima=True)
+        assert relerr(maxima, want_maxima) <= 1e-4
+        assert abs(got - want) <= 1e-3 * max(1.0, abs(want))
+        assert 0.0 <= got <= 2.0
+    np.random.seed(5)
+    avg = robustness.clever_score(net, xs, nb_batches=3, batch_size=3, radius=2, pool_factor=3)
+    assert 0.0 <= avg <= 2.0
+    with pytest.raises(NotImplementedError):
+        robustness.clever_u(net, xs[0], 3, 3, 0.1, norm=np.inf)
+
+
+def test_logits_program_matches_predict_and_the_oracle():
+    name = "pools_and_bn" if "pools_and_bn" in tiny_graphs() else sorted(tiny_graphs())[0]
+    net, eng, oracle = setup(name)
+    x = np.random.default_rng(23).random((7,) + tuple(net.input_shape[1:])).astype(np.float32)
+    z = net.logits(x)
+    oracle.forward(x.astype(np.float64))
+    assert relerr(z, oracle.logits) <= 1e-4
+    e = np.exp(z - z.max(axis=1, keepdims=True))
+    assert np.abs(e / e.sum(axis=1, keepdims=True) - net.predict(x)).max() <= 1e-6
+
+
+@pytest.mark.parametrize("strong", [False, True])
+def test_carlini_l2_matches_the_oracle(strong, monkeypatch):
+    from featurenet_b200 import robustness
+    name = "pools_and_bn" if "pools_and_bn" in tiny_graphs() else sorted(tiny_graphs())[0]
+    net, eng, oracle = setup(name)
+    x = np.random.default_rng(8).random((5,) + tuple(net.input_shape[1:])).astype(np.float32)
+    if strong:      # the data's own range and a setting that succeeds, so that every branch of the line search runs
+        monkeypatch.setattr(robustness, "CLIP_VALUES", (0.0, 1.0))
+        params = {"targeted": False, "norm": 2, "initial_const": 10.0, "learning_rate": 0.1}
+        want = attacks.carlini_l2(oracle, x, clip=(0.0, 1.0), initial_const=10.0, learning_rate=0.1)
+    else:           # exactly what tensorflow_generator.py:151-173 asks for
+        params = {"targeted": False, "norm": 2}
+        want = attacks.carlini_l2(oracle, x)
+    adv = robustness.craft(net, x, "cw", params)
+    assert adv.dtype == np.float32 and adv.shape == x.shape
+    # fp32 logits against float64 ones can flip a comparison of the line search on a rare row; the rows that took the
+    # same path agree tightly, and both sides fool the model on the same rows
+    close = np.abs(adv - want).reshape(5, -1).max(axis=1) <= 1e-3
+    assert close.sum() >= 4, np.abs(adv - want).reshape(5, -1).max(axis=1)
+    labels = np.argmax(net.predict(x), axis=1)
+    fooled = np.argmax(net.predict(adv), axis=1) != labels
+    fooled_want = np.argmax(oracle.forward(want)[-1], axis=1) != labels
+    assert np.array_equal(fooled[close], fooled_want[close])
+    if strong:
+        assert fooled.any()
+        value, _ = robustness.empirical_robustness(net, x, "cw", params)
+        assert value > 0.0
+    else:
+        assert not fooled.any() and robustness.empirical_robustness(net, x, "cw", params)[0] == 0.0
