@@ -96,13 +96,18 @@ def test_eval_robustness_through_the_reference_named_runner():
     out = io.StringIO()
     with contextlib.redirect_stdout(out):
         TensorflowGenerator.eval_robustness(model, ["fgsm", "pgd", "cw"], robustness_set_size=48)
-    assert "cw is not built" in out.getvalue()
-    for score in (model.fgsm_score, model.pgd_score):
+    assert "model robustness (clever, pgd, cw, fgsm)" in out.getvalue()
+    for score in (model.fgsm_score, model.pgd_score, model.cw_score):
         # 0.0 = no row changed its prediction within the attack's budget
         assert len(score) == 3 and score[0] >= 0.0 and 0.0 <= score[1] <= 1.0 and 0.0 <= score[2] <= 1.0
     assert model.robustness_score == model.fgsm_score[0]
-    assert model.cw_score == 0 and model.clever_score == 0
-    assert model.fgsm_score[1] == model.pgd_score[1]            # the same clean accuracy on the same rows
+    assert model.clever_score == 0                              # not requested
+    assert model.fgsm_score[1] == model.pgd_score[1] == model.cw_score[1]      # the same clean accuracy on the same rows
+    np.random.seed(3)
+    with contextlib.redirect_stdout(out):
+        TensorflowGenerator.eval_robustness(model, ["clever"], robustness_set_size=4)
+    assert 0.0 < model.clever_score <= 2.0                      # radius r_l2 = 2 caps every per-image score
+    assert model.robustness_score == model.clever_score
 
 
 @pytest.mark.parametrize("name", sorted(tiny_graphs()))
