@@ -212,6 +212,32 @@ int fnet_graph_step_fed(void *graph_exec, void *x_dev, const void *x_host, size_
     return FNET_OK;
 }
 
+int fnet_graph_step_streamed(void *graph_exec, void *x_slot, const void *x_host, void *x_stage, size_t x_bytes,
+                             void *y_slot, const void *y_host, void *y_stage, size_t y_bytes, const void *result_dev,
+                             void *result_host, void *result_prev, size_t result_bytes, void *copy_stream,
+                             void *compute_stream, void *slot_event, void *copied_event) {
+    FNET_REQUIRE(graph_exec != nullptr, "fnet_graph_step_streamed: null graph");
+    FNET_REQUIRE(x_slot && x_host && y_slot && y_host, "fnet_graph_step_streamed: null batch buffer");
+    FNET_REQUIRE(slot_event && copied_event, "fnet_graph_step_streamed: null event");
+    FNET_REQUIRE(result_bytes == 0 || (result_dev != nullptr && result_host != nullptr),
+                 "fnet_graph_step_streamed: null result buffer");
+    FNET_REQUIRE(copy_stream != compute_stream, "fnet_graph_step_streamed: the copies need a stream of their own");
+    cudaStream_t copy = as_stream(copy_stream), compute = as_stream(compute_stream);
+    cudaEvent_t slot = reinterpret_cast<cudaEvent_t>(slot_event), copied = reinterpret_cast<cudaEvent_t>(copied_event);
+    FNET_CUDA(cudaEventSynchronize(slot));                    // the slot's previous step is over: everything it used is free
+    if (result_prev && result_bytes) memcpy(result_prev, result_host, result_bytes);
+    if (x_stage) { memcpy(x_stage, x_host, x_bytes); x_host = x_stage; }
+    if (y_stage) { memcpy(y_stage, y_host, y_bytes); y_host = y_stage; }
+    FNET_CUDA(cudaMemcpyAsync(x_slot, x_host, x_bytes, cudaMemcpyHostToDevice, copy));
+    FNET_CUDA(cudaMemcpyAsync(y_slot, y_host, y_bytes, cudaMemcpyHostToDevice, copy));
+    FNET_CUDA(cudaEventRecord(copied, copy));
+    FNET_CUDA(cudaStreamWaitEvent(compute, copied, 0));
+    FNET_CUDA(cudaGraphLaunch(reinterpret_cast<cudaGraphExec_t>(graph_exec), compute));
+    if (result_bytes) FNET_CUDA(cudaMemcpyAsync(result_host, result_dev, result_bytes, cudaMemcpyDeviceToHost, compute));
+    FNET_CUDA(cudaEventRecord(slot, compute));
+    return FNET_OK;
+}
+
 int fnet_graph_destroy(void *graph_exec) {
     if (graph_exec) FNET_CUDA(cudaGraphExecDestroy(reinterpret_cast<cudaGraphExec_t>(graph_exec)));
     return FNET_OK;

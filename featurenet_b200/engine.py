@@ -619,9 +619,20 @@ class Engine(object):
             opt = self.net.optimizer
             b1, b2 = (opt.beta_1, opt.beta_2) if opt.kind == "adam" else (0.9, 0.999)
         fused_gather = kind in ("train", "eval")         # inputs + targets (+ lr_t) in one launch
-        if training and not fused_gather:
+        ring_slot = int(kind[len("train_ring"):]) if kind.startswith("train_ring") else None
+        if ring_slot is not None:
+            # pipelined host feed: the batch was uploaded into slot `ring_slot` of the ring while the previous step
+            # ran; the same launch as the resident path moves it into place (identity order, cursor stays 0)
+            xs, ys = self.ring["x"][ring_slot], self.ring["y"][ring_slot]
+            ops.append(("gather_batch", L.fnet_gather_batch,
+                        (batch, _prod(self.shape[0]), self.n_out, C.c_void_p(self.ring["order"].data_ptr()), st,
+                         C.c_void_p(xs.data_ptr()), C.c_void_p(ys.data_ptr()), C.c_void_p(self.act[0].data_ptr()),
+                         C.c_void_p(self.yb.data_ptr()), 1, b1, b2, sp)))
+        elif training and not fused_gather:
             ops.append(("step_begin", L.fnet_step_begin, (st, b1, b2, sp)))
-        if fused_gather:
+        if ring_slot is not None:
+            pass
+        elif fused_gather:
             xdev, ydev, perm = self.data[kind]
             ops.append(("gather_batch", L.fnet_gather_batch,
                         (batch, _prod(self.shape[0]), self.n_out, C.c_void_p(perm.data_ptr()), st,
@@ -646,7 +657,7 @@ class Engine(object):
         ops.append(self._loss_op(batch, training))
         if training:
             ops += self._backward_program(batch)
-            ops.append(self._optimizer_op(advance=batch))       # the update also closes the step
+            ops.append(self._optimizer_op(advance=0 if ring_slot is not None else batch))   # the update also closes the step
         else:
             ops.append(("step_end", L.fnet_step_end, (st, batch, sp)))
         return ops
@@ -781,6 +792,14 @@ class Engine(object):
 
     def _step(self, kind, batch):
         """Enqueue one step (captured CUDA graph after the first, eager run)."""
+        ops = self._program(kind, batch)
+        if not self.use_graphs or self.timeline is not None:
+            self._run_ops(ops)
+            return
+        self.lib.fnet_graph_launch(self._graph(kind, batch), self.sp)
+
+    def _program(self, kind, batch):
+        """The launch list of one step of `kind` at this batch size (built once)."""
         key = (kind, batch)
         ops = self.programs.get(key)
         if ops is None:
@@ -793,13 +812,15 @@ class Engine(object):
             ops = self.programs[key] = self._build_program(kind, batch)
             self.launches_per_step = getattr(self, "launches_per_step", {})
             self.launches_per_step[key] = sum(1 for op in ops if op[1] is not None)
-        if not self.use_graphs or self.timeline is not None:
-            self._run_ops(ops)
-            return
-        graph = self.graphs.get(key)
+        return ops
+
+    def _graph(self, kind, batch):
+        """The captured step (captured on first use; nothing runs during the capture)."""
+        ops = self._program(kind, batch)
+        graph = self.graphs.get((kind, batch))
         if graph is None:
-            graph = self.graphs[key] = self._capture(ops)
-        self.lib.fnet_graph_launch(graph, self.sp)
+            graph = self.graphs[(kind, batch)] = self._capture(ops)
+        return graph
 
     def _capture(self, ops):
         """Record a launch list into a CUDA graph (nothing executes until the graph is launched)."""
@@ -1076,17 +1097,136 @@ class Engine(object):
         return result
 
     def fit_generator(self, generator, steps_per_epoch=None, epochs=1, validation_data=None, callbacks=(), verbose=0, **kw):
-        """The augmentation path of helpers.py:115-167; the generator must expose the arrays it flows from."""
-        if not hasattr(generator, "x") or not hasattr(generator, "y"):
-            raise NotImplementedError("fit_generator needs a featurenet_b200 data generator (device-side augmentation)")
+        """keras Model.fit_generator (helpers.py:163).  A featurenet_b200 generator (it exposes the arrays it flows
+        from) takes the augmentation path of helpers.py:115-167 with the dataset resident on the device; any other
+        iterator of (x, y) host batches is streamed through the pipelined feed (_fit_stream)."""
         kw.pop("workers", None)
+        if not hasattr(generator, "x") or not hasattr(generator, "y"):
+            for name in ("max_queue_size", "use_multiprocessing", "shuffle", "class_weight"):
+                kw.pop(name, None)
+            return self._fit_stream(generator, steps_per_epoch, epochs, validation_data, callbacks, verbose, **kw)
         return self.fit(generator.x, generator.y, batch_size=generator.batch_size, epochs=epochs,
                         validation_data=validation_data, callbacks=callbacks, verbose=verbose, augment=generator, **kw)
+
+    # ------------------------------------------------------------------ pipelined host feed
+    RING_SLOTS = 2
+
+    def _ring_setup(self, batch):
+        """Two slots of (device batch, pinned staging batch, pinned result, two events) and a copy stream."""
+        self._ensure_capacity(max(batch, self.capacity))
+        ring = getattr(self, "ring", None)
+        if ring is not None and ring["capacity"] >= self.capacity:
+            return ring
+        self.stream.synchronize()
+        for key in [k for k in self.programs if k[0].startswith("train_ring")]:
+            if key in self.graphs:
+                self.lib.fnet_graph_destroy(self.graphs.pop(key))
+            self.programs.pop(key)
+        cap, n = self.capacity, self.RING_SLOTS
+        with torch.cuda.device(self.device):
+            ring = {"capacity": cap,
+                    "x": torch.empty((n, cap) + tuple(self.shape[0]), dtype=torch.float32, device=self.device),
+                    "y": torch.empty((n, cap, self.n_out), dtype=torch.float32, device=self.device),
+                    "order": torch.arange(cap, dtype=torch.int32, device=self.device),
+                    "x_stage": torch.empty((n, cap) + tuple(self.shape[0]), dtype=torch.float32).pin_memory(),
+                    "y_stage": torch.empty((n, cap, self.n_out), dtype=torch.float32).pin_memory(),
+                    "result": torch.zeros((n, 2), dtype=torch.int64).pin_memory(),
+                    "prev": np.zeros(2, np.int64),
+                    "copy_stream": torch.cuda.Stream(device=self.device),
+                    "slot_event": [torch.cuda.Event() for _ in range(n)],
+                    "copied_event": [torch.cuda.Event() for _ in range(n)]}
+            for ev in ring["slot_event"] + ring["copied_event"]:
+                ev.record(self.stream)                     # materialises the cudaEvent_t handle
+        self.stream.synchronize()
+        self.ring = ring
+        return ring
+
+    def _stream_step(self, step, x, y):
+        """Enqueue one optimisation step on a host batch without waiting for it.  Returns the running
+        (loss_sum, correct) as they stood after the step that used this slot before (RING_SLOTS steps ago)."""
+        b = int(x.shape[0])
+        ring = self._ring_setup(b)
+        slot = step % self.RING_SLOTS
+        xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+        yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
+        if xt.dtype != torch.float32 or yt.dtype != torch.float32 or not xt.is_contiguous() or not yt.is_contiguous():
+            xt, yt = xt.float().contiguous(), yt.float().contiguous()
+        if tuple(xt.shape[1:]) != tuple(self.shape[0]) or tuple(yt.shape) != (b, self.n_out):
+            raise ValueError("batch of shape %s / %s does not fit the model" % (tuple(xt.shape), tuple(yt.shape)))
+        pinned = xt.is_pinned() and yt.is_pinned()
+        graph = self._graph("train_ring%d" % slot, b)      # one captured step per (slot, batch size)
+        self._sync_lr()
+        keep = None if pinned else (ring["x_stage"][slot], ring["y_stage"][slot])
+        self.lib.fnet_graph_step_streamed(
+            graph, ring["x"][slot].data_ptr(), xt.data_ptr(), keep[0].data_ptr() if keep else None, xt.numel() * 4,
+            ring["y"][slot].data_ptr(), yt.data_ptr(), keep[1].data_ptr() if keep else None, yt.numel() * 4,
+            self.metrics.data_ptr(), ring["result"][slot].data_ptr(), ring["prev"].ctypes.data, 16,
+            ring["copy_stream"].cuda_stream, self.stream.cuda_stream,
+            ring["slot_event"][slot].cuda_event, ring["copied_event"][slot].cuda_event)
+        if pinned:
+            ring.setdefault("alive", {})[slot] = (xt, yt)   # the upload reads the caller's buffer until the slot's next turn
+        return float(ring["prev"].view(np.float64)[0]), int(ring["prev"][1])
+
+    def _fit_stream(self, generator, steps_per_epoch, epochs, validation_data, callbacks, verbose, initial_epoch=0, **_):
+        """fit_generator for host batches.  The upload of batch i+1 (copy stream) overlaps the kernels of batch i
+        (compute stream); the 16-byte result of every step comes back asynchronously and is handed to
+        on_batch_end RING_SLOTS steps late; epoch metrics are the sample-weighted means keras reports."""
+        from .callbacks import History, Callback
+        if self.net.optimizer is None:
+            raise RuntimeError("compile() the model first")
+        if steps_per_epoch is None:
+            if not hasattr(generator, "__len__"):
+                raise ValueError("steps_per_epoch is needed for a generator without a length")
+            steps_per_epoch = len(generator)
+        batches = iter(generator)
+        val = self._check_xy(validation_data[0], validation_data[1]) if validation_data is not None else None
+        history = History()
+        cbs = [history] + list(callbacks)
+        per_batch = [cb for cb in cbs if getattr(type(cb), "on_batch_end", None) not in (None, Callback.on_batch_end)]
+        for cb in cbs:
+            cb.set_model(self.net)
+            cb.set_params({"epochs": epochs, "steps": steps_per_epoch})
+        self.net.stop_training = False
+        for cb in cbs:
+            cb.on_train_begin({})
+        t_start = time.time()
+        step_no = getattr(self, "_stream_steps", 0)
+        for epoch in range(initial_epoch, epochs):
+            for cb in cbs:
+                cb.on_epoch_begin(epoch, {})
+            self._zero_metrics(self.state)                 # stream-ordered behind the previous epoch's steps; cursor = 0
+            seen = 0
+            for step in range(steps_per_epoch):
+                item = next(batches)
+                x, y = item[0], item[1]
+                b = int(x.shape[0])
+                loss_sum, correct = self._stream_step(step_no, x, y)
+                step_no += 1
+                seen += b
+                for cb in per_batch:
+                    cb.on_batch_end(step, {"batch": step, "size": b, "loss_sum_lagged": loss_sum, "correct_lagged": correct})
+            self._stream_steps = step_no
+            loss, acc = self._read_metrics(max(seen, 1))
+            logs = {"loss": loss, "acc": acc}
+            if val is not None:
+                logs["val_loss"], logs["val_acc"] = self.evaluate(val[0], val[1])
+            for cb in cbs:
+                cb.on_epoch_end(epoch, logs)
+            if verbose:
+                print("Epoch %d/%d - %.1fs - %s" % (epoch + 1, epochs, time.time() - t_start,
+                                                    " - ".join("%s: %.4f" % kv for kv in logs.items())))
+            if self.net.stop_training:
+                break
+        for cb in cbs:
+            cb.on_train_end({})
+        result = HistoryResult()
+        result.history, result.epoch = history.history, history.epoch
+        return result
 
     def release(self):
         self.stream.synchronize()
         self._drop_graphs()
-        for name in ("act", "gact", "aux", "ws", "params", "grads", "adam_m", "adam_v", "stats", "data"):
+        for name in ("act", "gact", "aux", "ws", "params", "grads", "adam_m", "adam_v", "stats", "data", "ring"):
             if hasattr(self, name):
                 delattr(self, name)
         self.capacity = 0

@@ -94,6 +94,8 @@ SIGNATURES = {
     "fnet_graph_launch": (C.c_int, [_P, _P]),
     "fnet_graph_destroy": (C.c_int, [_P]),
     "fnet_graph_step_fed": (C.c_int, [_P, _P, _P, C.c_size_t, _P, _P, C.c_size_t, _P, _P, C.c_size_t, _P]),
+    "fnet_graph_step_streamed": (C.c_int, [_P, _P, _P, _P, C.c_size_t, _P, _P, _P, C.c_size_t, _P, _P, _P, C.c_size_t,
+                                           _P, _P, _P, _P]),
 }
 
 _STATUS_RETURNING = {n for n, (r, _) in SIGNATURES.items() if r is C.c_int and n != "fnet_version"}

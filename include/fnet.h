@@ -299,6 +299,24 @@ int fnet_graph_step_fed(void *graph_exec, void *x_dev, const void *x_host, size_
                         const void *y_host, size_t y_bytes, const void *result_dev, void *result_host,
                         size_t result_bytes, void *stream);
 
+/* One step of a PIPELINED host feed, the shape of keras' fit_generator (helpers.py:163: batches arrive from a
+ * host-side queue while the previous step still runs).  The caller owns a ring of slots (two are enough); a slot is
+ * a device buffer pair (x_slot, y_slot) the captured step reads its batch from, optional pinned staging buffers,
+ * a pinned `result_host` and two events.  The call
+ *   1. waits on the host for `slot_event`, i.e. for the step that last used this slot, and copies that step's
+ *      results from `result_host` to `result_prev` (skipped when result_prev is NULL);
+ *   2. if x_stage / y_stage are given, memcpy()s the (pageable) host batch into them; without staging buffers the
+ *      host batch itself must be pinned and must stay untouched until the slot's next turn;
+ *   3. on `copy_stream`: both host-to-device copies, then records `copied_event`;
+ *   4. on `compute_stream`: waits for `copied_event`, replays the captured step, copies `result_bytes` from
+ *      `result_dev` to `result_host`, records `slot_event`.
+ * It does not wait for any of that: with two slots the upload of step i+1 overlaps the kernels of step i.
+ * Events are cudaEvent_t handles the caller created (record each once before the first use). */
+int fnet_graph_step_streamed(void *graph_exec, void *x_slot, const void *x_host, void *x_stage, size_t x_bytes,
+                             void *y_slot, const void *y_host, void *y_stage, size_t y_bytes, const void *result_dev,
+                             void *result_host, void *result_prev, size_t result_bytes, void *copy_stream,
+                             void *compute_stream, void *slot_event, void *copied_event);
+
 #ifdef __cplusplus
 }
 #endif
