@@ -20,7 +20,7 @@ int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *
              void *ws, size_t ws_bytes, cudaStream_t s) {
     int rc;
     if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
-    else if (tma_gemm_supported(g, math, 0)) rc = tma_gemm_fwd(g, act, x, w, bias, y, s);
+    else if (tma_gemm_supported(g, math, 0)) rc = tma_gemm_fwd(g, math, act, x, w, bias, y, s);
     else if (math != FNET_MATH_FP32 && tc_supported(g, math, 0)) rc = tc_conv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
     else rc = simt_conv_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
     if (rc == FNET_OK && act == FNET_ACT_SOFTMAX)
@@ -43,7 +43,7 @@ int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, flo
         int rc = conv_dgrad(gd, math, dz, w, t, DxEpilogue{0, 0, nullptr}, reinterpret_cast<char *>(ws) + t_bytes, ws_bytes - t_bytes, s);
         return rc == FNET_OK ? col2im_scatter(g, t, dx, ep, s) : rc;
     }
-    if (tma_gemm_supported(g, math, 1)) return tma_gemm_dgrad(g, dz, w, dx, ep, s);
+    if (tma_gemm_supported(g, math, 1)) return tma_gemm_dgrad(g, math, dz, w, dx, ep, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) return tc_conv_dgrad(g, math, dz, w, dx, ep, ws, ws_bytes, s);
     return simt_conv_dgrad(g, dz, w, dx, ep, ws, ws_bytes, s);
 }
@@ -51,7 +51,7 @@ int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, flo
 int conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                size_t ws_bytes, cudaStream_t s) {
     if (skinny_supported(g, 2, dbias != nullptr)) return skinny_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
-    if (tma_gemm_supported(g, math, 2)) return tma_gemm_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
+    if (tma_gemm_supported(g, math, 2)) return tma_gemm_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 2)) return tc_conv_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
     return simt_conv_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
 }

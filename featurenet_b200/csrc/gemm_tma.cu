@@ -22,6 +22,55 @@ namespace fnet {
 
 constexpr int TG_BM = 128, TG_BK = 32, TG_STAGES = 4, TG_THREADS = 192;
 constexpr int TG_A_BYTES = TG_BM * TG_BK * 4;
+// TF32x3 (fp32 accuracy): eight more warps rewrite every landed stage as hi = rna_tf32(v) in place and write the
+// tail lo = v - hi to a second copy of the stage with the same layout, then hand the stage to the MMA
+// warp, which issues lo*hi + hi*lo + hi*hi per k-step.  The layers this kernel serves are HBM-bound in plain tf32,
+// so the two extra MMAs and the pass over shared memory hide behind the loads.
+constexpr int TG_SPLITTERS = 256;                           // threads of the TF32x3 splitter warps (warps 6..13)
+constexpr int TG_THREADS_X3 = TG_THREADS + TG_SPLITTERS;
+constexpr int TG_SMEM_LIMIT = 209 * 1024;     // + 17 KB of static shared memory = the 227 KB a CTA may have
+
+// hi = x rounded to tf32 (nearest, ties away: what cvt.rna.tf32.f32 gives, in two integer instructions), lo = x - hi
+// exactly; the tensor core drops the low 13 mantissa bits of lo itself (2^-21 of x, below the lo*lo term left out).
+__device__ __forceinline__ void tg_hi_lo(uint32_t x, uint32_t &hi, uint32_t &lo) {
+    hi = (x + 0x1000u) & 0xffffe000u;
+    lo = __float_as_uint(__uint_as_float(x) - __uint_as_float(hi));
+}
+// hi in place, lo to the twin buffer `twin_offset` bytes further, for the 16-byte chunks [first, first + count) of a
+// stage; TG_SPLITTERS threads.  Four independent loads are in flight per thread before the first store (the loop is
+// latency-bound otherwise).  ones_box >= 0 (filter gradient, MN-major A): the chunk that holds row `32 * ones_box +
+// 4 * ones_sub` of every k becomes {1, 0, 0, 0} -- the all-ones row whose products are the column sums of dz, i.e.
+// the bias gradient, in a row of the A tile that the layer does not use.
+__device__ __forceinline__ void tg_split_chunks(uint8_t *stage, int first, int count, int twin_offset, int t, int ones_box,
+                                                int ones_sub) {
+    uint4 *hi = reinterpret_cast<uint4 *>(stage) + first;
+    uint4 *lo = reinterpret_cast<uint4 *>(stage + twin_offset) + first;
+    for (int c = t; c < count; c += 4 * TG_SPLITTERS) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (c + u * TG_SPLITTERS < count) v[u] = hi[c + u * TG_SPLITTERS];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = c + u * TG_SPLITTERS;
+            if (i < count) {
+                // MN-major box of 32 x 32: k-row of 128 bytes = 8 chunks, 32-byte pairs XORed with k % 4
+                if (ones_box >= 0 && (i >> 8) == ones_box && ((i & 7) ^ (((i >> 3) & 3) << 1)) == ones_sub)
+                    v[u] = make_uint4(0x3f800000u, 0u, 0u, 0u);
+                uint4 h, l;
+                tg_hi_lo(v[u].x, h.x, l.x);
+                tg_hi_lo(v[u].y, h.y, l.y);
+                tg_hi_lo(v[u].z, h.z, l.z);
+                tg_hi_lo(v[u].w, h.w, l.w);
+                hi[i] = h;
+                lo[i] = l;
+            }
+        }
+    }
+}
+__device__ __forceinline__ void tg_split_done() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> the tensor core's reads
+}
 
 __device__ __forceinline__ uint32_t tg_smem(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -83,21 +132,22 @@ __device__ __forceinline__ uint64_t tg_desc_mn(uint32_t saddr) {
     return d;
 }
 
-template <class P>
-__global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
-                                                                 const __grid_constant__ CUtensorMap map_b, P p, int M, int N,
-                                                                 int Kg, int BN, int n_tiles, int total_tiles, int tmem_cols) {
+template <class P, bool X3>
+__global__ void __launch_bounds__(X3 ? TG_THREADS_X3 : TG_THREADS, 1)
+tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, P p, int M, int N, int Kg,
+                int BN, int n_tiles, int total_tiles, int tmem_cols, int stages) {
     pdl_prologue();
     constexpr bool B_MN = !P::kBContigK;
     extern __shared__ uint8_t tg_smem_raw[];
-    __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], split_bar[TG_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_holder;
     __shared__ float xpose[4][32 * 33];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(tg_smem_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t smem_base = tg_smem(smem);
-    const int b_bytes = BN * TG_BK * 4, stage_bytes = TG_A_BYTES + b_bytes;
+    const int b_bytes = BN * TG_BK * 4, operand_bytes = TG_A_BYTES + b_bytes;      // what the TMA unit lands per stage
+    const int stage_bytes = X3 ? 2 * operand_bytes : operand_bytes;                // + the tails, same layout
     const int KT = (Kg + TG_BK - 1) / TG_BK;
 
     if (threadIdx.x == 0) {
@@ -106,7 +156,11 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_co
     }
     if (warp == 1) {
         if (lane == 0) {
-            for (int s = 0; s < TG_STAGES; ++s) { tg_bar_init(&full_bar[s], 1); tg_bar_init(&empty_bar[s], 1); }
+            for (int s = 0; s < stages; ++s) {
+                tg_bar_init(&full_bar[s], 1);
+                tg_bar_init(&empty_bar[s], 1);
+                tg_bar_init(&split_bar[s], TG_SPLITTERS / 32);
+            }
             for (int a = 0; a < 2; ++a) { tg_bar_init(&acc_full[a], 1); tg_bar_init(&acc_empty[a], 4); }
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
@@ -133,7 +187,7 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_co
                 tg_bar_wait(&empty_bar[stage], phase ^ 1);
                 const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
                 if (lane == 0) {
-                    tg_bar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+                    tg_bar_expect_tx(&full_bar[stage], (uint32_t)operand_bytes);
                     tg_tma_2d(sa, &map_a, &full_bar[stage], kt * TG_BK, m0);
                 }
                 if (B_MN) {
@@ -143,7 +197,20 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_co
                     tg_tma_2d(sb, &map_b, &full_bar[stage], kt * TG_BK, n0);
                 }
                 __syncwarp();
-                if (++stage == TG_STAGES) { stage = 0; phase ^= 1; }
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (X3 && warp >= 6) {
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            for (int kt = 0; kt < KT; ++kt) {
+                tg_bar_wait(&full_bar[stage], phase);
+                tg_split_chunks(smem + stage * stage_bytes, 0, operand_bytes / 16, operand_bytes, threadIdx.x - TG_THREADS, -1, 0);
+                tg_split_done();
+                __syncwarp();
+                if (lane == 0) tg_bar_arrive(&split_bar[stage]);
+                if (++stage == stages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -159,16 +226,27 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_co
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t d = tmem + acc * acc_stride;
                 for (int kt = 0; kt < KT; ++kt) {
-                    tg_bar_wait(&full_bar[stage], phase);
+                    tg_bar_wait(X3 ? &split_bar[stage] : &full_bar[stage], phase);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
                     const uint64_t da = tg_desc_k(sa), db = B_MN ? tg_desc_mn(sb) : tg_desc_k(sb);
                     const int badv = B_MN ? 64 : 2;          // 16-byte units per 8 k: two 4-row atoms / 32 bytes along the row
+                    if (X3) {
+                        const uint64_t la = tg_desc_k(sa + operand_bytes);
+                        const uint64_t lb = B_MN ? tg_desc_mn(sb + operand_bytes) : tg_desc_k(sb + operand_bytes);
 #pragma unroll
-                    for (int j = 0; j < TG_BK / 8; ++j)
-                        tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(badv * j), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+                        for (int j = 0; j < TG_BK / 8; ++j) {
+                            tg_mma(d, la + (uint64_t)(2 * j), db + (uint64_t)(badv * j), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+                            tg_mma(d, da + (uint64_t)(2 * j), lb + (uint64_t)(badv * j), idesc, 1u);
+                            tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(badv * j), idesc, 1u);      // the large term last
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < TG_BK / 8; ++j)
+                            tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(badv * j), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+                    }
                     tg_commit(&empty_bar[stage]);
-                    if (++stage == TG_STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
                 tg_commit(&acc_full[acc]);
             }
@@ -218,26 +296,31 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_gemm_kernel(const __grid_co
 // small: one (output tile, slice of the pixel axis) per CTA, partial tiles to the workspace, fixed-order reduce.
 // The bias gradient is the column sum of dz, i.e. a second accumulator fed by an all-ones A tile (an extra MMA per
 // k-step on a tensor pipe that is otherwise idle; the first row of that accumulator is the answer).
-__global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a,
-                                                                  const __grid_constant__ CUtensorMap map_b, WgradProblem p,
-                                                                  int M /* C (+1 bias row) */, int N, int pixels, int BN,
-                                                                  int n_tiles, int tiles, int kt_per_split, int stages,
-                                                                  int tmem_cols, float *__restrict__ partial) {
+template <bool X3>
+__global__ void __launch_bounds__(X3 ? TG_THREADS_X3 : TG_THREADS, 1)
+tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, WgradProblem p,
+                 int M /* C (+1 bias row) */, int N, int pixels, int BN, int n_tiles, int tiles, int kt_per_split, int stages,
+                 int tmem_cols, float *__restrict__ partial) {
     pdl_prologue();
     extern __shared__ uint8_t tg_smem_raw[];
-    __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], acc_full;
+    __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], split_bar[TG_STAGES], acc_full;
     __shared__ uint32_t tmem_holder;
     __shared__ float xpose[4][32 * 33];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(tg_smem_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t smem_base = tg_smem(smem);
-    const int b_bytes = BN * TG_BK * 4, stage_bytes = TG_A_BYTES + b_bytes;
+    const int b_bytes = BN * TG_BK * 4, operand_bytes = TG_A_BYTES + b_bytes;
+    const int stage_bytes = X3 ? 2 * operand_bytes : operand_bytes;
     const int tile = blockIdx.x % tiles, split = blockIdx.x / tiles;
     const int m0 = (tile / n_tiles) * TG_BM, n0 = (tile % n_tiles) * BN;
     const int KT_all = (pixels + TG_BK - 1) / TG_BK;
     const int kt_begin = split * kt_per_split, kt_end = min(KT_all, kt_begin + kt_per_split);
-    const bool with_bias = p.dbias != nullptr && m0 == 0;
+    // TF32x3: when the layer leaves a row of the A tile unused, the splitter makes it the all-ones row and the bias
+    // gradient is row taps_c of the main accumulator; otherwise (and in plain tf32, which has no pass over the stage)
+    // a second accumulator is fed by an all-ones tile
+    const int fold_row = (X3 && p.dbias != nullptr && p.taps_c >= m0 && p.taps_c < m0 + TG_BM) ? p.taps_c - m0 : -1;
+    const bool with_bias = p.dbias != nullptr && m0 == 0 && !(X3 && p.taps_c % TG_BM != 0);
     float *ones = reinterpret_cast<float *>(smem + stages * stage_bytes);
 
     if (threadIdx.x == 0) {
@@ -246,7 +329,11 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_c
     }
     if (warp == 1) {
         if (lane == 0) {
-            for (int s = 0; s < stages; ++s) { tg_bar_init(&full_bar[s], 1); tg_bar_init(&empty_bar[s], 1); }
+            for (int s = 0; s < stages; ++s) {
+                tg_bar_init(&full_bar[s], 1);
+                tg_bar_init(&empty_bar[s], 1);
+                tg_bar_init(&split_bar[s], TG_SPLITTERS / 32);
+            }
             tg_bar_init(&acc_full, 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
@@ -255,7 +342,7 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_c
                      "r"((uint32_t)tmem_cols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    } else if (warp >= 2 && with_bias) {
+    } else if (warp >= 2 && warp < 6 && with_bias) {
         for (int i = threadIdx.x - 64; i < TG_A_BYTES / 4; i += 128) ones[i] = 1.f;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -264,6 +351,8 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_c
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = tmem_holder;
     const uint32_t bias_col = (uint32_t)tmem_cols / 2;        // the column-sum accumulator
+    const int rows_here = min(TG_BM, p.taps_c - m0) + (fold_row >= 0 ? 1 : 0);      // rows of this tile that are stored
+    const int a_boxes = (rows_here + 31) / 32, b_boxes = (min(BN, N - n0) + 31) / 32;
 
     if (warp == 0) {
         int stage = 0;                                        // lanes 0..3: the A boxes, lanes 4..: the B boxes
@@ -271,11 +360,27 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_c
         for (int kt = kt_begin; kt < kt_end; ++kt) {
             tg_bar_wait(&empty_bar[stage], phase ^ 1);
             const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
-            if (lane == 0) tg_bar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+            if (lane == 0) tg_bar_expect_tx(&full_bar[stage], (uint32_t)operand_bytes);
             if (lane < TG_BM / 32) tg_tma_2d(sa + lane * 4096, &map_a, &full_bar[stage], m0 + 32 * lane, kt * TG_BK);
             else if (lane - TG_BM / 32 < BN / 32)
                 tg_tma_2d(sb + (lane - TG_BM / 32) * 4096, &map_b, &full_bar[stage], n0 + 32 * (lane - TG_BM / 32), kt * TG_BK);
             __syncwarp();
+            if (++stage == stages) { stage = 0; phase ^= 1; }
+        }
+    } else if (X3 && warp >= 6) {
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int kt = kt_begin; kt < kt_end; ++kt) {
+            tg_bar_wait(&full_bar[stage], phase);
+            // only the boxes that hold rows / columns of the layer (the TMA unit zero-fills the rest; their tails are
+            // never written, which can only reach output rows and columns that are not stored)
+            uint8_t *st = smem + stage * stage_bytes;
+            const int t = threadIdx.x - TG_THREADS;
+            tg_split_chunks(st, 0, a_boxes * 256, operand_bytes, t, fold_row >= 0 ? fold_row >> 5 : -1, (fold_row & 31) >> 2);
+            tg_split_chunks(st, TG_A_BYTES / 16, b_boxes * 256, operand_bytes, t, -1, 0);
+            tg_split_done();
+            __syncwarp();
+            if (lane == 0) tg_bar_arrive(&split_bar[stage]);
             if (++stage == stages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
@@ -287,15 +392,26 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_c
             int stage = 0;
             uint32_t phase = 0;
             for (int kt = kt_begin; kt < kt_end; ++kt) {
-                tg_bar_wait(&full_bar[stage], phase);
+                tg_bar_wait(X3 ? &split_bar[stage] : &full_bar[stage], phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
                 const uint64_t da = tg_desc_mn(sa), db = tg_desc_mn(sb);
+                const uint64_t la = tg_desc_mn(sa + operand_bytes), lb = tg_desc_mn(sb + operand_bytes);   // X3 only
 #pragma unroll
                 for (int j = 0; j < TG_BK / 8; ++j) {
                     const uint32_t accumulate = (kt > kt_begin || j > 0) ? 1u : 0u;
-                    tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, accumulate);
-                    if (with_bias) tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(64 * j), idesc_ones, accumulate);
+                    if (X3) {
+                        tg_mma(tmem, la + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, accumulate);
+                        tg_mma(tmem, da + (uint64_t)(64 * j), lb + (uint64_t)(64 * j), idesc, 1u);
+                        tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, 1u);
+                        if (with_bias) {
+                            tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), lb + (uint64_t)(64 * j), idesc_ones, accumulate);
+                            tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(64 * j), idesc_ones, 1u);
+                        }
+                    } else {
+                        tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, accumulate);
+                        if (with_bias) tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(64 * j), idesc_ones, accumulate);
+                    }
                 }
                 tg_commit(&empty_bar[stage]);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -311,7 +427,7 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tma_wgrad_kernel(const __grid_c
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
         const int taps_c = p.taps_c;
-        const int m_first = m0 + quad * 32, count = min(32, taps_c - m_first);
+        const int m_first = m0 + quad * 32, count = min(32, m0 + rows_here - m_first);
         for (int pass = 0; pass < (with_bias && quad == 0 ? 2 : 1); ++pass) {
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 uint32_t v[32];
@@ -390,9 +506,14 @@ static bool is_plain_gemm(const ConvGeom &g) {
     return g.kh == 1 && g.kw == 1 && g.sh == 1 && g.sw == 1 && g.pt == 0 && g.pl == 0 && g.Ho == g.H && g.Wo == g.W;
 }
 
-static int tg_bn(long long n) {
-    long long bn = ((n + 31) / 32) * 32;
-    return (int)(bn > 256 ? 256 : bn);
+// width of the output tile; wide layers are cut into equal tiles (260 -> 2 x 160 rather than 256 + 32).  The TF32x3
+// filter gradient stops at 128 columns: its stages are twice as large and three of them must fit (measured: 153 ->
+// 137 us on 64 -> 512; the forward product is better off with 256 columns and two stages, 115 vs 126 us)
+static int tg_bn(long long n, bool narrow = false) {
+    const long long cap = narrow ? 128 : 256;
+    const long long tiles = (n + cap - 1) / cap;
+    long long bn = (((n + tiles - 1) / tiles + 31) / 32) * 32;
+    return (int)(bn > cap ? cap : bn);
 }
 
 struct TgWgradPlan {
@@ -400,10 +521,17 @@ struct TgWgradPlan {
     size_t smem, ws_bytes;
 };
 
-static TgWgradPlan tg_wgrad_plan(const ConvGeom &g) {
+// pipeline depth that fits: TF32x3 stages carry a second copy (the tails) of both operand tiles
+static int tg_stages(int bn, bool x3, int most, size_t extra) {
+    size_t stage = (size_t)(x3 ? 2 : 1) * (TG_A_BYTES + bn * TG_BK * 4);
+    int n = (int)((TG_SMEM_LIMIT - 1024 - extra) / stage);
+    return n > most ? most : n;
+}
+
+static TgWgradPlan tg_wgrad_plan(const ConvGeom &g, bool x3) {
     TgWgradPlan t;
     const long long pixels = (long long)g.B * g.H * g.W, KT = ceil_div<long long>(pixels, TG_BK);
-    t.bn = tg_bn(g.K);
+    t.bn = tg_bn(g.K, x3);
     t.n_tiles = (int)ceil_div<long long>(g.K, t.bn);
     t.tiles = (int)ceil_div<long long>(g.C, TG_BM) * t.n_tiles;
     long long splits = kNumSMs / t.tiles, most = KT / 8;     // one CTA per SM, at least 8 k-tiles each
@@ -411,10 +539,10 @@ static TgWgradPlan tg_wgrad_plan(const ConvGeom &g) {
     if (splits < 1) splits = 1;
     t.kt_per_split = (int)ceil_div<long long>(KT, splits);
     t.splits = (int)ceil_div<long long>(KT, t.kt_per_split);
-    t.stages = 3;
+    t.stages = tg_stages(t.bn, x3, 3, TG_A_BYTES);
     t.tmem_cols = 64;
     while (t.tmem_cols < 2 * t.bn) t.tmem_cols *= 2;
-    t.smem = (size_t)t.stages * (TG_A_BYTES + t.bn * TG_BK * 4) + TG_A_BYTES + 1024;
+    t.smem = (size_t)t.stages * (x3 ? 2 : 1) * (TG_A_BYTES + t.bn * TG_BK * 4) + TG_A_BYTES + 1024;
     t.ws_bytes = t.splits > 1 ? (size_t)t.splits * (g.C + 1) * g.K * sizeof(float) : 0;
     return t;
 }
@@ -426,7 +554,8 @@ bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
         const char *e = getenv("FNET_TMA");
         mode = (e && e[0] == '0') ? 0 : 1;
     }
-    if (!mode || math != FNET_MATH_TF32 || product > 2 || !is_plain_gemm(g) || !encode_tiled()) return false;
+    if (!mode || (math != FNET_MATH_TF32 && math != FNET_MATH_TF32X3) || product > 2 || !is_plain_gemm(g) || !encode_tiled())
+        return false;
     long long M = (long long)g.B * g.H * g.W;
     if (product == 2)
         return !(g.C & 3) && !(g.K & 3) && g.C >= 16 && g.K >= 16 && M >= 8192 && M <= 0x7fffffffLL &&
@@ -437,7 +566,7 @@ bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
     return tiles >= kNumSMs;                                 // no split reduction here: the cp.async kernels do that
 }
 
-template <class P>
+template <class P, bool X3>
 static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, const float *b, long long N, bool b_mn,
                         cudaStream_t stream, const char *what) {
     if ((reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(b) & 15)) {
@@ -454,41 +583,49 @@ static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, c
     const long long total = ceil_div<long long>(M, TG_BM) * n_tiles;
     int tmem_cols = 64;
     while (tmem_cols < 2 * BN) tmem_cols *= 2;
-    const size_t smem = (size_t)TG_STAGES * (TG_A_BYTES + BN * TG_BK * 4) + 1024;
-    static bool configured = false;
+    const int stages = tg_stages(BN, X3, TG_STAGES, 0);
+    const size_t smem = (size_t)stages * (X3 ? 2 : 1) * (TG_A_BYTES + BN * TG_BK * 4) + 1024;
+    static bool configured = false;                          // one per instantiation
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(tma_gemm_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(tma_gemm_kernel<P, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TG_SMEM_LIMIT);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
         configured = true;
     }
     const unsigned grid = (unsigned)(total < kNumSMs ? total : kNumSMs);
-    launch_pdl(tma_gemm_kernel<P>, dim3(grid), dim3(TG_THREADS), smem, stream, map_a, map_b, p, (int)M, (int)N, (int)Kg, BN, n_tiles, (int)total,
-                                                          tmem_cols);
+    launch_pdl(tma_gemm_kernel<P, X3>, dim3(grid), dim3(X3 ? TG_THREADS_X3 : TG_THREADS), smem, stream, map_a, map_b, p, (int)M, (int)N, (int)Kg, BN,
+                                                              n_tiles, (int)total, tmem_cols, stages);
     return check_launch(what);
 }
 
-int tma_gemm_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t stream) {
+int tma_gemm_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
+                 cudaStream_t stream) {
     FwdProblem p{g, x, w, bias, y, act == FNET_ACT_SOFTMAX ? FNET_ACT_NONE : act};
-    return tma_gemm_run(p, x, (long long)g.B * g.H * g.W, g.C, w, g.K, true, stream, "conv2d_fwd[tf32,tma]");
+    const long long M = (long long)g.B * g.H * g.W;
+    if (math == FNET_MATH_TF32X3) return tma_gemm_run<FwdProblem, true>(p, x, M, g.C, w, g.K, true, stream, "conv2d_fwd[tf32x3,tma]");
+    return tma_gemm_run<FwdProblem, false>(p, x, M, g.C, w, g.K, true, stream, "conv2d_fwd[tf32,tma]");
 }
 
-int tma_gemm_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t stream) {
+int tma_gemm_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t stream) {
     DgradProblem p{g, dz, w, dx, ep.accumulate, ep.act, ep.y};
-    return tma_gemm_run(p, dz, (long long)g.B * g.H * g.W, g.K, w, g.C, false, stream, "conv2d_bwd_data[tf32,tma]");
+    const long long M = (long long)g.B * g.H * g.W;
+    if (math == FNET_MATH_TF32X3)
+        return tma_gemm_run<DgradProblem, true>(p, dz, M, g.K, w, g.C, false, stream, "conv2d_bwd_data[tf32x3,tma]");
+    return tma_gemm_run<DgradProblem, false>(p, dz, M, g.K, w, g.C, false, stream, "conv2d_bwd_data[tf32,tma]");
 }
 
 size_t tma_gemm_workspace(const ConvGeom &g, int math) {
-    return tma_gemm_supported(g, math, 2) ? tg_wgrad_plan(g).ws_bytes : 0;
+    return tma_gemm_supported(g, math, 2) ? tg_wgrad_plan(g, math == FNET_MATH_TF32X3).ws_bytes : 0;
 }
 
-int tma_gemm_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
-                   cudaStream_t stream) {
-    const char *what = "conv2d_bwd_filter[tf32,tma]";
+int tma_gemm_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
+                   size_t ws_bytes, cudaStream_t stream) {
+    const bool x3 = math == FNET_MATH_TF32X3;
+    const char *what = x3 ? "conv2d_bwd_filter[tf32x3,tma]" : "conv2d_bwd_filter[tf32,tma]";
     if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(dz) & 15)) {
         set_error("%s: operands must be 16-byte aligned for the TMA path", what);
         return FNET_ERR_ARG;
     }
-    TgWgradPlan t = tg_wgrad_plan(g);
+    TgWgradPlan t = tg_wgrad_plan(g, x3);
     float *partial = nullptr;
     if (t.splits > 1) {
         if (!ws || ws_bytes < t.ws_bytes) {
@@ -506,14 +643,20 @@ int tma_gemm_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw
     }
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(tma_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(tma_wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TG_SMEM_LIMIT);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(tma_wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TG_SMEM_LIMIT);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
         configured = true;
     }
     WgradProblem p{g, x, dz, dw, dbias, g.C};
     const int M = g.C + (dbias ? 1 : 0);
-    launch_pdl(tma_wgrad_kernel, dim3((unsigned)(t.tiles * t.splits)), dim3(TG_THREADS), t.smem, stream, map_a, map_b, p, M, g.K, (int)pixels, t.bn, t.n_tiles,
-                                                                                     t.tiles, t.kt_per_split, t.stages, t.tmem_cols, partial);
+    const dim3 grid((unsigned)(t.tiles * t.splits));
+    if (x3)
+        launch_pdl(tma_wgrad_kernel<true>, grid, dim3(TG_THREADS_X3), t.smem, stream, map_a, map_b, p, M, g.K, (int)pixels, t.bn, t.n_tiles, t.tiles,
+                                                                   t.kt_per_split, t.stages, t.tmem_cols, partial);
+    else
+        launch_pdl(tma_wgrad_kernel<false>, grid, dim3(TG_THREADS), t.smem, stream, map_a, map_b, p, M, g.K, (int)pixels, t.bn, t.n_tiles, t.tiles,
+                                                                 t.kt_per_split, t.stages, t.tmem_cols, partial);
     int rc = check_launch(what);
     if (rc == FNET_OK && t.splits > 1) rc = simt_reduce_wgrad_partials(g, dw, dbias, M, t.splits, partial, stream);
     return rc;

@@ -39,13 +39,15 @@ int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, 
 int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                   size_t ws_bytes, cudaStream_t stream);
 
-// FNET_MATH_TF32, layers that are plain GEMMs (Dense, 1x1 stride-1 convolutions): TMA-fed persistent kernel (gemm_tma.cu)
-bool tma_gemm_supported(const ConvGeom &g, int math, int product);   // product: 0 fwd, 1 dgrad
-int tma_gemm_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t stream);
-int tma_gemm_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t stream);
+// FNET_MATH_TF32 / FNET_MATH_TF32X3, layers that are plain GEMMs (Dense, 1x1 stride-1 convolutions): TMA-fed persistent
+// kernel (gemm_tma.cu)
+bool tma_gemm_supported(const ConvGeom &g, int math, int product);   // product: 0 fwd, 1 dgrad, 2 wgrad
+int tma_gemm_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
+                 cudaStream_t stream);
+int tma_gemm_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t stream);
 size_t tma_gemm_workspace(const ConvGeom &g, int math);
-int tma_gemm_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
-                   cudaStream_t stream);
+int tma_gemm_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
+                   size_t ws_bytes, cudaStream_t stream);
 int simt_reduce_wgrad_partials(const ConvGeom &g, float *dw, float *dbias, int M, int splits, const float *partial,
                                cudaStream_t stream);
 
