@@ -9,15 +9,36 @@ namespace {
 inline size_t max_sz(size_t a, size_t b) { return a > b ? a : b; }
 
 int check_math(int math, const char *what) {
-    if (math != FNET_MATH_FP32 && math != FNET_MATH_TF32 && math != FNET_MATH_BF16 && math != FNET_MATH_TF32X3) {
+    if (math != FNET_MATH_FP32 && math != FNET_MATH_TF32 && math != FNET_MATH_BF16 && math != FNET_MATH_TF32X3 &&
+        math != FNET_MATH_AUTO) {
         set_error("%s: unknown math mode %d", what, math);
         return FNET_ERR_ARG;
     }
     return FNET_OK;
 }
 
-int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
+// FNET_MATH_AUTO: both candidates meet the fp32 bar, so the choice is speed alone.  Measured on B200 at batch 128
+// (scripts/mode_sweep.sh): the three-MMA tensor-core kernels win once the output tile is not tiny -- 1.2x to 3.7x on
+// 24..192-channel convolutions and Dense layers -- and lose on the narrow ones (6 -> 12 5x5: 94 vs 56 us on the data
+// gradient, 101 vs 69 us on the filter gradient; 8-wide data gradients; 16 x 16 filter gradients).
+// product: 0 forward (N = K, reduction taps*C), 1 data gradient (N = C, reduction taps*K), 2 filter gradient
+// (rows taps*C, N = K, reduction over the pixels).
+static int resolve_math(const ConvGeom &g, int math, int product) {
+    if (math != FNET_MATH_AUTO) return math;
+    const long long taps = (long long)g.kh * g.kw;
+    bool tensor;
+    if (product == 2) {
+        tensor = g.K >= 24 && taps * g.C >= 32;
+    } else {
+        const long long n = product == 0 ? g.K : g.C, kg = taps * (product == 0 ? g.C : g.K);
+        tensor = (n >= 32 && kg >= 8) || (n >= 16 && kg >= 128) || (n >= 8 && kg >= 1024);
+    }
+    return tensor ? FNET_MATH_TF32X3 : FNET_MATH_FP32;
+}
+
+int conv_fwd(const ConvGeom &g, int math_in, int act, const float *x, const float *w, const float *bias, float *y,
              void *ws, size_t ws_bytes, cudaStream_t s) {
+    const int math = resolve_math(g, math_in, 0);
     int rc;
     if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
     else if (tma_gemm_supported(g, math, 0)) rc = tma_gemm_fwd(g, math, act, x, w, bias, y, s);
@@ -28,8 +49,9 @@ int conv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *
     return rc;
 }
 
-int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws,
+int conv_dgrad(const ConvGeom &g, int math_in, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws,
                size_t ws_bytes, cudaStream_t s) {
+    const int math = resolve_math(g, math_in, 1);
     // few channels on BOTH sides: the direct kernel beats GEMM + col2im (28x28x6 -> 12, 5x5: 54 vs 112 us)
     if (skinny_supported(g, 1, false)) return skinny_dgrad(g, dz, w, dx, ep, s);
     if (size_t t_bytes = col2im_t_bytes(g)) {
@@ -40,7 +62,7 @@ int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, flo
         }
         float *t = reinterpret_cast<float *>(ws);
         ConvGeom gd = dense_geom((long long)g.B * g.Ho * g.Wo, (long long)g.kh * g.kw * g.C, g.K);
-        int rc = conv_dgrad(gd, math, dz, w, t, DxEpilogue{0, 0, nullptr}, reinterpret_cast<char *>(ws) + t_bytes, ws_bytes - t_bytes, s);
+        int rc = conv_dgrad(gd, math_in, dz, w, t, DxEpilogue{0, 0, nullptr}, reinterpret_cast<char *>(ws) + t_bytes, ws_bytes - t_bytes, s);
         return rc == FNET_OK ? col2im_scatter(g, t, dx, ep, s) : rc;
     }
     if (tma_gemm_supported(g, math, 1)) return tma_gemm_dgrad(g, math, dz, w, dx, ep, s);
@@ -48,8 +70,9 @@ int conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, flo
     return simt_conv_dgrad(g, dz, w, dx, ep, ws, ws_bytes, s);
 }
 
-int conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
+int conv_wgrad(const ConvGeom &g, int math_in, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                size_t ws_bytes, cudaStream_t s) {
+    const int math = resolve_math(g, math_in, 2);
     if (skinny_supported(g, 2, dbias != nullptr)) return skinny_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
     if (tma_gemm_supported(g, math, 2)) return tma_gemm_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 2)) return tc_conv_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
@@ -72,7 +95,10 @@ size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
     ConvGeom g;
     if (geom_checked(d, g, "fnet_conv2d_workspace_bytes") != FNET_OK) return 0;
     size_t need = max_sz(simt_conv_workspace(g), skinny_workspace(g));
-    if (d->math != FNET_MATH_FP32) need = max_sz(need, max_sz(tc_conv_workspace(g, d->math), tma_gemm_workspace(g, d->math)));
+    if (d->math != FNET_MATH_FP32) {
+        const int tensor_math = d->math == FNET_MATH_AUTO ? FNET_MATH_TF32X3 : d->math;     // covers whatever AUTO resolves to
+        need = max_sz(need, max_sz(tc_conv_workspace(g, tensor_math), tma_gemm_workspace(g, tensor_math)));
+    }
     if (size_t t_bytes = col2im_t_bytes(g)) {
         ConvGeom gd = dense_geom((long long)g.B * g.Ho * g.Wo, (long long)g.kh * g.kw * g.C, g.K);
         need = max_sz(need, t_bytes + max_sz(simt_conv_workspace(gd), tc_conv_workspace(gd, FNET_MATH_TF32)));

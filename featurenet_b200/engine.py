@@ -81,7 +81,9 @@ class Engine(object):
         self.lib = fl.get()
         self.net = net
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
-        self.math = fl.MATH[(math_mode or os.environ.get("FNET_PRECISION", "fp32")).lower()]
+        # "auto" (the default) = fp32 accuracy with the faster of the FFMA and the three-MMA tensor-core kernel per
+        # product (FNET_MATH_AUTO); "fp32" forces FFMA everywhere, "tf32x3" the tensor core wherever it can run
+        self.math = fl.MATH[(math_mode or os.environ.get("FNET_PRECISION", "auto")).lower()]
         self.stream = torch.cuda.Stream(device=self.device)
         self.sp = C.c_void_p(self.stream.cuda_stream)
         # filter gradients run on a second stream, beside the data gradient of the same layer (both only read

@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(CSRC, "libfnet.so")
 
 ACT = {None: 0, "linear": 0, "relu": 1, "tanh": 2, "sigmoid": 3, "softmax": 4}
 POOL_MAX, POOL_AVG = 0, 1
-MATH = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3}
+MATH = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3, "auto": 4}
 STATIC_SCRATCH_BYTES = 4 << 20      # FNET_STATIC_SCRATCH_BYTES in include/fnet.h
 
 

@@ -209,10 +209,13 @@ class OracleNet(object):
         return grads
 
     # ------------------------------------------------------------------ one optimisation step
-    def train_step(self, x, targets, lr, dropout_masks=None, optimizer="adam"):
-        """Forward (training phase), loss/accuracy of that forward, backward, update. Returns (loss_sum, n_correct)."""
+    def train_step(self, x, targets, lr, dropout_masks=None, optimizer="adam", after_forward=None):
+        """Forward (training phase), loss/accuracy of that forward, backward, update. Returns (loss_sum, n_correct).
+        after_forward(self) may adjust self.outs before the backward pass (tests align ReLU kinks with it)."""
         outs = self.forward(x, training=True, dropout_masks=dropout_masks)
         loss, correct = ops.cce_fwd(outs[-1], np.asarray(targets, F64))
+        if after_forward is not None:
+            after_forward(self)
         grads = self.backward(targets)
         self.t += 1
         for i, row in enumerate(self.rows):

@@ -44,7 +44,7 @@ FULL_CONVS = [
 ]
 
 
-@pytest.mark.parametrize("math,tol", [("fp32", 2e-5), ("tf32", 4e-3), ("tf32x3", 2e-5)])
+@pytest.mark.parametrize("math,tol", [("fp32", 2e-5), ("tf32", 4e-3), ("tf32x3", 2e-5), ("auto", 2e-5)])
 @pytest.mark.parametrize("case_id", range(len(FULL_CONVS)))
 def test_conv_adjoint_linearity_determinism_full_size(L, case_id, math, tol):
     from featurenet_b200 import lib as fl
@@ -102,7 +102,7 @@ FULL_DENSE = [(25088, 120, 84),        # lenet5 Dense(84) on the rank-4 tensor @
               (128, 524288, 10)]       # keras template head (streaming kernels)
 
 
-@pytest.mark.parametrize("math,tol", [("fp32", 2e-5), ("tf32", 4e-3), ("tf32x3", 2e-5)])
+@pytest.mark.parametrize("math,tol", [("fp32", 2e-5), ("tf32", 4e-3), ("tf32x3", 2e-5), ("auto", 2e-5)])
 @pytest.mark.parametrize("m,k,n", FULL_DENSE)
 def test_dense_adjoint_full_size(L, m, k, n, math, tol):
     from featurenet_b200 import lib as fl
@@ -140,7 +140,7 @@ def intact(whole, n):
     return bool((whole[:GUARD] == 12345.0).all().item()) and bool((whole[GUARD + n:] == 12345.0).all().item())
 
 
-@pytest.mark.parametrize("math", ["fp32", "tf32", "tf32x3"])
+@pytest.mark.parametrize("math", ["fp32", "tf32", "tf32x3", "auto"])
 @pytest.mark.parametrize("xs,k,kout,s", [((3, 9, 7, 5), (3, 3), 7, (2, 2)), ((5, 13, 11, 33), (3, 3), 130, (1, 1)),
                                          ((130, 6, 6, 4), (1, 1), 16, (1, 1)), ((67, 16, 16, 24), (1, 1), 100, (1, 1)),
                                          ((40, 14, 14, 12), (5, 5), 120, (1, 1)), ((2, 5, 5, 2), (7, 7), 4, (1, 1))])

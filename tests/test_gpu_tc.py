@@ -32,7 +32,7 @@ TC_CONV_CASES = [
 ]
 
 
-MODES = [("tf32", TF32_TOL), ("tf32x3", 2e-5)]
+MODES = [("tf32", TF32_TOL), ("tf32x3", 2e-5), ("auto", 2e-5)]     # auto = fp32 or tf32x3 per product: the fp32 bar
 
 
 @pytest.mark.parametrize("math,tol", MODES)
