@@ -126,6 +126,15 @@ def test_forward_backward_and_adam_match_the_oracle(name):
         for a, b in zip(got_w, flat(oracle.weights)):
             bound = TOL * np.abs(b).max() + 0.05 * 1e-3
             assert np.abs(a - b).max() <= bound, "weights after step %d" % step
+        # every step is judged on its own: the next one starts from the engine's state on both sides, so that the
+        # (bounded, ill-conditioned) difference of an Adam step is not carried into the next step's gradients
+        torch.cuda.synchronize()
+        params, m, v = (t.cpu().numpy().astype(np.float64) for t in (eng.params, eng.adam_m, eng.adam_v))
+        for (i, k), (off, size) in eng.w_off.items():
+            shape = oracle.weights[i][k].shape
+            oracle.weights[i][k] = params[off: off + size].reshape(shape).copy()
+            oracle.adam_m[i][k] = m[off: off + size].reshape(shape).copy()
+            oracle.adam_v[i][k] = v[off: off + size].reshape(shape).copy()
 
 
 def test_inference_phase_uses_moving_statistics_and_no_dropout():
