@@ -103,6 +103,22 @@ __device__ __forceinline__ void tg_tma_2d(uint32_t dst, const CUtensorMap *map, 
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(tg_smem(bar)), "r"(c_inner), "r"(c_outer)
                  : "memory");
 }
+__device__ __forceinline__ void tg_tma_4d(uint32_t dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(tg_smem(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+
+// k x k stride-1 convolution as taps x ceil(C / 32) k-tiles of the same kernel: the A operand of k-tile (tap, chunk)
+// is the box {32 channels, W, rows, images} of the NHWC activation tensor, shifted by the tap.  Whatever the shift
+// moves outside the image the TMA unit zero-fills, which IS the convolution's padding; the box lands as 128
+// consecutive pixels x 32 channels, the K-major tile tcgen05 reads.  taps == 0: plain GEMM (2-D boxes).
+struct TgConv {
+    int taps, kw, chunks;       // k-tiles = taps * chunks
+    int tap_rows;               // rows of the weight matrix [taps * tap_rows][K] per tap (= C)
+    int H, W;                   // the OUTPUT grid of this product: a tile is 128 consecutive pixels of it
+    int off_h, off_w, step_h, step_w;   // input row of tap r at output row h: h + off_h + r * step_h
+};
 __device__ __forceinline__ void tg_mma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -135,7 +151,7 @@ __device__ __forceinline__ uint64_t tg_desc_mn(uint32_t saddr) {
 template <class P, bool X3>
 __global__ void __launch_bounds__(X3 ? TG_THREADS_X3 : TG_THREADS, 1)
 tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, P p, int M, int N, int Kg,
-                int BN, int n_tiles, int total_tiles, int tmem_cols, int stages) {
+                int BN, int n_tiles, int total_tiles, int tmem_cols, int stages, TgConv cv) {
     pdl_prologue();
     constexpr bool B_MN = !P::kBContigK;
     extern __shared__ uint8_t tg_smem_raw[];
@@ -148,7 +164,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const uint32_t smem_base = tg_smem(smem);
     const int b_bytes = BN * TG_BK * 4, operand_bytes = TG_A_BYTES + b_bytes;      // what the TMA unit lands per stage
     const int stage_bytes = X3 ? 2 * operand_bytes : operand_bytes;                // + the tails, same layout
-    const int KT = (Kg + TG_BK - 1) / TG_BK;
+    const int KT = cv.taps ? cv.taps * cv.chunks : (Kg + TG_BK - 1) / TG_BK;
 
     if (threadIdx.x == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
@@ -183,18 +199,36 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         uint32_t phase = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int m0 = (tile / n_tiles) * TG_BM, n0 = (tile % n_tiles) * BN;
+            int img = 0, row0 = 0;                            // convolution: the tile's first pixel is (img, row0, 0)
+            if (cv.taps) {
+                img = m0 / (cv.H * cv.W);
+                row0 = (m0 - img * cv.H * cv.W) / cv.W;
+            }
+            int tap = 0, chunk = 0, tr = 0, ts = 0;           // k-tile = (tap (tr, ts), 32-channel chunk)
             for (int kt = 0; kt < KT; ++kt) {
                 tg_bar_wait(&empty_bar[stage], phase ^ 1);
                 const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
+                // first reduction index of this k-tile in the weight matrix / in the plain A matrix
+                const int kb = cv.taps ? tap * cv.tap_rows + chunk * TG_BK : kt * TG_BK;
                 if (lane == 0) {
                     tg_bar_expect_tx(&full_bar[stage], (uint32_t)operand_bytes);
-                    tg_tma_2d(sa, &map_a, &full_bar[stage], kt * TG_BK, m0);
+                    if (cv.taps)
+                        tg_tma_4d(sa, &map_a, &full_bar[stage], chunk * TG_BK, cv.off_w + ts * cv.step_w,
+                                  row0 + cv.off_h + tr * cv.step_h, img);
+                    else
+                        tg_tma_2d(sa, &map_a, &full_bar[stage], kt * TG_BK, m0);
                 }
-                if (B_MN) {
+                if (B_MN) {                                   // forward: w [taps * C][K], boxes of 32 k-rows x 32 columns
                     if (lane >= 1 && lane <= BN / 32)
-                        tg_tma_2d(sb + (lane - 1) * 4096, &map_b, &full_bar[stage], n0 + 32 * (lane - 1), kt * TG_BK);
-                } else if (lane == 1) {
-                    tg_tma_2d(sb, &map_b, &full_bar[stage], kt * TG_BK, n0);
+                        tg_tma_2d(sb + (lane - 1) * 4096, &map_b, &full_bar[stage], n0 + 32 * (lane - 1), kb);
+                } else if (lane == 1) {                       // data gradient: w [taps * C][K] read as rows c, k along K
+                    if (cv.taps) tg_tma_2d(sb, &map_b, &full_bar[stage], chunk * TG_BK, tap * cv.tap_rows + n0);
+                    else tg_tma_2d(sb, &map_b, &full_bar[stage], kt * TG_BK, n0);
+                }
+                if (cv.taps && ++chunk == cv.chunks) {
+                    chunk = 0;
+                    ++tap;
+                    if (++ts == cv.kw) { ts = 0; ++tr; }
                 }
                 __syncwarp();
                 if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -300,7 +334,7 @@ template <bool X3>
 __global__ void __launch_bounds__(X3 ? TG_THREADS_X3 : TG_THREADS, 1)
 tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, WgradProblem p,
                  int M /* C (+1 bias row) */, int N, int pixels, int BN, int n_tiles, int tiles, int kt_per_split, int stages,
-                 int tmem_cols, float *__restrict__ partial) {
+                 int tmem_cols, float *__restrict__ partial, TgConv cv) {
     pdl_prologue();
     extern __shared__ uint8_t tg_smem_raw[];
     __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], split_bar[TG_STAGES], acc_full;
@@ -319,8 +353,11 @@ tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // TF32x3: when the layer leaves a row of the A tile unused, the splitter makes it the all-ones row and the bias
     // gradient is row taps_c of the main accumulator; otherwise (and in plain tf32, which has no pass over the stage)
     // a second accumulator is fed by an all-ones tile
-    const int fold_row = (X3 && p.dbias != nullptr && p.taps_c >= m0 && p.taps_c < m0 + TG_BM) ? p.taps_c - m0 : -1;
-    const bool with_bias = p.dbias != nullptr && m0 == 0 && !(X3 && p.taps_c % TG_BM != 0);
+    // k x k convolution (cv.taps > 0): the rows of the A tile are (tap, 32-channel chunk, channel), each 32-row block
+    // one shifted box of x; the reduction runs over 32-pixel boxes of the output grid.  Its bias gradient always
+    // takes the all-ones tile (the padded row layout has no fixed free row).
+    const int fold_row = (X3 && !cv.taps && p.dbias != nullptr && p.taps_c >= m0 && p.taps_c < m0 + TG_BM) ? p.taps_c - m0 : -1;
+    const bool with_bias = p.dbias != nullptr && m0 == 0 && !(X3 && !cv.taps && p.taps_c % TG_BM != 0);
     float *ones = reinterpret_cast<float *>(smem + stages * stage_bytes);
 
     if (threadIdx.x == 0) {
@@ -351,7 +388,8 @@ tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = tmem_holder;
     const uint32_t bias_col = (uint32_t)tmem_cols / 2;        // the column-sum accumulator
-    const int rows_here = min(TG_BM, p.taps_c - m0) + (fold_row >= 0 ? 1 : 0);      // rows of this tile that are stored
+    const int m_rows = cv.taps ? cv.taps * cv.chunks * 32 : p.taps_c;               // rows of the (padded) A matrix
+    const int rows_here = min(TG_BM, m_rows - m0) + (fold_row >= 0 ? 1 : 0);        // rows of this tile that are stored
     const int a_boxes = (rows_here + 31) / 32, b_boxes = (min(BN, N - n0) + 31) / 32;
 
     if (warp == 0) {
@@ -361,8 +399,20 @@ tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             tg_bar_wait(&empty_bar[stage], phase ^ 1);
             const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
             if (lane == 0) tg_bar_expect_tx(&full_bar[stage], (uint32_t)operand_bytes);
-            if (lane < TG_BM / 32) tg_tma_2d(sa + lane * 4096, &map_a, &full_bar[stage], m0 + 32 * lane, kt * TG_BK);
-            else if (lane - TG_BM / 32 < BN / 32)
+            if (lane < TG_BM / 32) {
+                if (cv.taps) {
+                    // row block -> (tap, chunk); k-tile -> the 32 output pixels starting at (img, row, col)
+                    const int rb = m0 / 32 + lane, tap = rb / cv.chunks, chunk = rb - tap * cv.chunks;
+                    const int tr = tap / cv.kw, ts = tap - tr * cv.kw;
+                    const int pix = kt * TG_BK, img = pix / (cv.H * cv.W), rem = pix - img * cv.H * cv.W;
+                    const int row = rem / cv.W, col = rem - row * cv.W;
+                    // a row block beyond the last tap reads outside the tensor (channel coordinate past C): zeros
+                    tg_tma_4d(sa + lane * 4096, &map_a, &full_bar[stage], tap < cv.taps ? chunk * 32 : (1 << 20),
+                              col + cv.off_w + ts * cv.step_w, row + cv.off_h + tr * cv.step_h, img);
+                } else {
+                    tg_tma_2d(sa + lane * 4096, &map_a, &full_bar[stage], m0 + 32 * lane, kt * TG_BK);
+                }
+            } else if (lane - TG_BM / 32 < BN / 32)
                 tg_tma_2d(sb + (lane - TG_BM / 32) * 4096, &map_b, &full_bar[stage], n0 + 32 * (lane - TG_BM / 32), kt * TG_BK);
             __syncwarp();
             if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -427,7 +477,12 @@ tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
         const int taps_c = p.taps_c;
-        const int m_first = m0 + quad * 32, count = min(32, m0 + rows_here - m_first);
+        int m_first = m0 + quad * 32, count = min(32, m0 + rows_here - m_first);
+        if (cv.taps) {                                        // padded row block -> rows tap * C + chunk * 32 ... of dw
+            const int rb = m_first / 32, tap = rb / cv.chunks, chunk = rb - tap * cv.chunks;
+            count = tap < cv.taps ? min(32, cv.tap_rows - chunk * 32) : 0;
+            m_first = tap * cv.tap_rows + chunk * 32;
+        }
         for (int pass = 0; pass < (with_bias && quad == 0 ? 2 : 1); ++pass) {
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 uint32_t v[32];
@@ -502,6 +557,39 @@ static bool make_map(CUtensorMap *map, const float *base, long long rows, long l
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+typedef EncodeTiledFn EncodeFn;
+
+// an NHWC fp32 tensor [B][H][W][C] seen through boxes of {32 channels, W_box, H_box, B_box}
+static bool make_map_nhwc(CUtensorMap *map, const float *base, long long B, long long H, long long W, long long C, int box_w,
+                          int box_h, int box_b, bool mn_major = false) {
+    EncodeFn fn = encode_tiled();
+    if (!fn) return false;
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+    cuuint32_t box[4] = {(cuuint32_t)TG_BK, (cuuint32_t)box_w, (cuuint32_t)box_h, (cuuint32_t)box_b};
+    cuuint32_t elem[4] = {1, 1, 1, 1};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float *>(base), dims, strides, box, elem,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// 128 consecutive pixels of an [H][W] grid as a box {W, rows, images}: W must divide 128 and the rows of a tile must
+// either divide H (tiles inside one image) or be whole images
+static bool tile_box(int H, int W, int &box_h, int &box_b) {
+    if (W < 1 || W > TG_BM || TG_BM % W) return false;
+    const int rows = TG_BM / W;
+    if (rows <= H) {
+        if (H % rows) return false;
+        box_h = rows;
+        box_b = 1;
+    } else {
+        if (rows % H) return false;
+        box_h = H;
+        box_b = rows / H;
+    }
+    return true;
+}
+
 static bool is_plain_gemm(const ConvGeom &g) {
     return g.kh == 1 && g.kw == 1 && g.sh == 1 && g.sw == 1 && g.pt == 0 && g.pl == 0 && g.Ho == g.H && g.Wo == g.W;
 }
@@ -528,12 +616,35 @@ static int tg_stages(int bn, bool x3, int most, size_t extra) {
     return n > most ? most : n;
 }
 
+// 32 consecutive pixels of an [H][W] grid as a box {W_box, rows, images} (the k-tile of the filter gradient)
+static bool pixel_box(int H, int W, int &box_w, int &box_h, int &box_b) {
+    if (W >= TG_BK) {
+        if (W % TG_BK) return false;
+        box_w = TG_BK; box_h = 1; box_b = 1;
+        return true;
+    }
+    if (W < 1 || TG_BK % W) return false;
+    const int rows = TG_BK / W;
+    box_w = W;
+    if (rows <= H) {
+        if (H % rows) return false;
+        box_h = rows; box_b = 1;
+    } else {
+        if (rows % H) return false;
+        box_h = H; box_b = rows / H;
+    }
+    return true;
+}
+
 static TgWgradPlan tg_wgrad_plan(const ConvGeom &g, bool x3) {
     TgWgradPlan t;
-    const long long pixels = (long long)g.B * g.H * g.W, KT = ceil_div<long long>(pixels, TG_BK);
+    const bool conv = !is_plain_gemm(g);
+    const long long pixels = (long long)g.B * g.Ho * g.Wo, KT = ceil_div<long long>(pixels, TG_BK);
+    // rows of the A matrix: C, or taps x (C rounded up to whole 32-channel chunks)
+    const long long m_rows = conv ? (long long)g.kh * g.kw * ceil_div<long long>(g.C, 32) * 32 : g.C;
     t.bn = tg_bn(g.K, x3);
     t.n_tiles = (int)ceil_div<long long>(g.K, t.bn);
-    t.tiles = (int)ceil_div<long long>(g.C, TG_BM) * t.n_tiles;
+    t.tiles = (int)ceil_div<long long>(m_rows, TG_BM) * t.n_tiles;
     long long splits = kNumSMs / t.tiles, most = KT / 8;     // one CTA per SM, at least 8 k-tiles each
     if (splits > most) splits = most;
     if (splits < 1) splits = 1;
@@ -543,7 +654,7 @@ static TgWgradPlan tg_wgrad_plan(const ConvGeom &g, bool x3) {
     t.tmem_cols = 64;
     while (t.tmem_cols < 2 * t.bn) t.tmem_cols *= 2;
     t.smem = (size_t)t.stages * (x3 ? 2 : 1) * (TG_A_BYTES + t.bn * TG_BK * 4) + TG_A_BYTES + 1024;
-    t.ws_bytes = t.splits > 1 ? (size_t)t.splits * (g.C + 1) * g.K * sizeof(float) : 0;
+    t.ws_bytes = t.splits > 1 ? (size_t)t.splits * ((size_t)g.kh * g.kw * g.C + 1) * g.K * sizeof(float) : 0;
     return t;
 }
 
@@ -554,8 +665,27 @@ bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
         const char *e = getenv("FNET_TMA");
         mode = (e && e[0] == '0') ? 0 : 1;
     }
-    if (!mode || (math != FNET_MATH_TF32 && math != FNET_MATH_TF32X3) || product > 2 || !is_plain_gemm(g) || !encode_tiled())
-        return false;
+    if (!mode || (math != FNET_MATH_TF32 && math != FNET_MATH_TF32X3) || product > 2 || !encode_tiled()) return false;
+    if (!is_plain_gemm(g)) {
+        // k x k convolutions, stride 1: forward and data gradient through shifted 4-D boxes (TgConv)
+        static int conv_mode = -1;                           // FNET_TMA_CONV=0 disables (A/B measurements)
+        if (conv_mode < 0) {
+            const char *e = getenv("FNET_TMA_CONV");
+            conv_mode = (e && e[0] == '0') ? 0 : 1;
+        }
+        int bw, bh, bb;
+        if (!conv_mode || g.sh != 1 || g.sw != 1 || (g.C & 3) || (g.K & 3)) return false;
+        if (product == 2) {
+            const long long pixels = (long long)g.B * g.Ho * g.Wo;
+            return pixel_box(g.Ho, g.Wo, bw, bh, bb) && g.K >= 16 && pixels >= 8192 && pixels <= 0x7fffffffLL &&
+                   (long long)g.kh * g.kw <= 64 && g.C <= 1024;
+        }
+        if (product == 0 ? !tile_box(g.Ho, g.Wo, bh, bb) : !tile_box(g.H, g.W, bh, bb)) return false;
+        const long long Mc = product == 0 ? (long long)g.B * g.Ho * g.Wo : (long long)g.B * g.H * g.W;
+        const long long Nc = product == 0 ? g.K : g.C;
+        if (Nc < 16 || Mc > 0x7fffffffLL || (long long)g.kh * g.kw > 64) return false;
+        return ceil_div<long long>(Mc, TG_BM) * ceil_div<long long>(Nc, tg_bn(Nc)) >= kNumSMs;
+    }
     long long M = (long long)g.B * g.H * g.W;
     if (product == 2)
         return !(g.C & 3) && !(g.K & 3) && g.C >= 16 && g.K >= 16 && M >= 8192 && M <= 0x7fffffffLL &&
@@ -566,18 +696,27 @@ bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
     return tiles >= kNumSMs;                                 // no split reduction here: the cp.async kernels do that
 }
 
+// a: the A operand, [M][Kg] for a plain GEMM, or (cv.taps > 0) the NHWC tensor [src_b][src_h][src_w][src_c] the
+// shifted boxes are cut from; b: the weights, [Kg][N] (b_mn) or [b_rows][Kg]
 template <class P, bool X3>
 static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, const float *b, long long N, bool b_mn,
-                        cudaStream_t stream, const char *what) {
+                        cudaStream_t stream, const char *what, const TgConv &cv = TgConv{}, int src_b = 0, int src_h = 0,
+                        int src_w = 0, int src_c = 0, long long b_rows = 0) {
     if ((reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(b) & 15)) {
         set_error("%s: operands must be 16-byte aligned for the TMA path", what);
         return FNET_ERR_ARG;
     }
     const int BN = tg_bn(N);
     CUtensorMap map_a, map_b;
-    bool ok = make_map(&map_a, a, M, Kg, TG_BM, TG_BK, CU_TENSOR_MAP_SWIZZLE_128B);
+    bool ok;
+    if (cv.taps) {
+        int box_h = 0, box_b = 0;
+        ok = tile_box(cv.H, cv.W, box_h, box_b) && make_map_nhwc(&map_a, a, src_b, src_h, src_w, src_c, cv.W, box_h, box_b);
+    } else {
+        ok = make_map(&map_a, a, M, Kg, TG_BM, TG_BK, CU_TENSOR_MAP_SWIZZLE_128B);
+    }
     if (b_mn) ok = ok && make_map(&map_b, b, Kg, N, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);    // w [K][N]
-    else ok = ok && make_map(&map_b, b, N, Kg, BN, TG_BK, CU_TENSOR_MAP_SWIZZLE_128B);               // w [C][Kg]
+    else ok = ok && make_map(&map_b, b, b_rows ? b_rows : N, Kg, BN, TG_BK, CU_TENSOR_MAP_SWIZZLE_128B);   // w [C][Kg]
     if (!ok) { set_error("%s: cuTensorMapEncodeTiled failed", what); return FNET_ERR_CUDA; }
     const int n_tiles = (int)ceil_div<long long>(N, BN);
     const long long total = ceil_div<long long>(M, TG_BM) * n_tiles;
@@ -593,20 +732,37 @@ static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, c
     }
     const unsigned grid = (unsigned)(total < kNumSMs ? total : kNumSMs);
     launch_pdl(tma_gemm_kernel<P, X3>, dim3(grid), dim3(X3 ? TG_THREADS_X3 : TG_THREADS), smem, stream, map_a, map_b, p, (int)M, (int)N, (int)Kg, BN,
-                                                              n_tiles, (int)total, tmem_cols, stages);
+                                                              n_tiles, (int)total, tmem_cols, stages, cv);
     return check_launch(what);
 }
 
 int tma_gemm_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
                  cudaStream_t stream) {
     FwdProblem p{g, x, w, bias, y, act == FNET_ACT_SOFTMAX ? FNET_ACT_NONE : act};
+    const bool x3 = math == FNET_MATH_TF32X3;
+    if (!is_plain_gemm(g)) {
+        const long long M = (long long)g.B * g.Ho * g.Wo, Kg = (long long)g.kh * g.kw * g.C;
+        TgConv cv{g.kh * g.kw, g.kw, (int)ceil_div<long long>(g.C, TG_BK), g.C, g.Ho, g.Wo, -g.pt, -g.pl, g.dh, g.dw};
+        const char *what = x3 ? "conv2d_fwd[tf32x3,tma,taps]" : "conv2d_fwd[tf32,tma,taps]";
+        if (x3) return tma_gemm_run<FwdProblem, true>(p, x, M, Kg, w, g.K, true, stream, what, cv, g.B, g.H, g.W, g.C);
+        return tma_gemm_run<FwdProblem, false>(p, x, M, Kg, w, g.K, true, stream, what, cv, g.B, g.H, g.W, g.C);
+    }
     const long long M = (long long)g.B * g.H * g.W;
-    if (math == FNET_MATH_TF32X3) return tma_gemm_run<FwdProblem, true>(p, x, M, g.C, w, g.K, true, stream, "conv2d_fwd[tf32x3,tma]");
+    if (x3) return tma_gemm_run<FwdProblem, true>(p, x, M, g.C, w, g.K, true, stream, "conv2d_fwd[tf32x3,tma]");
     return tma_gemm_run<FwdProblem, false>(p, x, M, g.C, w, g.K, true, stream, "conv2d_fwd[tf32,tma]");
 }
 
 int tma_gemm_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t stream) {
     DgradProblem p{g, dz, w, dx, ep.accumulate, ep.act, ep.y};
+    if (!is_plain_gemm(g)) {
+        // dx[h][w] = sum over taps of dz[h + pt - r*dh][w + pl - s*dw] . w[r][s]^T: the same shifted boxes, over dz
+        const long long M = (long long)g.B * g.H * g.W, rows = (long long)g.kh * g.kw * g.C;
+        TgConv cv{g.kh * g.kw, g.kw, (int)ceil_div<long long>(g.K, TG_BK), g.C, g.H, g.W, g.pt, g.pl, -g.dh, -g.dw};
+        const bool x3 = math == FNET_MATH_TF32X3;
+        const char *what = x3 ? "conv2d_bwd_data[tf32x3,tma,taps]" : "conv2d_bwd_data[tf32,tma,taps]";
+        if (x3) return tma_gemm_run<DgradProblem, true>(p, dz, M, g.K, w, g.C, false, stream, what, cv, g.B, g.Ho, g.Wo, g.K, rows);
+        return tma_gemm_run<DgradProblem, false>(p, dz, M, g.K, w, g.C, false, stream, what, cv, g.B, g.Ho, g.Wo, g.K, rows);
+    }
     const long long M = (long long)g.B * g.H * g.W;
     if (math == FNET_MATH_TF32X3)
         return tma_gemm_run<DgradProblem, true>(p, dz, M, g.K, w, g.C, false, stream, "conv2d_bwd_data[tf32x3,tma]");
@@ -634,10 +790,19 @@ int tma_gemm_wgrad(const ConvGeom &g, int math, const float *x, const float *dz,
         }
         partial = reinterpret_cast<float *>(ws);
     }
-    const long long pixels = (long long)g.B * g.H * g.W;
+    const bool conv = !is_plain_gemm(g);
+    const long long pixels = (long long)g.B * g.Ho * g.Wo;
     CUtensorMap map_a, map_b;
-    if (!make_map(&map_a, x, pixels, g.C, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) ||
-        !make_map(&map_b, dz, pixels, g.K, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) {
+    TgConv cv{};
+    bool ok;
+    if (conv) {
+        int bw = 0, bh = 0, bb = 0;
+        cv = TgConv{g.kh * g.kw, g.kw, (int)ceil_div<long long>(g.C, 32), g.C, g.Ho, g.Wo, -g.pt, -g.pl, g.dh, g.dw};
+        ok = pixel_box(g.Ho, g.Wo, bw, bh, bb) && make_map_nhwc(&map_a, x, g.B, g.H, g.W, g.C, bw, bh, bb, true);
+    } else {
+        ok = make_map(&map_a, x, pixels, g.C, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+    }
+    if (!ok || !make_map(&map_b, dz, pixels, g.K, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) {
         set_error("%s: cuTensorMapEncodeTiled failed", what);
         return FNET_ERR_CUDA;
     }
@@ -648,15 +813,15 @@ int tma_gemm_wgrad(const ConvGeom &g, int math, const float *x, const float *dz,
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
         configured = true;
     }
-    WgradProblem p{g, x, dz, dw, dbias, g.C};
-    const int M = g.C + (dbias ? 1 : 0);
+    WgradProblem p{g, x, dz, dw, dbias, g.kh * g.kw * g.C};
+    const int M = g.kh * g.kw * g.C + (dbias ? 1 : 0);
     const dim3 grid((unsigned)(t.tiles * t.splits));
     if (x3)
         launch_pdl(tma_wgrad_kernel<true>, grid, dim3(TG_THREADS_X3), t.smem, stream, map_a, map_b, p, M, g.K, (int)pixels, t.bn, t.n_tiles, t.tiles,
-                                                                   t.kt_per_split, t.stages, t.tmem_cols, partial);
+                                                                   t.kt_per_split, t.stages, t.tmem_cols, partial, cv);
     else
         launch_pdl(tma_wgrad_kernel<false>, grid, dim3(TG_THREADS), t.smem, stream, map_a, map_b, p, M, g.K, (int)pixels, t.bn, t.n_tiles, t.tiles,
-                                                                 t.kt_per_split, t.stages, t.tmem_cols, partial);
+                                                                 t.kt_per_split, t.stages, t.tmem_cols, partial, cv);
     int rc = check_launch(what);
     if (rc == FNET_OK && t.splits > 1) rc = simt_reduce_wgrad_partials(g, dw, dbias, M, t.splits, partial, stream);
     return rc;

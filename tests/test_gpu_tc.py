@@ -29,6 +29,12 @@ TC_CONV_CASES = [
     ((4, 14, 14, 12), (5, 5), 120, (1, 1)),     # lenet5 conv3: the data gradient has N = 12 (one 16-wide MMA), K = 3000
     ((2, 32, 32, 6), (5, 5), 12, (1, 1)),       # lenet5 conv2: N = 12 forward, C = 6 (scalar gather)
     ((3, 16, 16, 192), (1, 1), 3, (1, 1)),      # 192 -> 3 "Reg_" conv: forward N = 3 stays on the FFMA path, dgrad N = 192
+    # large enough (>= 148 output tiles) for the TMA-fed kernel with shifted 4-D boxes (forward and data gradient)
+    ((20, 32, 32, 24), (3, 1), 192, (1, 1)),    # the x8 expansion: C = 24 (one partly empty 32-channel chunk), 4 rows x 32 per tile
+    ((76, 16, 16, 32), (3, 3), 64, (1, 1)),     # 8 rows x 16 per tile
+    ((301, 8, 8, 64), (3, 3), 64, (1, 1)),      # whole 8 x 8 images, two per tile, the last tile half outside the batch
+    ((40, 32, 32, 12), (5, 5), 120, (1, 1)),    # 25 taps of 12 channels; the data gradient goes through col2im
+    ((38, 32, 32, 20), (2, 2), 36, (1, 1)),     # even kernel: SAME pads only bottom / right
 ]
 
 
