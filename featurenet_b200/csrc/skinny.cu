@@ -381,6 +381,56 @@ __global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const
     }
 }
 
+// Data gradient of a 1x1 / Dense layer with very few OUTPUT channels (the "Reg_" aligners back to 3 channels,
+// model/operation.py:186): dx[p][c] = sum over k <= 8 of dz[p][k] * w[c][k].  Nothing to tile: dz is tiny, dx is the
+// traffic, so a thread produces four consecutive channels of one pixel and a warp writes 512 contiguous bytes.
+// (The implicit-GEMM kernel spent 174 us on 262 144 x 192 <- 3, i.e. 1.2 TB/s for a pure store stream.)
+constexpr int kPointwiseK = 8;
+
+__global__ void __launch_bounds__(256) pointwise_dgrad_kernel(int M, int C, int K, const float *__restrict__ dz,
+                                                              const float *__restrict__ w, float *__restrict__ dx,
+                                                              int accumulate, int act, const float *__restrict__ yact,
+                                                              int vec_store) {
+    pdl_prologue();
+    extern __shared__ __align__(16) float wsm[];             // w transposed to [K][C]: a thread's four channels are one LDS.128
+    for (int i = threadIdx.x; i < C * K; i += 256) {
+        const int c = i / K, k = i - c * K;
+        wsm[k * C + c] = __ldg(w + i);
+    }
+    __syncthreads();
+    const int quads = C >> 2, total = M * quads;
+    for (int idx = blockIdx.x * 256 + threadIdx.x; idx < total; idx += gridDim.x * 256) {
+        const int p = idx / quads, c = (idx - p * quads) << 2;
+        float g[kPointwiseK];
+#pragma unroll
+        for (int k = 0; k < kPointwiseK; ++k) g[k] = k < K ? __ldg(dz + (long long)p * K + k) : 0.f;
+        float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int k = 0; k < kPointwiseK; ++k)
+            if (k < K) {
+                const float4 wv = *reinterpret_cast<const float4 *>(wsm + k * C + c);
+                v[0] = fmaf(g[k], wv.x, v[0]);
+                v[1] = fmaf(g[k], wv.y, v[1]);
+                v[2] = fmaf(g[k], wv.z, v[2]);
+                v[3] = fmaf(g[k], wv.w, v[3]);
+            }
+        const long long at = (long long)p * C + c;
+        if (vec_store) {
+            *reinterpret_cast<float4 *>(dx + at) = make_float4(v[0], v[1], v[2], v[3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) store_dx(dx, at + j, v[j], accumulate, act, yact);
+        }
+    }
+}
+
+static bool pointwise_dgrad_ok(const ConvGeom &g) {
+    const long long M = (long long)g.B * g.H * g.W;
+    return g.kh == 1 && g.kw == 1 && g.sh == 1 && g.sw == 1 && g.pt == 0 && g.pl == 0 && g.Ho == g.H && g.Wo == g.W &&
+           g.K <= kPointwiseK && !(g.C & 3) && g.C >= 32 && (long long)g.C * g.K * 4 <= 40 * 1024 && M >= 4096 &&
+           M * (g.C >> 2) < 0x7fffffffLL;
+}
+
 // filter gradient of the smallest convolutions: every (tap, c, k) partial sum (and the bias sums) lives in
 // registers; partial[block][row][k] goes to the workspace and is reduced in a fixed order afterwards
 constexpr int kWgradRegs = 64;
@@ -477,6 +527,7 @@ static bool small_wgrad_ok(const ConvGeom &g, bool with_bias) {
 
 bool skinny_supported(const ConvGeom &g, int product, bool with_bias) {
     // head-like only: a long reduction axis and a modest number of rows (one CTA per row / one thread per k)
+    if (product == 1 && pointwise_dgrad_ok(g)) return true;
     if (is_dense_geom(g)) return g.K <= kSkinnyN && g.C >= 512 && g.B >= 1 && g.B <= 8192;
     if (product == 0) return small_fwd_ok(g);
     if (product == 1) return small_dgrad_ok(g);
@@ -534,6 +585,15 @@ int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const
 }
 
 int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t s) {
+    if (pointwise_dgrad_ok(g)) {
+        const int vec_store = !ep.accumulate && !ep.act && !(reinterpret_cast<uintptr_t>(dx) & 15);
+        const long long M = (long long)g.B * g.H * g.W, total = M * (g.C >> 2);
+        long long blocks = ceil_div<long long>(total, 256);
+        const long long cap = (long long)kNumSMs * 16;
+        launch_pdl(pointwise_dgrad_kernel, dim3((unsigned)(blocks > cap ? cap : blocks)), dim3(256), (size_t)g.C * g.K * sizeof(float), s,
+                   (int)M, g.C, g.K, dz, w, dx, ep.accumulate, ep.act, ep.y, vec_store);
+        return check_launch("conv2d_bwd_data[pointwise]");
+    }
     if (is_dense_geom(g)) {
         long long bx = ceil_div<long long>(g.C, 256);
         if (bx > 4096) bx = 4096;

@@ -85,6 +85,8 @@ CONV_CASES = [
     ((16, 14, 14, 12), (5, 5), 120, (1, 1), "same", (1, 1), "tanh"),    # few in-channels: dgrad = dense GEMM + col2im
     ((64, 32, 32, 8), (3, 3), 64, (2, 2), "same", (1, 1), "relu"),      # col2im dgrad with stride 2
     ((48, 20, 20, 4), (3, 3), 100, (1, 1), "same", (2, 2), None),       # col2im dgrad with dilation 2
+    ((20, 16, 16, 192), (1, 1), 3, (1, 1), "same", (1, 1), None),       # "Reg_" 192 -> 3 at size: pointwise data gradient
+    ((17, 16, 16, 36), (1, 1), 8, (1, 1), "valid", (1, 1), "relu"),     # pointwise data gradient, 8 output channels
 ]
 
 

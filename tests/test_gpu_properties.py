@@ -143,7 +143,8 @@ def intact(whole, n):
 @pytest.mark.parametrize("math", ["fp32", "tf32", "tf32x3", "auto"])
 @pytest.mark.parametrize("xs,k,kout,s", [((3, 9, 7, 5), (3, 3), 7, (2, 2)), ((5, 13, 11, 33), (3, 3), 130, (1, 1)),
                                          ((130, 6, 6, 4), (1, 1), 16, (1, 1)), ((67, 16, 16, 24), (1, 1), 100, (1, 1)),
-                                         ((40, 14, 14, 12), (5, 5), 120, (1, 1)), ((2, 5, 5, 2), (7, 7), 4, (1, 1))])
+                                         ((40, 14, 14, 12), (5, 5), 120, (1, 1)), ((2, 5, 5, 2), (7, 7), 4, (1, 1)),
+                                         ((19, 16, 16, 36), (1, 1), 5, (1, 1)), ((160, 16, 16, 24), (3, 3), 40, (1, 1))])
 def test_no_kernel_writes_outside_its_output(L, xs, k, kout, s, math):
     """compute-sanitizer is closed on this pool: out-of-bounds WRITES are looked for with guard bands around every
     output of the three products, on ragged shapes that exercise every tile edge, in all math modes."""
