@@ -502,7 +502,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--quick", action="store_true", help="skip the secondary workloads")
     ap.add_argument("--population", type=int, default=32, help="candidates of the sharded population run (0 = skip)")
-    ap.add_argument("--resident", type=int, default=4, help="candidates kept resident per GPU in the population run")
+    ap.add_argument("--resident", type=int, default=8, help="candidates kept resident per GPU in the population run")
     args = ap.parse_args()
     claim_stdout()
     if args.impl == "reference":

@@ -424,6 +424,125 @@ __global__ void __launch_bounds__(256) pointwise_dgrad_kernel(int M, int C, int 
     }
 }
 
+// Forward of the same layers: y[p][k] = act(sum over c of x[p][c] * w[c][k] + b[k]), K <= 8.  LP lanes share a pixel,
+// each takes every LP-th group of four channels (one LDG.128 of x, K LDS.128 of the weights, which are stored as
+// w[c][k] so that four channels are 4K consecutive floats), then a shuffle tree: x is read once, coalesced.
+template <int K, int LP>
+__global__ void __launch_bounds__(256) pointwise_fwd_kernel(int M, int C, int act, const float *__restrict__ x,
+                                                            const float *__restrict__ w, const float *__restrict__ bias,
+                                                            float *__restrict__ y) {
+    pdl_prologue();
+    extern __shared__ __align__(16) float wsm[];             // w [C][K]
+    for (int i = threadIdx.x; i < C * K; i += 256) wsm[i] = __ldg(w + i);
+    __syncthreads();
+    const int quads = C >> 2, sub = threadIdx.x % LP;
+    const int per_block = 256 / LP;
+    // the trip count is uniform over the block (the shuffles below need whole warps); pixels past the end do no loads
+    for (int base = blockIdx.x * per_block; base < M; base += gridDim.x * per_block) {
+        const int p = base + threadIdx.x / LP;
+        float acc[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) acc[k] = 0.f;
+        const float4 *xp = reinterpret_cast<const float4 *>(x + (long long)p * C);
+        const int mine = p < M ? quads : 0;
+        for (int q0 = sub; q0 < mine; q0 += 4 * LP) {
+            float4 xv[4];                                     // four loads in flight before the first use
+#pragma unroll
+            for (int u = 0; u < 4; ++u) xv[u] = q0 + u * LP < mine ? __ldg(xp + q0 + u * LP) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int q = q0 + u * LP < mine ? q0 + u * LP : sub;      // zeros times any valid weights
+                float wf[4 * K];
+#pragma unroll
+                for (int j = 0; j < K; ++j)
+                    *reinterpret_cast<float4 *>(wf + 4 * j) = *reinterpret_cast<const float4 *>(wsm + 4 * q * K + 4 * j);
+#pragma unroll
+                for (int k = 0; k < K; ++k)
+                    acc[k] = fmaf(xv[u].x, wf[k], fmaf(xv[u].y, wf[K + k], fmaf(xv[u].z, wf[2 * K + k], fmaf(xv[u].w, wf[3 * K + k], acc[k]))));
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int o = LP / 2; o > 0; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+        if (sub == 0 && p < M) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) y[(long long)p * K + k] = act_apply(acc[k] + (bias ? __ldg(bias + k) : 0.f), act);
+        }
+    }
+}
+
+// Filter gradient of the same layers: dw[c][k] = sum over pixels of x[p][c] * dz[p][k] (+ the bias row).  A thread owns
+// four channels and keeps their 4K sums in registers while it walks the pixels; consecutive threads take consecutive
+// channel groups of one pixel (coalesced), 256 / (C/4) pixels per block step.  partial[block][(C + 1) * K], fixed-order reduce.
+template <int K>
+__global__ void __launch_bounds__(256) pointwise_wgrad_kernel(int M, int C, const float *__restrict__ x,
+                                                              const float *__restrict__ dz, float *__restrict__ partial) {
+    pdl_prologue();
+    extern __shared__ __align__(16) float red[];             // [pixel group][quad][4K] (+ [pixel group][K] bias sums)
+    const int quads = C >> 2, groups = 256 / quads;
+    const int pg = threadIdx.x / quads, q = threadIdx.x - pg * quads;
+    float acc[4 * K], bsum[K];
+#pragma unroll
+    for (int i = 0; i < 4 * K; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) bsum[k] = 0.f;
+    if (pg < groups) {
+        const int step = gridDim.x * groups;
+        for (int p0 = blockIdx.x * groups + pg; p0 < M; p0 += 4 * step) {
+            float4 xv[4];                                     // four pixels per trip: all loads issued before the first FMA
+            float g[4][K];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int p = p0 + u * step;
+                const bool in = p < M;
+                xv[u] = in ? __ldg(reinterpret_cast<const float4 *>(x + (long long)p * C) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int k = 0; k < K; ++k) g[u][k] = in ? __ldg(dz + (long long)p * K + k) : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    acc[k] = fmaf(xv[u].x, g[u][k], acc[k]);
+                    acc[K + k] = fmaf(xv[u].y, g[u][k], acc[K + k]);
+                    acc[2 * K + k] = fmaf(xv[u].z, g[u][k], acc[2 * K + k]);
+                    acc[3 * K + k] = fmaf(xv[u].w, g[u][k], acc[3 * K + k]);
+                    bsum[k] += g[u][k];
+                }
+        }
+        float *mine = red + ((long long)pg * quads + q) * 4 * K;
+#pragma unroll
+        for (int i = 0; i < 4 * K; ++i) mine[i] = acc[i];
+        if (q == 0) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) red[groups * quads * 4 * K + pg * K + k] = bsum[k];
+        }
+    }
+    __syncthreads();
+    // rows c = 4q + j of dw are red[.][q][j * K + k]: flat index (4q + j) * K + k = q * 4K + (j * K + k), the same order
+    const int total = C * K;
+    float *out = partial + (long long)blockIdx.x * (total + K);
+    for (int i = threadIdx.x; i < total + K; i += 256) {
+        float v = 0.f;
+        if (i < total) {
+            for (int z = 0; z < groups; ++z) v += red[(long long)z * total + i];
+        } else {
+            for (int z = 0; z < groups; ++z) v += red[groups * total + z * K + (i - total)];
+        }
+        out[i] = v;
+    }
+}
+
+constexpr int kPointwiseBlocks = 4 * kNumSMs;
+
+static bool pointwise_shape_ok(const ConvGeom &g) {
+    const long long M = (long long)g.B * g.H * g.W;
+    return g.kh == 1 && g.kw == 1 && g.sh == 1 && g.sw == 1 && g.pt == 0 && g.pl == 0 && g.Ho == g.H && g.Wo == g.W &&
+           g.K <= kPointwiseK && !(g.C & 3) && g.C >= 32 && g.C <= 1024 && (long long)g.C * g.K * 4 <= 40 * 1024 && M >= 4096 &&
+           M * (g.C >> 2) < 0x7fffffffLL;
+}
+
 static bool pointwise_dgrad_ok(const ConvGeom &g) {
     const long long M = (long long)g.B * g.H * g.W;
     return g.kh == 1 && g.kw == 1 && g.sh == 1 && g.sw == 1 && g.pt == 0 && g.pl == 0 && g.Ho == g.H && g.Wo == g.W &&
@@ -499,7 +618,7 @@ __global__ void __launch_bounds__(256) conv_small_wgrad_reduce_kernel(int blocks
                                                                       float *__restrict__ dw, float *__restrict__ dbias) {
     pdl_prologue();
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int i = warp; i < total; i += 8) {
+    for (int i = blockIdx.x * 8 + warp; i < total; i += gridDim.x * 8) {
         float s = 0.f;
         for (int z = lane; z < blocks; z += 32) s += partial[(long long)z * total + i];
         s = warp_sum(s);
@@ -528,6 +647,7 @@ static bool small_wgrad_ok(const ConvGeom &g, bool with_bias) {
 bool skinny_supported(const ConvGeom &g, int product, bool with_bias) {
     // head-like only: a long reduction axis and a modest number of rows (one CTA per row / one thread per k)
     if (product == 1 && pointwise_dgrad_ok(g)) return true;
+    if (product != 1 && pointwise_shape_ok(g)) return true;
     if (is_dense_geom(g)) return g.K <= kSkinnyN && g.C >= 512 && g.B >= 1 && g.B <= 8192;
     if (product == 0) return small_fwd_ok(g);
     if (product == 1) return small_dgrad_ok(g);
@@ -537,6 +657,7 @@ bool skinny_supported(const ConvGeom &g, int product, bool with_bias) {
 size_t skinny_workspace(const ConvGeom &g) {
     if (is_dense_geom(g))
         return (skinny_supported(g, 0, true) && g.C >= kStreamMinK) ? (size_t)stream_fwd_blocks(g) * g.B * g.K * sizeof(float) : 0;
+    if (pointwise_shape_ok(g)) return (size_t)kPointwiseBlocks * ((size_t)g.C + 1) * g.K * sizeof(float);
     if (small_wgrad_ok(g, true)) return (size_t)kWgradBlocks * kWgradRegs * sizeof(float);
     return 0;
 }
@@ -558,6 +679,22 @@ static int pixel_grid(long long pixels) {
 int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, void *ws,
                size_t ws_bytes, cudaStream_t s) {
     if (act == FNET_ACT_SOFTMAX) act = FNET_ACT_NONE;      // the caller runs the softmax pass
+    if (pointwise_shape_ok(g)) {
+        const int M = (int)((long long)g.B * g.H * g.W);
+        const size_t smem = (size_t)g.C * g.K * sizeof(float);
+        const bool narrow = (g.C >> 2) <= 64;                // <= 256 channels: 16 lanes per pixel keep every lane busy
+        const int per_block = narrow ? 16 : 8;
+        long long blocks = ceil_div<long long>(M, per_block);
+        if (blocks > (long long)kNumSMs * 16) blocks = (long long)kNumSMs * 16;
+#define FNET_PW_FWD(K_)                                                                                                              \
+    case K_:                                                                                                                         \
+        if (narrow) launch_pdl(pointwise_fwd_kernel<K_, 16>, dim3((unsigned)blocks), dim3(256), smem, s, M, g.C, act, x, w, bias, y); \
+        else launch_pdl(pointwise_fwd_kernel<K_, 32>, dim3((unsigned)blocks), dim3(256), smem, s, M, g.C, act, x, w, bias, y);        \
+        break;
+        switch (g.K) { FNET_PW_FWD(1) FNET_PW_FWD(2) FNET_PW_FWD(3) FNET_PW_FWD(4) FNET_PW_FWD(5) FNET_PW_FWD(6) FNET_PW_FWD(7) default: FNET_PW_FWD(8) }
+#undef FNET_PW_FWD
+        return check_launch("conv2d_fwd[pointwise]");
+    }
     if (is_dense_geom(g) && g.C >= kStreamMinK) {
         int blocks = stream_fwd_blocks(g);
         size_t need = (size_t)blocks * g.B * g.K * sizeof(float);
@@ -612,6 +749,26 @@ int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, 
 
 int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes,
                  cudaStream_t s) {
+    if (pointwise_shape_ok(g)) {
+        const int M = (int)((long long)g.B * g.H * g.W), quads = g.C >> 2, groups = 256 / quads;
+        const int total = (g.C + 1) * g.K;                   // the kernel always produces the bias row
+        long long blocks = ceil_div<long long>(M, groups);
+        if (blocks > kPointwiseBlocks) blocks = kPointwiseBlocks;
+        const size_t need = (size_t)blocks * total * sizeof(float);
+        if (!ws || ws_bytes < need) {
+            set_error("conv2d_bwd_filter[pointwise]: workspace of %zu bytes needed, %zu given", need, ws_bytes);
+            return FNET_ERR_WORKSPACE;
+        }
+        float *partial = reinterpret_cast<float *>(ws);
+        const size_t smem = ((size_t)groups * quads * 4 * g.K + (size_t)groups * g.K) * sizeof(float);
+#define FNET_PW_WGRAD(K_) case K_: launch_pdl(pointwise_wgrad_kernel<K_>, dim3((unsigned)blocks), dim3(256), smem, s, M, g.C, x, dz, partial); break;
+        switch (g.K) { FNET_PW_WGRAD(1) FNET_PW_WGRAD(2) FNET_PW_WGRAD(3) FNET_PW_WGRAD(4) FNET_PW_WGRAD(5) FNET_PW_WGRAD(6) FNET_PW_WGRAD(7) default: FNET_PW_WGRAD(8) }
+#undef FNET_PW_WGRAD
+        int rc = check_launch("conv2d_bwd_filter[pointwise]");
+        if (rc) return rc;
+        launch_pdl(conv_small_wgrad_reduce_kernel, dim3((unsigned)ceil_div<int>(total, 8)), dim3(256), 0, s, (int)blocks, g.C, g.K, total, partial, dw, dbias);
+        return check_launch("conv2d_bwd_filter[pointwise]");
+    }
     if (is_dense_geom(g) && g.C >= kStreamMinK) {
         unsigned blocks = (unsigned)ceil_div<long long>(g.C, 256);
 #define FNET_CALL(NM) launch_pdl(dense_stream_wgrad_kernel<NM>, dim3(blocks), dim3(256), 0, s, g.B, g.C, g.K, x, dz, dw, dbias)

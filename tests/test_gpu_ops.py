@@ -86,7 +86,9 @@ CONV_CASES = [
     ((64, 32, 32, 8), (3, 3), 64, (2, 2), "same", (1, 1), "relu"),      # col2im dgrad with stride 2
     ((48, 20, 20, 4), (3, 3), 100, (1, 1), "same", (2, 2), None),       # col2im dgrad with dilation 2
     ((20, 16, 16, 192), (1, 1), 3, (1, 1), "same", (1, 1), None),       # "Reg_" 192 -> 3 at size: pointwise data gradient
-    ((17, 16, 16, 36), (1, 1), 8, (1, 1), "valid", (1, 1), "relu"),     # pointwise data gradient, 8 output channels
+    ((17, 16, 16, 36), (1, 1), 8, (1, 1), "valid", (1, 1), "relu"),     # pointwise kernels, 8 output channels, ragged pixel groups
+    ((5, 30, 30, 260), (1, 1), 5, (1, 1), "same", (1, 1), "tanh"),      # pointwise kernels, > 256 channels (32 lanes per pixel)
+    ((33, 11, 13, 132), (1, 1), 1, (1, 1), "same", (1, 1), "sigmoid"),  # a single output channel, 33 channel groups
 ]
 
 
