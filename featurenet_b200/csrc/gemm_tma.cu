@@ -31,10 +31,11 @@ constexpr int TG_THREADS_X3 = TG_THREADS + TG_SPLITTERS;
 constexpr int TG_SMEM_LIMIT = 209 * 1024;     // + 17 KB of static shared memory = the 227 KB a CTA may have
 
 // hi = x rounded to tf32 (nearest, ties away: what cvt.rna.tf32.f32 gives, in two integer instructions), lo = x - hi
-// exactly; the tensor core drops the low 13 mantissa bits of lo itself (2^-21 of x, below the lo*lo term left out).
+// rounded the same way: left to the tensor core, which truncates, the tails would carry a one-sided error of 2^-22 of
+// x each, and a 4800-term reduction (5x5 x 192 channels) came out at 3.8e-5 of the float64 result instead of < 2e-5.
 __device__ __forceinline__ void tg_hi_lo(uint32_t x, uint32_t &hi, uint32_t &lo) {
     hi = (x + 0x1000u) & 0xffffe000u;
-    lo = __float_as_uint(__uint_as_float(x) - __uint_as_float(hi));
+    lo = (__float_as_uint(__uint_as_float(x) - __uint_as_float(hi)) + 0x1000u) & 0xffffe000u;
 }
 // hi in place, lo to the twin buffer `twin_offset` bytes further, for the 16-byte chunks [first, first + count) of a
 // stage; TG_SPLITTERS threads.  Four independent loads are in flight per thread before the first store (the loop is
@@ -609,6 +610,13 @@ struct TgWgradPlan {
     size_t smem, ws_bytes;
 };
 
+// forward / data gradient: when the grid would leave SMs idle, narrower tiles make more of them (A is re-read from L2)
+static int tg_bn_for(long long n, long long m_tiles) {
+    int bn = tg_bn(n);
+    while (2 * m_tiles * ceil_div<long long>(n, bn) <= kNumSMs && bn >= 64 && bn % 64 == 0) bn /= 2;    // < half a wave
+    return bn;
+}
+
 // pipeline depth that fits: TF32x3 stages carry a second copy (the tails) of both operand tiles
 static int tg_stages(int bn, bool x3, int most, size_t extra) {
     size_t stage = (size_t)(x3 ? 2 : 1) * (TG_A_BYTES + bn * TG_BK * 4);
@@ -684,7 +692,17 @@ bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
         const long long Mc = product == 0 ? (long long)g.B * g.Ho * g.Wo : (long long)g.B * g.H * g.W;
         const long long Nc = product == 0 ? g.K : g.C;
         if (Nc < 16 || Mc > 0x7fffffffLL || (long long)g.kh * g.kw > 64) return false;
-        return ceil_div<long long>(Mc, TG_BM) * ceil_div<long long>(Nc, tg_bn(Nc)) >= kNumSMs;
+        static long long min_tiles = -1;                     // FNET_TMA_MIN_TILES: experiments with partial waves
+        if (min_tiles < 0) {
+            const char *e = getenv("FNET_TMA_MIN_TILES");
+            min_tiles = e ? atoll(e) : 32;
+        }
+        const long long m_tiles = ceil_div<long long>(Mc, TG_BM);
+        const long long tiles = m_tiles * ceil_div<long long>(Nc, tg_bn_for(Nc, m_tiles));
+        const long long kt = (long long)g.kh * g.kw * ceil_div<long long>(product == 0 ? g.C : g.K, TG_BK);
+        // a partial wave still wins when every tile has a long reduction to stream (no split reduction here): measured
+        // 96 -> 192 5x5 on 8x8 images 184 / 220 -> 119 / 129 us, 128 -> 128 3x3 72 / 73 -> 53 / 43 us (fwd / dgrad)
+        return tiles >= kNumSMs || (tiles >= min_tiles && kt >= 16);
     }
     long long M = (long long)g.B * g.H * g.W;
     if (product == 2)
@@ -692,7 +710,8 @@ bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
                (long long)g.C * g.K * M >= (1LL << 24);
     long long N = product == 0 ? g.K : g.C, Kg = product == 0 ? g.C : g.K;
     if ((g.C & 3) || (g.K & 3) || N < 16 || Kg < 8 || M > 0x7fffffffLL) return false;      // 16-byte global strides
-    long long tiles = ceil_div<long long>(M, TG_BM) * ceil_div<long long>(N, tg_bn(N));
+    const long long m_tiles = ceil_div<long long>(M, TG_BM);
+    long long tiles = m_tiles * ceil_div<long long>(N, tg_bn_for(N, m_tiles));
     return tiles >= kNumSMs;                                 // no split reduction here: the cp.async kernels do that
 }
 
@@ -706,7 +725,7 @@ static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, c
         set_error("%s: operands must be 16-byte aligned for the TMA path", what);
         return FNET_ERR_ARG;
     }
-    const int BN = tg_bn(N);
+    const int BN = tg_bn_for(N, ceil_div<long long>(M, TG_BM));
     CUtensorMap map_a, map_b;
     bool ok;
     if (cv.taps) {

@@ -2,7 +2,8 @@
 
 tf32 operands carry 10 mantissa bits with fp32 accumulation, so the stated tolerance for FNET_MATH_TF32
 is 5e-3 relative (max-norm) per layer.  FNET_MATH_TF32X3 splits every operand into a tf32 head and tail
-(three MMAs per product) and has to meet the bar of the fp32 path: asserted at 2e-5, stated 1e-4.
+(three MMAs per product) and has to meet the bar of the fp32 path: asserted at 2e-5 (1e-4, the stated bar, for
+reductions longer than 2048 terms).
 """
 import ctypes as C
 
@@ -35,6 +36,7 @@ TC_CONV_CASES = [
     ((301, 8, 8, 64), (3, 3), 64, (1, 1)),      # whole 8 x 8 images, two per tile, the last tile half outside the batch
     ((40, 32, 32, 12), (5, 5), 120, (1, 1)),    # 25 taps of 12 channels; the data gradient goes through col2im
     ((38, 32, 32, 20), (2, 2), 36, (1, 1)),     # even kernel: SAME pads only bottom / right
+    ((66, 8, 8, 96), (5, 5), 192, (1, 1)),      # a partial wave (33 row tiles, narrowed to 96-column tiles), 75 k-tiles each
 ]
 
 
@@ -46,6 +48,11 @@ MODES = [("tf32", TF32_TOL), ("tf32x3", 2e-5), ("auto", 2e-5)]     # auto = fp32
 def test_conv2d_tf32_tensor_core(L, case_id, math, tol):
     from featurenet_b200 import lib as fl
     xs, k, kout, s = TC_CONV_CASES[case_id]
+    # the tensor core's fp32 accumulation is not round-to-nearest, so the error of the split products grows with the
+    # length of the reduction: 2e-5 holds up to ~2000 terms (all of FeatureNet's usual layers); the 4800-term data
+    # gradient of the 5x5 x 192 case measures 3.8e-5 and is held to the stated bar of the fp32 mode, 1e-4
+    if k[0] * k[1] * max(xs[3], kout) > 2048:
+        tol = max(tol, 1e-4)
     rng = np.random.default_rng(2000 + case_id)
     x = rng.standard_normal(xs)
     w = rng.standard_normal(k + (xs[3], kout)) / np.sqrt(k[0] * k[1] * xs[3])
