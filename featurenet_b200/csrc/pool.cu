@@ -56,6 +56,60 @@ __global__ void __launch_bounds__(256) pool_fwd_kernel(fnet_pool2d_desc d, const
     }
 }
 
+// Four channels per thread (channels % 4 == 0, 16-byte aligned tensors): the index decode and the window loop are
+// paid once per 16 bytes instead of once per 4.  The scalar kernel above spends ~250 instructions per element and is
+// issue-bound at a tenth of the HBM rate (2x2 stride-1 SAME pooling of 128 x 32 x 32 x 32: 65 us for 38 MB).
+__global__ void __launch_bounds__(256) pool_fwd_vec4_kernel(fnet_pool2d_desc d, const float4 *__restrict__ x,
+                                                            float4 *__restrict__ y, uchar4 *__restrict__ argmax) {
+    pdl_prologue();
+    const int quads = d.channels >> 2;
+    const int total = d.batch * d.out_h * d.out_w * quads;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        int q = i % quads, t = i / quads;
+        int wo = t % d.out_w;
+        t /= d.out_w;
+        int ho = t % d.out_h, b = t / d.out_h;
+        const int h0 = ho * d.stride_h - d.pad_top, w0 = wo * d.stride_w - d.pad_left;
+        const float4 *img = x + (int64_t)b * d.in_h * d.in_w * quads + q;
+        if (d.kind == FNET_POOL_MAX) {
+            float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+            uchar4 arg = make_uchar4(0, 0, 0, 0);
+            for (int r = 0; r < d.kh; ++r) {
+                const int h = h0 + r;
+                if ((unsigned)h >= (unsigned)d.in_h) continue;
+                for (int s = 0; s < d.kw; ++s) {
+                    const int w = w0 + s;
+                    if ((unsigned)w >= (unsigned)d.in_w) continue;
+                    const float4 v = __ldg(img + (h * d.in_w + w) * quads);
+                    const unsigned char tap = (unsigned char)(r * d.kw + s);
+                    if (v.x > best.x) { best.x = v.x; arg.x = tap; }       // strict: first maximum wins
+                    if (v.y > best.y) { best.y = v.y; arg.y = tap; }
+                    if (v.z > best.z) { best.z = v.z; arg.z = tap; }
+                    if (v.w > best.w) { best.w = v.w; arg.w = tap; }
+                }
+            }
+            y[i] = best;
+            if (argmax) argmax[i] = arg;
+        } else {
+            float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+            int cnt = 0;
+            for (int r = 0; r < d.kh; ++r) {
+                const int h = h0 + r;
+                if ((unsigned)h >= (unsigned)d.in_h) continue;
+                for (int s = 0; s < d.kw; ++s) {
+                    const int w = w0 + s;
+                    if ((unsigned)w >= (unsigned)d.in_w) continue;
+                    const float4 v = __ldg(img + (h * d.in_w + w) * quads);
+                    sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+                    ++cnt;
+                }
+            }
+            const float n = (float)cnt;
+            y[i] = make_float4(sum.x / n, sum.y / n, sum.z / n, sum.w / n);
+        }
+    }
+}
+
 __device__ __forceinline__ int taps_in_bounds(int o, int stride, int pad, int k, int extent) {
     int lo = o * stride - pad, hi = lo + k;
     if (lo < 0) lo = 0;
@@ -108,6 +162,53 @@ __global__ void __launch_bounds__(256) pool_bwd_kernel(fnet_pool2d_desc d, const
             }
         }
         dx[i] = accumulate ? dx[i] + g : g;
+    }
+}
+
+__global__ void __launch_bounds__(256) pool_bwd_vec4_kernel(fnet_pool2d_desc d, const float4 *__restrict__ dy,
+                                                            const uchar4 *__restrict__ argmax, float4 *__restrict__ dx,
+                                                            int accumulate) {
+    pdl_prologue();
+    const int quads = d.channels >> 2;
+    const int total = d.batch * d.in_h * d.in_w * quads;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        int q = i % quads, t = i / quads;
+        int w = t % d.in_w;
+        t /= d.in_w;
+        int h = t % d.in_h, b = t / d.in_h;
+        const int out_img = b * d.out_h * d.out_w;
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < d.kh; ++r) {
+            const int hh = h + d.pad_top - r;
+            if (hh < 0) break;
+            const int ho = pool_exact_div(hh, d.stride_h, d.out_h);
+            if (ho < 0) continue;
+            for (int s = 0; s < d.kw; ++s) {
+                const int ww = w + d.pad_left - s;
+                if (ww < 0) break;
+                const int wo = pool_exact_div(ww, d.stride_w, d.out_w);
+                if (wo < 0) continue;
+                const int o = (out_img + ho * d.out_w + wo) * quads + q;
+                const float4 v = __ldg(dy + o);
+                if (d.kind == FNET_POOL_MAX) {
+                    const uchar4 a = argmax[o];
+                    const unsigned char tap = (unsigned char)(r * d.kw + s);
+                    if (a.x == tap) g.x += v.x;
+                    if (a.y == tap) g.y += v.y;
+                    if (a.z == tap) g.z += v.z;
+                    if (a.w == tap) g.w += v.w;
+                } else {
+                    const float n = (float)(taps_in_bounds(ho, d.stride_h, d.pad_top, d.kh, d.in_h) *
+                                            taps_in_bounds(wo, d.stride_w, d.pad_left, d.kw, d.in_w));
+                    g.x += v.x / n; g.y += v.y / n; g.z += v.z / n; g.w += v.w / n;
+                }
+            }
+        }
+        if (accumulate) {
+            const float4 old = dx[i];
+            g.x += old.x; g.y += old.y; g.z += old.z; g.w += old.w;
+        }
+        dx[i] = g;
     }
 }
 
@@ -168,7 +269,12 @@ int fnet_pool2d_fwd(const fnet_pool2d_desc *d, const float *x, float *y, uint8_t
     int64_t total = (int64_t)d->batch * d->out_h * d->out_w * d->channels;
     if (total == 0) return FNET_OK;
     int64_t in_total = (int64_t)d->batch * d->in_h * d->in_w * d->channels;
-    if (total < 0x7fffffffLL - (1 << 26) && in_total < 0x7fffffffLL)      // the grid-stride increment must not overflow either
+    const bool aligned = !((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) &&
+                         !(reinterpret_cast<uintptr_t>(argmax) & 3);
+    if (!(d->channels & 3) && aligned && total < 0x7fffffffLL - (1 << 26) && in_total < 0x7fffffffLL)
+        launch_pdl(pool_fwd_vec4_kernel, dim3(stream_grid(total / 4, 256)), dim3(256), 0, as_stream(stream), *d,
+                   reinterpret_cast<const float4 *>(x), reinterpret_cast<float4 *>(y), reinterpret_cast<uchar4 *>(argmax));
+    else if (total < 0x7fffffffLL - (1 << 26) && in_total < 0x7fffffffLL)      // the grid-stride increment must not overflow either
         launch_pdl(pool_fwd_kernel<int>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, x, y, argmax);
     else
         launch_pdl(pool_fwd_kernel<int64_t>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, x, y, argmax);
@@ -183,7 +289,13 @@ int fnet_pool2d_bwd(const fnet_pool2d_desc *d, const float *dy, const uint8_t *a
     FNET_REQUIRE(d->kind != FNET_POOL_MAX || argmax != nullptr, "fnet_pool2d_bwd: max pooling needs the argmax of the forward");
     int64_t total = (int64_t)d->batch * d->in_h * d->in_w * d->channels;
     if (total == 0) return FNET_OK;
-    if (total < 0x7fffffffLL - (1 << 26))
+    const int64_t out_total = (int64_t)d->batch * d->out_h * d->out_w * d->channels;
+    const bool aligned = !((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx)) & 15) &&
+                         !(reinterpret_cast<uintptr_t>(argmax) & 3);
+    if (!(d->channels & 3) && aligned && total < 0x7fffffffLL - (1 << 26) && out_total < 0x7fffffffLL)
+        launch_pdl(pool_bwd_vec4_kernel, dim3(stream_grid(total / 4, 256)), dim3(256), 0, as_stream(stream), *d,
+                   reinterpret_cast<const float4 *>(dy), reinterpret_cast<const uchar4 *>(argmax), reinterpret_cast<float4 *>(dx), accumulate);
+    else if (total < 0x7fffffffLL - (1 << 26))
         launch_pdl(pool_bwd_kernel<int>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, dy, argmax, dx, accumulate);
     else
         launch_pdl(pool_bwd_kernel<int64_t>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, dy, argmax, dx, accumulate);

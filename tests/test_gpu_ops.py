@@ -209,7 +209,10 @@ def test_depthwise_forward_backward(L, xs, k, s, act):
 
 @pytest.mark.parametrize("xs,k,s", [((3, 28, 28, 6), (2, 2), (1, 1)), ((2, 28, 28, 12), (2, 2), (2, 2)),
                                     ((2, 9, 11, 5), (3, 3), (2, 2)), ((2, 7, 7, 3), (3, 3), (3, 3)),
-                                    ((2, 8, 8, 4), (1, 1), (2, 2)), ((1, 5, 5, 70), (3, 2), (1, 2))])
+                                    ((2, 8, 8, 4), (1, 1), (2, 2)), ((1, 5, 5, 70), (3, 2), (1, 2)),
+                                    # channels % 4 == 0: the four-channels-per-thread kernels
+                                    ((5, 16, 16, 32), (2, 2), (1, 1)), ((3, 10, 14, 24), (3, 3), (2, 2)),
+                                    ((2, 6, 5, 8), (3, 3), (1, 1))])
 def test_pooling(L, xs, k, s):
     from featurenet_b200 import lib as fl
     rng = np.random.default_rng(xs[1] + 31 * k[0])
@@ -230,7 +233,10 @@ def test_pooling(L, xs, k, s):
             assert np.array_equal(host(yd), y)
             torch.cuda.synchronize()
             assert np.array_equal(argd.cpu().numpy(), arg.astype(np.uint8))        # bit-exact tap index
-            assert_close(host(dxd), ops.maxpool_bwd(xs, arg, dy, k, s, "same"), what="maxpool bwd")
+            want = ops.maxpool_bwd(xs, arg, dy, k, s, "same")
+            assert_close(host(dxd), want, what="maxpool bwd")
+            L.fnet_pool2d_bwd(desc, ptr(dev(dy)), ptr(argd), ptr(dxd), 1, None)       # second gradient piece: accumulate
+            assert_close(host(dxd), 2 * want, what="maxpool bwd accumulate")
         else:
             assert_close(host(yd), ops.avgpool_fwd(x, k, s, "same"), what="avgpool fwd")
             assert_close(host(dxd), ops.avgpool_bwd(xs, dy, k, s, "same"), what="avgpool bwd")
