@@ -39,20 +39,48 @@ __device__ __forceinline__ int64_t bn_index(const BnShape &s, int a, int o0, uns
     unsigned j = e - q * (unsigned)s.inner;
     return ((int64_t)(o0 + q) * s.a + a) * s.inner + j;
 }
+// the same in units of V floats (V = 4: inner % 4 == 0 and 16-byte aligned tensors; one index decode per float4 --
+// the scalar kernels are issue-bound at 1 TB/s)
+template <int V>
+__device__ __forceinline__ int64_t bn_index_v(const BnShape &s, int a, int o0, unsigned e) {
+    const unsigned inner_v = (unsigned)s.inner / V;
+    unsigned q = e / inner_v;
+    unsigned j = e - q * inner_v;
+    return ((int64_t)(o0 + q) * s.a + a) * inner_v + j;
+}
+template <int V> struct BnVec;
+template <> struct BnVec<1> {
+    typedef float T;
+    static __device__ __forceinline__ void get(const float &v, float (&o)[1]) { o[0] = v; }
+    static __device__ __forceinline__ float make(const float (&o)[1]) { return o[0]; }
+};
+template <> struct BnVec<4> {
+    typedef float4 T;
+    static __device__ __forceinline__ void get(const float4 &v, float (&o)[4]) { o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
+    static __device__ __forceinline__ float4 make(const float (&o)[4]) { return make_float4(o[0], o[1], o[2], o[3]); }
+};
 
+template <int V>
 __global__ void __launch_bounds__(256) bn_stats_partial_kernel(BnShape s, const float *__restrict__ x,
                                                                float *__restrict__ partial) {
     pdl_prologue();
+    typedef typename BnVec<V>::T T;
     __shared__ float red[32];
     int a = blockIdx.x, part = blockIdx.y;
     int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
     float shift = __ldg(x + (int64_t)a * s.inner);
-    int64_t count = (int64_t)(o1 - o0) * s.inner;
+    int64_t count = (int64_t)(o1 - o0) * (s.inner / V);
     float s1 = 0.f, s2 = 0.f;
+    const T *xv = reinterpret_cast<const T *>(x);
     for (unsigned e = threadIdx.x; e < (unsigned)count; e += blockDim.x) {
-        float v = __ldg(x + bn_index(s, a, o0, e)) - shift;
-        s1 += v;
-        s2 = fmaf(v, v, s2);
+        float f[V];
+        BnVec<V>::get(__ldg(xv + bn_index_v<V>(s, a, o0, e)), f);
+#pragma unroll
+        for (int u = 0; u < V; ++u) {
+            float v = f[u] - shift;
+            s1 += v;
+            s2 = fmaf(v, v, s2);
+        }
     }
     s1 = block_sum(s1, red);
     s2 = block_sum(s2, red);
@@ -62,6 +90,7 @@ __global__ void __launch_bounds__(256) bn_stats_partial_kernel(BnShape s, const 
     }
 }
 
+template <int V>
 __global__ void __launch_bounds__(256) bn_normalize_train_kernel(BnShape s, float eps, float momentum,
                                                                  const float *__restrict__ x,
                                                                  const float *__restrict__ gamma,
@@ -100,10 +129,17 @@ __global__ void __launch_bounds__(256) bn_normalize_train_kernel(BnShape s, floa
     float inv = stat[1] * __ldg(gamma + a);
     float off = __ldg(beta + a) - stat[0] * inv;
     int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
-    int64_t count = (int64_t)(o1 - o0) * s.inner;
+    typedef typename BnVec<V>::T T;
+    int64_t count = (int64_t)(o1 - o0) * (s.inner / V);
+    const T *xv = reinterpret_cast<const T *>(x);
+    T *yv = reinterpret_cast<T *>(y);
     for (unsigned e = threadIdx.x; e < (unsigned)count; e += blockDim.x) {
-        int64_t at = bn_index(s, a, o0, e);
-        y[at] = fmaf(__ldg(x + at), inv, off);
+        int64_t at = bn_index_v<V>(s, a, o0, e);
+        float f[V];
+        BnVec<V>::get(__ldg(xv + at), f);
+#pragma unroll
+        for (int u = 0; u < V; ++u) f[u] = fmaf(f[u], inv, off);
+        yv[at] = BnVec<V>::make(f);
     }
 }
 
@@ -137,6 +173,7 @@ __global__ void __launch_bounds__(256) bn_infer_bwd_kernel(int64_t total, int a_
     }
 }
 
+template <int V>
 __global__ void __launch_bounds__(256) bn_bwd_partial_kernel(BnShape s, const float *__restrict__ x,
                                                              const float *__restrict__ dy,
                                                              const float *__restrict__ save_mean,
@@ -147,13 +184,20 @@ __global__ void __launch_bounds__(256) bn_bwd_partial_kernel(BnShape s, const fl
     int a = blockIdx.x, part = blockIdx.y;
     int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
     float mean = __ldg(save_mean + a), rstd = __ldg(save_rstd + a);
-    int64_t count = (int64_t)(o1 - o0) * s.inner;
+    typedef typename BnVec<V>::T T;
+    int64_t count = (int64_t)(o1 - o0) * (s.inner / V);
     float sb = 0.f, sg = 0.f;
+    const T *xv = reinterpret_cast<const T *>(x), *dyv = reinterpret_cast<const T *>(dy);
     for (unsigned e = threadIdx.x; e < (unsigned)count; e += blockDim.x) {
-        int64_t at = bn_index(s, a, o0, e);
-        float g = __ldg(dy + at);
-        sb += g;
-        sg = fmaf(g, (__ldg(x + at) - mean) * rstd, sg);
+        int64_t at = bn_index_v<V>(s, a, o0, e);
+        float g[V], f[V];
+        BnVec<V>::get(__ldg(dyv + at), g);
+        BnVec<V>::get(__ldg(xv + at), f);
+#pragma unroll
+        for (int u = 0; u < V; ++u) {
+            sb += g[u];
+            sg = fmaf(g[u], (f[u] - mean) * rstd, sg);
+        }
     }
     sb = block_sum(sb, red);
     sg = block_sum(sg, red);
@@ -163,6 +207,7 @@ __global__ void __launch_bounds__(256) bn_bwd_partial_kernel(BnShape s, const fl
     }
 }
 
+template <int V>
 __global__ void __launch_bounds__(256) bn_bwd_dx_kernel(BnShape s, const float *__restrict__ x,
                                                         const float *__restrict__ dy, const float *__restrict__ gamma,
                                                         const float *__restrict__ save_mean,
@@ -192,12 +237,23 @@ __global__ void __launch_bounds__(256) bn_bwd_dx_kernel(BnShape s, const float *
     float k = __ldg(gamma + a) * rstd / n;
     float sb = sums[0], sg = sums[1];
     int o0 = part * s.outer_per_split, o1 = min(s.outer, o0 + s.outer_per_split);
-    int64_t count = (int64_t)(o1 - o0) * s.inner;
+    typedef typename BnVec<V>::T T;
+    int64_t count = (int64_t)(o1 - o0) * (s.inner / V);
+    const T *xv = reinterpret_cast<const T *>(x), *dyv = reinterpret_cast<const T *>(dy);
+    T *dxv = reinterpret_cast<T *>(dx);
     for (unsigned e = threadIdx.x; e < (unsigned)count; e += blockDim.x) {
-        int64_t at = bn_index(s, a, o0, e);
-        float xhat = (__ldg(x + at) - mean) * rstd;
-        float v = k * (n * __ldg(dy + at) - sb - xhat * sg);
-        dx[at] = accumulate ? dx[at] + v : v;
+        int64_t at = bn_index_v<V>(s, a, o0, e);
+        float f[V], g[V], o[V];
+        BnVec<V>::get(__ldg(xv + at), f);
+        BnVec<V>::get(__ldg(dyv + at), g);
+        if (accumulate) BnVec<V>::get(dxv[at], o);
+#pragma unroll
+        for (int u = 0; u < V; ++u) {
+            float xhat = (f[u] - mean) * rstd;
+            float v = k * (n * g[u] - sb - xhat * sg);
+            o[u] = accumulate ? o[u] + v : v;
+        }
+        dxv[at] = BnVec<V>::make(o);
     }
 }
 
@@ -222,11 +278,17 @@ int fnet_bn_fwd_train(int32_t outer, int32_t a, int32_t inner, float eps, float 
     BnShape s = bn_shape(outer, a, inner);
     dim3 grid(a, s.splits);
     float *partial = reinterpret_cast<float *>(ws);
-    launch_pdl(bn_stats_partial_kernel, dim3(grid), dim3(256), 0, as_stream(stream), s, x, partial);
+    const bool vec = !(inner & 3) && !((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15);
+    if (vec) launch_pdl(bn_stats_partial_kernel<4>, dim3(grid), dim3(256), 0, as_stream(stream), s, x, partial);
+    else launch_pdl(bn_stats_partial_kernel<1>, dim3(grid), dim3(256), 0, as_stream(stream), s, x, partial);
     int rc = check_launch("fnet_bn_fwd_train");
     if (rc) return rc;
-    launch_pdl(bn_normalize_train_kernel, dim3(grid), dim3(256), 0, as_stream(stream), s, eps, momentum, x, gamma, beta, partial, y,
-                                                                   save_mean, save_rstd, moving_mean, moving_var);
+    if (vec)
+        launch_pdl(bn_normalize_train_kernel<4>, dim3(grid), dim3(256), 0, as_stream(stream), s, eps, momentum, x, gamma, beta, partial, y,
+                                                                          save_mean, save_rstd, moving_mean, moving_var);
+    else
+        launch_pdl(bn_normalize_train_kernel<1>, dim3(grid), dim3(256), 0, as_stream(stream), s, eps, momentum, x, gamma, beta, partial, y,
+                                                                          save_mean, save_rstd, moving_mean, moving_var);
     return check_launch("fnet_bn_fwd_train");
 }
 
@@ -264,11 +326,18 @@ int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const f
     BnShape s = bn_shape(outer, a, inner);
     dim3 grid(a, s.splits);
     float *partial = reinterpret_cast<float *>(ws);
-    launch_pdl(bn_bwd_partial_kernel, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, save_mean, save_rstd, partial);
+    const bool vec = !(inner & 3) &&
+                     !((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx)) & 15);
+    if (vec) launch_pdl(bn_bwd_partial_kernel<4>, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, save_mean, save_rstd, partial);
+    else launch_pdl(bn_bwd_partial_kernel<1>, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, save_mean, save_rstd, partial);
     int rc = check_launch("fnet_bn_bwd");
     if (rc) return rc;
-    launch_pdl(bn_bwd_dx_kernel, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, gamma, save_mean, save_rstd, partial, dx, dgamma,
-                                                          dbeta, accumulate);
+    if (vec)
+        launch_pdl(bn_bwd_dx_kernel<4>, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, gamma, save_mean, save_rstd, partial, dx,
+                                                                 dgamma, dbeta, accumulate);
+    else
+        launch_pdl(bn_bwd_dx_kernel<1>, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, gamma, save_mean, save_rstd, partial, dx,
+                                                                 dgamma, dbeta, accumulate);
     return check_launch("fnet_bn_bwd");
 }
 
