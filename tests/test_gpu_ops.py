@@ -252,7 +252,8 @@ def test_global_average_pooling(L):
     assert_close(host(dxd), 1.0 + ops.gap_bwd(x.shape, dy))
 
 
-@pytest.mark.parametrize("shape,axis", [((16, 32, 32, 24), 1), ((128, 14, 14, 12), 1), ((3, 5, 2, 2), 1), ((64, 100), 1)])
+@pytest.mark.parametrize("shape,axis", [((16, 32, 32, 24), 1), ((128, 14, 14, 12), 1), ((3, 5, 2, 2), 1), ((64, 100), 1),
+                                        ((4, 6, 5, 3), 1), ((9, 7, 3, 10), 1)])     # inner extents 15 and 30: the scalar kernels
 def test_batchnorm_axis1(L, shape, axis):
     rng = np.random.default_rng(shape[0])
     x = rng.standard_normal(shape) * 2.0 + 3.0             # mean >> std: the single-pass variance must survive
