@@ -282,7 +282,7 @@ def measure_workload(workload, args, torch, dist, world, device_index, full=True
     out["e2e"] = {"value": world * k * BATCH / streamed_s, "unit": "images/s",
                   "h2d_bytes_per_step": int(BATCH * (np.prod(x_train.shape[1:]) + y_train.shape[1]) * 4),
                   "d2h_bytes_per_step": 16, "last_loss": float(hist.history["loss"][-1]),
-                  "api": "Network.fit_generator on pinned host batches (2-slot pipelined feed)",
+                  "api": "Network.fit_generator on pinned host batches (3-slot pipelined feed)",
                   "train_on_batch_value": world * k * BATCH / blocking_s,
                   "train_on_batch_note": "same steps through the blocking per-step call (no overlap of upload and compute)"}
 

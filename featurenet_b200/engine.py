@@ -1111,7 +1111,8 @@ class Engine(object):
                         validation_data=validation_data, callbacks=callbacks, verbose=verbose, augment=generator, **kw)
 
     # ------------------------------------------------------------------ pipelined host feed
-    RING_SLOTS = 2
+    _ring_kinds = ["train_ring%d" % k for k in range(8)]
+    RING_SLOTS = 3      # two are enough to overlap upload and compute; the third absorbs host-side jitter
 
     def _ring_setup(self, batch):
         """Two slots of (device batch, pinned staging batch, pinned result, two events) and a copy stream."""
@@ -1140,6 +1141,13 @@ class Engine(object):
             for ev in ring["slot_event"] + ring["copied_event"]:
                 ev.record(self.stream)                     # materialises the cudaEvent_t handle
         self.stream.synchronize()
+        # raw addresses per slot, gathered once: the per-step call must cost the host less than a step costs the GPU
+        ring["ptrs"] = [(ring["x"][k].data_ptr(), ring["x_stage"][k].data_ptr(), ring["y"][k].data_ptr(),
+                         ring["y_stage"][k].data_ptr(), ring["result"][k].data_ptr(), ring["slot_event"][k].cuda_event,
+                         ring["copied_event"][k].cuda_event) for k in range(n)]
+        ring["fixed"] = (self.metrics.data_ptr(), ring["prev"].ctypes.data, ring["copy_stream"].cuda_stream,
+                         self.stream.cuda_stream)
+        ring["prev64"] = ring["prev"].view(np.float64)
         self.ring = ring
         return ring
 
@@ -1147,7 +1155,9 @@ class Engine(object):
         """Enqueue one optimisation step on a host batch without waiting for it.  Returns the running
         (loss_sum, correct) as they stood after the step that used this slot before (RING_SLOTS steps ago)."""
         b = int(x.shape[0])
-        ring = self._ring_setup(b)
+        ring = getattr(self, "ring", None)
+        if ring is None or b > ring["capacity"] or ring["capacity"] < self.capacity:
+            ring = self._ring_setup(b)
         slot = step % self.RING_SLOTS
         xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
         yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
@@ -1156,18 +1166,19 @@ class Engine(object):
         if tuple(xt.shape[1:]) != tuple(self.shape[0]) or tuple(yt.shape) != (b, self.n_out):
             raise ValueError("batch of shape %s / %s does not fit the model" % (tuple(xt.shape), tuple(yt.shape)))
         pinned = xt.is_pinned() and yt.is_pinned()
-        graph = self._graph("train_ring%d" % slot, b)      # one captured step per (slot, batch size)
+        graph = self.graphs.get((self._ring_kinds[slot], b))
+        if graph is None:
+            graph = self._graph(self._ring_kinds[slot], b)     # one captured step per (slot, batch size)
         self._sync_lr()
-        keep = None if pinned else (ring["x_stage"][slot], ring["y_stage"][slot])
+        x_slot, x_stage, y_slot, y_stage, result, slot_event, copied_event = ring["ptrs"][slot]
+        metrics, prev, copy_stream, compute_stream = ring["fixed"]
         self.lib.fnet_graph_step_streamed(
-            graph, ring["x"][slot].data_ptr(), xt.data_ptr(), keep[0].data_ptr() if keep else None, xt.numel() * 4,
-            ring["y"][slot].data_ptr(), yt.data_ptr(), keep[1].data_ptr() if keep else None, yt.numel() * 4,
-            self.metrics.data_ptr(), ring["result"][slot].data_ptr(), ring["prev"].ctypes.data, 16,
-            ring["copy_stream"].cuda_stream, self.stream.cuda_stream,
-            ring["slot_event"][slot].cuda_event, ring["copied_event"][slot].cuda_event)
+            graph, x_slot, xt.data_ptr(), None if pinned else x_stage, xt.numel() * 4,
+            y_slot, yt.data_ptr(), None if pinned else y_stage, yt.numel() * 4,
+            metrics, result, prev, 16, copy_stream, compute_stream, slot_event, copied_event)
         if pinned:
             ring.setdefault("alive", {})[slot] = (xt, yt)   # the upload reads the caller's buffer until the slot's next turn
-        return float(ring["prev"].view(np.float64)[0]), int(ring["prev"][1])
+        return float(ring["prev64"][0]), int(ring["prev"][1])
 
     def _fit_stream(self, generator, steps_per_epoch, epochs, validation_data, callbacks, verbose, initial_epoch=0, **_):
         """fit_generator for host batches.  The upload of batch i+1 (copy stream) overlaps the kernels of batch i
