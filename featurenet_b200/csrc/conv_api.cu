@@ -70,6 +70,15 @@ int conv_dgrad(const ConvGeom &g, int math_in, const float *dz, const float *w, 
     return simt_conv_dgrad(g, dz, w, dx, ep, ws, ws_bytes, s);
 }
 
+// Does the data gradient's epilogue run on a tensor-core kernel (where folding act'(y) into it does not pay)?
+// Mirrors conv_dgrad's dispatch; the col2im path applies the epilogue in its scatter pass (cheap).
+static int dgrad_on_tensor_core(const ConvGeom &g, int math_in) {
+    const int math = resolve_math(g, math_in, 1);
+    if (skinny_supported(g, 1, false) || col2im_t_bytes(g)) return 0;
+    if (tma_gemm_supported(g, math, 1)) return 1;
+    return (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) ? 1 : 0;
+}
+
 int conv_wgrad(const ConvGeom &g, int math_in, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                size_t ws_bytes, cudaStream_t s) {
     const int math = resolve_math(g, math_in, 2);
@@ -147,6 +156,17 @@ int fnet_conv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const floa
     if ((rc = check_math(d->math, "fnet_conv2d_bwd_filter"))) return rc;
     FNET_REQUIRE(x && dz && dw, "fnet_conv2d_bwd_filter: null pointer");
     return conv_wgrad(g, d->math, x, dz, dw, dbias, ws, ws_bytes, as_stream(stream));
+}
+
+int fnet_conv2d_bwd_data_on_tensor_core(const fnet_conv2d_desc *d) {
+    ConvGeom g;
+    if (geom_checked(d, g, "fnet_conv2d_bwd_data_on_tensor_core") != FNET_OK) return -1;
+    return dgrad_on_tensor_core(g, d->math);
+}
+
+int fnet_dense_bwd_data_on_tensor_core(int64_t m, int64_t k, int64_t n, int math) {
+    if (check_dense(m, k, n, "fnet_dense_bwd_data_on_tensor_core") != FNET_OK || check_math(math, "fnet_dense_bwd_data_on_tensor_core")) return -1;
+    return m == 0 ? 0 : dgrad_on_tensor_core(dense_geom(m, k, n), math);
 }
 
 size_t fnet_dense_workspace_bytes(int64_t m, int64_t k, int64_t n) {

@@ -93,7 +93,8 @@ class Engine(object):
         self.overlap_wgrad = os.environ.get("FNET_NO_OVERLAP", "0") != "1"
         # folding act'(y) into the producing data gradient pays on the FFMA kernels; the tensor-core epilogues are
         # the critical path of their kernels (one tile's epilogue per main loop) and do not hide the extra loads
-        self.fuse_act_bwd = os.environ.get("FNET_NO_ACT_FUSION", "0") != "1" and self.math == fl.MATH["fp32"]
+        # (in "auto" mode the planner asks the library, per consumer layer, which kind of kernel its data gradient gets)
+        self.fuse_act_bwd = os.environ.get("FNET_NO_ACT_FUSION", "0") != "1" and self.math in (fl.MATH["fp32"], fl.MATH["auto"])
         self.nodes = list(net.layers)
         self.index = {id(n): i for i, n in enumerate(self.nodes)}
         self.src = [[self.index[id(t.node)] for t in n.inputs] for n in self.nodes]
@@ -401,6 +402,14 @@ class Engine(object):
                 raise NotImplementedError(kind)
         return ops
 
+    def _dgrad_on_tensor_core(self, i, batch):
+        """True when layer i's data gradient runs on a tensor-core kernel: its epilogue is that kernel's critical path,
+        so the activation derivative of the producer stays a separate pass there."""
+        if self.nodes[i].kind == "dense":
+            m, k, n = self._dense_mkn(i, batch)
+            return self.lib.fnet_dense_bwd_data_on_tensor_core(m, k, n, self.math) == 1
+        return self.lib.fnet_conv2d_bwd_data_on_tensor_core(C.byref(self._conv_desc(i, batch))) == 1
+
     def _needs_grad(self, input_grad=False):
         """True for nodes that have a trainable weight at or above them (a gradient must reach them);
         with input_grad, for every node: the gradient is wanted at the network input itself."""
@@ -460,7 +469,8 @@ class Engine(object):
                 node_r = self.nodes[r]
                 if (len(users) == 1 and r != last and node_r.kind in GEMM_KINDS + ("dwconv2d",) and need[r]
                         and fl.ACT[node_r.cfg["activation"]] in (1, 2, 3)
-                        and self.nodes[users[0]].kind in ("conv2d", "dense") and len(self.src[users[0]]) == 1):
+                        and self.nodes[users[0]].kind in ("conv2d", "dense") and len(self.src[users[0]]) == 1
+                        and not self._dgrad_on_tensor_core(users[0], batch)):
                     fused_into[r] = users[0]
 
         def dx_epilogue(i, s0):

@@ -94,11 +94,14 @@ SIGNATURES = {
     "fnet_graph_launch": (C.c_int, [_P, _P]),
     "fnet_graph_destroy": (C.c_int, [_P]),
     "fnet_graph_step_fed": (C.c_int, [_P, _P, _P, C.c_size_t, _P, _P, C.c_size_t, _P, _P, C.c_size_t, _P]),
+    "fnet_conv2d_bwd_data_on_tensor_core": (C.c_int, [_CD]),
+    "fnet_dense_bwd_data_on_tensor_core": (C.c_int, [C.c_int64, C.c_int64, C.c_int64, C.c_int]),
     "fnet_graph_step_streamed": (C.c_int, [_P, _P, _P, _P, C.c_size_t, _P, _P, _P, C.c_size_t, _P, _P, _P, C.c_size_t,
                                            _P, _P, _P, _P]),
 }
 
-_STATUS_RETURNING = {n for n, (r, _) in SIGNATURES.items() if r is C.c_int and n != "fnet_version"}
+_QUERIES = {"fnet_version", "fnet_conv2d_bwd_data_on_tensor_core", "fnet_dense_bwd_data_on_tensor_core"}    # return a value, not a status
+_STATUS_RETURNING = {n for n, (r, _) in SIGNATURES.items() if r is C.c_int and n not in _QUERIES}
 
 
 def build(verbose=False):

@@ -87,6 +87,11 @@ int fnet_conv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const floa
  * (model/input.py:190) and the classifier head (model/keras_model.py:124).
  * x[M,K], w[K,N], y[M,N]; M = product of the leading axes.
  * ------------------------------------------------------------------------------------------ */
+/* 1 when the data gradient of this layer runs on a tensor-core kernel, 0 when on the FFMA / streaming kernels, -1 on a
+ * bad argument.  A planner's question, not a computation (no reference counterpart): the activation derivative of
+ * the producing layer is folded into fnet_*_bwd_data_act only where that epilogue is cheap. */
+int fnet_conv2d_bwd_data_on_tensor_core(const fnet_conv2d_desc *d);
+int fnet_dense_bwd_data_on_tensor_core(int64_t m, int64_t k, int64_t n, int math);
 size_t fnet_dense_workspace_bytes(int64_t m, int64_t k, int64_t n);
 int fnet_dense_fwd(int64_t m, int64_t k, int64_t n, int act, int math, const float *x, const float *w,
                    const float *bias, float *y, void *ws, size_t ws_bytes, void *stream);
