@@ -1,20 +1,23 @@
-// TMA-fed, warp-specialised, persistent tcgen05 GEMM for the layers that ARE plain GEMMs: Dense and 1x1
-// stride-1 convolutions (most of a FeatureNet product: the "Reg_" channel aligners, the x8 / x0.25 1x1
-// expansions, Dense on rank-4 tensors).  No im2col gather is involved, so both operands are 2-D boxes that
-// the TMA engine copies straight into the swizzled shared-memory layouts tcgen05 reads:
+// TMA-fed, warp-specialised, persistent tcgen05 GEMM for the layers whose operands are boxes: Dense and 1x1 stride-1
+// convolutions (plain GEMMs: the "Reg_" channel aligners, the x8 / x0.25 1x1 expansions, Dense on rank-4 tensors)
+// and k x k stride-1 convolutions (TgConv: one shifted 4-D box of the NHWC tensor per tap and 32-channel chunk).
+// No gather instructions are involved: the TMA engine copies the boxes straight into the swizzled shared-memory
+// layouts tcgen05 reads, and zero-fills whatever lies outside the tensor (ragged edges, convolution padding).
 //
 //   warp 0 (one lane)  producer: waits for a free stage, arms its mbarrier with the byte count and issues
-//                      cp.async.bulk.tensor.2d for A (128 x 32) and B (BN x 32);
-//   warp 1 (one lane)  issues four tcgen05.mma.kind::tf32 per stage into one of two TMEM accumulators and
-//                      releases the stage (tcgen05.commit -> mbarrier);
+//                      cp.async.bulk.tensor.{2d,4d} for A (128 x 32) and B (BN x 32);
+//   warp 1 (one lane)  issues four tcgen05.mma.kind::tf32 per stage (twelve in TF32x3 mode) into one of two TMEM
+//                      accumulators and releases the stage (tcgen05.commit -> mbarrier);
 //   warps 2..5         epilogue: tcgen05.ld their TMEM lane quadrant, bias + activation, coalesced stores --
-//                      while the other accumulator is already being filled for the CTA's next tile.
+//                      while the other accumulator is already being filled for the CTA's next tile;
+//   warps 6..13        TF32x3 only: split every landed stage into tf32 heads (in place) and tails (twin buffer).
 //
 // One CTA per SM walks the output tiles (persistent), so barrier setup, TMEM allocation and descriptor
 // prefetch are paid once per SM instead of once per tile, and the epilogue of tile i overlaps the main loop
 // of tile i+1.  Forward: A = x [M][K] (K-major), B = w [K][N] (MN-major, SWIZZLE_128B_ATOM_32B boxes of
-// 32 x 32).  Data gradient: A = dz [M][N] (K-major), B = w [C][N] (K-major).  Rows / columns / k beyond the
-// tensor are zero-filled by the TMA unit, so ragged edges need no code.  The tensor core truncates fp32 to tf32.
+// 32 x 32).  Data gradient: A = dz [M][N] (K-major), B = w [C][N] (K-major).  The filter gradient has its own
+// kernel below (both operands MN-major, reduction over the pixels, split over CTAs).  In plain TF32 mode the tensor
+// core truncates fp32 to tf32.  All loads read this GPU's memory only; no multicast is used.
 #include <cuda.h>
 #include "igemm_problems.cuh"
 

@@ -39,7 +39,7 @@ int tc_conv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, 
 int tc_conv_wgrad(const ConvGeom &g, int math, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                   size_t ws_bytes, cudaStream_t stream);
 
-// FNET_MATH_TF32 / FNET_MATH_TF32X3, layers that are plain GEMMs (Dense, 1x1 stride-1 convolutions): TMA-fed persistent
+// FNET_MATH_TF32 / FNET_MATH_TF32X3, layers whose operands are boxes (Dense, 1x1 and k x k stride-1 convolutions): TMA-fed persistent
 // kernel (gemm_tma.cu)
 bool tma_gemm_supported(const ConvGeom &g, int math, int product);   // product: 0 fwd, 1 dgrad, 2 wgrad
 int tma_gemm_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y,
