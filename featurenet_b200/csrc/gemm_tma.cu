@@ -17,7 +17,7 @@
 // of tile i+1.  Forward: A = x [M][K] (K-major), B = w [K][N] (MN-major, SWIZZLE_128B_ATOM_32B boxes of
 // 32 x 32).  Data gradient: A = dz [M][N] (K-major), B = w [C][N] (K-major).  The filter gradient has its own
 // kernel below (both operands MN-major, reduction over the pixels, split over CTAs).  In plain TF32 mode the tensor
-// core truncates fp32 to tf32.  All loads read this GPU's memory only; no multicast is used.
+// core truncates fp32 to tf32.
 #include <cuda.h>
 #include "igemm_problems.cuh"
 
