@@ -64,37 +64,114 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(fnet_conv2d_desc d, const
     }
 }
 
+// Four channels per thread (C % 4 == 0, 16-byte aligned tensors, < 2^31 elements): 32-bit index arithmetic and one
+// decode, one bounds check and two LDG.128 per tap for four outputs.  The scalar kernels above are issue-bound at
+// ~350 GB/s (3x3 on 128 x 32 x 32 x 64: 191 us for 67 MB).
+__global__ void __launch_bounds__(256) dw_fwd_vec4_kernel(fnet_conv2d_desc d, const float4 *__restrict__ x,
+                                                          const float4 *__restrict__ w, const float4 *__restrict__ bias,
+                                                          float4 *__restrict__ y, int act) {
+    pdl_prologue();
+    const int quads = d.in_c >> 2;
+    const int total = d.batch * d.out_h * d.out_w * quads;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        int q = i % quads, t = i / quads;
+        int wo = t % d.out_w;
+        t /= d.out_w;
+        int ho = t % d.out_h, b = t / d.out_h;
+        const int h0 = ho * d.stride_h - d.pad_top, w0 = wo * d.stride_w - d.pad_left;
+        const float4 *img = x + (int64_t)b * d.in_h * d.in_w * quads + q;
+        float4 acc = bias ? __ldg(bias + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < d.kh; ++r) {
+            const int h = h0 + r;
+            if ((unsigned)h >= (unsigned)d.in_h) continue;
+            for (int s = 0; s < d.kw; ++s) {
+                const int ww = w0 + s;
+                if ((unsigned)ww >= (unsigned)d.in_w) continue;
+                const float4 xv = __ldg(img + (h * d.in_w + ww) * quads), wv = __ldg(w + (r * d.kw + s) * quads + q);
+                acc.x = fmaf(xv.x, wv.x, acc.x);
+                acc.y = fmaf(xv.y, wv.y, acc.y);
+                acc.z = fmaf(xv.z, wv.z, acc.z);
+                acc.w = fmaf(xv.w, wv.w, acc.w);
+            }
+        }
+        y[i] = make_float4(act_apply(acc.x, act), act_apply(acc.y, act), act_apply(acc.z, act), act_apply(acc.w, act));
+    }
+}
+
+__global__ void __launch_bounds__(256) dw_dgrad_vec4_kernel(fnet_conv2d_desc d, const float4 *__restrict__ dz,
+                                                            const float4 *__restrict__ w, float4 *__restrict__ dx,
+                                                            int accumulate) {
+    pdl_prologue();
+    const int quads = d.in_c >> 2;
+    const int total = d.batch * d.in_h * d.in_w * quads;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        int q = i % quads, t = i / quads;
+        int wi = t % d.in_w;
+        t /= d.in_w;
+        int hi = t % d.in_h, b = t / d.in_h;
+        const float4 *img = dz + (int64_t)b * d.out_h * d.out_w * quads + q;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < d.kh; ++r) {
+            const int hh = hi + d.pad_top - r;
+            if (hh < 0) break;
+            const int ho = hh / d.stride_h;
+            if (ho * d.stride_h != hh || ho >= d.out_h) continue;
+            for (int s = 0; s < d.kw; ++s) {
+                const int ww = wi + d.pad_left - s;
+                if (ww < 0) break;
+                const int wo = ww / d.stride_w;
+                if (wo * d.stride_w != ww || wo >= d.out_w) continue;
+                const float4 gv = __ldg(img + (ho * d.out_w + wo) * quads), wv = __ldg(w + (r * d.kw + s) * quads + q);
+                acc.x = fmaf(gv.x, wv.x, acc.x);
+                acc.y = fmaf(gv.y, wv.y, acc.y);
+                acc.z = fmaf(gv.z, wv.z, acc.z);
+                acc.w = fmaf(gv.w, wv.w, acc.w);
+            }
+        }
+        if (accumulate) {
+            const float4 old = dx[i];
+            acc.x += old.x; acc.y += old.y; acc.z += old.z; acc.w += old.w;
+        }
+        dx[i] = acc;
+    }
+}
+
 // stage 1: CTA (cgroup, split) walks its share of output pixels; thread = (channel lane, pixel lane).
 // partial[split][tap or bias][c]
 constexpr int kDwChan = 32;   // channels per CTA (x dimension of the thread block)
 constexpr int kDwPix = 8;     // pixel lanes per CTA (y dimension)
 
-template <int MAXROWS>
+// I = type of the pixel index: int whenever the tensor allows it (64-bit division is a long software routine and the
+// loop decodes the pixel index three times per trip)
+template <int MAXROWS, typename I>
 __global__ void __launch_bounds__(kDwChan * kDwPix) dw_wgrad_partial_kernel(fnet_conv2d_desc d, int pix_per_split,
                                                                            const float *__restrict__ x,
                                                                            const float *__restrict__ dz,
                                                                            float *__restrict__ partial, int rows) {
     pdl_prologue();
-    __shared__ float red[kDwPix][kDwChan + 1];
+    // blockDim = (channel lanes, pixel lanes), 256 threads: 32 x 8 for wide layers, 4 x 64 for 3-channel ones (with a
+    // fixed 32 x 8 split a 3-channel layer left 29 of 32 lanes idle: 186 us for a 5x5 on 128 x 32 x 32 x 3)
+    __shared__ float red[kDwChan * kDwPix + kDwPix * 8];
+    const int lanes_c = blockDim.x, lanes_p = blockDim.y, pitch = lanes_c + 1;
     int C = d.in_c;
-    int c = blockIdx.x * kDwChan + threadIdx.x;
+    int c = blockIdx.x * lanes_c + threadIdx.x;
     int split = blockIdx.y;
-    int64_t npix = (int64_t)d.batch * d.out_h * d.out_w;
-    int64_t p0 = (int64_t)split * pix_per_split;
-    int64_t p1 = p0 + pix_per_split < npix ? p0 + pix_per_split : npix;
+    I npix = (I)d.batch * d.out_h * d.out_w;
+    I p0 = (I)split * pix_per_split;
+    I p1 = p0 + pix_per_split < npix ? p0 + pix_per_split : npix;
     int taps = d.kh * d.kw;
     float acc[MAXROWS];                 // one accumulator per tap (+ bias): x and dz are read once
 #pragma unroll
     for (int t = 0; t < MAXROWS; ++t) acc[t] = 0.f;
     if (c < C) {
-        for (int64_t p = p0 + threadIdx.y; p < p1; p += kDwPix) {
-            float g = __ldg(dz + p * C + c);
-            int wo = (int)(p % d.out_w);
-            int64_t q = p / d.out_w;
-            int ho = (int)(q % d.out_h);
-            int64_t b = q / d.out_h;
+        for (I p = p0 + threadIdx.y; p < p1; p += lanes_p) {
+            float g = __ldg(dz + (int64_t)p * C + c);
+            int wo = (int)(p % (I)d.out_w);
+            I q = p / (I)d.out_w;
+            int ho = (int)(q % (I)d.out_h);
+            I b = q / (I)d.out_h;
             int h0 = ho * d.stride_h - d.pad_top, w0 = wo * d.stride_w - d.pad_left;
-            const float *img = x + b * d.in_h * d.in_w * C + c;
+            const float *img = x + (int64_t)b * d.in_h * d.in_w * C + c;
             int r = 0, s = 0;
 #pragma unroll
             for (int t = 0; t < MAXROWS; ++t) {
@@ -112,12 +189,11 @@ __global__ void __launch_bounds__(kDwChan * kDwPix) dw_wgrad_partial_kernel(fnet
 #pragma unroll
     for (int t = 0; t < MAXROWS; ++t) {
         if (t < rows) {
-            red[threadIdx.y][threadIdx.x] = acc[t];
+            red[threadIdx.y * pitch + threadIdx.x] = acc[t];
             __syncthreads();
             if (threadIdx.y == 0 && c < C) {
                 float sum = 0.f;
-#pragma unroll
-                for (int j = 0; j < kDwPix; ++j) sum += red[j][threadIdx.x];
+                for (int j = 0; j < lanes_p; ++j) sum += red[j * pitch + threadIdx.x];
                 partial[((int64_t)split * rows + t) * C + c] = sum;
             }
             __syncthreads();
@@ -139,11 +215,19 @@ __global__ void __launch_bounds__(256) dw_wgrad_reduce_kernel(int splits, int ro
     }
 }
 
+// channel lanes of the filter-gradient CTA: the smallest power of two >= C, between 4 and 32
+static int dw_chan_lanes(int c) {
+    int lanes = 4;
+    while (lanes < c && lanes < kDwChan) lanes *= 2;
+    return lanes;
+}
+
 static int dw_splits(const fnet_conv2d_desc *d) {
     int64_t npix = (int64_t)d->batch * d->out_h * d->out_w;
-    int cgroups = ceil_div(d->in_c, kDwChan);
+    const int lanes_c = dw_chan_lanes(d->in_c), lanes_p = kDwChan * kDwPix / lanes_c;
+    int cgroups = ceil_div(d->in_c, lanes_c);
     int64_t want = ceil_div(4 * kNumSMs, cgroups);
-    int64_t most = ceil_div<int64_t>(npix, 4 * kDwPix);
+    int64_t most = ceil_div<int64_t>(npix, 4 * lanes_p);
     if (want > most) want = most;
     if (want < 1) want = 1;
     if (want > 1024) want = 1024;
@@ -180,7 +264,16 @@ int fnet_dwconv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w,
     int64_t total = (int64_t)d->batch * d->out_h * d->out_w * d->in_c;
     if (total == 0) return FNET_OK;
     int act = d->act == FNET_ACT_SOFTMAX ? FNET_ACT_NONE : d->act;
-    launch_pdl(dw_fwd_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, x, w, bias, y, act);
+    const int64_t in_total = (int64_t)d->batch * d->in_h * d->in_w * d->in_c;
+    const bool vec = !(d->in_c & 3) && total < 0x7fffffffLL - (1 << 26) && in_total < 0x7fffffffLL &&
+                     !((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(bias) |
+                        reinterpret_cast<uintptr_t>(y)) & 15);
+    if (vec)
+        launch_pdl(dw_fwd_vec4_kernel, dim3(stream_grid(total / 4, 256)), dim3(256), 0, as_stream(stream), *d,
+                   reinterpret_cast<const float4 *>(x), reinterpret_cast<const float4 *>(w), reinterpret_cast<const float4 *>(bias),
+                   reinterpret_cast<float4 *>(y), act);
+    else
+        launch_pdl(dw_fwd_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, x, w, bias, y, act);
     rc = check_launch("fnet_dwconv2d_fwd");
     if (rc == FNET_OK && d->act == FNET_ACT_SOFTMAX)
         rc = fnet_act_fwd(FNET_ACT_SOFTMAX, total / d->in_c, d->in_c, y, y, stream);
@@ -194,7 +287,14 @@ int fnet_dwconv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const flo
     FNET_REQUIRE(dz && w && dx, "fnet_dwconv2d_bwd_data: null pointer");
     int64_t total = (int64_t)d->batch * d->in_h * d->in_w * d->in_c;
     if (total == 0) return FNET_OK;
-    launch_pdl(dw_dgrad_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, dz, w, dx, accumulate);
+    const int64_t out_total = (int64_t)d->batch * d->out_h * d->out_w * d->in_c;
+    const bool vec = !(d->in_c & 3) && total < 0x7fffffffLL - (1 << 26) && out_total < 0x7fffffffLL &&
+                     !((reinterpret_cast<uintptr_t>(dz) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(dx)) & 15);
+    if (vec)
+        launch_pdl(dw_dgrad_vec4_kernel, dim3(stream_grid(total / 4, 256)), dim3(256), 0, as_stream(stream), *d,
+                   reinterpret_cast<const float4 *>(dz), reinterpret_cast<const float4 *>(w), reinterpret_cast<float4 *>(dx), accumulate);
+    else
+        launch_pdl(dw_dgrad_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, dz, w, dx, accumulate);
     return check_launch("fnet_dwconv2d_bwd_data");
 }
 
@@ -216,17 +316,22 @@ int fnet_dwconv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const fl
     int pix_per_split = (int)ceil_div<int64_t>(npix, splits);
     splits = (int)ceil_div<int64_t>(npix, pix_per_split);
     float *partial = reinterpret_cast<float *>(ws);
-    dim3 grid(ceil_div(d->in_c, kDwChan), splits), block(kDwChan, kDwPix);
-    if (taps + 1 <= 10)
-        launch_pdl(dw_wgrad_partial_kernel<10>, dim3(grid), dim3(block), 0, as_stream(stream), *d, pix_per_split, x, dz, partial, rows);
-    else if (taps + 1 <= 26)
-        launch_pdl(dw_wgrad_partial_kernel<26>, dim3(grid), dim3(block), 0, as_stream(stream), *d, pix_per_split, x, dz, partial, rows);
-    else if (taps + 1 <= 50)
-        launch_pdl(dw_wgrad_partial_kernel<50>, dim3(grid), dim3(block), 0, as_stream(stream), *d, pix_per_split, x, dz, partial, rows);
+    const int lanes_c = dw_chan_lanes(d->in_c);
+    dim3 grid(ceil_div(d->in_c, lanes_c), splits), block(lanes_c, kDwChan * kDwPix / lanes_c);
+    const bool small = npix < 0x7fffffffLL - (1 << 20);
+#define FNET_DW_WGRAD(R_)                                                                                                              \
+    do {                                                                                                                               \
+        if (small) launch_pdl(dw_wgrad_partial_kernel<R_, int>, dim3(grid), dim3(block), 0, as_stream(stream), *d, pix_per_split, x, dz, partial, rows); \
+        else launch_pdl(dw_wgrad_partial_kernel<R_, int64_t>, dim3(grid), dim3(block), 0, as_stream(stream), *d, pix_per_split, x, dz, partial, rows);   \
+    } while (0)
+    if (taps + 1 <= 10) FNET_DW_WGRAD(10);
+    else if (taps + 1 <= 26) FNET_DW_WGRAD(26);
+    else if (taps + 1 <= 50) FNET_DW_WGRAD(50);
     else {
         set_error("fnet_dwconv2d_bwd_filter: kernels above 7x7 are outside the FeatureNet vocabulary");
         return FNET_ERR_UNSUPPORTED;
     }
+#undef FNET_DW_WGRAD
     rc = check_launch("fnet_dwconv2d_bwd_filter");
     if (rc) return rc;
     launch_pdl(dw_wgrad_reduce_kernel, dim3(stream_grid((int64_t)rows * d->in_c, 256)), dim3(256), 0, as_stream(stream), 

@@ -184,7 +184,10 @@ def test_workspace_too_small_is_an_error_not_a_crash(L):
 
 
 @pytest.mark.parametrize("xs,k,s,act", [((3, 9, 8, 5), (3, 3), (1, 1), "relu"), ((2, 16, 16, 40), (5, 1), (2, 2), None),
-                                        ((2, 7, 7, 3), (2, 2), (2, 2), "tanh"), ((1, 6, 6, 33), (7, 7), (1, 1), "sigmoid")])
+                                        ((2, 7, 7, 3), (2, 2), (2, 2), "tanh"), ((1, 6, 6, 33), (7, 7), (1, 1), "sigmoid"),
+                                        # channels % 4 == 0: the four-channels-per-thread kernels
+                                        ((4, 12, 10, 16), (3, 3), (1, 1), "relu"), ((3, 9, 9, 8), (3, 3), (2, 2), None),
+                                        ((2, 5, 6, 64), (5, 5), (1, 1), "tanh")])
 def test_depthwise_forward_backward(L, xs, k, s, act):
     from featurenet_b200 import lib as fl
     rng = np.random.default_rng(xs[1] * 13 + k[0])
@@ -200,6 +203,9 @@ def test_depthwise_forward_backward(L, xs, k, s, act):
     dxd = torch.empty(xs, device="cuda")
     L.fnet_dwconv2d_bwd_data(desc, ptr(dzd), ptr(wd), ptr(dxd), 0, None)
     assert_close(host(dxd), dx, what="dw dgrad")
+    L.fnet_dwconv2d_bwd_data(desc, ptr(dzd), ptr(wd), ptr(dxd), 1, None)
+    assert_close(host(dxd), 2 * dx, what="dw dgrad accumulate")
+    L.fnet_dwconv2d_bwd_data(desc, ptr(dzd), ptr(wd), ptr(dxd), 0, None)
     ws = workspace(L.fnet_dwconv2d_workspace_bytes(C.byref(desc)))
     dwd, dbd = torch.empty(w.shape, device="cuda"), torch.empty(xs[3], device="cuda")
     L.fnet_dwconv2d_bwd_filter(desc, ptr(xd), ptr(dzd), ptr(dwd), ptr(dbd), ptr(ws), ws.numel(), None)
