@@ -59,9 +59,13 @@ __global__ void __launch_bounds__(256) pool_fwd_kernel(fnet_pool2d_desc d, const
 // Four channels per thread (channels % 4 == 0, 16-byte aligned tensors): the index decode and the window loop are
 // paid once per 16 bytes instead of once per 4.  The scalar kernel above spends ~250 instructions per element and is
 // issue-bound at a tenth of the HBM rate (2x2 stride-1 SAME pooling of 128 x 32 x 32 x 32: 65 us for 38 MB).
+// KH, KW > 0: window known at compile time (2x2 and 3x3, the sizes of the NAS space): loops unroll, loads are issued
+// together with a clamped address.  0: runtime window.
+template <int KH, int KW>
 __global__ void __launch_bounds__(256) pool_fwd_vec4_kernel(fnet_pool2d_desc d, const float4 *__restrict__ x,
                                                             float4 *__restrict__ y, uchar4 *__restrict__ argmax) {
     pdl_prologue();
+    if (KH > 0) { d.kh = KH; d.kw = KW; }
     const int quads = d.channels >> 2;
     const int total = d.batch * d.out_h * d.out_w * quads;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -74,6 +78,25 @@ __global__ void __launch_bounds__(256) pool_fwd_vec4_kernel(fnet_pool2d_desc d, 
         if (d.kind == FNET_POOL_MAX) {
             float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
             uchar4 arg = make_uchar4(0, 0, 0, 0);
+            if (KH > 0) {
+                constexpr int T = KH * KW > 0 ? KH * KW : 1;
+                float4 v[T];
+                bool ok[T];
+#pragma unroll
+                for (int t2 = 0; t2 < T; ++t2) {
+                    const int h = h0 + t2 / (KW > 0 ? KW : 1), w = w0 + t2 % (KW > 0 ? KW : 1);
+                    ok[t2] = (unsigned)h < (unsigned)d.in_h && (unsigned)w < (unsigned)d.in_w;
+                    v[t2] = __ldg(img + (ok[t2] ? (h * d.in_w + w) * quads : 0));
+                }
+#pragma unroll
+                for (int t2 = 0; t2 < T; ++t2)
+                    if (ok[t2]) {
+                        if (v[t2].x > best.x) { best.x = v[t2].x; arg.x = (unsigned char)t2; }
+                        if (v[t2].y > best.y) { best.y = v[t2].y; arg.y = (unsigned char)t2; }
+                        if (v[t2].z > best.z) { best.z = v[t2].z; arg.z = (unsigned char)t2; }
+                        if (v[t2].w > best.w) { best.w = v[t2].w; arg.w = (unsigned char)t2; }
+                    }
+            } else
             for (int r = 0; r < d.kh; ++r) {
                 const int h = h0 + r;
                 if ((unsigned)h >= (unsigned)d.in_h) continue;
@@ -272,8 +295,15 @@ int fnet_pool2d_fwd(const fnet_pool2d_desc *d, const float *x, float *y, uint8_t
     const bool aligned = !((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) &&
                          !(reinterpret_cast<uintptr_t>(argmax) & 3);
     if (!(d->channels & 3) && aligned && total < 0x7fffffffLL - (1 << 26) && in_total < 0x7fffffffLL)
-        launch_pdl(pool_fwd_vec4_kernel, dim3(stream_grid(total / 4, 256)), dim3(256), 0, as_stream(stream), *d,
-                   reinterpret_cast<const float4 *>(x), reinterpret_cast<float4 *>(y), reinterpret_cast<uchar4 *>(argmax));
+    {
+        const float4 *x4 = reinterpret_cast<const float4 *>(x);
+        float4 *y4 = reinterpret_cast<float4 *>(y);
+        uchar4 *a4 = reinterpret_cast<uchar4 *>(argmax);
+        const dim3 grid(stream_grid(total / 4, 256));
+        if (d->kh == 2 && d->kw == 2) launch_pdl(pool_fwd_vec4_kernel<2, 2>, grid, dim3(256), 0, as_stream(stream), *d, x4, y4, a4);
+        else if (d->kh == 3 && d->kw == 3) launch_pdl(pool_fwd_vec4_kernel<3, 3>, grid, dim3(256), 0, as_stream(stream), *d, x4, y4, a4);
+        else launch_pdl(pool_fwd_vec4_kernel<0, 0>, grid, dim3(256), 0, as_stream(stream), *d, x4, y4, a4);
+    }
     else if (total < 0x7fffffffLL - (1 << 26) && in_total < 0x7fffffffLL)      // the grid-stride increment must not overflow either
         launch_pdl(pool_fwd_kernel<int>, dim3(stream_grid(total, 256)), dim3(256), 0, as_stream(stream), *d, x, y, argmax);
     else
