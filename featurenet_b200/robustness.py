@@ -120,14 +120,9 @@ def random_sphere_l2(nb_points, nb_dims, radius):
     return a * (gammainc(nb_dims / 2.0, s2 / 2.0) ** (1.0 / nb_dims) * radius / np.sqrt(s2))[:, None]
 
 
-def _weibull_location(maxima, c_init):
-    from scipy.optimize import fmin
-    from scipy.stats import weibull_min
-    return weibull_min.fit(-np.asarray(maxima, np.float64), c_init, optimizer=fmin)[1]
-
-
-def clever_u(net, x, nb_batches, batch_size, radius, norm=2, c_init=1, pool_factor=10, return_maxima=False):
-    """Untargeted CLEVER score of ONE sample ``x`` (model/metrics.py:205-239)."""
+def _clever_maxima(net, x, nb_batches, batch_size, radius, norm, pool_factor):
+    """The GPU half of clever_u: (margins z[pred] - z[target] per target class, per-batch gradient-norm maxima per
+    target class).  All random draws of the sample happen here, in the reference's order."""
     if norm != 2:
         raise NotImplementedError("only norm=2, the one the reference uses (tensorflow_generator.py:186), is built")
     if pool_factor < 1:
@@ -153,20 +148,37 @@ def clever_u(net, x, nb_batches, batch_size, radius, norm=2, c_init=1, pool_fact
     norms = np.linalg.norm(grad.reshape(grad.shape[0], -1).cpu().numpy().astype(np.float64), axis=1)
     if np.isnan(norms).any():
         raise Exception("The classifier results NaN gradients.")
-    scores, all_maxima = [], []
-    for t, j in enumerate(targets):
-        maxima = [float(np.max(norms[t * pool_n + idx])) for idx in picks[t]]
-        loc = _weibull_location(maxima, c_init)
-        scores.append(min(-(z[pred] - z[j]) / loc, radius))
-        all_maxima.append(maxima)
-    score = float(np.min(scores))
-    return (score, np.asarray(all_maxima)) if return_maxima else score
+    maxima = [[float(np.max(norms[t * pool_n + idx])) for idx in picks[t]] for t in range(len(targets))]
+    return [z[pred] - z[j] for j in targets], maxima
 
 
-def clever_score(net, x_set, nb_batches=10, batch_size=5, radius=2, norm=2, pool_factor=3):
-    """tensorflow_generator.py:188-203: the average untargeted CLEVER score over a set of samples."""
-    return float(np.average([clever_u(net, element, nb_batches, batch_size, radius, norm=norm, pool_factor=pool_factor)
-                             for element in x_set]))
+def _clever_from_fits(margins, locs, radius):
+    """model/metrics.py:319-324 and :239: min over the target classes of min(-margin / loc, radius)."""
+    return float(np.min([min(-m / loc, radius) for m, loc in zip(margins, locs)]))
+
+
+def clever_u(net, x, nb_batches, batch_size, radius, norm=2, c_init=1, pool_factor=10, return_maxima=False):
+    """Untargeted CLEVER score of ONE sample ``x`` (model/metrics.py:205-239)."""
+    from . import weibull
+    margins, maxima = _clever_maxima(net, x, nb_batches, batch_size, radius, norm, pool_factor)
+    score = _clever_from_fits(margins, [weibull.location(m, c_init) for m in maxima], radius)
+    return (score, np.asarray(maxima)) if return_maxima else score
+
+
+def clever_score(net, x_set, nb_batches=10, batch_size=5, radius=2, norm=2, pool_factor=3, workers=None):
+    """tensorflow_generator.py:188-203: the average untargeted CLEVER score over a set of samples.  The gradients of
+    all samples first (GPU; the random draws stay in the reference's order), then every Weibull fit of the set over
+    worker processes (featurenet_b200/weibull.py): same numbers as sample by sample, a fraction of the wall time."""
+    from . import weibull
+    per_sample = [_clever_maxima(net, element, nb_batches, batch_size, radius, norm, pool_factor) for element in x_set]
+    if not per_sample:
+        return float("nan")
+    locs = weibull.locations([m for _, maxima in per_sample for m in maxima], 1, workers)
+    scores, at = [], 0
+    for margins, maxima in per_sample:
+        scores.append(_clever_from_fits(margins, locs[at: at + len(maxima)], radius))
+        at += len(maxima)
+    return float(np.average(scores))
 
 
 # ---------------------------------------------------------------------------------------------- Carlini-Wagner L2
