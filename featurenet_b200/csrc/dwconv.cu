@@ -373,13 +373,20 @@ __global__ void __launch_bounds__(256) dw_wgrad_reduce_kernel(int splits, int ro
                                                               const float *__restrict__ partial, float *__restrict__ dw,
                                                               float *__restrict__ dbias) {
     pdl_prologue();
-    int total = rows * C;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    // one warp per output: lanes over the splits (coalescing does not matter for a few hundred KB, the depth of the
+    // dependent chain does: one thread per output walked up to 1024 partials in sequence), fixed shuffle tree
+    const int total = rows * C, lane = threadIdx.x & 31;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < total; i += warps) {
         float s = 0.f;
-        for (int z = 0; z < splits; ++z) s += partial[(int64_t)z * total + i];
-        int row = i / C, c = i - row * C;
-        if (row < taps) dw[i] = s;
-        else dbias[c] = s;
+        for (int z = lane; z < splits; z += 32) s += partial[(int64_t)z * total + i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) {
+            int row = i / C, c = i - row * C;
+            if (row < taps) dw[i] = s;
+            else dbias[c] = s;
+        }
     }
 }
 
@@ -535,7 +542,7 @@ int fnet_dwconv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const fl
     }
     rc = check_launch("fnet_dwconv2d_bwd_filter");
     if (rc) return rc;
-    launch_pdl(dw_wgrad_reduce_kernel, dim3(stream_grid((int64_t)rows * d->in_c, 256)), dim3(256), 0, as_stream(stream), 
+    launch_pdl(dw_wgrad_reduce_kernel, dim3(stream_grid((int64_t)rows * d->in_c * 32, 256)), dim3(256), 0, as_stream(stream), 
         splits, rows, taps, d->in_c, partial, dw, dbias);
     return check_launch("fnet_dwconv2d_bwd_filter");
 }
