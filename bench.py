@@ -15,8 +15,10 @@ threads): the reference's own TF 1.12 / Keras 2.2.4 cannot be installed on this 
 """
 import argparse
 import contextlib
+import copy
 import io
 import json
+import math
 import os
 import subprocess
 import sys
@@ -66,6 +68,14 @@ def emit(line):
     out.flush()
 
 
+def config_for(workload, gpus):
+    """The `config` object of the JSON line: identical, key for key, in the product arm and the reference arm."""
+    return {"workload": WORKLOADS[workload][3], "batch": BATCH, "optimizer": "adam(1e-3)",
+            "parallelism": "candidate-sharded x%d (no collective)" % gpus,
+            "l2": "inputs larger than L2: the resident dataset (614 MB CIFAR-shape / 188 MB MNIST-shape) is streamed "
+                  "batch by batch through the epoch permutation"}
+
+
 def build_candidate(workload):
     from model.keras_model import KerasFeatureModel
     from products_tree import ProductSet
@@ -83,13 +93,30 @@ def build_candidate(workload):
     return model, net, dataset
 
 
-def peaks():
+def peaks(math="auto"):
+    """Roofline denominators: HBM copy rate and the dense rate of the arithmetic the math mode runs on.
+
+    MEASURED_PEAKS.json (driver-written) has HBM and bf16; profiles/r2_peaks_tf32_ffma.json (scripts/measure_peaks.py,
+    same method: 8192^3 matmul, best of 10) adds cuBLAS TF32 and fp32-FFMA.  fp32 mode -> FFMA peak; tf32 -> TF32 peak;
+    auto / tf32x3 -> TF32 peak / 3 on the tensor-core kernels (three MMAs per algorithmic product); bf16 -> bf16 peak."""
+    out = {"hbm_gbs": 6650.0, "tflops": 1590.0, "source": "fallback (B200_PROFILING.md)"}
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(path):
         with open(path) as handle:
             p = json.load(handle)
-        return {"hbm_gbs": p["hbm_gbs"], "tflops": p["bf16_tflops"], "source": "measured (MEASURED_PEAKS.json, burst)"}
-    return {"hbm_gbs": 6650.0, "tflops": 1590.0, "source": "fallback (B200_PROFILING.md)"}
+        out = {"hbm_gbs": p["hbm_gbs"], "tflops": p["bf16_tflops"], "source": "measured (MEASURED_PEAKS.json, burst)"}
+    extra = os.path.join(ROOT, "profiles", "r2_peaks_tf32_ffma.json")
+    if math != "bf16" and os.path.isfile(extra):
+        with open(extra) as handle:
+            q = json.load(handle)
+        if math == "fp32":
+            out["tflops"], what = q["fp32_ffma_tflops"], "fp32 FFMA"
+        elif math == "tf32":
+            out["tflops"], what = q["tf32_tflops"], "TF32"
+        else:
+            out["tflops"], what = q["tf32_tflops"] / 3.0, "TF32 / 3 (three MMAs per product)"
+        out["source"] += "; tensor peak = %s from profiles/r2_peaks_tf32_ffma.json" % what
+    return out
 
 
 class ClockSampler(object):
@@ -108,6 +135,12 @@ class ClockSampler(object):
             self.thread.start()
         except OSError:
             self.proc = None
+
+    def wait_for_samples(self, count=2, limit_s=3.0):
+        """Block until nvidia-smi is up and sampling: its start-up (NVML init) must not fall into the timed region."""
+        t0 = time.perf_counter()
+        while self.proc is not None and len(self.rows) < count and time.perf_counter() - t0 < limit_s:
+            time.sleep(0.05)
 
     def _read(self):
         for line in self.proc.stdout:
@@ -181,7 +214,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": rate, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / done, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload][3], "batch": BATCH},
+        "config": config_for(args.workload, args.gpus),
         "cpu_baseline": {"value": rate, "unit": "images/s", "cores": threads, "kind": "port",
                          "sample": "%d train steps of batch %d through oracle/torch_cpu.py (TF1.12/Keras2.2.4 "
                                    "is not installable here)" % (done, BATCH)},
@@ -189,6 +222,9 @@ def run_reference(args):
         "wall_s": time.perf_counter() - t0,
     }
     emit(line)
+
+
+MIN_TIMED_SECONDS = 0.5
 
 
 def measure_workload(workload, args, torch, dist, world, device_index, full=True):
@@ -201,40 +237,67 @@ def measure_workload(workload, args, torch, dist, world, device_index, full=True
     n = x_train.shape[0]
     net.compile(loss="categorical_crossentropy", metrics=["accuracy"], optimizer=Adam(lr=1e-3))
     eng = net._need_engine()
-    eng._ensure_capacity(BATCH)
+    eng._ensure_capacity(BATCH, BATCH)
     eng._set_data("train", x_train, y_train)
     perm = torch.from_numpy(np.random.default_rng(1237).permutation(n).astype(np.int32))
     with torch.cuda.stream(eng.stream):
         eng.data["train"][2].copy_(perm)
     eng._sync_lr()
     steps_per_epoch = n // BATCH
+    done_in_epoch = [0]
+    graph = eng._graph("train", BATCH)
 
     def run(k):
-        for i in range(k):
-            if i % steps_per_epoch == 0:
+        """k optimisation steps; the host side is one library call per stretch of an epoch (as Engine.fit does it)."""
+        while k > 0:
+            if done_in_epoch[0] == 0:
                 eng._zero_metrics(eng.state)            # epoch boundary: cursor back to 0
-            eng._step("train", BATCH)
+            stretch = min(k, steps_per_epoch - done_in_epoch[0])
+            eng.lib.fnet_graph_launch_n(graph, stretch, eng.sp)
+            done_in_epoch[0] = (done_in_epoch[0] + stretch) % steps_per_epoch
+            k -= stretch
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    # warm-up, and a first estimate of the step time: the timed region is the driver's `--steps` block repeated until
+    # it lasts at least MIN_TIMED_SECONDS (a 20-step block of a 40 us step is 0.8 ms: shorter than one clock sample)
     run(max(args.warmup, 3))
     barrier()
-    sampler = ClockSampler(device_index)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(eng.stream)
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record(eng.stream)
     run(args.steps)
-    e1.record(eng.stream)
+    p1.record(eng.stream)
     barrier()
-    ms = e0.elapsed_time(e1)
+    est_block_ms = max(p0.elapsed_time(p1), 1e-3)
+    repeats = int(min(max(1, math.ceil(1e3 * MIN_TIMED_SECONDS / est_block_ms)), 20000))
+    if world > 1:                                       # every rank runs the same number of blocks
+        t = torch.tensor([repeats], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        repeats = int(t.item())
+    sampler = ClockSampler(device_index)
+    sampler.wait_for_samples()
+    time.sleep(1.0)                                     # the sampler has been up for >= 1 s before the first event
+    barrier()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(repeats + 1)]
+    marks[0].record(eng.stream)
+    for r in range(repeats):
+        run(args.steps)
+        marks[r + 1].record(eng.stream)
+    barrier()
+    blocks = [marks[r].elapsed_time(marks[r + 1]) for r in range(repeats)]
+    total_ms = marks[0].elapsed_time(marks[-1])
     clocks = sampler.stop()
+    ms = total_ms / repeats                              # mean block: exactly `--steps` steps
     if world > 1:
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     out = {"ms": ms, "value": world * args.steps * BATCH / (ms / 1e3), "clocks": clocks,
+           "repeats": repeats, "timed_s": total_ms / 1e3, "block_ms_median": float(np.median(blocks)),
+           "block_ms_min": float(min(blocks)), "block_ms_max": float(max(blocks)),
            "launch_calls_per_step": eng.launches_per_step[("train", BATCH)],
            "params": net.count_params(), "layers": len(net.layers),
            "train_mflop_per_image": 3 * net.train_flops_per_image() / 1e6}
@@ -243,15 +306,27 @@ def measure_workload(workload, args, torch, dist, world, device_index, full=True
         return out, net
 
     # ---- end to end through the public API with host buffers
-    k = args.steps
+    k = max(args.steps, int(math.ceil(MIN_TIMED_SECONDS / max(ms / args.steps / 1e3, 1e-6))))
+    k = min(k, 20000)
+    (xu8, _), _ = synth.make_synth_uint8(synth.SHAPES[dataset], BATCH * 8, 0, synth.CLASSES[dataset])
+    xs_u8 = torch.from_numpy(np.ascontiguousarray(xu8)).pin_memory()          # the same pixels, before `/ 255`
     xs = torch.from_numpy(x_train[: BATCH * 8]).pin_memory()
     ys = torch.from_numpy(y_train[: BATCH * 8]).pin_memory()
-    def host_batches():
-        i = 0
-        while True:
-            lo = (i % 8) * BATCH
-            yield xs[lo: lo + BATCH], ys[lo: lo + BATCH]
-            i += 1
+
+    class HostBatches(object):
+        """An endless generator of pinned host batches; with `scale` set they are the uint8 pixels."""
+        def __init__(self, x, scale=None):
+            self.xh, self.i = x, 0
+            if scale is not None:
+                self.scale = scale
+
+        def __iter__(self):
+            return self
+
+        def __next__(self):
+            lo = (self.i % 8) * BATCH
+            self.i += 1
+            return self.xh[lo: lo + BATCH], ys[lo: lo + BATCH]
 
     def wall_max(seconds):
         if world > 1:
@@ -260,35 +335,47 @@ def measure_workload(workload, args, torch, dist, world, device_index, full=True
             seconds = float(t.item())
         return seconds
 
+    def streamed(feed):
+        net.fit_generator(feed, steps_per_epoch=max(args.warmup, 100), epochs=1)     # captures the slots' graphs, warms the host loop
+        barrier()
+        t0 = time.perf_counter()
+        hist = net.fit_generator(feed, steps_per_epoch=k, epochs=1)   # ends with the epoch's loss/accuracy read
+        barrier()
+        return wall_max(time.perf_counter() - t0), float(hist.history["loss"][-1])
+
     # (1) fit_generator: the reference's streaming call (helpers.py:163).  Every step uploads its own batch from
     # pinned host memory and returns its 16-byte result; the upload of step i+1 overlaps the kernels of step i.
-    feed = host_batches()
-    net.fit_generator(feed, steps_per_epoch=max(args.warmup, 100), epochs=1)     # captures both slots' graphs, warms the host loop
-    barrier()
-    t0 = time.perf_counter()
-    hist = net.fit_generator(feed, steps_per_epoch=k, epochs=1)       # ends with the epoch's loss/accuracy read
-    barrier()
-    streamed_s = wall_max(time.perf_counter() - t0)
+    # (a) the batch travels as the dataset's uint8 pixels and is divided by 255 on the device (what
+    # tensorflow_generator.py:310-313 does on the host); (b) the batch travels as float32, already scaled.
+    u8_s, u8_loss = streamed(HostBatches(xs_u8, scale=255.0))
+    f32_s, f32_loss = streamed(HostBatches(xs))
     # (2) train_on_batch: one blocking call per step (upload, step, result, wait)
+    kb = min(k, 2000)
     for i in range(3):
-        net_loss = eng.train_on_batch(xs[:BATCH], ys[:BATCH])
+        eng.train_on_batch(xs[:BATCH], ys[:BATCH])
     barrier()
     t0 = time.perf_counter()
-    for i in range(k):
+    for i in range(kb):
         lo = (i % 8) * BATCH
-        net_loss = eng.train_on_batch(xs[lo: lo + BATCH], ys[lo: lo + BATCH])
+        eng.train_on_batch(xs[lo: lo + BATCH], ys[lo: lo + BATCH])
     barrier()
     blocking_s = wall_max(time.perf_counter() - t0)
-    out["e2e"] = {"value": world * k * BATCH / streamed_s, "unit": "images/s",
-                  "h2d_bytes_per_step": int(BATCH * (np.prod(x_train.shape[1:]) + y_train.shape[1]) * 4),
-                  "d2h_bytes_per_step": 16, "last_loss": float(hist.history["loss"][-1]),
-                  "api": "Network.fit_generator on pinned host batches (3-slot pipelined feed)",
-                  "train_on_batch_value": world * k * BATCH / blocking_s,
-                  "train_on_batch_note": "same steps through the blocking per-step call (no overlap of upload and compute)"}
+    row = int(np.prod(x_train.shape[1:]))
+    out["e2e"] = {"value": world * k * BATCH / u8_s, "unit": "images/s",
+                  "h2d_bytes_per_step": int(BATCH * (row + y_train.shape[1] * 4)),
+                  "d2h_bytes_per_step": 16, "steps": k, "last_loss": u8_loss,
+                  "api": "Network.fit_generator on pinned host batches of uint8 pixels (generator.scale = 255: the "
+                         "`astype(float32) / 255` of tensorflow_generator.py:310-313 runs on the device), 3-slot pipelined feed",
+                  "fp32_feed_value": world * k * BATCH / f32_s,
+                  "fp32_feed_h2d_bytes_per_step": int(BATCH * (row + y_train.shape[1]) * 4),
+                  "fp32_feed_note": "the same call on float32 batches scaled on the host (4x the upload)",
+                  "train_on_batch_value": world * kb * BATCH / blocking_s,
+                  "train_on_batch_note": "float32 batches through the blocking per-step call (no overlap of upload and compute)"}
 
     # ---- per-kernel profile (CUDA events around every launch on the launching stream)
-    table = eng.profile_steps("train", BATCH, steps=min(args.steps, 50))
+    table = eng.profile_steps("train", BATCH, steps=50)
     out["profile"] = table
+    out["profiled_steps"] = 50
 
     # ---- one whole candidate: build + compile + 1 epoch + validation + evaluate (rank-local)
     from tensorflow_generator import TensorflowGenerator
@@ -305,29 +392,39 @@ def measure_workload(workload, args, torch, dist, world, device_index, full=True
             product = ProductSet(os.path.join(ROOT, source)).format_products()[index][0]
     net.release()
     cycles = []
-    for _ in range(2):                                   # second cycle = steady state (dataset resident)
+    for _ in range(3):                                   # later cycles = steady state (dataset resident)
         barrier()
         t0 = time.perf_counter()
         with quiet():
-            gen = TensorflowGenerator(product, epochs=1, dataset=dataset, data_augmentation=False, batch_size=BATCH)
+            gen = TensorflowGenerator(copy.deepcopy(product), epochs=1, dataset=dataset, data_augmentation=False, batch_size=BATCH)
         barrier()
         cycles.append(time.perf_counter() - t0)
+    timing = dict(gen.model.model._engine.timing)
     out["candidate_cycle_s"] = cycles[-1]
     out["candidate_accuracy"] = float(gen.accuracy)
+    out["candidate_phases"] = {
+        "train_steps": timing["train_steps"], "train_s": timing["train_s"], "capture_s": timing["capture_s"],
+        "alloc_s": timing["alloc_s"], "validation_and_evaluate_s": timing["eval_s"], "eval_steps": timing["eval_steps"],
+        "build_and_host_s": cycles[-1] - timing["train_s"] - timing["eval_s"] - timing["alloc_s"],
+        "train_us_per_step": 1e6 * (timing["train_s"] - timing["capture_s"]) / max(timing["train_steps"], 1),
+        "note": "host seconds; train_s spans the enqueue of the whole epoch to the read of its loss (it contains "
+                "capture_s, the one-off capture of the train graphs); eval = validation after the epoch + final evaluate"}
     return out, net
 
 
-def run_population_bench(args, dist, world, rank):
-    """A fixed population (nas_5_5_10 sample) sharded by candidate over the ranks: build + 1 epoch + evaluate each."""
+POPULATION_FILE = "featurenet_b200/data/nas_5_5_10_pop32_seed7.pdt"
+
+
+def run_population_bench(args, dist, world, rank, n_train, n_test, epochs=1):
+    """A fixed population (nas_5_5_10 sample) sharded by candidate over the ranks: build + train + evaluate each."""
     from featurenet_b200 import population as pop
     from featurenet_b200 import synth
     from model.keras_model import KerasFeatureModel
     from products_tree import ProductSet
     from tensorflow_generator import TensorflowGenerator
     import torch
-    n_train, n_test = 10000, 2000
     with quiet():
-        formatted = ProductSet(os.path.join(ROOT, "featurenet_b200/data/nas_5_5_10_pop32_seed7.pdt")).format_products()
+        formatted = ProductSet(os.path.join(ROOT, POPULATION_FILE)).format_products()
         # weak scaling: the same `--population` candidates PER GPU (the sample repeated), so that the number of
         # candidates grows with the box and the makespan is not bound by the single heaviest candidate
         formatted = formatted[: args.population] * world
@@ -336,19 +433,21 @@ def run_population_bench(args, dist, world, rank):
     TensorflowGenerator.X_train, TensorflowGenerator.Y_train = x_train, y_train
     TensorflowGenerator.X_test, TensorflowGenerator.Y_test = x_test, y_test
     TensorflowGenerator.input_shape = synth.SHAPES["cifar"]
-    costs = []
+    costs, mem, buildable = [], [], 0
     for product, _ in formatted:
         with quiet():
-            import copy
             net = KerasFeatureModel.parse_feature_model(copy.deepcopy(product)).build(synth.SHAPES["cifar"], 10)
-        costs.append(pop.estimate_cost(net, n_train, n_test, 1) if net else 1.0)
+        costs.append(pop.estimate_cost(net, n_train, n_test, epochs) if net else 1.0)
+        mem.append(pop.estimate_bytes(net, BATCH, n_test) if net else 0)
+        buildable += 1 if net else 0
 
-    import copy
     workers = max(1, args.resident)
+    free_bytes, _ = torch.cuda.mem_get_info()
+    budget = pop.MemoryBudget(int(0.8 * free_bytes)) if workers > 1 else None
 
     def train_one(index, item):
         product, original = copy.deepcopy(item)        # parsing reverses the product's children in place
-        return pop.train_product(product, "cifar", epochs=1, batch_size=BATCH, product_features=original,
+        return pop.train_product(product, "cifar", epochs=epochs, batch_size=BATCH, product_features=original,
                                  shared_gpu=workers > 1)
 
     def one_pass():
@@ -358,17 +457,22 @@ def run_population_bench(args, dist, world, rank):
         t0 = time.perf_counter()
         with quiet():
             res = pop.run_population(formatted, train_one, costs, rank=rank, world_size=world,
-                                     dist=dist if world > 1 else None, workers=workers)
+                                     dist=dist if world > 1 else None, workers=workers, mem_bytes=mem, budget=budget)
         torch.cuda.synchronize()
         return res, pop.max_over_ranks(time.perf_counter() - t0, dist if world > 1 else None, device="cuda")
 
     _, first_seconds = one_pass()      # first pass also pays one-off costs: lazy kernel loading, first allocations
     results, seconds = one_pass()      # steady state, what a long evolution run sees
     valid = [r for _, r in results if r.get("valid")]
-    return {"candidates": len(results), "valid": len(valid), "seconds": seconds, "first_pass_seconds": first_seconds,
-            "resident_per_gpu": workers,
+    errors = [{"candidate": i, "rank": r.get("rank"), "error": str(r.get("error"))[:300]}
+              for i, r in results if r.get("error") and not r.get("valid")]
+    retried = sum(1 for _, r in results if r.get("retried_alone_after"))
+    return {"candidates": len(results), "valid": len(valid), "expected_valid": buildable, "errors": errors,
+            "retried_alone": retried, "seconds": seconds, "first_pass_seconds": first_seconds,
+            "resident_per_gpu": workers, "epochs": epochs,
             "candidates_per_hour": 3600.0 * len(results) / seconds, "scaling": "weak (%d candidates per GPU, LPT-sharded over all ranks)" % args.population,
-            "what": "nas_5_5_10 seed-7 sample: build + 1 epoch on %d synthetic CIFAR-shape images + evaluate on %d" % (n_train, n_test),
+            "what": "nas_5_5_10 seed-7 sample (%d products, %d buildable): build + %d epoch(s) on %d synthetic CIFAR-shape images + "
+                    "validation + evaluate on %d" % (len(results), buildable, epochs, n_train, n_test),
             "mean_accuracy": float(np.mean([r["accuracy"] for r in valid])) if valid else 0.0,
             "per_rank_candidates": [sum(1 for _, r in results if r.get("rank") == k) for k in range(world)]}
 
@@ -384,13 +488,17 @@ def roofline_from(table, pk):
         achieved, peak, unit, bound = row["flops"] / secs / 1e12, pk["tflops"], "TFLOP/s", "tensor"
     else:
         achieved, peak, unit, bound = row["bytes"] / secs / 1e9, pk["hbm_gbs"], "GB/s", "hbm"
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    # dram bytes per launch of this kernel from a committed `ncu --set full` capture of this program, when there is
+    # one for the kernel that is dominant today (profiles/r2_traffic.json names the capture); otherwise null
+    traffic, traffic_source = None, None
+    tpath = os.path.join(ROOT, "profiles", "r2_traffic.json")
     if os.path.isfile(tpath):
         with open(tpath) as handle:
-            traffic = json.load(handle).get(label)
+            entry = json.load(handle).get(label)
+        if entry:
+            traffic, traffic_source = entry.get("dram_bytes_per_launch"), entry.get("source")
     return {"bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
-            "traffic": traffic, "kernel": label, "launches": row["launches"],
+            "traffic": traffic, "traffic_source": traffic_source, "kernel": label, "launches": row["launches"],
             "avg_us": 1e3 * row["ms_total"] / row["launches"], "share_of_step": row["ms_total"] / total_ms,
             "algorithmic_bytes_per_launch": row["bytes"] / row["launches"],
             "algorithmic_flops_per_launch": row["flops"] / row["launches"], "peak_source": pk["source"],
@@ -409,7 +517,10 @@ def run_ours(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if args.dp:
+        return run_dp(args, torch, dist, world, rank, local)
     t_wall = time.perf_counter()
+    math_mode = os.environ.get("FNET_PRECISION", "auto").lower()
     main, net = measure_workload(args.workload, args, torch, dist, world, local, full=True)
     extra = {}
     if rank == 0 and world == 1 and not args.quick:
@@ -434,43 +545,49 @@ def run_ours(args):
                 else:
                     os.environ["FNET_PRECISION"] = saved
                 extra[other]["ms_per_step_other_modes"] = by_mode
-    population = run_population_bench(args, dist, world, rank) if args.population > 0 else None
-    if population is not None and world == 1 and not args.quick:
-        # the same population in the two tensor-core modes, reported beside the fp32 figure
-        saved = os.environ.get("FNET_PRECISION")
-        by_mode = {}
-        for mode in ("fp32", "tf32x3", "tf32"):
-            os.environ["FNET_PRECISION"] = mode
-            by_mode[mode] = run_population_bench(args, dist, world, rank)["candidates_per_hour"]
-        if saved is None:
-            os.environ.pop("FNET_PRECISION", None)
-        else:
-            os.environ["FNET_PRECISION"] = saved
-        population["candidates_per_hour_other_modes"] = by_mode
+    population = population_small = None
+    if args.population > 0:
+        # BASELINE configs[2..3]: the population on the full-size synthetic set (50 000 / 10 000 images)
+        population = run_population_bench(args, dist, world, rank, 50000, 10000, epochs=args.population_epochs)
+        if not args.quick:
+            population_small = run_population_bench(args, dist, world, rank, 10000, 2000, epochs=1)
+    # every rank holds the same gathered results, so every rank takes the same decision
+    for name, p in (("population", population), ("population_small", population_small)):
+        if p is not None and p["valid"] != p["expected_valid"]:
+            if rank == 0:
+                sys.stderr.write("bench.py: %s trained %d of %d buildable candidates; errors: %s\n"
+                                 % (name, p["valid"], p["expected_valid"], json.dumps(p["errors"])))
+                sys.stderr.write("bench.py: refusing to report a throughput that lost candidates\n")
+            if world > 1:
+                dist.barrier()
+                dist.destroy_process_group()
+            raise SystemExit(3)
     if rank == 0:
-        pk = peaks()
+        pk = peaks(math_mode)
         line = {
             "metric": METRIC, "value": main["value"], "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": main["ms"] / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "f32 (tf32x3 on tensor cores)"}.get(os.environ.get("FNET_PRECISION", "auto").lower(), "f32"), "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][3], "batch": BATCH, "optimizer": "adam(1e-3)",
-                       "math": os.environ.get("FNET_PRECISION", "auto").lower() +
-                               " (auto = fp32 accuracy: FFMA or three-MMA tf32 split per product, both asserted <= 2e-5 of the float64 oracle)",
-                       "parallelism": "candidate-sharded x%d (no collective)" % world,
-                       "l2": "inputs larger than L2: the 614 MB resident dataset is streamed batch by batch; "
-                             "activations and weights are step-resident by design",
-                       "params": main["params"], "layers": main["layers"],
-                       "train_mflop_per_image": main["train_mflop_per_image"]},
+            "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "f32 (tf32x3 on tensor cores)", "bf16": "bf16"}.get(math_mode, "f32"), "data": "synthetic",
+            "config": config_for(args.workload, world),
+            "math": math_mode + " (auto = fp32 accuracy: FFMA or three-MMA tf32 split per product, both asserted <= 2e-5 of the float64 oracle)",
+            "candidate": {"params": main["params"], "layers": main["layers"], "train_mflop_per_image": main["train_mflop_per_image"]},
+            "timing": {"repeats": main["repeats"], "timed_s": main["timed_s"], "block_ms_median": main["block_ms_median"],
+                       "block_ms_min": main["block_ms_min"], "block_ms_max": main["block_ms_max"],
+                       "what": "the `--steps` block repeated `repeats` times back to back between CUDA events (>= %.1f s in all); "
+                               "ms_per_step = mean block / steps, max over ranks; the clock sampler runs >= 1 s before the first event"
+                               % MIN_TIMED_SECONDS},
             "clocks": main["clocks"], "e2e": main["e2e"],
             "gpu_launches": main["launch_calls_per_step"] * args.steps,
             "roofline": roofline_from(main["profile"], pk),
             "candidates_per_hour": world * 3600.0 / main["candidate_cycle_s"],
             "candidate_cycle": {"seconds": main["candidate_cycle_s"], "accuracy": main["candidate_accuracy"],
-                                "what": "build + compile + 1 epoch (full-size synthetic set) + validation + evaluate"},
+                                "what": "build + compile + 1 epoch (full-size synthetic set) + validation + evaluate",
+                                "phases": main["candidate_phases"]},
             "profile": {k: {"launches": v["launches"], "ms_total": round(v["ms_total"], 4)}
                         for k, v in sorted(main["profile"].items(), key=lambda kv: -kv[1]["ms_total"])},
             "other_workloads": extra,
             "population": population,
+            "population_small": population_small,
         }
         if world == 1:
             _, net2, dataset = build_candidate(args.workload)
@@ -479,9 +596,8 @@ def run_ours(args):
                                     "sample": "%d train steps of batch %d in %.1f s through oracle/torch_cpu.py"
                                               % (done, BATCH, elapsed)}
         # whole-step roofline: every launch at the better of its two ceilings vs the measured step
-        profiled_steps = max(1, min(args.steps, 50))
         ideal_s = sum(max(r["flops"] / (pk["tflops"] * 1e12), r["bytes"] / (pk["hbm_gbs"] * 1e9))
-                      for r in main["profile"].values()) / profiled_steps
+                      for r in main["profile"].values()) / main["profiled_steps"]
         line["roofline"]["whole_step"] = {
             "ideal_us": 1e6 * ideal_s, "measured_us": 1e3 * line["ms_per_step"], "frac": 1e3 * ideal_s / line["ms_per_step"],
             "formula": "sum over launches of max(flops / peak_tensor, bytes / peak_hbm), over the measured step time"}
@@ -503,6 +619,9 @@ def main():
     ap.add_argument("--quick", action="store_true", help="skip the secondary workloads")
     ap.add_argument("--population", type=int, default=32, help="candidates of the sharded population run (0 = skip)")
     ap.add_argument("--resident", type=int, default=8, help="candidates kept resident per GPU in the population run")
+    ap.add_argument("--population-epochs", type=int, default=1, help="epochs per candidate of the full-size population run")
+    ap.add_argument("--dp", action="store_true", help="data-parallel training of ONE large candidate (the `keras` "
+                    "template) over all ranks: NCCL all-reduce of the gradient arena every step")
     args = ap.parse_args()
     claim_stdout()
     if args.impl == "reference":

@@ -8,12 +8,27 @@ An out-of-memory candidate yields ``(None, history)`` instead of raising.
 """
 import math
 import os
+import threading
 
 import numpy as np
 import torch
 
 from featurenet_b200.callbacks import (Callback, EarlyStopping, LearningRateScheduler, ModelCheckpoint,  # noqa: F401
                                        ReduceLROnPlateau)
+
+
+# The reference swallows an out-of-memory candidate (helpers.py:172-174: print, model = None).  The convention is kept;
+# the reason is also left here, per host thread, for a scheduler that trains several candidates side by side and has
+# to tell "does not fit this GPU" from "did not fit beside its neighbours" (featurenet_b200/population.py).
+_failure = threading.local()
+
+
+def clear_failure():
+    _failure.text = None
+
+
+def last_failure():
+    return getattr(_failure, "text", None)
 
 
 class TimedStopping(Callback):
@@ -83,5 +98,6 @@ def train_model(model, x_train, y_train, x_test, y_test, epochs, batch_size, sch
         model = checkpoint.restore()          # keras.models.load_model(best checkpoint); os.remove(...)
     except torch.cuda.OutOfMemoryError as e:
         print("model exhausted memory while training, error {}".format(e))
+        _failure.text = "OutOfMemoryError: {}".format(str(e)[:300])
         model = None
     return model, history

@@ -11,9 +11,8 @@ Differences that cannot be avoided on this box, all loud:
   * datasets: ``keras.datasets`` needs a download; ``init_dataset`` uses ``FNET_DATA_DIR/<name>.npz``
     (keys x_train, y_train, x_test, y_test; uint8 images, integer labels) when present, otherwise a
     synthetic set of the same shape and size (featurenet_b200.synth), and says which;
-  * robustness (``eval_robustness``): the L2 gradient attacks (fgsm, pgd) run on the engine
-    (featurenet_b200/robustness.py); Carlini-Wagner and CLEVER of SURVEY.md 8(f) item 1 are not built:
-    the scores stay 0 and a notice is printed;
+  * robustness (``eval_robustness``): all four scores (clever, pgd, cw, fgsm) run on the engine
+    (featurenet_b200/robustness.py), restated from ART 0.9.0's published algorithms (ART is un-vendored);
   * ``export_png`` needs Graphviz ``dot``; it is a no-op after the first failure, as in the reference.
 """
 from __future__ import absolute_import, division, print_function, unicode_literals
@@ -116,6 +115,7 @@ class TensorflowGenerator(object):
                     self.model.metrics[m] = f(keras_model)
 
             self.params = self.model.nb_params
+            self.flops = self.model.nb_flops
             self.training_time = training_time
             self.accuracy = self.model.accuracy
             self.history = (history.history["acc"], history.history["val_acc"])
@@ -200,6 +200,9 @@ class TensorflowGenerator(object):
         keras_model.compile(loss="categorical_crossentropy", metrics=["accuracy"], optimizer=Adam(lr=lr_schedule(0)))
         TensorflowGenerator._last_network = keras_model
         model.nb_params = keras_model.count_params()
+        # the reference leaves nb_flops at 0 (its get_flops() is never called, tensorflow_generator.py:272); the vector
+        # consumers (ui/back, plots) get the analytic training cost per image: 3 x the forward multiply-adds x 2
+        model.nb_flops = 3 * keras_model.train_flops_per_image()
         print("model blocks,layers,params,flops: {} ".format(model.to_kerasvector()))
         return keras_model
 

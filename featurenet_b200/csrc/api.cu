@@ -34,6 +34,11 @@ __global__ void step_end_kernel(int32_t *state, int32_t batch) {
     }
 }
 
+__global__ void state_set_lr_kernel(int32_t *state, float lr) {
+    pdl_prologue();
+    if (threadIdx.x == 0 && blockIdx.x == 0) state[2] = __float_as_int(lr);
+}
+
 __global__ void fill_kernel(int64_t n, float value, float *__restrict__ dst) {
     pdl_prologue();
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -103,6 +108,37 @@ __global__ void gather_batch_kernel(int32_t batch, int64_t x_row, int64_t y_row,
     }
 }
 
+// A batch that arrived from the host as uint8 pixels: x_dst = float(x_src) / scale (numpy's rounding, see
+// u8_to_f32_kernel), targets copied as they are, lr_t of the step computed by the first thread -- the first launch
+// of a streamed train step.  16 pixels per thread per pass (one 16-byte load, four 16-byte stores).
+__global__ void feed_batch_u8_kernel(int64_t x_elems, int64_t y_elems, int32_t *__restrict__ state,
+                                     const uint8_t *__restrict__ x_src, float scale, const float *__restrict__ y_src,
+                                     float *__restrict__ x_dst, float *__restrict__ y_dst, int begin_step, float beta1,
+                                     float beta2) {
+    pdl_prologue();
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+    if (begin_step && tid == 0) {
+        double t = (double)(state[0] + 1);
+        double lr = (double)__int_as_float(state[2]);
+        state[3] = __float_as_int((float)(lr * sqrt(1.0 - pow((double)beta2, t)) / (1.0 - pow((double)beta1, t))));
+    }
+    const int64_t vec = x_elems >> 4;
+    const uint4 *s16 = reinterpret_cast<const uint4 *>(x_src);
+    float4 *d4 = reinterpret_cast<float4 *>(x_dst);
+    for (int64_t i = tid; i < vec; i += stride) {
+        const uint4 q = __ldg(s16 + i);
+        const uint32_t words[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t wd = words[k];
+            d4[i * 4 + k] = make_float4((float)(wd & 255u) / scale, (float)((wd >> 8) & 255u) / scale,
+                                        (float)((wd >> 16) & 255u) / scale, (float)(wd >> 24) / scale);
+        }
+    }
+    for (int64_t i = (vec << 4) + tid; i < x_elems; i += stride) x_dst[i] = (float)x_src[i] / scale;
+    for (int64_t i = tid; i < y_elems; i += stride) y_dst[i] = __ldg(y_src + i);
+}
+
 }  // namespace fnet
 
 using namespace fnet;
@@ -140,6 +176,26 @@ int fnet_step_end(int32_t *state, int32_t batch, void *stream) {
     FNET_REQUIRE(state != nullptr, "fnet_step_end: null state");
     launch_pdl(step_end_kernel, dim3(1), dim3(32), 0, as_stream(stream), state, batch);
     return check_launch("fnet_step_end");
+}
+
+int fnet_state_set_lr(int32_t *state, float lr, void *stream) {
+    FNET_REQUIRE(state != nullptr, "fnet_state_set_lr: null state");
+    launch_pdl(state_set_lr_kernel, dim3(1), dim3(32), 0, as_stream(stream), state, lr);
+    return check_launch("fnet_state_set_lr");
+}
+
+int fnet_feed_batch_u8(int32_t batch, int64_t x_row, int64_t y_row, int32_t *state, const uint8_t *x_src, float scale,
+                       const float *y_src, float *x_dst, float *y_dst, int begin_step, float beta1, float beta2,
+                       void *stream) {
+    FNET_REQUIRE(batch >= 0 && x_row > 0 && y_row > 0 && scale != 0.f, "fnet_feed_batch_u8: bad sizes");
+    FNET_REQUIRE(state && x_src && y_src && x_dst && y_dst, "fnet_feed_batch_u8: null pointer");
+    FNET_REQUIRE(((reinterpret_cast<uintptr_t>(x_src) | reinterpret_cast<uintptr_t>(x_dst)) & 15) == 0,
+                 "fnet_feed_batch_u8: 16-byte aligned buffers needed");
+    if (batch == 0) return begin_step ? fnet_step_begin(state, beta1, beta2, stream) : FNET_OK;
+    const int64_t x_elems = (int64_t)batch * x_row, y_elems = (int64_t)batch * y_row;
+    launch_pdl(feed_batch_u8_kernel, dim3(stream_grid(ceil_div<int64_t>(x_elems, 16), 256)), dim3(256), 0, as_stream(stream),
+               x_elems, y_elems, state, x_src, scale, y_src, x_dst, y_dst, begin_step, beta1, beta2);
+    return check_launch("fnet_feed_batch_u8");
 }
 
 int fnet_fill(int64_t n, float value, float *dst, void *stream) {
@@ -193,6 +249,14 @@ int fnet_graph_end(void *stream, void **graph_exec_out) {
 int fnet_graph_launch(void *graph_exec, void *stream) {
     FNET_REQUIRE(graph_exec != nullptr, "fnet_graph_launch: null graph");
     FNET_CUDA(cudaGraphLaunch(reinterpret_cast<cudaGraphExec_t>(graph_exec), as_stream(stream)));
+    return FNET_OK;
+}
+
+int fnet_graph_launch_n(void *graph_exec, int32_t n, void *stream) {
+    FNET_REQUIRE(graph_exec != nullptr && n >= 0, "fnet_graph_launch_n: null graph or negative count");
+    cudaGraphExec_t exec = reinterpret_cast<cudaGraphExec_t>(graph_exec);
+    cudaStream_t s = as_stream(stream);
+    for (int32_t i = 0; i < n; ++i) FNET_CUDA(cudaGraphLaunch(exec, s));
     return FNET_OK;
 }
 

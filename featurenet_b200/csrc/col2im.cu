@@ -42,11 +42,7 @@ __global__ void __launch_bounds__(256) col2im_kernel(ConvGeom g, const float *__
 
 // bytes of T, or 0 when this formulation is not the better one
 size_t col2im_t_bytes(const ConvGeom &g) {
-    static int mode = -1;                                    // FNET_COL2IM=0 disables (A/B measurements)
-    if (mode < 0) {
-        const char *e = getenv("FNET_COL2IM");
-        mode = (e && e[0] == '0') ? 0 : 1;
-    }
+    static const int mode = env_switch("FNET_COL2IM", 1);    // FNET_COL2IM=0 disables (A/B measurements)
     long long taps = (long long)g.kh * g.kw;
     if (!mode || taps < 4 || g.C > 16 || g.K < 32) return 0;   // few output channels: the implicit GEMM is cheaper (K = 12: 54 vs 107 us)
     long long mo = (long long)g.B * g.Ho * g.Wo;

@@ -6,6 +6,7 @@
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
+#include <atomic>
 #include "../../include/fnet.h"
 
 namespace fnet {
@@ -58,13 +59,32 @@ __device__ __forceinline__ void pdl_prologue() {
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
+// An on/off switch read from the environment.  Callers keep the result in a function-local `static const`, whose
+// initialisation the language makes thread-safe: libfnet is driven by several host threads at once (one per resident
+// candidate, featurenet_b200/population.py), and ctypes releases the GIL around every call.
+inline int env_switch(const char *name, int fallback) {
+    const char *e = getenv(name);
+    if (!e || !e[0]) return fallback;
+    return e[0] == '0' ? 0 : 1;
+}
+
 inline bool pdl_enabled() {
-    static int mode = -1;
-    if (mode < 0) {
-        const char *e = getenv("FNET_PDL");
-        mode = (e && e[0] == '0') ? 0 : 1;
-    }
+    static const int mode = env_switch("FNET_PDL", 1);
     return mode == 1;
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the (kernel, device) pair.  `done` is one bit per device
+// ordinal, one mask per kernel instantiation; setting the attribute twice from two racing threads is harmless.
+template <typename Kernel>
+inline cudaError_t allow_dynamic_smem(Kernel kernel, int bytes, std::atomic<uint64_t> &done) {
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return e;
+    const uint64_t bit = 1ull << (device & 63);
+    if (done.load(std::memory_order_acquire) & bit) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) done.fetch_or(bit, std::memory_order_release);
+    return e;
 }
 
 template <typename... KArgs, typename... Args>

@@ -533,17 +533,20 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+static EncodeTiledFn lookup_encode_tiled() {
+    void *sym = nullptr;
+    cudaDriverEntryPointQueryResult status;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &status) == cudaSuccess &&
+        status == cudaDriverEntryPointSuccess)
+        return reinterpret_cast<EncodeTiledFn>(sym);
+    return nullptr;
+}
+
+// looked up once; a function-local static is initialised exactly once even when several host threads arrive together
+// (a hand-rolled `tried` flag let a second thread see "looked up" before the pointer was stored: it then sized its
+// workspace for the non-TMA kernels and failed at launch, when the TMA kernel was chosen after all)
 static EncodeTiledFn encode_tiled() {
-    static EncodeTiledFn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void *sym = nullptr;
-        cudaDriverEntryPointQueryResult status;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &status) == cudaSuccess &&
-            status == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(sym);
-    }
+    static const EncodeTiledFn fn = lookup_encode_tiled();
     return fn;
 }
 
@@ -671,19 +674,11 @@ static TgWgradPlan tg_wgrad_plan(const ConvGeom &g, bool x3) {
 
 // product: 0 forward (N = g.K, reduction g.C), 1 data gradient (N = g.C, reduction g.K), 2 filter gradient
 bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
-    static int mode = -1;                                    // FNET_TMA=0 disables (A/B measurements)
-    if (mode < 0) {
-        const char *e = getenv("FNET_TMA");
-        mode = (e && e[0] == '0') ? 0 : 1;
-    }
+    static const int mode = env_switch("FNET_TMA", 1);      // FNET_TMA=0 disables (A/B measurements)
     if (!mode || (math != FNET_MATH_TF32 && math != FNET_MATH_TF32X3) || product > 2 || !encode_tiled()) return false;
     if (!is_plain_gemm(g)) {
         // k x k convolutions, stride 1: forward and data gradient through shifted 4-D boxes (TgConv)
-        static int conv_mode = -1;                           // FNET_TMA_CONV=0 disables (A/B measurements)
-        if (conv_mode < 0) {
-            const char *e = getenv("FNET_TMA_CONV");
-            conv_mode = (e && e[0] == '0') ? 0 : 1;
-        }
+        static const int conv_mode = env_switch("FNET_TMA_CONV", 1);   // FNET_TMA_CONV=0 disables (A/B measurements)
         int bw, bh, bb;
         if (!conv_mode || g.sh != 1 || g.sw != 1 || (g.C & 3) || (g.K & 3)) return false;
         if (product == 2) {
@@ -695,11 +690,10 @@ bool tma_gemm_supported(const ConvGeom &g, int math, int product) {
         const long long Mc = product == 0 ? (long long)g.B * g.Ho * g.Wo : (long long)g.B * g.H * g.W;
         const long long Nc = product == 0 ? g.K : g.C;
         if (Nc < 16 || Mc > 0x7fffffffLL || (long long)g.kh * g.kw > 64) return false;
-        static long long min_tiles = -1;                     // FNET_TMA_MIN_TILES: experiments with partial waves
-        if (min_tiles < 0) {
+        static const long long min_tiles = [] {             // FNET_TMA_MIN_TILES: experiments with partial waves
             const char *e = getenv("FNET_TMA_MIN_TILES");
-            min_tiles = e ? atoll(e) : 32;
-        }
+            return e ? atoll(e) : 32LL;
+        }();
         const long long m_tiles = ceil_div<long long>(Mc, TG_BM);
         const long long tiles = m_tiles * ceil_div<long long>(Nc, tg_bn_for(Nc, m_tiles));
         const long long kt = (long long)g.kh * g.kw * ceil_div<long long>(product == 0 ? g.C : g.K, TG_BK);
@@ -746,11 +740,10 @@ static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, c
     while (tmem_cols < 2 * BN) tmem_cols *= 2;
     const int stages = tg_stages(BN, X3, TG_STAGES, 0);
     const size_t smem = (size_t)stages * (X3 ? 2 : 1) * (TG_A_BYTES + BN * TG_BK * 4) + 1024;
-    static bool configured = false;                          // one per instantiation
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(tma_gemm_kernel<P, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TG_SMEM_LIMIT);
+    static std::atomic<uint64_t> configured{0};              // one mask per instantiation, one bit per device
+    {
+        cudaError_t e = allow_dynamic_smem(tma_gemm_kernel<P, X3>, TG_SMEM_LIMIT, configured);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
-        configured = true;
     }
     const unsigned grid = (unsigned)(total < kNumSMs ? total : kNumSMs);
     launch_pdl(tma_gemm_kernel<P, X3>, dim3(grid), dim3(X3 ? TG_THREADS_X3 : TG_THREADS), smem, stream, map_a, map_b, p, (int)M, (int)N, (int)Kg, BN,
@@ -828,12 +821,11 @@ int tma_gemm_wgrad(const ConvGeom &g, int math, const float *x, const float *dz,
         set_error("%s: cuTensorMapEncodeTiled failed", what);
         return FNET_ERR_CUDA;
     }
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(tma_wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TG_SMEM_LIMIT);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(tma_wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TG_SMEM_LIMIT);
+    static std::atomic<uint64_t> configured_plain{0}, configured_x3{0};
+    {
+        cudaError_t e = allow_dynamic_smem(tma_wgrad_kernel<false>, TG_SMEM_LIMIT, configured_plain);
+        if (e == cudaSuccess) e = allow_dynamic_smem(tma_wgrad_kernel<true>, TG_SMEM_LIMIT, configured_x3);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
-        configured = true;
     }
     WgradProblem p{g, x, dz, dw, dbias, g.kh * g.kw * g.C};
     const int M = g.kh * g.kw * g.C + (dbias ? 1 : 0);

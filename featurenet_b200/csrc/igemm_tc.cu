@@ -428,22 +428,17 @@ static TcPlan tc_plan(long long M, long long N, long long Kg, bool x3 = false) {
 }
 
 static int tc_layout_mode() {
-    static int mode = -1;
-    if (mode < 0) {
-        const char *e = getenv("FNET_TC_LAYOUT");      // 0 = SWIZZLE_128B (default), 1 = no swizzle; for bring-up
-        mode = (e && e[0] == '1') ? 1 : 0;
-    }
+    static const int mode = env_switch("FNET_TC_LAYOUT", 0);     // 0 = SWIZZLE_128B (default), 1 = no swizzle; for bring-up
     return mode;
 }
 
 template <class P, int BN, int STAGES, int X3>
 static int tc_launch(const P &p, dim3 grid, size_t smem, int m, int n, int kg, int per, float *partial,
                      cudaStream_t stream, const char *what) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(tc_igemm_kernel<P, BN, STAGES, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static std::atomic<uint64_t> configured{0};              // one mask per instantiation, one bit per device
+    {
+        cudaError_t e = allow_dynamic_smem(tc_igemm_kernel<P, BN, STAGES, X3>, (int)smem, configured);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
-        configured = true;
     }
     launch_pdl(tc_igemm_kernel<P, BN, STAGES, X3>, dim3(grid), dim3(TC_THREADS), smem, stream, p, m, n, kg, per, partial, tc_layout_mode());
     return check_launch(what);

@@ -71,7 +71,7 @@ class DataParallelTrainer(object):
     def prepare(self, x, y, global_batch):
         eng = self.eng
         sizes, _ = split_batch(global_batch, self.world)
-        eng._ensure_capacity(max(max(sizes), 1, eng.capacity))
+        eng._ensure_capacity(max(max(sizes), 1), max(max(sizes), 1))
         eng._set_data("train", x, y)
 
     def set_epoch(self, order):

@@ -74,6 +74,10 @@ class SideLabel(str):
 
 
 class Engine(object):
+    # inference batches are as large as this many bytes of activations allow (at most 1000 rows): results do not depend
+    # on the batch, launches per evaluated image do; a bound on the whole footprint keeps co-resident candidates small
+    EVAL_ACT_BYTES = 1 << 30
+
     def __init__(self, net, device=None, math_mode=None, seed=None):
         if not torch.cuda.is_available():
             raise fl.FnetError("featurenet_b200 needs a CUDA device: there is no CPU execution path")
@@ -106,9 +110,13 @@ class Engine(object):
         self.seed = int(seed if seed is not None else int(os.environ.get("FNET_SEED", "0")) or
                         np.random.SeedSequence().entropy % (1 << 62))
         self.dropout_seed = (self.seed * 0x9E3779B97F4A7C15 + 0x1234567) & 0xFFFFFFFFFFFFFFFF
-        self.capacity = 0
+        self.capacity = 0             # rows the activation buffers hold (training AND inference batches)
+        self.grad_capacity = 0        # rows the gradient buffers hold (training / attack batches only)
+        self.generation = 0           # bumped whenever buffers that captured graphs point at are replaced
         self.graphs = {}
         self.programs = {}
+        # host seconds per phase of this candidate's life (bench.py prints them inside candidate_cycle)
+        self.timing = {"alloc_s": 0.0, "capture_s": 0.0, "train_s": 0.0, "eval_s": 0.0, "train_steps": 0, "eval_steps": 0}
         self.use_graphs = os.environ.get("FNET_NO_GRAPH", "0") != "1"
         self._plan_params()
         self._init_weights()
@@ -122,9 +130,12 @@ class Engine(object):
             self._metrics_host = torch.zeros(2, dtype=torch.int64).pin_memory()
             self._metrics_np = self._metrics_host.numpy()      # same pinned memory, cheap to read from Python
             self._metrics_seen = (0.0, 0)
-            self._lr_host = torch.zeros(1, dtype=torch.float32).pin_memory()
         self._lr_on_device = None
         self.timeline = None          # when a list: (label, start_event, end_event) per launch (profiling mode)
+        # the arenas above were zero-filled by kernels on the thread's CURRENT stream; this engine works on its own
+        # (non-blocking) stream, which must not overtake them -- with several candidates resident per GPU the fills can
+        # be queued behind other candidates' work for a long time
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))
 
     # ------------------------------------------------------------------ parameters
     def _plan_params(self):
@@ -232,11 +243,17 @@ class Engine(object):
             np.savez(handle, __order__=np.array(names), **arrays)
 
     # ------------------------------------------------------------------ activations
-    def _ensure_capacity(self, batch):
-        if batch <= self.capacity:
+    def _ensure_capacity(self, batch, grad_batch=0):
+        """Activation buffers for `batch` rows, gradient buffers (and what only a backward pass needs: pooling taps,
+        the separable convolution's inner gradient) for `grad_batch` rows.  Inference batches are larger than
+        training batches, and several candidates share one GPU: gradient memory follows the training batch only."""
+        if batch <= self.capacity and grad_batch <= self.grad_capacity:
             return
+        t_alloc = time.perf_counter()
+        self.stream.synchronize()             # launches that still use the old buffers
         self._drop_graphs()
-        self.capacity = batch
+        batch = self.capacity = max(batch, self.capacity)
+        gbatch = self.grad_capacity = max(grad_batch, self.grad_capacity)
         dev = self.device
         with torch.cuda.device(dev):
             f32 = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)
@@ -246,19 +263,20 @@ class Engine(object):
                 if node.kind == "flatten":
                     continue                       # a view of its input (resolved in _buf)
                 self.act[i] = f32(batch, *self.shape[i])
-                if node.kind != "input":
-                    self.gact[i] = f32(batch, *self.shape[i])
+                if node.kind != "input" and gbatch:
+                    self.gact[i] = f32(gbatch, *self.shape[i])
                 if node.kind == "maxpool":
-                    self.aux[i] = torch.empty((batch,) + self.shape[i], dtype=torch.uint8, device=dev)
+                    self.aux[i] = torch.empty((max(gbatch, 1),) + self.shape[i], dtype=torch.uint8, device=dev)
                 elif node.kind == "sepconv2d":
                     mid = self.shape[i][:2] + (self.shape[self.src[i][0]][2],)
-                    self.aux[i] = (f32(batch, *mid), f32(batch, *mid))
+                    self.aux[i] = (f32(batch, *mid), f32(max(gbatch, 1), *mid))
                 elif node.kind == "bn":
                     a = self.shape[i][node.cfg["axis"] - 1]
                     self.aux[i] = (f32(a), f32(a))
                 ws_bytes = max(ws_bytes, self._workspace_need(i, batch))
             self._alloc_workspace(ws_bytes)
             self.yb = f32(batch, self.n_out)
+        self.timing["alloc_s"] += time.perf_counter() - t_alloc
 
     def _alloc_workspace(self, need):
         """Two halves of `need` bytes: the main stream's scratch and the side stream's (they run concurrently)."""
@@ -266,6 +284,7 @@ class Engine(object):
         with torch.cuda.device(self.device):
             self.ws = torch.empty(2 * need, dtype=torch.uint8, device=self.device)
         self.ws_bytes = need
+        self.generation += 1
 
     def _workspace_need(self, i, batch):
         node, need = self.nodes[i], 0
@@ -631,8 +650,16 @@ class Engine(object):
             opt = self.net.optimizer
             b1, b2 = (opt.beta_1, opt.beta_2) if opt.kind == "adam" else (0.9, 0.999)
         fused_gather = kind in ("train", "eval")         # inputs + targets (+ lr_t) in one launch
-        ring_slot = int(kind[len("train_ring"):]) if kind.startswith("train_ring") else None
-        if ring_slot is not None:
+        ring_u8 = kind.startswith("train_ringu8_")
+        ring_slot = int(kind[len("train_ringu8_" if ring_u8 else "train_ring"):]) if kind.startswith("train_ring") else None
+        if ring_u8:
+            # the batch was uploaded as uint8 pixels: scale on the device while moving it into place
+            xs, ys = self.ring["x_u8"][ring_slot], self.ring["y"][ring_slot]
+            ops.append(("feed_batch_u8", L.fnet_feed_batch_u8,
+                        (batch, _prod(self.shape[0]), self.n_out, st, C.c_void_p(xs.data_ptr()), float(self.ring["scale"]),
+                         C.c_void_p(ys.data_ptr()), C.c_void_p(self.act[0].data_ptr()), C.c_void_p(self.yb.data_ptr()),
+                         1, b1, b2, sp)))
+        elif ring_slot is not None:
             # pipelined host feed: the batch was uploaded into slot `ring_slot` of the ring while the previous step
             # ran; the same launch as the resident path moves it into place (identity order, cursor stays 0)
             xs, ys = self.ring["x"][ring_slot], self.ring["y"][ring_slot]
@@ -763,6 +790,8 @@ class Engine(object):
             b = 4 * 2 * args[0] * args[1]
         elif label == "gather_batch":
             b = 4 * 2 * args[0] * (args[1] + args[2])
+        elif label == "feed_batch_u8":
+            b = args[0] * (5 * args[1] + 8 * args[2])
         elif label == "gather_shift_flip":
             b = 4 * 2 * args[0] * args[1] * args[2] * args[3]
         return f, b
@@ -801,6 +830,7 @@ class Engine(object):
         for g in self.graphs.values():
             self.lib.fnet_graph_destroy(g)
         self.graphs, self.programs = {}, {}
+        self.generation += 1
 
     def _step(self, kind, batch):
         """Enqueue one step (captured CUDA graph after the first, eager run)."""
@@ -836,22 +866,36 @@ class Engine(object):
 
     def _capture(self, ops):
         """Record a launch list into a CUDA graph (nothing executes until the graph is launched)."""
+        t0 = time.perf_counter()
         self.lib.fnet_graph_begin(self.sp)
+        handle = C.c_void_p()
         try:
             self._run_ops(ops)
-        finally:
-            handle = C.c_void_p()
-            self.lib.fnet_graph_end(self.sp, C.byref(handle))
+        except BaseException:
+            # close the capture without letting its own error replace the one that matters; a fork without its join
+            # leaves the side stream inside the (now invalid) capture, so both streams are replaced
+            try:
+                self.lib.fnet_graph_end(self.sp, C.byref(handle))
+                if handle.value:
+                    self.lib.fnet_graph_destroy(handle)
+            except fl.FnetError:
+                pass
+            self.stream = torch.cuda.Stream(device=self.device)
+            self.side = torch.cuda.Stream(device=self.device)
+            self.sp, self.sp2 = C.c_void_p(self.stream.cuda_stream), C.c_void_p(self.side.cuda_stream)
+            self._drop_graphs()               # programs hold the old stream handles
+            raise
+        self.lib.fnet_graph_end(self.sp, C.byref(handle))
+        self.timing["capture_s"] += time.perf_counter() - t0
         return handle
 
     # ------------------------------------------------------------------ host-side loop pieces
     def _sync_lr(self):
+        """The optimizer's learning rate lives in state[2]; a change is one stream-ordered launch that carries the
+        value as a kernel argument (SGDRScheduler changes it every batch: no host wait, no pinned scalar to keep alive)."""
         lr = float(self.net.optimizer.lr)
         if lr != self._lr_on_device:
-            self._lr_host[0] = lr
-            with torch.cuda.stream(self.stream):
-                self.state[2:3].view(torch.float32).copy_(self._lr_host, non_blocking=True)
-            self.stream.synchronize()      # the pinned scalar may be rewritten by the next call
+            self.lib.fnet_state_set_lr(C.c_void_p(self.state.data_ptr()), lr, self.sp)
             self._lr_on_device = lr
 
     def _set_data(self, split, x, y):
@@ -897,33 +941,39 @@ class Engine(object):
 
     def eval_batch_size(self, n):
         """Inference batch: results do not depend on it, so use large batches bounded by activation size."""
-        widest = max(_prod(s) for s in self.shape)
-        cap = max(32, (256 << 20) // (4 * widest))
+        per_image = 4 * sum(_prod(s) for i, s in enumerate(self.shape) if self.nodes[i].kind != "flatten")
+        cap = max(32, self.EVAL_ACT_BYTES // max(per_image, 1))
         return int(min(n, cap, 1000))
 
     def evaluate(self, x, y, batch_size=32):
         """keras Model.evaluate -> [loss, accuracy] in inference phase (tensorflow_generator.py:270)."""
+        t_eval = time.perf_counter()
         x, y = self._check_xy(x, y)
         n = x.shape[0]
         eb = self.eval_batch_size(n)
-        self._ensure_capacity(max(eb, self.capacity))
+        self._ensure_capacity(eb)
         self._set_data("eval", x, y)
         with torch.cuda.stream(self.stream):
             self.data["eval"][2].copy_(torch.arange(n, dtype=torch.int32, device=self.device))
         self._zero_metrics(self.state_eval)
-        done = 0
-        while done < n:
-            b = min(eb, n - done)
-            self._step("eval", b)
-            done += b
+        full = n // eb
+        if full and self.use_graphs and self.timeline is None:
+            self.lib.fnet_graph_launch_n(self._graph("eval", eb), full, self.sp)
+        else:
+            for _ in range(full):
+                self._step("eval", eb)
+        if n - full * eb:
+            self._step("eval", n - full * eb)
         loss, acc = self._read_metrics(n)
+        self.timing["eval_s"] += time.perf_counter() - t_eval
+        self.timing["eval_steps"] += -(-n // eb)
         return [loss, acc]
 
     def predict(self, x, batch_size=32):
         x = np.asarray(x, dtype=np.float32)
         n = x.shape[0]
         eb = self.eval_batch_size(n)
-        self._ensure_capacity(max(eb, self.capacity))
+        self._ensure_capacity(eb)
         out = np.empty((n, self.n_out), np.float32)
         last = len(self.nodes) - 1
         for lo in range(0, n, eb):
@@ -940,7 +990,7 @@ class Engine(object):
         if self.net.optimizer is None:
             raise RuntimeError("compile() the model first")
         b = x.shape[0]
-        self._ensure_capacity(max(b, self.capacity))
+        self._ensure_capacity(b, b)
         self._sync_lr()
         xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
         yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
@@ -986,7 +1036,7 @@ class Engine(object):
         x = np.ascontiguousarray(x, dtype=np.float32)
         n = x.shape[0]
         eb = self.eval_batch_size(n)
-        self._ensure_capacity(max(eb, self.capacity))
+        self._ensure_capacity(eb)
         out = np.empty((n, self.n_out), np.float32)
         last = self._resolve(len(self.nodes) - 1, False)
         for lo in range(0, n, eb):
@@ -1000,10 +1050,10 @@ class Engine(object):
 
     def _prepare_input_gradient(self, b):
         """Buffers for a gradient that reaches the network input (training never needs dL/dx)."""
-        self._ensure_capacity(max(b, self.capacity))
-        if 0 not in self.gact or self.gact[0].shape[0] < self.capacity:
+        self._ensure_capacity(b, b)
+        if 0 not in self.gact or self.gact[0].shape[0] < self.grad_capacity:
             with torch.cuda.device(self.device):
-                self.gact[0] = torch.empty((self.capacity,) + tuple(self.shape[0]), dtype=torch.float32, device=self.device)
+                self.gact[0] = torch.empty((self.grad_capacity,) + tuple(self.shape[0]), dtype=torch.float32, device=self.device)
             for key in [k for k in self.programs if k[0] in ("grad_input", "grad_logits")]:
                 if key in self.graphs:
                     self.lib.fnet_graph_destroy(self.graphs.pop(key))
@@ -1039,8 +1089,8 @@ class Engine(object):
         val = None
         if validation_data is not None:
             val = self._check_xy(validation_data[0], validation_data[1])
-        cap = max(batch_size, self.eval_batch_size(val[0].shape[0]) if val else 0, self.capacity)
-        self._ensure_capacity(cap)
+        cap = max(batch_size, self.eval_batch_size(val[0].shape[0]) if val else 0)
+        self._ensure_capacity(cap, batch_size)
         self._set_data("train", x, y)
         perm_dev = self.data["train"][2]
         train_kind = "train"
@@ -1085,13 +1135,26 @@ class Engine(object):
                     for dev_arr, host_arr in zip(self.aug_dev, augment.draw(n)):
                         dev_arr.copy_(torch.from_numpy(host_arr))
             self._zero_metrics(self.state)
-            for step in range(steps):
-                b = min(batch_size, n - step * batch_size)
+            t_train = time.perf_counter()
+            if not per_batch and self.use_graphs and self.timeline is None:
+                # nothing on the host looks at single batches: the epoch's full batches are ONE call into the library
+                # (floor(n / batch) replays of the captured step), the ragged last batch a second one
                 self._sync_lr()
-                self._step(train_kind, b)
-                for cb in per_batch:
-                    cb.on_batch_end(step, {"batch": step, "size": b})
+                full = n // batch_size
+                if full:
+                    self.lib.fnet_graph_launch_n(self._graph(train_kind, batch_size), full, self.sp)
+                if n - full * batch_size:
+                    self._step(train_kind, n - full * batch_size)
+            else:
+                for step in range(steps):
+                    b = min(batch_size, n - step * batch_size)
+                    self._sync_lr()
+                    self._step(train_kind, b)
+                    for cb in per_batch:
+                        cb.on_batch_end(step, {"batch": step, "size": b})
             loss, acc = self._read_metrics(n)
+            self.timing["train_s"] += time.perf_counter() - t_train
+            self.timing["train_steps"] += steps
             logs = {"loss": loss, "acc": acc}
             if val is not None:
                 logs["val_loss"], logs["val_acc"] = self.evaluate(val[0], val[1])
@@ -1122,11 +1185,12 @@ class Engine(object):
 
     # ------------------------------------------------------------------ pipelined host feed
     _ring_kinds = ["train_ring%d" % k for k in range(8)]
+    _ring_kinds_u8 = ["train_ringu8_%d" % k for k in range(8)]
     RING_SLOTS = 3      # two are enough to overlap upload and compute; the third absorbs host-side jitter
 
     def _ring_setup(self, batch):
         """Two slots of (device batch, pinned staging batch, pinned result, two events) and a copy stream."""
-        self._ensure_capacity(max(batch, self.capacity))
+        self._ensure_capacity(batch, batch)
         ring = getattr(self, "ring", None)
         if ring is not None and ring["capacity"] >= self.capacity:
             return ring
@@ -1141,6 +1205,8 @@ class Engine(object):
                     "x": torch.empty((n, cap) + tuple(self.shape[0]), dtype=torch.float32, device=self.device),
                     "y": torch.empty((n, cap, self.n_out), dtype=torch.float32, device=self.device),
                     "order": torch.arange(cap, dtype=torch.int32, device=self.device),
+                    "x_u8": torch.empty((n, cap) + tuple(self.shape[0]), dtype=torch.uint8, device=self.device),
+                    "scale": 255.0,
                     "x_stage": torch.empty((n, cap) + tuple(self.shape[0]), dtype=torch.float32).pin_memory(),
                     "y_stage": torch.empty((n, cap, self.n_out), dtype=torch.float32).pin_memory(),
                     "result": torch.zeros((n, 2), dtype=torch.int64).pin_memory(),
@@ -1154,36 +1220,54 @@ class Engine(object):
         # raw addresses per slot, gathered once: the per-step call must cost the host less than a step costs the GPU
         ring["ptrs"] = [(ring["x"][k].data_ptr(), ring["x_stage"][k].data_ptr(), ring["y"][k].data_ptr(),
                          ring["y_stage"][k].data_ptr(), ring["result"][k].data_ptr(), ring["slot_event"][k].cuda_event,
-                         ring["copied_event"][k].cuda_event) for k in range(n)]
+                         ring["copied_event"][k].cuda_event, ring["x_u8"][k].data_ptr()) for k in range(n)]
         ring["fixed"] = (self.metrics.data_ptr(), ring["prev"].ctypes.data, ring["copy_stream"].cuda_stream,
                          self.stream.cuda_stream)
         ring["prev64"] = ring["prev"].view(np.float64)
         self.ring = ring
         return ring
 
-    def _stream_step(self, step, x, y):
+    def _stream_step(self, step, x, y, scale=None):
         """Enqueue one optimisation step on a host batch without waiting for it.  Returns the running
-        (loss_sum, correct) as they stood after the step that used this slot before (RING_SLOTS steps ago)."""
+        (loss_sum, correct) as they stood after the step that used this slot before (RING_SLOTS steps ago).
+        A uint8 batch is uploaded as it is (a quarter of the bytes) and divided by `scale` on the device, which is
+        what tensorflow_generator.py:310-313 does to the whole dataset on the host."""
         b = int(x.shape[0])
         ring = getattr(self, "ring", None)
         if ring is None or b > ring["capacity"] or ring["capacity"] < self.capacity:
             ring = self._ring_setup(b)
         slot = step % self.RING_SLOTS
-        xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+        xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x))
         yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32))
-        if xt.dtype != torch.float32 or yt.dtype != torch.float32 or not xt.is_contiguous() or not yt.is_contiguous():
-            xt, yt = xt.float().contiguous(), yt.float().contiguous()
+        as_u8 = xt.dtype == torch.uint8
+        if as_u8:
+            if scale is None:
+                raise ValueError("uint8 batches need the divisor that makes them the model's inputs (generator.scale)")
+            if float(scale) != ring["scale"]:
+                self.stream.synchronize()
+                for key in [k for k in self.programs if k[0].startswith("train_ringu8_")]:
+                    if key in self.graphs:
+                        self.lib.fnet_graph_destroy(self.graphs.pop(key))
+                    self.programs.pop(key)
+                ring["scale"] = float(scale)
+            if not xt.is_contiguous():
+                xt = xt.contiguous()
+        elif xt.dtype != torch.float32 or not xt.is_contiguous():
+            xt = xt.float().contiguous()
+        if yt.dtype != torch.float32 or not yt.is_contiguous():
+            yt = yt.float().contiguous()
         if tuple(xt.shape[1:]) != tuple(self.shape[0]) or tuple(yt.shape) != (b, self.n_out):
             raise ValueError("batch of shape %s / %s does not fit the model" % (tuple(xt.shape), tuple(yt.shape)))
         pinned = xt.is_pinned() and yt.is_pinned()
-        graph = self.graphs.get((self._ring_kinds[slot], b))
+        kinds = self._ring_kinds_u8 if as_u8 else self._ring_kinds
+        graph = self.graphs.get((kinds[slot], b))
         if graph is None:
-            graph = self._graph(self._ring_kinds[slot], b)     # one captured step per (slot, batch size)
+            graph = self._graph(kinds[slot], b)     # one captured step per (slot, batch size)
         self._sync_lr()
-        x_slot, x_stage, y_slot, y_stage, result, slot_event, copied_event = ring["ptrs"][slot]
+        x_slot, x_stage, y_slot, y_stage, result, slot_event, copied_event, x_slot_u8 = ring["ptrs"][slot]
         metrics, prev, copy_stream, compute_stream = ring["fixed"]
         self.lib.fnet_graph_step_streamed(
-            graph, x_slot, xt.data_ptr(), None if pinned else x_stage, xt.numel() * 4,
+            graph, x_slot_u8 if as_u8 else x_slot, xt.data_ptr(), None if pinned else x_stage, xt.numel() * xt.element_size(),
             y_slot, yt.data_ptr(), None if pinned else y_stage, yt.numel() * 4,
             metrics, result, prev, 16, copy_stream, compute_stream, slot_event, copied_event)
         if pinned:
@@ -1223,7 +1307,7 @@ class Engine(object):
                 item = next(batches)
                 x, y = item[0], item[1]
                 b = int(x.shape[0])
-                loss_sum, correct = self._stream_step(step_no, x, y)
+                loss_sum, correct = self._stream_step(step_no, x, y, scale=getattr(generator, "scale", None))
                 step_no += 1
                 seen += b
                 for cb in per_batch:

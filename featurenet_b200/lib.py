@@ -92,6 +92,9 @@ SIGNATURES = {
     "fnet_graph_begin": (C.c_int, [_P]),
     "fnet_graph_end": (C.c_int, [_P, C.POINTER(_P)]),
     "fnet_graph_launch": (C.c_int, [_P, _P]),
+    "fnet_graph_launch_n": (C.c_int, [_P, _I32, _P]),
+    "fnet_state_set_lr": (C.c_int, [_P, _F, _P]),
+    "fnet_feed_batch_u8": (C.c_int, [_I32, _I64, _I64, _P, _P, _F, _P, _P, _P, C.c_int, _F, _F, _P]),
     "fnet_graph_destroy": (C.c_int, [_P]),
     "fnet_graph_step_fed": (C.c_int, [_P, _P, _P, C.c_size_t, _P, _P, C.c_size_t, _P, _P, C.c_size_t, _P]),
     "fnet_conv2d_bwd_data_on_tensor_core": (C.c_int, [_CD]),

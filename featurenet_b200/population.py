@@ -16,6 +16,7 @@ A generation barrier exists only because the evolution drivers select on all fit
 """
 import contextlib
 import io
+import threading
 import time
 
 
@@ -29,6 +30,52 @@ def estimate_cost(network, n_train, n_eval, epochs):
     steps_images = float(n_train) * epochs
     launch_term = 4.0e6 * len(network.layers)          # ~ flops a B200 could do in one launch latency, per image-batch
     return steps_images * (flops_per_image + launch_term / 128.0) + n_eval * flops_per_image / 3.0
+
+
+def estimate_bytes(network, batch_size, n_eval):
+    """Device memory one resident candidate needs, from the layer shapes alone (what Engine allocates: activations for
+    the inference batch, gradients for the training batch, four parameter arenas, workspace allowance)."""
+    per_image = 0
+    for node in network.layers:
+        if node.kind == "flatten":
+            continue
+        n = 1
+        for d in node.output.shape.as_list()[1:]:
+            n *= int(d)
+        per_image += 4 * n * (2 if node.kind == "sepconv2d" else 1)
+    from .engine import Engine
+    eval_batch = int(min(n_eval, max(32, Engine.EVAL_ACT_BYTES // max(per_image, 1)), 1000))
+    rows = max(eval_batch, batch_size) + batch_size               # activations + gradients
+    return int(1.25 * per_image * rows + 24 * network.count_params() + (64 << 20))
+
+
+class MemoryBudget(object):
+    """Admission control for candidates that share one GPU: a candidate starts once its estimated footprint fits in
+    what is left of the budget.  Without it, which candidates happen to be resident together decides whether one of
+    them runs out of memory -- and the reference's convention turns that into accuracy 0 (helpers.py:172-174)."""
+
+    def __init__(self, total_bytes):
+        self.total = int(total_bytes)
+        self.free = int(total_bytes)
+        self.cv = threading.Condition()
+
+    def acquire(self, need):
+        need = min(int(need), self.total)                         # a candidate larger than the budget runs alone
+        with self.cv:
+            while self.free < need:
+                self.cv.wait()
+            self.free -= need
+        return need
+
+    def release(self, held):
+        with self.cv:
+            self.free += held
+            self.cv.notify_all()
+
+
+def is_oom(result):
+    return isinstance(result, dict) and (result.get("oom") or "OutOfMemory" in str(result.get("error", "")) or
+                                         "out of memory" in str(result.get("error", "")))
 
 
 def assign_lpt(costs, world_size):
@@ -53,7 +100,7 @@ def max_over_ranks(value, dist=None, device=None):
     return float(t.item())
 
 
-def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, workers=1):
+def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, workers=1, mem_bytes=None, budget=None):
     """Train this rank's share of ``products``; gather (index, result) pairs on every rank, in index order.
 
     train_one(index, product) -> picklable result (e.g. dict(accuracy=..., history=..., params=...)).
@@ -64,15 +111,25 @@ def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, 
     thread on its own CUDA stream.  FeatureNet's candidates are mostly launch-latency-bound chains of tiny
     kernels (a step of a 6-feature network is ~15 launches of a few microseconds), so several chains
     interleave on the 148 SMs almost for free; the work queue is longest-first, pulled dynamically.
+
+    mem_bytes[i] (estimate_bytes) with a MemoryBudget makes the co-residency memory-aware; a candidate that still runs
+    out of memory beside its neighbours is trained again ALONE after the others are done, so that only a candidate
+    that does not fit the GPU by itself is scored 0.
     """
     mine = assign_lpt(costs, world_size)[rank]
 
     def one(index):
         started = time.time()
+        held = budget.acquire(mem_bytes[index]) if (budget is not None and mem_bytes is not None) else 0
         try:
             result = train_one(index, products[index])
         except Exception as e:                       # noqa: BLE001 -- one bad candidate must not kill the population
-            result = {"error": "%s: %s" % (type(e).__name__, e), "accuracy": 0}
+            import traceback
+            result = {"error": "%s: %s" % (type(e).__name__, e), "accuracy": 0,
+                      "traceback": traceback.format_exc(limit=6)}
+        finally:
+            if held:
+                budget.release(held)
         if isinstance(result, dict):
             result.setdefault("seconds", time.time() - started)
             result.setdefault("rank", rank)
@@ -92,6 +149,20 @@ def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, 
             local = list(pool.map(one, mine))            # `mine` is already longest-first
     else:
         local = [one(index) for index in mine]
+    retry = [k for k, (_, result) in enumerate(local) if is_oom(result)]
+    if retry and workers > 1:
+        try:
+            import torch
+            torch.cuda.synchronize()
+            torch.cuda.empty_cache()
+        except ImportError:
+            pass
+        for k in retry:
+            index, first = local[k]
+            index, again = one(index)
+            if isinstance(again, dict):
+                again["retried_alone_after"] = str(first.get("error", "out of memory"))[:200]
+            local[k] = (index, again)
     if dist is not None and dist.is_initialized() and world_size > 1:
         gathered = [None] * world_size
         dist.all_gather_object(gathered, local)
@@ -109,6 +180,8 @@ def train_product(product, dataset, epochs, batch_size, product_features=None, d
     releases its own network when it is done, and it does not touch the process-wide stdout.
     """
     from tensorflow_generator import TensorflowGenerator
+    import helpers
+    helpers.clear_failure()
     if shared_gpu:
         gen = TensorflowGenerator(product, epochs=epochs, dataset=dataset, data_augmentation=data_augmentation,
                                   batch_size=batch_size, product_features=product_features, clear_memory=False)
@@ -119,5 +192,9 @@ def train_product(product, dataset, epochs, batch_size, product_features=None, d
         with contextlib.redirect_stdout(io.StringIO()):
             gen = TensorflowGenerator(product, epochs=epochs, dataset=dataset, data_augmentation=data_augmentation,
                                       batch_size=batch_size, product_features=product_features)
-    return {"accuracy": float(gen.accuracy), "params": int(gen.params), "training_time": float(gen.training_time),
-            "history": (list(gen.history[0]), list(gen.history[1])), "valid": bool(gen.params)}
+    out = {"accuracy": float(gen.accuracy), "params": int(gen.params), "training_time": float(gen.training_time),
+           "history": (list(gen.history[0]), list(gen.history[1])), "valid": bool(gen.params)}
+    failure = helpers.last_failure()
+    if failure:                       # the runner swallowed it (reference convention); the scheduler wants to know
+        out["oom"], out["error"] = True, failure
+    return out

@@ -120,9 +120,10 @@ def random_sphere_l2(nb_points, nb_dims, radius):
     return a * (gammainc(nb_dims / 2.0, s2 / 2.0) ** (1.0 / nb_dims) * radius / np.sqrt(s2))[:, None]
 
 
-def _clever_maxima(net, x, nb_batches, batch_size, radius, norm, pool_factor):
+def _clever_maxima(net, x, nb_batches, batch_size, radius, norm, pool_factor, only_target=None):
     """The GPU half of clever_u: (margins z[pred] - z[target] per target class, per-batch gradient-norm maxima per
-    target class).  All random draws of the sample happen here, in the reference's order."""
+    target class).  All random draws of the sample happen here, in the reference's order.  only_target restricts
+    the work to one target class (clever_t)."""
     if norm != 2:
         raise NotImplementedError("only norm=2, the one the reference uses (tensorflow_generator.py:186), is built")
     if pool_factor < 1:
@@ -135,6 +136,10 @@ def _clever_maxima(net, x, nb_batches, batch_size, radius, norm, pool_factor):
     z = z[0].cpu().numpy().astype(np.float64)
     pred = int(np.argmax(z))
     targets = [j for j in range(classes) if j != pred]
+    if only_target is not None:
+        if int(only_target) == pred:
+            raise ValueError("The targeted class is the predicted class.")
+        targets = [int(only_target)]
     rows = np.empty((len(targets) * pool_n,) + x.shape, np.float32)
     head = np.zeros((len(targets) * pool_n, classes), np.float32)
     picks = []
@@ -163,6 +168,13 @@ def clever_u(net, x, nb_batches, batch_size, radius, norm=2, c_init=1, pool_fact
     margins, maxima = _clever_maxima(net, x, nb_batches, batch_size, radius, norm, pool_factor)
     score = _clever_from_fits(margins, [weibull.location(m, c_init) for m in maxima], radius)
     return (score, np.asarray(maxima)) if return_maxima else score
+
+
+def clever_t(net, x, target_class, nb_batches, batch_size, radius, norm=2, c_init=1, pool_factor=10):
+    """Targeted CLEVER score of ONE sample for ONE target class (model/metrics.py:242-324)."""
+    from . import weibull
+    margins, maxima = _clever_maxima(net, x, nb_batches, batch_size, radius, norm, pool_factor, only_target=target_class)
+    return _clever_from_fits(margins, [weibull.location(maxima[0], c_init)], radius)
 
 
 def clever_score(net, x_set, nb_batches=10, batch_size=5, radius=2, norm=2, pool_factor=3, workers=None):

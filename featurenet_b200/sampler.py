@@ -284,3 +284,48 @@ def write_pdt(path, fm, products):
         for signed in products:
             handle.write("".join("%d;" % x for x in signed) + "\n")
     return path
+
+
+def generate_products(feature_model, nb_products, output, seed=None, nb_cells=None, nb_blocks=None, p_select=0.6):
+    """What ``java -jar PLEDGE.jar generate_products -fm <xml> -nbProds <n> -o <pdt>`` does for the reference
+    (pledge_evolution.py:36-47): read the feature model -- including the negated-leaf constraints that
+    ``PledgeEvolution.generate_children`` appends (pledge_evolution.py:70-99, ``~Architecture  or  ~<leaf>``) --
+    draw n valid products and write them in PLEDGE's .pdt format.  Returns the number written."""
+    fm = parse_splot(feature_model, nb_cells=nb_cells, nb_blocks=nb_blocks)
+    if seed is None:
+        seed = random.SystemRandom().randrange(1 << 30)
+    products = sample_products(fm, int(nb_products), seed=seed, p_select=p_select)
+    if not products:
+        raise SystemExit("the feature model %s has no valid product" % feature_model)
+    for signed in products:
+        if not check_product(fm, signed):
+            raise AssertionError("sampler produced an invalid product")
+    write_pdt(output, fm, products)
+    return len(products)
+
+
+def main(argv=None):
+    """Command line with PLEDGE's own flags, so that the ``java`` stand-in of featurenet_b200/compat/bin can forward
+    the reference's argument list unchanged:  generate_products -fm X.xml -nbProds N -o OUT.pdt [-timeAllowedMS T]"""
+    import sys
+    argv = list(sys.argv[1:] if argv is None else argv)
+    if "-jar" in argv:                       # called as `java -jar <path to PLEDGE.jar> ...`
+        at = argv.index("-jar")
+        del argv[at: at + 2]
+    if not argv or argv[0] != "generate_products":
+        raise SystemExit("usage: generate_products -fm <model.xml> -nbProds <n> -o <out.pdt> [-timeAllowedMS <ms>] [-seed <s>]")
+    opts, i = {}, 1
+    while i + 1 < len(argv):
+        opts[argv[i]] = argv[i + 1]
+        i += 2
+    for needed in ("-fm", "-nbProds", "-o"):
+        if needed not in opts:
+            raise SystemExit("missing %s" % needed)
+    n = generate_products(opts["-fm"], int(opts["-nbProds"]), opts["-o"],
+                          seed=int(opts["-seed"]) if "-seed" in opts else None)
+    print("%d products written to %s" % (n, opts["-o"]))
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

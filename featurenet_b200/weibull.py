@@ -30,5 +30,10 @@ def locations(all_maxima, c_init=1, workers=None):
     jobs = [(list(map(float, m)), c_init) for m in all_maxima]
     if workers <= 1 or len(jobs) < 4 * workers:
         return [location(*j) for j in jobs]
-    with multiprocessing.get_context("fork").Pool(workers) as pool:
+    # "forkserver", never "fork": the caller is a multi-threaded process that owns a CUDA context, and a forked child
+    # inherits locks held by threads that do not exist in it.  The server process is started once (from a clean
+    # interpreter) and only ever imports this module: numpy and scipy, no CUDA.
+    ctx = multiprocessing.get_context("forkserver")
+    ctx.set_forkserver_preload(["numpy", "scipy.optimize", "scipy.stats"])
+    with ctx.Pool(workers) as pool:
         return pool.map(_job, jobs, chunksize=max(1, len(jobs) // (8 * workers)))

@@ -249,6 +249,10 @@ int fnet_softmax_cce(int32_t batch, int32_t classes, const float *input, const f
  * sample of the epoch, [2] lr (float bits), [3] lr_t (float bits, written by step_begin).
  * ------------------------------------------------------------------------------------------ */
 int fnet_step_begin(int32_t *state, float beta1, float beta2, void *stream);
+/* state[2] = lr, in stream order.  The value travels as a kernel argument, so callbacks that change the learning
+ * rate (LearningRateScheduler per epoch, helpers.py:45-67; SGDRScheduler per batch, sgdr.py:60-66) cost one tiny
+ * launch and no host wait. */
+int fnet_state_set_lr(int32_t *state, float lr, void *stream);
 int fnet_step_end(int32_t *state, int32_t batch, void *stream);
 /* advance >= 0: the optimizer launch also does fnet_step_end(state, advance); advance < 0: state is only read */
 int fnet_adam_step(int64_t n, float *params, const float *grads, float *m, float *v, int32_t *state, float beta1,
@@ -275,6 +279,12 @@ int fnet_gather_shift_flip(int32_t batch, int32_t h, int32_t w, int32_t c, const
                            const float *src, float *dst, void *stream);
 /* dst = float(src) * scale : the `astype('float32') / 255` of tensorflow_generator.py:310-313 */
 int fnet_u8_to_f32(int64_t n, const uint8_t *src, float scale, float *dst, void *stream);
+/* First launch of a train step whose batch was uploaded as uint8 pixels (a quarter of the fp32 upload): the
+ * `astype('float32') / 255` of tensorflow_generator.py:310-313 applied on the device to the whole batch
+ * [batch][x_row], targets [batch][y_row] copied, and (begin_step != 0) the work of fnet_step_begin. */
+int fnet_feed_batch_u8(int32_t batch, int64_t x_row, int64_t y_row, int32_t *state, const uint8_t *x_src, float scale,
+                       const float *y_src, float *x_dst, float *y_dst, int begin_step, float beta1, float beta2,
+                       void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * One step of an L2 gradient attack on a batch of inputs (the FGSM / PGD updates behind the robustness
@@ -296,6 +306,9 @@ int fnet_l2_attack_step(int32_t batch, int64_t row, const float *x0, const float
 int fnet_graph_begin(void *stream);
 int fnet_graph_end(void *stream, void **graph_exec_out);
 int fnet_graph_launch(void *graph_exec, void *stream);
+/* n back-to-back replays in one call: an epoch of Model.fit (helpers.py:105) without per-batch callbacks is
+ * floor(N / batch) identical steps -- one transition from the host language per epoch instead of one per step. */
+int fnet_graph_launch_n(void *graph_exec, int32_t n, void *stream);
 int fnet_graph_destroy(void *graph_exec);
 /* One step fed from HOST memory, the shape of keras' train_on_batch / test_on_batch (one session.run with a
  * feed_dict, helpers.py:105 -> Model.fit -> train_function): copy the inputs and the targets to the device,

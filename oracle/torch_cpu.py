@@ -26,15 +26,19 @@ def _pad_same(x, k, s, padding, d=(1, 1)):
 class TorchCpuNet(object):
     """Activations are kept NCHW (torch's fast layout); weights are converted once from Keras layouts."""
 
-    def __init__(self, rows, weights, threads=None):
+    def __init__(self, rows, weights, threads=None, dtype=torch.float32):
+        """dtype=torch.float64 turns the port into a fast float64 checker for layers and candidates at BASELINE's
+        full sizes (batch 128), where the NumPy oracle of oracle/net.py takes minutes."""
         if threads:
             torch.set_num_threads(int(threads))
+        self.dtype = dtype
+        self.np_dtype = np.float64 if dtype == torch.float64 else np.float32
         self.rows = rows
         self.params = []          # per layer: list of torch tensors (requires_grad for trainable ones)
         for row, ws in zip(rows, weights):
             cls, ts = row["class"], []
             for k, w in enumerate(ws):
-                t = torch.tensor(np.asarray(w, np.float32))
+                t = torch.tensor(np.asarray(w, self.np_dtype))
                 if cls in ("Conv2D",) and k == 0:
                     t = t.permute(3, 2, 0, 1).contiguous()                       # HWIO -> OIHW
                 elif cls in ("DepthwiseConv2D", "SeparableConv2D") and k == 0:
@@ -89,7 +93,7 @@ class TorchCpuNet(object):
                 y = F.max_pool2d(xp, tuple(cfg["pool"]), tuple(cfg["strides"]))
             elif cls == "AveragePooling2D":
                 xp = _pad_same(ins[0], cfg["pool"], cfg["strides"], cfg["padding"])
-                ones = _pad_same(torch.ones(1, 1, ins[0].shape[2], ins[0].shape[3]), cfg["pool"], cfg["strides"], cfg["padding"])
+                ones = _pad_same(torch.ones(1, 1, ins[0].shape[2], ins[0].shape[3], dtype=self.dtype), cfg["pool"], cfg["strides"], cfg["padding"])
                 num = F.avg_pool2d(xp, tuple(cfg["pool"]), tuple(cfg["strides"]), divisor_override=1)
                 den = F.avg_pool2d(ones, tuple(cfg["pool"]), tuple(cfg["strides"]), divisor_override=1)
                 y = num / den
@@ -100,7 +104,7 @@ class TorchCpuNet(object):
             elif cls == "Dropout":
                 if training:
                     if dropout_masks is not None:
-                        mask = torch.tensor(np.asarray(dropout_masks[i], np.float32)).reshape(
+                        mask = torch.tensor(np.asarray(dropout_masks[i], self.np_dtype)).reshape(
                             (-1,) + tuple(row["out_shape"][1:]))
                         mask = mask.permute(0, 3, 1, 2) if is4 else mask
                         y = ins[0] * mask / (1.0 - cfg["rate"])
@@ -150,9 +154,10 @@ class TorchCpuNet(object):
         return loss, (t.argmax(dim=-1) == p.argmax(dim=-1))
 
     def train_step(self, x, t, lr=1e-3, dropout_masks=None):
-        x = torch.as_tensor(x, dtype=torch.float32)
-        t = torch.as_tensor(t, dtype=torch.float32)
+        x = torch.as_tensor(x, dtype=self.dtype)
+        t = torch.as_tensor(t, dtype=self.dtype)
         outs = self.forward(x, True, dropout_masks)
+        self.outs = outs
         loss, correct = self.loss_and_correct(outs[-1], t)
         for p in self.trainable:
             p.grad = None
@@ -171,9 +176,62 @@ class TorchCpuNet(object):
         loss_sum, n_correct = 0.0, 0
         with torch.no_grad():
             for lo in range(0, x.shape[0], batch_size):
-                xb = torch.as_tensor(x[lo: lo + batch_size], dtype=torch.float32)
-                tb = torch.as_tensor(t[lo: lo + batch_size], dtype=torch.float32)
+                xb = torch.as_tensor(x[lo: lo + batch_size], dtype=self.dtype)
+                tb = torch.as_tensor(t[lo: lo + batch_size], dtype=self.dtype)
                 loss, correct = self.loss_and_correct(self.forward(xb, False)[-1], tb)
                 loss_sum += float(loss.sum())
                 n_correct += int(correct.sum())
         return loss_sum / x.shape[0], n_correct / x.shape[0]
+
+    # ---- views in the engine's conventions (NHWC activations, Keras weight layouts), for the parity tests
+    def out_nhwc(self, i):
+        y = self.outs[i].detach()
+        return (y.permute(0, 2, 3, 1) if y.dim() == 4 else y).contiguous().numpy()
+
+    @staticmethod
+    def _to_keras(cls, k, t):
+        if cls == "Conv2D" and k == 0:
+            return t.permute(2, 3, 1, 0)                                         # OIHW -> HWIO
+        if cls in ("DepthwiseConv2D", "SeparableConv2D") and k == 0:
+            return t.permute(2, 3, 0, 1)                                         # [C,1,kh,kw] -> [kh,kw,C,1]
+        if cls == "SeparableConv2D" and k == 1:
+            return t.permute(2, 3, 1, 0)
+        return t
+
+    def grads_keras(self):
+        """{(layer, weight index): gradient in the Keras layout} of the last train_step."""
+        out = {}
+        for i, (row, ts) in enumerate(zip(self.rows, self.params)):
+            for k, t in enumerate(ts):
+                if t.requires_grad:
+                    g = t.grad if t.grad is not None else torch.zeros_like(t)
+                    out[(i, k)] = self._to_keras(row["class"], k, g.detach()).contiguous().numpy()
+        return out
+
+    def weights_keras(self):
+        return [self._to_keras(row["class"], k, t.detach()).contiguous().numpy()
+                for row, ts in zip(self.rows, self.params) for k, t in enumerate(ts)]
+
+    def fit_epoch(self, x, t, batch_size, permutation, lr=1e-3):
+        """One epoch in Keras' order (helpers.py:105): batches cut from the given permutation, ragged last batch kept.
+        Returns (mean loss, accuracy) over the epoch's samples."""
+        loss_sum, correct = 0.0, 0
+        for lo in range(0, x.shape[0], batch_size):
+            idx = permutation[lo: lo + batch_size]
+            ls, c = self.train_step(x[idx], t[idx], lr)
+            loss_sum += ls
+            correct += c
+        return loss_sum / x.shape[0], correct / x.shape[0]
+
+
+def conv_products64(x, w, b, dy, strides, padding, dilation=(1, 1)):
+    """Forward, data gradient, filter gradient and bias gradient of one Conv2D in float64 (NHWC / HWIO in and out):
+    the checker for the three GEMM-shaped products at batch 128.  Dense is the 1x1 case on a [M,1,1,K] tensor."""
+    xt = torch.tensor(np.asarray(x, np.float64)).permute(0, 3, 1, 2).requires_grad_(True)
+    wt = torch.tensor(np.asarray(w, np.float64)).permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+    bt = torch.tensor(np.asarray(b, np.float64)).requires_grad_(True) if b is not None else None
+    xp = _pad_same(xt, w.shape[:2], strides, padding, dilation)
+    y = F.conv2d(xp, wt, bt, stride=tuple(strides), dilation=tuple(dilation))
+    y.backward(torch.tensor(np.asarray(dy, np.float64)).permute(0, 3, 1, 2))
+    return (y.detach().permute(0, 2, 3, 1).contiguous().numpy(), xt.grad.permute(0, 2, 3, 1).contiguous().numpy(),
+            wt.grad.permute(2, 3, 1, 0).contiguous().numpy(), bt.grad.numpy() if bt is not None else None)

@@ -29,7 +29,7 @@ for rep in range(2):
     mark("parse+build graph")
     net.compile(loss="categorical_crossentropy", optimizer=Adam(1e-3))
     eng = net._need_engine(); mark("engine init (arenas, weights)")
-    eng._ensure_capacity(1000); mark("activation buffers")
+    eng._ensure_capacity(1000, 128); mark("activation buffers")
     eng._set_data("train", xtr, ytr); eng._sync_lr(); mark("set data")
     eng._zero_metrics(eng.state); eng._step("train", 128); mark("first step (program + capture + run)")
     for _ in range(77): eng._step("train", 128)

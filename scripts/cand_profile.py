@@ -19,7 +19,7 @@ for r in net.describe():
     print("  ", r["class"], r["in_shapes"], "->", r["out_shape"], {k: v for k, v in r["cfg"].items() if k in ("kernel", "strides", "activation", "filters", "units", "rate")}, r["params"])
 net.compile(loss="categorical_crossentropy", optimizer=Adam(1e-3))
 eng = net._need_engine()
-eng._ensure_capacity(128)
+eng._ensure_capacity(128, 128)
 eng._set_data("train", xtr, ytr)
 eng._sync_lr()
 table = eng.profile_steps("train", 128, steps=10)

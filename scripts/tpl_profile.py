@@ -19,7 +19,7 @@ with contextlib.redirect_stdout(io.StringIO()):
     (xtr, ytr), _ = synth.load(ds, 16384, 16)
 net.compile(loss="categorical_crossentropy", optimizer=Adam(1e-3))
 eng = net._need_engine()
-eng._ensure_capacity(128)
+eng._ensure_capacity(128, 128)
 eng._set_data("train", xtr, ytr)
 eng._sync_lr()
 table = eng.profile_steps("train", 128, steps=10)

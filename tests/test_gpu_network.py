@@ -4,6 +4,7 @@ fit loop (callbacks, best-checkpoint restore) and evaluate; plus properties at B
 """
 import contextlib
 import io
+import os
 
 import numpy as np
 import pytest
@@ -16,6 +17,7 @@ from tests.util import init_weights, build_template, tiny_graphs
 torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
 
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 TOL = 1e-4           # north_star: per-layer forward/backward within 1e-4 relative in fp32
 
 
@@ -274,4 +276,60 @@ def test_tensorflow_generator_drop_in(monkeypatch):
     assert gen.model.model is not None and gen.model.nb_params == 212902
     vec = gen.model.to_kerasvector().to_vector()
     assert vec[0] == gen.accuracy and vec[1][1][:3] == [5, 9, 212902]
+    TensorflowGenerator.dataset = None
+
+
+REFERENCE = os.environ.get("FNET_REFERENCE_DIR", "/root/reference")
+
+
+def _small_cifar(monkeypatch):
+    monkeypatch.setenv("FNET_SYNTH_TRAIN", "2048")
+    monkeypatch.setenv("FNET_SYNTH_TEST", "512")
+    from tensorflow_generator import TensorflowGenerator
+    TensorflowGenerator.dataset = None
+    return TensorflowGenerator
+
+
+@pytest.mark.skipif(not os.path.isfile(os.path.join(REFERENCE, "full.py")),
+                    reason="the reference tree is only present in the build container, which has no GPU")
+def test_unmodified_reference_driver_full_py(monkeypatch, tmp_path):
+    """/root/reference/full.py, imported as it is, drives the engine: main() over a 6-product .pdt."""
+    import shutil
+    import sys
+    TensorflowGenerator = _small_cifar(monkeypatch)
+    monkeypatch.setattr(sys, "path", sys.path + [REFERENCE])
+    monkeypatch.chdir(tmp_path)
+    os.mkdir("products")
+    shutil.copy(os.path.join(ROOT, "featurenet_b200/data/main_1block_nas_5cells_seed0.pdt"), "six.pdt")
+    import importlib
+    full = importlib.import_module("full")
+    with contextlib.redirect_stdout(io.StringIO()):
+        full.main("six", datasets=["cifar"], epochs=1, output_folder="./products/")
+    with open("six_cifar_1epochs_1.txt") as handle:
+        rows = [ln for ln in handle.read().split("\r\n") if ln.strip()]
+    assert len(rows) == 6
+    TensorflowGenerator.dataset = None
+
+
+def test_driver_sequence_of_full_py_on_the_engine(monkeypatch, tmp_path):
+    """The call sequence of full.py:9-36 (ProductSet -> format_products -> json dump -> TensorflowGenerator(product,
+    epochs, dataset, depth=..., data_augmentation=...) -> report line), written out here because the reference tree
+    does not travel to the GPU box; test_unmodified_reference_driver_full_py runs the file itself where it exists."""
+    import json
+    from products_tree import ProductSet
+    TensorflowGenerator = _small_cifar(monkeypatch)
+    with contextlib.redirect_stdout(io.StringIO()):
+        product_set = ProductSet(os.path.join(ROOT, "featurenet_b200/data/main_1block_nas_5cells_seed0.pdt"))
+        report = []
+        for index, (product, features) in enumerate(product_set.format_products()):
+            (tmp_path / ("p_%d.json" % index)).write_text(json.dumps(product))
+            gen = TensorflowGenerator(product, 1, "cifar", depth=1, data_augmentation=False)
+            history = "{}|{}".format("#".join(map(str, gen.history[0])), "#".join(map(str, gen.history[1])))
+            report.append("{0}: {1} {2} {3} {4} {5} {6}".format(index, gen.accuracy, gen.stop_training, gen.training_time,
+                                                                 gen.params, gen.flops, history))
+            if gen.params:
+                assert 0.0 <= gen.accuracy <= 1.0 and len(gen.history[0]) == 1
+                assert gen.flops == gen.model.nb_flops > 0                   # the vector's flops entry is filled
+                assert gen.model.to_kerasvector().to_vector()[1][1][3] == gen.flops
+    assert len(report) == 6
     TensorflowGenerator.dataset = None

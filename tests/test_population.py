@@ -84,3 +84,30 @@ def test_cost_estimate_orders_small_and_large_candidates():
     small = build_template("lenet5", (28, 28, 1))
     large = build_template("keras", (32, 32, 3))
     assert pop.estimate_cost(large, 50000, 10000, 1) > 3 * pop.estimate_cost(small, 50000, 10000, 1)
+
+
+def test_memory_budget_serialises_what_does_not_fit():
+    import threading
+    import time
+    from featurenet_b200.population import MemoryBudget
+    budget = MemoryBudget(100)
+    active, peak = [0], [0]
+    lock = threading.Lock()
+
+    def job(need):
+        held = budget.acquire(need)
+        with lock:
+            active[0] += held
+            peak[0] = max(peak[0], active[0])
+        time.sleep(0.02)
+        with lock:
+            active[0] -= held
+        budget.release(held)
+
+    threads = [threading.Thread(target=job, args=(n,)) for n in (60, 60, 30, 500, 10, 40)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=10)
+        assert not t.is_alive()
+    assert peak[0] <= 100 and budget.free == 100

@@ -36,6 +36,11 @@ def run_both(L, fl, m, k, n, act, seed):
     L.fnet_dense_fwd(m, k, n, fl.ACT[act], fl.MATH["fp32"], ptr(x), ptr(w), ptr(b), ptr(want), ptr(ws), ws.numel(), None)
     L.fnet_dense_fwd_static(m, k, n, fl.ACT[act], ptr(x), ptr(w), ptr(b), ptr(got), None)
     torch.cuda.synchronize()
+    # and against the float64 CPU oracle of the same layer, so that the pair cannot agree on a wrong answer
+    from oracle import ops
+    z = ops.dense_fwd(x.cpu().numpy().astype(np.float64), w.cpu().numpy().astype(np.float64), b.cpu().numpy().astype(np.float64))
+    oracle = ops.act_fwd(z, act)
+    assert np.abs(got.cpu().numpy() - oracle).max() <= TOL * np.abs(oracle).max()
     return got.cpu().numpy(), want.cpu().numpy(), need
 
 
