@@ -506,7 +506,9 @@ class Engine(object):
             s0 = self.src[i][0]
             x, y, dy = self._a(s0, training), self._a(i, training), self._g(i)
             n_out = batch * _prod(self.shape[i])
-            want_dx = need[s0]
+            # a merge owes a gradient to whichever of its inputs has trainable weights upstream -- not only to the first
+            # one (concat([network input, branch]) is how every FeatureNet cell stacks its branch onto its input)
+            want_dx = any(need[j] for j in self.src[i]) if kind in ("add", "mul", "concat") else need[s0]
             if kind in GEMM_KINDS or kind == "dwconv2d":
                 act = fl.ACT[cfg["activation"]]
                 if act and i != last and i not in fused_into:   # the head's dz comes straight from the loss kernel

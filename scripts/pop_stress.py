@@ -14,6 +14,7 @@ import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("FNET_SEED", "20261106")     # same weights and permutations every pass
 import featurenet_b200  # noqa: E402
 
 featurenet_b200.install_compat()

@@ -88,5 +88,16 @@ def tiny_graphs():
         t = L.Activation("softmax")(t)
         return L.Model(inputs=x, outputs=_head(t))
 
-    return {"conv_chain": conv_chain, "separable_depthwise": separable_depthwise, "pools_and_bn": pools_and_bn,
+    def merges_with_the_input():
+        """Merges whose FIRST operand is the network input (no gradient owed to it): the second one still is."""
+        x = L.Input((4, 4, 2))
+        a = L.Conv2D(2, (3, 3), padding="same", activation="relu")(x)
+        s = L.Add()([x, a])
+        b = L.Conv2D(2, (1, 1), padding="same", activation="tanh")(s)
+        c = L.Concatenate(axis=1)([x, b])              # what every FeatureNet cell does with its input
+        d = L.Conv2D(2, (1, 1), padding="same")(c)
+        m = L.Multiply()([c, d])
+        return L.Model(inputs=x, outputs=_head(m))
+
+    return {"merges_with_the_input": merges_with_the_input, "conv_chain": conv_chain, "separable_depthwise": separable_depthwise, "pools_and_bn": pools_and_bn,
             "merges": merges, "dropout_pad_act_gap": dropout_pad_act_gap}
