@@ -225,6 +225,20 @@ int fnet_gather_rows(int32_t batch, int64_t row_elems, const int32_t *perm, cons
     return check_launch("fnet_gather_rows");
 }
 
+// ---------------------------------------------------------------- streams
+int fnet_stream_create(void **stream_out) {
+    FNET_REQUIRE(stream_out != nullptr, "fnet_stream_create: null output");
+    cudaStream_t s = nullptr;
+    FNET_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    *stream_out = s;
+    return FNET_OK;
+}
+
+int fnet_stream_destroy(void *stream) {
+    if (stream) FNET_CUDA(cudaStreamDestroy(as_stream(stream)));
+    return FNET_OK;
+}
+
 // ---------------------------------------------------------------- CUDA graphs
 int fnet_graph_begin(void *stream) {
     FNET_CUDA(cudaStreamBeginCapture(as_stream(stream), cudaStreamCaptureModeThreadLocal));

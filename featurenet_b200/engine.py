@@ -18,8 +18,11 @@ Memory layout (all fp32, NHWC, allocated once per candidate through torch, sized
 PyTorch is used for allocation, streams and host<->device copies only; every arithmetic
 kernel is launched through the C ABI (featurenet_b200.lib).  No CPU execution path exists.
 """
+import contextlib
 import ctypes as C
 import math
+import sys
+import threading
 import time
 
 import numpy as np
@@ -51,18 +54,23 @@ class DeviceDataCache(object):
     """Datasets stay resident in HBM across candidates (the reference re-feeds every batch from host RAM)."""
     _store = {}
 
+    _lock = threading.Lock()
+
     @classmethod
     def get(cls, array, device, dtype=torch.float32):
         key = (id(array), array.shape, str(array.dtype), str(device))
-        hit = cls._store.get(key)
-        if hit is not None and hit[0] is array:
-            return hit[1]
-        host = np.ascontiguousarray(array)
-        t = torch.from_numpy(host).to(device=device, dtype=dtype, non_blocking=False).contiguous()
-        if len(cls._store) > 16:
-            cls._store.clear()
-        cls._store[key] = (array, t)
-        return t
+        with cls._lock:                   # candidates resident side by side ask for the same dataset at the same time
+            hit = cls._store.get(key)
+            if hit is not None and hit[0] is array:
+                return hit[1]
+            host = np.ascontiguousarray(array)
+            with torch.cuda.device(device):
+                t = torch.from_numpy(host).to(device=device, dtype=dtype, non_blocking=False).contiguous()
+                torch.cuda.current_stream().synchronize()      # read by every engine's own stream from here on
+            if len(cls._store) > 16:
+                cls._store.clear()
+            cls._store[key] = (array, t)
+            return t
 
     @classmethod
     def clear(cls):
@@ -88,11 +96,16 @@ class Engine(object):
         # "auto" (the default) = fp32 accuracy with the faster of the FFMA and the three-MMA tensor-core kernel per
         # product (FNET_MATH_AUTO); "fp32" forces FFMA everywhere, "tf32x3" the tensor core wherever it can run
         self.math = fl.MATH[(math_mode or os.environ.get("FNET_PRECISION", "auto")).lower()]
-        self.stream = torch.cuda.Stream(device=self.device)
+        # Streams of this engine's OWN (fnet_stream_create), not torch.cuda.Stream(): torch hands out 32 pooled streams
+        # per device round-robin, so with several candidates resident per GPU a long-lived engine ends up sharing a
+        # stream with a later one -- and whatever that one launches while this one is capturing a graph on the shared
+        # stream is recorded into the wrong graph instead of being executed.
+        self._streams = []
+        self.stream = self._new_stream()
         self.sp = C.c_void_p(self.stream.cuda_stream)
         # filter gradients run on a second stream, beside the data gradient of the same layer (both only read
         # dz); inside a captured step this becomes a fork/join of the CUDA graph, see _backward_program
-        self.side = torch.cuda.Stream(device=self.device)
+        self.side = self._new_stream()
         self.sp2 = C.c_void_p(self.side.cuda_stream)
         self.overlap_wgrad = os.environ.get("FNET_NO_OVERLAP", "0") != "1"
         # folding act'(y) into the producing data gradient pays on the FFMA kernels; the tensor-core epilogues are
@@ -118,9 +131,10 @@ class Engine(object):
         # host seconds per phase of this candidate's life (bench.py prints them inside candidate_cycle)
         self.timing = {"alloc_s": 0.0, "capture_s": 0.0, "train_s": 0.0, "eval_s": 0.0, "train_steps": 0, "eval_steps": 0}
         self.use_graphs = os.environ.get("FNET_NO_GRAPH", "0") != "1"
+        self.poison = os.environ.get("FNET_POISON", "0") == "1"
         self._plan_params()
         self._init_weights()
-        with torch.cuda.device(self.device):
+        with self._on_stream():
             self.state = torch.zeros(8, dtype=torch.int32, device=self.device)
             self.state_eval = torch.zeros(8, dtype=torch.int32, device=self.device)
             # one 16-byte block: [loss sum (double bits), correct count] -> a single D2H copy reads both
@@ -132,10 +146,34 @@ class Engine(object):
             self._metrics_seen = (0.0, 0)
         self._lr_on_device = None
         self.timeline = None          # when a list: (label, start_event, end_event) per launch (profiling mode)
-        # the arenas above were zero-filled by kernels on the thread's CURRENT stream; this engine works on its own
-        # (non-blocking) stream, which must not overtake them -- with several candidates resident per GPU the fills can
-        # be queued behind other candidates' work for a long time
-        self.stream.wait_stream(torch.cuda.current_stream(self.device))
+
+    # Streams an engine is done with are parked here and leased again, never destroyed: torch remembers the streams a
+    # pinned host block was used on and records an event on each when the block is freed (possibly long after this
+    # engine), which must not meet a dead handle.  A stream has exactly one owner while it is leased.
+    _idle_streams = {}
+    _idle_lock = threading.Lock()
+
+    @contextlib.contextmanager
+    def _on_stream(self):
+        """Everything an engine allocates or initialises with torch is created ON ITS OWN STREAM: torch's fills
+        (zeros, arange, NaN poison) are kernels on the current stream, and the thread's default stream is shared by
+        every candidate resident on the GPU -- a fill queued there can land after this engine's first copy into the
+        same buffer.  It also ties the memory to this stream in torch's allocator, so a block an earlier engine freed
+        is reused in stream order."""
+        with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
+            yield
+
+    def _new_stream(self):
+        key = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        with Engine._idle_lock:
+            idle = Engine._idle_streams.setdefault(key, [])
+            handle = idle.pop() if idle else None
+        if handle is None:
+            handle = C.c_void_p()
+            with torch.cuda.device(self.device):
+                self.lib.fnet_stream_create(C.byref(handle))
+        self._streams.append(handle)
+        return torch.cuda.ExternalStream(handle.value, device=self.device)
 
     # ------------------------------------------------------------------ parameters
     def _plan_params(self):
@@ -150,7 +188,7 @@ class Engine(object):
                     self.s_off[(i, k)] = (s, spec.size)
                     s += -(-spec.size // ALIGN) * ALIGN
         self.n_params, self.n_stats = p, s
-        with torch.cuda.device(self.device):
+        with self._on_stream():
             mk = lambda n: torch.zeros(max(n, ALIGN), dtype=torch.float32, device=self.device)
             self.params, self.grads, self.adam_m, self.adam_v = mk(p), mk(p), mk(p), mk(p)
             self.stats = mk(s)
@@ -218,7 +256,7 @@ class Engine(object):
 
     def snapshot(self, into=None):
         """Device-to-device copy of the weights (ModelCheckpoint / SGDR restarts)."""
-        with torch.cuda.stream(self.stream):
+        with self._on_stream():
             if into is None:
                 into = (torch.empty_like(self.params), torch.empty_like(self.stats))
             into[0].copy_(self.params)
@@ -255,7 +293,7 @@ class Engine(object):
         batch = self.capacity = max(batch, self.capacity)
         gbatch = self.grad_capacity = max(grad_batch, self.grad_capacity)
         dev = self.device
-        with torch.cuda.device(dev):
+        with self._on_stream():
             f32 = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)
             self.act, self.gact, self.aux = {}, {}, {}
             ws_bytes = 256
@@ -276,12 +314,22 @@ class Engine(object):
                 ws_bytes = max(ws_bytes, self._workspace_need(i, batch))
             self._alloc_workspace(ws_bytes)
             self.yb = f32(batch, self.n_out)
+            if self.poison:
+                # debugging aid (FNET_POISON=1): every buffer starts as NaN, so a launch that reads what no launch of
+                # the step wrote shows up as a NaN loss instead of depending on what the allocator handed out
+                for store in (self.act, self.gact):
+                    for t in store.values():
+                        t.fill_(float("nan"))
+                for t in self.aux.values():
+                    for u in (t if isinstance(t, tuple) else (t,)):
+                        u.fill_(float("nan")) if u.dtype == torch.float32 else u.fill_(255)
+                self.ws.view(torch.float32).fill_(float("nan"))
         self.timing["alloc_s"] += time.perf_counter() - t_alloc
 
     def _alloc_workspace(self, need):
         """Two halves of `need` bytes: the main stream's scratch and the side stream's (they run concurrently)."""
         need = -(-int(need) // 256) * 256
-        with torch.cuda.device(self.device):
+        with self._on_stream():
             self.ws = torch.empty(2 * need, dtype=torch.uint8, device=self.device)
         self.ws_bytes = need
         self.generation += 1
@@ -882,8 +930,7 @@ class Engine(object):
                     self.lib.fnet_graph_destroy(handle)
             except fl.FnetError:
                 pass
-            self.stream = torch.cuda.Stream(device=self.device)
-            self.side = torch.cuda.Stream(device=self.device)
+            self.stream, self.side = self._new_stream(), self._new_stream()
             self.sp, self.sp2 = C.c_void_p(self.stream.cuda_stream), C.c_void_p(self.side.cuda_stream)
             self._drop_graphs()               # programs hold the old stream handles
             raise
@@ -908,7 +955,8 @@ class Engine(object):
         if old is not None and old[0] is xd and old[1] is yd:
             return old
         n = xd.shape[0]
-        perm = torch.arange(n, dtype=torch.int32, device=self.device)
+        with self._on_stream():
+            perm = torch.arange(n, dtype=torch.int32, device=self.device)
         for key in [k for k in self.programs if k[0] == split]:
             if key in self.graphs:
                 self.lib.fnet_graph_destroy(self.graphs.pop(key))
@@ -955,8 +1003,7 @@ class Engine(object):
         eb = self.eval_batch_size(n)
         self._ensure_capacity(eb)
         self._set_data("eval", x, y)
-        with torch.cuda.stream(self.stream):
-            self.data["eval"][2].copy_(torch.arange(n, dtype=torch.int32, device=self.device))
+        # (the identity order the validation set was given in _set_data is never overwritten: nothing to upload)
         self._zero_metrics(self.state_eval)
         full = n // eb
         if full and self.use_graphs and self.timeline is None:
@@ -1054,7 +1101,7 @@ class Engine(object):
         """Buffers for a gradient that reaches the network input (training never needs dL/dx)."""
         self._ensure_capacity(b, b)
         if 0 not in self.gact or self.gact[0].shape[0] < self.grad_capacity:
-            with torch.cuda.device(self.device):
+            with self._on_stream():
                 self.gact[0] = torch.empty((self.grad_capacity,) + tuple(self.shape[0]), dtype=torch.float32, device=self.device)
             for key in [k for k in self.programs if k[0] in ("grad_input", "grad_logits")]:
                 if key in self.graphs:
@@ -1106,7 +1153,7 @@ class Engine(object):
                     if key in self.graphs:
                         self.lib.fnet_graph_destroy(self.graphs.pop(key))
                     self.programs.pop(key)
-                with torch.cuda.device(self.device):
+                with self._on_stream():
                     self.aug_dev = (torch.zeros(n, dtype=torch.float32, device=self.device),
                                     torch.zeros(n, dtype=torch.float32, device=self.device),
                                     torch.zeros(n, dtype=torch.uint8, device=self.device))
@@ -1202,7 +1249,7 @@ class Engine(object):
                 self.lib.fnet_graph_destroy(self.graphs.pop(key))
             self.programs.pop(key)
         cap, n = self.capacity, self.RING_SLOTS
-        with torch.cuda.device(self.device):
+        with self._on_stream():
             ring = {"capacity": cap,
                     "x": torch.empty((n, cap) + tuple(self.shape[0]), dtype=torch.float32, device=self.device),
                     "y": torch.empty((n, cap, self.n_out), dtype=torch.float32, device=self.device),
@@ -1213,7 +1260,7 @@ class Engine(object):
                     "y_stage": torch.empty((n, cap, self.n_out), dtype=torch.float32).pin_memory(),
                     "result": torch.zeros((n, 2), dtype=torch.int64).pin_memory(),
                     "prev": np.zeros(2, np.int64),
-                    "copy_stream": torch.cuda.Stream(device=self.device),
+                    "copy_stream": self._new_stream(),
                     "slot_event": [torch.cuda.Event() for _ in range(n)],
                     "copied_event": [torch.cuda.Event() for _ in range(n)]}
             for ev in ring["slot_event"] + ring["copied_event"]:
@@ -1333,9 +1380,26 @@ class Engine(object):
         return result
 
     def release(self):
-        self.stream.synchronize()
-        self._drop_graphs()
-        for name in ("act", "gact", "aux", "ws", "params", "grads", "adam_m", "adam_v", "stats", "data", "ring"):
-            if hasattr(self, name):
-                delattr(self, name)
-        self.capacity = 0
+        if not self._streams:
+            return
+        with torch.cuda.device(self.device):
+            for handle in self._streams:
+                torch.cuda.ExternalStream(handle.value, device=self.device).synchronize()
+            self._drop_graphs()
+            for name in ("act", "gact", "aux", "ws", "params", "grads", "adam_m", "adam_v", "stats", "data", "ring", "yb",
+                         "_metrics_np", "_metrics_host", "loss_sum", "correct", "metrics", "state", "state_eval", "aug_dev"):
+                if hasattr(self, name):
+                    delattr(self, name)
+            self.capacity = self.grad_capacity = 0
+        key = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        with Engine._idle_lock:
+            Engine._idle_streams.setdefault(key, []).extend(self._streams)
+        self._streams = []
+
+    def __del__(self):
+        if sys is None or sys.is_finalizing():
+            return                 # interpreter shutdown: the CUDA context may be gone; the process frees everything
+        try:
+            self.release()
+        except Exception:          # noqa: BLE001
+            pass

@@ -89,6 +89,8 @@ SIGNATURES = {
     "fnet_gather_rows": (C.c_int, [_I32, _I64, _P, _P, _P, _P, _P]),
     "fnet_gather_shift_flip": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "fnet_u8_to_f32": (C.c_int, [_I64, _P, _F, _P, _P]),
+    "fnet_stream_create": (C.c_int, [C.POINTER(_P)]),
+    "fnet_stream_destroy": (C.c_int, [_P]),
     "fnet_graph_begin": (C.c_int, [_P]),
     "fnet_graph_end": (C.c_int, [_P, C.POINTER(_P)]),
     "fnet_graph_launch": (C.c_int, [_P, _P]),

@@ -303,6 +303,12 @@ int fnet_l2_attack_step(int32_t batch, int64_t row, const float *x0, const float
  * CUDA-graph helpers: one train step (or eval step) is captured once and replayed, which
  * replaces one `session.run` per step.
  * ------------------------------------------------------------------------------------------ */
+/* A stream of the caller's own (cudaStreamNonBlocking).  Every candidate that is resident on a GPU captures and replays
+ * its steps on streams nobody else uses: a stream handed out by a framework's pool (torch recycles 32 per device)
+ * can be shared by two candidates, and launches that one host thread issues while another thread is capturing on
+ * the same stream are recorded into the wrong graph instead of being run. */
+int fnet_stream_create(void **stream_out);
+int fnet_stream_destroy(void *stream);
 int fnet_graph_begin(void *stream);
 int fnet_graph_end(void *stream, void **graph_exec_out);
 int fnet_graph_launch(void *graph_exec, void *stream);

@@ -70,10 +70,13 @@ def main():
         if reference is None:
             reference = accs
         same = accs == reference
+        differ = [(i, a, b) for i, (a, b) in enumerate(zip(accs, reference)) if a != b and not (a != a and b != b)]
         if valid != buildable or not same:
             bad += 1
         print("pass %2d: valid %d/%d retried %d same_accuracies %s %.2fs peak_mem %.1f GB %s" % (
             n, valid, buildable, retried, same, dt, torch.cuda.max_memory_allocated() / 2**30, json.dumps(errors)[:600]), flush=True)
+        if not same:
+            print("   differ (index, now, pass 0):", differ[:12], flush=True)
     print("RESULT bad_passes=%d of %d" % (bad, args.passes))
     return 1 if bad else 0
 
