@@ -43,6 +43,7 @@ WORKLOADS = {
     "lenet5": ("lenet5", None, "mnist", "lenet5 template, MNIST-shape 28x28x1, batch 128"),
     "wide": ("tests/golden/nas_5_5_10_seed0.pdt", 9, "cifar",
              "nas_5_5_10.xml seed-0 sample, product #9 (98.6 MFLOP/img fwd), CIFAR-shape, batch 128"),
+    "keras": ("keras", None, "cifar", "keras template (5.34 M parameters, 634 MFLOP/img train), CIFAR-shape, batch 128"),
 }
 
 
@@ -503,6 +504,102 @@ def roofline_from(table, pk):
             "algorithmic_bytes_per_launch": row["bytes"] / row["launches"],
             "algorithmic_flops_per_launch": row["flops"] / row["launches"], "peak_source": pk["source"],
             "tflops_achieved": row["flops"] / secs / 1e12}
+
+
+def run_dp(args, torch, dist, world, rank, local):
+    """BASELINE configs[4], the single large candidate: the `keras` template (5.34 M parameters) trained data-parallel
+    over all ranks, global batch 128, through Engine's ordinary step with the NCCL all-reduce captured in its graph."""
+    from featurenet_b200 import synth
+    from featurenet_b200.optimizers import Adam
+    os.environ["FNET_DP"] = "1"
+    workload = args.workload if args.workload != "nas1" else "keras"
+    model, net, dataset = build_candidate(workload)
+    with quiet():
+        (x_train, y_train), _ = synth.load(dataset, 12800, 128)
+    n = x_train.shape[0]
+    net.compile(loss="categorical_crossentropy", metrics=["accuracy"], optimizer=Adam(lr=1e-3))
+    eng = net._need_engine()
+    if world > 1 and eng.dp is None:
+        raise SystemExit("--dp needs the process group (launch with torchrun)")
+    local_rows = eng.dp.slice_of(BATCH)[0] if eng.dp else BATCH
+    eng._ensure_capacity(max(local_rows, 1), max(local_rows, 1))
+    eng._set_data("train", x_train, y_train)
+    eng._sync_lr()
+    kind = "train_dp:%d" % BATCH if eng.dp else "train"
+    steps_per_epoch = n // BATCH
+    done = [0]
+
+    def run(k):
+        for _ in range(k):
+            if done[0] % steps_per_epoch == 0:
+                eng._zero_metrics(eng.state)
+            eng._step(kind, local_rows)
+            done[0] += 1
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    run(max(args.warmup, 3))
+    barrier()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record(eng.stream)
+    run(args.steps)
+    p1.record(eng.stream)
+    barrier()
+    repeats = int(min(max(1, math.ceil(1e3 * MIN_TIMED_SECONDS / max(p0.elapsed_time(p1), 1e-3))), 2000))
+    if world > 1:
+        t = torch.tensor([repeats], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        repeats = int(t.item())
+    sampler = ClockSampler(local)
+    sampler.wait_for_samples()
+    time.sleep(1.0)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(eng.stream)
+    for _ in range(repeats):
+        run(args.steps)
+    e1.record(eng.stream)
+    barrier()
+    ms = e0.elapsed_time(e1) / repeats
+    clocks = sampler.stop()
+    # the collective alone, same message, same stream
+    ar_ms = None
+    if eng.dp:
+        for _ in range(5):
+            eng._allreduce_grads()
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(eng.stream)
+        for _ in range(50):
+            eng._allreduce_grads()
+        a1.record(eng.stream)
+        barrier()
+        ar_ms = a0.elapsed_time(a1) / 50
+    if world > 1:
+        t = torch.tensor([ms, ar_ms or 0.0], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ar_ms = float(t[0].item()), float(t[1].item())
+    if rank == 0:
+        msg = 4 * eng.n_params
+        line = {"metric": METRIC, "value": args.steps * BATCH / (ms / 1e3), "unit": "images/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": dict(config_for(workload, world), parallelism="data-parallel x%d, global batch %d (%d rows per rank), "
+                               "NCCL all-reduce of the flat gradient arena inside the captured step" % (world, BATCH, local_rows)),
+                "clocks": clocks, "gpu_launches": eng.launches_per_step[(kind, local_rows)] * args.steps,
+                "timing": {"repeats": repeats},
+                "data_parallel": {"params": net.count_params(), "allreduce_bytes": msg if eng.dp else 0,
+                                  "allreduce_ms_alone": ar_ms, "single_graph": bool(eng.dp and eng.dp_single_graph),
+                                  "allreduce_algbw_gbs": (msg / (ar_ms * 1e-3) / 1e9) if ar_ms else None,
+                                  "allreduce_busbw_gbs": (msg / (ar_ms * 1e-3) / 1e9 * 2 * (world - 1) / world) if ar_ms else None,
+                                  "allreduce_share_of_step": (ar_ms / (ms / args.steps)) if ar_ms else None}}
+        emit(line)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def run_ours(args):

@@ -6,9 +6,9 @@ appends ``Flatten`` + ``Dense(n_classes, softmax, name="out")``, rejects candida
 20 M parameters and turns any construction error into ``None`` (printed traceback), which
 is what makes ``TensorflowGenerator`` report "model is not valid".
 
-The reference's ``multi_gpu_model`` branch (keras_model.py:137-146) has no counterpart
-here: whole candidates are placed on GPUs by ``featurenet_b200.population`` and the one
-large candidate is trained data-parallel by ``featurenet_b200.dataparallel``.
+The reference's ``multi_gpu_model`` branch (keras_model.py:137-146) becomes data-parallel training over the
+ranks of the process group when ``FNET_DP=1`` (``featurenet_b200.dataparallel``); without it whole candidates
+are placed on GPUs by ``featurenet_b200.population``.
 """
 from __future__ import absolute_import, division, print_function, unicode_literals
 
@@ -123,6 +123,18 @@ class KerasFeatureModel(MutableModel):
                 print("#### model is bigger than 20M params. Skipped")
                 model.summary()
                 return None
+
+            if KerasFeatureModel.use_multigpu:
+                # keras_model.py:137-146: with two or more GPUs the model is wrapped for batch-split data parallelism,
+                # otherwise "multi gpu not available" is printed and the switch turns itself off.  Here the GPUs are the
+                # ranks of the process group and the mode is asked for with FNET_DP=1 (a population run keeps whole
+                # candidates per GPU instead: featurenet_b200.population).
+                from featurenet_b200 import dataparallel
+                if dataparallel.wanted():
+                    model = dataparallel.multi_gpu_model(model)
+                else:
+                    print("multi gpu not available")
+                    KerasFeatureModel.use_multigpu = False
         except Exception as e:
             print("error", e)
             print(traceback.format_exc())

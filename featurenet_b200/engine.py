@@ -132,6 +132,10 @@ class Engine(object):
         self.timing = {"alloc_s": 0.0, "capture_s": 0.0, "train_s": 0.0, "eval_s": 0.0, "train_steps": 0, "eval_steps": 0}
         self.use_graphs = os.environ.get("FNET_NO_GRAPH", "0") != "1"
         self.poison = os.environ.get("FNET_POISON", "0") == "1"
+        self.dp = None                # featurenet_b200.dataparallel.DataParallel once enable_data_parallel() ran
+        # the NCCL all-reduce is captured into the step's CUDA graph (FNET_DP_SINGLE_GRAPH=0: two graphs around an
+        # eagerly issued collective)
+        self.dp_single_graph = os.environ.get("FNET_DP_SINGLE_GRAPH", "1") != "0"
         self._plan_params()
         self._init_weights()
         with self._on_stream():
@@ -253,6 +257,35 @@ class Engine(object):
             self.adam_v.zero_()
             self.state.zero_()
         self._lr_on_device = None
+
+    # ------------------------------------------------------------------ data-parallel mode (one large candidate)
+    def enable_data_parallel(self, dist, rank=None, world=None):
+        """Train this candidate over all ranks of the process group (see featurenet_b200/dataparallel.py)."""
+        from .dataparallel import DataParallel
+        self.dp = DataParallel(dist, rank, world)
+        self.stream.synchronize()
+        self._drop_graphs()
+        with self._on_stream():
+            dist.broadcast(self.params, src=0)            # replicas start identical: rank 0's weights win
+            dist.broadcast(self.stats, src=0)
+        self.stream.synchronize()
+        # every rank draws its own dropout masks (the towers of multi_gpu_model do)
+        self.dropout_seed = (self.dropout_seed + 0x9E3779B97F4A7C15 * self.dp.rank) & 0xFFFFFFFFFFFFFFFF
+        return self
+
+    def _allreduce_grads(self):
+        """SUM of the flat gradient arena over the ranks, in stream order (captured into the step's graph)."""
+        with self._on_stream():
+            self.dp.dist.all_reduce(self.grads, op=self.dp.dist.ReduceOp.SUM)
+        self.dp.allreduce_calls += 1
+        self.dp.allreduce_bytes = 4 * self.n_params
+
+    def _average_stats(self):
+        """BatchNorm moving statistics: mean over the ranks (each rank saw its own slices)."""
+        if self.n_stats:
+            with self._on_stream():
+                self.dp.dist.all_reduce(self.stats, op=self.dp.dist.ReduceOp.SUM)
+                self.stats.mul_(1.0 / self.dp.world)
 
     def snapshot(self, into=None):
         """Device-to-device copy of the weights (ModelCheckpoint / SGDR restarts)."""
@@ -691,6 +724,8 @@ class Engine(object):
         if kind == "grad_logits":       # as above, but the caller also fills the head's dz: no loss in between
             return (self._forward_program(batch, False, save_for_backward=True) +
                     self._backward_program(batch, training=False, input_grad=True))
+        if kind.startswith("train_dp:"):
+            return self._build_dp_program(int(kind.split(":")[1]), batch)
         training = kind.startswith("train")
         state = self.state if training else self.state_eval
         st = C.c_void_p(state.data_ptr())
@@ -751,6 +786,32 @@ class Engine(object):
             ops.append(("step_end", L.fnet_step_end, (st, batch, sp)))
         return ops
 
+    def _build_dp_program(self, global_batch, local):
+        """One data-parallel step: this rank's slice (`local` rows, possibly none) of a global batch, the gradient
+        all-reduce, and the optimizer, which advances the epoch cursor by the GLOBAL batch."""
+        L, sp = self.lib, self.sp
+        st = C.c_void_p(self.state.data_ptr())
+        opt = self.net.optimizer
+        b1, b2 = (opt.beta_1, opt.beta_2) if opt.kind == "adam" else (0.9, 0.999)
+        _, start = self.dp.slice_of(global_batch)
+        xdev, ydev, perm = self.data["train"]
+        ops = []
+        if local > 0:
+            # the cursor points at the global batch; this rank's slice starts `start` rows further into the permutation
+            ops.append(("gather_batch", L.fnet_gather_batch,
+                        (local, _prod(self.shape[0]), self.n_out, C.c_void_p(perm.data_ptr() + 4 * start), st,
+                         C.c_void_p(xdev.data_ptr()), C.c_void_p(ydev.data_ptr()), C.c_void_p(self.act[0].data_ptr()),
+                         C.c_void_p(self.yb.data_ptr()), 1, b1, b2, sp)))
+            ops += self._forward_program(local, True)
+            ops.append(self._loss_op(local, True, scale_batch=global_batch))
+            ops += self._backward_program(local)
+        else:
+            ops.append(("step_begin", L.fnet_step_begin, (st, b1, b2, sp)))
+            ops.append(("fill", L.fnet_fill, (self.n_params, 0.0, C.c_void_p(self.grads.data_ptr()), sp)))
+        ops.append(("allreduce", None, ()))
+        ops.append(self._optimizer_op(advance=global_batch))
+        return ops
+
     def _fork(self):
         """Everything enqueued so far on the main stream happens before what the side stream gets next."""
         event = torch.cuda.Event()
@@ -771,12 +832,17 @@ class Engine(object):
                     fn(*args)
                 elif label == "fork":
                     self._fork()
+                elif label == "allreduce":
+                    self._allreduce_grads()
                 else:
                     self._join()
             return
         # profiling: one event pair per launch, on the stream it runs on; side launches are serialised
         # (fork, launch, join) so that every kernel is timed alone
         for label, fn, args in ops:
+            if label == "allreduce":
+                self._allreduce_grads()
+                continue
             if fn is None:
                 continue
             on_side = isinstance(label, SideLabel)
@@ -888,6 +954,17 @@ class Engine(object):
         if not self.use_graphs or self.timeline is not None:
             self._run_ops(ops)
             return
+        if self.dp is not None and kind.startswith("train_dp:") and not self.dp_single_graph:
+            # the collective stays outside the graphs: [slice forward/backward] -> all-reduce -> [optimizer]
+            first, second = self.graphs.get((kind + "/a", batch)), self.graphs.get((kind + "/b", batch))
+            if first is None:
+                at = [op[0] for op in ops].index("allreduce")
+                first = self.graphs[(kind + "/a", batch)] = self._capture(ops[:at])
+                second = self.graphs[(kind + "/b", batch)] = self._capture(ops[at + 1:])
+            self.lib.fnet_graph_launch(first, self.sp)
+            self._allreduce_grads()
+            self.lib.fnet_graph_launch(second, self.sp)
+            return
         self.lib.fnet_graph_launch(self._graph(kind, batch), self.sp)
 
     def _program(self, kind, batch):
@@ -896,7 +973,7 @@ class Engine(object):
         ops = self.programs.get(key)
         if ops is None:
             # split plans depend on the batch (fewer rows -> more splits), so the shared workspace may have to grow
-            need = max(self._workspace_need(i, batch) for i in range(len(self.nodes)))
+            need = max(self._workspace_need(i, max(batch, 1)) for i in range(len(self.nodes)))
             if need > self.ws_bytes:
                 self.stream.synchronize()
                 self._drop_graphs()                      # programs hold the old workspace pointer
@@ -973,6 +1050,9 @@ class Engine(object):
 
     def _read_metrics(self, n):
         loss_sum, correct = self._fetch_metrics()
+        if self.dp is not None:       # every rank scored its slices / its shard: one all-reduce, same numbers everywhere
+            from .dataparallel import reduce_metrics
+            loss_sum, correct = reduce_metrics(self.dp.dist, loss_sum, correct, device=self.device)
         return loss_sum / n, correct / n
 
     def _zero_metrics(self, state):
@@ -1005,14 +1085,21 @@ class Engine(object):
         self._set_data("eval", x, y)
         # (the identity order the validation set was given in _set_data is never overwritten: nothing to upload)
         self._zero_metrics(self.state_eval)
-        full = n // eb
+        rows = n
+        if self.dp is not None:
+            # sharded by sample: this rank scores rows [lo, hi) of the set; _read_metrics sums over the ranks
+            lo, hi = self.dp.shard_of(n)
+            rows = hi - lo
+            with self._on_stream():
+                self.state_eval[1:2].fill_(lo)
+        full = rows // eb
         if full and self.use_graphs and self.timeline is None:
             self.lib.fnet_graph_launch_n(self._graph("eval", eb), full, self.sp)
         else:
             for _ in range(full):
                 self._step("eval", eb)
-        if n - full * eb:
-            self._step("eval", n - full * eb)
+        if rows - full * eb:
+            self._step("eval", rows - full * eb)
         loss, acc = self._read_metrics(n)
         self.timing["eval_s"] += time.perf_counter() - t_eval
         self.timing["eval_steps"] += -(-n // eb)
@@ -1179,13 +1266,24 @@ class Engine(object):
             else:
                 order = np.arange(n, dtype=np.int32)
             with torch.cuda.stream(self.stream):
-                perm_dev.copy_(torch.from_numpy(order))
+                if self.dp is not None:
+                    perm_dev.copy_(self.dp.broadcast_order(order, self.device))      # rank 0's shuffle, everywhere
+                else:
+                    perm_dev.copy_(torch.from_numpy(order))
                 if augment is not None:                 # this epoch's random shifts / flips, indexed by position
                     for dev_arr, host_arr in zip(self.aug_dev, augment.draw(n)):
                         dev_arr.copy_(torch.from_numpy(host_arr))
             self._zero_metrics(self.state)
             t_train = time.perf_counter()
-            if not per_batch and self.use_graphs and self.timeline is None:
+            if self.dp is not None:
+                for step in range(steps):
+                    g = min(batch_size, n - step * batch_size)
+                    self._sync_lr()
+                    self._step("train_dp:%d" % g, self.dp.slice_of(g)[0])
+                    for cb in per_batch:
+                        cb.on_batch_end(step, {"batch": step, "size": g})
+                self._average_stats()
+            elif not per_batch and self.use_graphs and self.timeline is None:
                 # nothing on the host looks at single batches: the epoch's full batches are ONE call into the library
                 # (floor(n / batch) replays of the captured step), the ragged last batch a second one
                 self._sync_lr()

@@ -84,8 +84,21 @@ class Network(object):
     def _need_engine(self):
         if self._engine is None:
             from .engine import Engine
+            from . import dataparallel
             self._engine = Engine(self)
+            if getattr(self, "data_parallel", False) or dataparallel.wanted():
+                import torch.distributed as dist
+                self._engine.enable_data_parallel(dist)
         return self._engine
+
+    def enable_data_parallel(self, dist=None):
+        """Train this candidate data-parallel over the process group (keras_model.py:137-146's multi_gpu_model)."""
+        self.data_parallel = True
+        if self._engine is not None and self._engine.dp is None:
+            if dist is None:
+                import torch.distributed as dist
+            self._engine.enable_data_parallel(dist)
+        return self
 
     def compile(self, loss="categorical_crossentropy", metrics=None, optimizer=None, **_):
         from .optimizers import resolve_optimizer
