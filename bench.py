@@ -508,7 +508,7 @@ def roofline_from(table, pk):
 
 def run_dp(args, torch, dist, world, rank, local):
     """BASELINE configs[4], the single large candidate: the `keras` template (5.34 M parameters) trained data-parallel
-    over all ranks, global batch 128, through Engine's ordinary step with the NCCL all-reduce captured in its graph."""
+    over all ranks, global batch 128, through Engine's ordinary data-parallel step."""
     from featurenet_b200 import synth
     from featurenet_b200.optimizers import Adam
     os.environ["FNET_DP"] = "1"
@@ -588,7 +588,7 @@ def run_dp(args, torch, dist, world, rank, local):
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": dict(config_for(workload, world), parallelism="data-parallel x%d, global batch %d (%d rows per rank), "
-                               "NCCL all-reduce of the flat gradient arena inside the captured step" % (world, BATCH, local_rows)),
+                               "one NCCL all-reduce of the flat gradient arena between the captured backward and optimizer graphs" % (world, BATCH, local_rows)),
                 "clocks": clocks, "gpu_launches": eng.launches_per_step[(kind, local_rows)] * args.steps,
                 "timing": {"repeats": repeats},
                 "data_parallel": {"params": net.count_params(), "allreduce_bytes": msg if eng.dp else 0,

@@ -12,8 +12,8 @@ equivalent here, one process per GPU (torchrun), lives INSIDE the ordinary engin
   each rank runs forward, loss and backward on its slice with the loss scaled by 1/G, so the SUM
   of the per-rank gradients is the gradient of the global-batch mean;
 * ONE ``all_reduce(SUM)`` over the flat ``grads`` arena (4 bytes x parameters: 21 MB for the
-  ``keras`` template, <= 80 MB at the 20 M-parameter cap), issued between the backward pass and the
-  optimizer INSIDE the captured step -- on NVSwitch every GPU reaches every peer at full bandwidth, so a
+  ``keras`` template, <= 80 MB at the 20 M-parameter cap), issued between the captured backward pass and the
+  captured optimizer launch -- on NVSwitch every GPU reaches every peer at full bandwidth, so a
   single large message is the bandwidth-optimal shape;
 * the ordinary fused Adam launch on every rank (replicas stay bit-identical because the
   all-reduce result is), which also advances the epoch cursor by the GLOBAL batch;

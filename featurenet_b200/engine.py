@@ -133,9 +133,11 @@ class Engine(object):
         self.use_graphs = os.environ.get("FNET_NO_GRAPH", "0") != "1"
         self.poison = os.environ.get("FNET_POISON", "0") == "1"
         self.dp = None                # featurenet_b200.dataparallel.DataParallel once enable_data_parallel() ran
-        # the NCCL all-reduce is captured into the step's CUDA graph (FNET_DP_SINGLE_GRAPH=0: two graphs around an
-        # eagerly issued collective)
-        self.dp_single_graph = os.environ.get("FNET_DP_SINGLE_GRAPH", "1") != "0"
+        # A data-parallel step is two captured graphs around an eagerly issued NCCL all-reduce.  FNET_DP_SINGLE_GRAPH=1
+        # captures the collective into one graph with the rest of the step: it replays correctly in a steady loop, but
+        # mixed with the eager collectives of the mode (metric reduction, permutation broadcast) through
+        # torch.distributed it deadlocked in tests/dp_check.py on 2 B200s -- kept as an experiment, off by default.
+        self.dp_single_graph = os.environ.get("FNET_DP_SINGLE_GRAPH", "0") == "1"
         self._plan_params()
         self._init_weights()
         with self._on_stream():
