@@ -132,6 +132,8 @@ class Engine(object):
         self.timing = {"alloc_s": 0.0, "capture_s": 0.0, "train_s": 0.0, "eval_s": 0.0, "train_steps": 0, "eval_steps": 0}
         self.use_graphs = os.environ.get("FNET_NO_GRAPH", "0") != "1"
         self.poison = os.environ.get("FNET_POISON", "0") == "1"
+        self.fuse_steps = os.environ.get("FNET_FUSED", "1") != "0"
+        self._fused_keep, self.fused_summary = {}, {}
         self.dp = None                # featurenet_b200.dataparallel.DataParallel once enable_data_parallel() ran
         # A data-parallel step is two captured graphs around an eagerly issued NCCL all-reduce.  FNET_DP_SINGLE_GRAPH=1
         # captures the collective into one graph with the rest of the step: it replays correctly in a steady loop, but
@@ -863,6 +865,9 @@ class Engine(object):
     def op_work(label, args):
         """Algorithmic (flops, bytes) of one launch, the figures of SURVEY.md section 8(d) used for rooflines."""
         f = b = 0
+        if label == "fused_step":
+            from . import fused
+            return fused.WORK.get(args[0].value, (0, 0))
         if label.startswith("conv2d") or label.startswith("dwconv2d"):
             d = args[0]
             m_out, m_in = d.batch * d.out_h * d.out_w, d.batch * d.in_h * d.in_w
@@ -948,6 +953,7 @@ class Engine(object):
         for g in self.graphs.values():
             self.lib.fnet_graph_destroy(g)
         self.graphs, self.programs = {}, {}
+        self._fused_keep, self.fused_summary = {}, {}
         self.generation += 1
 
     def _step(self, kind, batch):
@@ -980,7 +986,17 @@ class Engine(object):
                 self.stream.synchronize()
                 self._drop_graphs()                      # programs hold the old workspace pointer
                 self._alloc_workspace(need)
-            ops = self.programs[key] = self._build_program(kind, batch)
+            ops = self._build_program(kind, batch)
+            if self.fuse_steps and batch > 0 and (kind.startswith("train") or kind == "eval") and ":" not in kind:
+                # a step made of small-channel layers only becomes ONE launch of the fused step kernel (fused.py)
+                from . import fused
+                made = fused.try_fuse(self, ops)
+                if made is not None:
+                    launch, keep, summary = made
+                    ops = [launch]
+                    self._fused_keep[key] = keep
+                    self.fused_summary[key] = summary
+            self.programs[key] = ops
             self.launches_per_step = getattr(self, "launches_per_step", {})
             self.launches_per_step[key] = sum(1 for op in ops if op[1] is not None)
         return ops

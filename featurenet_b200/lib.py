@@ -89,6 +89,10 @@ SIGNATURES = {
     "fnet_gather_rows": (C.c_int, [_I32, _I64, _P, _P, _P, _P, _P]),
     "fnet_gather_shift_flip": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "fnet_u8_to_f32": (C.c_int, [_I64, _P, _F, _P, _P]),
+    "fnet_fused_step_grid": (C.c_int, []),
+    "fnet_fused_conv_supported": (C.c_int, [_CD, C.c_int, C.c_int]),
+    "fnet_fused_head_supported": (C.c_int, [_I64, _I64, _I64]),
+    "fnet_fused_step": (C.c_int, [_P, _I32, _P, _P]),
     "fnet_stream_create": (C.c_int, [C.POINTER(_P)]),
     "fnet_stream_destroy": (C.c_int, [_P]),
     "fnet_graph_begin": (C.c_int, [_P]),
@@ -105,7 +109,8 @@ SIGNATURES = {
                                            _P, _P, _P, _P]),
 }
 
-_QUERIES = {"fnet_version", "fnet_conv2d_bwd_data_on_tensor_core", "fnet_dense_bwd_data_on_tensor_core"}    # return a value, not a status
+_QUERIES = {"fnet_version", "fnet_conv2d_bwd_data_on_tensor_core", "fnet_dense_bwd_data_on_tensor_core",
+            "fnet_fused_step_grid", "fnet_fused_conv_supported", "fnet_fused_head_supported"}    # return a value, not a status
 _STATUS_RETURNING = {n for n, (r, _) in SIGNATURES.items() if r is C.c_int and n not in _QUERIES}
 
 

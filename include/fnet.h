@@ -303,6 +303,47 @@ int fnet_l2_attack_step(int32_t batch, int64_t row, const float *x0, const float
  * CUDA-graph helpers: one train step (or eval step) is captured once and replayed, which
  * replaces one `session.run` per step.
  * ------------------------------------------------------------------------------------------ */
+/* ------------------------------------------------------------------------------------------
+ * Fused step.  A candidate with a handful of narrow layers (the products of main_1block_nas.xml: 1x1 / 2x2
+ * convolutions between 3 and 6 channels, a concatenation, the softmax head -- 61 k parameters, 3 MB of activations
+ * per batch) spends its step in launch latency: 13 launches of 4 us for 7 us of memory traffic.  Replaces the
+ * whole `train_function` of one step (helpers.py:105 -> Model.fit) with ONE cooperative launch: a persistent
+ * kernel, one CTA per SM, walks the list of operations below and separates dependent operations by a grid-wide
+ * barrier instead of a kernel boundary; the activations stay in L2 from one operation to the next.
+ * `ops` lives in DEVICE memory (the caller uploads it once per program); operations are executed in order, and
+ * `barrier_after` says where later operations depend on earlier ones.  `sync` is two zero-initialised uint32 in
+ * device memory owned by this program (never shared between programs that may run concurrently).
+ * ------------------------------------------------------------------------------------------ */
+enum {
+    FNET_FK_BEGIN = 1,        /* p0 state; f0 beta1, f1 beta2: fnet_step_begin */
+    FNET_FK_GATHER = 2,       /* fnet_gather_batch: d0 batch d1 x_row d2 y_row d3 begin_step; p0 perm p1 state p2 x_src p3 y_src p4 x_dst p5 y_dst; f0 f1 betas */
+    FNET_FK_FEED_U8 = 3,      /* fnet_feed_batch_u8: d0 batch d1 x_row d2 y_row d3 begin_step; p0 state p1 x_src(u8) p2 y_src p3 x_dst p4 y_dst; f0 f1 betas f2 scale */
+    FNET_FK_CONV_FWD = 4,     /* d0..d14 = B H W C Ho Wo K kh kw sh sw pt pl dh dw; act; p0 x p1 w p2 bias p3 y */
+    FNET_FK_CONV_DGRAD = 5,   /* geometry as above; flags bit0 accumulate; act = activation of the producer (0 none); p0 dz p1 w p2 dx p3 y_of_producer */
+    FNET_FK_CONV_WGRAD = 6,   /* geometry; flags bit0 = with bias row; p0 x p1 dz p2 partial[grid][rows*K] */
+    FNET_FK_REDUCE = 7,       /* d0 parts d1 total d2 split (first d2 values -> p1, the rest -> p2); p0 partial p1 dw p2 dbias */
+    FNET_FK_CONCAT_FWD = 8,   /* d0 outer d1 blk_a d2 blk_b (elements per outer index); p0 a p1 b p2 y */
+    FNET_FK_CONCAT_BWD = 9,   /* same dims; flags bit0 acc_a bit1 acc_b; p0 dy p1 da (may be NULL) p2 db (may be NULL) */
+    FNET_FK_HEAD_FWD_LOSS = 10, /* Dense(softmax) + categorical cross-entropy: d0 M d1 K d2 N; f0 scale; p0 x p1 w p2 bias p3 probs p4 targets p5 dz p6 row_loss[M] p7 row_hit[M] */
+    FNET_FK_HEAD_DGRAD = 11,  /* d0 M d1 K d2 N; flags bit0 accumulate; act; p0 dz p1 w p2 dx p3 y_of_producer */
+    FNET_FK_HEAD_WGRAD = 12,  /* d0 M d1 K d2 N; p0 x p1 dz p2 dw p3 dbias */
+    FNET_FK_ACT_BWD = 13,     /* d0 n (low 31 bits) ; flags bit0 accumulate; act; p0 y p1 dy p2 dx */
+    FNET_FK_ADAM = 14,        /* d0 n d1 advance d2 M (rows of the loss, 0 = none); f0 b1 f1 b2 f2 eps; p0 params p1 grads p2 m p3 v p4 state p5 row_loss p6 row_hit p7 metrics(double loss_sum, int64 correct) */
+    FNET_FK_SGD = 15          /* d0 n d1 advance d2 M d3 nesterov; f0 momentum; p0 params p1 grads p2 velocity p4 state p5 row_loss p6 row_hit p7 metrics */
+};
+typedef struct fnet_fused_op {
+    int32_t kind, barrier_after, flags, act;
+    int32_t d[16];
+    float f[4];
+    void *p[8];
+} fnet_fused_op;
+/* CTAs the fused kernel must be launched with on the current device (its operation list sizes partials by it). */
+int fnet_fused_step_grid(void);
+/* 1 when a convolution / head of this shape has a fused implementation (small channel counts only), else 0. */
+int fnet_fused_conv_supported(const fnet_conv2d_desc *d, int product /* 0 fwd, 1 dgrad, 2 wgrad */, int with_bias);
+int fnet_fused_head_supported(int64_t m, int64_t k, int64_t n);
+int fnet_fused_step(const fnet_fused_op *ops_dev, int32_t n_ops, uint32_t *sync, void *stream);
+
 /* A stream of the caller's own (cudaStreamNonBlocking).  Every candidate that is resident on a GPU captures and replays
  * its steps on streams nobody else uses: a stream handed out by a framework's pool (torch recycles 32 per device)
  * can be shared by two candidates, and launches that one host thread issues while another thread is capturing on
