@@ -21,6 +21,7 @@ namespace fnet {
 
 constexpr int FS_THREADS = 512;
 constexpr int FS_SMEM_FLOATS = 10240;          // 40 KB: a layer's filter (+ bias row), or the head's dz block
+constexpr int FS_MAX_OPS = 48;                 // operations of one step (7.5 KB of shared memory)
 constexpr int FS_WGRAD_ACC = 64;               // partial sums of a small filter gradient a thread keeps in registers
 
 // ------------------------------------------------------------------ grid-wide barrier
@@ -30,10 +31,14 @@ __device__ __forceinline__ void grid_barrier(unsigned *counter) {
     __syncthreads();
     if (threadIdx.x == 0) {
         const unsigned add = blockIdx.x == 0 ? 0x80000000u - (gridDim.x - 1) : 1u;
-        __threadfence();
-        const unsigned seen = atomicAdd(counter, add);
-        while ((((seen ^ *reinterpret_cast<volatile unsigned *>(counter)) & 0x80000000u) == 0)) { }
-        __threadfence();
+        unsigned seen, now;
+        // release: everything this CTA wrote (ordered before by the __syncthreads above) is visible to whoever
+        // acquires the counter afterwards; acquire: ... and what the others wrote is visible to this CTA after the
+        // __syncthreads below
+        asm volatile("atom.add.release.gpu.global.u32 %0, [%1], %2;" : "=r"(seen) : "l"(counter), "r"(add) : "memory");
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(now) : "l"(counter) : "memory");
+        } while (((seen ^ now) & 0x80000000u) == 0);
     }
     __syncthreads();
 }
@@ -110,33 +115,52 @@ __device__ void fs_feed_u8(const fnet_fused_op &op) {
 }
 
 // ------------------------------------------------------------------ merges, activation derivative
+template <typename T>
+__device__ __forceinline__ void concat_fwd_body(int outer, int blk_a, int blk_b, const T *a, const T *b, T *y) {
+    const int blk = blk_a + blk_b, total = outer * blk;
+    for (int i = blockIdx.x * FS_THREADS + threadIdx.x; i < total; i += gridDim.x * FS_THREADS) {
+        const int o = i / blk, e = i - o * blk;
+        y[i] = e < blk_a ? a[o * blk_a + e] : b[o * blk_b + (e - blk_a)];
+    }
+}
+
 __device__ void fs_concat_fwd(const fnet_fused_op &op) {
-    const int outer = op.d[0], blk_a = op.d[1], blk_b = op.d[2], blk = blk_a + blk_b;
+    const int outer = op.d[0], blk_a = op.d[1], blk_b = op.d[2];
     const float *a = static_cast<const float *>(op.p[0]), *b = static_cast<const float *>(op.p[1]);
     float *y = static_cast<float *>(op.p[2]);
-    const long long total = (long long)outer * blk;
-    for (long long i = (long long)blockIdx.x * FS_THREADS + threadIdx.x; i < total; i += (long long)gridDim.x * FS_THREADS) {
-        const int o = (int)(i / blk), e = (int)(i - (long long)o * blk);
-        y[i] = e < blk_a ? a[(long long)o * blk_a + e] : b[(long long)o * blk_b + (e - blk_a)];
+    if (!((blk_a | blk_b) & 3) && !((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(y)) & 15))
+        concat_fwd_body(outer, blk_a >> 2, blk_b >> 2, reinterpret_cast<const float4 *>(a), reinterpret_cast<const float4 *>(b),
+                        reinterpret_cast<float4 *>(y));
+    else
+        concat_fwd_body(outer, blk_a, blk_b, a, b, y);
+}
+
+__device__ __forceinline__ float vsum(float a, float b) { return a + b; }
+__device__ __forceinline__ float4 vsum(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+
+template <typename T>
+__device__ __forceinline__ void concat_bwd_body(int outer, int blk_a, int blk_b, const T *dy, T *da, T *db, int acc_a, int acc_b) {
+    const int blk = blk_a + blk_b, total = outer * blk;
+    for (int i = blockIdx.x * FS_THREADS + threadIdx.x; i < total; i += gridDim.x * FS_THREADS) {
+        const int o = i / blk, e = i - o * blk;
+        if (e < blk_a) {
+            if (da) { T *d = da + o * blk_a + e; *d = acc_a ? vsum(*d, dy[i]) : dy[i]; }
+        } else if (db) {
+            T *d = db + o * blk_b + (e - blk_a);
+            *d = acc_b ? vsum(*d, dy[i]) : dy[i];
+        }
     }
 }
 
 __device__ void fs_concat_bwd(const fnet_fused_op &op) {
-    const int outer = op.d[0], blk_a = op.d[1], blk_b = op.d[2], blk = blk_a + blk_b;
+    const int outer = op.d[0], blk_a = op.d[1], blk_b = op.d[2], acc_a = op.flags & 1, acc_b = op.flags & 2;
     const float *dy = static_cast<const float *>(op.p[0]);
     float *da = static_cast<float *>(op.p[1]), *db = static_cast<float *>(op.p[2]);
-    const int acc_a = op.flags & 1, acc_b = op.flags & 2;
-    const long long total = (long long)outer * blk;
-    for (long long i = (long long)blockIdx.x * FS_THREADS + threadIdx.x; i < total; i += (long long)gridDim.x * FS_THREADS) {
-        const int o = (int)(i / blk), e = (int)(i - (long long)o * blk);
-        const float g = dy[i];
-        if (e < blk_a) {
-            if (da) { float *d = da + (long long)o * blk_a + e; *d = acc_a ? *d + g : g; }
-        } else if (db) {
-            float *d = db + (long long)o * blk_b + (e - blk_a);
-            *d = acc_b ? *d + g : g;
-        }
-    }
+    if (!((blk_a | blk_b) & 3) && !((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(da) | reinterpret_cast<uintptr_t>(db)) & 15))
+        concat_bwd_body(outer, blk_a >> 2, blk_b >> 2, reinterpret_cast<const float4 *>(dy), reinterpret_cast<float4 *>(da),
+                        reinterpret_cast<float4 *>(db), acc_a, acc_b);
+    else
+        concat_bwd_body(outer, blk_a, blk_b, dy, da, db, acc_a, acc_b);
 }
 
 __device__ void fs_act_bwd(const fnet_fused_op &op) {
@@ -332,9 +356,23 @@ struct SmemRow {
     __device__ float operator()(int c) const { return q[c]; }
 };
 
-// Dense(softmax) + categorical cross-entropy: one CTA per sample row.  Threads split the K inputs, the N sums are
-// folded (shuffle tree, warp slots in order), one thread finishes the row: softmax as keras does it
-// (exp(z - max) / sum), loss / hit / scale * dL/dlogits as fnet_softmax_cce does (loss_row.cuh).
+// (value, index) argmax over the first `n` lanes of a warp, first index on ties (what a scan with a strict > gives)
+__device__ __forceinline__ int warp_argmax(float v, int lane, int n) {
+    int idx = lane < n ? lane : 0x7fffffff;
+    if (lane >= n) v = -INFINITY;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+    }
+    return idx;
+}
+
+// Dense(softmax) + categorical cross-entropy: one CTA per sample row.  Threads split the K inputs (four at a time, so
+// that forty weight loads are in flight per thread), the N sums are folded (shuffle tree, warp slots in order), and the
+// first warp finishes the row with one class per lane: softmax as keras does it (exp(z - max) / sum), then loss / hit /
+// scale * dL/dlogits with the formulas of fnet_softmax_cce (loss_row.cuh), sums taken by shuffle trees.
 __device__ void fs_head_fwd_loss(const fnet_fused_op &op, float *smem) {
     const int M = op.d[0], K = op.d[1], N = op.d[2];
     const float *x = static_cast<const float *>(op.p[0]), *w = static_cast<const float *>(op.p[1]);
@@ -345,18 +383,23 @@ __device__ void fs_head_fwd_loss(const fnet_fused_op &op, float *smem) {
     const float scale = op.f[0];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float *red = smem;                       // [16 warps][16]
-    float *z = smem + 256;                   // [16] probabilities of the row
     for (int m = blockIdx.x; m < M; m += gridDim.x) {
         float acc[16];
 #pragma unroll
         for (int n = 0; n < 16; ++n) acc[n] = 0.f;
         const float *xr = x + (long long)m * K;
-        for (int k = threadIdx.x; k < K; k += FS_THREADS) {
-            const float xv = xr[k];
-            const float *wr = w + (long long)k * N;
+        for (int k0 = threadIdx.x; k0 < K; k0 += 4 * FS_THREADS) {
+            float xv[4];
 #pragma unroll
-            for (int n = 0; n < 16; ++n)
-                if (n < N) acc[n] = fmaf(xv, wr[n], acc[n]);
+            for (int u = 0; u < 4; ++u) xv[u] = k0 + u * FS_THREADS < K ? xr[k0 + u * FS_THREADS] : 0.f;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = k0 + u * FS_THREADS < K ? k0 + u * FS_THREADS : k0;       // a zero times a valid row
+                const float *wr = w + (long long)k * N;
+#pragma unroll
+                for (int n = 0; n < 16; ++n)
+                    if (n < N) acc[n] = fmaf(xv[u], wr[n], acc[n]);
+            }
         }
 #pragma unroll
         for (int n = 0; n < 16; ++n) {
@@ -364,22 +407,32 @@ __device__ void fs_head_fwd_loss(const fnet_fused_op &op, float *smem) {
             if (lane == 0) red[warp * 16 + n] = v;
         }
         __syncthreads();
-        if (threadIdx.x < N) {
-            float v = bias ? bias[threadIdx.x] : 0.f;
+        if (warp == 0) {
+            const bool mine = lane < N;
+            float zv = mine && bias ? bias[lane] : 0.f;
+            const float tv = mine ? targets[(long long)m * N + lane] : 0.f;
+            if (mine) {
 #pragma unroll
-            for (int wv = 0; wv < FS_THREADS / 32; ++wv) v += red[wv * 16 + threadIdx.x];
-            z[threadIdx.x] = v;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            float mx = -INFINITY, se = 0.f;
-            for (int n = 0; n < N; ++n) mx = fmaxf(mx, z[n]);
-            for (int n = 0; n < N; ++n) { z[n] = expf(z[n] - mx); se += z[n]; }
-            for (int n = 0; n < N; ++n) { z[n] = z[n] / se; probs[(long long)m * N + n] = z[n]; }
-            bool hit = false;
-            const float loss = row_loss(N, SmemRow{z}, SmemRow{targets + (long long)m * N}, scale, dz ? dz + (long long)m * N : nullptr, hit);
-            row_loss_out[m] = loss;
-            row_hit[m] = hit ? 1.f : 0.f;
+                for (int wv = 0; wv < FS_THREADS / 32; ++wv) zv += red[wv * 16 + lane];
+            }
+            const float mx = warp_max(mine ? zv : -INFINITY);
+            const float e = mine ? expf(zv - mx) : 0.f;
+            const float p = e / warp_sum(e);
+            if (mine) probs[(long long)m * N + lane] = p;
+            // categorical_crossentropy on the probabilities: renormalise, clip, -sum t log q; gradient through all of it
+            const float sum = warp_sum(mine ? p : 0.f);
+            const bool hit = warp_argmax(p, lane, N) == warp_argmax(tv, lane, N);
+            const float q = p / sum;
+            const float cl = fminf(fmaxf(q, kClipEps), 1.f - kClipEps);
+            const float loss = warp_sum(mine ? -tv * logf(cl) : 0.f);
+            const float g = (mine && q >= kClipEps && q <= 1.f - kClipEps) ? -tv / cl : 0.f;
+            const float dot = warp_sum(mine ? g * q : 0.f);
+            const float dot2 = warp_sum(mine ? (g - dot) / sum * p : 0.f);
+            if (mine && dz) dz[(long long)m * N + lane] = scale * p * ((g - dot) / sum - dot2);
+            if (lane == 0) {
+                row_loss_out[m] = loss;
+                row_hit[m] = hit ? 1.f : 0.f;
+            }
         }
         __syncthreads();
     }
@@ -395,14 +448,31 @@ __device__ void fs_head_dgrad(const fnet_fused_op &op, float *smem) {
     for (int m = blockIdx.x; m < M; m += gridDim.x) {
         if (threadIdx.x < N) smem[threadIdx.x] = dz[(long long)m * N + threadIdx.x];
         __syncthreads();
-        for (int k = threadIdx.x; k < K; k += FS_THREADS) {
-            const float *wr = w + (long long)k * N;
-            float v = 0.f;
-            for (int n = 0; n < N; ++n) v = fmaf(smem[n], wr[n], v);
-            const long long at = (long long)m * K + k;
-            if (accumulate) v += dx[at];
-            if (act) v *= act_grad(yact[at], act);
-            dx[at] = v;
+        float gz[16];
+#pragma unroll
+        for (int n = 0; n < 16; ++n) gz[n] = n < N ? smem[n] : 0.f;
+        for (int k0 = threadIdx.x; k0 < K; k0 += 4 * FS_THREADS) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = k0 + u * FS_THREADS < K ? k0 + u * FS_THREADS : k0;
+                const float *wr = w + (long long)k * N;
+                v[u] = 0.f;
+#pragma unroll
+                for (int n = 0; n < 16; ++n)
+                    if (n < N) v[u] = fmaf(gz[n], wr[n], v[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = k0 + u * FS_THREADS;
+                if (k < K) {
+                    const long long at = (long long)m * K + k;
+                    float r = v[u];
+                    if (accumulate) r += dx[at];
+                    if (act) r *= act_grad(yact[at], act);
+                    dx[at] = r;
+                }
+            }
         }
         __syncthreads();
     }
@@ -457,21 +527,29 @@ __device__ void fs_head_wgrad(const fnet_fused_op &op, float *smem) {
 
 // ------------------------------------------------------------------ optimizer + end of the step
 __device__ void fs_close(const fnet_fused_op &op) {
-    // one thread: the batch's loss and hits in row order into the running accumulators, iteration += 1, cursor += advance
-    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    // first warp of CTA 0: the batch's loss and hits (lane l takes rows l, l + 32, ...; then a shuffle tree: a fixed
+    // order) into the running accumulators, iteration += 1, cursor += advance
+    if (blockIdx.x != 0 || threadIdx.x >= 32) return;
     int32_t *state = static_cast<int32_t *>(op.p[4]);
-    const int rows = op.d[2];
+    const int rows = op.d[2], lane = threadIdx.x;
     if (rows > 0) {
         const float *row_loss_in = static_cast<const float *>(op.p[5]), *row_hit = static_cast<const float *>(op.p[6]);
         double loss = 0.0;
-        long long hits = 0;
-        for (int m = 0; m < rows; ++m) { loss += (double)row_loss_in[m]; hits += row_hit[m] != 0.f ? 1 : 0; }
-        double *loss_sum = static_cast<double *>(op.p[7]);
-        long long *correct = reinterpret_cast<long long *>(loss_sum + 1);
-        *loss_sum += loss;
-        *correct += hits;
+        int hits = 0;
+        for (int m = lane; m < rows; m += 32) { loss += (double)row_loss_in[m]; hits += row_hit[m] != 0.f ? 1 : 0; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            loss += __shfl_xor_sync(0xffffffffu, loss, o);
+            hits += __shfl_xor_sync(0xffffffffu, hits, o);
+        }
+        if (lane == 0) {
+            double *loss_sum = static_cast<double *>(op.p[7]);
+            long long *correct = reinterpret_cast<long long *>(loss_sum + 1);
+            *loss_sum += loss;
+            *correct += hits;
+        }
     }
-    if (op.d[1] >= 0) { state[0] += 1; state[1] += op.d[1]; }
+    if (lane == 0 && op.d[1] >= 0) { state[0] += 1; state[1] += op.d[1]; }
 }
 
 __device__ void fs_adam(const fnet_fused_op &op) {
@@ -509,15 +587,24 @@ __device__ void fs_sgd(const fnet_fused_op &op) {
 }
 
 // ------------------------------------------------------------------ the kernel
-__global__ void __launch_bounds__(FS_THREADS, 1) fused_step_kernel(const fnet_fused_op *__restrict__ ops, int n_ops, unsigned *sync) {
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// stamps (optional, profiling): CTA 0 writes the global timer at kernel entry and after every operation
+__global__ void __launch_bounds__(FS_THREADS, 1) fused_step_kernel(const fnet_fused_op *__restrict__ ops, int n_ops, unsigned *sync,
+                                                                   unsigned long long *stamps) {
     extern __shared__ __align__(16) float smem[];
-    __shared__ fnet_fused_op op;
+    __shared__ fnet_fused_op list[FS_MAX_OPS];
+    // the list is constant for the lifetime of the program: one trip to memory for all of it, not one per operation
+    for (int i = threadIdx.x; i < n_ops * (int)(sizeof(fnet_fused_op) / 4); i += FS_THREADS)
+        reinterpret_cast<uint32_t *>(list)[i] = __ldg(reinterpret_cast<const uint32_t *>(ops) + i);
+    __syncthreads();
+    if (stamps && blockIdx.x == 0 && threadIdx.x == 0) stamps[0] = global_ns();
     for (int i = 0; i < n_ops; ++i) {
-        // the list itself is constant for the lifetime of the program: every CTA reads operation i into shared memory
-        constexpr int words = sizeof(fnet_fused_op) / 4;
-        if (threadIdx.x < words)
-            reinterpret_cast<uint32_t *>(&op)[threadIdx.x] = __ldg(reinterpret_cast<const uint32_t *>(ops + i) + threadIdx.x);
-        __syncthreads();
+        const fnet_fused_op &op = list[i];
         switch (op.kind) {
             case FNET_FK_BEGIN:
                 if (blockIdx.x == 0 && threadIdx.x == 0) lr_t_update(static_cast<int32_t *>(op.p[0]), op.f[0], op.f[1]);
@@ -546,6 +633,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) fused_step_kernel(const fnet_fu
         }
         if (op.barrier_after) grid_barrier(sync);       // uniform: every CTA reads the same list
         else __syncthreads();                            // shared memory (op, staging) is reused by the next operation
+        if (stamps && blockIdx.x == 0 && threadIdx.x == 0) stamps[i + 1] = global_ns();
     }
 }
 
@@ -582,7 +670,12 @@ int fnet_fused_head_supported(int64_t m, int64_t k, int64_t n) {
 }
 
 int fnet_fused_step(const fnet_fused_op *ops_dev, int32_t n_ops, uint32_t *sync, void *stream) {
+    return fnet_fused_step_timed(ops_dev, n_ops, sync, nullptr, stream);
+}
+
+int fnet_fused_step_timed(const fnet_fused_op *ops_dev, int32_t n_ops, uint32_t *sync, uint64_t *stamps, void *stream) {
     FNET_REQUIRE(ops_dev != nullptr && sync != nullptr && n_ops > 0, "fnet_fused_step: null operation list or barrier word");
+    FNET_REQUIRE(n_ops <= FS_MAX_OPS, "fnet_fused_step: at most %d operations per step", FS_MAX_OPS);
     const int grid = fnet_fused_step_grid();
     FNET_REQUIRE(grid > 0, "fnet_fused_step: no device");
     static std::atomic<uint64_t> checked{0};             // one bit per device: the whole grid must be co-resident
@@ -606,7 +699,7 @@ int fnet_fused_step(const fnet_fused_op *ops_dev, int32_t n_ops, uint32_t *sync,
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     unsigned *counter = sync;
-    (void)cudaLaunchKernelEx(&cfg, fused_step_kernel, ops_dev, (int)n_ops, counter);
+    (void)cudaLaunchKernelEx(&cfg, fused_step_kernel, ops_dev, (int)n_ops, counter, reinterpret_cast<unsigned long long *>(stamps));
     return check_launch("fnet_fused_step");
 }
 

@@ -132,7 +132,12 @@ class Engine(object):
         self.timing = {"alloc_s": 0.0, "capture_s": 0.0, "train_s": 0.0, "eval_s": 0.0, "train_steps": 0, "eval_steps": 0}
         self.use_graphs = os.environ.get("FNET_NO_GRAPH", "0") != "1"
         self.poison = os.environ.get("FNET_POISON", "0") == "1"
-        self.fuse_steps = os.environ.get("FNET_FUSED", "1") != "0"
+        # FNET_FUSED=1: steps made of small-channel layers only run as ONE persistent cooperative kernel (fused.py,
+        # csrc/fused_step.cu).  Correct and deterministic (tests/test_gpu_fused.py), but measured SLOWER than the
+        # separate launches on the bench candidate (64 vs 55 us per step on B200: 11 phases of ~4 us, each two dependent
+        # trips to L2 plus a grid barrier, against launches whose latencies overlap through programmatic dependent
+        # launch), so it stays opt-in; profiles/r2_fused_phases.txt has the per-phase timers.
+        self.fuse_steps = os.environ.get("FNET_FUSED", "0") == "1"
         self._fused_keep, self.fused_summary = {}, {}
         self.dp = None                # featurenet_b200.dataparallel.DataParallel once enable_data_parallel() ran
         # A data-parallel step is two captured graphs around an eagerly issued NCCL all-reduce.  FNET_DP_SINGLE_GRAPH=1

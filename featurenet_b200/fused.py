@@ -167,6 +167,8 @@ def try_fuse(engine, ops):
             out.append(_Op(FK_CONCAT_FWD, d=[outer, ra * inner, rb * inner], p=[a, b, y], reads=[a, b], writes=[y]))
         elif name == "concat_bwd":
             outer, ra, rb, inner, dy, ga, gb, fa, fb = args[:9]
+            if outer * (ra + rb) * inner >= 2 ** 31:
+                return None
             out.append(_Op(FK_CONCAT_BWD, d=[outer, ra * inner, rb * inner], p=[dy, ga, gb],
                            flags=(1 if fa else 0) | (2 if fb else 0), reads=[dy], writes=[ga, gb]))
         elif name == "act_bwd":
@@ -194,6 +196,8 @@ def try_fuse(engine, ops):
         else:
             return None
     if pending_head is not None or row_buffers is not None or not out or not out[-1].everything:
+        return None
+    if len(out) > 48:                 # FS_MAX_OPS of csrc/fused_step.cu
         return None
 
     # ---- phases: an operation comes after everything it conflicts with (read-after-write, write-after-read, write-after-write)

@@ -93,6 +93,7 @@ SIGNATURES = {
     "fnet_fused_conv_supported": (C.c_int, [_CD, C.c_int, C.c_int]),
     "fnet_fused_head_supported": (C.c_int, [_I64, _I64, _I64]),
     "fnet_fused_step": (C.c_int, [_P, _I32, _P, _P]),
+    "fnet_fused_step_timed": (C.c_int, [_P, _I32, _P, _P, _P]),
     "fnet_stream_create": (C.c_int, [C.POINTER(_P)]),
     "fnet_stream_destroy": (C.c_int, [_P]),
     "fnet_graph_begin": (C.c_int, [_P]),

@@ -343,6 +343,9 @@ int fnet_fused_step_grid(void);
 int fnet_fused_conv_supported(const fnet_conv2d_desc *d, int product /* 0 fwd, 1 dgrad, 2 wgrad */, int with_bias);
 int fnet_fused_head_supported(int64_t m, int64_t k, int64_t n);
 int fnet_fused_step(const fnet_fused_op *ops_dev, int32_t n_ops, uint32_t *sync, void *stream);
+/* The same launch; CTA 0 also writes the GPU's nanosecond timer at kernel entry and after every operation into
+ * stamps[0 .. n_ops] (device memory): where the time of a step goes, phase by phase (scripts/fused_phases.py). */
+int fnet_fused_step_timed(const fnet_fused_op *ops_dev, int32_t n_ops, uint32_t *sync, uint64_t *stamps, void *stream);
 
 /* A stream of the caller's own (cudaStreamNonBlocking).  Every candidate that is resident on a GPU captures and replays
  * its steps on streams nobody else uses: a stream handed out by a framework's pool (torch recycles 32 per device)

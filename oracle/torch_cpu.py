@@ -54,8 +54,21 @@ class TorchCpuNet(object):
         self.v = [torch.zeros_like(t) for t in self.trainable]
         self.t = 0
 
-    def forward(self, x_nhwc, training=True, dropout_masks=None):
+    def forward(self, x_nhwc, training=True, dropout_masks=None, relu_masks=None):
+        """relu_masks {layer: 0/1 array in NHWC}: use this mask instead of (z > 0) for that layer's ReLU.  A parity test
+        passes the masks of the implementation under test: an element that lands on the other side of the kink within
+        fp32 rounding is a difference of the backward pass's INPUTS (it switches a whole gradient path on or off)."""
         outs = []
+        relu_masks = relu_masks or {}
+
+        def activate(i, z, name, channel_dim=1):
+            if name == "relu" and i in relu_masks:
+                mask = torch.as_tensor(np.asarray(relu_masks[i], self.np_dtype))
+                return z * (mask.permute(0, 3, 1, 2) if z.dim() == 4 else mask)
+            if name == "softmax":
+                return torch.softmax(z, dim=channel_dim)
+            return ACT[name](z)
+
         rank4 = []              # whether outs[i] is stored NCHW (True) or as a plain [B, F] tensor
         for i, row in enumerate(self.rows):
             cls, cfg, W = row["class"], row["cfg"], self.params[i]
@@ -65,25 +78,20 @@ class TorchCpuNet(object):
                 y = x_nhwc.permute(0, 3, 1, 2).contiguous(memory_format=torch.channels_last) if is4 else x_nhwc
             elif cls == "Conv2D":
                 xp = _pad_same(ins[0], cfg["kernel"], cfg["strides"], cfg["padding"], cfg["dilation"])
-                y = ACT[cfg["activation"] if cfg["activation"] != "softmax" else None](
-                    F.conv2d(xp, W[0], W[1], stride=tuple(cfg["strides"]), dilation=tuple(cfg["dilation"])))
-                if cfg["activation"] == "softmax":
-                    y = torch.softmax(y, dim=1)
+                y = activate(i, F.conv2d(xp, W[0], W[1], stride=tuple(cfg["strides"]), dilation=tuple(cfg["dilation"])),
+                             cfg["activation"])
             elif cls == "DepthwiseConv2D":
                 xp = _pad_same(ins[0], cfg["kernel"], cfg["strides"], cfg["padding"])
-                y = F.conv2d(xp, W[0], W[1], stride=tuple(cfg["strides"]), groups=xp.shape[1])
-                y = torch.softmax(y, dim=1) if cfg["activation"] == "softmax" else ACT[cfg["activation"]](y)
+                y = activate(i, F.conv2d(xp, W[0], W[1], stride=tuple(cfg["strides"]), groups=xp.shape[1]), cfg["activation"])
             elif cls == "SeparableConv2D":
                 xp = _pad_same(ins[0], cfg["kernel"], cfg["strides"], cfg["padding"])
                 mid = F.conv2d(xp, W[0], None, stride=tuple(cfg["strides"]), groups=xp.shape[1])
-                y = F.conv2d(mid, W[1], W[2])
-                y = torch.softmax(y, dim=1) if cfg["activation"] == "softmax" else ACT[cfg["activation"]](y)
+                y = activate(i, F.conv2d(mid, W[1], W[2]), cfg["activation"])
             elif cls == "Dense":
                 if rank4[row["inbound"][0]]:
-                    z = F.conv2d(ins[0], W[0].t().reshape(W[0].shape[1], W[0].shape[0], 1, 1), W[1])
-                    y = torch.softmax(z, dim=1) if cfg["activation"] == "softmax" else ACT[cfg["activation"]](z)
+                    y = activate(i, F.conv2d(ins[0], W[0].t().reshape(W[0].shape[1], W[0].shape[0], 1, 1), W[1]), cfg["activation"])
                 else:
-                    y = ACT[cfg["activation"]](ins[0] @ W[0] + W[1])
+                    y = activate(i, ins[0] @ W[0] + W[1], cfg["activation"], channel_dim=-1)
             elif cls == "MaxPooling2D":
                 xp = _pad_same(ins[0], cfg["pool"], cfg["strides"], cfg["padding"])
                 if xp is not ins[0]:
@@ -130,7 +138,7 @@ class TorchCpuNet(object):
                 yb = xin * inv.reshape(shape) + (W[1] - mean * inv).reshape(shape)
                 y = yb.transpose(1, 2) if is4 else yb
             elif cls == "Activation":
-                y = torch.softmax(ins[0], dim=1 if is4 else -1) if cfg["activation"] == "softmax" else ACT[cfg["activation"]](ins[0])
+                y = activate(i, ins[0], cfg["activation"], channel_dim=1 if is4 else -1)
             elif cls == "Add":
                 y = ins[0] + ins[1]
             elif cls == "Multiply":
@@ -153,11 +161,15 @@ class TorchCpuNet(object):
         loss = -(t * torch.log(c)).sum(dim=-1)
         return loss, (t.argmax(dim=-1) == p.argmax(dim=-1))
 
-    def train_step(self, x, t, lr=1e-3, dropout_masks=None):
+    def train_step(self, x, t, lr=1e-3, dropout_masks=None, relu_masks=None):
         x = torch.as_tensor(x, dtype=self.dtype)
         t = torch.as_tensor(t, dtype=self.dtype)
-        outs = self.forward(x, True, dropout_masks)
+        outs = self.forward(x, True, dropout_masks, relu_masks)
         self.outs = outs
+        if getattr(self, "keep_activation_grads", False):       # parity debugging: dL/d(output of every layer)
+            for y in outs:
+                if y.requires_grad:
+                    y.retain_grad()
         loss, correct = self.loss_and_correct(outs[-1], t)
         for p in self.trainable:
             p.grad = None
@@ -187,6 +199,12 @@ class TorchCpuNet(object):
     def out_nhwc(self, i):
         y = self.outs[i].detach()
         return (y.permute(0, 2, 3, 1) if y.dim() == 4 else y).contiguous().numpy()
+
+    def out_grad_nhwc(self, i):
+        g = self.outs[i].grad
+        if g is None:
+            return None
+        return (g.permute(0, 2, 3, 1) if g.dim() == 4 else g).contiguous().numpy()
 
     @staticmethod
     def _to_keras(cls, k, t):

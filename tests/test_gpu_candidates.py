@@ -26,13 +26,7 @@ torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-TOL = 1e-4           # forward outputs and the loss: the per-layer bar of north_star
-# Weight gradients of a WHOLE candidate: the rounding of every layer between a weight and the loss accumulates, and a
-# ReLU / max-pool element that lands on the other side of its kink within fp32 rounding moves single gradient entries
-# of all layers below it (the layer-by-layer bar of 1e-4, with identical inputs per layer, is asserted at these sizes in
-# tests/test_gpu_fullsize_oracle.py and step by step with kink alignment in tests/test_gpu_network.py).  Measured: 6e-4
-# on the first layer of the 12-layer "wide" candidate.
-TOL_GRAD = 1e-3
+TOL = 1e-4           # forward outputs, the loss and every weight gradient: the bar of north_star
 BATCH = 128
 
 
@@ -109,7 +103,24 @@ def test_benchmarked_candidate_step_matches_float64_port_at_batch_128(name):
             masks[i] = ops.dropout_keep_mask(n, row["cfg"]["rate"], eng.dropout_seed, i, 0)
     loss_e, acc_e = eng.train_on_batch(x, t)
     torch.cuda.synchronize()
-    loss_o, correct_o = port.train_step(x, t, float(np.float32(1e-3)), masks)
+    # ReLU outputs of the engine decide which gradient paths are open on BOTH sides: an element within fp32 rounding of
+    # zero that lands on the other side of the kink is a different INPUT of the backward pass (one such element among
+    # 50 M moves single entries of a filter gradient by 2e-3 of its largest entry -- measured on the "wide" candidate with
+    # the plain FFMA kernels); how many there are is bounded below
+    relu_masks, flips = {}, 0
+    for i, row in enumerate(rows):
+        if row["cfg"].get("activation") == "relu":
+            relu_masks[i] = (eng.act[eng._resolve(i, True)][:BATCH] > 0).cpu().numpy().reshape((BATCH,) + tuple(row["out_shape"][1:]))
+    loss_o, correct_o = port.train_step(x, t, float(np.float32(1e-3)), masks, relu_masks=relu_masks)
+    probe = TorchCpuNet(rows, w32, dtype=torch.float64)
+    with torch.no_grad():
+        plain = probe.forward(torch.as_tensor(x, dtype=torch.float64), True, masks)
+    for i in relu_masks:
+        y = plain[i].permute(0, 2, 3, 1).numpy() if plain[i].dim() == 4 else plain[i].numpy()
+        wrong = (y > 0) != relu_masks[i]
+        assert np.abs(y[wrong]).max(initial=0.0) <= 1e-5 * np.abs(y).max(), "a flipped ReLU element must be within rounding of zero"
+        flips += int(wrong.sum())
+    assert flips <= 64, "too many ReLU sign disagreements to be rounding: %d" % flips
     assert abs(loss_e * BATCH - loss_o) <= TOL * max(1.0, abs(loss_o))
     assert abs(round(acc_e * BATCH) - correct_o) <= 1          # an argmax tie within rounding may flip one sample
     for i, row in enumerate(rows):
@@ -119,9 +130,7 @@ def test_benchmarked_candidate_step_matches_float64_port_at_batch_128(name):
     want = port.grads_keras()
     for (i, k), (off, size) in eng.w_off.items():
         got = g[off: off + size].reshape(eng.nodes[i].weights[k].shape)
-        # a ReLU / max-pool element that lands on the other side of its kink within fp32 rounding moves single
-        # gradient entries of the layers below it; the bar stays relative to the gradient's largest entry
-        assert relerr(got, want[(i, k)]) <= TOL_GRAD, "gradient of layer %d (%s) weight %d" % (i, rows[i]["class"], k)
+        assert relerr(got, want[(i, k)]) <= TOL, "gradient of layer %d (%s) weight %d" % (i, rows[i]["class"], k)
     for a, b in zip(eng.get_weights(), port.weights_keras()):
         assert np.abs(a - b).max() <= TOL * np.abs(b).max() + 0.05 * 1e-3
 

@@ -148,8 +148,8 @@ def test_fused_step_with_sgd_and_streamed_uint8_batches(monkeypatch):
 
         def __init__(self):
             rng = np.random.default_rng(8)
-            self.x = rng.integers(0, 256, size=(4, 32, 8, 8, 3), dtype=np.uint8)
-            self.y = np.eye(10, dtype=np.float32)[rng.integers(0, 10, (4, 32))]
+            self.px = rng.integers(0, 256, size=(4, 32, 8, 8, 3), dtype=np.uint8)
+            self.labels = np.eye(10, dtype=np.float32)[rng.integers(0, 10, (4, 32))]
             self.i = 0
 
         def __iter__(self):
@@ -158,7 +158,7 @@ def test_fused_step_with_sgd_and_streamed_uint8_batches(monkeypatch):
         def __next__(self):
             k = self.i % 4
             self.i += 1
-            return self.x[k], self.y[k]
+            return self.px[k], self.labels[k]
 
     results = []
     for fused in (True, False):
