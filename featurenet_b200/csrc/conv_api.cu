@@ -40,6 +40,13 @@ int conv_fwd(const ConvGeom &g, int math_in, int act, const float *x, const floa
              void *ws, size_t ws_bytes, cudaStream_t s) {
     const int math = resolve_math(g, math_in, 0);
     int rc;
+    if (strided_pointwise_ok(g) && !skinny_supported(g, 0, bias != nullptr)) {
+        const size_t sub = strided_sub_bytes(g);
+        if (!ws || ws_bytes < sub) { set_error("conv2d_fwd[1x1 strided]: workspace of %zu bytes needed, %zu given", sub, ws_bytes); return FNET_ERR_WORKSPACE; }
+        float *x_sub = reinterpret_cast<float *>(ws);
+        if ((rc = strided_subsample(g, x, x_sub, s)) != FNET_OK) return rc;
+        return conv_fwd(strided_inner(g), math_in, act, x_sub, w, bias, y, reinterpret_cast<char *>(ws) + sub, ws_bytes - sub, s);
+    }
     if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
     else if (tma_gemm_supported(g, math, 0)) rc = tma_gemm_fwd(g, math, act, x, w, bias, y, s);
     else if (math != FNET_MATH_FP32 && tc_supported(g, math, 0)) rc = tc_conv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
@@ -52,6 +59,14 @@ int conv_fwd(const ConvGeom &g, int math_in, int act, const float *x, const floa
 int conv_dgrad(const ConvGeom &g, int math_in, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws,
                size_t ws_bytes, cudaStream_t s) {
     const int math = resolve_math(g, math_in, 1);
+    if (strided_pointwise_ok(g) && !skinny_supported(g, 1, false)) {
+        const size_t sub = strided_sub_bytes(g);
+        if (!ws || ws_bytes < sub) { set_error("conv2d_bwd_data[1x1 strided]: workspace of %zu bytes needed, %zu given", sub, ws_bytes); return FNET_ERR_WORKSPACE; }
+        float *dx_sub = reinterpret_cast<float *>(ws);
+        int rc = conv_dgrad(strided_inner(g), math_in, dz, w, dx_sub, DxEpilogue{0, 0, nullptr}, reinterpret_cast<char *>(ws) + sub,
+                            ws_bytes - sub, s);
+        return rc == FNET_OK ? strided_scatter(g, dx_sub, dx, ep, s) : rc;
+    }
     // few channels on BOTH sides: the direct kernel beats GEMM + col2im (28x28x6 -> 12, 5x5: 54 vs 112 us)
     if (skinny_supported(g, 1, false)) return skinny_dgrad(g, dz, w, dx, ep, s);
     if (size_t t_bytes = col2im_t_bytes(g)) {
@@ -74,6 +89,7 @@ int conv_dgrad(const ConvGeom &g, int math_in, const float *dz, const float *w, 
 // Mirrors conv_dgrad's dispatch; the col2im path applies the epilogue in its scatter pass (cheap).
 static int dgrad_on_tensor_core(const ConvGeom &g, int math_in) {
     const int math = resolve_math(g, math_in, 1);
+    if (strided_pointwise_ok(g)) return 0;                   // the scatter pass carries the epilogue
     if (skinny_supported(g, 1, false) || col2im_t_bytes(g)) return 0;
     if (tma_gemm_supported(g, math, 1)) return 1;
     return (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) ? 1 : 0;
@@ -82,6 +98,13 @@ static int dgrad_on_tensor_core(const ConvGeom &g, int math_in) {
 int conv_wgrad(const ConvGeom &g, int math_in, const float *x, const float *dz, float *dw, float *dbias, void *ws,
                size_t ws_bytes, cudaStream_t s) {
     const int math = resolve_math(g, math_in, 2);
+    if (strided_pointwise_ok(g) && !skinny_supported(g, 2, dbias != nullptr)) {
+        const size_t sub = strided_sub_bytes(g);
+        if (!ws || ws_bytes < sub) { set_error("conv2d_bwd_filter[1x1 strided]: workspace of %zu bytes needed, %zu given", sub, ws_bytes); return FNET_ERR_WORKSPACE; }
+        float *x_sub = reinterpret_cast<float *>(ws);
+        int rc = strided_subsample(g, x, x_sub, s);
+        return rc == FNET_OK ? conv_wgrad(strided_inner(g), math_in, x_sub, dz, dw, dbias, reinterpret_cast<char *>(ws) + sub, ws_bytes - sub, s) : rc;
+    }
     if (skinny_supported(g, 2, dbias != nullptr)) return skinny_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
     if (tma_gemm_supported(g, math, 2)) return tma_gemm_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 2)) return tc_conv_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
@@ -103,6 +126,11 @@ extern "C" {
 size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
     ConvGeom g;
     if (geom_checked(d, g, "fnet_conv2d_workspace_bytes") != FNET_OK) return 0;
+    size_t front = 0;
+    if (strided_pointwise_ok(g)) {                           // sub(x) / dx_sub first, then whatever the stride-1 layer needs
+        front = strided_sub_bytes(g);
+        g = strided_inner(g);
+    }
     size_t need = max_sz(simt_conv_workspace(g), skinny_workspace(g));
     if (d->math != FNET_MATH_FP32) {
         const int tensor_math = d->math == FNET_MATH_AUTO ? FNET_MATH_TF32X3 : d->math;     // covers whatever AUTO resolves to
@@ -112,7 +140,7 @@ size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
         ConvGeom gd = dense_geom((long long)g.B * g.Ho * g.Wo, (long long)g.kh * g.kw * g.C, g.K);
         need = max_sz(need, t_bytes + max_sz(simt_conv_workspace(gd), tc_conv_workspace(gd, FNET_MATH_TF32)));
     }
-    return need;
+    return front + need;
 }
 
 int fnet_conv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w, const float *bias, float *y, void *ws,

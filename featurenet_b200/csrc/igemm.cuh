@@ -67,6 +67,13 @@ int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, 
 size_t col2im_t_bytes(const ConvGeom &g);                    // 0 = not applicable
 int col2im_scatter(const ConvGeom &g, const float *t, float *dx, DxEpilogue ep, cudaStream_t stream);
 
+// 1x1 convolutions with a stride as "keep every s-th pixel" + a plain GEMM (strided.cu)
+bool strided_pointwise_ok(const ConvGeom &g);
+ConvGeom strided_inner(const ConvGeom &g);                   // the stride-1 layer over the kept pixels
+size_t strided_sub_bytes(const ConvGeom &g);                 // bytes of sub(x) / dx_sub in the workspace
+int strided_subsample(const ConvGeom &g, const float *x, float *x_sub, cudaStream_t stream);
+int strided_scatter(const ConvGeom &g, const float *dx_sub, float *dx, DxEpilogue ep, cudaStream_t stream);
+
 int run_softmax_rows(int64_t rows, int64_t cols, const float *x, float *y, cudaStream_t stream);
 
 }  // namespace fnet

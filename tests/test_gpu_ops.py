@@ -89,6 +89,11 @@ CONV_CASES = [
     ((17, 16, 16, 36), (1, 1), 8, (1, 1), "valid", (1, 1), "relu"),     # pointwise kernels, 8 output channels, ragged pixel groups
     ((5, 30, 30, 260), (1, 1), 5, (1, 1), "same", (1, 1), "tanh"),      # pointwise kernels, > 256 channels (32 lanes per pixel)
     ((33, 11, 13, 132), (1, 1), 1, (1, 1), "same", (1, 1), "sigmoid"),  # a single output channel, 33 channel groups
+    ((24, 32, 16, 24), (1, 1), 192, (2, 2), "same", (1, 1), "relu"),    # 1x1 stride 2, the NAS space's staple: subsample + plain GEMM
+    ((16, 16, 8, 192), (1, 1), 264, (2, 2), "same", (1, 1), None),      # the same, wide on both sides
+    ((9, 7, 5, 20), (1, 1), 33, (2, 2), "same", (1, 1), "tanh"),        # odd extents: the last row / column is kept (ceil)
+    ((6, 9, 10, 7), (1, 1), 40, (1, 3), "valid", (1, 1), None),         # stride along one axis only, channels not a multiple of 4
+    ((40, 32, 32, 3), (1, 1), 24, (2, 2), "same", (1, 1), "relu"),      # 3 -> 24 stride 2: first layer of most sampled products
 ]
 
 
@@ -128,6 +133,31 @@ def test_conv2d_forward_backward(L, case_id):
     dw2 = torch.empty(w.shape, device="cuda")
     L.fnet_conv2d_bwd_filter(desc, ptr(xd), ptr(dzd), ptr(dw2), None, ptr(ws), ws.numel(), None)
     assert torch.equal(dwd, dw2)
+
+
+@pytest.mark.parametrize("math", ["fp32", "auto"])
+@pytest.mark.parametrize("case_id", [0, 2, 7, 9, 12, 16, 17, 18, 19, 20])
+def test_conv2d_bwd_data_with_the_producers_activation_derivative(L, case_id, math):
+    """fnet_conv2d_bwd_data_act: dx = (accumulate ? dx + v : v) * act'(y), y = output of the layer that produced x."""
+    from featurenet_b200 import lib as fl
+    xs, k, kout, s, padding, d, _ = CONV_CASES[case_id]
+    rng = np.random.default_rng(2000 + case_id)
+    w = rng.standard_normal(k + (xs[3], kout)) * 0.3
+    desc = conv_desc(fl, xs, k, kout, s, padding, d, None, math)
+    ws = workspace(L.fnet_conv2d_workspace_bytes(C.byref(desc)))
+    ho, wo = desc.out_h, desc.out_w
+    dz = rng.standard_normal((xs[0], ho, wo, kout))
+    x = rng.standard_normal(xs)
+    dx, _, _ = ops.conv2d_bwd(x, w, dz, s, padding, d)
+    before = rng.standard_normal(xs)
+    for act in ("relu", "tanh", "sigmoid"):
+        y = ops.act_fwd(rng.standard_normal(xs), act)                  # what the producing layer put out
+        for accumulate in (0, 1):
+            want = ops.act_bwd(y, dx + (before if accumulate else 0.0), act)
+            dxd = dev(before)
+            L.fnet_conv2d_bwd_data_act(desc, ptr(dev(dz)), ptr(dev(w)), ptr(dxd), accumulate, fl.ACT[act], ptr(dev(y)), ptr(ws),
+                                       ws.numel(), None)
+            assert_close(host(dxd), want, what="dgrad epilogue %s accumulate=%d" % (act, accumulate))
 
 
 def test_conv2d_softmax_activation_and_no_bias(L):
