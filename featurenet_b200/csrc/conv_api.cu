@@ -9,8 +9,14 @@ namespace {
 inline size_t max_sz(size_t a, size_t b) { return a > b ? a : b; }
 
 int check_math(int math, const char *what) {
-    if (math != FNET_MATH_FP32 && math != FNET_MATH_TF32 && math != FNET_MATH_BF16 && math != FNET_MATH_TF32X3 &&
-        math != FNET_MATH_AUTO) {
+    if (math == FNET_MATH_BF16) {
+        // refused rather than served by the fp32 kernels under another name: a bf16 mode means bf16 STORAGE of the
+        // activations (half the HBM traffic of these bandwidth-bound layers), which every kernel of the library would
+        // have to read and write; it is not built
+        set_error("%s: FNET_MATH_BF16 is not built (use FNET_MATH_TF32 for the reduced-precision tensor-core mode)", what);
+        return FNET_ERR_UNSUPPORTED;
+    }
+    if (math != FNET_MATH_FP32 && math != FNET_MATH_TF32 && math != FNET_MATH_TF32X3 && math != FNET_MATH_AUTO) {
         set_error("%s: unknown math mode %d", what, math);
         return FNET_ERR_ARG;
     }

@@ -95,7 +95,11 @@ class Engine(object):
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         # "auto" (the default) = fp32 accuracy with the faster of the FFMA and the three-MMA tensor-core kernel per
         # product (FNET_MATH_AUTO); "fp32" forces FFMA everywhere, "tf32x3" the tensor core wherever it can run
-        self.math = fl.MATH[(math_mode or os.environ.get("FNET_PRECISION", "auto")).lower()]
+        mode = (math_mode or os.environ.get("FNET_PRECISION", "auto")).lower()
+        if mode == "bf16":
+            raise NotImplementedError("FNET_PRECISION=bf16 is not built (it needs bf16 activation storage in every kernel); "
+                                      "the reduced-precision tensor-core mode is 'tf32'")
+        self.math = fl.MATH[mode]
         # Streams of this engine's OWN (fnet_stream_create), not torch.cuda.Stream(): torch hands out 32 pooled streams
         # per device round-robin, so with several candidates resident per GPU a long-lived engine ends up sharing a
         # stream with a later one -- and whatever that one launches while this one is capturing a graph on the shared

@@ -41,7 +41,8 @@ enum { FNET_POOL_MAX = 0, FNET_POOL_AVG = 1 };
 /* arithmetic used by the GEMM-shaped kernels */
 enum { FNET_MATH_FP32 = 0,   /* FFMA, fp32 end to end: the parity mode                  */
        FNET_MATH_TF32 = 1,   /* tcgen05.mma kind::tf32, fp32 accumulate in TMEM         */
-       FNET_MATH_BF16 = 2,   /* tcgen05.mma kind::f16 (bf16 operands), fp32 accumulate  */
+       FNET_MATH_BF16 = 2,   /* reserved: bf16 activation storage is NOT built; every entry point refuses it with
+                              * FNET_ERR_UNSUPPORTED instead of running another mode under its name      */
        FNET_MATH_TF32X3 = 3,   /* fp32 accuracy on the tensor cores: every operand is split into a tf32 head and
                                 * a tf32 tail, three tcgen05 MMAs per product (hi*hi + lo*hi + hi*lo)          */
        FNET_MATH_AUTO = 4 };   /* fp32 accuracy, fastest kernel: FNET_MATH_FP32 or FNET_MATH_TF32X3 per product,

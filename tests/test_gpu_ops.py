@@ -160,6 +160,22 @@ def test_conv2d_bwd_data_with_the_producers_activation_derivative(L, case_id, ma
             assert_close(host(dxd), want, what="dgrad epilogue %s accumulate=%d" % (act, accumulate))
 
 
+def test_bf16_mode_is_refused_not_aliased(L):
+    """SURVEY.md names a bf16 mode; it is not built, and asking for it must fail loudly rather than run fp32 kernels."""
+    from featurenet_b200 import lib as fl
+    desc = conv_desc(fl, (2, 6, 6, 4), (3, 3), 5, (1, 1), "same", math="bf16")
+    x, w, y = (torch.zeros(n, device="cuda") for n in (2 * 6 * 6 * 4, 3 * 3 * 4 * 5, 2 * 6 * 6 * 5))
+    ws = workspace(1 << 20)
+    with pytest.raises(fl.FnetError, match="not built"):
+        L.fnet_conv2d_fwd(desc, ptr(x), ptr(w), None, ptr(y), ptr(ws), ws.numel(), None)
+    with pytest.raises(fl.FnetError, match="not built"):
+        L.fnet_dense_fwd(4, 4, 4, 0, fl.MATH["bf16"], ptr(x), ptr(w), None, ptr(y), ptr(ws), ws.numel(), None)
+    from featurenet_b200.engine import Engine
+    from tests.util import tiny_graphs
+    with pytest.raises(NotImplementedError, match="bf16"):
+        Engine(tiny_graphs()["conv_chain"](), math_mode="bf16")
+
+
 def test_conv2d_softmax_activation_and_no_bias(L):
     from featurenet_b200 import lib as fl
     rng = np.random.default_rng(5)
