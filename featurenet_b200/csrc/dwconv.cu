@@ -224,6 +224,80 @@ __global__ void __launch_bounds__(256) dw_dgrad_vec4_fixed_kernel(fnet_conv2d_de
     }
 }
 
+// Stride-1 depthwise correlation, four consecutive destination pixels per thread.  dst[h][w] = sum over taps of
+// src[h + off_h + r][w + off_w + s] * w[tap(r, s)] serves both the forward pass (src = x, off = -pad) and the data
+// gradient (src = dz, off = pad - (k - 1), taps flipped).  One pixel per thread loads k*k source quads and k*k weight
+// quads per output quad (18 loads for 3x3); a strip of four shares its window: per filter row k + 3 source loads and k
+// weight loads feed four outputs (6.75 loads per output quad for 3x3), all of a row's loads issued before the first FMA.
+template <int KH, int KW, int WP>
+__global__ void __launch_bounds__(256, 2) dw_strip_kernel(int batch, int hs, int ws_, int hd, int wd, int quads, int off_h, int off_w,
+                                                       int flip, const float4 *__restrict__ src, const float4 *__restrict__ w,
+                                                       const float4 *__restrict__ bias, float4 *dst, int act, int accumulate) {
+    pdl_prologue();
+    const int strips = (wd + WP - 1) / WP;
+    const int total = batch * hd * strips * quads;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        int q = i % quads, t = i / quads;
+        const int st = t % strips;
+        t /= strips;
+        const int h = t % hd, b = t / hd, w0 = st * WP;
+        const float4 *img = src + (int64_t)b * hs * ws_ * quads + q;
+        float4 acc[WP];
+        const float4 b4 = bias ? __ldg(bias + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int p = 0; p < WP; ++p) acc[p] = b4;
+#pragma unroll 1                                   // one filter row's loads at a time: all rows at once is 128 registers
+        for (int r = 0; r < KH; ++r) {
+            const int hh = h + off_h + r;
+            const bool row_ok = (unsigned)hh < (unsigned)hs;
+            float4 xv[KW + WP - 1], wv[KW];
+#pragma unroll
+            for (int c = 0; c < KW + WP - 1; ++c) {
+                const int ww = w0 + off_w + c;
+                const bool ok = row_ok && (unsigned)ww < (unsigned)ws_;
+                xv[c] = __ldg(img + (ok ? (hh * ws_ + ww) * quads : 0));
+                if (!ok) xv[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int sx = 0; sx < KW; ++sx) wv[sx] = __ldg(w + (flip ? (KH - 1 - r) * KW + (KW - 1 - sx) : r * KW + sx) * quads + q);
+#pragma unroll
+            for (int p = 0; p < WP; ++p)
+#pragma unroll
+                for (int sx = 0; sx < KW; ++sx) {
+                    acc[p].x = fmaf(xv[p + sx].x, wv[sx].x, acc[p].x);
+                    acc[p].y = fmaf(xv[p + sx].y, wv[sx].y, acc[p].y);
+                    acc[p].z = fmaf(xv[p + sx].z, wv[sx].z, acc[p].z);
+                    acc[p].w = fmaf(xv[p + sx].w, wv[sx].w, acc[p].w);
+                }
+        }
+        float4 *out = dst + ((int64_t)(b * hd + h) * wd + w0) * quads + q;
+#pragma unroll
+        for (int p = 0; p < WP; ++p)
+            if (w0 + p < wd) {
+                float4 v = acc[p];
+                if (accumulate) { const float4 o = out[p * quads]; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+                out[p * quads] = make_float4(act_apply(v.x, act), act_apply(v.y, act), act_apply(v.z, act), act_apply(v.w, act));
+            }
+    }
+}
+
+static bool dw_strip_ok(const fnet_conv2d_desc *d) {
+    return d->stride_h == 1 && d->stride_w == 1 && d->dil_h == 1 && d->dil_w == 1 && d->kh * d->kw <= 9 && d->kh * d->kw > 1;
+}
+
+template <int KH, int KW>
+static void dw_strip_launch(const fnet_conv2d_desc *d, bool dgrad, const float4 *src, const float4 *w, const float4 *bias,
+                            float4 *dst, int act, int accumulate, cudaStream_t stream) {
+    constexpr int WP = 4;
+    const int quads = d->in_c >> 2;
+    const int hs = dgrad ? d->out_h : d->in_h, ws_ = dgrad ? d->out_w : d->in_w, hd = dgrad ? d->in_h : d->out_h,
+              wd = dgrad ? d->in_w : d->out_w;
+    const int off_h = dgrad ? d->pad_top - (KH - 1) : -d->pad_top, off_w = dgrad ? d->pad_left - (KW - 1) : -d->pad_left;
+    const int64_t total = (int64_t)d->batch * hd * ((wd + WP - 1) / WP) * quads;
+    launch_pdl(dw_strip_kernel<KH, KW, WP>, dim3(stream_grid(total, 256)), dim3(256), 0, stream, d->batch, hs, ws_, hd, wd, quads, off_h,
+               off_w, dgrad ? 1 : 0, src, w, bias, dst, act, accumulate);
+}
+
 // stage 1: CTA (cgroup, split) walks its share of output pixels; thread = (channel lane, pixel lane).
 // partial[split][tap or bias][c]
 constexpr int kDwChan = 32;   // channels per CTA (x dimension of the thread block)
@@ -457,7 +531,10 @@ int fnet_dwconv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w,
         const dim3 grid(stream_grid(total / 4, 256));
 #define FNET_DW_FWD(KH_, KW_) \
     else if (d->kh == KH_ && d->kw == KW_) launch_pdl(dw_fwd_vec4_fixed_kernel<KH_, KW_>, grid, dim3(256), 0, as_stream(stream), *d, x4, w4, b4, y4, act)
-        if (false) {}
+        if (dw_strip_ok(d) && d->kh == 3 && d->kw == 3) dw_strip_launch<3, 3>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 1 && d->kw == 3) dw_strip_launch<1, 3>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 3 && d->kw == 1) dw_strip_launch<3, 1>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 2 && d->kw == 2) dw_strip_launch<2, 2>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
         FNET_DW_FWD(1, 1); FNET_DW_FWD(1, 3); FNET_DW_FWD(3, 1); FNET_DW_FWD(3, 3); FNET_DW_FWD(1, 5); FNET_DW_FWD(5, 1);
         // up to nine taps; 5x5 measured slower unrolled (65 vs 44 us on 128 x 32 x 32 x 24) and keeps the loops
         else launch_pdl(dw_fwd_vec4_kernel, grid, dim3(256), 0, as_stream(stream), *d, x4, w4, b4, y4, act);
@@ -486,7 +563,10 @@ int fnet_dwconv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const flo
         const dim3 grid(stream_grid(total / 4, 256));
 #define FNET_DW_DGRAD(KH_, KW_) \
     else if (d->kh == KH_ && d->kw == KW_) launch_pdl(dw_dgrad_vec4_fixed_kernel<KH_, KW_>, grid, dim3(256), 0, as_stream(stream), *d, g4, w4, dx4, accumulate)
-        if (false) {}
+        if (dw_strip_ok(d) && d->kh == 3 && d->kw == 3) dw_strip_launch<3, 3>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 1 && d->kw == 3) dw_strip_launch<1, 3>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 3 && d->kw == 1) dw_strip_launch<3, 1>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 2 && d->kw == 2) dw_strip_launch<2, 2>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
         FNET_DW_DGRAD(1, 1); FNET_DW_DGRAD(1, 3); FNET_DW_DGRAD(3, 1); FNET_DW_DGRAD(3, 3); FNET_DW_DGRAD(1, 5); FNET_DW_DGRAD(5, 1);
         else launch_pdl(dw_dgrad_vec4_kernel, grid, dim3(256), 0, as_stream(stream), *d, g4, w4, dx4, accumulate);
 #undef FNET_DW_DGRAD

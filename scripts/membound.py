@@ -23,7 +23,9 @@ try:
     PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
 except OSError:
     pass
-flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+# L2 is flushed by READING 256 MB (clean lines).  Flushing by writing leaves the 126 MB L2 full of dirty lines whose
+# write-back then competes with the kernel under test for HBM: on 33 MB tensors that halves the figure.
+flush = torch.zeros(64 << 20, dtype=torch.int32, device="cuda")
 rows = []
 
 
@@ -34,7 +36,7 @@ def timed(name, label, args, fn):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     best, total = 1e9, 0.0
     for _ in range(reps):
-        flush.zero_()
+        flush.sum()
         e0.record()
         fn()
         e1.record()

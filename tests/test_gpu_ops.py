@@ -234,7 +234,10 @@ def test_workspace_too_small_is_an_error_not_a_crash(L):
                                         # channels % 4 == 0: the four-channels-per-thread kernels
                                         ((4, 12, 10, 16), (3, 3), (1, 1), "relu"), ((3, 9, 9, 8), (3, 3), (2, 2), None),
                                         ((2, 5, 6, 64), (5, 5), (1, 1), "tanh"), ((3, 8, 7, 12), (1, 3), (1, 1), None),
-                                        ((2, 9, 6, 20), (1, 5), (2, 1), "relu"), ((5, 4, 4, 4), (1, 1), (1, 1), None)])
+                                        ((2, 9, 6, 20), (1, 5), (2, 1), "relu"), ((5, 4, 4, 4), (1, 1), (1, 1), None),
+                                        # stride 1, up to nine taps: four destination pixels per thread (ragged strips, all tap shapes)
+                                        ((2, 11, 9, 8), (3, 1), (1, 1), None), ((3, 6, 5, 12), (2, 2), (1, 1), "relu"),
+                                        ((2, 33, 31, 24), (3, 3), (1, 1), "tanh"), ((1, 3, 2, 4), (3, 3), (1, 1), None)])
 def test_depthwise_forward_backward(L, xs, k, s, act):
     from featurenet_b200 import lib as fl
     rng = np.random.default_rng(xs[1] * 13 + k[0])
