@@ -637,6 +637,41 @@ __global__ void __launch_bounds__(FS_THREADS, 1) fused_step_kernel(const fnet_fu
     }
 }
 
+// The head as a launch of its own (the default, unfused path): Dense(softmax) + loss in ONE kernel instead of
+// dense_fwd + softmax_cce.  The CTA that finishes last (a ticket) adds the batch's loss and hits, in row order, to the
+// running accumulators and re-arms the ticket.
+__global__ void __launch_bounds__(FS_THREADS) head_fwd_loss_kernel(fnet_fused_op op, double *loss_sum, long long *correct,
+                                                                   unsigned *ticket) {
+    pdl_prologue();
+    extern __shared__ __align__(16) float smem[];
+    __shared__ bool last;
+    fs_head_fwd_loss(op, smem);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last || threadIdx.x >= 32) return;
+    __threadfence();
+    const int rows = op.d[0], lane = threadIdx.x;
+    const float *row_loss_in = static_cast<const float *>(op.p[6]), *row_hit = static_cast<const float *>(op.p[7]);
+    double loss = 0.0;
+    int hits = 0;
+    for (int m = lane; m < rows; m += 32) {
+        loss += (double)*reinterpret_cast<const volatile float *>(row_loss_in + m);
+        hits += *reinterpret_cast<const volatile float *>(row_hit + m) != 0.f ? 1 : 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        loss += __shfl_xor_sync(0xffffffffu, loss, o);
+        hits += __shfl_xor_sync(0xffffffffu, hits, o);
+    }
+    if (lane == 0) {
+        *loss_sum += loss;
+        *correct += hits;
+        *ticket = 0;
+    }
+}
+
 static bool fused_geom_ok(const fnet_conv2d_desc *d) {
     return d && d->batch > 0 && d->in_c >= 1 && d->in_c <= 16 && d->out_c >= 1 && d->out_c <= 16 && d->kh >= 1 && d->kw >= 1 &&
            (long long)d->batch * d->in_h * d->in_w < 0x7fffffffLL / 16 && (long long)d->batch * d->out_h * d->out_w < 0x7fffffffLL / 16;
@@ -667,6 +702,28 @@ int fnet_fused_conv_supported(const fnet_conv2d_desc *d, int product, int with_b
 
 int fnet_fused_head_supported(int64_t m, int64_t k, int64_t n) {
     return (m >= 1 && n >= 1 && n <= 16 && m * n <= 2048 && k >= 1 && m * k < 0x7fffffffLL) ? 1 : 0;
+}
+
+size_t fnet_head_fwd_loss_workspace_bytes(int64_t m) { return m > 0 ? (size_t)(2 * ((m + 63) / 64) * 64) * sizeof(float) : 0; }
+
+int fnet_head_fwd_loss(int64_t m, int64_t k, int64_t n, const float *x, const float *w, const float *bias, float *probs,
+                       const float *targets, float scale, float *dlogits, double *loss_sum, int64_t *correct, uint32_t *ticket,
+                       void *ws, size_t ws_bytes, void *stream) {
+    FNET_REQUIRE(fnet_fused_head_supported(m, k, n), "fnet_head_fwd_loss: shape m=%lld k=%lld n=%lld not supported (n <= 16, m * n <= 2048)",
+                 (long long)m, (long long)k, (long long)n);
+    FNET_REQUIRE(x && w && probs && targets && loss_sum && correct && ticket, "fnet_head_fwd_loss: null pointer");
+    const size_t need = fnet_head_fwd_loss_workspace_bytes(m);
+    if (!ws || ws_bytes < need) { set_error("fnet_head_fwd_loss: workspace of %zu bytes needed, %zu given", need, ws_bytes); return FNET_ERR_WORKSPACE; }
+    fnet_fused_op op = {};
+    op.kind = FNET_FK_HEAD_FWD_LOSS;
+    op.d[0] = (int32_t)m; op.d[1] = (int32_t)k; op.d[2] = (int32_t)n;
+    op.f[0] = scale;
+    float *rows = reinterpret_cast<float *>(ws);
+    op.p[0] = const_cast<float *>(x); op.p[1] = const_cast<float *>(w); op.p[2] = const_cast<float *>(bias); op.p[3] = probs;
+    op.p[4] = const_cast<float *>(targets); op.p[5] = dlogits; op.p[6] = rows; op.p[7] = rows + ((m + 63) / 64) * 64;
+    launch_pdl(head_fwd_loss_kernel, dim3((unsigned)m), dim3(FS_THREADS), 2048, as_stream(stream), op, loss_sum,
+               reinterpret_cast<long long *>(correct), reinterpret_cast<unsigned *>(ticket));
+    return check_launch("fnet_head_fwd_loss");
 }
 
 int fnet_fused_step(const fnet_fused_op *ops_dev, int32_t n_ops, uint32_t *sync, void *stream) {

@@ -142,6 +142,8 @@ class Engine(object):
         # trips to L2 plus a grid barrier, against launches whose latencies overlap through programmatic dependent
         # launch), so it stays opt-in; profiles/r2_fused_phases.txt has the per-phase timers.
         self.fuse_steps = os.environ.get("FNET_FUSED", "0") == "1"
+        # the classifier head and its loss as ONE launch (fnet_head_fwd_loss) instead of dense_fwd + softmax_cce
+        self.fuse_head = os.environ.get("FNET_NO_HEAD_FUSION", "0") != "1"
         self._fused_keep, self.fused_summary = {}, {}
         self.dp = None                # featurenet_b200.dataparallel.DataParallel once enable_data_parallel() ran
         # A data-parallel step is two captured graphs around an eagerly issued NCCL all-reduce.  FNET_DP_SINGLE_GRAPH=1
@@ -158,6 +160,7 @@ class Engine(object):
             self.metrics = torch.zeros(2, dtype=torch.int64, device=self.device)
             self.loss_sum = self.metrics[0:1].view(torch.float64)
             self.correct = self.metrics[1:2]
+            self.ticket = torch.zeros(4, dtype=torch.int32, device=self.device)      # fnet_head_fwd_loss's "who finishes last"
             self._metrics_host = torch.zeros(2, dtype=torch.int64).pin_memory()
             self._metrics_np = self._metrics_host.numpy()      # same pinned memory, cheap to read from Python
             self._metrics_seen = (0.0, 0)
@@ -391,7 +394,7 @@ class Engine(object):
             need = max(self.lib.fnet_dwconv2d_workspace_bytes(C.byref(dw)), self.lib.fnet_conv2d_workspace_bytes(C.byref(pw)))
         elif node.kind == "dense":
             m, k, n = self._dense_mkn(i, batch)
-            need = self.lib.fnet_dense_workspace_bytes(m, k, n)
+            need = max(self.lib.fnet_dense_workspace_bytes(m, k, n), self.lib.fnet_head_fwd_loss_workspace_bytes(m))
         elif node.kind == "bn":
             need = self.lib.fnet_bn_workspace_bytes(self.shape[i][node.cfg["axis"] - 1])
         return int(need)
@@ -728,6 +731,33 @@ class Engine(object):
 
     def _build_program(self, kind, batch):
         """kind: 'train' / 'eval' read the resident dataset through the permutation; '*_fed' expect xb/yb filled."""
+        return self._fuse_head(self._build_program_plain(kind, batch))
+
+    def _fuse_head(self, ops):
+        """dense_fwd(head logits) directly followed by softmax_cce(from logits, in place) -> one fnet_head_fwd_loss."""
+        if not self.fuse_head:
+            return ops
+        val = lambda p: p.value if isinstance(p, C.c_void_p) else p
+        out, i = [], 0
+        while i < len(ops):
+            a = ops[i]
+            b = ops[i + 1] if i + 1 < len(ops) else None
+            if b is not None and str(a[0]) == "dense_fwd" and str(b[0]) == "softmax_cce":
+                m, k, n, act = a[2][:4]
+                x, w, bias, y = a[2][5:9]
+                batch, classes, logits, targets, scale, from_logits, probs, dz, loss_sum, correct = b[2][:10]
+                if (act == 0 and from_logits and m == batch and n == classes and val(y) == val(logits) == val(probs)
+                        and k < 32768 and self.lib.fnet_fused_head_supported(m, k, n)):
+                    out.append(("head_fwd_loss", self.lib.fnet_head_fwd_loss,
+                                (m, k, n, x, w, bias, probs, targets, scale, dz, loss_sum, correct,
+                                 C.c_void_p(self.ticket.data_ptr()), C.c_void_p(self.ws.data_ptr()), self.ws_bytes, self.sp)))
+                    i += 2
+                    continue
+            out.append(a)
+            i += 1
+        return out
+
+    def _build_program_plain(self, kind, batch):
         L, sp = self.lib, self.sp
         if kind == "grad_input":        # act[0] / yb are filled by the caller; inference graph, gradient down to the input
             return (self._forward_program(batch, False, save_for_backward=True) + [self._loss_op(batch, True)] +
@@ -887,6 +917,9 @@ class Engine(object):
             else:
                 f = 2 * m_out * d.in_c * taps
                 b = 4 * (m_in * d.in_c + m_out * d.in_c + taps * d.in_c)
+        elif label == "head_fwd_loss":
+            m, k, n = args[0], args[1], args[2]
+            f, b = 2 * m * k * n, 4 * (m * k + k * n + m * n) + 12 * m * n
         elif label.startswith("dense"):
             m, k, n = args[0], args[1], args[2]
             f, b = 2 * m * k * n, 4 * (m * k + k * n + m * n)
@@ -1512,7 +1545,7 @@ class Engine(object):
                 torch.cuda.ExternalStream(handle.value, device=self.device).synchronize()
             self._drop_graphs()
             for name in ("act", "gact", "aux", "ws", "params", "grads", "adam_m", "adam_v", "stats", "data", "ring", "yb",
-                         "_metrics_np", "_metrics_host", "loss_sum", "correct", "metrics", "state", "state_eval", "aug_dev"):
+                         "_metrics_np", "_metrics_host", "loss_sum", "correct", "metrics", "state", "state_eval", "aug_dev", "ticket"):
                 if hasattr(self, name):
                     delattr(self, name)
             self.capacity = self.grad_capacity = 0

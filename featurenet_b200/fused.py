@@ -133,6 +133,13 @@ def try_fuse(engine, ops):
             if act != 0 or not L.fnet_fused_head_supported(m, k, n):
                 return None       # only the classifier head (logits for the loss) is fused
             pending_head = (m, k, n, x, w, b, y)
+        elif name == "head_fwd_loss":
+            m, k, n, x, w, b, probs, targets, scale, dz, loss_sum, correct = args[:12]
+            if _ptr(correct) != _ptr(loss_sum) + 8:
+                return None
+            row_buffers = (scratch(m), scratch(m), m, loss_sum)
+            out.append(_Op(FK_HEAD_FWD_LOSS, d=[m, k, n], f=[scale], p=[x, w, b, probs, targets, dz, row_buffers[0], row_buffers[1]],
+                           reads=[x, w, b, targets], writes=[probs, dz, row_buffers[0], row_buffers[1]]))
         elif name == "softmax_cce":
             batch, classes, logits, targets, scale, from_logits, probs, dz, loss_sum, correct = args[:10]
             if pending_head is None or not from_logits:

@@ -89,6 +89,8 @@ SIGNATURES = {
     "fnet_gather_rows": (C.c_int, [_I32, _I64, _P, _P, _P, _P, _P]),
     "fnet_gather_shift_flip": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "fnet_u8_to_f32": (C.c_int, [_I64, _P, _F, _P, _P]),
+    "fnet_head_fwd_loss_workspace_bytes": (_SZ, [_I64]),
+    "fnet_head_fwd_loss": (C.c_int, [_I64, _I64, _I64, _P, _P, _P, _P, _P, _F, _P, _P, _P, _P, _P, _SZ, _P]),
     "fnet_fused_step_grid": (C.c_int, []),
     "fnet_fused_conv_supported": (C.c_int, [_CD, C.c_int, C.c_int]),
     "fnet_fused_head_supported": (C.c_int, [_I64, _I64, _I64]),

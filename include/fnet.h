@@ -338,6 +338,15 @@ typedef struct fnet_fused_op {
     float f[4];
     void *p[8];
 } fnet_fused_op;
+/* The classifier head and its loss in ONE launch: Dense(n <= 16, softmax) of keras_model.py:124 on x[m][k], categorical
+ * cross-entropy and accuracy of tensorflow_generator.py:232-235 against targets[m][n]: probs = softmax(x.w + bias),
+ * dlogits (may be NULL) = scale * dL/dlogits, *loss_sum += batch loss, *correct += hits -- what fnet_dense_fwd followed
+ * by fnet_softmax_cce(from_logits) computes, without the second launch.  `ticket`: one zero-initialised uint32 in
+ * device memory owned by the caller (the kernel re-arms it); ws: fnet_head_fwd_loss_workspace_bytes(m) of scratch. */
+size_t fnet_head_fwd_loss_workspace_bytes(int64_t m);
+int fnet_head_fwd_loss(int64_t m, int64_t k, int64_t n, const float *x, const float *w, const float *bias, float *probs,
+                       const float *targets, float scale, float *dlogits, double *loss_sum, int64_t *correct, uint32_t *ticket,
+                       void *ws, size_t ws_bytes, void *stream);
 /* CTAs the fused kernel must be launched with on the current device (its operation list sizes partials by it). */
 int fnet_fused_step_grid(void);
 /* 1 when a convolution / head of this shape has a fused implementation (small channel counts only), else 0. */

@@ -459,6 +459,39 @@ def test_softmax_cross_entropy_and_accuracy(L, batch, classes):
     assert_close(host(dz2), ops.act_bwd(p64, ops.cce_bwd_probs(p64, t, 1.0 / batch), "softmax"), tol=5e-5, what="dlogits from logits")
 
 
+@pytest.mark.parametrize("m,k,n", [(128, 6144, 10), (37, 999, 16), (5, 16464, 3), (200, 64, 10), (1, 7, 2)])
+def test_head_forward_and_loss_in_one_launch(L, m, k, n):
+    """fnet_head_fwd_loss == fnet_dense_fwd (logits) + softmax + categorical cross-entropy of the oracle, twice in a row
+    (the accumulators keep running, the ticket re-arms itself)."""
+    rng = np.random.default_rng(m + k + n)
+    x = rng.standard_normal((m, k))
+    w = rng.standard_normal((k, n)) / np.sqrt(k) * 3.0
+    b = rng.standard_normal(n)
+    t = np.eye(n)[rng.integers(0, n, m)]
+    z = ops.dense_fwd(x.astype(np.float32).astype(np.float64), w.astype(np.float32).astype(np.float64), b.astype(np.float32).astype(np.float64))
+    p = ops.act_fwd(z, "softmax")
+    loss, correct = ops.cce_fwd(p, t)
+    dz = ops.act_bwd(p, ops.cce_bwd_probs(p, t, 1.0 / m), "softmax")
+    probs, dzd = torch.empty((m, n), device="cuda"), torch.empty((m, n), device="cuda")
+    metrics = torch.zeros(2, dtype=torch.int64, device="cuda")
+    ticket = torch.zeros(4, dtype=torch.int32, device="cuda")
+    ws = workspace(L.fnet_head_fwd_loss_workspace_bytes(m))
+    xd, wd, bd, td = dev(x), dev(w), dev(b), dev(t)
+    for _ in range(2):
+        L.fnet_head_fwd_loss(m, k, n, ptr(xd), ptr(wd), ptr(bd), ptr(probs), ptr(td), 1.0 / m, ptr(dzd),
+                             C.c_void_p(metrics.data_ptr()), C.c_void_p(metrics.data_ptr() + 8), ptr(ticket), ptr(ws), ws.numel(), None)
+    torch.cuda.synchronize()
+    assert_close(host(probs), p, what="probabilities")
+    assert_close(host(dzd), dz, tol=5e-5, what="dlogits")
+    assert abs(metrics[0:1].view(torch.float64).item() - 2 * loss.sum()) <= 1e-5 * abs(2 * loss.sum())
+    assert abs(int(metrics[1].item()) - 2 * int(correct.sum())) <= 2
+    assert int(ticket[0].item()) == 0
+    # without a gradient (evaluation) and without a bias
+    L.fnet_head_fwd_loss(m, k, n, ptr(xd), ptr(wd), None, ptr(probs), ptr(td), 1.0 / m, None,
+                         C.c_void_p(metrics.data_ptr()), C.c_void_p(metrics.data_ptr() + 8), ptr(ticket), ptr(ws), ws.numel(), None)
+    assert_close(host(probs), ops.act_fwd(z - b.astype(np.float32).astype(np.float64), "softmax"), what="probabilities without bias")
+
+
 def test_adam_and_sgd_follow_keras(L):
     rng = np.random.default_rng(4)
     n = 1003
