@@ -34,7 +34,9 @@ static int resolve_math(const ConvGeom &g, int math, int product) {
     const long long taps = (long long)g.kh * g.kw;
     bool tensor;
     if (product == 2) {
-        tensor = g.K >= 24 && taps * g.C >= 32;
+        // 1x1 layers from 16 input channels on reach the TMA-fed filter gradient (24 -> 192 on 262 144 pixels: 112 us against
+        // 188 us for the FFMA kernel); the 32-row bound is for the gathered kernels, whose A tile is mostly padding below it
+        tensor = g.K >= 24 && (taps * g.C >= 32 || (taps == 1 && g.C >= 16 && !(g.C & 3) && !(g.K & 3)));
     } else {
         const long long n = product == 0 ? g.K : g.C, kg = taps * (product == 0 ? g.C : g.K);
         tensor = (n >= 32 && kg >= 8) || (n >= 16 && kg >= 128) || (n >= 8 && kg >= 1024);

@@ -416,6 +416,16 @@ __global__ void __launch_bounds__(256) pointwise_dgrad_kernel(int M, int C, int 
             }
         const long long at = (long long)p * C + c;
         if (vec_store) {
+            // the epilogue with 16-byte accesses as well: with the producer's activation derivative folded in (which is
+            // how the engine calls the `Reg_` aligners' data gradient) the scalar path ran at 1.5 TB/s, 137 us on 192 <- 3
+            if (accumulate) {
+                const float4 o = *reinterpret_cast<const float4 *>(dx + at);
+                v[0] += o.x; v[1] += o.y; v[2] += o.z; v[3] += o.w;
+            }
+            if (act) {
+                const float4 yy = __ldg(reinterpret_cast<const float4 *>(yact + at));
+                v[0] *= act_grad(yy.x, act); v[1] *= act_grad(yy.y, act); v[2] *= act_grad(yy.z, act); v[3] *= act_grad(yy.w, act);
+            }
             *reinterpret_cast<float4 *>(dx + at) = make_float4(v[0], v[1], v[2], v[3]);
         } else {
 #pragma unroll
@@ -723,7 +733,7 @@ int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const
 
 int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t s) {
     if (pointwise_dgrad_ok(g)) {
-        const int vec_store = !ep.accumulate && !ep.act && !(reinterpret_cast<uintptr_t>(dx) & 15);
+        const int vec_store = !((reinterpret_cast<uintptr_t>(dx) | (ep.act ? reinterpret_cast<uintptr_t>(ep.y) : 0)) & 15);
         const long long M = (long long)g.B * g.H * g.W, total = M * (g.C >> 2);
         long long blocks = ceil_div<long long>(total, 256);
         const long long cap = (long long)kNumSMs * 16;
