@@ -44,6 +44,10 @@ static int resolve_math(const ConvGeom &g, int math, int product) {
     return tensor ? FNET_MATH_TF32X3 : FNET_MATH_FP32;
 }
 
+static inline bool al16(const void *a, const void *b = nullptr, const void *c = nullptr) {
+    return !((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c)) & 15);
+}
+
 int conv_fwd(const ConvGeom &g, int math_in, int act, const float *x, const float *w, const float *bias, float *y,
              void *ws, size_t ws_bytes, cudaStream_t s) {
     const int math = resolve_math(g, math_in, 0);
@@ -54,6 +58,11 @@ int conv_fwd(const ConvGeom &g, int math_in, int act, const float *x, const floa
         float *x_sub = reinterpret_cast<float *>(ws);
         if ((rc = strided_subsample(g, x, x_sub, s)) != FNET_OK) return rc;
         return conv_fwd(strided_inner(g), math_in, act, x_sub, w, bias, y, reinterpret_cast<char *>(ws) + sub, ws_bytes - sub, s);
+    }
+    if (fewc_supported(g, 0, bias != nullptr) && al16(y)) {
+        rc = fewc_fwd(g, act, x, w, bias, y, s);
+        if (rc == FNET_OK && act == FNET_ACT_SOFTMAX) rc = run_softmax_rows((int64_t)g.B * g.Ho * g.Wo, g.K, y, y, s);
+        return rc;
     }
     if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
     else if (tma_gemm_supported(g, math, 0)) rc = tma_gemm_fwd(g, math, act, x, w, bias, y, s);
@@ -75,6 +84,7 @@ int conv_dgrad(const ConvGeom &g, int math_in, const float *dz, const float *w, 
                             ws_bytes - sub, s);
         return rc == FNET_OK ? strided_scatter(g, dx_sub, dx, ep, s) : rc;
     }
+    if (fewc_supported(g, 1, false) && al16(dz)) return fewc_dgrad(g, dz, w, dx, ep, s);
     // few channels on BOTH sides: the direct kernel beats GEMM + col2im (28x28x6 -> 12, 5x5: 54 vs 112 us)
     if (skinny_supported(g, 1, false)) return skinny_dgrad(g, dz, w, dx, ep, s);
     if (size_t t_bytes = col2im_t_bytes(g)) {
@@ -98,6 +108,7 @@ int conv_dgrad(const ConvGeom &g, int math_in, const float *dz, const float *w, 
 static int dgrad_on_tensor_core(const ConvGeom &g, int math_in) {
     const int math = resolve_math(g, math_in, 1);
     if (strided_pointwise_ok(g)) return 0;                   // the scatter pass carries the epilogue
+    if (fewc_supported(g, 1, false)) return 0;
     if (skinny_supported(g, 1, false) || col2im_t_bytes(g)) return 0;
     if (tma_gemm_supported(g, math, 1)) return 1;
     return (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) ? 1 : 0;
@@ -113,6 +124,7 @@ int conv_wgrad(const ConvGeom &g, int math_in, const float *x, const float *dz, 
         int rc = strided_subsample(g, x, x_sub, s);
         return rc == FNET_OK ? conv_wgrad(strided_inner(g), math_in, x_sub, dz, dw, dbias, reinterpret_cast<char *>(ws) + sub, ws_bytes - sub, s) : rc;
     }
+    if (fewc_supported(g, 2, dbias != nullptr) && al16(dz)) return fewc_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
     if (skinny_supported(g, 2, dbias != nullptr)) return skinny_wgrad(g, x, dz, dw, dbias, ws, ws_bytes, s);
     if (tma_gemm_supported(g, math, 2)) return tma_gemm_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 2)) return tc_conv_wgrad(g, math, x, dz, dw, dbias, ws, ws_bytes, s);
@@ -139,7 +151,7 @@ size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
         front = strided_sub_bytes(g);
         g = strided_inner(g);
     }
-    size_t need = max_sz(simt_conv_workspace(g), skinny_workspace(g));
+    size_t need = max_sz(max_sz(simt_conv_workspace(g), skinny_workspace(g)), fewc_workspace(g));
     if (d->math != FNET_MATH_FP32) {
         const int tensor_math = d->math == FNET_MATH_AUTO ? FNET_MATH_TF32X3 : d->math;     // covers whatever AUTO resolves to
         need = max_sz(need, max_sz(tc_conv_workspace(g, tensor_math), tma_gemm_workspace(g, tensor_math)));

@@ -67,6 +67,13 @@ int skinny_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, 
 size_t col2im_t_bytes(const ConvGeom &g);                    // 0 = not applicable
 int col2im_scatter(const ConvGeom &g, const float *t, float *dx, DxEpilogue ep, cudaStream_t stream);
 
+// very few input channels, up to 64 output channels: direct kernels over groups of eight output channels (fewc.cu)
+bool fewc_supported(const ConvGeom &g, int product, bool with_bias);
+size_t fewc_workspace(const ConvGeom &g);
+int fewc_fwd(const ConvGeom &g, int act, const float *x, const float *w, const float *bias, float *y, cudaStream_t s);
+int fewc_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, DxEpilogue ep, cudaStream_t s);
+int fewc_wgrad(const ConvGeom &g, const float *x, const float *dz, float *dw, float *dbias, void *ws, size_t ws_bytes, cudaStream_t s);
+
 // 1x1 convolutions with a stride as "keep every s-th pixel" + a plain GEMM (strided.cu)
 bool strided_pointwise_ok(const ConvGeom &g);
 ConvGeom strided_inner(const ConvGeom &g);                   // the stride-1 layer over the kept pixels

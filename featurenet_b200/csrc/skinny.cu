@@ -639,6 +639,10 @@ __global__ void __launch_bounds__(256) conv_small_wgrad_reduce_kernel(int blocks
     }
 }
 
+void launch_small_wgrad_reduce(int blocks, int taps_c, int K, int total, const float *partial, float *dw, float *dbias, cudaStream_t s) {
+    launch_pdl(conv_small_wgrad_reduce_kernel, dim3((unsigned)ceil_div<int>(total, 8)), dim3(256), 0, s, blocks, taps_c, K, total, partial, dw, dbias);
+}
+
 // ------------------------------------------------------------------ dispatch (called from conv_api.cu)
 // "small" = few channels on BOTH sides: a thread walks its pixel's channels serially, which only coalesces
 // (through L1) when a pixel is a few dozen bytes

@@ -94,6 +94,13 @@ CONV_CASES = [
     ((9, 7, 5, 20), (1, 1), 33, (2, 2), "same", (1, 1), "tanh"),        # odd extents: the last row / column is kept (ceil)
     ((6, 9, 10, 7), (1, 1), 40, (1, 3), "valid", (1, 1), None),         # stride along one axis only, channels not a multiple of 4
     ((40, 32, 32, 3), (1, 1), 24, (2, 2), "same", (1, 1), "relu"),      # 3 -> 24 stride 2: first layer of most sampled products
+    # very few input channels, 17..64 output channels: direct kernels over groups of eight output channels (fewc.cu)
+    ((7, 16, 12, 3), (3, 1), 24, (1, 1), "same", (1, 1), "relu"),       # 9 filter rows: forward / data gradient there, filter gradient elsewhere
+    ((5, 9, 9, 3), (2, 2), 24, (2, 2), "same", (1, 1), "tanh"),         # even kernel, stride 2, odd extents
+    ((3, 10, 8, 1), (3, 3), 32, (1, 1), "same", (1, 1), None),          # a single input channel (MNIST-shaped first layers)
+    ((6, 8, 8, 4), (1, 1), 64, (1, 1), "valid", (1, 1), "sigmoid"),     # the widest case: 4 -> 64
+    ((4, 8, 6, 2), (1, 3), 20, (1, 2), "same", (1, 1), None),           # a last group of four channels only (K = 20)
+    ((9, 7, 5, 3), (1, 1), 28, (1, 1), "same", (2, 2), "relu"),         # 1x1 with a dilation (ignored), K = 28
 ]
 
 
@@ -136,7 +143,7 @@ def test_conv2d_forward_backward(L, case_id):
 
 
 @pytest.mark.parametrize("math", ["fp32", "auto"])
-@pytest.mark.parametrize("case_id", [0, 2, 7, 9, 12, 16, 17, 18, 19, 20])
+@pytest.mark.parametrize("case_id", [0, 2, 7, 9, 12, 16, 17, 18, 19, 20, 21, 22, 24, 26])
 def test_conv2d_bwd_data_with_the_producers_activation_derivative(L, case_id, math):
     """fnet_conv2d_bwd_data_act: dx = (accumulate ? dx + v : v) * act'(y), y = output of the layer that produced x."""
     from featurenet_b200 import lib as fl
