@@ -109,6 +109,9 @@ static int dgrad_on_tensor_core(const ConvGeom &g, int math_in) {
     const int math = resolve_math(g, math_in, 1);
     if (strided_pointwise_ok(g)) return 0;                   // the scatter pass carries the epilogue
     if (fewc_supported(g, 1, false)) return 0;
+    // a small dx (< 16 MB) is a launch-bound layer: one launch less beats the extra read of y in the epilogue (the
+    // population's candidates spent 5 % of their steps in separate 7 us act_bwd launches)
+    if ((long long)g.B * g.H * g.W * g.C < (1LL << 22)) return 0;
     if (skinny_supported(g, 1, false) || col2im_t_bytes(g)) return 0;
     if (tma_gemm_supported(g, math, 1)) return 1;
     return (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) ? 1 : 0;
