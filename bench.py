@@ -380,6 +380,7 @@ def measure_workload(workload, args, torch, dist, world, device_index, full=True
 
     # ---- one whole candidate: build + compile + 1 epoch + validation + evaluate (rank-local)
     from tensorflow_generator import TensorflowGenerator
+    from featurenet_b200.population import copy_product
     TensorflowGenerator.dataset = dataset
     TensorflowGenerator.X_train, TensorflowGenerator.Y_train = x_train, y_train
     TensorflowGenerator.X_test, TensorflowGenerator.Y_test = x_test, y_test
@@ -397,7 +398,7 @@ def measure_workload(workload, args, torch, dist, world, device_index, full=True
         barrier()
         t0 = time.perf_counter()
         with quiet():
-            gen = TensorflowGenerator(copy.deepcopy(product), epochs=1, dataset=dataset, data_augmentation=False, batch_size=BATCH)
+            gen = TensorflowGenerator(copy_product(product), epochs=1, dataset=dataset, data_augmentation=False, batch_size=BATCH)
         barrier()
         cycles.append(time.perf_counter() - t0)
     timing = dict(gen.model.model._engine.timing)
@@ -447,7 +448,7 @@ def run_population_bench(args, dist, world, rank, n_train, n_test, epochs=1):
     budget = pop.MemoryBudget(int(0.8 * free_bytes)) if workers > 1 else None
 
     def train_one(index, item):
-        product, original = copy.deepcopy(item)        # parsing reverses the product's children in place
+        product, original = pop.copy_product(item)        # parsing reverses the product's children in place
         return pop.train_product(product, "cifar", epochs=epochs, batch_size=BATCH, product_features=original,
                                  shared_gpu=workers > 1)
 

@@ -172,6 +172,27 @@ def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, 
     return sorted(merged, key=lambda pair: pair[0])
 
 
+def copy_product(item):
+    """A product (list of block dicts, or a (product, original features) pair) that can be parsed without changing the
+    caller's copy.  Parsing reverses `children` IN PLACE on the block dicts (keras_model.py:199) and on the cell dicts two
+    levels below (cell.py:87 of the reference), so a population that is trained twice must hand out copies; a deepcopy
+    of the whole feature tree costs 4.5 ms per candidate (a quarter of the host time of a small candidate), this one
+    copies the three levels that are written to and shares the rest."""
+    if isinstance(item, tuple):
+        return (copy_product(item[0]),) + tuple(item[1:])
+    if isinstance(item, str):
+        return item
+
+    def level(node, depth):
+        fresh = dict(node)
+        kids = node.get("children")
+        if kids is not None:
+            fresh["children"] = [level(k, depth - 1) if depth > 0 and isinstance(k, dict) else k for k in kids]
+        return fresh
+
+    return [level(block, 2) for block in item]
+
+
 def train_product(product, dataset, epochs, batch_size, product_features=None, data_augmentation=False, shared_gpu=False):
     """One candidate through the reference-named runner; returns the fields the drivers log.
 

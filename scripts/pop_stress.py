@@ -52,7 +52,7 @@ def main():
     print("buildable %d of %d, estimated bytes %.1f GB total, largest %.1f GB" % (buildable, len(formatted), sum(mem) / 2**30, max(mem) / 2**30))
 
     def train_one(index, item):
-        product, original = copy.deepcopy(item)
+        product, original = pop.copy_product(item)
         return pop.train_product(product, "cifar", epochs=1, batch_size=128, product_features=original, shared_gpu=args.resident > 1)
 
     reference = None

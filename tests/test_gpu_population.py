@@ -46,11 +46,11 @@ def test_eight_resident_candidates_score_what_they_score_alone():
     jobs, job_costs, job_mem = chosen * 8, costs * 8, mem * 8
 
     def train_one_shared(index, item):
-        product, original = copy.deepcopy(item)
+        product, original = pop.copy_product(item)
         return pop.train_product(product, "cifar", epochs=1, batch_size=128, product_features=original, shared_gpu=True)
 
     def train_one_alone(index, item):
-        product, original = copy.deepcopy(item)
+        product, original = pop.copy_product(item)
         return pop.train_product(product, "cifar", epochs=1, batch_size=128, product_features=original, shared_gpu=False)
 
     alone = pop.run_population(chosen, train_one_alone, costs, workers=1)

@@ -111,3 +111,27 @@ def test_memory_budget_serialises_what_does_not_fit():
         t.join(timeout=10)
         assert not t.is_alive()
     assert peak[0] <= 100 and budget.free == 100
+
+
+def test_copy_product_protects_the_callers_tree_and_parses_the_same():
+    """Parsing mutates the product tree in place; the scheduler's cheap copy must protect the caller exactly as a deepcopy."""
+    import contextlib
+    import copy
+    import io
+    import os
+    from model.keras_model import KerasFeatureModel
+    from products_tree import ProductSet
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with contextlib.redirect_stdout(io.StringIO()):
+        formatted = ProductSet(os.path.join(root, "featurenet_b200/data/nas_5_5_10_pop32_seed7.pdt")).format_products()[:8]
+    pristine = copy.deepcopy(formatted)
+    for item, reference in zip(formatted, pristine):
+        with contextlib.redirect_stdout(io.StringIO()):
+            a = KerasFeatureModel.parse_feature_model(pop.copy_product(item)[0]).build((32, 32, 3), 10)
+            b = KerasFeatureModel.parse_feature_model(copy.deepcopy(reference)[0]).build((32, 32, 3), 10)
+            again = KerasFeatureModel.parse_feature_model(pop.copy_product(item)[0]).build((32, 32, 3), 10)
+        assert item == reference                                     # the caller's tree is untouched
+        assert bool(a) == bool(b)
+        if a:
+            strip = lambda rows: [{k: v for k, v in r.items() if k != "name"} for r in rows]
+            assert strip(a.describe()) == strip(b.describe()) == strip(again.describe())
