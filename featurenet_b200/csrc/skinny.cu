@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(256) dense_stream_wgrad_kernel(int M, int K, i
 }
 
 // data gradient (every K): a thread keeps its weight row in registers and walks the 16 samples of its CTA
-template <int NMAX>
+template <int NMAX, bool EPI>
 __global__ void __launch_bounds__(256) dense_rows_dgrad_kernel(int M, int K, int N, const float *__restrict__ dz,
                                                                const float *__restrict__ w, float *__restrict__ dx,
                                                                int accumulate, int act, const float *__restrict__ yact) {
@@ -266,18 +266,51 @@ __global__ void __launch_bounds__(256) dense_rows_dgrad_kernel(int M, int K, int
 #pragma unroll
         for (int n = 0; n < NMAX; ++n) wr[n] = n < N ? __ldg(w + (long long)k * N + n) : 0.f;
         float *out = dx + (long long)m0 * K + k;
+        const float *yin = yact ? yact + (long long)m0 * K + k : nullptr;
+        // four rows at a time, what the epilogue reads (y of the producing layer, the old dx) fetched BEFORE the sums:
+        // with the loads inside the row loop every row waited for its own (ncu: 23 stall cycles per issue on the long
+        // scoreboard, 289 us for the 524 288-wide head of the `keras` template against 98 us without an epilogue)
+        if (!EPI) {                                           // plain store: the row loop as it always was
 #pragma unroll 4
-        for (int r = 0; r < rows; ++r) {
-            float v = 0.f;
+            for (int r = 0; r < rows; ++r) {
+                float v = 0.f;
 #pragma unroll
-            for (int q = 0; q < NMAX / 4; ++q) {
-                float4 d = *reinterpret_cast<const float4 *>(&g_s[r][4 * q]);
-                v = fmaf(d.x, wr[4 * q], v);
-                v = fmaf(d.y, wr[4 * q + 1], v);
-                v = fmaf(d.z, wr[4 * q + 2], v);
-                v = fmaf(d.w, wr[4 * q + 3], v);
+                for (int q = 0; q < NMAX / 4; ++q) {
+                    float4 d = *reinterpret_cast<const float4 *>(&g_s[r][4 * q]);
+                    v = fmaf(d.x, wr[4 * q], v);
+                    v = fmaf(d.y, wr[4 * q + 1], v);
+                    v = fmaf(d.z, wr[4 * q + 2], v);
+                    v = fmaf(d.w, wr[4 * q + 3], v);
+                }
+                out[(long long)r * K] = v;
             }
-            store_dx(out, (long long)r * K, v, accumulate, act, yact ? yact + (long long)m0 * K + k : nullptr);
+            continue;
+        }
+        for (int r0 = 0; r0 < rows; r0 += 4) {
+            float yv[4], old[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const bool in = r0 + u < rows;
+                yv[u] = (act && in) ? __ldg(yin + (long long)(r0 + u) * K) : 0.f;
+                old[u] = (accumulate && in) ? out[(long long)(r0 + u) * K] : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (r0 + u < rows) {
+                    float v = 0.f;
+#pragma unroll
+                    for (int q = 0; q < NMAX / 4; ++q) {
+                        float4 d = *reinterpret_cast<const float4 *>(&g_s[r0 + u][4 * q]);
+                        v = fmaf(d.x, wr[4 * q], v);
+                        v = fmaf(d.y, wr[4 * q + 1], v);
+                        v = fmaf(d.z, wr[4 * q + 2], v);
+                        v = fmaf(d.w, wr[4 * q + 3], v);
+                    }
+                    v += old[u];
+                    if (act) v *= act_grad(yv[u], act);
+                    out[(long long)(r0 + u) * K] = v;
+                }
+            }
         }
     }
 }
@@ -749,7 +782,11 @@ int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, 
         long long bx = ceil_div<long long>(g.C, 256);
         if (bx > 4096) bx = 4096;
         dim3 grid((unsigned)bx, (unsigned)ceil_div<long long>(g.B, 16));
-#define FNET_CALL(NM) launch_pdl(dense_rows_dgrad_kernel<NM>, dim3(grid), dim3(256), 0, s, g.B, g.C, g.K, dz, w, dx, ep.accumulate, ep.act, ep.y)
+#define FNET_CALL(NM)                                                                                                                  \
+    do {                                                                                                                                \
+        if (ep.accumulate || ep.act) launch_pdl(dense_rows_dgrad_kernel<NM, true>, dim3(grid), dim3(256), 0, s, g.B, g.C, g.K, dz, w, dx, ep.accumulate, ep.act, ep.y); \
+        else launch_pdl(dense_rows_dgrad_kernel<NM, false>, dim3(grid), dim3(256), 0, s, g.B, g.C, g.K, dz, w, dx, 0, 0, ep.y);           \
+    } while (0)
         FNET_BY_COLUMNS(g.K, FNET_CALL);
 #undef FNET_CALL
         return check_launch("dense_bwd_data[skinny]");
