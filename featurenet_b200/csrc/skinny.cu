@@ -331,10 +331,15 @@ __global__ void __launch_bounds__(256) conv_small_fwd_kernel(ConvGeom g, int act
                                                              const float *__restrict__ w, const float *__restrict__ bias,
                                                              float *__restrict__ y) {
     pdl_prologue();
-    extern __shared__ float w_s[];                  // [taps*C][K] as in memory (HWIO), then the bias
+    // [taps*C + 1][NMAX]: the filter (HWIO) with its rows padded to NMAX columns by zeros, then the bias row.  A row is
+    // read as NMAX / 4 LDS.128 (the unpadded layout cost one shared load per FMA: lenet5's 6 -> 12 5x5 ran at 10 % of
+    // the FFMA rate)
+    extern __shared__ __align__(16) float w_s[];
     const int KG = g.kh * g.kw * g.C, N = g.K;
-    for (int i = threadIdx.x; i < KG * N; i += 256) w_s[i] = __ldg(w + i);
-    for (int i = threadIdx.x; i < N; i += 256) w_s[KG * N + i] = bias ? __ldg(bias + i) : 0.f;
+    for (int i = threadIdx.x; i < (KG + 1) * NMAX; i += 256) {
+        const int row = i / NMAX, n = i - row * NMAX;
+        w_s[i] = n < N ? (row < KG ? __ldg(w + row * N + n) : (bias ? __ldg(bias + n) : 0.f)) : 0.f;
+    }
     __syncthreads();
     const long long M = (long long)g.B * g.Ho * g.Wo;
     for (long long m = (long long)blockIdx.x * 256 + threadIdx.x; m < M; m += (long long)gridDim.x * 256) {
@@ -344,7 +349,7 @@ __global__ void __launch_bounds__(256) conv_small_fwd_kernel(ConvGeom g, int act
         const float *img = x + b * g.H * g.W * g.C;
         float acc[NMAX];
 #pragma unroll
-        for (int n = 0; n < NMAX; ++n) acc[n] = n < N ? w_s[KG * N + n] : 0.f;
+        for (int n = 0; n < NMAX; ++n) acc[n] = w_s[KG * NMAX + n];
         for (int r = 0; r < g.kh; ++r) {
             int h = ho * g.sh - g.pt + r * g.dh;
             if ((unsigned)h >= (unsigned)g.H) continue;
@@ -352,12 +357,17 @@ __global__ void __launch_bounds__(256) conv_small_fwd_kernel(ConvGeom g, int act
                 int ww = wo * g.sw - g.pl + s * g.dw;
                 if ((unsigned)ww >= (unsigned)g.W) continue;
                 const float *px = img + ((long long)h * g.W + ww) * g.C;
-                const float *wt = w_s + (r * g.kw + s) * g.C * N;
+                const float4 *wt = reinterpret_cast<const float4 *>(w_s + (r * g.kw + s) * g.C * NMAX);
                 for (int c = 0; c < g.C; ++c) {
                     float xv = __ldg(px + c);
 #pragma unroll
-                    for (int n = 0; n < NMAX; ++n)
-                        if (n < N) acc[n] = fmaf(xv, wt[c * N + n], acc[n]);
+                    for (int q = 0; q < NMAX / 4; ++q) {
+                        const float4 wv = wt[c * (NMAX / 4) + q];
+                        acc[4 * q] = fmaf(xv, wv.x, acc[4 * q]);
+                        acc[4 * q + 1] = fmaf(xv, wv.y, acc[4 * q + 1]);
+                        acc[4 * q + 2] = fmaf(xv, wv.z, acc[4 * q + 2]);
+                        acc[4 * q + 3] = fmaf(xv, wv.w, acc[4 * q + 3]);
+                    }
                 }
             }
         }
@@ -374,9 +384,14 @@ __global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const
                                                                const float *__restrict__ w, float *__restrict__ dx,
                                                                int accumulate, int act, const float *__restrict__ yact) {
     pdl_prologue();
-    extern __shared__ float w_s[];                  // [taps][C][K]
-    const int total_w = g.kh * g.kw * g.C * g.K, C = g.C, K = g.K;
-    for (int i = threadIdx.x; i < total_w; i += 256) w_s[i] = __ldg(w + i);
+    // [taps][K][NMAX]: the filter transposed so that the input channels a thread accumulates are contiguous (padded to
+    // NMAX by zeros): NMAX / 4 LDS.128 per (tap, output channel) instead of one shared load per FMA
+    extern __shared__ __align__(16) float w_s[];
+    const int taps = g.kh * g.kw, C = g.C, K = g.K;
+    for (int i = threadIdx.x; i < taps * K * NMAX; i += 256) {
+        const int c = i % NMAX, t2 = i / NMAX, ko = t2 % K, tap = t2 / K;
+        w_s[i] = c < C ? __ldg(w + (tap * C + c) * K + ko) : 0.f;
+    }
     __syncthreads();
     const long long M = (long long)g.B * g.H * g.W;
     for (long long m = (long long)blockIdx.x * 256 + threadIdx.x; m < M; m += (long long)gridDim.x * 256) {
@@ -398,12 +413,17 @@ __global__ void __launch_bounds__(256) conv_small_dgrad_kernel(ConvGeom g, const
                 int wo = ww / g.sw;
                 if (wo * g.sw != ww || wo >= g.Wo) continue;
                 const float *pz = img + ((long long)ho * g.Wo + wo) * K;
-                const float *wt = w_s + (r * g.kw + s) * C * K;
+                const float4 *wt = reinterpret_cast<const float4 *>(w_s + (r * g.kw + s) * K * NMAX);
                 for (int ko = 0; ko < K; ++ko) {
                     float gv = __ldg(pz + ko);
 #pragma unroll
-                    for (int c = 0; c < NMAX; ++c)
-                        if (c < C) acc[c] = fmaf(gv, wt[c * K + ko], acc[c]);
+                    for (int q = 0; q < NMAX / 4; ++q) {
+                        const float4 wv = wt[ko * (NMAX / 4) + q];
+                        acc[4 * q] = fmaf(gv, wv.x, acc[4 * q]);
+                        acc[4 * q + 1] = fmaf(gv, wv.y, acc[4 * q + 1]);
+                        acc[4 * q + 2] = fmaf(gv, wv.z, acc[4 * q + 2]);
+                        acc[4 * q + 3] = fmaf(gv, wv.w, acc[4 * q + 3]);
+                    }
                 }
             }
         }
@@ -761,9 +781,12 @@ int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const
         launch_pdl(dense_skinny_fwd_kernel<kSkinnyN>, dim3(g.B), dim3(1024), 0, s, g.C, g.K, act, x, w, bias, y);
         return check_launch("dense_fwd[skinny]");
     }
-    size_t smem = ((size_t)g.kh * g.kw * g.C + 1) * g.K * sizeof(float);
+    const int np = g.K <= 4 ? 4 : (g.K <= 8 ? 8 : (g.K <= 12 ? 12 : 16));
+    size_t smem = ((size_t)g.kh * g.kw * g.C + 1) * np * sizeof(float);
     long long M = (long long)g.B * g.Ho * g.Wo;
-    if (g.K <= 8) launch_pdl(conv_small_fwd_kernel<8>, dim3(pixel_grid(M)), dim3(256), smem, s, g, act, x, w, bias, y);
+    if (np == 4) launch_pdl(conv_small_fwd_kernel<4>, dim3(pixel_grid(M)), dim3(256), smem, s, g, act, x, w, bias, y);
+    else if (np == 8) launch_pdl(conv_small_fwd_kernel<8>, dim3(pixel_grid(M)), dim3(256), smem, s, g, act, x, w, bias, y);
+    else if (np == 12) launch_pdl(conv_small_fwd_kernel<12>, dim3(pixel_grid(M)), dim3(256), smem, s, g, act, x, w, bias, y);
     else launch_pdl(conv_small_fwd_kernel<16>, dim3(pixel_grid(M)), dim3(256), smem, s, g, act, x, w, bias, y);
     return check_launch("conv2d_fwd[small]");
 }
@@ -791,9 +814,12 @@ int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, 
 #undef FNET_CALL
         return check_launch("dense_bwd_data[skinny]");
     }
-    size_t smem = (size_t)g.kh * g.kw * g.C * g.K * sizeof(float);
+    const int cp = g.C <= 4 ? 4 : (g.C <= 8 ? 8 : (g.C <= 12 ? 12 : 16));
+    size_t smem = (size_t)g.kh * g.kw * g.K * cp * sizeof(float);
     long long M = (long long)g.B * g.H * g.W;
-    if (g.C <= 8) launch_pdl(conv_small_dgrad_kernel<8>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, ep.accumulate, ep.act, ep.y);
+    if (cp == 4) launch_pdl(conv_small_dgrad_kernel<4>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, ep.accumulate, ep.act, ep.y);
+    else if (cp == 8) launch_pdl(conv_small_dgrad_kernel<8>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, ep.accumulate, ep.act, ep.y);
+    else if (cp == 12) launch_pdl(conv_small_dgrad_kernel<12>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, ep.accumulate, ep.act, ep.y);
     else launch_pdl(conv_small_dgrad_kernel<16>, dim3(pixel_grid(M)), dim3(256), smem, s, g, dz, w, dx, ep.accumulate, ep.act, ep.y);
     return check_launch("conv2d_bwd_data[small]");
 }
