@@ -304,6 +304,36 @@ __global__ void __launch_bounds__(256) concat_rows_bwd_kernel(I outer, I blk_a, 
 }
 
 
+// concat backward that also applies the activation derivative of the layer(s) that produced the operands:
+// da = (acc_a ? da + slice : slice) * act_a'(ya), likewise b.  One pass instead of the copy plus an act_bwd per operand.
+__device__ __forceinline__ float4 grad4(float4 g, float4 y, int act) {
+    return make_float4(g.x * act_grad(y.x, act), g.y * act_grad(y.y, act), g.z * act_grad(y.z, act), g.w * act_grad(y.w, act));
+}
+__device__ __forceinline__ float grad4(float g, float y, int act) { return g * act_grad(y, act); }
+
+template <typename T>
+__global__ void __launch_bounds__(256) concat_rows_bwd_act_kernel(int outer, int blk_a, int blk_b, const T *__restrict__ dy, T *da, T *db,
+                                                                  int acc_a, int acc_b, int act_a, const T *__restrict__ ya, int act_b,
+                                                                  const T *__restrict__ yb) {
+    pdl_prologue();
+    const int blk = blk_a + blk_b, total = outer * blk;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int o = i / blk, e = i - o * blk;
+        T g = __ldg(dy + i);
+        if (e < blk_a) {
+            if (da) {
+                const int at = o * blk_a + e;
+                if (acc_a) g = vadd(da[at], g);
+                da[at] = act_a ? grad4(g, __ldg(ya + at), act_a) : g;
+            }
+        } else if (db) {
+            const int at = o * blk_b + (e - blk_a);
+            if (acc_b) g = vadd(db[at], g);
+            db[at] = act_b ? grad4(g, __ldg(yb + at), act_b) : g;
+        }
+    }
+}
+
 int run_softmax_rows(int64_t rows, int64_t cols, const float *x, float *y, cudaStream_t stream) {
     int64_t blocks = ceil_div<int64_t>(rows, 8);
     int64_t cap = (int64_t)kNumSMs * 8;
@@ -421,6 +451,26 @@ int fnet_concat_rows_bwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t 
     else
         launch_pdl(concat_rows_bwd_kernel<float, int64_t>, dim3(stream_grid(total, 256)), dim3(256), 0, s, outer, blk_a, blk_b, dy, da, db, acc_a, acc_b);
     return check_launch("fnet_concat_rows_bwd");
+}
+
+int fnet_concat_rows_bwd_act(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t inner, const float *dy, float *da, float *db,
+                             int acc_a, int acc_b, int act_a, const float *ya, int act_b, const float *yb, void *stream) {
+    FNET_REQUIRE(outer >= 0 && rows_a >= 0 && rows_b >= 0 && inner > 0 && dy, "fnet_concat_rows_bwd_act: bad arguments");
+    FNET_REQUIRE(act_a >= FNET_ACT_NONE && act_a <= FNET_ACT_SIGMOID && act_b >= FNET_ACT_NONE && act_b <= FNET_ACT_SIGMOID &&
+                 (!act_a || ya) && (!act_b || yb), "fnet_concat_rows_bwd_act: relu / tanh / sigmoid with the operand's forward output, or none");
+    int64_t total = (int64_t)outer * (rows_a + rows_b) * inner;
+    if (total == 0 || (!da && !db)) return FNET_OK;
+    FNET_REQUIRE(total < 0x7fffffffLL - (1 << 26), "fnet_concat_rows_bwd_act: tensor too large");
+    const int64_t blk_a = (int64_t)rows_a * inner, blk_b = (int64_t)rows_b * inner;
+    cudaStream_t s = as_stream(stream);
+    if (!(blk_a & 3) && !(blk_b & 3) && aligned16(dy) && aligned16(da) && aligned16(db) && aligned16(ya) && aligned16(yb))
+        launch_pdl(concat_rows_bwd_act_kernel<float4>, dim3(stream_grid(total / 4, 256)), dim3(256), 0, s, outer, (int)(blk_a / 4), (int)(blk_b / 4),
+                   reinterpret_cast<const float4 *>(dy), reinterpret_cast<float4 *>(da), reinterpret_cast<float4 *>(db), acc_a, acc_b,
+                   act_a, reinterpret_cast<const float4 *>(ya), act_b, reinterpret_cast<const float4 *>(yb));
+    else
+        launch_pdl(concat_rows_bwd_act_kernel<float>, dim3(stream_grid(total, 256)), dim3(256), 0, s, outer, (int)blk_a, (int)blk_b, dy, da, db,
+                   acc_a, acc_b, act_a, ya, act_b, yb);
+    return check_launch("fnet_concat_rows_bwd_act");
 }
 
 int fnet_pad2d_fwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h, int32_t pad_w, const float *x,

@@ -583,10 +583,15 @@ class Engine(object):
                     consumers.setdefault(self._resolve(s, True), []).append(j)
             for r, users in consumers.items():
                 node_r = self.nodes[r]
-                if (len(users) == 1 and r != last and node_r.kind in GEMM_KINDS + ("dwconv2d",) and need[r]
-                        and fl.ACT[node_r.cfg["activation"]] in (1, 2, 3)
-                        and self.nodes[users[0]].kind in ("conv2d", "dense") and len(self.src[users[0]]) == 1
-                        and not self._dgrad_on_tensor_core(users[0], batch)):
+                if not (len(users) == 1 and r != last and node_r.kind in GEMM_KINDS + ("dwconv2d",) and need[r]
+                        and fl.ACT[node_r.cfg["activation"]] in (1, 2, 3)):
+                    continue
+                user = self.nodes[users[0]]
+                if user.kind in ("conv2d", "dense") and len(self.src[users[0]]) == 1 and not self._dgrad_on_tensor_core(users[0], batch):
+                    fused_into[r] = users[0]
+                elif user.kind in ("add", "concat"):
+                    # the merge's backward is a copy of (a slice of) dy into this layer's gradient buffer: the derivative
+                    # rides along (act_bwd reading the merge's dy / fnet_concat_rows_bwd_act) instead of a pass of its own
                     fused_into[r] = users[0]
 
         def dx_epilogue(i, s0):
@@ -677,7 +682,13 @@ class Engine(object):
             elif kind == "add":
                 for j in self.src[i]:
                     if need[j]:
-                        add("add_bwd", L.fnet_accumulate, n_out, dy, self._g(j), acc_flag(j), sp)
+                        rj = self._resolve(j, True)
+                        if fused_into.get(rj) == i:
+                            cols = self.shape[rj][-1]
+                            add("act_bwd", L.fnet_act_bwd, fl.ACT[self.nodes[rj].cfg["activation"]], n_out // cols, cols,
+                                self._a(rj, True), dy, self._g(j), acc_flag(j), sp)
+                        else:
+                            add("add_bwd", L.fnet_accumulate, n_out, dy, self._g(j), acc_flag(j), sp)
             elif kind == "mul":
                 a, b = self.src[i]
                 if need[a]:
@@ -698,7 +709,18 @@ class Engine(object):
                 elif need[a] or need[b]:
                     ga, fa = (self._g(a), acc_flag(a)) if need[a] else (None, 0)
                     gb, fb = (self._g(b), acc_flag(b)) if need[b] else (None, 0)
-                    add("concat_bwd", L.fnet_concat_rows_bwd, outer, ra, rb, inner, dy, ga, gb, fa, fb, sp)
+                    folded = []
+                    for operand, wanted in ((a, need[a]), (b, need[b])):
+                        r_op = self._resolve(operand, True)
+                        if wanted and fused_into.get(r_op) == i:
+                            folded.append((fl.ACT[self.nodes[r_op].cfg["activation"]], self._a(r_op, True)))
+                        else:
+                            folded.append((0, None))
+                    if folded[0][0] or folded[1][0]:
+                        add("concat_bwd", L.fnet_concat_rows_bwd_act, outer, ra, rb, inner, dy, ga, gb, fa, fb,
+                            folded[0][0], folded[0][1], folded[1][0], folded[1][1], sp)
+                    else:
+                        add("concat_bwd", L.fnet_concat_rows_bwd, outer, ra, rb, inner, dy, ga, gb, fa, fb, sp)
             elif kind == "pad":
                 h, w, c = self.shape[s0]
                 add("pad2d_bwd", L.fnet_pad2d_bwd, batch, h, w, c, cfg["pad"][0], cfg["pad"][1], dy, self._g(s0), acc_flag(s0), sp)

@@ -173,6 +173,8 @@ def try_fuse(engine, ops):
                 return None
             out.append(_Op(FK_CONCAT_FWD, d=[outer, ra * inner, rb * inner], p=[a, b, y], reads=[a, b], writes=[y]))
         elif name == "concat_bwd":
+            if len(args) != 10:
+                return None       # the variant with a folded activation derivative has no fused counterpart
             outer, ra, rb, inner, dy, ga, gb, fa, fb = args[:9]
             if outer * (ra + rb) * inner >= 2 ** 31:
                 return None

@@ -86,6 +86,7 @@ SIGNATURES = {
     "fnet_gather_batch": (C.c_int, [_I32, _I64, _I64, _P, _P, _P, _P, _P, _P, C.c_int, _F, _F, _P]),
     "fnet_concat_rows_fwd": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _P]),
     "fnet_concat_rows_bwd": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, C.c_int, C.c_int, _P]),
+    "fnet_concat_rows_bwd_act": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, C.c_int, _P, _P]),
     "fnet_gather_rows": (C.c_int, [_I32, _I64, _P, _P, _P, _P, _P]),
     "fnet_gather_shift_flip": (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "fnet_u8_to_f32": (C.c_int, [_I64, _P, _F, _P, _P]),

@@ -221,6 +221,10 @@ int fnet_concat_rows_fwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t 
                          float *y, void *stream);
 int fnet_concat_rows_bwd(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t inner, const float *dy, float *da,
                          float *db, int acc_a, int acc_b, void *stream);
+/* The same, with the activation derivative of the layer(s) that produced the operands folded in:
+ * da = (acc_a ? da + slice : slice) * act_a'(ya) (ya = that layer's forward output; act 0 = none), likewise b. */
+int fnet_concat_rows_bwd_act(int32_t outer, int32_t rows_a, int32_t rows_b, int32_t inner, const float *dy, float *da, float *db,
+                             int acc_a, int acc_b, int act_a, const float *ya, int act_b, const float *yb, void *stream);
 int fnet_pad2d_fwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h, int32_t pad_w, const float *x,
                    float *y, void *stream);
 int fnet_pad2d_bwd(int32_t batch, int32_t h, int32_t w, int32_t c, int32_t pad_h, int32_t pad_w, const float *dy,

@@ -499,6 +499,29 @@ def test_head_forward_and_loss_in_one_launch(L, m, k, n):
     assert_close(host(probs), ops.act_fwd(z - b.astype(np.float32).astype(np.float64), "softmax"), what="probabilities without bias")
 
 
+@pytest.mark.parametrize("outer,ra,rb,inner", [(6, 4, 4, 12), (5, 3, 2, 7), (128, 32, 32, 96)])
+def test_concat_backward_with_folded_activation_derivatives(L, outer, ra, rb, inner):
+    from featurenet_b200 import lib as fl
+    rng = np.random.default_rng(outer + inner)
+    dy = rng.standard_normal((outer, ra + rb, inner))
+    ya, yb = ops.act_fwd(rng.standard_normal((outer, ra, inner)), "relu"), ops.act_fwd(rng.standard_normal((outer, rb, inner)), "tanh")
+    da0, db0 = rng.standard_normal(ya.shape), rng.standard_normal(yb.shape)
+    for acc_a, acc_b, act_a, act_b in ((0, 0, "relu", "tanh"), (1, 0, "relu", None), (0, 1, None, "tanh"), (1, 1, "relu", "tanh")):
+        want_a = dy[:, :ra] + (da0 if acc_a else 0.0)
+        want_b = dy[:, ra:] + (db0 if acc_b else 0.0)
+        want_a = ops.act_bwd(ya, want_a, act_a) if act_a else want_a
+        want_b = ops.act_bwd(yb, want_b, act_b) if act_b else want_b
+        da, db = dev(da0), dev(db0)
+        L.fnet_concat_rows_bwd_act(outer, ra, rb, inner, ptr(dev(dy)), ptr(da), ptr(db), acc_a, acc_b, fl.ACT[act_a],
+                                   ptr(dev(ya)) if act_a else None, fl.ACT[act_b], ptr(dev(yb)) if act_b else None, None)
+        assert_close(host(da), want_a, what="da %s" % act_a)
+        assert_close(host(db), want_b, what="db %s" % act_b)
+    # one operand only (the other one needs no gradient)
+    db = dev(db0)
+    L.fnet_concat_rows_bwd_act(outer, ra, rb, inner, ptr(dev(dy)), None, ptr(db), 0, 0, 0, None, fl.ACT["tanh"], ptr(dev(yb)), None)
+    assert_close(host(db), ops.act_bwd(yb, dy[:, ra:], "tanh"), what="db alone")
+
+
 def test_adam_and_sgd_follow_keras(L):
     rng = np.random.default_rng(4)
     n = 1003
