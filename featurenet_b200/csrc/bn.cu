@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(256) bn_bwd_dx_kernel(BnShape s, const float *
                                                         const float *__restrict__ save_rstd,
                                                         const float *__restrict__ partial, float *__restrict__ dx,
                                                         float *__restrict__ dgamma, float *__restrict__ dbeta,
-                                                        int accumulate) {
+                                                        int accumulate, int act) {
     pdl_prologue();
     __shared__ float sums[2];
     int a = blockIdx.x, part = blockIdx.y;
@@ -251,7 +251,9 @@ __global__ void __launch_bounds__(256) bn_bwd_dx_kernel(BnShape s, const float *
         for (int u = 0; u < V; ++u) {
             float xhat = (f[u] - mean) * rstd;
             float v = k * (n * g[u] - sb - xhat * sg);
-            o[u] = accumulate ? o[u] + v : v;
+            v = accumulate ? o[u] + v : v;
+            // x is the OUTPUT of the layer below: its activation derivative comes from x itself, no extra read
+            o[u] = act ? v * act_grad(f[u], act) : v;
         }
         dxv[at] = BnVec<V>::make(o);
     }
@@ -317,6 +319,14 @@ int fnet_bn_bwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const 
 int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,
                 const float *save_mean, const float *save_rstd, float *dx, float *dgamma, float *dbeta,
                 int accumulate, void *ws, size_t ws_bytes, void *stream) {
+    return fnet_bn_bwd_act(outer, a, inner, x, dy, gamma, save_mean, save_rstd, dx, dgamma, dbeta, accumulate, FNET_ACT_NONE, ws,
+                           ws_bytes, stream);
+}
+
+int fnet_bn_bwd_act(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,
+                    const float *save_mean, const float *save_rstd, float *dx, float *dgamma, float *dbeta,
+                    int accumulate, int act, void *ws, size_t ws_bytes, void *stream) {
+    FNET_REQUIRE(act >= FNET_ACT_NONE && act <= FNET_ACT_SIGMOID, "fnet_bn_bwd_act: relu / tanh / sigmoid, or none");
     FNET_REQUIRE(outer > 0 && a > 0 && inner > 0 && (int64_t)outer * a * inner < 0x7fffffffLL, "fnet_bn_bwd: bad shape");
     FNET_REQUIRE(x && dy && gamma && save_mean && save_rstd && dx && dgamma && dbeta, "fnet_bn_bwd: null pointer");
     if (!ws || ws_bytes < fnet_bn_workspace_bytes(a)) {
@@ -334,10 +344,10 @@ int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const f
     if (rc) return rc;
     if (vec)
         launch_pdl(bn_bwd_dx_kernel<4>, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, gamma, save_mean, save_rstd, partial, dx,
-                                                                 dgamma, dbeta, accumulate);
+                                                                 dgamma, dbeta, accumulate, act);
     else
         launch_pdl(bn_bwd_dx_kernel<1>, dim3(grid), dim3(256), 0, as_stream(stream), s, x, dy, gamma, save_mean, save_rstd, partial, dx,
-                                                                 dgamma, dbeta, accumulate);
+                                                                 dgamma, dbeta, accumulate, act);
     return check_launch("fnet_bn_bwd");
 }
 

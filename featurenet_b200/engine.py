@@ -589,6 +589,8 @@ class Engine(object):
                 user = self.nodes[users[0]]
                 if user.kind in ("conv2d", "dense") and len(self.src[users[0]]) == 1 and not self._dgrad_on_tensor_core(users[0], batch):
                     fused_into[r] = users[0]
+                elif user.kind == "bn" and training:
+                    fused_into[r] = users[0]          # BatchNorm's backward reads this layer's output anyway (fnet_bn_bwd_act)
                 elif user.kind in ("add", "concat"):
                     # the merge's backward is a copy of (a slice of) dy into this layer's gradient buffer: the derivative
                     # rides along (act_bwd reading the merge's dy / fnet_concat_rows_bwd_act) instead of a pass of its own
@@ -660,8 +662,13 @@ class Engine(object):
                 outer, a, inner = self._bn_view(i, batch)
                 mean, rstd = self.aux[i]
                 dx, flag = (self._g(s0), acc_flag(s0)) if want_dx else (dy, 0)
-                add("bn_bwd", L.fnet_bn_bwd, outer, a, inner, x, dy, self._wp(i, 0), C.c_void_p(mean.data_ptr()),
-                    C.c_void_p(rstd.data_ptr()), dx, gw(i, 0), gw(i, 1), flag, ws, wsb, sp)
+                r0 = self._resolve(s0, True)
+                if want_dx and fused_into.get(r0) == i:
+                    add("bn_bwd", L.fnet_bn_bwd_act, outer, a, inner, x, dy, self._wp(i, 0), C.c_void_p(mean.data_ptr()),
+                        C.c_void_p(rstd.data_ptr()), dx, gw(i, 0), gw(i, 1), flag, fl.ACT[self.nodes[r0].cfg["activation"]], ws, wsb, sp)
+                else:
+                    add("bn_bwd", L.fnet_bn_bwd, outer, a, inner, x, dy, self._wp(i, 0), C.c_void_p(mean.data_ptr()),
+                        C.c_void_p(rstd.data_ptr()), dx, gw(i, 0), gw(i, 1), flag, ws, wsb, sp)
             elif not want_dx:
                 continue
             elif kind in ("maxpool", "avgpool"):
@@ -1073,8 +1080,37 @@ class Engine(object):
             graph = self.graphs[(kind, batch)] = self._capture(ops)
         return graph
 
+    # While a thread records a graph (thread-local capture mode) it must not make "unsafe" CUDA calls: a stream or device
+    # synchronisation, an allocation.  An Engine that the garbage collector finalises in the middle of a capture does
+    # exactly that (release() waits for its streams), and the capture dies with "operation failed due to a previous error
+    # during capture".  So finalisers that arrive on a capturing thread are parked and run when the capture is over.
+    _capturing = threading.local()
+    _parked = []
+    _parked_lock = threading.Lock()
+
+    @classmethod
+    def _run_parked(cls):
+        with cls._parked_lock:
+            todo, cls._parked[:] = list(cls._parked), []
+        for state in todo:
+            ghost = object.__new__(cls)
+            ghost.__dict__.update(state)
+            try:
+                ghost.release()
+            except Exception:          # noqa: BLE001
+                pass
+
     def _capture(self, ops):
         """Record a launch list into a CUDA graph (nothing executes until the graph is launched)."""
+        Engine._capturing.depth = getattr(Engine._capturing, "depth", 0) + 1
+        try:
+            return self._capture_now(ops)
+        finally:
+            Engine._capturing.depth -= 1
+            if Engine._capturing.depth == 0 and Engine._parked:
+                Engine._run_parked()
+
+    def _capture_now(self, ops):
         t0 = time.perf_counter()
         self.lib.fnet_graph_begin(self.sp)
         handle = C.c_void_p()
@@ -1580,6 +1616,10 @@ class Engine(object):
         if sys is None or sys.is_finalizing():
             return                 # interpreter shutdown: the CUDA context may be gone; the process frees everything
         try:
+            if getattr(Engine._capturing, "depth", 0) > 0 and getattr(self, "_streams", None):
+                with Engine._parked_lock:              # this thread is recording a graph: release later (see _capture)
+                    Engine._parked.append(dict(self.__dict__))
+                return
             self.release()
         except Exception:          # noqa: BLE001
             pass

@@ -66,6 +66,7 @@ SIGNATURES = {
     "fnet_bn_bwd_infer": (C.c_int, [_I32, _I32, _I32, _F, _P, _P, _P, _P, C.c_int, _P]),
     "fnet_l2_attack_step": (C.c_int, [_I32, _I64, _P, _P, _P, _P, _F, _F, _F, _F, _P, _P]),
     "fnet_bn_bwd": (C.c_int, [_I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int, _P, _SZ, _P]),
+    "fnet_bn_bwd_act": (C.c_int, [_I32, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, _P, _SZ, _P]),
     "fnet_act_fwd": (C.c_int, [C.c_int, _I64, _I64, _P, _P, _P]),
     "fnet_act_bwd": (C.c_int, [C.c_int, _I64, _I64, _P, _P, _P, C.c_int, _P]),
     "fnet_dropout_fwd": (C.c_int, [_I64, _F, _U64, _U32, _P, _P, _P, _P]),

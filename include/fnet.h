@@ -186,6 +186,11 @@ int fnet_bn_bwd_infer(int32_t outer, int32_t a, int32_t inner, float eps, const 
 int fnet_bn_bwd(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,
                 const float *save_mean, const float *save_rstd, float *dx, float *dgamma, float *dbeta,
                 int accumulate, void *ws, size_t ws_bytes, void *stream);
+/* The same when x is the OUTPUT of an activated layer with no other consumer: dx is also multiplied by that
+ * activation's derivative, taken from x itself (act = FNET_ACT_RELU / TANH / SIGMOID; NONE = fnet_bn_bwd). */
+int fnet_bn_bwd_act(int32_t outer, int32_t a, int32_t inner, const float *x, const float *dy, const float *gamma,
+                    const float *save_mean, const float *save_rstd, float *dx, float *dgamma, float *dbeta,
+                    int accumulate, int act, void *ws, size_t ws_bytes, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * Element-wise and data-movement ops.

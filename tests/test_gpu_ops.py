@@ -344,6 +344,17 @@ def test_batchnorm_axis1(L, shape, axis):
     assert_close(host(dxd), dx, tol=5e-5, what="bn dx")
     assert_close(host(dgd), dgamma, what="bn dgamma")
     assert_close(host(dbd), dbeta, what="bn dbeta")
+    # x as the output of an activated layer below: the derivative of that activation (taken from x itself) rides along,
+    # also on top of what the buffer already holds
+    from featurenet_b200 import lib as fl
+    for act in ("relu", "tanh", "sigmoid"):
+        for accumulate in (0, 1):
+            before = np.full(shape, 0.25)
+            dxa = dev(before)
+            L.fnet_bn_bwd_act(outer, a, inner, ptr(xd), ptr(dev(dy)), ptr(gd), ptr(sm), ptr(sr), ptr(dxa), ptr(dgd), ptr(dbd),
+                              accumulate, fl.ACT[act], ptr(ws), ws.numel(), None)
+            want = ops.act_bwd(x.astype(np.float32).astype(np.float64), dx + (before if accumulate else 0.0), act)
+            assert_close(host(dxa), want, tol=5e-5, what="bn dx with %s' accumulate=%d" % (act, accumulate))
     yi = torch.empty(shape, device="cuda")
     L.fnet_bn_fwd_infer(outer, a, inner, 1e-3, ptr(xd), ptr(gd), ptr(bd), ptr(dev(mm)), ptr(dev(mv)), ptr(yi), None)
     assert_close(host(yi), ops.bn_infer_fwd(x, gamma, beta, mm, mv, axis), what="bn infer")
