@@ -433,7 +433,7 @@ def run_population_bench(args, dist, world, rank, n_train, n_test, epochs=1):
         formatted = ProductSet(os.path.join(ROOT, source)).format_products()
         # weak scaling: the same `--population` candidates PER GPU (the sample repeated), so that the number of
         # candidates grows with the box and the makespan is not bound by the single heaviest candidate
-        formatted = formatted[: args.population] * world
+        formatted = formatted[: args.population] * (1 if args.population_total else world)
         (x_train, y_train), (x_test, y_test) = synth.load("cifar", n_train, n_test)
     TensorflowGenerator.dataset = "cifar"
     TensorflowGenerator.X_train, TensorflowGenerator.Y_train = x_train, y_train
@@ -476,7 +476,9 @@ def run_population_bench(args, dist, world, rank, n_train, n_test, epochs=1):
     return {"candidates": len(results), "valid": len(valid), "expected_valid": buildable, "errors": errors,
             "retried_alone": retried, "seconds": seconds, "first_pass_seconds": first_seconds,
             "resident_per_gpu": workers, "epochs": epochs,
-            "candidates_per_hour": 3600.0 * len(results) / seconds, "scaling": "weak (%d candidates per GPU, LPT-sharded over all ranks)" % args.population,
+            "candidates_per_hour": 3600.0 * len(results) / seconds,
+            "scaling": ("strong (%d candidates in all, LPT-sharded over all ranks)" if args.population_total else
+                        "weak (%d candidates per GPU, LPT-sharded over all ranks)") % args.population,
             "what": "%s (%d products, %d buildable): build + %d epoch(s) on %d synthetic CIFAR-shape images + "
                     "validation + evaluate on %d" % (os.path.basename(source), len(results), buildable, epochs, n_train, n_test),
             "mean_accuracy": float(np.mean([r["accuracy"] for r in valid])) if valid else 0.0,
@@ -721,6 +723,8 @@ def main():
     ap.add_argument("--quick", action="store_true", help="skip the secondary workloads")
     ap.add_argument("--population", type=int, default=32, help="candidates of the sharded population run (0 = skip)")
     ap.add_argument("--resident", type=int, default=8, help="candidates kept resident per GPU in the population run")
+    ap.add_argument("--population-total", action="store_true", help="--population counts the candidates of the whole job "
+                    "(strong scaling: BASELINE configs[3], one 100-product population over 8 GPUs) instead of per GPU")
     ap.add_argument("--population-epochs", type=int, default=1, help="epochs per candidate of the full-size population run")
     ap.add_argument("--dp", action="store_true", help="data-parallel training of ONE large candidate (the `keras` "
                     "template) over all ranks: NCCL all-reduce of the gradient arena every step")
