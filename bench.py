@@ -456,6 +456,12 @@ def run_population_bench(args, dist, world, rank, n_train, n_test, epochs=1):
         return pop.train_product(product, "cifar", epochs=epochs, batch_size=BATCH, product_features=original,
                                  shared_gpu=workers > 1)
 
+    def train_giant(index, item):
+        product, original = pop.copy_product(item)
+        return pop.train_product(product, "cifar", epochs=epochs, batch_size=BATCH, product_features=original, data_parallel=True)
+
+    giants = pop.pick_giants(costs, world, args.giant_share) if (args.population_total and world > 1 and not args.no_dp_giants) else []
+
     def one_pass():
         if world > 1:
             dist.barrier()
@@ -463,7 +469,8 @@ def run_population_bench(args, dist, world, rank, n_train, n_test, epochs=1):
         t0 = time.perf_counter()
         with quiet():
             res = pop.run_population(formatted, train_one, costs, rank=rank, world_size=world,
-                                     dist=dist if world > 1 else None, workers=workers, mem_bytes=mem, budget=budget)
+                                     dist=dist if world > 1 else None, workers=workers, mem_bytes=mem, budget=budget,
+                                     train_giant=train_giant if giants else None, giant_share=args.giant_share)
         torch.cuda.synchronize()
         return res, pop.max_over_ranks(time.perf_counter() - t0, dist if world > 1 else None, device="cuda")
 
@@ -474,7 +481,7 @@ def run_population_bench(args, dist, world, rank, n_train, n_test, epochs=1):
               for i, r in results if r.get("error") and not r.get("valid")]
     retried = sum(1 for _, r in results if r.get("retried_alone_after"))
     return {"candidates": len(results), "valid": len(valid), "expected_valid": buildable, "errors": errors,
-            "retried_alone": retried, "seconds": seconds, "first_pass_seconds": first_seconds,
+            "retried_alone": retried, "data_parallel_giants": giants, "seconds": seconds, "first_pass_seconds": first_seconds,
             "resident_per_gpu": workers, "epochs": epochs,
             "candidates_per_hour": 3600.0 * len(results) / seconds,
             "scaling": ("strong (%d candidates in all, LPT-sharded over all ranks)" if args.population_total else
@@ -725,6 +732,10 @@ def main():
     ap.add_argument("--resident", type=int, default=8, help="candidates kept resident per GPU in the population run")
     ap.add_argument("--population-total", action="store_true", help="--population counts the candidates of the whole job "
                     "(strong scaling: BASELINE configs[3], one 100-product population over 8 GPUs) instead of per GPU")
+    ap.add_argument("--no-dp-giants", action="store_true", help="with --population-total: do not train the candidates that "
+                    "exceed a rank's fair share data-parallel over all ranks (plain longest-first placement)")
+    ap.add_argument("--giant-share", type=float, default=0.6, help="a candidate whose estimated cost exceeds this part of a "
+                    "rank's fair share of the population is trained data-parallel over all ranks")
     ap.add_argument("--population-epochs", type=int, default=1, help="epochs per candidate of the full-size population run")
     ap.add_argument("--dp", action="store_true", help="data-parallel training of ONE large candidate (the `keras` "
                     "template) over all ranks: NCCL all-reduce of the gradient arena every step")

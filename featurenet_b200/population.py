@@ -90,6 +90,27 @@ def assign_lpt(costs, world_size):
     return shards
 
 
+def assign_lpt_subset(indices, costs, world_size):
+    """assign_lpt over a subset of the candidates (the others are trained some other way)."""
+    order = sorted(indices, key=lambda i: (-costs[i], i))
+    loads = [0.0] * world_size
+    shards = [[] for _ in range(world_size)]
+    for i in order:
+        r = min(range(world_size), key=lambda j: (loads[j], j))
+        shards[r].append(i)
+        loads[r] += costs[i]
+    return shards
+
+
+def pick_giants(costs, world_size, share=0.6):
+    """Candidates too large to be one GPU's job: each would take more than `share` of a rank's fair part of the whole
+    population, so whatever rank gets it decides the makespan.  They are trained data-parallel over ALL ranks first."""
+    if world_size < 2 or not costs:
+        return []
+    fair = sum(costs) / world_size
+    return sorted(i for i in range(len(costs)) if costs[i] > share * fair)
+
+
 def max_over_ranks(value, dist=None, device=None):
     """The slowest rank's value (a multi-GPU time is the max over ranks, never a wall clock of one)."""
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
@@ -100,7 +121,8 @@ def max_over_ranks(value, dist=None, device=None):
     return float(t.item())
 
 
-def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, workers=1, mem_bytes=None, budget=None):
+def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, workers=1, mem_bytes=None, budget=None,
+                   train_giant=None, giant_share=0.6):
     """Train this rank's share of ``products``; gather (index, result) pairs on every rank, in index order.
 
     train_one(index, product) -> picklable result (e.g. dict(accuracy=..., history=..., params=...)).
@@ -115,8 +137,25 @@ def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, 
     mem_bytes[i] (estimate_bytes) with a MemoryBudget makes the co-residency memory-aware; a candidate that still runs
     out of memory beside its neighbours is trained again ALONE after the others are done, so that only a candidate
     that does not fit the GPU by itself is scored 0.
+
+    train_giant(index, product), when given with an initialised process group, is called by ALL ranks together for
+    every candidate that pick_giants() names, before the rest is sharded: the one-large-candidate mode of the engine
+    (featurenet_b200.dataparallel) applied to the candidates that would otherwise be the tail of the population.
     """
-    mine = assign_lpt(costs, world_size)[rank]
+    giants = pick_giants(costs, world_size, giant_share) if (train_giant is not None and dist is not None and dist.is_initialized()) else []
+    giant_results = []
+    for index in giants:
+        started = time.time()
+        try:
+            result = train_giant(index, products[index])
+        except Exception as e:                       # noqa: BLE001
+            result = {"error": "%s: %s" % (type(e).__name__, e), "accuracy": 0}
+        if isinstance(result, dict):
+            result.setdefault("seconds", time.time() - started)
+            result["rank"], result["data_parallel"] = -1, world_size
+        giant_results.append((index, result))
+    rest = [i for i in range(len(costs)) if i not in set(giants)]
+    mine = assign_lpt_subset(rest, costs, world_size)[rank]
 
     def one(index):
         started = time.time()
@@ -169,6 +208,7 @@ def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, 
         merged = [pair for part in gathered for pair in part]
     else:
         merged = local
+    merged = merged + giant_results
     return sorted(merged, key=lambda pair: pair[0])
 
 
@@ -193,7 +233,8 @@ def copy_product(item):
     return [level(block, 2) for block in item]
 
 
-def train_product(product, dataset, epochs, batch_size, product_features=None, data_augmentation=False, shared_gpu=False):
+def train_product(product, dataset, epochs, batch_size, product_features=None, data_augmentation=False, shared_gpu=False,
+                  data_parallel=False):
     """One candidate through the reference-named runner; returns the fields the drivers log.
 
     shared_gpu=True is for candidates that run side by side on one GPU (run_population(workers > 1)): the runner
@@ -202,8 +243,25 @@ def train_product(product, dataset, epochs, batch_size, product_features=None, d
     """
     from tensorflow_generator import TensorflowGenerator
     import helpers
+    import os
     helpers.clear_failure()
-    if shared_gpu:
+    if data_parallel:
+        # every rank of the process group makes this call together: the engine cuts each batch into per-rank slices
+        previous = os.environ.get("FNET_DP")
+        os.environ["FNET_DP"] = "1"
+        try:
+            with contextlib.redirect_stdout(io.StringIO()):
+                gen = TensorflowGenerator(product, epochs=epochs, dataset=dataset, data_augmentation=data_augmentation,
+                                          batch_size=batch_size, product_features=product_features, clear_memory=False)
+            network = getattr(getattr(gen, "model", None), "model", None)
+            if network is not None:
+                network.release()
+        finally:
+            if previous is None:
+                os.environ.pop("FNET_DP", None)
+            else:
+                os.environ["FNET_DP"] = previous
+    elif shared_gpu:
         gen = TensorflowGenerator(product, epochs=epochs, dataset=dataset, data_augmentation=data_augmentation,
                                   batch_size=batch_size, product_features=product_features, clear_memory=False)
         network = getattr(getattr(gen, "model", None), "model", None)
