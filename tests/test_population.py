@@ -135,3 +135,48 @@ def test_copy_product_protects_the_callers_tree_and_parses_the_same():
         if a:
             strip = lambda rows: [{k: v for k, v in r.items() if k != "name"} for r in rows]
             assert strip(a.describe()) == strip(b.describe()) == strip(again.describe())
+
+
+def _giant_worker(rank, world, port, queue):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        products = ["p%d" % i for i in range(6)]
+        costs = [1.0, 30.0, 1.0, 2.0, 1.0, 1.0]            # candidate 1 alone exceeds a rank's fair share (18)
+        alone, together = [], []
+
+        def train_one(index, product):
+            alone.append(index)
+            return {"accuracy": index / 10.0}
+
+        def train_giant(index, product):
+            together.append(index)
+            t = torch.tensor([1.0])
+            dist.all_reduce(t)                              # every rank is here: a collective completes
+            return {"accuracy": 0.5, "ranks_present": int(t.item())}
+
+        results = pop.run_population(products, train_one, costs, rank=rank, world_size=world, dist=dist, train_giant=train_giant)
+        queue.put((rank, alone, together, results))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_giants_are_trained_by_all_ranks_together_and_the_rest_is_sharded():
+    assert pop.pick_giants([1.0, 30.0, 1.0, 2.0, 1.0, 1.0], 2) == [1]
+    assert pop.pick_giants([1.0] * 8, 2) == [] and pop.pick_giants([5.0, 1.0], 1) == []
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_giant_worker, args=(r, 2, port, queue)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted(queue.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, alone0, together0, res0), (_, alone1, together1, res1) = got
+    assert together0 == together1 == [1]                            # both ranks trained the giant, together
+    assert sorted(alone0 + alone1) == [0, 2, 3, 4, 5] and not set(alone0) & set(alone1)
+    assert res0 == res1 and [i for i, _ in res0] == list(range(6))
+    assert res0[1][1]["ranks_present"] == 2 and res0[1][1]["data_parallel"] == 2
