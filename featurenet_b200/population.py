@@ -154,6 +154,10 @@ def run_population(products, train_one, costs, rank=0, world_size=1, dist=None, 
             result.setdefault("seconds", time.time() - started)
             result["rank"], result["data_parallel"] = -1, world_size
         giant_results.append((index, result))
+    if giants:
+        box = [giant_results]
+        dist.broadcast_object_list(box, src=0)       # every rank keeps rank 0's record: identical result lists everywhere
+        giant_results = box[0]
     rest = [i for i in range(len(costs)) if i not in set(giants)]
     mine = assign_lpt_subset(rest, costs, world_size)[rank]
 
