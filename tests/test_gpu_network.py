@@ -333,3 +333,43 @@ def test_driver_sequence_of_full_py_on_the_engine(monkeypatch, tmp_path):
                 assert gen.model.to_kerasvector().to_vector()[1][1][3] == gen.flops
     assert len(report) == 6
     TensorflowGenerator.dataset = None
+
+
+def test_one_generation_of_the_evolution_loop_on_the_engine(monkeypatch, tmp_path):
+    """The call sequence of full_evolution.py:166-262 for one generation (the file itself does not travel to the GPU
+    box): a trained base model -> survivors -> breed -> generate_mutant (parse_blocks of the dumped blocks + mutate) ->
+    TensorflowGenerator.build(model, dataset) -> TensorflowGenerator.train(model, epochs, default_batchsize, dataset) ->
+    to_kerasvector().to_vector(); individuals kept from the previous generation (accuracy != 0) are not retrained."""
+    import copy
+    import json
+    from model.keras_model import KerasFeatureModel
+    TensorflowGenerator = _small_cifar(monkeypatch)
+    np.random.seed(5)
+    import random
+    random.seed(5)
+    with contextlib.redirect_stdout(io.StringIO()):
+        base = TensorflowGenerator("lenet5", 1, "cifar", data_augmentation=False)      # :229 model_name = "lenet5"
+        assert base.params and base.model.accuracy > 0
+        population = [base.model]
+        mutants = []
+        for parent in population:                                                       # evolve(), :166-181
+            for _ in range(3):
+                individual = parent.breed(population[0])
+                blocks = copy.deepcopy(individual.dump_blocks())                         # generate_mutant(), :108-123
+                mutant = KerasFeatureModel.parse_blocks({"blocks": blocks["blocks"]})
+                mutant.mutate(0.1)
+                mutants.append(mutant)
+        trained = 0
+        for model in population + mutants:                                              # :243-262
+            if model.accuracy == 0:
+                keras_model = TensorflowGenerator.build(model, "cifar")
+                if keras_model:
+                    TensorflowGenerator.train(model, 1, TensorflowGenerator.default_batchsize, "cifar", data_augmentation=False,
+                                              save_path=str(tmp_path / ("e1_%s" % model._name)))
+                    trained += 1
+                    assert 0.0 <= model.accuracy <= 1.0 and model.nb_params > 0
+            vect = model.to_kerasvector().to_vector()
+            json.dumps(vect)                                                            # what the driver logs per model
+    assert trained >= 1, "at least one mutant must be a buildable network"
+    assert population[0].accuracy == base.accuracy                                      # the survivor was not retrained
+    TensorflowGenerator.dataset = None
