@@ -161,3 +161,24 @@ def test_lenet5_end_of_training_accuracy_band():
     assert np.mean(accs_o) > 0.15, "the task must be learnable for a band to mean anything: %r" % accs_o
     assert abs(np.mean(accs_e) - np.mean(accs_o)) <= 0.01, (accs_e, accs_o)
     assert max(abs(a - b) for a, b in zip(accs_e, accs_o)) <= 0.03, (accs_e, accs_o)
+
+
+@pytest.mark.parametrize("name", sorted(CANDIDATES))
+def test_no_launch_reads_what_no_launch_of_the_step_wrote(name, monkeypatch):
+    """FNET_POISON=1 fills every activation, gradient and workspace buffer with NaN at allocation: a launch that reads a
+    buffer no earlier launch of the step wrote (a gradient nobody produced -- round 1's dropped cell branches left the
+    convolutions training on whatever the allocator handed out) turns the loss or a weight into NaN."""
+    from featurenet_b200.optimizers import Adam
+    monkeypatch.setenv("FNET_POISON", "1")
+    net = CANDIDATES[name]()
+    rng = np.random.default_rng(3)
+    net.compile(loss="categorical_crossentropy", metrics=["accuracy"], optimizer=Adam(lr=1e-3))
+    eng = net._need_engine()
+    assert eng.poison
+    x = rng.random((300, 32, 32, 3)).astype(np.float32)
+    y = np.eye(10, dtype=np.float32)[rng.integers(0, 10, 300)]
+    hist = net.fit(x, y, batch_size=128, epochs=2, validation_data=(x[:100], y[:100]))
+    assert all(np.isfinite(v) for key in ("loss", "val_loss", "acc", "val_acc") for v in hist.history[key]), hist.history
+    assert all(np.isfinite(w).all() for w in eng.get_weights())
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(eng.grads).all())
