@@ -16,7 +16,10 @@ bool strided_pointwise_ok(const ConvGeom &g) {
     static const int mode = env_switch("FNET_STRIDED_POINTWISE", 1);     // 0 disables (A/B measurements)
     // from 16 input channels on: below that the copy of sub(x) costs a launch that the GEMM does not win back
     // (3 -> 24 on 32x32, stride 2: 15.4 -> 17.3 us forward, 16.0 -> 19.9 us filter gradient with the extra launch)
-    return mode && g.C >= 16 && g.kh == 1 && g.kw == 1 && (g.sh > 1 || g.sw > 1) && g.pt == 0 && g.pl == 0 &&
+    // ... and from half a million input elements on: a layer smaller than that is one launch either way, and the copy
+    // would be a second one (the deep 2x1 / 1x1 layers of the sampled products: 128 pixels x 96..768 channels)
+    return mode && g.C >= 16 && (long long)g.B * g.H * g.W * g.C >= (1LL << 19) && g.kh == 1 && g.kw == 1 &&
+           (g.sh > 1 || g.sw > 1) && g.pt == 0 && g.pl == 0 &&
            (long long)g.B * g.H * g.W * g.C < 0x7fffffffLL && (long long)g.B * g.Ho * g.Wo * g.C < 0x7fffffffLL;
 }
 
