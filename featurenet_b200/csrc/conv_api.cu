@@ -65,6 +65,7 @@ int conv_fwd(const ConvGeom &g, int math_in, int act, const float *x, const floa
         return rc;
     }
     if (skinny_supported(g, 0, bias != nullptr)) rc = skinny_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
+    else if (dconv_supported(g, math, 0)) rc = dconv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
     else if (tma_gemm_supported(g, math, 0)) rc = tma_gemm_fwd(g, math, act, x, w, bias, y, s);
     else if (math != FNET_MATH_FP32 && tc_supported(g, math, 0)) rc = tc_conv_fwd(g, math, act, x, w, bias, y, ws, ws_bytes, s);
     else rc = simt_conv_fwd(g, act, x, w, bias, y, ws, ws_bytes, s);
@@ -98,6 +99,7 @@ int conv_dgrad(const ConvGeom &g, int math_in, const float *dz, const float *w, 
         int rc = conv_dgrad(gd, math_in, dz, w, t, DxEpilogue{0, 0, nullptr}, reinterpret_cast<char *>(ws) + t_bytes, ws_bytes - t_bytes, s);
         return rc == FNET_OK ? col2im_scatter(g, t, dx, ep, s) : rc;
     }
+    if (dconv_supported(g, math, 1)) return dconv_dgrad(g, math, dz, w, dx, ep, ws, ws_bytes, s);
     if (tma_gemm_supported(g, math, 1)) return tma_gemm_dgrad(g, math, dz, w, dx, ep, s);
     if (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) return tc_conv_dgrad(g, math, dz, w, dx, ep, ws, ws_bytes, s);
     return simt_conv_dgrad(g, dz, w, dx, ep, ws, ws_bytes, s);
@@ -113,7 +115,7 @@ static int dgrad_on_tensor_core(const ConvGeom &g, int math_in) {
     // population's candidates spent 5 % of their steps in separate 7 us act_bwd launches)
     if ((long long)g.B * g.H * g.W * g.C < (1LL << 22)) return 0;
     if (skinny_supported(g, 1, false) || col2im_t_bytes(g)) return 0;
-    if (tma_gemm_supported(g, math, 1)) return 1;
+    if (dconv_supported(g, math, 1) || tma_gemm_supported(g, math, 1)) return 1;
     return (math != FNET_MATH_FP32 && tc_supported(g, math, 1)) ? 1 : 0;
 }
 
@@ -158,6 +160,7 @@ size_t fnet_conv2d_workspace_bytes(const fnet_conv2d_desc *d) {
     if (d->math != FNET_MATH_FP32) {
         const int tensor_math = d->math == FNET_MATH_AUTO ? FNET_MATH_TF32X3 : d->math;     // covers whatever AUTO resolves to
         need = max_sz(need, max_sz(tc_conv_workspace(g, tensor_math), tma_gemm_workspace(g, tensor_math)));
+        need = max_sz(need, max_sz(dconv_workspace(g, FNET_MATH_TF32X3), dconv_workspace(g, FNET_MATH_TF32)));
     }
     if (size_t t_bytes = col2im_t_bytes(g)) {
         ConvGeom gd = dense_geom((long long)g.B * g.Ho * g.Wo, (long long)g.kh * g.kw * g.C, g.K);

@@ -102,6 +102,16 @@ __device__ __forceinline__ void tg_bar_arrive(uint64_t *bar) {
 __device__ __forceinline__ void tg_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(tg_smem(bar)) : "memory");
 }
+// one lane of a converged warp (the same one every time)
+__device__ __forceinline__ bool tg_elect() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "elect.sync _|P, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tg_tma_2d(uint32_t dst, const CUtensorMap *map, uint64_t *bar, int c_inner, int c_outer) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(tg_smem(bar)), "r"(c_inner), "r"(c_outer)
@@ -252,30 +262,35 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // instruction descriptor: D fp32, A / B tf32, A K-major, B as the problem says, N = BN, M = 128
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (B_MN ? (1u << 16) : 0u) | ((uint32_t)(BN >> 3) << 17) |
-                                   ((uint32_t)(TG_BM >> 4) << 24);
-            int stage = 0, it = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-                const int acc = it & 1;
-                tg_bar_wait(&acc_empty[acc], (uint32_t)(((it >> 1) & 1) ^ 1));      // the epilogue has drained this accumulator
+        // The whole warp walks the loop (warp-uniform control flow: addresses and descriptors stay in uniform registers)
+        // and one elected lane issues the MMAs.  Issued from inside `if (lane == 0)`, every tcgen05.mma was wrapped in
+        // a divergence-serialising loop with its descriptors rebuilt in vector registers and moved over (R2UR): about
+        // twenty dependent instructions of a lone warp per MMA -- more than a 128 x 64 x 8 MMA takes to execute.
+        // instruction descriptor: D fp32, A / B tf32, A K-major, B as the problem says, N = BN, M = 128
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (B_MN ? (1u << 16) : 0u) | ((uint32_t)(BN >> 3) << 17) |
+                               ((uint32_t)(TG_BM >> 4) << 24);
+        const bool leader = tg_elect();
+        // descriptors of stage 0; a stage further is stage_bytes / 16 more in the start-address field, the tails operand_bytes / 16
+        const uint64_t da0 = tg_desc_k(smem_base), db0 = B_MN ? tg_desc_mn(smem_base + TG_A_BYTES) : tg_desc_k(smem_base + TG_A_BYTES);
+        const uint32_t stage_step = (uint32_t)stage_bytes >> 4, tail = (uint32_t)operand_bytes >> 4;
+        constexpr int badv = B_MN ? 64 : 2;                  // 16-byte units per 8 k: two 4-row atoms / 32 bytes along the row
+        int stage = 0, it = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+            const int acc = it & 1;
+            tg_bar_wait(&acc_empty[acc], (uint32_t)(((it >> 1) & 1) ^ 1));      // the epilogue has drained this accumulator
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t d = tmem + acc * acc_stride;
+            for (int kt = 0; kt < KT; ++kt) {
+                tg_bar_wait(X3 ? &split_bar[stage] : &full_bar[stage], phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t d = tmem + acc * acc_stride;
-                for (int kt = 0; kt < KT; ++kt) {
-                    tg_bar_wait(X3 ? &split_bar[stage] : &full_bar[stage], phase);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
-                    const uint64_t da = tg_desc_k(sa), db = B_MN ? tg_desc_mn(sb) : tg_desc_k(sb);
-                    const int badv = B_MN ? 64 : 2;          // 16-byte units per 8 k: two 4-row atoms / 32 bytes along the row
+                if (leader) {
+                    const uint64_t da = da0 + (uint64_t)((uint32_t)stage * stage_step), db = db0 + (uint64_t)((uint32_t)stage * stage_step);
                     if (X3) {
-                        const uint64_t la = tg_desc_k(sa + operand_bytes);
-                        const uint64_t lb = B_MN ? tg_desc_mn(sb + operand_bytes) : tg_desc_k(sb + operand_bytes);
 #pragma unroll
                         for (int j = 0; j < TG_BK / 8; ++j) {
-                            tg_mma(d, la + (uint64_t)(2 * j), db + (uint64_t)(badv * j), idesc, (kt > 0 || j > 0) ? 1u : 0u);
-                            tg_mma(d, da + (uint64_t)(2 * j), lb + (uint64_t)(badv * j), idesc, 1u);
+                            tg_mma(d, da + (uint64_t)(tail + 2 * j), db + (uint64_t)(badv * j), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+                            tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(tail + badv * j), idesc, 1u);
                             tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(badv * j), idesc, 1u);      // the large term last
                         }
                     } else {
@@ -284,11 +299,12 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                             tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(badv * j), idesc, (kt > 0 || j > 0) ? 1u : 0u);
                     }
                     tg_commit(&empty_bar[stage]);
-                    if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
-                tg_commit(&acc_full[acc]);
+                if (++stage == stages) { stage = 0; phase ^= 1; }
             }
+            if (leader) tg_commit(&acc_full[acc]);
         }
+        __syncwarp();
     } else {
         const int quad = warp & 3;                            // the TMEM lane quadrant this warp may read
         float *xp = xpose[warp - 2];
@@ -438,39 +454,44 @@ tma_wgrad_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             if (++stage == stages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {
+            // all lanes walk the loop, one elected lane issues (see tma_gemm_kernel)
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) |
                                    ((uint32_t)(TG_BM >> 4) << 24);
             const uint32_t idesc_ones = idesc & ~(1u << 15);  // the all-ones tile is read K-major (any layout of ones is ones)
             const uint64_t d_ones = tg_desc_k(tg_smem(ones));
+            const bool leader = tg_elect();
+            const uint64_t da0 = tg_desc_mn(smem_base), db0 = tg_desc_mn(smem_base + TG_A_BYTES);
+            const uint32_t stage_step = (uint32_t)stage_bytes >> 4, tail = (uint32_t)operand_bytes >> 4;
             int stage = 0;
             uint32_t phase = 0;
             for (int kt = kt_begin; kt < kt_end; ++kt) {
                 tg_bar_wait(X3 ? &split_bar[stage] : &full_bar[stage], phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
-                const uint64_t da = tg_desc_mn(sa), db = tg_desc_mn(sb);
-                const uint64_t la = tg_desc_mn(sa + operand_bytes), lb = tg_desc_mn(sb + operand_bytes);   // X3 only
+                if (leader) {
+                    const uint64_t da = da0 + (uint64_t)((uint32_t)stage * stage_step), db = db0 + (uint64_t)((uint32_t)stage * stage_step);
 #pragma unroll
-                for (int j = 0; j < TG_BK / 8; ++j) {
-                    const uint32_t accumulate = (kt > kt_begin || j > 0) ? 1u : 0u;
-                    if (X3) {
-                        tg_mma(tmem, la + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, accumulate);
-                        tg_mma(tmem, da + (uint64_t)(64 * j), lb + (uint64_t)(64 * j), idesc, 1u);
-                        tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, 1u);
-                        if (with_bias) {
-                            tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), lb + (uint64_t)(64 * j), idesc_ones, accumulate);
-                            tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(64 * j), idesc_ones, 1u);
+                    for (int j = 0; j < TG_BK / 8; ++j) {
+                        const uint32_t accumulate = (kt > kt_begin || j > 0) ? 1u : 0u;
+                        if (X3) {
+                            tg_mma(tmem, da + (uint64_t)(tail + 64 * j), db + (uint64_t)(64 * j), idesc, accumulate);
+                            tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(tail + 64 * j), idesc, 1u);
+                            tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, 1u);
+                            if (with_bias) {
+                                tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(tail + 64 * j), idesc_ones, accumulate);
+                                tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(64 * j), idesc_ones, 1u);
+                            }
+                        } else {
+                            tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, accumulate);
+                            if (with_bias) tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(64 * j), idesc_ones, accumulate);
                         }
-                    } else {
-                        tg_mma(tmem, da + (uint64_t)(64 * j), db + (uint64_t)(64 * j), idesc, accumulate);
-                        if (with_bias) tg_mma(tmem + bias_col, d_ones + (uint64_t)(2 * j), db + (uint64_t)(64 * j), idesc_ones, accumulate);
                     }
+                    tg_commit(&empty_bar[stage]);
                 }
-                tg_commit(&empty_bar[stage]);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
-            tg_commit(&acc_full);
+            if (leader) tg_commit(&acc_full);
+            __syncwarp();
         }
     } else {
         const int quad = warp & 3;

@@ -81,6 +81,14 @@ size_t strided_sub_bytes(const ConvGeom &g);                 // bytes of sub(x) 
 int strided_subsample(const ConvGeom &g, const float *x, float *x_sub, cudaStream_t stream);
 int strided_scatter(const ConvGeom &g, const float *dx_sub, float *dx, DxEpilogue ep, cudaStream_t stream);
 
+// k x k stride-1 convolutions, forward and data gradient, with the input tile resident in shared memory (dconv.cu)
+bool dconv_supported(const ConvGeom &g, int math, int product);
+size_t dconv_workspace(const ConvGeom &g, int math);
+int dconv_fwd(const ConvGeom &g, int math, int act, const float *x, const float *w, const float *bias, float *y, void *ws,
+              size_t ws_bytes, cudaStream_t stream);
+int dconv_dgrad(const ConvGeom &g, int math, const float *dz, const float *w, float *dx, DxEpilogue ep, void *ws, size_t ws_bytes,
+                cudaStream_t stream);
+
 int run_softmax_rows(int64_t rows, int64_t cols, const float *x, float *y, cudaStream_t stream);
 
 }  // namespace fnet

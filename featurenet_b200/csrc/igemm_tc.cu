@@ -63,6 +63,17 @@ __device__ __forceinline__ float to_tf32(float v) {
     return __uint_as_float(r);
 }
 
+// one lane of a converged warp (the same one every time)
+__device__ __forceinline__ bool tc_elect() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "elect.sync _|P, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // byte offset of element (row, kc) of a [rows x 32 fp32] K-major tile
 __device__ __forceinline__ uint32_t tile_offset(int row, int kc, int layout) {
     if (layout == 0)   // SWIZZLE_128B: 8-row x 128-byte atoms, 16-byte chunks XOR-ed with the row
@@ -326,7 +337,9 @@ __global__ void __launch_bounds__(TC_THREADS, 2) tc_igemm_kernel(P p, int M, int
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
         }
-        if (tid == 0) {
+        // one elected lane of the (converged) first warp issues: under `if (tid == 0)` the compiler wraps every
+        // tcgen05.mma in a divergence-serialising loop and rebuilds its descriptors in vector registers (see gemm_tma.cu)
+        if (warp == 0 && tc_elect()) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + TC_A_BYTES;
             uint64_t da = A_MN ? make_smem_desc_mn(sa, 4) : make_smem_desc(sa, layout);

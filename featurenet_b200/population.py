@@ -249,6 +249,7 @@ def train_product(product, dataset, epochs, batch_size, product_features=None, d
     import helpers
     import os
     helpers.clear_failure()
+    phases = None
     if data_parallel:
         # every rank of the process group makes this call together: the engine cuts each batch into per-rank slices
         previous = os.environ.get("FNET_DP")
@@ -270,6 +271,8 @@ def train_product(product, dataset, epochs, batch_size, product_features=None, d
                                   batch_size=batch_size, product_features=product_features, clear_memory=False)
         network = getattr(getattr(gen, "model", None), "model", None)
         if network is not None:
+            engine = getattr(network, "_engine", None)
+            phases = dict(engine.timing) if engine is not None else None
             network.release()
     else:
         with contextlib.redirect_stdout(io.StringIO()):
@@ -277,6 +280,8 @@ def train_product(product, dataset, epochs, batch_size, product_features=None, d
                                       batch_size=batch_size, product_features=product_features)
     out = {"accuracy": float(gen.accuracy), "params": int(gen.params), "training_time": float(gen.training_time),
            "history": (list(gen.history[0]), list(gen.history[1])), "valid": bool(gen.params)}
+    if phases:                        # host seconds of this candidate's engine (alloc, capture, train, eval)
+        out["phases"] = phases
     failure = helpers.last_failure()
     if failure:                       # the runner swallowed it (reference convention); the scheduler wants to know
         out["oom"], out["error"] = True, failure

@@ -27,6 +27,8 @@ def main():
     ap.add_argument("--train", type=int, default=10000)
     ap.add_argument("--test", type=int, default=2000)
     ap.add_argument("--no-budget", action="store_true")
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--per-candidate", action="store_true")
     args = ap.parse_args()
     import torch
     from featurenet_b200 import population as pop, synth
@@ -46,14 +48,14 @@ def main():
         with quiet():
             net = KerasFeatureModel.parse_feature_model(copy.deepcopy(product)).build((32, 32, 3), 10)
         costs.append(pop.estimate_cost(net, args.train, args.test, 1) if net else 1.0)
-        mem.append(pop.estimate_bytes(net, 128, args.test) if net else 0)
+        mem.append(pop.estimate_bytes(net, args.batch, args.test) if net else 0)
         buildable += 1 if net else 0
     budget = None if args.no_budget else pop.MemoryBudget(int(0.8 * torch.cuda.mem_get_info()[0]))
     print("buildable %d of %d, estimated bytes %.1f GB total, largest %.1f GB" % (buildable, len(formatted), sum(mem) / 2**30, max(mem) / 2**30))
 
     def train_one(index, item):
         product, original = pop.copy_product(item)
-        return pop.train_product(product, "cifar", epochs=1, batch_size=128, product_features=original, shared_gpu=args.resident > 1)
+        return pop.train_product(product, "cifar", epochs=1, batch_size=args.batch, product_features=original, shared_gpu=args.resident > 1 or args.per_candidate)
 
     reference = None
     bad = 0
@@ -75,6 +77,18 @@ def main():
             bad += 1
         print("pass %2d: valid %d/%d retried %d same_accuracies %s %.2fs peak_mem %.1f GB %s" % (
             n, valid, buildable, retried, same, dt, torch.cuda.max_memory_allocated() / 2**30, json.dumps(errors)[:600]), flush=True)
+        ph = [r.get("phases") for _, r in res if r.get("phases")]
+        if ph:
+            keys = sorted(ph[0])
+            print("   engine seconds summed over candidates: " + ", ".join("%s %.2f" % (k, sum(p[k] for p in ph)) for k in keys)
+                  + ", training_time %.2f" % sum(r.get("training_time", 0) for _, r in res), flush=True)
+        if args.per_candidate and n == args.passes - 1:
+            for i, r in res:
+                p = r.get("phases")
+                if p:
+                    print("   candidate %2d params %8d train %.3fs (%d steps, %.0f us/step) eval %.3fs (%d steps, %.0f us/step)" % (
+                        i, r["params"], p["train_s"], p["train_steps"], 1e6 * (p["train_s"] - p["capture_s"]) / max(p["train_steps"], 1),
+                        p["eval_s"], p["eval_steps"], 1e6 * p["eval_s"] / max(p["eval_steps"], 1)), flush=True)
         if not same:
             print("   differ (index, now, pass 0):", differ[:12], flush=True)
     print("RESULT bad_passes=%d of %d" % (bad, args.passes))
