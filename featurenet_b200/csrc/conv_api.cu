@@ -32,14 +32,26 @@ int check_math(int math, const char *what) {
 static int resolve_math(const ConvGeom &g, int math, int product) {
     if (math != FNET_MATH_AUTO) return math;
     const long long taps = (long long)g.kh * g.kw;
+    // pixels of the product: the rows of the forward / data-gradient GEMM, the reduction of the filter gradient
+    const long long pixels = product == 1 ? (long long)g.B * g.H * g.W : (long long)g.B * g.Ho * g.Wo;
     bool tensor;
     if (product == 2) {
         // 1x1 layers from 16 input channels on reach the TMA-fed filter gradient (24 -> 192 on 262 144 pixels: 112 us against
         // 188 us for the FFMA kernel); the 32-row bound is for the gathered kernels, whose A tile is mostly padding below it
         tensor = g.K >= 24 && (taps * g.C >= 32 || (taps == 1 && g.C >= 16 && !(g.C & 3) && !(g.K & 3)));
+        // the deep cells of a sampled candidate: a few thousand pixels at most.  The tensor-core kernels' fixed costs
+        // (TMEM, barriers, the split pass, a separate reduce) are then the whole launch (scripts/conv_sweep.py, warm L2:
+        // 192 -> 24 on 4096 pixels 24.4 vs 13.9 us, on 2048 pixels 23.6 vs 11.2 us, 192 -> 1536 on 256 pixels 22.7 vs 14.7 us)
+        // ... unless the product is large anyway (192 -> 1536 on 4096 pixels, 1.2 G multiply-adds: 80 vs 92 us)
+        if (pixels <= 4096 && pixels * taps * g.C * g.K <= (1LL << 27)) tensor = false;
     } else {
         const long long n = product == 0 ? g.K : g.C, kg = taps * (product == 0 ? g.C : g.K);
         tensor = (n >= 32 && kg >= 8) || (n >= 16 && kg >= 128) || (n >= 8 && kg >= 1024);
+        // few rows, a narrow output and a short reduction: FFMA (same sweep; data gradients 192 -> 24 on 1024 pixels 16.1 vs
+        // 9.9 us, 768 -> 96 on 128 pixels 24.6 vs 13.5 us; forward 192 -> 24 on 2048 pixels 13.9 vs 11.6 us).  Wide outputs
+        // (192 columns from 24) and long reductions (1536) stay on the tensor cores: 11.8 vs 14.7 us, 28.3 vs 34.0 us.
+        if (product == 1 && pixels <= 8192 && n <= 96 && kg <= 1024) tensor = false;
+        if (product == 0 && pixels <= 4096 && n <= 32 && kg <= 1024) tensor = false;
     }
     return tensor ? FNET_MATH_TF32X3 : FNET_MATH_FP32;
 }

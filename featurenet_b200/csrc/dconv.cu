@@ -71,6 +71,7 @@ struct DcParams {
     int slab_stage_bytes, slab_stages, b_stage_bytes, b_part_bytes, b_stages;
     int total_positions, tiles, tmem_cols;
     DcDiv div_wp, div_hs, div_kc;
+    long long *trace;       // FNET_DC_TRACE: per-role clock64 stamps of CTA 0 (development aid), else null
 };
 
 __device__ __forceinline__ uint32_t dc_smem(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -134,6 +135,14 @@ __device__ __forceinline__ void dc_hi_lo(float x, float &hi, float &lo) {
     const uint32_t h = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
     hi = __uint_as_float(h);
     lo = __uint_as_float((__float_as_uint(x - hi) + 0x1000u) & 0xffffe000u);
+}
+
+// development aid: CTA 0 writes (role, event, clock) triples; slot 0 of the buffer is the running count
+__device__ __forceinline__ void dc_stamp(const DcParams &p, int role, int event) {
+    if (p.trace && blockIdx.x == 0) {
+        const unsigned long long i = atomicAdd(reinterpret_cast<unsigned long long *>(p.trace), 1ull);
+        if (i < 4000) { p.trace[1 + 3 * i] = role; p.trace[2 + 3 * i] = event; p.trace[3 + 3 * i] = clock64(); }
+    }
 }
 
 // position q of the padded grid -> (image, padded row, padded column)
@@ -250,12 +259,16 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
         uint32_t sphase = 0, bphase = 0, b_lo = b0_lo;
         for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
             const int acc = it & 1;
+            if (leader) dc_stamp(p, 1, 3);
             dc_bar_wait(&acc_empty[acc], (uint32_t)(((it >> 1) & 1) ^ 1));
+            if (leader) dc_stamp(p, 1, 4);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t d = tmem + acc * acc_stride;
             uint32_t accumulate = 0;
             for (int chunk = 0; chunk < p.chunks; ++chunk) {
+                if (leader) dc_stamp(p, 1, 0);
                 dc_bar_wait(&slab_full[ss], sphase);
+                if (leader) dc_stamp(p, 1, 1);
                 uint32_t a_row = slab0_lo + (uint32_t)ss * slab_stride;         // + 16 bytes per position of the tap's shift
                 int s = 0;
                 for (int tap = 0; tap < p.taps; ++tap) {
@@ -279,7 +292,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
                     if (++bs == p.b_stages) { bs = 0; bphase ^= 1; b_lo = b0_lo; }
                     if (++s == p.kw) { s = 0; a_row += (uint32_t)p.Wp; }
                 }
-                if (leader) dc_commit(&slab_empty[ss]);
+                if (leader) { dc_commit(&slab_empty[ss]); dc_stamp(p, 1, 2); }
                 if (++ss == p.slab_stages) { ss = 0; sphase ^= 1; }
             }
             if (leader) dc_commit(&acc_full[acc]);
@@ -297,7 +310,9 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
                 dc_decode(p, (uint32_t)tile * DC_BM + quad * 32 + lane, img, hh, ww);
                 mypix = (img < p.B && hh < p.Ho && ww < p.Wo) ? (img * p.Ho + hh) * p.Wo + ww : -1;
             }
+            if (e == 0 && lane == 0) dc_stamp(p, 2, 0);
             dc_bar_wait(&acc_full[acc], (uint32_t)((it >> 1) & 1));
+            if (e == 0 && lane == 0) dc_stamp(p, 2, 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             for (int c0 = half * 32; c0 < p.BN; c0 += 64) {
                 uint32_t v[32];
@@ -371,6 +386,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) dc_bar_arrive(&acc_empty[acc]);
+            if (e == 0 && lane == 0) dc_stamp(p, 2, 2);
         }
     } else {
         // thread t owns one 16-byte channel column (kc = t % KC; KC is 2, 4, 6 or 8 and divides the 192 loaders) and the
@@ -405,7 +421,9 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
         request(blockIdx.x, 0);
         for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
             for (int chunk = 0; chunk < p.chunks; ++chunk) {
+                if (t == 0) dc_stamp(p, 3, 0);
                 dc_bar_wait(&slab_empty[ss], phase ^ 1);
+                if (t == 0) dc_stamp(p, 3, 1);
                 uint8_t *col = slabs + ss * p.slab_stage_bytes + kc * p.pitch;
 #pragma unroll
                 for (int u = 0; u < DC_LOAD_DEPTH; ++u) {
@@ -427,6 +445,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy stores -> the tensor core's reads
                 __syncwarp();
                 if (lane == 0) dc_bar_arrive(&slab_full[ss]);
+                if (t == 0) dc_stamp(p, 3, 2);
                 if (++ss == p.slab_stages) { ss = 0; phase ^= 1; }
                 if (chunk + 1 < p.chunks) request(tile, chunk + 1);
                 else request(tile + (int)gridDim.x, 0);
@@ -557,6 +576,12 @@ static int dc_run(const ConvGeom &g, DcPlan &t, const float *w, void *ws, size_t
                p.taps, p.chunks, p.CK, p.KC, p.BN, p.Ci, p.N, p.b_stage_bytes / 4, p.b_part_bytes / 4);
     const unsigned grid = (unsigned)(p.tiles < kNumSMs ? p.tiles : kNumSMs);
     cudaError_t e = cudaSuccess;
+    p.trace = nullptr;
+    static const char *trace_path = getenv("FNET_DC_TRACE");   // development aid: dump CTA 0's role timeline of every launch
+    if (trace_path) {
+        cudaMalloc(&p.trace, (1 + 3 * 4000) * sizeof(long long));
+        cudaMemsetAsync(p.trace, 0, (1 + 3 * 4000) * sizeof(long long), stream);
+    }
 #define FNET_DC_LAUNCH(KS)                                                                                        \
     case KS: {                                                                                                    \
         static std::atomic<uint64_t> configured{0}; /* one mask per instantiation, one bit per device */          \
@@ -567,6 +592,18 @@ static int dc_run(const ConvGeom &g, DcPlan &t, const float *w, void *ws, size_t
     switch (p.CK >> 3) { FNET_DC_LAUNCH(1) FNET_DC_LAUNCH(2) FNET_DC_LAUNCH(3) default: FNET_DC_LAUNCH(4) }
 #undef FNET_DC_LAUNCH
     if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
+    if (trace_path) {
+        static long long host[1 + 3 * 4000];
+        cudaStreamSynchronize(stream);
+        cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost);
+        cudaFree(p.trace);
+        if (FILE *f = fopen(trace_path, "w")) {
+            fprintf(f, "# %s tiles %d chunks %d taps %d slab_stages %d b_stages %d\n", what, p.tiles, p.chunks, p.taps, p.slab_stages, p.b_stages);
+            const long long n = host[0] < 4000 ? host[0] : 4000;
+            for (long long i = 0; i < n; ++i) fprintf(f, "%lld %lld %lld\n", host[1 + 3 * i], host[2 + 3 * i], host[3 + 3 * i]);
+            fclose(f);
+        }
+    }
     return check_launch(what);
 }
 
