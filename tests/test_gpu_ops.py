@@ -275,7 +275,11 @@ def test_depthwise_forward_backward(L, xs, k, s, act):
                                     ((2, 8, 8, 4), (1, 1), (2, 2)), ((1, 5, 5, 70), (3, 2), (1, 2)),
                                     # channels % 4 == 0: the four-channels-per-thread kernels
                                     ((5, 16, 16, 32), (2, 2), (1, 1)), ((3, 10, 14, 24), (3, 3), (2, 2)),
-                                    ((2, 6, 5, 8), (3, 3), (1, 1))])
+                                    ((2, 6, 5, 8), (3, 3), (1, 1)),
+                                    # the strip kernels (2x2 / 3x3, stride 1 / 2): odd extents, ragged last strips
+                                    ((4, 13, 9, 16), (2, 2), (2, 2)), ((2, 17, 19, 4), (3, 3), (1, 1)),
+                                    ((3, 12, 10, 20), (2, 2), (1, 1)), ((2, 15, 15, 8), (3, 3), (2, 2)),
+                                    ((2, 3, 2, 8), (3, 3), (1, 1)), ((2, 5, 1, 4), (2, 2), (2, 2))])
 def test_pooling(L, xs, k, s):
     from featurenet_b200 import lib as fl
     rng = np.random.default_rng(xs[1] + 31 * k[0])
