@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(256, 2) dw_strip_kernel(int batch, int hs, int
 }
 
 static bool dw_strip_ok(const fnet_conv2d_desc *d) {
-    return d->stride_h == 1 && d->stride_w == 1 && d->dil_h == 1 && d->dil_w == 1 && d->kh * d->kw <= 9 && d->kh * d->kw > 1;
+    return d->stride_h == 1 && d->stride_w == 1 && d->dil_h == 1 && d->dil_w == 1 && d->kh * d->kw <= 25 && d->kh * d->kw > 1;
 }
 
 template <int KH, int KW>
@@ -443,6 +443,94 @@ __global__ void __launch_bounds__(kDwChan * kDwPix) dw_wgrad_partial_vec4_kernel
     }
 }
 
+// Stride 1, four channels per thread, FOUR neighbouring output pixels of one row per trip: a row of the window is
+// loaded once for the four pixels (KH * (3 + KW) loads of x instead of 4 * KH * KW: 18 instead of 36 for 3x3) and the
+// pixel index is decoded once per strip.  Same CTA shape, partial layout and reduction as the kernels above.
+template <int KH, int KW>
+__global__ void __launch_bounds__(kDwChan * kDwPix) dw_wgrad_strip_kernel(fnet_conv2d_desc d, int strips_per_split,
+                                                                         const float4 *__restrict__ x,
+                                                                         const float4 *__restrict__ dz,
+                                                                         float4 *__restrict__ partial, int rows) {
+    pdl_prologue();
+    constexpr int WP = 4, NCOL = WP - 1 + KW, TAPS = KH * KW;
+    __shared__ float4 red[kDwChan * kDwPix + 64];
+    const int lanes_q = blockDim.x, lanes_p = blockDim.y, pitch = lanes_q + 1;
+    const int quads = d.in_c >> 2;
+    const int q = blockIdx.x * lanes_q + threadIdx.x;
+    const int split = blockIdx.y;
+    const int strips_w = (d.out_w + WP - 1) / WP;
+    const int nstrips = d.batch * d.out_h * strips_w;
+    const int s0 = split * strips_per_split, s1 = min(s0 + strips_per_split, nstrips);
+    float4 acc[TAPS + 1];
+#pragma unroll
+    for (int t = 0; t <= TAPS; ++t) acc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (q < quads) {
+        for (int si = s0 + threadIdx.y; si < s1; si += lanes_p) {
+            const int ws_ = si % strips_w, t2 = si / strips_w;
+            const int ho = t2 % d.out_h, b = t2 / d.out_h;
+            const int wo0 = ws_ * WP, w0 = wo0 - d.pad_left, h0 = ho - d.pad_top;
+            const float4 *gp = dz + ((int64_t)(b * d.out_h + ho) * d.out_w + wo0) * quads + q;
+            float4 g[WP];
+#pragma unroll
+            for (int j = 0; j < WP; ++j) g[j] = wo0 + j < d.out_w ? __ldg(gp + j * quads) : make_float4(0.f, 0.f, 0.f, 0.f);
+            acc[TAPS].x += (g[0].x + g[1].x) + (g[2].x + g[3].x);      // bias row
+            acc[TAPS].y += (g[0].y + g[1].y) + (g[2].y + g[3].y);
+            acc[TAPS].z += (g[0].z + g[1].z) + (g[2].z + g[3].z);
+            acc[TAPS].w += (g[0].w + g[1].w) + (g[2].w + g[3].w);
+            const float4 *img = x + (int64_t)b * d.in_h * d.in_w * quads + q;
+#pragma unroll
+            for (int r = 0; r < KH; ++r) {
+                const int h = h0 + r;
+                if ((unsigned)h >= (unsigned)d.in_h) continue;
+                float4 xv[NCOL];
+#pragma unroll
+                for (int c = 0; c < NCOL; ++c) {
+                    const int w = w0 + c;
+                    const bool ok = (unsigned)w < (unsigned)d.in_w;
+                    xv[c] = __ldg(img + (h * d.in_w + (ok ? w : 0)) * quads);
+                    if (!ok) xv[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int s2 = 0; s2 < KW; ++s2) {
+#pragma unroll
+                    for (int j = 0; j < WP; ++j) {
+                        float4 &a = acc[r * KW + s2];
+                        a.x = fmaf(g[j].x, xv[j + s2].x, a.x);
+                        a.y = fmaf(g[j].y, xv[j + s2].y, a.y);
+                        a.z = fmaf(g[j].z, xv[j + s2].z, a.z);
+                        a.w = fmaf(g[j].w, xv[j + s2].w, a.w);
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int t = 0; t <= TAPS; ++t) {
+        if (t < rows) {
+            float4 v = acc[t];
+            for (int o = lanes_q; o < 32; o <<= 1) {
+                v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+                v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+                v.z += __shfl_xor_sync(0xffffffffu, v.z, o);
+                v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+            }
+            const int tid = threadIdx.y * lanes_q + threadIdx.x;
+            if ((tid & 31) < lanes_q) red[(tid >> 5) * pitch + (tid & 31)] = v;
+            __syncthreads();
+            if (threadIdx.y == 0 && q < quads) {
+                float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int j = 0; j < kDwChan * kDwPix / 32; ++j) {
+                    const float4 w8 = red[j * pitch + threadIdx.x];
+                    sum.x += w8.x; sum.y += w8.y; sum.z += w8.z; sum.w += w8.w;
+                }
+                partial[((int64_t)split * rows + t) * quads + q] = sum;
+            }
+            __syncthreads();
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) dw_wgrad_reduce_kernel(int splits, int rows, int taps, int C,
                                                               const float *__restrict__ partial, float *__restrict__ dw,
                                                               float *__restrict__ dbias) {
@@ -535,6 +623,9 @@ int fnet_dwconv2d_fwd(const fnet_conv2d_desc *d, const float *x, const float *w,
         else if (dw_strip_ok(d) && d->kh == 1 && d->kw == 3) dw_strip_launch<1, 3>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
         else if (dw_strip_ok(d) && d->kh == 3 && d->kw == 1) dw_strip_launch<3, 1>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
         else if (dw_strip_ok(d) && d->kh == 2 && d->kw == 2) dw_strip_launch<2, 2>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 5 && d->kw == 5) dw_strip_launch<5, 5>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 1 && d->kw == 5) dw_strip_launch<1, 5>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 5 && d->kw == 1) dw_strip_launch<5, 1>(d, false, x4, w4, b4, y4, act, 0, as_stream(stream));
         FNET_DW_FWD(1, 1); FNET_DW_FWD(1, 3); FNET_DW_FWD(3, 1); FNET_DW_FWD(3, 3); FNET_DW_FWD(1, 5); FNET_DW_FWD(5, 1);
         // up to nine taps; 5x5 measured slower unrolled (65 vs 44 us on 128 x 32 x 32 x 24) and keeps the loops
         else launch_pdl(dw_fwd_vec4_kernel, grid, dim3(256), 0, as_stream(stream), *d, x4, w4, b4, y4, act);
@@ -567,6 +658,9 @@ int fnet_dwconv2d_bwd_data(const fnet_conv2d_desc *d, const float *dz, const flo
         else if (dw_strip_ok(d) && d->kh == 1 && d->kw == 3) dw_strip_launch<1, 3>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
         else if (dw_strip_ok(d) && d->kh == 3 && d->kw == 1) dw_strip_launch<3, 1>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
         else if (dw_strip_ok(d) && d->kh == 2 && d->kw == 2) dw_strip_launch<2, 2>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 5 && d->kw == 5) dw_strip_launch<5, 5>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 1 && d->kw == 5) dw_strip_launch<1, 5>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
+        else if (dw_strip_ok(d) && d->kh == 5 && d->kw == 1) dw_strip_launch<5, 1>(d, true, g4, w4, nullptr, dx4, 0, accumulate, as_stream(stream));
         FNET_DW_DGRAD(1, 1); FNET_DW_DGRAD(1, 3); FNET_DW_DGRAD(3, 1); FNET_DW_DGRAD(3, 3); FNET_DW_DGRAD(1, 5); FNET_DW_DGRAD(5, 1);
         else launch_pdl(dw_dgrad_vec4_kernel, grid, dim3(256), 0, as_stream(stream), *d, g4, w4, dx4, accumulate);
 #undef FNET_DW_DGRAD
@@ -597,7 +691,22 @@ int fnet_dwconv2d_bwd_filter(const fnet_conv2d_desc *d, const float *x, const fl
     const int units = dw_wgrad_vec4(d) ? d->in_c / 4 : d->in_c;     // the split plan (workspace) follows the shape alone
     const int lanes_c = dw_chan_lanes(vec ? units : d->in_c);
     dim3 grid(ceil_div(vec ? units : d->in_c, lanes_c), splits), block(lanes_c, kDwChan * kDwPix / lanes_c);
-    if (vec) {
+    const bool strip = vec && d->stride_h == 1 && d->stride_w == 1 &&
+                       ((d->kh == 3 && d->kw == 3) || (d->kh == 1 && d->kw == 3) || (d->kh == 3 && d->kw == 1) || (d->kh == 2 && d->kw == 2) ||
+                        (d->kh == 5 && d->kw == 5));
+    if (strip) {
+        // the same number of CTAs per channel group, each over a share of the four-pixel strips
+        const float4 *x4 = reinterpret_cast<const float4 *>(x), *dz4 = reinterpret_cast<const float4 *>(dz);
+        float4 *p4 = reinterpret_cast<float4 *>(ws);
+        const int64_t nstrips = (int64_t)d->batch * d->out_h * ((d->out_w + 3) / 4);
+        const int strips_per_split = (int)ceil_div<int64_t>(nstrips, splits);
+        splits = (int)ceil_div<int64_t>(nstrips, strips_per_split);
+        grid.y = splits;
+#define FNET_DW_WSTRIP(KH_, KW_) \
+    if (d->kh == KH_ && d->kw == KW_) launch_pdl(dw_wgrad_strip_kernel<KH_, KW_>, dim3(grid), dim3(block), 0, as_stream(stream), *d, strips_per_split, x4, dz4, p4, rows)
+        FNET_DW_WSTRIP(3, 3); FNET_DW_WSTRIP(1, 3); FNET_DW_WSTRIP(3, 1); FNET_DW_WSTRIP(2, 2); FNET_DW_WSTRIP(5, 5);
+#undef FNET_DW_WSTRIP
+    } else if (vec) {
         const float4 *x4 = reinterpret_cast<const float4 *>(x), *dz4 = reinterpret_cast<const float4 *>(dz);
         float4 *p4 = reinterpret_cast<float4 *>(ws);
         if (taps + 1 <= 10)

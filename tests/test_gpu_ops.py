@@ -244,7 +244,10 @@ def test_workspace_too_small_is_an_error_not_a_crash(L):
                                         ((2, 9, 6, 20), (1, 5), (2, 1), "relu"), ((5, 4, 4, 4), (1, 1), (1, 1), None),
                                         # stride 1, up to nine taps: four destination pixels per thread (ragged strips, all tap shapes)
                                         ((2, 11, 9, 8), (3, 1), (1, 1), None), ((3, 6, 5, 12), (2, 2), (1, 1), "relu"),
-                                        ((2, 33, 31, 24), (3, 3), (1, 1), "tanh"), ((1, 3, 2, 4), (3, 3), (1, 1), None)])
+                                        ((2, 33, 31, 24), (3, 3), (1, 1), "tanh"), ((1, 3, 2, 4), (3, 3), (1, 1), None),
+                                        # 25 taps and 1 x 5 / 5 x 1 in strips (forward, data gradient and filter gradient)
+                                        ((3, 14, 13, 16), (5, 5), (1, 1), "relu"), ((2, 9, 11, 8), (1, 5), (1, 1), None),
+                                        ((2, 10, 7, 12), (5, 1), (1, 1), "tanh")])
 def test_depthwise_forward_backward(L, xs, k, s, act):
     from featurenet_b200 import lib as fl
     rng = np.random.default_rng(xs[1] * 13 + k[0])
