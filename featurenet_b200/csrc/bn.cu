@@ -23,7 +23,9 @@ struct BnShape {
 static BnShape bn_shape(int outer, int a, int inner) {
     BnShape s;
     s.outer = outer; s.a = a; s.inner = inner;
-    int want = ceil_div(2 * kNumSMs, a);
+    // eight 256-thread CTAs per SM: every thread has one 16-byte load in flight at a time, so the bytes in flight -- and the
+    // bandwidth -- are set by how many threads are resident (two CTAs per SM moved 1.3 TB/s on 25 MB)
+    int want = ceil_div(8 * kNumSMs, a);
     if (want > kBnMaxSplits) want = kBnMaxSplits;
     if (want > outer) want = outer;
     if (want < 1) want = 1;
