@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(256) dw_dgrad_vec4_fixed_kernel(fnet_conv2d_de
 // quads per output quad (18 loads for 3x3); a strip of four shares its window: per filter row k + 3 source loads and k
 // weight loads feed four outputs (6.75 loads per output quad for 3x3), all of a row's loads issued before the first FMA.
 template <int KH, int KW, int WP>
-__global__ void __launch_bounds__(256, 2) dw_strip_kernel(int batch, int hs, int ws_, int hd, int wd, int quads, int off_h, int off_w,
+__global__ void __launch_bounds__(256, 3) dw_strip_kernel(int batch, int hs, int ws_, int hd, int wd, int quads, int off_h, int off_w,
                                                        int flip, const float4 *__restrict__ src, const float4 *__restrict__ w,
                                                        const float4 *__restrict__ bias, float4 *dst, int act, int accumulate) {
     pdl_prologue();

@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(256) pool_bwd_vec4_kernel(fnet_pool2d_desc d, 
 constexpr int POOL_WP = 4;
 
 template <int KH, int KW, int S, bool MAX>
-__global__ void __launch_bounds__(256) pool_fwd_strip_kernel(fnet_pool2d_desc d, const float4 *__restrict__ x,
+__global__ void __launch_bounds__(256, 4) pool_fwd_strip_kernel(fnet_pool2d_desc d, const float4 *__restrict__ x,
                                                              float4 *__restrict__ y, uchar4 *__restrict__ argmax) {
     pdl_prologue();
     constexpr int WP = POOL_WP, NCOL = (WP - 1) * S + KW;
@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(256) pool_fwd_strip_kernel(fnet_pool2d_desc d,
 // backward: one thread gathers the gradient of WP = 4 neighbouring input pixels of one row; a row of dy (and of the
 // argmax bytes) that reaches the strip is loaded once for all four
 template <int KH, int KW, int S, bool MAX>
-__global__ void __launch_bounds__(256) pool_bwd_strip_kernel(fnet_pool2d_desc d, const float4 *__restrict__ dy,
+__global__ void __launch_bounds__(256, 4) pool_bwd_strip_kernel(fnet_pool2d_desc d, const float4 *__restrict__ dy,
                                                              const uchar4 *__restrict__ argmax, float4 *__restrict__ dx,
                                                              int accumulate) {
     pdl_prologue();
