@@ -41,6 +41,7 @@ FULL_CONVS = [
     ((128, 32, 32, 3), (1, 1), 6, (1, 1)),        # main_1block_nas product #4: 1x1 3 -> 6
     ((128, 32, 32, 32), (3, 3), 64, (1, 1)),      # keras template: (131 072, 64, 288)
     ((128, 32, 32, 64), (3, 3), 64, (2, 2)),      # stride-2 block conv, wide
+    ((128, 32, 32, 64), (3, 3), 64, (1, 1)),      # keras template's widest: two channel chunks of the resident-tile kernel
 ]
 
 
