@@ -171,7 +171,6 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     extern __shared__ uint8_t tg_smem_raw[];
     __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], split_bar[TG_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_holder;
-    __shared__ float xpose[4][32 * 33];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(tg_smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -307,32 +306,32 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         __syncwarp();
     } else {
         const int quad = warp & 3;                            // the TMEM lane quadrant this warp may read
-        float *xp = xpose[warp - 2];
         int it = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
             const int acc = it & 1;
             const int m0 = (tile / n_tiles) * TG_BM, n0 = (tile % n_tiles) * BN;
             tg_bar_wait(&acc_full[acc], (uint32_t)((it >> 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int m_first = m0 + quad * 32, count = min(32, M - m_first);
+            // tcgen05.ld.16x256b: 16 lanes x 8 columns per repeat, laid out like an MMA accumulator fragment (thread t: rows
+            // t / 4 and t / 4 + 8, columns 2 (t % 4) + {0, 1}).  The four lanes of a row then store one whole 32-byte sector
+            // and a warp instruction eight of them, straight from the registers: the transpose through shared memory (a
+            // quarter of the kernel's shared-memory traffic on wide outputs) is gone.
+            const int m_first = m0 + quad * 32;
             for (int c0 = 0; c0 < BN; c0 += 32) {
-                uint32_t v[32];
-                uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + acc * acc_stride + (uint32_t)c0;
-                asm volatile(
-                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                    : "r"(taddr));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                const int cols = N - (n0 + c0 + 2 * (lane & 3));          // columns that exist from this thread's first one on
 #pragma unroll
-                for (int j = 0; j < 32; ++j) xp[lane * 33 + j] = __uint_as_float(v[j]);      // thread = row
-                __syncwarp();
-                const int n = n0 + c0 + lane;                                                 // thread = column
-                if (n < N && count > 0) p.store_col(m_first, count, n, xp + lane, 33);
-                __syncwarp();
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t v[16];
+                    const uint32_t taddr = tmem + ((uint32_t)(quad * 32 + half * 16) << 16) + acc * acc_stride + (uint32_t)c0;
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                        : "r"(taddr));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const int m = m_first + half * 16 + (lane >> 2);
+                    if (cols > 0 && m < M) p.store_frag(m, true, m + 8 < M, n0 + c0 + 2 * (lane & 3), cols, v);
+                }
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
@@ -739,8 +738,9 @@ template <class P, bool X3>
 static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, const float *b, long long N, bool b_mn,
                         cudaStream_t stream, const char *what, const TgConv &cv = TgConv{}, int src_b = 0, int src_h = 0,
                         int src_w = 0, int src_c = 0, long long b_rows = 0) {
-    if ((reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(b) & 15)) {
-        set_error("%s: operands must be 16-byte aligned for the TMA path", what);
+    if ((reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(b) & 15) ||
+        ((reinterpret_cast<uintptr_t>(p.out_ptr()) | reinterpret_cast<uintptr_t>(p.out_aux_ptr())) & 7)) {
+        set_error("%s: operands must be 16-byte aligned (results 8-byte) for the TMA path", what);
         return FNET_ERR_ARG;
     }
     const int BN = tg_bn_for(N, ceil_div<long long>(M, TG_BM));

@@ -161,6 +161,33 @@ struct FwdProblem {
     __device__ bool has_pre() const { return false; }
     __device__ float pre(int, int) const { return 1.f; }
     __device__ void store_pre(int m, int n, float v, float) const { store(m, n, v); }
+    // A tcgen05.ld.16x256b.x4 fragment: thread t holds, for each of four 8-column blocks i, columns n + 8 i + {0, 1}
+    // (n already includes 2 * (t % 4)) of rows m and m + 8 (v[4 i + 0 .. 1] and v[4 i + 2 .. 3]).  Eight-byte stores:
+    // the four lanes of a row write one 32-byte sector, a warp instruction eight full sectors -- no trip through
+    // shared memory.  cols = columns that exist from n on; K % 2 == 0 and y 8-byte aligned.
+    __device__ void store_frag(int m, bool row_a, bool row_b, int n, int cols, const uint32_t (&v)[16]) const {
+        float2 bv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            bv[i] = (bias && 8 * i < cols) ? make_float2(__ldg(bias + n + 8 * i), __ldg(bias + n + 8 * i + 1)) : make_float2(0.f, 0.f);
+        float *qa = y + (long long)m * g.K + n, *qb = qa + 8LL * g.K;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (8 * i < cols) {
+                float2 a = make_float2(__uint_as_float(v[4 * i]) + bv[i].x, __uint_as_float(v[4 * i + 1]) + bv[i].y);
+                float2 b = make_float2(__uint_as_float(v[4 * i + 2]) + bv[i].x, __uint_as_float(v[4 * i + 3]) + bv[i].y);
+                if (act == FNET_ACT_RELU) {
+                    a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); b.x = fmaxf(b.x, 0.f); b.y = fmaxf(b.y, 0.f);
+                } else if (act != FNET_ACT_NONE) {
+                    a.x = act_apply(a.x, act); a.y = act_apply(a.y, act); b.x = act_apply(b.x, act); b.y = act_apply(b.y, act);
+                }
+                if (row_a) *reinterpret_cast<float2 *>(qa + 8 * i) = a;
+                if (row_b) *reinterpret_cast<float2 *>(qb + 8 * i) = b;
+            }
+        }
+    }
+    __host__ __device__ const void *out_ptr() const { return y; }
+    __host__ __device__ const void *out_aux_ptr() const { return nullptr; }
     // rows m .. m+count-1 of column n; src[r * src_stride] holds row r.  Bias and the activation switch are
     // taken out of the row loop (the tensor-core epilogue spends most of its instructions here).
     __device__ void store_col(int m, int count, int n, const float *src, int src_stride) const {
@@ -237,6 +264,42 @@ struct DgradProblem {
         if (accumulate) v += dx[at];
         dx[at] = v * act_grad(yv, act);
     }
+    // see FwdProblem::store_frag; every load (act'(y) multipliers, old values) before the first store
+    __device__ void store_frag(int m, bool row_a, bool row_b, int n, int cols, const uint32_t (&v)[16]) const {
+        float *qa = dx + (long long)m * g.C + n, *qb = qa + 8LL * g.C;
+        float2 ya[4], yb[4], oa[4], ob[4];
+        if (act) {
+            const float *pa = yact + (long long)m * g.C + n, *pb = pa + 8LL * g.C;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                ya[i] = (row_a && 8 * i < cols) ? __ldg(reinterpret_cast<const float2 *>(pa + 8 * i)) : make_float2(0.f, 0.f);
+                yb[i] = (row_b && 8 * i < cols) ? __ldg(reinterpret_cast<const float2 *>(pb + 8 * i)) : make_float2(0.f, 0.f);
+            }
+        }
+        if (accumulate) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                oa[i] = (row_a && 8 * i < cols) ? *reinterpret_cast<const float2 *>(qa + 8 * i) : make_float2(0.f, 0.f);
+                ob[i] = (row_b && 8 * i < cols) ? *reinterpret_cast<const float2 *>(qb + 8 * i) : make_float2(0.f, 0.f);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (8 * i < cols) {
+                float2 a = make_float2(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]));
+                float2 b = make_float2(__uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                if (accumulate) { a.x += oa[i].x; a.y += oa[i].y; b.x += ob[i].x; b.y += ob[i].y; }
+                if (act) {
+                    a.x *= act_grad(ya[i].x, act); a.y *= act_grad(ya[i].y, act);
+                    b.x *= act_grad(yb[i].x, act); b.y *= act_grad(yb[i].y, act);
+                }
+                if (row_a) *reinterpret_cast<float2 *>(qa + 8 * i) = a;
+                if (row_b) *reinterpret_cast<float2 *>(qb + 8 * i) = b;
+            }
+        }
+    }
+    __host__ __device__ const void *out_ptr() const { return dx; }
+    __host__ __device__ const void *out_aux_ptr() const { return act ? yact : nullptr; }
     __device__ void store_col(int m, int count, int n, const float *src, int src_stride) const {
         float *q = dx + (long long)m * g.C + n;
         const long long ld = g.C;
