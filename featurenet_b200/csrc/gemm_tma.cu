@@ -32,6 +32,8 @@ constexpr int TG_A_BYTES = TG_BM * TG_BK * 4;
 constexpr int TG_SPLITTERS = 256;                           // threads of the TF32x3 splitter warps (warps 6..13)
 constexpr int TG_THREADS_X3 = TG_THREADS + TG_SPLITTERS;
 constexpr int TG_SMEM_LIMIT = 209 * 1024;     // + 17 KB of static shared memory = the 227 KB a CTA may have
+constexpr int TG_SMEM_LIMIT_GEMM = 226 * 1024;       // tma_gemm_kernel keeps only its barriers in static shared memory
+constexpr int TG_STAGES_MAX = 8;                       // weights-resident mode: the stages carry A alone and are small
 
 // hi = x rounded to tf32 (nearest, ties away: what cvt.rna.tf32.f32 gives, in two integer instructions), lo = x - hi
 // rounded the same way: left to the tensor core, which truncates, the tails would carry a one-sided error of 2^-22 of
@@ -165,19 +167,31 @@ __device__ __forceinline__ uint64_t tg_desc_mn(uint32_t saddr) {
 template <class P, bool X3>
 __global__ void __launch_bounds__(X3 ? TG_THREADS_X3 : TG_THREADS, 1)
 tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, P p, int M, int N, int Kg,
-                int BN, int n_tiles, int total_tiles, int tmem_cols, int stages, TgConv cv) {
+                int BN, int n_tiles, int total_tiles, int tmem_cols, int stages, TgConv cv, int resident) {
     pdl_prologue();
     constexpr bool B_MN = !P::kBContigK;
     extern __shared__ uint8_t tg_smem_raw[];
-    __shared__ uint64_t full_bar[TG_STAGES], empty_bar[TG_STAGES], split_bar[TG_STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint64_t full_bar[TG_STAGES_MAX], empty_bar[TG_STAGES_MAX], split_bar[TG_STAGES_MAX], acc_full[2], acc_empty[2],
+        bres_full, bres_split;
     __shared__ uint32_t tmem_holder;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(tg_smem_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t smem_base = tg_smem(smem);
-    const int b_bytes = BN * TG_BK * 4, operand_bytes = TG_A_BYTES + b_bytes;      // what the TMA unit lands per stage
+    // Streaming mode: a stage = A tile + B tile (+ their tails).  Weights-resident mode (plain GEMMs whose whole B
+    // column block fits: K <= 64 into 256 columns, 24 / 192 channels into anything): the CTA keeps ONE column block, loads
+    // (and splits) its KT B tiles once, and the stages carry A alone -- a third of the bytes, so more of them are in
+    // flight; the per-tile re-load and re-split of the same weights is gone.
+    const int b_bytes = BN * TG_BK * 4;
+    const int operand_bytes = resident ? TG_A_BYTES : TG_A_BYTES + b_bytes;        // what the TMA unit lands per stage
     const int stage_bytes = X3 ? 2 * operand_bytes : operand_bytes;                // + the tails, same layout
     const int KT = cv.taps ? cv.taps * cv.chunks : (Kg + TG_BK - 1) / TG_BK;
+    const int bres_stage = X3 ? 2 * b_bytes : b_bytes;                              // resident B tile kt: heads, then tails
+    uint8_t *stage0 = smem + (resident ? KT * bres_stage : 0);                      // the resident tiles come first
+    const uint32_t stage0_addr = tg_smem(stage0);
+    // this CTA's tiles: streaming = every gridDim-th (m, n) tile; resident = every (gridDim / n_tiles)-th row block of one column block
+    const int tile_first = resident ? blockIdx.x / n_tiles : blockIdx.x, tile_step = resident ? gridDim.x / n_tiles : gridDim.x;
+    const int tile_end = resident ? total_tiles / n_tiles : total_tiles, cta_n0 = (blockIdx.x % n_tiles) * BN;
 
     if (threadIdx.x == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
@@ -191,6 +205,8 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 tg_bar_init(&split_bar[s], TG_SPLITTERS / 32);
             }
             for (int a = 0; a < 2; ++a) { tg_bar_init(&acc_full[a], 1); tg_bar_init(&acc_empty[a], 4); }
+            tg_bar_init(&bres_full, 1);
+            tg_bar_init(&bres_split, TG_SPLITTERS / 32);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
         __syncwarp();
@@ -205,13 +221,27 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const uint32_t tmem = tmem_holder;
     const uint32_t acc_stride = (uint32_t)tmem_cols / 2;      // column offset of the second accumulator
 
+    if (warp == 0 && resident && tile_first < tile_end) {
+        // the column block's weights, once: all k-tiles on one barrier
+        if (lane == 0) tg_bar_expect_tx(&bres_full, (uint32_t)(KT * b_bytes));
+        __syncwarp();
+        for (int kt = 0; kt < KT; ++kt) {
+            const uint32_t sb = smem_base + kt * bres_stage;
+            if (B_MN) {
+                if (lane >= 1 && lane <= BN / 32) tg_tma_2d(sb + (lane - 1) * 4096, &map_b, &bres_full, cta_n0 + 32 * (lane - 1), kt * TG_BK);
+            } else if (lane == 1) {
+                tg_tma_2d(sb, &map_b, &bres_full, kt * TG_BK, cta_n0);
+            }
+        }
+        __syncwarp();
+    }
     if (warp == 0) {
         // every lane issues at most one box per stage: a 4 KB box costs as much issue time as a 16 KB one, so the
         // MN-major operand (32 x 32 boxes) is spread over the lanes instead of being issued serially by one
         int stage = 0;
         uint32_t phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const int m0 = (tile / n_tiles) * TG_BM, n0 = (tile % n_tiles) * BN;
+        for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+            const int m0 = (resident ? tile : tile / n_tiles) * TG_BM, n0 = resident ? cta_n0 : (tile % n_tiles) * BN;
             int img = 0, row0 = 0;                            // convolution: the tile's first pixel is (img, row0, 0)
             if (cv.taps) {
                 img = m0 / (cv.H * cv.W);
@@ -220,7 +250,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             int tap = 0, chunk = 0, tr = 0, ts = 0;           // k-tile = (tap (tr, ts), 32-channel chunk)
             for (int kt = 0; kt < KT; ++kt) {
                 tg_bar_wait(&empty_bar[stage], phase ^ 1);
-                const uint32_t sa = smem_base + stage * stage_bytes, sb = sa + TG_A_BYTES;
+                const uint32_t sa = stage0_addr + stage * stage_bytes, sb = sa + TG_A_BYTES;
                 // first reduction index of this k-tile in the weight matrix / in the plain A matrix
                 const int kb = cv.taps ? tap * cv.tap_rows + chunk * TG_BK : kt * TG_BK;
                 if (lane == 0) {
@@ -231,7 +261,9 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     else
                         tg_tma_2d(sa, &map_a, &full_bar[stage], kt * TG_BK, m0);
                 }
-                if (B_MN) {                                   // forward: w [taps * C][K], boxes of 32 k-rows x 32 columns
+                if (resident) {
+                    // the weights are already here
+                } else if (B_MN) {                            // forward: w [taps * C][K], boxes of 32 k-rows x 32 columns
                     if (lane >= 1 && lane <= BN / 32)
                         tg_tma_2d(sb + (lane - 1) * 4096, &map_b, &full_bar[stage], n0 + 32 * (lane - 1), kb);
                 } else if (lane == 1) {                       // data gradient: w [taps * C][K] read as rows c, k along K
@@ -250,10 +282,18 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     } else if (X3 && warp >= 6) {
         int stage = 0;
         uint32_t phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        if (resident && tile_first < tile_end) {              // the resident weights: split once
+            tg_bar_wait(&bres_full, 0);
+            for (int kt = 0; kt < KT; ++kt)
+                tg_split_chunks(smem + kt * bres_stage, 0, b_bytes / 16, b_bytes, threadIdx.x - TG_THREADS, -1, 0);
+            tg_split_done();
+            __syncwarp();
+            if (lane == 0) tg_bar_arrive(&bres_split);
+        }
+        for (int tile = tile_first; tile < tile_end; tile += tile_step) {
             for (int kt = 0; kt < KT; ++kt) {
                 tg_bar_wait(&full_bar[stage], phase);
-                tg_split_chunks(smem + stage * stage_bytes, 0, operand_bytes / 16, operand_bytes, threadIdx.x - TG_THREADS, -1, 0);
+                tg_split_chunks(stage0 + stage * stage_bytes, 0, operand_bytes / 16, operand_bytes, threadIdx.x - TG_THREADS, -1, 0);
                 tg_split_done();
                 __syncwarp();
                 if (lane == 0) tg_bar_arrive(&split_bar[stage]);
@@ -270,12 +310,19 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                                ((uint32_t)(TG_BM >> 4) << 24);
         const bool leader = tg_elect();
         // descriptors of stage 0; a stage further is stage_bytes / 16 more in the start-address field, the tails operand_bytes / 16
-        const uint64_t da0 = tg_desc_k(smem_base), db0 = B_MN ? tg_desc_mn(smem_base + TG_A_BYTES) : tg_desc_k(smem_base + TG_A_BYTES);
+        // resident mode: B tile kt lives at kt * bres_stage from the start of shared memory, its tails b_bytes further
+        const uint32_t b_at = resident ? smem_base : stage0_addr + TG_A_BYTES;
+        const uint64_t da0 = tg_desc_k(stage0_addr), db0 = B_MN ? tg_desc_mn(b_at) : tg_desc_k(b_at);
         const uint32_t stage_step = (uint32_t)stage_bytes >> 4, tail = (uint32_t)operand_bytes >> 4;
+        const uint32_t b_step = resident ? (uint32_t)bres_stage >> 4 : stage_step, b_tail = resident ? (uint32_t)b_bytes >> 4 : tail;
         constexpr int badv = B_MN ? 64 : 2;                  // 16-byte units per 8 k: two 4-row atoms / 32 bytes along the row
         int stage = 0, it = 0;
         uint32_t phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        if (resident && tile_first < tile_end) {
+            tg_bar_wait(X3 ? &bres_split : &bres_full, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+        for (int tile = tile_first; tile < tile_end; tile += tile_step, ++it) {
             const int acc = it & 1;
             tg_bar_wait(&acc_empty[acc], (uint32_t)(((it >> 1) & 1) ^ 1));      // the epilogue has drained this accumulator
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -284,12 +331,13 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 tg_bar_wait(X3 ? &split_bar[stage] : &full_bar[stage], phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 if (leader) {
-                    const uint64_t da = da0 + (uint64_t)((uint32_t)stage * stage_step), db = db0 + (uint64_t)((uint32_t)stage * stage_step);
+                    const uint64_t da = da0 + (uint64_t)((uint32_t)stage * stage_step);
+                    const uint64_t db = db0 + (uint64_t)((uint32_t)(resident ? kt : stage) * b_step);
                     if (X3) {
 #pragma unroll
                         for (int j = 0; j < TG_BK / 8; ++j) {
                             tg_mma(d, da + (uint64_t)(tail + 2 * j), db + (uint64_t)(badv * j), idesc, (kt > 0 || j > 0) ? 1u : 0u);
-                            tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(tail + badv * j), idesc, 1u);
+                            tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(b_tail + badv * j), idesc, 1u);
                             tg_mma(d, da + (uint64_t)(2 * j), db + (uint64_t)(badv * j), idesc, 1u);      // the large term last
                         }
                     } else {
@@ -307,9 +355,9 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     } else {
         const int quad = warp & 3;                            // the TMEM lane quadrant this warp may read
         int it = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        for (int tile = tile_first; tile < tile_end; tile += tile_step, ++it) {
             const int acc = it & 1;
-            const int m0 = (tile / n_tiles) * TG_BM, n0 = (tile % n_tiles) * BN;
+            const int m0 = (resident ? tile : tile / n_tiles) * TG_BM, n0 = resident ? cta_n0 : (tile % n_tiles) * BN;
             tg_bar_wait(&acc_full[acc], (uint32_t)((it >> 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             // tcgen05.ld.16x256b: 16 lanes x 8 columns per repeat, laid out like an MMA accumulator fragment (thread t: rows
@@ -756,19 +804,35 @@ static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, c
     else ok = ok && make_map(&map_b, b, b_rows ? b_rows : N, Kg, BN, TG_BK, CU_TENSOR_MAP_SWIZZLE_128B);   // w [C][Kg]
     if (!ok) { set_error("%s: cuTensorMapEncodeTiled failed", what); return FNET_ERR_CUDA; }
     const int n_tiles = (int)ceil_div<long long>(N, BN);
-    const long long total = ceil_div<long long>(M, TG_BM) * n_tiles;
+    const long long m_tiles = ceil_div<long long>(M, TG_BM), total = m_tiles * n_tiles;
     int tmem_cols = 64;
     while (tmem_cols < 2 * BN) tmem_cols *= 2;
-    const int stages = tg_stages(BN, X3, TG_STAGES, 0);
-    const size_t smem = (size_t)stages * (X3 ? 2 : 1) * (TG_A_BYTES + BN * TG_BK * 4) + 1024;
+    // weights-resident mode (see the kernel): the whole column block of B stays in shared memory, the stages carry A alone
+    static const int resident_mode = env_switch("FNET_TMA_RESIDENT", 1);       // FNET_TMA_RESIDENT=0: A/B measurements
+    const long long KT = ceil_div<long long>(Kg, TG_BK), parts = X3 ? 2 : 1;
+    const long long b_region = KT * parts * BN * TG_BK * 4, a_stage = parts * TG_A_BYTES;
+    const bool resident = resident_mode && !cv.taps && n_tiles <= kNumSMs && m_tiles * n_tiles >= kNumSMs &&
+                          b_region + 3 * a_stage + 1024 <= TG_SMEM_LIMIT_GEMM;
+    int stages;
+    size_t smem;
+    unsigned grid;
+    if (resident) {
+        long long most = (TG_SMEM_LIMIT_GEMM - 1024 - b_region) / a_stage;
+        stages = (int)(most > TG_STAGES_MAX ? TG_STAGES_MAX : most);
+        smem = (size_t)(b_region + stages * a_stage + 1024);
+        grid = (unsigned)((kNumSMs / n_tiles) * n_tiles);        // every CTA owns one column block
+    } else {
+        stages = tg_stages(BN, X3, TG_STAGES, 0);
+        smem = (size_t)stages * (X3 ? 2 : 1) * (TG_A_BYTES + BN * TG_BK * 4) + 1024;
+        grid = (unsigned)(total < kNumSMs ? total : kNumSMs);
+    }
     static std::atomic<uint64_t> configured{0};              // one mask per instantiation, one bit per device
     {
-        cudaError_t e = allow_dynamic_smem(tma_gemm_kernel<P, X3>, TG_SMEM_LIMIT, configured);
+        cudaError_t e = allow_dynamic_smem(tma_gemm_kernel<P, X3>, TG_SMEM_LIMIT_GEMM, configured);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
     }
-    const unsigned grid = (unsigned)(total < kNumSMs ? total : kNumSMs);
     launch_pdl(tma_gemm_kernel<P, X3>, dim3(grid), dim3(X3 ? TG_THREADS_X3 : TG_THREADS), smem, stream, map_a, map_b, p, (int)M, (int)N, (int)Kg, BN,
-                                                              n_tiles, (int)total, tmem_cols, stages, cv);
+                                                              n_tiles, (int)total, tmem_cols, stages, cv, resident ? 1 : 0);
     return check_launch(what);
 }
 
