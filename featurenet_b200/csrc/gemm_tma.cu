@@ -8,9 +8,9 @@
 //                      cp.async.bulk.tensor.{2d,4d} for A (128 x 32) and B (BN x 32);
 //   warp 1 (one lane)  issues four tcgen05.mma.kind::tf32 per stage (twelve in TF32x3 mode) into one of two TMEM
 //                      accumulators and releases the stage (tcgen05.commit -> mbarrier);
-//   warps 2..5         epilogue: tcgen05.ld their TMEM lane quadrant, bias + activation, coalesced stores --
-//                      while the other accumulator is already being filled for the CTA's next tile;
-//   warps 6..13        TF32x3 only: split every landed stage into tf32 heads (in place) and tails (twin buffer).
+//   warps 2..9         epilogue (tma_gemm_kernel; 2..5 in the filter gradient): tcgen05.ld of their TMEM lane quadrant,
+//                      bias + activation, stores -- while the other accumulator is already being filled for the next tile;
+//   the next 8 warps   TF32x3 only: split every landed stage into tf32 heads (in place) and tails (twin buffer).
 //
 // One CTA per SM walks the output tiles (persistent), so barrier setup, TMEM allocation and descriptor
 // prefetch are paid once per SM instead of once per tile, and the epilogue of tile i overlaps the main loop
@@ -31,6 +31,9 @@ constexpr int TG_A_BYTES = TG_BM * TG_BK * 4;
 // so the two extra MMAs and the pass over shared memory hide behind the loads.
 constexpr int TG_SPLITTERS = 256;                           // threads of the TF32x3 splitter warps (warps 6..13)
 constexpr int TG_THREADS_X3 = TG_THREADS + TG_SPLITTERS;
+// tma_gemm_kernel: eight epilogue warps (two per TMEM lane quadrant, alternating 32-column groups) -- its epilogue works from
+// registers alone, and on wide outputs it is what the kernel waits for
+constexpr int TG_GEMM_THREADS = 64 + 256, TG_GEMM_THREADS_X3 = TG_GEMM_THREADS + TG_SPLITTERS;
 constexpr int TG_SMEM_LIMIT = 209 * 1024;     // + 17 KB of static shared memory = the 227 KB a CTA may have
 constexpr int TG_SMEM_LIMIT_GEMM = 226 * 1024;       // tma_gemm_kernel keeps only its barriers in static shared memory
 constexpr int TG_STAGES_MAX = 8;                       // weights-resident mode: the stages carry A alone and are small
@@ -165,7 +168,7 @@ __device__ __forceinline__ uint64_t tg_desc_mn(uint32_t saddr) {
 }
 
 template <class P, bool X3>
-__global__ void __launch_bounds__(X3 ? TG_THREADS_X3 : TG_THREADS, 1)
+__global__ void __launch_bounds__(X3 ? TG_GEMM_THREADS_X3 : TG_GEMM_THREADS, 1)
 tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, P p, int M, int N, int Kg,
                 int BN, int n_tiles, int total_tiles, int tmem_cols, int stages, TgConv cv, int resident) {
     pdl_prologue();
@@ -204,7 +207,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 tg_bar_init(&empty_bar[s], 1);
                 tg_bar_init(&split_bar[s], TG_SPLITTERS / 32);
             }
-            for (int a = 0; a < 2; ++a) { tg_bar_init(&acc_full[a], 1); tg_bar_init(&acc_empty[a], 4); }
+            for (int a = 0; a < 2; ++a) { tg_bar_init(&acc_full[a], 1); tg_bar_init(&acc_empty[a], (TG_GEMM_THREADS - 64) / 32); }
             tg_bar_init(&bres_full, 1);
             tg_bar_init(&bres_split, TG_SPLITTERS / 32);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -279,13 +282,13 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (X3 && warp >= 6) {
+    } else if (X3 && warp >= TG_GEMM_THREADS / 32) {
         int stage = 0;
         uint32_t phase = 0;
         if (resident && tile_first < tile_end) {              // the resident weights: split once
             tg_bar_wait(&bres_full, 0);
             for (int kt = 0; kt < KT; ++kt)
-                tg_split_chunks(smem + kt * bres_stage, 0, b_bytes / 16, b_bytes, threadIdx.x - TG_THREADS, -1, 0);
+                tg_split_chunks(smem + kt * bres_stage, 0, b_bytes / 16, b_bytes, threadIdx.x - TG_GEMM_THREADS, -1, 0);
             tg_split_done();
             __syncwarp();
             if (lane == 0) tg_bar_arrive(&bres_split);
@@ -293,7 +296,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         for (int tile = tile_first; tile < tile_end; tile += tile_step) {
             for (int kt = 0; kt < KT; ++kt) {
                 tg_bar_wait(&full_bar[stage], phase);
-                tg_split_chunks(stage0 + stage * stage_bytes, 0, operand_bytes / 16, operand_bytes, threadIdx.x - TG_THREADS, -1, 0);
+                tg_split_chunks(stage0 + stage * stage_bytes, 0, operand_bytes / 16, operand_bytes, threadIdx.x - TG_GEMM_THREADS, -1, 0);
                 tg_split_done();
                 __syncwarp();
                 if (lane == 0) tg_bar_arrive(&split_bar[stage]);
@@ -365,7 +368,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             // and a warp instruction eight of them, straight from the registers: the transpose through shared memory (a
             // quarter of the kernel's shared-memory traffic on wide outputs) is gone.
             const int m_first = m0 + quad * 32;
-            for (int c0 = 0; c0 < BN; c0 += 32) {
+            for (int c0 = ((warp - 2) >> 2) * 32; c0 < BN; c0 += 64) {
                 const int cols = N - (n0 + c0 + 2 * (lane & 3));          // columns that exist from this thread's first one on
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
@@ -831,7 +834,7 @@ static int tma_gemm_run(const P &p, const float *a, long long M, long long Kg, c
         cudaError_t e = allow_dynamic_smem(tma_gemm_kernel<P, X3>, TG_SMEM_LIMIT_GEMM, configured);
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return FNET_ERR_CUDA; }
     }
-    launch_pdl(tma_gemm_kernel<P, X3>, dim3(grid), dim3(X3 ? TG_THREADS_X3 : TG_THREADS), smem, stream, map_a, map_b, p, (int)M, (int)N, (int)Kg, BN,
+    launch_pdl(tma_gemm_kernel<P, X3>, dim3(grid), dim3(X3 ? TG_GEMM_THREADS_X3 : TG_GEMM_THREADS), smem, stream, map_a, map_b, p, (int)M, (int)N, (int)Kg, BN,
                                                               n_tiles, (int)total, tmem_cols, stages, cv, resident ? 1 : 0);
     return check_launch(what);
 }
