@@ -22,7 +22,7 @@
 //
 //   warp 0        B producer (cp.async.bulk + mbarrier), one lane
 //   warp 1        tcgen05.mma issue (one lane), TMEM allocation; two accumulators so the epilogue of tile i overlaps tile i+1
-//   warps 2..9    epilogue: tcgen05.ld, transpose through shared memory, bias / activation / dx epilogue, coalesced stores
+//   warps 2..9    epilogue: tcgen05.ld in the MMA fragment layout, bias / activation / dx epilogue, 32-byte-sector stores
 //   warps 10..15  slab loaders: 16-byte global loads, (split,) conflict-free 16-byte shared stores
 //
 // The filter gradient keeps its own kernels (gemm_tma.cu / igemm_tc.cu): its reduction runs over the pixels.
@@ -37,7 +37,6 @@ constexpr int DC_LOADERS = 32 * DC_LOAD_WARPS;
 constexpr int DC_SLAB_STAGES_MAX = 4, DC_B_STAGES_MAX = 4;
 constexpr int DC_LOAD_DEPTH = 12;
 constexpr int DC_SMEM_LIMIT = 224 * 1024;
-constexpr int DC_XPOSE_BYTES = DC_EPI_WARPS * 32 * 33 * 4;
 
 // n / d for n < 2^31 without a division: q = (umulhi(n, mul) + n) >> shr
 struct DcDiv {
@@ -207,7 +206,6 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(dc_smem_raw) + 127) & ~(uintptr_t)127);
     uint8_t *slabs = smem;
     uint8_t *bst = slabs + p.slab_stages * p.slab_stage_bytes;
-    float *xpose = reinterpret_cast<float *>(bst + p.b_stages * p.b_stage_bytes);
     const int slab_part = p.KC * p.pitch;                     // bytes of the head slab (the tails follow)
 
     if (warp == 1) {
@@ -299,87 +297,89 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
         }
         __syncwarp();
     } else if (warp < 2 + DC_EPI_WARPS) {
-        const int e = warp - 2, quad = warp & 3, half = e >> 2;          // TMEM lane quadrant = warp % 4; two warps share it
-        float *xp = xpose + e * 32 * 33;
+        // tcgen05.ld.16x256b: the accumulator arrives in the MMA fragment layout -- thread t holds rows t / 4 and t / 4 + 8 of a
+        // 16-lane half, columns 2 (t % 4) + {0, 1} of every 8-column block -- so the four lanes of a row store one 32-byte
+        // sector and a warp instruction eight of them, straight from the registers (no transpose through shared memory).
+        const int e = warp - 2, quad = warp & 3, group = e >> 2;         // TMEM lane quadrant = warp % 4; two warps share it
         int it = 0;
         for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
             const int acc = it & 1;
-            int mypix;                                                   // lane = row: the output pixel of this row, -1 = not an output
-            {
-                int img, hh, ww;
-                dc_decode(p, (uint32_t)tile * DC_BM + quad * 32 + lane, img, hh, ww);
-                mypix = (img < p.B && hh < p.Ho && ww < p.Wo) ? (img * p.Ho + hh) * p.Wo + ww : -1;
-            }
+            long long pix[2][2];                                         // [16-lane half][row, row + 8]: element offset of the pixel, -1 = not an output
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int r = 0; r < 2; ++r) {
+                    int img, hh, ww;
+                    dc_decode(p, (uint32_t)tile * DC_BM + quad * 32 + h * 16 + r * 8 + (lane >> 2), img, hh, ww);
+                    pix[h][r] = (img < p.B && hh < p.Ho && ww < p.Wo) ? (long long)((img * p.Ho + hh) * p.Wo + ww) * p.N : -1;
+                }
             if (e == 0 && lane == 0) dc_stamp(p, 2, 0);
             dc_bar_wait(&acc_full[acc], (uint32_t)((it >> 1) & 1));
             if (e == 0 && lane == 0) dc_stamp(p, 2, 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            for (int c0 = half * 32; c0 < p.BN; c0 += 64) {
-                uint32_t v[32];
-                const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + acc * acc_stride + (uint32_t)c0;
-                asm volatile(
-                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                    : "r"(taddr));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            for (int c0 = group * 32; c0 < p.BN; c0 += 64) {
+                const int n = c0 + 2 * (lane & 3), cols = p.N - n;       // this thread's first column, and how many exist from it on
 #pragma unroll
-                for (int j = 0; j < 32; ++j) xp[lane * 33 + j] = __uint_as_float(v[j]);      // thread = row
-                __syncwarp();
-                // thread = column from here on.  The 32 values of the column come back into registers BEFORE the first
-                // store, and the rows' pixels by shuffle: with either read from shared memory inside the store loop the
-                // compiler keeps loads and (generic-pointer) stores in program order, one memory latency per row.
-                float val[32];
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t v[16];
+                    const uint32_t taddr = tmem + ((uint32_t)(quad * 32 + h * 16) << 16) + acc * acc_stride + (uint32_t)c0;
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                        : "r"(taddr));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (cols <= 0) continue;
+                    const bool ra = pix[h][0] >= 0, rb = pix[h][1] >= 0;
+                    float *qa = p.out + (ra ? pix[h][0] : 0) + n, *qb = p.out + (rb ? pix[h][1] : 0) + n;
+                    if (!p.dgrad) {
 #pragma unroll
-                for (int r = 0; r < 32; ++r) val[r] = xp[r * 33 + lane];
-                __syncwarp();
-                const int n = c0 + lane;
-                const bool col_ok = n < p.N;
-                float *dst = p.out + n;
-                if (!p.dgrad) {
-                    const float bv = (p.bias && col_ok) ? __ldg(p.bias + n) : 0.f;
-                    if (p.act == FNET_ACT_NONE) {
-#pragma unroll
-                        for (int r = 0; r < 32; ++r) {
-                            const int px = __shfl_sync(0xffffffffu, mypix, r);
-                            if (px >= 0 && col_ok) dst[(size_t)px * p.N] = val[r] + bv;
-                        }
-                    } else if (p.act == FNET_ACT_RELU) {
-#pragma unroll
-                        for (int r = 0; r < 32; ++r) {
-                            const int px = __shfl_sync(0xffffffffu, mypix, r);
-                            if (px >= 0 && col_ok) dst[(size_t)px * p.N] = fmaxf(val[r] + bv, 0.f);
+                        for (int i = 0; i < 4; ++i) {
+                            if (8 * i < cols) {
+                                const float bx = p.bias ? __ldg(p.bias + n + 8 * i) : 0.f, by = p.bias ? __ldg(p.bias + n + 8 * i + 1) : 0.f;
+                                float2 a = make_float2(__uint_as_float(v[4 * i]) + bx, __uint_as_float(v[4 * i + 1]) + by);
+                                float2 b = make_float2(__uint_as_float(v[4 * i + 2]) + bx, __uint_as_float(v[4 * i + 3]) + by);
+                                if (p.act == FNET_ACT_RELU) {
+                                    a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); b.x = fmaxf(b.x, 0.f); b.y = fmaxf(b.y, 0.f);
+                                } else if (p.act != FNET_ACT_NONE) {
+                                    a.x = act_apply(a.x, p.act); a.y = act_apply(a.y, p.act); b.x = act_apply(b.x, p.act); b.y = act_apply(b.y, p.act);
+                                }
+                                if (ra) *reinterpret_cast<float2 *>(qa + 8 * i) = a;
+                                if (rb) *reinterpret_cast<float2 *>(qb + 8 * i) = b;
+                            }
                         }
                     } else {
+                        // multipliers act'(y) and old values first, all loads in flight at once
+                        float2 ya[4], yb[4], oa[4], ob[4];
+                        if (p.act) {
+                            const float *pa = p.yact + (ra ? pix[h][0] : 0) + n, *pb = p.yact + (rb ? pix[h][1] : 0) + n;
 #pragma unroll
-                        for (int r = 0; r < 32; ++r) {
-                            const int px = __shfl_sync(0xffffffffu, mypix, r);
-                            if (px >= 0 && col_ok) dst[(size_t)px * p.N] = act_apply(val[r] + bv, p.act);
+                            for (int i = 0; i < 4; ++i) {
+                                ya[i] = (ra && 8 * i < cols) ? __ldg(reinterpret_cast<const float2 *>(pa + 8 * i)) : make_float2(0.f, 0.f);
+                                yb[i] = (rb && 8 * i < cols) ? __ldg(reinterpret_cast<const float2 *>(pb + 8 * i)) : make_float2(0.f, 0.f);
+                            }
                         }
-                    }
-                } else if (p.act || p.accumulate) {
-                    // multipliers act'(y) and old values first, all loads in flight at once
-                    float yv[32];
+                        if (p.accumulate) {
 #pragma unroll
-                    for (int r = 0; r < 32; ++r) {
-                        const int px = __shfl_sync(0xffffffffu, mypix, r);
-                        const bool ok = px >= 0 && col_ok;
-                        yv[r] = (p.act && ok) ? __ldg(p.yact + (size_t)px * p.N + n) : 1.f;
-                        if (p.accumulate && ok) val[r] += dst[(size_t)px * p.N];
-                    }
+                            for (int i = 0; i < 4; ++i) {
+                                oa[i] = (ra && 8 * i < cols) ? *reinterpret_cast<const float2 *>(qa + 8 * i) : make_float2(0.f, 0.f);
+                                ob[i] = (rb && 8 * i < cols) ? *reinterpret_cast<const float2 *>(qb + 8 * i) : make_float2(0.f, 0.f);
+                            }
+                        }
 #pragma unroll
-                    for (int r = 0; r < 32; ++r) {
-                        const int px = __shfl_sync(0xffffffffu, mypix, r);
-                        if (px >= 0 && col_ok) dst[(size_t)px * p.N] = val[r] * act_grad(yv[r], p.act);
-                    }
-                } else {
-#pragma unroll
-                    for (int r = 0; r < 32; ++r) {
-                        const int px = __shfl_sync(0xffffffffu, mypix, r);
-                        if (px >= 0 && col_ok) dst[(size_t)px * p.N] = val[r];
+                        for (int i = 0; i < 4; ++i) {
+                            if (8 * i < cols) {
+                                float2 a = make_float2(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]));
+                                float2 b = make_float2(__uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                                if (p.accumulate) { a.x += oa[i].x; a.y += oa[i].y; b.x += ob[i].x; b.y += ob[i].y; }
+                                if (p.act) {
+                                    a.x *= act_grad(ya[i].x, p.act); a.y *= act_grad(ya[i].y, p.act);
+                                    b.x *= act_grad(yb[i].x, p.act); b.y *= act_grad(yb[i].y, p.act);
+                                }
+                                if (ra) *reinterpret_cast<float2 *>(qa + 8 * i) = a;
+                                if (rb) *reinterpret_cast<float2 *>(qb + 8 * i) = b;
+                            }
+                        }
                     }
                 }
             }
@@ -499,7 +499,7 @@ static DcPlan dc_plan(const ConvGeom &g, bool x3, int product) {
     p.tiles = (int)((positions + DC_BM - 1) / DC_BM);
     // shared memory: two slab stages and two B stages at least; then B up to three stages, then slabs up to four
     // (a slab stage is refilled while the other chunks are multiplied: more stages = more loads in flight), then B up to four
-    const long long work = (long long)p.chunks * p.taps, avail = DC_SMEM_LIMIT - 128 - DC_XPOSE_BYTES;
+    const long long work = (long long)p.chunks * p.taps, avail = DC_SMEM_LIMIT - 128;
     long long ns = 2, nb = work < 2 ? work : 2;
     if (ns * p.slab_stage_bytes + nb * p.b_stage_bytes > avail) return t;
     auto fits = [&](long long a, long long b) { return a * p.slab_stage_bytes + b * p.b_stage_bytes <= avail; };
@@ -508,7 +508,7 @@ static DcPlan dc_plan(const ConvGeom &g, bool x3, int product) {
     while (nb < work && nb < DC_B_STAGES_MAX && fits(ns, nb + 1)) ++nb;
     p.slab_stages = (int)ns;
     p.b_stages = (int)nb;
-    const long long fixed = 128 + ns * p.slab_stage_bytes + DC_XPOSE_BYTES, b_stages = nb;
+    const long long fixed = 128 + ns * p.slab_stage_bytes, b_stages = nb;
     p.tmem_cols = 64;
     while (p.tmem_cols < 2 * ((p.BN + 31) / 32 * 32)) p.tmem_cols *= 2;
     p.div_wp = dc_div((uint32_t)p.Wp);
@@ -565,8 +565,9 @@ static int dc_run(const ConvGeom &g, DcPlan &t, const float *w, void *ws, size_t
         set_error("%s: workspace of %zu bytes needed, %zu given", what, t.ws_bytes, ws_bytes);
         return FNET_ERR_WORKSPACE;
     }
-    if ((reinterpret_cast<uintptr_t>(p.in) & 15) || (reinterpret_cast<uintptr_t>(ws) & 15)) {
-        set_error("%s: operands must be 16-byte aligned", what);
+    if ((reinterpret_cast<uintptr_t>(p.in) & 15) || (reinterpret_cast<uintptr_t>(ws) & 15) ||
+        ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.yact)) & 7)) {
+        set_error("%s: operands must be 16-byte aligned (results 8-byte)", what);
         return FNET_ERR_ARG;
     }
     float *wprep = reinterpret_cast<float *>(ws);
