@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(512) dense_stream_fwd_kernel(int M, int K, int
             w_s[kk * (NMAX + 1) + n] = __ldg(w + (long long)kb * N + i);
         }
         __syncthreads();
-#pragma unroll 2
+#pragma unroll 4                                    // 16 loads of x in flight per thread: the kernel is bound by bytes in flight
         for (int kk = lane; kk < kc; kk += 32) {
             float xv[4];
 #pragma unroll
