@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(256) dense_stream_wgrad_kernel(int M, int K, i
             dz_s[r][n] = (r < rows && n < N) ? __ldg(dz + (long long)(m0 + r) * N + n) : 0.f;
         }
         __syncthreads();
-#pragma unroll 8
+#pragma unroll 16
         for (int r = 0; r < rows; ++r) {
             float xv = __ldg(xk + (long long)(m0 + r) * K);
 #pragma unroll
@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(256) dense_rows_dgrad_kernel(int M, int K, int
         for (int n = 0; n < NMAX; ++n) wr[n] = n < N ? __ldg(w + (long long)k * N + n) : 0.f;
         float *out = dx + (long long)m0 * K + k;
         const float *yin = yact ? yact + (long long)m0 * K + k : nullptr;
-        // four rows at a time, what the epilogue reads (y of the producing layer, the old dx) fetched BEFORE the sums:
+        // four rows at a time (eight measured slower: 205 -> 254 us), what the epilogue reads (y of the producing layer, the old dx) fetched BEFORE the sums:
         // with the loads inside the row loop every row waited for its own (ncu: 23 stall cycles per issue on the long
         // scoreboard, 289 us for the 524 288-wide head of the `keras` template against 98 us without an epilogue)
         if (!EPI) {                                           // plain store: the row loop as it always was
