@@ -398,22 +398,26 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dconv_kernel(const DcParams p) 
         const int kc = t % p.KC, j_first = t / p.KC, step = DC_LOADERS / p.KC;
         const int step_rows = step / p.Wp, step_cols = step - step_rows * p.Wp;
         float4 v[DC_LOAD_DEPTH];
+        // The element offset of the pixel is carried along with (img, hh, ww): a step of `step` positions is a handful of
+        // integer adds (no multiplication per load), a wrap of the padded column / row a constant correction.
+        const int d_col = step_cols * p.Ci, d_row = p.Wi * p.Ci, d_wrap_w = -p.Wp * p.Ci, d_wrap_h = -p.Hs * p.Wi * p.Ci + p.Hi * p.Wi * p.Ci;
         auto request = [&](int tile, int chunk) {
             int img, hh, ww;
             dc_decode(p, (uint32_t)tile * DC_BM + (uint32_t)j_first, img, hh, ww);
             const int c = chunk * p.CK + kc * 4;
             const bool c_ok = c < p.Ci && tile < p.tiles;
-            const float *src_c = p.in + c;
+            int off = ((img * p.Hi + (hh - p.pad_top)) * p.Wi + (ww - p.pad_left)) * p.Ci + c;   // < 2^31: dconv_supported
+            int row = hh - p.pad_top, cl = ww - p.pad_left;
 #pragma unroll
             for (int u = 0; u < DC_LOAD_DEPTH; ++u) {
                 v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                const int row = hh - p.pad_top, cl = ww - p.pad_left;
                 if (c_ok && j_first + u * step < p.slab_positions && img < p.B && (unsigned)row < (unsigned)p.Hi && (unsigned)cl < (unsigned)p.Wi)
-                    v[u] = __ldg(reinterpret_cast<const float4 *>(src_c + ((size_t)(img * p.Hi + row) * p.Wi + cl) * p.Ci));
-                ww += step_cols;
-                hh += step_rows;
-                if (ww >= p.Wp) { ww -= p.Wp; ++hh; }
-                while (hh >= p.Hs) { hh -= p.Hs; ++img; }
+                    v[u] = __ldg(reinterpret_cast<const float4 *>(p.in + off));
+                cl += step_cols;
+                row += step_rows;
+                off += d_col + step_rows * d_row;
+                if (cl >= p.Wp - p.pad_left) { cl -= p.Wp; ++row; off += d_wrap_w + d_row; }
+                while (row >= p.Hs - p.pad_top) { row -= p.Hs; ++img; off += d_wrap_h; }
             }
         };
         int ss = 0;
@@ -494,6 +498,7 @@ static DcPlan dc_plan(const ConvGeom &g, bool x3, int product) {
     p.b_stage_bytes = parts * p.b_part_bytes;
     const long long positions = (long long)p.B * p.Hs * p.Wp;
     if (positions + p.slab_positions + DC_BM >= 0x7fffffffLL || p.BN > 256) return t;
+    if (((long long)p.B + 1) * p.Hs * p.Wp * p.Ci >= 0x7fffffffLL) return t;      // the loaders carry 32-bit element offsets (with slack for the halo)
     if (p.slab_positions > DC_LOAD_DEPTH * (DC_LOADERS / p.KC)) return t;       // a slab must fit in the loaders' registers
     p.total_positions = (int)positions;
     p.tiles = (int)((positions + DC_BM - 1) / DC_BM);
