@@ -69,7 +69,7 @@ struct DcParams {
     int slab_positions, pitch;              // positions per slab, bytes between 16-byte columns (== 16 mod 128)
     int slab_stage_bytes, slab_stages, b_stage_bytes, b_part_bytes, b_stages;
     int total_positions, tiles, tmem_cols;
-    DcDiv div_wp, div_hs, div_kc;
+    DcDiv div_wp, div_hs;
     long long *trace;       // FNET_DC_TRACE: per-role clock64 stamps of CTA 0 (development aid), else null
 };
 
@@ -518,7 +518,6 @@ static DcPlan dc_plan(const ConvGeom &g, bool x3, int product) {
     while (p.tmem_cols < 2 * ((p.BN + 31) / 32 * 32)) p.tmem_cols *= 2;
     p.div_wp = dc_div((uint32_t)p.Wp);
     p.div_hs = dc_div((uint32_t)p.Hs);
-    p.div_kc = dc_div((uint32_t)p.KC);
     t.smem = (size_t)(fixed + b_stages * p.b_stage_bytes);
     t.ws_bytes = (size_t)p.chunks * p.taps * p.b_stage_bytes;
     t.ok = true;
