@@ -81,7 +81,9 @@ def test_conv2d_tf32_tensor_core(L, case_id, math, tol):
 @pytest.mark.parametrize("math,tol", MODES)
 @pytest.mark.parametrize("m,k,n", [(4096, 64, 512), (16384, 64, 512), (1000, 200, 33), (256, 4096, 100),
                                    # the TMA-fed persistent kernel (tf32 mode): ragged M, k tail, N > 256
-                                   (20001, 200, 96), (33000, 24, 192), (19000, 128, 260)])
+                                   (20001, 200, 96), (33000, 24, 192), (19000, 128, 260),
+                                   # weights-resident mode with three column blocks (147 CTAs, 49 per block), ragged rows and columns
+                                   (20001, 64, 650)])
 def test_dense_tf32_tensor_core(L, m, k, n, math, tol):
     from featurenet_b200 import lib as fl
     rng = np.random.default_rng(m + n)
