@@ -315,6 +315,71 @@ __global__ void __launch_bounds__(256) dense_rows_dgrad_kernel(int M, int K, int
     }
 }
 
+// The same for long heads (K % 4 == 0, 16-byte aligned tensors): FOUR consecutive inputs k per thread, so every access
+// to dx and to the producing layer's output is 16 bytes per lane (a warp instruction moves 512 bytes instead of 128);
+// the four weight rows (4 x NMAX registers) are read once for the 16 samples.  dx of a 524 288-wide head is 268 MB.
+template <int NMAX, bool EPI>
+__global__ void __launch_bounds__(256) dense_rows_dgrad4_kernel(int M, int K, int N, const float *__restrict__ dz,
+                                                                const float *__restrict__ w, float *__restrict__ dx,
+                                                                int accumulate, int act, const float *__restrict__ yact) {
+    pdl_prologue();
+    constexpr int ROWS = 16;
+    __shared__ __align__(16) float g_s[ROWS][NMAX];
+    const int m0 = blockIdx.y * ROWS, rows = min(ROWS, M - m0);
+    for (int i = threadIdx.x; i < ROWS * NMAX; i += 256) {
+        int r = i / NMAX, n = i - r * NMAX;
+        g_s[r][n] = (r < rows && n < N) ? __ldg(dz + (long long)(m0 + r) * N + n) : 0.f;
+    }
+    __syncthreads();
+    const int quads = K >> 2;
+    for (int kq = blockIdx.x * 256 + threadIdx.x; kq < quads; kq += gridDim.x * 256) {
+        float wr[4][NMAX];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n) wr[j][n] = n < N ? __ldg(w + (long long)(4 * kq + j) * N + n) : 0.f;
+        float4 *out = reinterpret_cast<float4 *>(dx + (long long)m0 * K) + kq;
+        const float4 *yin = yact ? reinterpret_cast<const float4 *>(yact + (long long)m0 * K) + kq : nullptr;
+        for (int r0 = 0; r0 < rows; r0 += 4) {
+            float4 yv[4], old[4];
+            if (EPI) {                                        // what the epilogue reads, fetched before the sums
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const bool in = r0 + u < rows;
+                    yv[u] = (act && in) ? __ldg(yin + (long long)(r0 + u) * quads) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    old[u] = (accumulate && in) ? out[(long long)(r0 + u) * quads] : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (r0 + u < rows) {
+                    float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int q = 0; q < NMAX / 4; ++q) {
+                        const float4 d = *reinterpret_cast<const float4 *>(&g_s[r0 + u][4 * q]);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            v[j] = fmaf(d.x, wr[j][4 * q], v[j]);
+                            v[j] = fmaf(d.y, wr[j][4 * q + 1], v[j]);
+                            v[j] = fmaf(d.z, wr[j][4 * q + 2], v[j]);
+                            v[j] = fmaf(d.w, wr[j][4 * q + 3], v[j]);
+                        }
+                    }
+                    float4 o = make_float4(v[0], v[1], v[2], v[3]);
+                    if (EPI) {
+                        o.x += old[u].x; o.y += old[u].y; o.z += old[u].z; o.w += old[u].w;
+                        if (act) {
+                            o.x *= act_grad(yv[u].x, act); o.y *= act_grad(yv[u].y, act);
+                            o.z *= act_grad(yv[u].z, act); o.w *= act_grad(yv[u].w, act);
+                        }
+                    }
+                    out[(long long)(r0 + u) * quads] = o;
+                }
+            }
+        }
+    }
+}
+
 static bool is_dense_geom(const ConvGeom &g) { return g.H == 1 && g.W == 1 && g.kh == 1 && g.kw == 1 && g.Ho == 1 && g.Wo == 1; }
 
 static int stream_fwd_blocks(const ConvGeom &g) {
@@ -800,6 +865,20 @@ int skinny_dgrad(const ConvGeom &g, const float *dz, const float *w, float *dx, 
         launch_pdl(pointwise_dgrad_kernel, dim3((unsigned)(blocks > cap ? cap : blocks)), dim3(256), (size_t)g.C * g.K * sizeof(float), s,
                    (int)M, g.C, g.K, dz, w, dx, ep.accumulate, ep.act, ep.y, vec_store);
         return check_launch("conv2d_bwd_data[pointwise]");
+    }
+    if (is_dense_geom(g) && g.C >= kStreamMinK && !(g.C & 3) &&
+        !((reinterpret_cast<uintptr_t>(dx) | (ep.act ? reinterpret_cast<uintptr_t>(ep.y) : 0)) & 15)) {
+        long long bx = ceil_div<long long>(g.C / 4, 256);
+        if (bx > 4096) bx = 4096;
+        dim3 grid((unsigned)bx, (unsigned)ceil_div<long long>(g.B, 16));
+#define FNET_CALL(NM)                                                                                                                  \
+    do {                                                                                                                                \
+        if (ep.accumulate || ep.act) launch_pdl(dense_rows_dgrad4_kernel<NM, true>, dim3(grid), dim3(256), 0, s, g.B, g.C, g.K, dz, w, dx, ep.accumulate, ep.act, ep.y); \
+        else launch_pdl(dense_rows_dgrad4_kernel<NM, false>, dim3(grid), dim3(256), 0, s, g.B, g.C, g.K, dz, w, dx, 0, 0, ep.y);           \
+    } while (0)
+        FNET_BY_COLUMNS(g.K, FNET_CALL);
+#undef FNET_CALL
+        return check_launch("dense_bwd_data[skinny, 4 k per thread]");
     }
     if (is_dense_geom(g)) {
         long long bx = ceil_div<long long>(g.C, 256);

@@ -167,6 +167,31 @@ def test_conv2d_bwd_data_with_the_producers_activation_derivative(L, case_id, ma
             assert_close(host(dxd), want, what="dgrad epilogue %s accumulate=%d" % (act, accumulate))
 
 
+@pytest.mark.parametrize("m,k,n", [(20, 300, 10), (37, 32772, 10), (5, 40000, 3), (130, 32768, 16), (9, 33001, 7)])
+def test_dense_bwd_data_with_the_producers_activation_derivative(L, m, k, n):
+    """fnet_dense_bwd_data_act on heads: dx = (accumulate ? dx + v : v) * act'(y); K >= 32 768 with K % 4 == 0 takes the
+    four-inputs-per-thread kernel, K % 4 != 0 the one-input-per-thread kernel."""
+    from featurenet_b200 import lib as fl
+    rng = np.random.default_rng(m + k + n)
+    w = rng.standard_normal((k, n)) / np.sqrt(n)
+    dz = rng.standard_normal((m, n))
+    x = rng.standard_normal((m, k))
+    dx, _, _ = ops.dense_bwd(x, w, dz)
+    before = rng.standard_normal((m, k))
+    ws = workspace(L.fnet_dense_workspace_bytes(m, k, n))
+    plain = torch.empty((m, k), device="cuda")
+    L.fnet_dense_bwd_data(m, k, n, fl.MATH["fp32"], ptr(dev(dz)), ptr(dev(w)), ptr(plain), 0, ptr(ws), ws.numel(), None)
+    assert_close(host(plain), dx, what="dense dgrad")
+    for act in ("relu", "tanh"):
+        y = ops.act_fwd(rng.standard_normal((m, k)), act)
+        for accumulate in (0, 1):
+            want = ops.act_bwd(y, dx + (before if accumulate else 0.0), act)
+            dxd = dev(before)
+            L.fnet_dense_bwd_data_act(m, k, n, fl.MATH["fp32"], ptr(dev(dz)), ptr(dev(w)), ptr(dxd), accumulate, fl.ACT[act], ptr(dev(y)),
+                                      ptr(ws), ws.numel(), None)
+            assert_close(host(dxd), want, what="dense dgrad epilogue %s accumulate=%d" % (act, accumulate))
+
+
 def test_bf16_mode_is_refused_not_aliased(L):
     """SURVEY.md names a bf16 mode; it is not built, and asking for it must fail loudly rather than run fp32 kernels."""
     from featurenet_b200 import lib as fl
