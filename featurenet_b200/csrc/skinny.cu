@@ -202,6 +202,68 @@ __global__ void __launch_bounds__(512) dense_stream_fwd_kernel(int M, int K, int
         }
 }
 
+// The same with FOUR consecutive k per lane (K % 4 == 0, x 16-byte aligned): x arrives 16 bytes per lane and sample, all
+// sixteen loads of a 512-row chunk (4 samples x 4 trips) in flight at once -- 256 bytes per thread instead of 64; the
+// kernel is bound by the bytes it keeps in flight.  The staged weights are transposed ([n][k], rows padded by four) so
+// that a lane reads its four k of one column as one conflict-free 16-byte load.
+template <int NMAX>
+__global__ void __launch_bounds__(512) dense_stream_fwd4_kernel(int M, int K, int N, const float *__restrict__ x,
+                                                                const float *__restrict__ w, float *__restrict__ partial) {
+    pdl_prologue();
+    constexpr int PITCH = kStreamChunk + 4;
+    __shared__ __align__(16) float w_t[NMAX * PITCH];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int m0 = blockIdx.y * kStreamRows + warp * 4;
+    float acc[4][NMAX];
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) acc[s][n] = 0.f;
+    const float4 *xr[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) xr[s] = reinterpret_cast<const float4 *>(x + (long long)min(m0 + s, M - 1) * K);   // clamped rows are never stored
+    for (int kb = blockIdx.x * kStreamChunk; kb < K; kb += gridDim.x * kStreamChunk) {
+        const int kc = min(kStreamChunk, K - kb);
+        __syncthreads();
+        for (int i = threadIdx.x; i < NMAX * PITCH; i += 512) w_t[i] = 0.f;          // padding columns and a short last chunk stay zero
+        __syncthreads();
+        for (int i = threadIdx.x; i < kc * N; i += 512) {
+            int kk = i / N, n = i - kk * N;
+            w_t[n * PITCH + kk] = __ldg(w + (long long)kb * N + i);
+        }
+        __syncthreads();
+        float4 xv[4][4];                                      // [trip][sample]
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int kk = 4 * lane + 128 * j;
+#pragma unroll
+            for (int s = 0; s < 4; ++s) xv[j][s] = kk < kc ? __ldg(xr[s] + ((kb + kk) >> 2)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int kk = 4 * lane + 128 * j;
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n) {
+                const float4 wv = *reinterpret_cast<const float4 *>(&w_t[n * PITCH + kk]);
+#pragma unroll
+                for (int s = 0; s < 4; ++s) {
+                    acc[s][n] = fmaf(xv[j][s].x, wv.x, acc[s][n]);
+                    acc[s][n] = fmaf(xv[j][s].y, wv.y, acc[s][n]);
+                    acc[s][n] = fmaf(xv[j][s].z, wv.z, acc[s][n]);
+                    acc[s][n] = fmaf(xv[j][s].w, wv.w, acc[s][n]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) {
+            float v = warp_sum(acc[s][n]);
+            if (lane == 0 && m0 + s < M && n < N) partial[((long long)blockIdx.x * M + m0 + s) * N + n] = v;
+        }
+}
+
 // filter gradient: one thread per weight row k, all samples in sequence -- no cross-thread reduction at all
 template <int NMAX>
 __global__ void __launch_bounds__(256) dense_stream_wgrad_kernel(int M, int K, int N, const float *__restrict__ x,
@@ -836,9 +898,15 @@ int skinny_fwd(const ConvGeom &g, int act, const float *x, const float *w, const
         }
         float *partial = reinterpret_cast<float *>(ws);
         dim3 grid(blocks, (unsigned)ceil_div<long long>(g.B, kStreamRows));
-#define FNET_CALL(NM) launch_pdl(dense_stream_fwd_kernel<NM>, dim3(grid), dim3(512), 0, s, g.B, g.C, g.K, x, w, partial)
-        FNET_BY_COLUMNS(g.K, FNET_CALL);
+        if (!(g.C & 3) && !(reinterpret_cast<uintptr_t>(x) & 15)) {
+#define FNET_CALL(NM) launch_pdl(dense_stream_fwd4_kernel<NM>, dim3(grid), dim3(512), 0, s, g.B, g.C, g.K, x, w, partial)
+            FNET_BY_COLUMNS(g.K, FNET_CALL);
 #undef FNET_CALL
+        } else {
+#define FNET_CALL(NM) launch_pdl(dense_stream_fwd_kernel<NM>, dim3(grid), dim3(512), 0, s, g.B, g.C, g.K, x, w, partial)
+            FNET_BY_COLUMNS(g.K, FNET_CALL);
+#undef FNET_CALL
+        }
         int rc = check_launch("dense_fwd[stream]");
         return rc ? rc : simt_reduce_fwd_partials(g, act, bias, y, blocks, partial, s);
     }
